@@ -1,0 +1,172 @@
+/*
+ * perseus_b200.h — C ABI of the B200-native perseus hot path (libperseus_b200.so).
+ *
+ * This is the drop-in boundary: everything the Python host side (perseus_b200/) does on the
+ * GPU goes through these entry points.  There are no torch types in the signatures — plain
+ * pointers, sizes and a cudaStream_t passed as void*.
+ *
+ * Conventions
+ *   - every function returns int: 0 = OK, non-zero = error; pb200_last_error() returns a
+ *     thread-local message for the last failing call on this thread.
+ *   - unless stated otherwise pointers are DEVICE pointers owned by the caller; calls are
+ *     asynchronous on `stream` and do no allocation after pb200_plan_create().
+ *   - there is no CPU fallback anywhere behind this ABI: with no usable sm_100 device the
+ *     compute entry points fail with PB200_ERR_NO_DEVICE.
+ *
+ * Reference interfaces replaced (paths relative to the reference checkout):
+ *   pb200_plan_create / _load_weights / _destroy
+ *        <- KeypointCNN.__init__               perseus/detector/models.py:9-32
+ *        <- checkpoint load                    perseus/detector/validate.py:92-98,
+ *                                              scripts/streaming.py:112-119
+ *   pb200_ingest
+ *        <- ZEDCamera.get_frame math           scripts/streaming.py:68-80
+ *        <- dataset u8 -> f32 conversion       perseus/detector/data.py:78,84-85
+ *        <- RGBD concat                        perseus/detector/validate.py:122-124,
+ *                                              perseus/detector/train.py:266-268
+ *        <- val-mode depth near/far clip       perseus/detector/augmentations.py:137-168
+ *   pb200_forward / pb200_forward_nchw_f32
+ *        <- KeypointCNN.forward                perseus/detector/models.py:34-40
+ *           (torchvision ResNet._forward_impl, BasicBlock.forward)
+ *        <- kornia denormalize_pixel_coordinates call sites
+ *                                              perseus/detector/validate.py:144-153,
+ *                                              scripts/streaming.py:129-131
+ *   pb200_factors_projection  <- KeypointProjectionFactor.error_func  perseus/smoother/factors.py:216-275
+ *   pb200_factors_dynamics    <- PoseDynamicsFactor.error_func        perseus/smoother/factors.py:54-142
+ *   pb200_factors_constvel    <- ConstantVelocityFactor.error_func    perseus/smoother/factors.py:160-171
+ */
+#ifndef PERSEUS_B200_H_
+#define PERSEUS_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PB200_VERSION 100 /* 0.1.0 */
+
+/* error codes */
+#define PB200_OK 0
+#define PB200_ERR_INVALID 1     /* bad argument / unsupported shape */
+#define PB200_ERR_CUDA 2        /* a CUDA runtime / driver call failed */
+#define PB200_ERR_NO_DEVICE 3   /* no sm_100 device: there is no CPU fallback */
+#define PB200_ERR_STATE 4       /* e.g. forward before load_weights */
+
+/* arithmetic of the conv backbone (the "precision ladder") */
+#define PB200_PREC_FP32 0   /* SIMT fp32 FFMA implicit GEMM: the <=1e-3 px parity mode          */
+#define PB200_PREC_BF16 1   /* tcgen05 kind::f16 bf16 x bf16 -> fp32 TMEM: the throughput mode   */
+#define PB200_PREC_BF16X3 2 /* split-bf16 (hi*hi + lo*hi + hi*lo) on tcgen05: tensor parity mode */
+
+typedef struct pb200_plan pb200_plan;
+typedef void* pb200_stream; /* cudaStream_t */
+
+int pb200_version(void);
+const char* pb200_last_error(void);
+
+/* ---- detector plan -------------------------------------------------------------------- */
+
+/* Creates the plan for KeypointCNN(n_keypoints, in_channels, H, W) on `device`:
+ * allocates packed-weight storage and fixes every buffer offset for up to max_batch frames. */
+int pb200_plan_create(pb200_plan** out, int device, int max_batch, int in_channels, int H, int W,
+                      int n_keypoints, int precision);
+void pb200_plan_destroy(pb200_plan* plan);
+
+/* Bytes of caller-owned device scratch pb200_forward* needs (for max_batch frames). */
+int pb200_plan_workspace_bytes(const pb200_plan* plan, size_t* bytes);
+/* Bytes of one ingested-frames buffer holding B frames in the plan's internal layout
+ * (zero-margined NHWC4: bf16 for the tcgen05 modes, fp32 for PB200_PREC_FP32). */
+int pb200_plan_frames_bytes(const pb200_plan* plan, int B, size_t* bytes);
+
+/* Consumes the reference state_dict: n HOST fp32 tensors in the reference layout (OIHW conv
+ * weights, BN weight/bias/running_mean/running_var, fc weight/bias), names without the
+ * "module." prefix ("resnet.conv1.weight", ...).  Folds eval-mode BatchNorm (eps 1e-5) into
+ * the conv weights and a per-channel bias, packs to the kernel layouts and uploads on `stream`
+ * (synchronises that stream before returning).  Unknown names (num_batches_tracked) are ignored;
+ * a missing tensor is PB200_ERR_INVALID. */
+int pb200_plan_load_weights(pb200_plan* plan, const float* const* tensors,
+                            const int64_t* const* shapes, const int* ndims,
+                            const char* const* names, int n, pb200_stream stream);
+
+/* Fused frame ingest -> plan-format frames buffer.
+ *   rgb         : uint8 [B][src_h][src_w][rgb_channels] (3 = RGB/BGR, 4 = RGBA/BGRA), row pitch
+ *                 rgb_pitch_bytes (>= src_w*rgb_channels), frame pitch rgb_pitch_bytes*src_h
+ *   bgr         : non-zero = channel order is B,G,R(,A)  (ZED camera; streaming.py:68-69)
+ *   depth       : float [B][src_h][src_w] or NULL (NULL -> depth channel written as 0)
+ *   depth_scale : multiplied into depth after NaN/Inf -> 0  (1/0.035 for metres, 1 for data units)
+ *   near_plane, far_plane : if far_plane > 0, zero the depth where 0.035*d < near (+jitter) or
+ *                 0.035*d > far (+jitter); jitter_or_null is float [B][2][H][W] (near, far).
+ *   The centred H x W window of the source is taken (streaming.py:79-80). */
+int pb200_ingest(const pb200_plan* plan, const uint8_t* rgb, int rgb_channels,
+                 int64_t rgb_pitch_bytes, int src_h, int src_w, int bgr, const float* depth,
+                 float depth_scale, float near_plane, float far_plane, const float* jitter_or_null,
+                 void* out_frames, int B, pb200_stream stream);
+
+/* Backbone + head + decode on ingested frames.
+ *   out_norm : float [B][2*n_keypoints] normalised coordinates (the reference forward() output)
+ *   out_px   : float [B][n_keypoints][2] pixel coordinates, or NULL */
+int pb200_forward(pb200_plan* plan, const void* frames, void* workspace, float* out_norm,
+                  float* out_px_or_null, int B, pb200_stream stream);
+
+/* Compatibility entry used by KeypointCNN.forward(x): x is float [B][C][H][W] (RGB in [0,1],
+ * depth in data units); fuses the NCHW->frames repack in front of pb200_forward. */
+int pb200_forward_nchw_f32(pb200_plan* plan, const float* x_nchw, void* workspace, float* out_norm,
+                           float* out_px_or_null, int B, pb200_stream stream);
+
+/* Per-kernel timing of one forward (CUDA events around every launch; synchronises).
+ * ms has room for pb200_plan_num_ops() floats. */
+int pb200_plan_num_ops(const pb200_plan* plan);
+const char* pb200_plan_op_name(const pb200_plan* plan, int i);
+/* algorithmic FLOPs (2*MAC, unpadded) and algorithmic HBM bytes of op i for B frames */
+int pb200_plan_op_work(const pb200_plan* plan, int i, int B, double* flops, double* bytes);
+int pb200_forward_profile(pb200_plan* plan, const void* frames, void* workspace, float* out_norm,
+                          float* out_px_or_null, int B, pb200_stream stream, float* ms);
+/* number of kernel launches one pb200_forward issues */
+int pb200_plan_launches_per_forward(const pb200_plan* plan);
+
+/* ---- stand-alone pieces (also used by the parity tests) ------------------------------- */
+
+/* (x+1)*(W-1)/2, (y+1)*(H-1)/2 on n (x,y) pairs — kornia denormalize_pixel_coordinates. */
+int pb200_decode_pixels(const float* xy_norm, float* xy_px, int64_t n_points, int H, int W,
+                        pb200_stream stream);
+
+/* One conv layer through the tcgen05 path, for unit tests: NHWC bf16 in/out, OIHW fp32 HOST
+ * weights and bias (packed internally; allocates and synchronises — not a product entry). */
+int pb200_debug_conv_bf16(const void* in_nhwc, int B, int H, int W, int Cin, const float* w_oihw_host,
+                          const float* bias_host, int Cout, int R, int stride, int pad,
+                          const void* residual_nhwc_or_null, int relu, void* out_nhwc,
+                          pb200_stream stream);
+
+/* ---- smoother factors (float64, batched) ---------------------------------------------- */
+
+/* KeypointProjectionFactor over N poses x P body points.
+ *   poses      : double [N][12]  row-major R (9) then t (3)    (gtsam.Pose3)
+ *   meas       : double [N][P][2]
+ *   pts_body   : double [P][3]
+ *   K5         : double [5] fx, fy, s, u0, v0                  (gtsam.Cal3_S2)
+ *   cam_pose12 : double [12] camera pose in the world, or NULL = identity
+ *   resid      : double [N][P][2]
+ *   jac        : double [N][P][12] 2x6 column-major (Fortran, as GTSAM expects), tangent order
+ *                [rot; trans], right perturbation; or NULL
+ *   cheirality : uint8 [N][P] 1 where the point is behind the camera (GTSAM would throw), or NULL */
+int pb200_factors_projection(const double* poses, const double* meas, const double* pts_body,
+                             const double* K5, const double* cam_pose12_or_null, double* resid,
+                             double* jac_or_null, uint8_t* cheirality_or_null, int64_t N, int P,
+                             pb200_stream stream);
+
+/* PoseDynamicsFactor over N (pose1, ang_vel1, vel1, pose2) tuples.
+ *   resid : double [N][6] [rot; trans];  H0,H3 : double [N][36] 6x6 column-major;
+ *   H1,H2 : double [N][18] 6x3 column-major; all four NULL = residual only. */
+int pb200_factors_dynamics(const double* pose1, const double* ang_vel1, const double* vel1,
+                           const double* pose2, double dt, int world_frame, double* resid,
+                           double* H0, double* H1, double* H2, double* H3, int64_t N,
+                           pb200_stream stream);
+
+/* ConstantVelocityFactor: resid = vel2 - vel1 [N][3]; H0 = -I, H1 = +I ([N][9] each) or NULL. */
+int pb200_factors_constvel(const double* vel1, const double* vel2, double* resid, double* H0,
+                           double* H1, int64_t N, pb200_stream stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PERSEUS_B200_H_ */

@@ -1,0 +1,223 @@
+// Batched residual / Jacobian evaluation of the smoother factors: float64 SIMT, HBM-bound.
+// One thread per factor; inputs and outputs move through shared memory so that every global
+// access of a warp is a run of consecutive 8-byte words (the AoS records are 16..288 B long).
+//
+// Replaces the per-factor Python callbacks of perseus/smoother/factors.py (:54-142, :160-171,
+// :216-275) that GTSAM invokes one at a time on the CPU.
+#include "common.cuh"
+#include "factors_math.h"
+
+namespace pb200 {
+
+constexpr int kFacThreads = 128;
+
+// Cooperative, coalesced copy of `n` doubles between global and shared memory.
+__device__ __forceinline__ void copy_in(double* dst, const double* __restrict__ src, int n) {
+  for (int i = threadIdx.x; i < n; i += blockDim.x) dst[i] = __ldg(src + i);
+}
+__device__ __forceinline__ void copy_out(double* __restrict__ dst, const double* src, int n) {
+  for (int i = threadIdx.x; i < n; i += blockDim.x) dst[i] = src[i];
+}
+
+// ---- dynamics -----------------------------------------------------------------------------
+// smem per block: inputs 30 doubles/factor, outputs 114 doubles/factor (padded strides are odd
+// multiples so that per-thread records do not collide on banks more than 2-way).
+template <bool JAC>
+__global__ void __launch_bounds__(kFacThreads)
+dynamics_kernel(const double* __restrict__ pose1, const double* __restrict__ angvel,
+                const double* __restrict__ vel, const double* __restrict__ pose2, double dt,
+                int world_frame, double* __restrict__ resid, double* __restrict__ H0,
+                double* __restrict__ H1, double* __restrict__ H2, double* __restrict__ H3,
+                long long N) {
+  extern __shared__ double sm[];
+  const long long base = static_cast<long long>(blockIdx.x) * kFacThreads;
+  const int cnt = static_cast<int>(min(static_cast<long long>(kFacThreads), N - base));
+  double* s_p1 = sm;                       // 12 * T
+  double* s_p2 = s_p1 + 12 * kFacThreads;  // 12 * T
+  double* s_w = s_p2 + 12 * kFacThreads;   // 3 * T
+  double* s_v = s_w + 3 * kFacThreads;     // 3 * T
+  double* s_out = s_v + 3 * kFacThreads;   // JAC ? 114*T : 6*T
+  copy_in(s_p1, pose1 + base * 12, cnt * 12);
+  copy_in(s_p2, pose2 + base * 12, cnt * 12);
+  copy_in(s_w, angvel + base * 3, cnt * 3);
+  copy_in(s_v, vel + base * 3, cnt * 3);
+  __syncthreads();
+  const int t = threadIdx.x;
+  double* o_res = s_out;                                   // 6 * T
+  double* o_h0 = s_out + 6 * kFacThreads;                  // 36 * T
+  double* o_h1 = o_h0 + 36 * kFacThreads;                  // 18 * T
+  double* o_h2 = o_h1 + 18 * kFacThreads;                  // 18 * T
+  double* o_h3 = o_h2 + 18 * kFacThreads;                  // 36 * T
+  if (t < cnt) {
+    const fm::Pose x1 = fm::load_pose12(s_p1 + t * 12);
+    const fm::Pose x2 = fm::load_pose12(s_p2 + t * 12);
+    const fm::V3 w = fm::v3(s_w[t * 3], s_w[t * 3 + 1], s_w[t * 3 + 2]);
+    const fm::V3 v = fm::v3(s_v[t * 3], s_v[t * 3 + 1], s_v[t * 3 + 2]);
+    double r[6];
+    if (JAC) {
+      double h0[36], h1[18], h2[18], h3[36];
+      fm::dynamics_factor(x1, w, v, x2, dt, world_frame, 1, r, h0, h1, h2, h3);
+#pragma unroll
+      for (int i = 0; i < 36; ++i) { o_h0[t * 36 + i] = h0[i]; o_h3[t * 36 + i] = h3[i]; }
+#pragma unroll
+      for (int i = 0; i < 18; ++i) { o_h1[t * 18 + i] = h1[i]; o_h2[t * 18 + i] = h2[i]; }
+    } else {
+      fm::dynamics_factor(x1, w, v, x2, dt, world_frame, 0, r, nullptr, nullptr, nullptr, nullptr);
+    }
+#pragma unroll
+    for (int i = 0; i < 6; ++i) o_res[t * 6 + i] = r[i];
+  }
+  __syncthreads();
+  copy_out(resid + base * 6, o_res, cnt * 6);
+  if (JAC) {
+    copy_out(H0 + base * 36, o_h0, cnt * 36);
+    copy_out(H1 + base * 18, o_h1, cnt * 18);
+    copy_out(H2 + base * 18, o_h2, cnt * 18);
+    copy_out(H3 + base * 36, o_h3, cnt * 36);
+  }
+}
+
+// ---- projection -----------------------------------------------------------------------------
+// One thread per (pose, point).  A block handles kFacThreads consecutive factors = a run of
+// consecutive poses (P divides the run when P | 128; otherwise poses straddle blocks, which is
+// fine because every thread indexes its own pose).
+template <bool JAC>
+__global__ void __launch_bounds__(kFacThreads)
+projection_kernel(const double* __restrict__ poses, const double* __restrict__ meas,
+                  const double* __restrict__ pts_body, const double* __restrict__ K5,
+                  const double* __restrict__ cam12, double* __restrict__ resid,
+                  double* __restrict__ jac, uint8_t* __restrict__ cheir, long long NP, int P) {
+  extern __shared__ double sm[];
+  const long long base = static_cast<long long>(blockIdx.x) * kFacThreads;
+  const int cnt = static_cast<int>(min(static_cast<long long>(kFacThreads), NP - base));
+  const long long pose_lo = base / P;
+  const long long pose_hi = (base + cnt - 1) / P;
+  const int npose = static_cast<int>(pose_hi - pose_lo + 1);
+  double* s_pose = sm;                          // 12 * (T/1 + 1) worst case P = 1
+  double* s_meas = s_pose + 12 * (kFacThreads + 1);  // 2 * T
+  double* s_res = s_meas + 2 * kFacThreads;     // 2 * T
+  double* s_jac = s_res + 2 * kFacThreads;      // 12 * T
+  copy_in(s_pose, poses + pose_lo * 12, npose * 12);
+  copy_in(s_meas, meas + base * 2, cnt * 2);
+  __syncthreads();
+  const int t = threadIdx.x;
+  if (t < cnt) {
+    const long long f = base + t;
+    const long long n = f / P;
+    const int p = static_cast<int>(f - n * P);
+    const fm::Pose body = fm::load_pose12(s_pose + (n - pose_lo) * 12);
+    fm::Pose cam;
+    if (cam12) {
+      cam = fm::load_pose12(cam12);
+    } else {
+      cam.R = fm::eye3();
+      cam.t = fm::v3(0, 0, 0);
+    }
+    double k5[5];
+#pragma unroll
+    for (int i = 0; i < 5; ++i) k5[i] = __ldg(K5 + i);
+    const fm::V3 pb = fm::v3(__ldg(pts_body + p * 3), __ldg(pts_body + p * 3 + 1), __ldg(pts_body + p * 3 + 2));
+    double r[2], J[12];
+    const int behind =
+        fm::projection_factor(body, pb, k5, cam, s_meas[t * 2], s_meas[t * 2 + 1], JAC ? 1 : 0, r, J);
+    s_res[t * 2] = r[0];
+    s_res[t * 2 + 1] = r[1];
+    if (JAC) {
+#pragma unroll
+      for (int i = 0; i < 12; ++i) s_jac[t * 12 + i] = J[i];
+    }
+    if (cheir) cheir[f] = static_cast<uint8_t>(behind);
+  }
+  __syncthreads();
+  copy_out(resid + base * 2, s_res, cnt * 2);
+  if (JAC) copy_out(jac + base * 12, s_jac, cnt * 12);
+}
+
+__global__ void constvel_kernel(const double* __restrict__ v1, const double* __restrict__ v2,
+                                double* __restrict__ resid, double* __restrict__ H0,
+                                double* __restrict__ H1, long long n3, long long n9) {
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i < n3) resid[i] = v2[i] - v1[i];                          // factors.py:169
+  if (H0 != nullptr && i < n9) {
+    const int k = static_cast<int>(i % 9);
+    const double d = (k == 0 || k == 4 || k == 8) ? 1.0 : 0.0;
+    H0[i] = -d;                                                  // factors.py:166
+    H1[i] = d;                                                   // factors.py:167
+  }
+}
+
+}  // namespace pb200
+
+using namespace pb200;
+
+extern "C" int pb200_factors_dynamics(const double* pose1, const double* ang_vel1,
+                                      const double* vel1, const double* pose2, double dt,
+                                      int world_frame, double* resid, double* H0, double* H1,
+                                      double* H2, double* H3, int64_t N, pb200_stream stream) {
+  if (int rc = require_device()) return rc;
+  PB_CHECK(N >= 0, "factors_dynamics: N < 0");
+  PB_CHECK(pose1 && ang_vel1 && vel1 && pose2 && resid, "factors_dynamics: null input");
+  const bool jac = H0 || H1 || H2 || H3;
+  PB_CHECK(!jac || (H0 && H1 && H2 && H3), "factors_dynamics: pass all four Jacobians or none");
+  if (N == 0) return PB200_OK;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const unsigned grid = static_cast<unsigned>((N + kFacThreads - 1) / kFacThreads);
+  if (jac) {
+    const size_t smem = sizeof(double) * kFacThreads * (30 + 114);
+    static bool attr_set = false;
+    if (!attr_set) {
+      PB_CUDA(cudaFuncSetAttribute(dynamics_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   static_cast<int>(smem)));
+      attr_set = true;
+    }
+    dynamics_kernel<true><<<grid, kFacThreads, smem, st>>>(pose1, ang_vel1, vel1, pose2, dt,
+                                                            world_frame, resid, H0, H1, H2, H3, N);
+  } else {
+    const size_t smem = sizeof(double) * kFacThreads * (30 + 6);
+    dynamics_kernel<false><<<grid, kFacThreads, smem, st>>>(
+        pose1, ang_vel1, vel1, pose2, dt, world_frame, resid, nullptr, nullptr, nullptr, nullptr, N);
+  }
+  PB_CUDA(cudaGetLastError());
+  return PB200_OK;
+}
+
+extern "C" int pb200_factors_projection(const double* poses, const double* meas,
+                                        const double* pts_body, const double* K5,
+                                        const double* cam_pose12_or_null, double* resid,
+                                        double* jac_or_null, uint8_t* cheirality_or_null, int64_t N,
+                                        int P, pb200_stream stream) {
+  if (int rc = require_device()) return rc;
+  PB_CHECK(N >= 0 && P > 0, "factors_projection: bad N/P");
+  PB_CHECK(poses && meas && pts_body && K5 && resid, "factors_projection: null input");
+  if (N == 0) return PB200_OK;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const long long NP = static_cast<long long>(N) * P;
+  const unsigned grid = static_cast<unsigned>((NP + kFacThreads - 1) / kFacThreads);
+  const size_t smem = sizeof(double) * (12 * (kFacThreads + 1) + 16 * kFacThreads);
+  if (jac_or_null) {
+    projection_kernel<true><<<grid, kFacThreads, smem, st>>>(poses, meas, pts_body, K5,
+                                                              cam_pose12_or_null, resid, jac_or_null,
+                                                              cheirality_or_null, NP, P);
+  } else {
+    projection_kernel<false><<<grid, kFacThreads, smem, st>>>(poses, meas, pts_body, K5,
+                                                               cam_pose12_or_null, resid, nullptr,
+                                                               cheirality_or_null, NP, P);
+  }
+  PB_CUDA(cudaGetLastError());
+  return PB200_OK;
+}
+
+extern "C" int pb200_factors_constvel(const double* vel1, const double* vel2, double* resid,
+                                      double* H0, double* H1, int64_t N, pb200_stream stream) {
+  if (int rc = require_device()) return rc;
+  PB_CHECK(N >= 0, "factors_constvel: N < 0");
+  PB_CHECK(vel1 && vel2 && resid, "factors_constvel: null input");
+  PB_CHECK((H0 == nullptr) == (H1 == nullptr), "factors_constvel: pass both Jacobians or none");
+  if (N == 0) return PB200_OK;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const long long n9 = static_cast<long long>(N) * 9;
+  const unsigned grid = static_cast<unsigned>((n9 + 255) / 256);
+  constvel_kernel<<<grid, 256, 0, st>>>(vel1, vel2, resid, H0, H1, static_cast<long long>(N) * 3, n9);
+  PB_CUDA(cudaGetLastError());
+  return PB200_OK;
+}
