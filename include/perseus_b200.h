@@ -93,14 +93,19 @@ int pb200_plan_load_weights(pb200_plan* plan, const float* const* tensors,
  *                 rgb_pitch_bytes (>= src_w*rgb_channels), frame pitch rgb_pitch_bytes*src_h
  *   bgr         : non-zero = channel order is B,G,R(,A)  (ZED camera; streaming.py:68-69)
  *   depth       : float [B][src_h][src_w] or NULL (NULL -> depth channel written as 0)
- *   depth_scale : multiplied into depth after NaN/Inf -> 0  (1/0.035 for metres, 1 for data units)
- *   near_plane, far_plane : if far_plane > 0, zero the depth where 0.035*d < near (+jitter) or
- *                 0.035*d > far (+jitter); jitter_or_null is float [B][2][H][W] (near, far).
- *   The centred H x W window of the source is taken (streaming.py:79-80). */
+ *   depth_divisor : after NaN/+-Inf -> 0 the depth is DIVIDED by this in fp32, exactly as
+ *                 streaming.py:74-76 does (0.035 for a camera in metres, 1 for dataset units)
+ *   clip        : non-zero = val-mode DepthPlaneAugmentation (augmentations.py:137-168):
+ *                 s = cube_scale*d; s = 0 where s < near_plane + jn; s = 0 where s > far_plane + jf;
+ *                 d = s / cube_scale.  jitter_or_null is float [B][2][H][W] holding (jn, jf) —
+ *                 the reference draws them at random even in val mode;
+ *                 NULL = the deterministic planes.
+ *   The centred H x W window of the source is taken (streaming.py:79-80):
+ *   rows src_h/2 - H/2 .., cols src_w/2 - W/2 .. */
 int pb200_ingest(const pb200_plan* plan, const uint8_t* rgb, int rgb_channels,
                  int64_t rgb_pitch_bytes, int src_h, int src_w, int bgr, const float* depth,
-                 float depth_scale, float near_plane, float far_plane, const float* jitter_or_null,
-                 void* out_frames, int B, pb200_stream stream);
+                 float depth_divisor, int clip, float cube_scale, float near_plane, float far_plane,
+                 const float* jitter_or_null, void* out_frames, int B, pb200_stream stream);
 
 /* Backbone + head + decode on ingested frames.
  *   out_norm : float [B][2*n_keypoints] normalised coordinates (the reference forward() output)

@@ -1,0 +1,395 @@
+// Convolution as a TMA-fed tcgen05 implicit GEMM (sm_100a), BN folded, bias + residual + ReLU in
+// the epilogue.  Replaces cuDNN fprop + BN + ReLU (+ add) of torchvision's ResNet-18
+// (resnet.py:89-105, 268-276) that perseus/detector/models.py:34-40 runs.
+//
+// GEMM view: D[M = B*Ho*Wo][N = Cout] = A[M][K] * W[N][K]^T, K = (r, s, c).
+//   * A is never materialised.  An M tile is 128 consecutive output pixels = a box of
+//     (bh rows x Wo cols x imgs) of the NHWC input; for filter tap (r, s) the box is simply
+//     shifted by (r - pad, s - pad), so ONE 4-D tiled TMA load per (tap, 64-channel block)
+//     lands a 128 x 64 bf16 K-major SWIZZLE_128B operand tile in shared memory; out-of-image
+//     taps are zero-filled by TMA's bounds check (the conv's zero padding).  Stride-2 layers use
+//     four parity-split views of the input (even/odd rows x even/odd cols), one per tap parity.
+//   * the stem reads the zero-margined frames buffer: a K block is one filter row = 8 taps x 4
+//     channels = 32 contiguous bf16 per output pixel, pixels 16 B apart (overlapping TMA rows),
+//     SWIZZLE_64B tiles.
+//   * warp roles (192 threads): warp 0 = TMA producer, warp 1 = MMA issuer (one thread) + TMEM
+//     owner, warps 2..5 = epilogue (TMEM -> registers -> bias/residual/ReLU -> bf16 NHWC).
+//   * persistent CTAs (grid = #SMs), static tile round-robin, smem ring of kStages stages,
+//     two TMEM accumulators so the epilogue of tile i overlaps the MMAs of tile i+1.
+#include "common.cuh"
+#include "conv_umma.cuh"
+#include "tma_host.h"
+
+namespace pb200 {
+
+constexpr int kUmmaThreads = 192;
+constexpr int kTileM = 128;
+
+template <int BLOCK_N, int SW>
+struct UmmaCfg {
+  static constexpr int kABytes = kTileM * SW;
+  static constexpr int kBBytes = BLOCK_N * SW;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kStages = (192 * 1024 / kStageBytes) > 8 ? 8 : (192 * 1024 / kStageBytes);
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024;  // + alignment slack
+  static constexpr int kBlockK = SW / 2;                             // bf16 elements per k-block
+  static constexpr int kKSteps = kBlockK / 16;                       // UMMA K = 16
+  static constexpr int kTmemCols = 2 * BLOCK_N;                      // double-buffered accumulator
+};
+
+template <int BLOCK_N, int SW>
+__global__ void __launch_bounds__(kUmmaThreads, 1)
+conv_umma_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams p) {
+  using Cfg = UmmaCfg<BLOCK_N, SW>;
+  constexpr int kStages = Cfg::kStages;
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t full_bar[kStages];
+  __shared__ __align__(8) uint64_t empty_bar[kStages];
+  __shared__ __align__(8) uint64_t tmem_full_bar[2];
+  __shared__ __align__(8) uint64_t tmem_empty_bar[2];
+  __shared__ uint32_t tmem_base_slot;
+
+  const uint32_t raw_addr = smem_u32(smem_raw);
+  const uint32_t tiles_addr = (raw_addr + 1023u) & ~1023u;
+  uint8_t* tiles = smem_raw + (tiles_addr - raw_addr);
+  uint8_t* smem_a = tiles;
+  uint8_t* smem_b = tiles + kStages * Cfg::kABytes;
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&maps.a[0]);
+    tma_prefetch_desc(&maps.b);
+#pragma unroll
+    for (int i = 0; i < kStages; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+    }
+    mbar_init(&tmem_full_bar[0], 1);
+    mbar_init(&tmem_full_bar[1], 1);
+    mbar_init(&tmem_empty_bar[0], 4);
+    mbar_init(&tmem_empty_bar[1], 4);
+    fence_barrier_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(&tmem_base_slot, Cfg::kTmemCols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_slot;
+
+  if (warp == 0) {
+    // ================================ TMA producer ================================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+        const int m_tile = tile / p.num_n_tiles;
+        const int n_tile = tile - m_tile * p.num_n_tiles;
+        int n0, ho0;
+        if (p.stem) {
+          n0 = m_tile / p.Ho;
+          ho0 = m_tile - n0 * p.Ho;
+        } else if (p.tiles_per_img > 0) {
+          n0 = m_tile / p.tiles_per_img;
+          ho0 = (m_tile - n0 * p.tiles_per_img) * p.bh;
+        } else {
+          n0 = m_tile * p.imgs_per_tile;
+          ho0 = 0;
+        }
+        for (int kb = 0; kb < p.num_kblocks; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1u);
+          mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+          uint8_t* a_dst = smem_a + stage * Cfg::kABytes;
+          uint8_t* b_dst = smem_b + stage * Cfg::kBBytes;
+          if (p.stem) {
+            // one filter row: frames row 2*ho + r, all 128 output columns, 32 elements each
+            tma_load_4d(a_dst, &maps.a[0], &full_bar[stage], 0, 0, 2 * ho0 + kb, n0);
+          } else {
+            const int tap = kb / p.cblocks;
+            const int cb = kb - tap * p.cblocks;
+            const int r = tap / p.S;
+            const int s = tap - r * p.S;
+            int dh = r - p.pad, dw = s - p.pad, mi = 0;
+            if (p.stride == 2) {
+              const int hp = dh & 1, wp = dw & 1;
+              dh = (dh - hp) >> 1;
+              dw = (dw - wp) >> 1;
+              mi = hp * 2 + wp;
+            }
+            tma_load_4d(a_dst, &maps.a[mi], &full_bar[stage], cb * 64, dw, ho0 + dh, n0);
+          }
+          tma_load_2d(b_dst, &maps.b, &full_bar[stage], kb * Cfg::kBlockK, n_tile * BLOCK_N);
+          if (++stage == kStages) {
+            stage = 0;
+            phase ^= 1u;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================================ MMA issuer ==================================
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(kTileM, BLOCK_N);
+      int stage = 0;
+      uint32_t phase = 0;
+      int it = 0;
+      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+        const int acc = it & 1;
+        const uint32_t acc_phase = (it >> 1) & 1;
+        mbar_wait(&tmem_empty_bar[acc], acc_phase ^ 1u);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * BLOCK_N;
+        for (int kb = 0; kb < p.num_kblocks; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint64_t adesc = umma_desc_kmajor(smem_u32(smem_a + stage * Cfg::kABytes), SW);
+          const uint64_t bdesc = umma_desc_kmajor(smem_u32(smem_b + stage * Cfg::kBBytes), SW);
+#pragma unroll
+          for (int k = 0; k < Cfg::kKSteps; ++k) {
+            // advancing K by 16 elements = 32 bytes inside the swizzle span: +2 in the address field
+            umma_bf16(d_tmem, adesc + static_cast<uint64_t>(2 * k), bdesc + static_cast<uint64_t>(2 * k),
+                      idesc, (kb | k) != 0 ? 1u : 0u);
+          }
+          umma_commit(&empty_bar[stage]);  // frees the smem stage once these MMAs have read it
+          if (kb == p.num_kblocks - 1) umma_commit(&tmem_full_bar[acc]);
+          if (++stage == kStages) {
+            stage = 0;
+            phase ^= 1u;
+          }
+        }
+      }
+    }
+  } else {
+    // ================================ epilogue ====================================
+    const int q = warp & 3;  // TMEM lane quarter this warp may access
+    const int row = q * 32 + lane;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+      const int m_tile = tile / p.num_n_tiles;
+      const int n_tile = tile - m_tile * p.num_n_tiles;
+      const int acc = it & 1;
+      const uint32_t acc_phase = (it >> 1) & 1;
+      mbar_wait(&tmem_full_bar[acc], acc_phase);
+      tc_fence_after();
+      const long long gm = static_cast<long long>(m_tile) * kTileM + row;
+      const bool valid = gm < p.M_total;
+      const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BLOCK_N;
+      __nv_bfloat16* out_row = static_cast<__nv_bfloat16*>(p.out) + gm * p.Cout + n_tile * BLOCK_N;
+      const __nv_bfloat16* res_row =
+          p.residual ? static_cast<const __nv_bfloat16*>(p.residual) + gm * p.Cout + n_tile * BLOCK_N
+                     : nullptr;
+      const float* bias = p.bias + n_tile * BLOCK_N;
+#pragma unroll 1
+      for (int chunk = 0; chunk < BLOCK_N / 32; ++chunk) {
+        uint32_t v[32];
+        tmem_ld_32x32(t_addr + chunk * 32, v);
+        tmem_ld_wait();
+        if (valid) {
+          float f[32];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float4 bv = __ldg(reinterpret_cast<const float4*>(bias + chunk * 32) + j);
+            f[4 * j] = __uint_as_float(v[4 * j]) + bv.x;
+            f[4 * j + 1] = __uint_as_float(v[4 * j + 1]) + bv.y;
+            f[4 * j + 2] = __uint_as_float(v[4 * j + 2]) + bv.z;
+            f[4 * j + 3] = __uint_as_float(v[4 * j + 3]) + bv.w;
+          }
+          if (res_row != nullptr) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const uint4 rv = __ldg(reinterpret_cast<const uint4*>(res_row + chunk * 32) + j);
+              f[8 * j] += bf16_lo(rv.x); f[8 * j + 1] += bf16_hi(rv.x);
+              f[8 * j + 2] += bf16_lo(rv.y); f[8 * j + 3] += bf16_hi(rv.y);
+              f[8 * j + 4] += bf16_lo(rv.z); f[8 * j + 5] += bf16_hi(rv.z);
+              f[8 * j + 6] += bf16_lo(rv.w); f[8 * j + 7] += bf16_hi(rv.w);
+            }
+          }
+          if (p.relu) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
+          }
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const uint4 o = make_uint4(pack_bf16x2(f[8 * j], f[8 * j + 1]), pack_bf16x2(f[8 * j + 2], f[8 * j + 3]),
+                                       pack_bf16x2(f[8 * j + 4], f[8 * j + 5]), pack_bf16x2(f[8 * j + 6], f[8 * j + 7]));
+            reinterpret_cast<uint4*>(out_row + chunk * 32)[j] = o;
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, Cfg::kTmemCols);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------
+template <int BLOCK_N, int SW>
+static int set_attr() {
+  PB_CUDA(cudaFuncSetAttribute(conv_umma_kernel<BLOCK_N, SW>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               UmmaCfg<BLOCK_N, SW>::kSmemBytes));
+  return PB200_OK;
+}
+
+int umma_conv_init() {
+  static bool done = false;
+  if (done) return PB200_OK;
+  if (int rc = set_attr<64, 128>()) return rc;
+  if (int rc = set_attr<128, 128>()) return rc;
+  if (int rc = set_attr<256, 128>()) return rc;
+  if (int rc = set_attr<64, 64>()) return rc;
+  done = true;
+  return PB200_OK;
+}
+
+static int encode_weight_map(CUtensorMap* m, const void* w, int Cout, int Ktot, int block_n, int sw) {
+  const uint64_t dims[2] = {static_cast<uint64_t>(Ktot), static_cast<uint64_t>(Cout)};
+  const uint64_t strides[1] = {static_cast<uint64_t>(Ktot) * 2};
+  const uint32_t box[2] = {static_cast<uint32_t>(sw / 2), static_cast<uint32_t>(block_n)};
+  return encode_tma_bf16(m, w, 2, dims, strides, box, sw);
+}
+
+int build_umma_conv(UmmaConvLaunch* L, const void* in, int B, int Hin, int Win, int Cin,
+                    const void* wpacked, const float* bias, const void* residual, void* out, int Cout,
+                    int R, int stride, int pad, int relu, int block_n) {
+  PB_CHECK(stride == 1 || stride == 2, "umma conv: stride %d unsupported", stride);
+  PB_CHECK(Cin % 64 == 0, "umma conv: Cin %d not a multiple of 64", Cin);
+  PB_CHECK(block_n == 64 || block_n == 128 || block_n == 256, "umma conv: block_n %d", block_n);
+  PB_CHECK(Cout % block_n == 0, "umma conv: Cout %d %% block_n %d", Cout, block_n);
+  const int Ho = (Hin + 2 * pad - R) / stride + 1;
+  const int Wo = (Win + 2 * pad - R) / stride + 1;
+  PB_CHECK(stride == 1 || (Hin % 2 == 0 && Win % 2 == 0), "umma conv: stride 2 needs even H, W");
+  PB_CHECK(Wo <= kTileM && kTileM % Wo == 0, "umma conv: Wo=%d must divide 128", Wo);
+  const int P = Ho * Wo;
+  int bh, imgs, tiles_per_img;
+  if (P >= kTileM) {
+    PB_CHECK(P % kTileM == 0, "umma conv: Ho*Wo=%d must be a multiple of 128", P);
+    bh = kTileM / Wo;
+    imgs = 1;
+    tiles_per_img = P / kTileM;
+  } else {
+    PB_CHECK(kTileM % P == 0, "umma conv: Ho*Wo=%d must divide 128", P);
+    bh = Ho;
+    imgs = kTileM / P;
+    tiles_per_img = 0;
+  }
+  const long long M = static_cast<long long>(B) * P;
+  memset(L, 0, sizeof(*L));
+  UmmaConvParams& p = L->p;
+  p.M_total = static_cast<int>(M);
+  p.Cout = Cout;
+  p.stem = 0;
+  p.Ho = Ho;
+  p.Wo = Wo;
+  p.tiles_per_img = tiles_per_img;
+  p.imgs_per_tile = imgs;
+  p.bh = bh;
+  p.stride = stride;
+  p.pad = pad;
+  p.S = R;
+  p.cblocks = Cin / 64;
+  p.num_kblocks = R * R * p.cblocks;
+  p.num_n_tiles = Cout / block_n;
+  const int m_tiles = static_cast<int>((M + kTileM - 1) / kTileM);
+  p.num_tiles = m_tiles * p.num_n_tiles;
+  p.relu = relu;
+  p.bias = bias;
+  p.residual = residual;
+  p.out = out;
+  L->block_n = block_n;
+  L->sw = 128;
+  L->grid = p.num_tiles < num_sms() ? p.num_tiles : num_sms();
+  L->flops = 2.0 * static_cast<double>(M) * Cout * R * R * Cin;
+
+  const uint32_t box[4] = {64u, static_cast<uint32_t>(Wo), static_cast<uint32_t>(bh),
+                           static_cast<uint32_t>(imgs)};
+  const uint64_t e = 2;  // bytes per element
+  if (stride == 1) {
+    const uint64_t dims[4] = {(uint64_t)Cin, (uint64_t)Win, (uint64_t)Hin, (uint64_t)B};
+    const uint64_t str[3] = {Cin * e, (uint64_t)Win * Cin * e, (uint64_t)Hin * Win * Cin * e};
+    if (int rc = encode_tma_bf16(&L->maps.a[0], in, 4, dims, str, box, 128)) return rc;
+    for (int i = 1; i < 4; ++i) L->maps.a[i] = L->maps.a[0];
+  } else {
+    for (int hp = 0; hp < 2; ++hp)
+      for (int wp = 0; wp < 2; ++wp) {
+        const uint8_t* base = static_cast<const uint8_t*>(in) + (static_cast<uint64_t>(hp) * Win + wp) * Cin * e;
+        const uint64_t dims[4] = {(uint64_t)Cin, (uint64_t)Win / 2, (uint64_t)Hin / 2, (uint64_t)B};
+        const uint64_t str[3] = {2 * Cin * e, 2 * (uint64_t)Win * Cin * e, (uint64_t)Hin * Win * Cin * e};
+        if (int rc = encode_tma_bf16(&L->maps.a[hp * 2 + wp], base, 4, dims, str, box, 128)) return rc;
+      }
+  }
+  return encode_weight_map(&L->maps.b, wpacked, Cout, R * R * Cin, block_n, 128);
+}
+
+int build_umma_stem(UmmaConvLaunch* L, const void* frames, int B, int H, int W, const void* wpacked,
+                    const float* bias, void* out, int Cout) {
+  const int Ho = H / 2, Wo = W / 2;
+  PB_CHECK(Wo == kTileM, "umma stem: needs W = 256 (one 128-pixel output row per tile), got W=%d", W);
+  PB_CHECK(H % 2 == 0, "umma stem: odd H");
+  PB_CHECK(Cout == 64, "umma stem: Cout must be 64");
+  const int Hp = H + 6, Wp = W + 8;
+  memset(L, 0, sizeof(*L));
+  UmmaConvParams& p = L->p;
+  const long long M = static_cast<long long>(B) * Ho * Wo;
+  p.M_total = static_cast<int>(M);
+  p.Cout = Cout;
+  p.stem = 1;
+  p.Ho = Ho;
+  p.Wo = Wo;
+  p.tiles_per_img = Ho;
+  p.imgs_per_tile = 1;
+  p.bh = 1;
+  p.stride = 2;
+  p.pad = 0;
+  p.S = 8;
+  p.cblocks = 1;
+  p.num_kblocks = 7;
+  p.num_n_tiles = 1;
+  p.num_tiles = B * Ho;
+  p.relu = 1;
+  p.bias = bias;
+  p.residual = nullptr;
+  p.out = out;
+  L->block_n = 64;
+  L->sw = 64;
+  L->grid = p.num_tiles < num_sms() ? p.num_tiles : num_sms();
+  L->flops = 0.0;  // filled by the plan (depends on the real channel count)
+  // virtual tensor V[n][row][wo][j] = frames[n][row][2*wo + j/4][j%4], j in [0,32):
+  // element strides (1, 8, Wp*4, Hp*Wp*4) -> overlapping 64-byte rows, 16 bytes apart.
+  const uint64_t dims[4] = {32, (uint64_t)Wo, (uint64_t)Hp, (uint64_t)B};
+  const uint64_t str[3] = {16, (uint64_t)Wp * 8, (uint64_t)Hp * Wp * 8};
+  const uint32_t box[4] = {32, (uint32_t)Wo, 1, 1};
+  if (int rc = encode_tma_bf16(&L->maps.a[0], frames, 4, dims, str, box, 64)) return rc;
+  for (int i = 1; i < 4; ++i) L->maps.a[i] = L->maps.a[0];
+  return encode_weight_map(&L->maps.b, wpacked, Cout, 224, 64, 64);
+}
+
+int launch_umma_conv(const UmmaConvLaunch& L, cudaStream_t st) {
+  if (L.p.num_tiles == 0) return PB200_OK;
+  if (L.sw == 64) {
+    conv_umma_kernel<64, 64><<<L.grid, kUmmaThreads, UmmaCfg<64, 64>::kSmemBytes, st>>>(L.maps, L.p);
+  } else if (L.block_n == 64) {
+    conv_umma_kernel<64, 128><<<L.grid, kUmmaThreads, UmmaCfg<64, 128>::kSmemBytes, st>>>(L.maps, L.p);
+  } else if (L.block_n == 128) {
+    conv_umma_kernel<128, 128><<<L.grid, kUmmaThreads, UmmaCfg<128, 128>::kSmemBytes, st>>>(L.maps, L.p);
+  } else {
+    conv_umma_kernel<256, 128><<<L.grid, kUmmaThreads, UmmaCfg<256, 128>::kSmemBytes, st>>>(L.maps, L.p);
+  }
+  PB_CUDA(cudaGetLastError());
+  return PB200_OK;
+}
+
+}  // namespace pb200

@@ -1,0 +1,50 @@
+// Host interface of the tcgen05 implicit-GEMM convolution (conv_umma.cu).
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace pb200 {
+
+struct alignas(64) UmmaConvMaps {
+  CUtensorMap a[4];  // activation maps: [0] for stride 1 / the stem, [hp*2+wp] parity maps for stride 2
+  CUtensorMap b;     // packed weights [Cout][Kpad]
+};
+
+struct UmmaConvParams {
+  int num_tiles, num_n_tiles, num_kblocks;
+  int M_total;  // B*Ho*Wo output pixels
+  int Cout;
+  int stem;     // 1: A rows come from the frames buffer (7 k-blocks = 7 filter rows)
+  int Ho, Wo;
+  int tiles_per_img;  // Ho*Wo/128 when >= 1, else 0
+  int imgs_per_tile;  // 128/(Ho*Wo) when the image is smaller than a tile, else 1
+  int bh;             // output rows per tile
+  int stride, pad, S, cblocks;
+  int relu;
+  const float* bias;            // [Cout] (folded BN shift)
+  const void* residual;         // bf16 [M_total][Cout] or null
+  void* out;                    // bf16 [M_total][Cout]
+};
+
+struct UmmaConvLaunch {
+  UmmaConvMaps maps;
+  UmmaConvParams p;
+  int block_n;  // 64 / 128 / 256
+  int sw;       // swizzle bytes = bytes of K per smem row: 128 (generic) or 64 (stem)
+  int grid;
+  double flops;  // algorithmic 2*MAC (unpadded)
+};
+
+// Generic conv (R x R, stride 1 or 2, Cin % 64 == 0) on NHWC bf16.  wpacked: bf16 [Cout][R*R*Cin]
+// with K order (r, s, c).
+int build_umma_conv(UmmaConvLaunch* L, const void* in, int B, int Hin, int Win, int Cin,
+                    const void* wpacked, const float* bias, const void* residual, void* out, int Cout,
+                    int R, int stride, int pad, int relu, int block_n);
+// Stem 7x7/2 on the frames buffer [B][H+6][W+8][4] bf16.  wpacked: bf16 [64][224], K = r*32+s8*4+c.
+int build_umma_stem(UmmaConvLaunch* L, const void* frames, int B, int H, int W, const void* wpacked,
+                    const float* bias, void* out, int Cout);
+int launch_umma_conv(const UmmaConvLaunch& L, cudaStream_t st);
+int umma_conv_init();  // sets the dynamic shared-memory attributes once per process
+
+}  // namespace pb200

@@ -1,0 +1,591 @@
+// The detector plan: weight folding/packing, buffer layout, and the forward launch sequence.
+// Mirrors KeypointCNN (perseus/detector/models.py:6-40) = torchvision resnet18 with conv1 swapped
+// for RGBD and fc -> Linear(512, 2*n_keypoints); forward = ResNet._forward_impl (resnet.py:266-282).
+#include <math.h>
+#include <string.h>
+
+#include <map>
+#include <string>
+#include <vector>
+
+#include "common.cuh"
+#include "conv_umma.cuh"
+#include "layout.h"
+
+namespace pb200 {
+
+struct ConvSpec {
+  std::string name;     // "conv1", "layer1.0.conv1", "layer2.0.downsample.0", ...
+  std::string bn;       // matching BN prefix
+  int Cin, Cout, R, stride, pad;
+  int Hin, Win, Ho, Wo;
+  bool stem;
+  // device storage (offsets into the weight arena)
+  size_t w_off = 0;     // packed weights
+  size_t b_off = 0;     // fp32 bias [Cout]
+  size_t w_bytes = 0;
+};
+
+enum OpKind { OP_REPACK, OP_CONV, OP_MAXPOOL, OP_HEAD };
+
+struct Op {
+  OpKind kind;
+  std::string name;
+  int conv = -1;   // index into convs
+  int in_buf = -1, out_buf = -1, res_buf = -1;  // activation buffer ids
+  int relu = 0;
+};
+
+// activation buffer ids
+enum { BUF_FRAMES = 0, BUF_STEM = 1, BUF_R0 = 2, BUF_R1 = 3, BUF_R2 = 4, BUF_R3 = 5, BUF_COUNT = 6 };
+
+}  // namespace pb200
+
+struct pb200_plan {
+  int device = 0, max_batch = 0, C = 3, H = 256, W = 256, n_kp = 8, precision = PB200_PREC_BF16;
+  bool bf16 = true;
+  size_t elt = 2;
+  std::vector<pb200::ConvSpec> convs;
+  std::vector<pb200::Op> ops;
+  size_t buf_per_frame[pb200::BUF_COUNT] = {0};  // bytes per frame
+  size_t buf_off[pb200::BUF_COUNT] = {0};        // offsets in the workspace (for max_batch)
+  size_t workspace_bytes = 0;
+  // weights
+  uint8_t* arena = nullptr;
+  size_t arena_bytes = 0;
+  size_t fc_w_off = 0, fc_b_off = 0;
+  bool loaded = false;
+  // cached launch descriptors (TMA maps bake in pointers and the batch size)
+  const void* cache_frames = nullptr;
+  void* cache_ws = nullptr;
+  int cache_B = -1;
+  std::vector<pb200::UmmaConvLaunch> umma;  // per conv
+  std::vector<std::string> op_names;
+};
+
+namespace pb200 {
+
+static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+static uint16_t f32_to_bf16_rne(float f) {
+  uint32_t u;
+  memcpy(&u, &f, 4);
+  if ((u & 0x7fffffffu) > 0x7f800000u) return static_cast<uint16_t>((u >> 16) | 0x40);  // NaN
+  const uint32_t lsb = (u >> 16) & 1u;
+  u += 0x7fffu + lsb;
+  return static_cast<uint16_t>(u >> 16);
+}
+
+static void add_conv(pb200_plan* pl, const std::string& name, const std::string& bn, int Cin, int Cout,
+                     int R, int stride, int pad, int Hin, int Win, bool stem = false) {
+  ConvSpec c;
+  c.name = name;
+  c.bn = bn;
+  c.Cin = Cin; c.Cout = Cout; c.R = R; c.stride = stride; c.pad = pad;
+  c.Hin = Hin; c.Win = Win;
+  c.Ho = (Hin + 2 * pad - R) / stride + 1;
+  c.Wo = (Win + 2 * pad - R) / stride + 1;
+  c.stem = stem;
+  pl->convs.push_back(c);
+}
+
+static void build_graph(pb200_plan* pl) {
+  const int H = pl->H, W = pl->W;
+  // stem (resnet.py:268-270; RGBD conv at models.py:27-28)
+  add_conv(pl, "conv1", "bn1", pl->C, 64, 7, 2, 3, H, W, true);
+  const int H1 = (H + 6 - 7) / 2 + 1, W1 = (W + 6 - 7) / 2 + 1;   // after conv1
+  const int H2 = (H1 + 2 - 3) / 2 + 1, W2 = (W1 + 2 - 3) / 2 + 1; // after maxpool
+  if (pl->precision != PB200_PREC_FP32 || true) {
+    Op op;
+    op.kind = OP_CONV; op.name = "conv1+bn1+relu"; op.conv = 0; op.in_buf = BUF_FRAMES; op.out_buf = BUF_STEM; op.relu = 1;
+    pl->ops.push_back(op);
+  }
+  {
+    Op op;
+    op.kind = OP_MAXPOOL; op.name = "maxpool"; op.in_buf = BUF_STEM; op.out_buf = BUF_R0;
+    pl->ops.push_back(op);
+  }
+  int cur = 0;  // rotating buffer index holding the block input
+  int h = H2, w = W2, cin = 64;
+  const int planes[4] = {64, 128, 256, 512};
+  for (int L = 0; L < 4; ++L) {
+    for (int b = 0; b < 2; ++b) {
+      const int cout = planes[L];
+      const int stride = (L > 0 && b == 0) ? 2 : 1;
+      const std::string pre = "layer" + std::to_string(L + 1) + "." + std::to_string(b);
+      const int t = (cur + 1) % 4, y = (cur + 2) % 4, ds = (cur + 3) % 4;
+      int res = cur;
+      if (stride != 1 || cin != cout) {  // resnet.py:240-243
+        add_conv(pl, pre + ".downsample.0", pre + ".downsample.1", cin, cout, 1, stride, 0, h, w);
+        Op op;
+        op.kind = OP_CONV; op.name = pre + ".downsample"; op.conv = static_cast<int>(pl->convs.size()) - 1;
+        op.in_buf = BUF_R0 + cur; op.out_buf = BUF_R0 + ds; op.relu = 0;
+        pl->ops.push_back(op);
+        res = ds;
+      }
+      add_conv(pl, pre + ".conv1", pre + ".bn1", cin, cout, 3, stride, 1, h, w);
+      {
+        Op op;
+        op.kind = OP_CONV; op.name = pre + ".conv1+bn1+relu"; op.conv = static_cast<int>(pl->convs.size()) - 1;
+        op.in_buf = BUF_R0 + cur; op.out_buf = BUF_R0 + t; op.relu = 1;
+        pl->ops.push_back(op);
+      }
+      const int ho = pl->convs.back().Ho, wo = pl->convs.back().Wo;
+      add_conv(pl, pre + ".conv2", pre + ".bn2", cout, cout, 3, 1, 1, ho, wo);
+      {
+        Op op;
+        op.kind = OP_CONV; op.name = pre + ".conv2+bn2+add+relu"; op.conv = static_cast<int>(pl->convs.size()) - 1;
+        op.in_buf = BUF_R0 + t; op.out_buf = BUF_R0 + y; op.res_buf = BUF_R0 + res; op.relu = 1;
+        pl->ops.push_back(op);
+      }
+      cur = y;
+      h = ho; w = wo; cin = cout;
+    }
+  }
+  {
+    Op op;
+    op.kind = OP_HEAD; op.name = "avgpool+fc+decode"; op.in_buf = BUF_R0 + cur;
+    pl->ops.push_back(op);
+  }
+  // buffers (bytes per frame)
+  const size_t e = pl->elt;
+  pl->buf_per_frame[BUF_FRAMES] = static_cast<size_t>(H + 6) * (W + 8) * 4 * e;
+  pl->buf_per_frame[BUF_STEM] = static_cast<size_t>(H1) * W1 * 64 * e;
+  for (int i = 0; i < 4; ++i) pl->buf_per_frame[BUF_R0 + i] = static_cast<size_t>(H2) * W2 * 64 * e;
+  size_t off = 0;
+  for (int i = 0; i < BUF_COUNT; ++i) {
+    pl->buf_off[i] = off;
+    off += align_up(pl->buf_per_frame[i] * pl->max_batch, 1024);
+  }
+  pl->workspace_bytes = off;
+  // weight arena
+  size_t woff = 0;
+  for (auto& c : pl->convs) {
+    const size_t K = c.stem ? kStemK : static_cast<size_t>(c.R) * c.R * c.Cin;
+    c.w_bytes = K * c.Cout * e;
+    c.w_off = woff;
+    woff = align_up(woff + c.w_bytes, 1024);
+    c.b_off = woff;
+    woff = align_up(woff + sizeof(float) * c.Cout, 1024);
+  }
+  pl->fc_w_off = woff;
+  woff = align_up(woff + sizeof(float) * 512 * 2 * pl->n_kp, 1024);
+  pl->fc_b_off = woff;
+  woff = align_up(woff + sizeof(float) * 2 * pl->n_kp, 1024);
+  pl->arena_bytes = woff;
+  for (auto& o : pl->ops) pl->op_names.push_back(o.name);
+}
+
+}  // namespace pb200
+
+// ------------------------------------------------------------------------------------------
+// C ABI: plan lifecycle and weights
+// ------------------------------------------------------------------------------------------
+using namespace pb200;
+
+extern "C" int pb200_plan_create(pb200_plan** out, int device, int max_batch, int in_channels, int H,
+                                 int W, int n_keypoints, int precision) {
+  PB_CHECK(out != nullptr, "plan_create: null out");
+  *out = nullptr;
+  PB_CHECK(max_batch >= 1, "plan_create: max_batch %d", max_batch);
+  PB_CHECK(in_channels >= 1 && in_channels <= 4,
+           "plan_create: in_channels %d (the frames layout carries up to 4: R,G,B,D)", in_channels);
+  PB_CHECK(n_keypoints >= 1, "plan_create: n_keypoints %d", n_keypoints);
+  PB_CHECK(precision == PB200_PREC_FP32 || precision == PB200_PREC_BF16,
+           "plan_create: precision %d not available (0 = fp32 SIMT, 1 = bf16 tcgen05)", precision);
+  PB_CHECK(H % 32 == 0 && W % 32 == 0 && H >= 32 && W >= 32, "plan_create: H, W must be multiples of 32");
+  if (precision != PB200_PREC_FP32)
+    PB_CHECK(H == 256 && W == 256, "plan_create: the tcgen05 path is tiled for 256x256 frames (got %dx%d); "
+             "use PB200_PREC_FP32 for other sizes", H, W);
+  PB_CUDA(cudaSetDevice(device));
+  if (int rc = require_device()) return rc;
+  pb200_plan* pl = new pb200_plan();
+  pl->device = device;
+  pl->max_batch = max_batch;
+  pl->C = in_channels;
+  pl->H = H;
+  pl->W = W;
+  pl->n_kp = n_keypoints;
+  pl->precision = precision;
+  pl->bf16 = precision != PB200_PREC_FP32;
+  pl->elt = pl->bf16 ? 2 : 4;
+  build_graph(pl);
+  cudaError_t e = cudaMalloc(reinterpret_cast<void**>(&pl->arena), pl->arena_bytes);
+  if (e != cudaSuccess) {
+    delete pl;
+    return cuda_fail(e, "cudaMalloc(weight arena)", __FILE__, __LINE__);
+  }
+  if (pl->bf16) {
+    if (int rc = umma_conv_init()) {
+      cudaFree(pl->arena);
+      delete pl;
+      return rc;
+    }
+  }
+  *out = pl;
+  return PB200_OK;
+}
+
+extern "C" void pb200_plan_destroy(pb200_plan* plan) {
+  if (!plan) return;
+  if (plan->arena) cudaFree(plan->arena);
+  delete plan;
+}
+
+extern "C" int pb200_plan_workspace_bytes(const pb200_plan* plan, size_t* bytes) {
+  PB_CHECK(plan && bytes, "plan_workspace_bytes: null argument");
+  *bytes = plan->workspace_bytes;
+  return PB200_OK;
+}
+
+extern "C" int pb200_plan_frames_bytes(const pb200_plan* plan, int B, size_t* bytes) {
+  PB_CHECK(plan && bytes && B >= 0, "plan_frames_bytes: bad argument");
+  *bytes = plan->buf_per_frame[BUF_FRAMES] * static_cast<size_t>(B);
+  return PB200_OK;
+}
+
+namespace pb200 {
+struct HostTensor {
+  const float* data;
+  std::vector<int64_t> shape;
+  int64_t numel() const {
+    int64_t n = 1;
+    for (auto s : shape) n *= s;
+    return n;
+  }
+};
+}  // namespace pb200
+
+extern "C" int pb200_plan_load_weights(pb200_plan* plan, const float* const* tensors,
+                                       const int64_t* const* shapes, const int* ndims,
+                                       const char* const* names, int n, pb200_stream stream) {
+  PB_CHECK(plan && tensors && shapes && ndims && names, "load_weights: null argument");
+  std::map<std::string, HostTensor> sd;
+  for (int i = 0; i < n; ++i) {
+    HostTensor t;
+    t.data = tensors[i];
+    t.shape.assign(shapes[i], shapes[i] + ndims[i]);
+    std::string nm(names[i]);
+    const std::string mod = "module.";
+    size_t pos;
+    while ((pos = nm.find(mod)) != std::string::npos) nm.erase(pos, mod.size());  // validate.py:94-96
+    sd[nm] = t;
+  }
+  auto need = [&](const std::string& key, std::vector<int64_t> shape, const HostTensor** out) -> int {
+    auto it = sd.find(key);
+    PB_CHECK(it != sd.end(), "load_weights: missing tensor '%s'", key.c_str());
+    PB_CHECK(it->second.shape == shape, "load_weights: tensor '%s' has the wrong shape", key.c_str());
+    PB_CHECK(it->second.data != nullptr, "load_weights: tensor '%s' is null", key.c_str());
+    *out = &it->second;
+    return PB200_OK;
+  };
+  std::vector<uint8_t> host(plan->arena_bytes, 0);
+  for (const auto& c : plan->convs) {
+    const HostTensor *w, *g, *b, *mu, *var;
+    const std::string wn = "resnet." + c.name + ".weight", bp = "resnet." + c.bn;
+    if (int rc = need(wn, {c.Cout, c.Cin, c.R, c.R}, &w)) return rc;
+    if (int rc = need(bp + ".weight", {c.Cout}, &g)) return rc;
+    if (int rc = need(bp + ".bias", {c.Cout}, &b)) return rc;
+    if (int rc = need(bp + ".running_mean", {c.Cout}, &mu)) return rc;
+    if (int rc = need(bp + ".running_var", {c.Cout}, &var)) return rc;
+    float* bias = reinterpret_cast<float*>(host.data() + c.b_off);
+    const int K = c.stem ? kStemK : c.R * c.R * c.Cin;
+    for (int co = 0; co < c.Cout; ++co) {
+      // eval-mode BatchNorm2d, eps = 1e-5: y = (x - mean) / sqrt(var + eps) * gamma + beta
+      const double sc = static_cast<double>(g->data[co]) / sqrt(static_cast<double>(var->data[co]) + 1e-5);
+      bias[co] = static_cast<float>(static_cast<double>(b->data[co]) - static_cast<double>(mu->data[co]) * sc);
+      for (int r = 0; r < c.R; ++r)
+        for (int s = 0; s < c.R; ++s)
+          for (int ci = 0; ci < c.Cin; ++ci) {
+            double v = static_cast<double>(w->data[((static_cast<size_t>(co) * c.Cin + ci) * c.R + r) * c.R + s]) * sc;
+            int k;
+            if (c.stem) {
+              k = r * (kStemTaps * kFrameC) + (s + 1) * kFrameC + ci;
+              if (plan->bf16 && ci < 3) v /= 255.0;  // frames carry RGB as integers 0..255
+            } else {
+              k = (r * c.R + s) * c.Cin + ci;
+            }
+            if (plan->bf16) {
+              reinterpret_cast<uint16_t*>(host.data() + c.w_off)[static_cast<size_t>(co) * K + k] =
+                  f32_to_bf16_rne(static_cast<float>(v));
+            } else {
+              reinterpret_cast<float*>(host.data() + c.w_off)[static_cast<size_t>(k) * c.Cout + co] =
+                  static_cast<float>(v);
+            }
+          }
+    }
+  }
+  const HostTensor *fw, *fb;
+  const int n_out = 2 * plan->n_kp;
+  if (int rc = need("resnet.fc.weight", {n_out, 512}, &fw)) return rc;
+  if (int rc = need("resnet.fc.bias", {n_out}, &fb)) return rc;
+  memcpy(host.data() + plan->fc_w_off, fw->data, sizeof(float) * 512 * n_out);
+  memcpy(host.data() + plan->fc_b_off, fb->data, sizeof(float) * n_out);
+  PB_CUDA(cudaSetDevice(plan->device));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  PB_CUDA(cudaMemcpyAsync(plan->arena, host.data(), plan->arena_bytes, cudaMemcpyHostToDevice, st));
+  PB_CUDA(cudaStreamSynchronize(st));
+  plan->loaded = true;
+  return PB200_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// forward
+// ------------------------------------------------------------------------------------------
+namespace pb200 {
+
+static inline uint8_t* buf_ptr(const pb200_plan* pl, const void* frames, void* ws, int id) {
+  if (id == BUF_FRAMES) return const_cast<uint8_t*>(static_cast<const uint8_t*>(frames));
+  return static_cast<uint8_t*>(ws) + pl->buf_off[id];
+}
+
+static int choose_block_n(const ConvSpec& c, int B) {
+  // widest N tile that still gives every SM a tile; ties go to the wider tile (less A re-reading)
+  const long long m_tiles = (static_cast<long long>(B) * c.Ho * c.Wo + 127) / 128;
+  int bn = c.Cout < 256 ? c.Cout : 256;
+  while (bn > 64 && m_tiles * (c.Cout / bn) < num_sms()) bn /= 2;
+  return bn;
+}
+
+// (re)build the TMA descriptors / launch parameters when a pointer or the batch size changed
+static int prepare(pb200_plan* pl, const void* frames, void* ws, int B) {
+  if (!pl->bf16) return PB200_OK;
+  if (pl->cache_frames == frames && pl->cache_ws == ws && pl->cache_B == B) return PB200_OK;
+  pl->umma.assign(pl->convs.size(), UmmaConvLaunch());
+  for (const auto& op : pl->ops) {
+    if (op.kind != OP_CONV) continue;
+    const ConvSpec& c = pl->convs[op.conv];
+    UmmaConvLaunch* L = &pl->umma[op.conv];
+    const void* in = buf_ptr(pl, frames, ws, op.in_buf);
+    void* out = buf_ptr(pl, frames, ws, op.out_buf);
+    const void* res = op.res_buf >= 0 ? buf_ptr(pl, frames, ws, op.res_buf) : nullptr;
+    const float* bias = reinterpret_cast<const float*>(pl->arena + c.b_off);
+    int rc;
+    if (c.stem) {
+      rc = build_umma_stem(L, in, B, pl->H, pl->W, pl->arena + c.w_off, bias, out, c.Cout);
+      L->flops = 2.0 * B * c.Ho * c.Wo * c.Cout * 49.0 * c.Cin;
+    } else {
+      rc = build_umma_conv(L, in, B, c.Hin, c.Win, c.Cin, pl->arena + c.w_off, bias, res, out, c.Cout,
+                           c.R, c.stride, c.pad, op.relu, choose_block_n(c, B));
+    }
+    if (rc) {
+      pl->cache_B = -1;
+      return rc;
+    }
+  }
+  pl->cache_frames = frames;
+  pl->cache_ws = ws;
+  pl->cache_B = B;
+  return PB200_OK;
+}
+
+static int run_op(pb200_plan* pl, const Op& op, const void* frames, void* ws, float* out_norm,
+                  float* out_px, int B, cudaStream_t st) {
+  switch (op.kind) {
+    case OP_CONV: {
+      const ConvSpec& c = pl->convs[op.conv];
+      if (pl->bf16) return launch_umma_conv(pl->umma[op.conv], st);
+      SimtConv s;
+      s.in = reinterpret_cast<const float*>(buf_ptr(pl, frames, ws, op.in_buf));
+      s.w = reinterpret_cast<const float*>(pl->arena + c.w_off);
+      s.bias = reinterpret_cast<const float*>(pl->arena + c.b_off);
+      s.residual = op.res_buf >= 0 ? reinterpret_cast<const float*>(buf_ptr(pl, frames, ws, op.res_buf)) : nullptr;
+      s.out = reinterpret_cast<float*>(buf_ptr(pl, frames, ws, op.out_buf));
+      s.B = B; s.Ho = c.Ho; s.Wo = c.Wo; s.Cout = c.Cout; s.relu = op.relu;
+      if (c.stem) {  // 7 x 8 taps over the zero-margined frames buffer (layout.h)
+        s.Hin = pl->H + 6; s.Win = pl->W + 8; s.Cin = kFrameC; s.R = 7; s.S = kStemTaps; s.stride = 2; s.pad = 0;
+      } else {
+        s.Hin = c.Hin; s.Win = c.Win; s.Cin = c.Cin; s.R = c.R; s.S = c.R; s.stride = c.stride; s.pad = c.pad;
+      }
+      return launch_conv_simt(s, st);
+    }
+    case OP_MAXPOOL: {
+      const ConvSpec& c = pl->convs[0];
+      return launch_maxpool(buf_ptr(pl, frames, ws, op.in_buf), buf_ptr(pl, frames, ws, op.out_buf), B,
+                            c.Ho, c.Wo, c.Cout, pl->bf16, st);
+    }
+    case OP_HEAD: {
+      const ConvSpec& c = pl->convs.back();
+      return launch_head(buf_ptr(pl, frames, ws, op.in_buf),
+                         reinterpret_cast<const float*>(pl->arena + pl->fc_w_off),
+                         reinterpret_cast<const float*>(pl->arena + pl->fc_b_off), out_norm, out_px, B,
+                         c.Ho * c.Wo, c.Cout, 2 * pl->n_kp, pl->H, pl->W, pl->bf16, st);
+    }
+    default:
+      return PB200_OK;
+  }
+}
+
+static int check_forward_args(pb200_plan* plan, const void* frames, void* ws, float* out_norm, int B) {
+  PB_CHECK(plan && frames && ws && out_norm, "forward: null argument");
+  PB_CHECK(B >= 1 && B <= plan->max_batch, "forward: batch %d outside [1, max_batch=%d]", B,
+           plan->max_batch);
+  if (!plan->loaded) {
+    set_error("forward: pb200_plan_load_weights has not been called");
+    return PB200_ERR_STATE;
+  }
+  return PB200_OK;
+}
+
+}  // namespace pb200
+
+extern "C" int pb200_forward(pb200_plan* plan, const void* frames, void* workspace, float* out_norm,
+                             float* out_px_or_null, int B, pb200_stream stream) {
+  if (int rc = check_forward_args(plan, frames, workspace, out_norm, B)) return rc;
+  if (int rc = prepare(plan, frames, workspace, B)) return rc;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  for (const auto& op : plan->ops)
+    if (int rc = run_op(plan, op, frames, workspace, out_norm, out_px_or_null, B, st)) return rc;
+  return PB200_OK;
+}
+
+extern "C" int pb200_forward_nchw_f32(pb200_plan* plan, const float* x_nchw, void* workspace,
+                                      float* out_norm, float* out_px_or_null, int B,
+                                      pb200_stream stream) {
+  if (int rc = check_forward_args(plan, x_nchw, workspace, out_norm, B)) return rc;
+  void* frames = static_cast<uint8_t*>(workspace) + plan->buf_off[BUF_FRAMES];
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (int rc = launch_repack_nchw(x_nchw, plan->C, plan->H, plan->W, B, frames, plan->bf16, st)) return rc;
+  return pb200_forward(plan, frames, workspace, out_norm, out_px_or_null, B, stream);
+}
+
+extern "C" int pb200_plan_num_ops(const pb200_plan* plan) {
+  return plan ? static_cast<int>(plan->ops.size()) : 0;
+}
+extern "C" const char* pb200_plan_op_name(const pb200_plan* plan, int i) {
+  if (!plan || i < 0 || i >= static_cast<int>(plan->ops.size())) return "";
+  return plan->op_names[i].c_str();
+}
+extern "C" int pb200_plan_launches_per_forward(const pb200_plan* plan) {
+  return plan ? static_cast<int>(plan->ops.size()) : 0;
+}
+
+extern "C" int pb200_plan_op_work(const pb200_plan* plan, int i, int B, double* flops, double* bytes) {
+  PB_CHECK(plan && i >= 0 && i < static_cast<int>(plan->ops.size()) && flops && bytes, "op_work: bad argument");
+  const Op& op = plan->ops[i];
+  const double e = static_cast<double>(plan->elt);
+  *flops = 0.0;
+  *bytes = 0.0;
+  if (op.kind == OP_CONV) {
+    const ConvSpec& c = plan->convs[op.conv];
+    const double M = static_cast<double>(B) * c.Ho * c.Wo;
+    *flops = 2.0 * M * c.Cout * c.R * c.R * c.Cin;
+    const double in_el = c.stem ? static_cast<double>(B) * (plan->H + 6) * (plan->W + 8) * 4
+                                : static_cast<double>(B) * c.Hin * c.Win * c.Cin;
+    *bytes = e * (in_el + M * c.Cout * (op.res_buf >= 0 ? 2.0 : 1.0) +
+                  static_cast<double>(c.Cout) * c.R * c.R * c.Cin);
+  } else if (op.kind == OP_MAXPOOL) {
+    const ConvSpec& c = plan->convs[0];
+    *bytes = e * static_cast<double>(B) * c.Cout * (c.Ho * c.Wo + (c.Ho / 2) * (c.Wo / 2));
+  } else if (op.kind == OP_HEAD) {
+    const ConvSpec& c = plan->convs.back();
+    *flops = 2.0 * B * 512.0 * 2 * plan->n_kp;
+    *bytes = e * static_cast<double>(B) * c.Ho * c.Wo * c.Cout + 4.0 * B * 2 * plan->n_kp * 2;
+  }
+  return PB200_OK;
+}
+
+extern "C" int pb200_forward_profile(pb200_plan* plan, const void* frames, void* workspace,
+                                     float* out_norm, float* out_px_or_null, int B,
+                                     pb200_stream stream, float* ms) {
+  if (int rc = check_forward_args(plan, frames, workspace, out_norm, B)) return rc;
+  PB_CHECK(ms != nullptr, "forward_profile: null ms");
+  if (int rc = prepare(plan, frames, workspace, B)) return rc;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int n = static_cast<int>(plan->ops.size());
+  std::vector<cudaEvent_t> ev(n + 1);
+  for (auto& e : ev) PB_CUDA(cudaEventCreate(&e));
+  int rc = PB200_OK;
+  PB_CUDA(cudaEventRecord(ev[0], st));
+  for (int i = 0; i < n && rc == PB200_OK; ++i) {
+    rc = run_op(plan, plan->ops[i], frames, workspace, out_norm, out_px_or_null, B, st);
+    if (rc == PB200_OK && cudaEventRecord(ev[i + 1], st) != cudaSuccess) rc = PB200_ERR_CUDA;
+  }
+  if (rc == PB200_OK) {
+    cudaError_t e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess) rc = cuda_fail(e, "cudaStreamSynchronize", __FILE__, __LINE__);
+  }
+  if (rc == PB200_OK)
+    for (int i = 0; i < n; ++i) cudaEventElapsedTime(&ms[i], ev[i], ev[i + 1]);
+  for (auto& e : ev) cudaEventDestroy(e);
+  return rc;
+}
+
+// ------------------------------------------------------------------------------------------
+// ingest + the single-layer debug entry
+// ------------------------------------------------------------------------------------------
+extern "C" int pb200_ingest(const pb200_plan* plan, const uint8_t* rgb, int rgb_channels,
+                            int64_t rgb_pitch_bytes, int src_h, int src_w, int bgr, const float* depth,
+                            float depth_divisor, int clip, float cube_scale, float near_plane,
+                            float far_plane, const float* jitter_or_null, void* out_frames, int B,
+                            pb200_stream stream) {
+  PB_CHECK(plan && rgb && out_frames, "ingest: null argument");
+  PB_CHECK(B >= 1, "ingest: B = %d", B);
+  PB_CHECK(rgb_channels == 3 || rgb_channels == 4, "ingest: rgb_channels must be 3 or 4, got %d", rgb_channels);
+  PB_CHECK(src_h >= plan->H && src_w >= plan->W, "ingest: source %dx%d smaller than the %dx%d window",
+           src_h, src_w, plan->H, plan->W);
+  PB_CHECK(rgb_pitch_bytes >= static_cast<int64_t>(src_w) * rgb_channels, "ingest: row pitch too small");
+  PB_CHECK(depth == nullptr || depth_divisor != 0.f, "ingest: depth_divisor is 0");
+  PB_CHECK(!clip || cube_scale != 0.f, "ingest: cube_scale is 0");
+  PB_CHECK(plan->W % 4 == 0, "ingest: W must be a multiple of 4");
+  if (int rc = require_device()) return rc;
+  IngestArgs a;
+  a.rgb = rgb;
+  a.pitch = rgb_pitch_bytes;
+  a.frame_pitch = rgb_pitch_bytes * src_h;
+  a.ch = rgb_channels;
+  a.bgr = bgr;
+  a.src_h = src_h;
+  a.src_w = src_w;
+  a.y0 = src_h / 2 - plan->H / 2;  // streaming.py:79-80
+  a.x0 = src_w / 2 - plan->W / 2;
+  a.depth = depth;
+  a.depth_divisor = depth_divisor;
+  a.clip = clip;
+  a.cube_scale = cube_scale;
+  a.near_plane = near_plane;
+  a.far_plane = far_plane;
+  a.jitter = jitter_or_null;
+  a.H = plan->H;
+  a.W = plan->W;
+  a.B = B;
+  a.rgb_integer = plan->bf16 ? 1 : 0;
+  return launch_ingest(a, out_frames, plan->bf16, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int pb200_debug_conv_bf16(const void* in_nhwc, int B, int H, int W, int Cin,
+                                     const float* w_oihw_host, const float* bias_host, int Cout, int R,
+                                     int stride, int pad, const void* residual_nhwc_or_null, int relu,
+                                     void* out_nhwc, pb200_stream stream) {
+  if (int rc = require_device()) return rc;
+  if (int rc = umma_conv_init()) return rc;
+  PB_CHECK(in_nhwc && w_oihw_host && bias_host && out_nhwc, "debug_conv: null argument");
+  const size_t K = static_cast<size_t>(R) * R * Cin;
+  std::vector<uint16_t> wp(K * Cout);
+  for (int co = 0; co < Cout; ++co)
+    for (int ci = 0; ci < Cin; ++ci)
+      for (int r = 0; r < R; ++r)
+        for (int s = 0; s < R; ++s)
+          wp[co * K + (static_cast<size_t>(r) * R + s) * Cin + ci] =
+              f32_to_bf16_rne(w_oihw_host[((static_cast<size_t>(co) * Cin + ci) * R + r) * R + s]);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  void *dw = nullptr, *db = nullptr;
+  PB_CUDA(cudaMalloc(&dw, wp.size() * 2));
+  PB_CUDA(cudaMalloc(&db, sizeof(float) * Cout));
+  int rc = PB200_OK;
+  if (cudaMemcpyAsync(dw, wp.data(), wp.size() * 2, cudaMemcpyHostToDevice, st) != cudaSuccess ||
+      cudaMemcpyAsync(db, bias_host, sizeof(float) * Cout, cudaMemcpyHostToDevice, st) != cudaSuccess)
+    rc = PB200_ERR_CUDA;
+  UmmaConvLaunch L;
+  if (rc == PB200_OK) {
+    int bn = Cout < 256 ? Cout : 256;
+    rc = build_umma_conv(&L, in_nhwc, B, H, W, Cin, dw, static_cast<const float*>(db),
+                         residual_nhwc_or_null, out_nhwc, Cout, R, stride, pad, relu, bn);
+  }
+  if (rc == PB200_OK) rc = launch_umma_conv(L, st);
+  cudaError_t e = cudaStreamSynchronize(st);
+  if (rc == PB200_OK && e != cudaSuccess) rc = cuda_fail(e, "debug_conv sync", __FILE__, __LINE__);
+  cudaFree(dw);
+  cudaFree(db);
+  return rc;
+}

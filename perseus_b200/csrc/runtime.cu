@@ -1,0 +1,126 @@
+// Error plumbing, device checks and the driver entry point for TMA descriptor encoding.
+#include <stdarg.h>
+#include <string.h>
+
+#include "common.cuh"
+#include "tma_host.h"
+
+namespace pb200 {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int cuda_fail(cudaError_t e, const char* what, const char* file, int line) {
+  set_error("CUDA error %d (%s) at %s:%d: %s", static_cast<int>(e), cudaGetErrorString(e), file, line,
+            what);
+  return PB200_ERR_CUDA;
+}
+
+int require_device() {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) {
+    (void)cudaGetLastError();
+    set_error("no CUDA device available (%s): perseus_b200 has no CPU fallback", cudaGetErrorString(e));
+    return PB200_ERR_NO_DEVICE;
+  }
+  static thread_local int cached_dev = -1;
+  static thread_local int cached_ok = 0;
+  if (cached_dev == dev) return cached_ok ? PB200_OK : PB200_ERR_NO_DEVICE;
+  int major = 0;
+  e = cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev);
+  if (e != cudaSuccess) {
+    (void)cudaGetLastError();
+    set_error("cannot query device %d (%s)", dev, cudaGetErrorString(e));
+    return PB200_ERR_NO_DEVICE;
+  }
+  cached_dev = dev;
+  cached_ok = (major == 10);
+  if (!cached_ok) {
+    set_error("device %d has compute capability %d.x; the kernels are sm_100a-only and there is no "
+              "fallback path", dev, major);
+    return PB200_ERR_NO_DEVICE;
+  }
+  return PB200_OK;
+}
+
+int num_sms() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess ||
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) {
+      (void)cudaGetLastError();
+      n = 148;
+    }
+  }
+  return n;
+}
+
+// ---- TMA descriptor encoding (cuTensorMapEncodeTiled through the runtime's driver entry point,
+// so the library links without libcuda and loads on a box with no driver) --------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  if (fn) return fn;
+  void* p = nullptr;
+  cudaDriverEntryPointQueryResult qres;
+  cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres);
+  if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || p == nullptr) {
+    (void)cudaGetLastError();
+    return nullptr;
+  }
+  fn = reinterpret_cast<EncodeTiledFn>(p);
+  return fn;
+}
+
+int encode_tma_bf16(CUtensorMap* map, const void* base, int rank, const uint64_t* dims,
+                    const uint64_t* strides_bytes /* rank-1 */, const uint32_t* box,
+                    int swizzle_bytes) {
+  EncodeTiledFn fn = get_encode();
+  if (!fn) {
+    set_error("cuTensorMapEncodeTiled entry point unavailable");
+    return PB200_ERR_CUDA;
+  }
+  cuuint64_t gdim[5];
+  cuuint64_t gstr[4];
+  cuuint32_t bx[5];
+  cuuint32_t es[5];
+  for (int i = 0; i < rank; ++i) {
+    gdim[i] = dims[i];
+    bx[i] = box[i];
+    es[i] = 1;
+    if (i > 0) gstr[i - 1] = strides_bytes[i - 1];
+  }
+  CUtensorMapSwizzle sw = swizzle_bytes == 128  ? CU_TENSOR_MAP_SWIZZLE_128B
+                          : swizzle_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B
+                          : swizzle_bytes == 32 ? CU_TENSOR_MAP_SWIZZLE_32B
+                                                : CU_TENSOR_MAP_SWIZZLE_NONE;
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, static_cast<cuuint32_t>(rank),
+                  const_cast<void*>(base), gdim, gstr, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled failed (%d): rank %d dims [%llu %llu %llu %llu] box [%u %u %u %u] "
+              "base %p", static_cast<int>(r), rank, (unsigned long long)dims[0],
+              (unsigned long long)(rank > 1 ? dims[1] : 0), (unsigned long long)(rank > 2 ? dims[2] : 0),
+              (unsigned long long)(rank > 3 ? dims[3] : 0), box[0], rank > 1 ? box[1] : 0,
+              rank > 2 ? box[2] : 0, rank > 3 ? box[3] : 0, base);
+    return PB200_ERR_CUDA;
+  }
+  return PB200_OK;
+}
+
+}  // namespace pb200
+
+extern "C" int pb200_version(void) { return PB200_VERSION; }
+extern "C" const char* pb200_last_error(void) { return pb200::g_err; }
