@@ -1,0 +1,2 @@
+from .models import KeypointCNN  # noqa: F401
+from .decode import denormalize_pixel_coordinates, normalize_pixel_coordinates  # noqa: F401

@@ -1,0 +1,297 @@
+"""Drop-in `KeypointCNN` (reference: perseus/detector/models.py:6-40).
+
+Same constructor, attributes (`.resnet .n_keypoints .num_channels .H .W`), `state_dict()` keys
+(`resnet.*`, 122 tensors) and `forward(x) -> (B, 2*n_keypoints)` contract as the reference, so the
+reference's validate / streaming / train callers keep working; checkpoints saved by the reference
+(`train.py:355`, optionally with DDP's `module.` prefix) load unchanged.
+
+What differs (documented in DESIGN.md):
+  * inference (`model.eval()`, as every reference inference caller does) runs hand-written sm_100a CUDA through the C ABI
+    (libperseus_b200.so): frames repack -> tcgen05 implicit-GEMM backbone with BN folded -> head.
+    There is NO CPU / PyTorch fallback on that path: a CPU tensor or a missing library raises.
+  * construction does not download ImageNet weights (the reference does, models.py:20).
+  * training-mode forward goes through the torch module tree (library autograd),
+    which is what DDP wraps for the data-parallel training step (train.py:152,287).
+"""
+from __future__ import annotations
+
+import ctypes
+
+import torch
+from torch import nn
+from torchvision import models as tv_models
+
+from .. import _lib
+
+
+class _Plan:
+    """Owns one pb200_plan + its workspace for a (device, precision, max_batch)."""
+
+    def __init__(self, device: torch.device, max_batch: int, C: int, H: int, W: int, n_kp: int, precision: str):
+        if precision not in _lib.PRECISIONS:
+            raise ValueError(f"precision must be one of {sorted(_lib.PRECISIONS)}, got {precision!r}")
+        self.lib = _lib.lib()
+        self.device = device
+        self.max_batch = max_batch
+        self.precision = precision
+        handle = ctypes.c_void_p()
+        _lib.check(
+            self.lib.pb200_plan_create(
+                ctypes.byref(handle), device.index or 0, max_batch, C, H, W, n_kp, _lib.PRECISIONS[precision]
+            )
+        )
+        self.handle = handle
+        nbytes = ctypes.c_size_t()
+        _lib.check(self.lib.pb200_plan_workspace_bytes(self.handle, ctypes.byref(nbytes)))
+        self.workspace = torch.empty(nbytes.value, dtype=torch.uint8, device=device)
+        self.weights_key = None
+
+    def frames_bytes(self, B: int) -> int:
+        nbytes = ctypes.c_size_t()
+        _lib.check(self.lib.pb200_plan_frames_bytes(self.handle, B, ctypes.byref(nbytes)))
+        return nbytes.value
+
+    def load_weights(self, state_dict: dict) -> None:
+        names, tensors = [], []
+        for k, v in state_dict.items():
+            if not torch.is_floating_point(v):
+                continue  # num_batches_tracked
+            names.append(k.encode())
+            tensors.append(v.detach().to(device="cpu", dtype=torch.float32).contiguous())
+        n = len(names)
+        ptrs = (ctypes.c_void_p * n)(*[t.data_ptr() for t in tensors])
+        shape_arrs = [(ctypes.c_int64 * max(t.dim(), 1))(*t.shape) for t in tensors]
+        shapes = (ctypes.POINTER(ctypes.c_int64) * n)(
+            *[ctypes.cast(a, ctypes.POINTER(ctypes.c_int64)) for a in shape_arrs]
+        )
+        ndims = (ctypes.c_int * n)(*[t.dim() for t in tensors])
+        cnames = (ctypes.c_char_p * n)(*names)
+        with torch.cuda.device(self.device):
+            _lib.check(
+                self.lib.pb200_plan_load_weights(
+                    self.handle, ptrs, shapes, ndims, cnames, n, _lib.current_stream_ptr()
+                )
+            )
+
+    def __del__(self):
+        try:
+            if getattr(self, "handle", None):
+                self.lib.pb200_plan_destroy(self.handle)
+                self.handle = None
+        except Exception:
+            pass
+
+
+class KeypointCNN(nn.Module):
+    """perseus keypoint CNN (ResNet-18 regressor), B200-native inference.
+
+    Args mirror the reference (models.py:9): n_keypoints, num_channels, H, W.
+    Extra keyword-only knobs: `precision` ("bf16" = tcgen05 throughput mode, "fp32" = SIMT parity
+    mode) and `max_batch` (initial plan capacity; grows on demand).
+    """
+
+    def __init__(
+        self,
+        n_keypoints: int = 8,
+        num_channels: int = 3,
+        H: int = 256,
+        W: int = 256,
+        *,
+        precision: str = "bf16",
+        max_batch: int = 256,
+    ) -> None:
+        super().__init__()
+        # Same module tree as the reference so state_dict keys/shapes are identical
+        # (models.py:20,27-32); random init instead of the ImageNet download.
+        self.resnet = tv_models.resnet18(weights=None)
+        self.n_keypoints = n_keypoints
+        self.num_channels = num_channels
+        self.H = H
+        self.W = W
+        if num_channels != 3:  # models.py:27-28
+            self.resnet.conv1 = nn.Conv2d(num_channels, 64, kernel_size=7, stride=2, padding=3, bias=False)
+        self.resnet.avgpool = nn.AdaptiveAvgPool2d((1, 1))  # models.py:31
+        self.resnet.fc = nn.Linear(self.resnet.fc.in_features, 2 * n_keypoints)  # models.py:32
+        self.precision = precision
+        self._max_batch = max_batch
+        self._plans: dict = {}
+        self._tensors = None
+
+    # ---- plan / weight management ----------------------------------------------------------
+    def __getstate__(self):
+        state = self.__dict__.copy()
+        state["_plans"] = {}  # native handles are per-process; rebuilt lazily
+        state["_tensors"] = None
+        return state
+
+    def _apply(self, fn, *args, **kwargs):
+        out = super()._apply(fn, *args, **kwargs)
+        self._tensors = None
+        return out
+
+    def _weights_key(self):
+        if self._tensors is None:
+            self._tensors = tuple(t for t in self.state_dict(keep_vars=True).values() if torch.is_floating_point(t))
+        ts = self._tensors
+        return (ts[0].data_ptr(), sum(t._version for t in ts))
+
+    def refresh_weights(self) -> None:
+        """Forces the folded/packed device weights to be rebuilt on the next native forward."""
+        self._tensors = None
+        for p in self._plans.values():
+            p.weights_key = None
+
+    def _plan(self, device: torch.device, B: int) -> _Plan:
+        key = (device.index or 0, self.precision)
+        plan = self._plans.get(key)
+        if plan is None or plan.max_batch < B:
+            cap = max(B, self._max_batch if plan is None else plan.max_batch)
+            self._plans.pop(key, None)
+            del plan
+            plan = _Plan(device, cap, self.num_channels, self.H, self.W, self.n_keypoints, self.precision)
+            self._plans[key] = plan
+        wk = self._weights_key()
+        if plan.weights_key != wk:
+            plan.load_weights(self.state_dict())
+            plan.weights_key = wk
+        return plan
+
+    # ---- reference API -----------------------------------------------------------------------
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        """x: (B, num_channels, H, W) float, RGB in [0,1], depth in data units -> (B, 2*n_keypoints)."""
+        if self.training:
+            # train mode = batch-statistics BatchNorm + autograd: the data-parallel training step
+            # (train.py:287) runs on the torch module tree that DDP wraps.
+            return self.resnet(x)
+        norm, _ = self._native_forward(x, want_pixels=False)
+        return norm.to(x.dtype) if norm.dtype != x.dtype else norm
+
+    def forward_pixels(self, x: torch.Tensor):
+        """forward() plus the pixel decode (validate.py:144-153) fused in the head kernel.
+
+        Returns (normalised (B, 2K), pixels (B, K, 2)) in float32."""
+        return self._native_forward(x, want_pixels=True)
+
+    def _native_forward(self, x: torch.Tensor, want_pixels: bool):
+        squeeze = x.dim() == 3
+        if squeeze:
+            x = x[None]
+        if x.dim() != 4 or x.shape[1] != self.num_channels or x.shape[2] != self.H or x.shape[3] != self.W:
+            raise ValueError(
+                f"expected (B, {self.num_channels}, {self.H}, {self.W}) input, got {tuple(x.shape)}"
+            )
+        if not x.is_cuda:
+            raise RuntimeError(
+                "perseus_b200.KeypointCNN inference runs only on a B200 (sm_100a) through "
+                "libperseus_b200.so; got a CPU tensor and there is no CPU fallback — move the model and "
+                "input to cuda"
+            )
+        B = x.shape[0]
+        xf = x.detach().to(torch.float32).contiguous()
+        plan = self._plan(x.device, B)
+        out_norm = torch.empty((B, 2 * self.n_keypoints), dtype=torch.float32, device=x.device)
+        out_px = torch.empty((B, self.n_keypoints, 2), dtype=torch.float32, device=x.device) if want_pixels else None
+        with torch.cuda.device(x.device):
+            _lib.check(
+                plan.lib.pb200_forward_nchw_f32(
+                    plan.handle, xf.data_ptr(), plan.workspace.data_ptr(), out_norm.data_ptr(),
+                    _lib.ptr(out_px), B, _lib.current_stream_ptr(),
+                )
+            )
+        if squeeze:
+            out_norm = out_norm[0]
+            out_px = out_px[0] if out_px is not None else None
+        return out_norm, out_px
+
+    # ---- fast path: raw camera / dataset frames ------------------------------------------------
+    def ingest(
+        self,
+        rgb_u8: torch.Tensor,
+        depth: torch.Tensor | None = None,
+        *,
+        bgr: bool = False,
+        depth_divisor: float = 1.0,
+        clip: tuple | None = None,
+        cube_scale: float = 0.035,
+        jitter: torch.Tensor | None = None,
+        out: torch.Tensor | None = None,
+    ) -> torch.Tensor:
+        """uint8 (B, h, w, 3|4) [+ float32 depth (B, h, w)] -> the plan's frames buffer (uint8 view).
+
+        Fuses scripts/streaming.py:68-80 (BGR(A)->RGB, /255, NaN/Inf->0, /0.035, centre crop) and
+        the val-mode depth clip of augmentations.py:137-168 (`clip=(near, far)` in scaled metres,
+        optional `jitter` (B, 2, H, W))."""
+        if not rgb_u8.is_cuda:
+            raise RuntimeError("ingest: frames must be cuda tensors (no CPU fallback)")
+        if rgb_u8.dtype != torch.uint8 or rgb_u8.dim() != 4 or rgb_u8.shape[-1] not in (3, 4):
+            raise ValueError("ingest: rgb_u8 must be uint8 (B, h, w, 3|4)")
+        rgb_u8 = rgb_u8.contiguous()
+        B, sh, sw, ch = rgb_u8.shape
+        if depth is not None:
+            if depth.shape != (B, sh, sw):
+                raise ValueError(f"ingest: depth must be (B, h, w) = {(B, sh, sw)}, got {tuple(depth.shape)}")
+            depth = depth.to(torch.float32).contiguous()
+        if jitter is not None:
+            jitter = jitter.to(torch.float32).contiguous()
+            if jitter.shape != (B, 2, self.H, self.W):
+                raise ValueError("ingest: jitter must be (B, 2, H, W)")
+        plan = self._plan(rgb_u8.device, B)
+        nbytes = plan.frames_bytes(B)
+        if out is None:
+            out = torch.empty(nbytes, dtype=torch.uint8, device=rgb_u8.device)
+        elif out.numel() * out.element_size() < nbytes:
+            raise ValueError("ingest: out buffer too small")
+        near, far = clip if clip is not None else (0.0, 0.0)
+        with torch.cuda.device(rgb_u8.device):
+            _lib.check(
+                plan.lib.pb200_ingest(
+                    plan.handle, rgb_u8.data_ptr(), ch, sw * ch, sh, sw, int(bgr), _lib.ptr(depth),
+                    float(depth_divisor), int(clip is not None), float(cube_scale), float(near), float(far),
+                    _lib.ptr(jitter), out.data_ptr(), B, _lib.current_stream_ptr(),
+                )
+            )
+        return out
+
+    def forward_ingested(self, frames: torch.Tensor, B: int):
+        """Backbone + head + decode on an ingested frames buffer -> (norm (B,2K), pixels (B,K,2))."""
+        plan = self._plan(frames.device, B)
+        out_norm = torch.empty((B, 2 * self.n_keypoints), dtype=torch.float32, device=frames.device)
+        out_px = torch.empty((B, self.n_keypoints, 2), dtype=torch.float32, device=frames.device)
+        with torch.cuda.device(frames.device):
+            _lib.check(
+                plan.lib.pb200_forward(
+                    plan.handle, frames.data_ptr(), plan.workspace.data_ptr(), out_norm.data_ptr(),
+                    out_px.data_ptr(), B, _lib.current_stream_ptr(),
+                )
+            )
+        return out_norm, out_px
+
+    def forward_frames(self, rgb_u8: torch.Tensor, depth: torch.Tensor | None = None, **ingest_kwargs):
+        """Ingest + forward + decode: uint8 frames -> pixel keypoints (B, K, 2) float32."""
+        if self.num_channels == 4 and depth is None:
+            raise ValueError("forward_frames: an RGBD model needs a depth tensor")
+        if self.num_channels == 3:
+            depth = None
+        frames = self.ingest(rgb_u8, depth, **ingest_kwargs)
+        _, px = self.forward_ingested(frames, rgb_u8.shape[0])
+        return px
+
+    def profile_ops(self, frames: torch.Tensor, B: int):
+        """Per-kernel CUDA-event times of one forward: list of (name, ms, flops, bytes)."""
+        plan = self._plan(frames.device, B)
+        n = plan.lib.pb200_plan_num_ops(plan.handle)
+        ms = (ctypes.c_float * n)()
+        out_norm = torch.empty((B, 2 * self.n_keypoints), dtype=torch.float32, device=frames.device)
+        with torch.cuda.device(frames.device):
+            _lib.check(
+                plan.lib.pb200_forward_profile(
+                    plan.handle, frames.data_ptr(), plan.workspace.data_ptr(), out_norm.data_ptr(), None, B,
+                    _lib.current_stream_ptr(), ms,
+                )
+            )
+        rows = []
+        for i in range(n):
+            fl, by = ctypes.c_double(), ctypes.c_double()
+            _lib.check(plan.lib.pb200_plan_op_work(plan.handle, i, B, ctypes.byref(fl), ctypes.byref(by)))
+            rows.append((plan.lib.pb200_plan_op_name(plan.handle, i).decode(), float(ms[i]), fl.value, by.value))
+        return rows
