@@ -1,0 +1,222 @@
+"""-m gpu: detector hot path through the C ABI vs the oracle.
+
+Tolerances (stated per test):
+  * ingest: bit-exact (byte/float-division work)
+  * fp32 mode vs the reference fp32 forward: <= 1e-3 px RGB (north_star), <= 4e-3 px RGBD (the
+    reference's own fp32-vs-fp64 error is 1.1e-3 px there)
+  * bf16 mode vs the operand-matched bf16 emulation of the reference: <= 0.5 px max (only fp32
+    accumulation order + rare 1-ulp bf16 rounding flips differ); vs the fp32 reference it is
+    REPORTED, not asserted at 0.05 px (single-pass bf16 cannot meet that on random-init weights,
+    BASELINE.md §4: PyTorch's own bf16 path is 0.79 px off).
+"""
+import ctypes
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import detector_oracle as do
+from oracle.make_golden import golden_input
+from tests import gpu_util as gu
+
+pytestmark = pytest.mark.gpu
+
+
+# ---- ingest -------------------------------------------------------------------------------------
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_ingest_streaming_bgra_depth_bit_exact(precision):
+    """ZED-shaped frames (376x672 BGRA + metres with NaN/Inf), centre crop: streaming.py:68-80."""
+    model, _ = gu.native_model(4, precision)
+    B = 2
+    bgra = gu.synth_u8_frames(B, 376, 672, 4, seed=1)
+    depth = gu.synth_depth_m(B, 376, 672, seed=1)
+    buf = model.ingest(bgra.cuda(), depth.cuda(), bgr=True, depth_divisor=0.035)
+    fr = gu.frames_view(model, buf, B).float().cpu()
+    # zero margins
+    assert fr[:, :3].abs().max() == 0 and fr[:, -3:].abs().max() == 0
+    assert fr[:, :, :4].abs().max() == 0 and fr[:, :, -4:].abs().max() == 0
+    inner = fr[:, 3:-3, 4:-4]  # (B, 256, 256, 4)
+    for b in range(B):
+        want = do.streaming_ingest(bgra[b].numpy(), depth[b].numpy(), 4).permute(1, 2, 0)  # HWC f32
+        if precision == "fp32":
+            assert torch.equal(inner[b], want), "fp32 ingest must equal the reference bit for bit"
+        else:
+            # bf16 frames carry RGB as exact integers (1/255 lives in the stem weights), depth as bf16
+            assert torch.equal(inner[b][..., :3], torch.round(want[..., :3] * 255.0))
+            assert torch.equal(inner[b][..., 3], want[..., 3].bfloat16().float())
+
+
+def test_ingest_dataset_rgb_and_clip_bit_exact():
+    """data.py:84-85 + validate.py:122-124 + val-mode DepthPlaneAugmentation with explicit jitter."""
+    model, _ = gu.native_model(4, "fp32")
+    B = 3
+    rgb = gu.synth_u8_frames(B, 256, 256, 3, seed=2)
+    g = torch.Generator().manual_seed(5)
+    depth_units = torch.rand(B, 256, 256, generator=g) * 20.0  # 0..0.7 m scaled: both planes bite
+    jitter = (torch.rand(B, 2, 256, 256, generator=g) - 0.5) * 0.1
+    for jit in (None, jitter):
+        buf = model.ingest(rgb.cuda(), depth_units.cuda(), clip=(0.1, 0.5), jitter=None if jit is None else jit.cuda())
+        inner = gu.frames_view(model, buf, B).cpu()[:, 3:-3, 4:-4]
+        for b in range(B):
+            x = do.dataset_ingest(rgb[b].numpy(), depth_units[b].numpy())  # (4,H,W)
+            d = do.depth_plane_clip(x[3], 0.1, 0.5, None if jit is None else jit[b, 0], None if jit is None else jit[b, 1])
+            assert torch.equal(inner[b][..., :3], x[:3].permute(1, 2, 0))
+            assert torch.equal(inner[b][..., 3], d)
+    # RGB-only model: depth channel stays zero
+    m3, _ = gu.native_model(3, "fp32")
+    buf = m3.ingest(rgb.cuda())
+    assert gu.frames_view(m3, buf, B)[..., 3].abs().max().item() == 0
+
+
+def test_decode_matches_kornia_definition():
+    from perseus_b200.detector import denormalize_pixel_coordinates
+
+    g = torch.Generator().manual_seed(0)
+    xy = torch.rand(1000, 8, 2, generator=g) * 2.4 - 1.2
+    got = denormalize_pixel_coordinates(xy.cuda(), 256, 256).cpu()
+    assert torch.equal(got, do.denormalize_pixel_coordinates(xy, 256, 256))
+    got = denormalize_pixel_coordinates(xy.cuda(), 376, 672).cpu()
+    assert torch.equal(got, do.denormalize_pixel_coordinates(xy, 376, 672))
+
+
+# ---- one conv layer on the tensor cores --------------------------------------------------------
+CONV_CASES = [
+    # (B, H, W, Cin, Cout, R, stride, pad, residual, relu)
+    (2, 64, 64, 64, 64, 3, 1, 1, False, True),     # layer1 shape
+    (2, 64, 64, 64, 64, 3, 1, 1, True, True),      # + residual
+    (3, 64, 64, 64, 128, 3, 2, 1, False, True),    # layer2.0.conv1 (stride 2, parity maps)
+    (3, 64, 64, 64, 128, 1, 2, 0, False, False),   # layer2.0.downsample
+    (2, 32, 32, 128, 128, 3, 1, 1, True, True),    # layer2
+    (2, 16, 16, 256, 256, 3, 1, 1, True, True),    # layer3, N tile 256
+    (3, 16, 16, 256, 512, 3, 2, 1, False, True),   # layer4.0.conv1: 8x8 images, 2 per tile, ragged tail
+    (1, 8, 8, 512, 512, 3, 1, 1, True, True),      # layer4 at batch 1: half-empty tile
+]
+
+
+@pytest.mark.parametrize("case", CONV_CASES, ids=[str(c) for c in CONV_CASES])
+def test_umma_conv_layer_vs_exact_operand_reference(case):
+    """tcgen05 implicit GEMM vs F.conv2d in fp64 on the SAME bf16-rounded operands: only fp32
+    accumulation order and the final bf16 rounding differ (tolerance 2 bf16 ulps of the value)."""
+    from perseus_b200 import _lib
+
+    B, H, W, Cin, Cout, R, stride, pad, use_res, relu = case
+    g = torch.Generator().manual_seed(hash(case) % 1000)
+    x = torch.randn(B, H, W, Cin, generator=g).bfloat16()
+    w = (torch.randn(Cout, Cin, R, R, generator=g) / (R * R * Cin) ** 0.5).bfloat16().float()
+    bias = torch.randn(Cout, generator=g)
+    Ho, Wo = (H + 2 * pad - R) // stride + 1, (W + 2 * pad - R) // stride + 1
+    res = torch.randn(B, Ho, Wo, Cout, generator=g).bfloat16() if use_res else None
+    want = torch.nn.functional.conv2d(x.double().permute(0, 3, 1, 2), w.double(), bias.double(), stride, pad)
+    want = want.permute(0, 2, 3, 1)
+    if use_res:
+        want = want + res.double()
+    if relu:
+        want = want.relu()
+    xd, outd = x.cuda(), torch.full((B, Ho, Wo, Cout), float("nan"), dtype=torch.bfloat16, device="cuda")
+    resd = res.cuda() if use_res else None
+    wc, bc = w.contiguous(), bias.contiguous()
+    _lib.check(
+        _lib.lib().pb200_debug_conv_bf16(
+            xd.data_ptr(), B, H, W, Cin, wc.data_ptr(), bc.data_ptr(), Cout, R, stride, pad,
+            None if resd is None else resd.data_ptr(), int(relu), outd.data_ptr(), _lib.current_stream_ptr(),
+        )
+    )
+    torch.cuda.synchronize()
+    got = outd.double().cpu()
+    assert torch.isfinite(got).all(), "unwritten (NaN) outputs"
+    err = (got - want).abs()
+    tol = 2.0 ** -7 * want.abs() + 1e-2
+    bad = err > tol
+    assert not bad.any(), f"{int(bad.sum())} / {bad.numel()} outputs off; max err {float(err.max()):.4f}; first bad idx {bad.nonzero()[:4].tolist()}"
+
+
+# ---- whole forward --------------------------------------------------------------------------------
+@pytest.mark.parametrize("C", [3, 4])
+def test_forward_fp32_mode_matches_reference(C):
+    """BASELINE.json configs[0] through forward(x): golden fixture generated by the real reference."""
+    g = np.load(gu.os.path.join(gu.os.path.dirname(__file__), "golden", "detector_golden.npz"))
+    for bn in (0, 1):
+        model, sd = gu.native_model(C, "fp32", seed=0, randomize_bn=bool(bn))
+        x = golden_input(C)
+        y = model(x.cuda())
+        assert y.shape == (2, 16) and y.dtype == torch.float32
+        mx32, _ = gu.px_err(y, torch.from_numpy(g[f"c{C}_bn{bn}_out32"]))
+        mx64, _ = gu.px_err(y, torch.from_numpy(g[f"c{C}_bn{bn}_out64"]))
+        tol = 1e-3 if C == 3 else 4e-3
+        assert mx32 <= tol, f"C={C} bn={bn}: {mx32:.2e} px vs reference fp32 (vs fp64 truth {mx64:.2e})"
+        assert mx64 <= tol
+
+
+@pytest.mark.parametrize("C", [3, 4])
+def test_forward_bf16_mode_matches_operand_matched_reference(C):
+    model, sd = gu.native_model(C, "bf16")
+    x = golden_input(C, B=3, seed=3)
+    y = model(x.cuda())
+    emu = do.bf16_emulated_forward(sd, x)
+    ref = do.reference_forward(sd, x, torch.float32)
+    mx, mean = gu.px_err(y, emu)
+    mx_ref, mean_ref = gu.px_err(y, ref)
+    mx_emu_ref, _ = gu.px_err(emu, ref)
+    print(f"[bf16 C={C}] vs emulation max {mx:.4f} mean {mean:.4f} px | vs fp32 ref max {mx_ref:.3f} mean "
+          f"{mean_ref:.3f} px | emulation vs ref {mx_emu_ref:.3f} px")
+    scale = float(ref.abs().max())
+    assert mx <= 0.5 * max(1.0, scale / 4), f"bf16 path vs operand-matched emulation: {mx:.3f} px"
+    # format noise, not a bug: same order of magnitude as the emulation's own distance to fp32
+    assert mx_ref <= 3.0 * mx_emu_ref + 0.5
+
+
+def test_forward_frames_equals_forward_on_ingested_tensor():
+    """ingest -> forward (u8 frames) == forward(x) on the reference-style float tensor (fp32 mode)."""
+    model, sd = gu.native_model(4, "fp32")
+    B = 2
+    rgb = gu.synth_u8_frames(B, 256, 256, 3, seed=4)
+    depth = gu.synth_depth_m(B, 256, 256, seed=4)
+    px = model.forward_frames(rgb.cuda(), depth.cuda(), depth_divisor=0.035)
+    x = torch.stack([do.streaming_ingest(
+        torch.cat([rgb[b].flip(-1), torch.zeros(256, 256, 1, dtype=torch.uint8)], -1).numpy(), depth[b].numpy(), 4)
+        for b in range(B)])
+    norm, px2 = model.forward_pixels(x.cuda())
+    assert torch.equal(px, px2)
+    want = do.denormalize_pixel_coordinates(do.reference_forward(sd, x).reshape(B, 8, 2), 256, 256)
+    assert (px.cpu() - want).abs().max() <= 4e-3
+    assert px.shape == (B, 8, 2)
+
+
+def test_batch_edge_cases_and_determinism():
+    model, sd = gu.native_model(3, "bf16", max_batch=8)
+    x = golden_input(3, B=5, seed=9).cuda()
+    y5 = model(x)
+    y1 = torch.cat([model(x[i:i + 1]) for i in range(5)])
+    assert torch.equal(y5, y1), "per-frame results must not depend on the batch they ride in"
+    assert torch.equal(model(x), y5), "run-to-run determinism"
+    # growing past max_batch re-plans transparently
+    xb = golden_input(3, B=11, seed=9).cuda()
+    assert torch.equal(model(xb)[:5], y5)
+    # 3-D input (the streaming caller adds the batch dim itself; accept both)
+    assert torch.equal(model(x[0]), y5[0])
+    with pytest.raises(ValueError):
+        model(torch.rand(1, 4, 256, 256).cuda())
+
+
+def test_load_state_dict_refreshes_device_weights():
+    from perseus_b200.detector import KeypointCNN
+
+    m = KeypointCNN(precision="fp32", max_batch=2).eval().cuda()
+    x = golden_input(3, B=1).cuda()
+    y0 = m(x)
+    sd = do.seeded_state_dict(3, 8, seed=5)
+    m.load_state_dict(sd)
+    y1 = m(x)
+    assert not torch.equal(y0, y1)
+    assert gu.px_err(y1, do.reference_forward(sd, x.cpu()))[0] <= 1e-3
+
+
+def test_full_size_batch256_properties():
+    """BASELINE.json configs[1] size: batch 256 bf16.  Oracle-free properties: every frame equals
+    the same frame evaluated in a batch of 2; all outputs finite."""
+    model, _ = gu.native_model(3, "bf16", max_batch=256)
+    rgb = gu.synth_u8_frames(256, seed=11).cuda()
+    px = model.forward_frames(rgb)
+    assert px.shape == (256, 8, 2) and torch.isfinite(px).all()
+    for i in (0, 127, 254):
+        assert torch.equal(model.forward_frames(rgb[i:i + 2]), px[i:i + 2])
