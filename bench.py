@@ -1,0 +1,338 @@
+#!/usr/bin/env python
+"""Headline benchmark: keypoint frames/sec of the detector hot path (BASELINE.json metric).
+
+  python bench.py --gpus N --steps K --warmup W            # this repo's sm_100a path
+  python bench.py --impl reference --gpus N --steps K ...  # the reference's PyTorch CPU path
+
+Workload (BASELINE.json configs[1]): the default RGB keypoint detector, batch 256 per GPU, bf16,
+random-init weights (seeded, BN statistics randomised), synthetic uint8 frames 256x256x3.
+A step = ingest (u8 HWC -> frames) -> backbone -> head + pixel decode for one batch.
+  value : frames/s with the uint8 batch already resident in HBM (CUDA events, max over ranks)
+  e2e   : frames/s through the public API from PINNED HOST frames: H2D of the batch and D2H of the
+          keypoints inside the timed region
+N > 1: one process per GPU (torchrun), batch-sharded, no collective on the data path (weak scaling).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+BATCH = 256
+H = W = 256
+FLOPS_PER_FRAME_RGB = 4_737_482_752  # 2*MAC, unpadded, conv + fc
+METRIC = "keypoint_frames_per_sec_bs256_bf16"
+WORKLOAD = "RGB keypoint detector forward (ingest+backbone+head+decode), bs256/GPU, 256x256, bf16, random-init"
+
+
+def load_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
+            p = json.load(fh)
+        return {"hbm_gbs": float(p["hbm_gbs"]), "bf16_tflops": float(p["bf16_tflops"]),
+                "bf16_tflops_sustained": float(p.get("bf16_tflops_sustained", p["bf16_tflops"])),
+                "source": "measured (MEASURED_PEAKS.json)"}
+    except Exception:
+        return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0,
+                "source": "fallback (B200_PROFILING.md)"}
+
+
+class ClockSampler:
+    """Samples SM clocks / throttle reasons through NVML while the benchmark runs."""
+
+    def __init__(self, index: int):
+        self.index = index
+        self.samples = []
+        self.reasons = set()
+        self.max_mhz = None
+        self._stop = threading.Event()
+        self._thread = None
+        self.error = None
+
+    def start(self):
+        self._thread = threading.Thread(target=self._run, daemon=True)
+        self._thread.start()
+
+    def _run(self):
+        try:
+            import pynvml as nv
+
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            self.max_mhz = int(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))
+            names = {
+                "hw_slowdown": getattr(nv, "nvmlClocksThrottleReasonHwSlowdown", 0x8),
+                "hw_thermal_slowdown": getattr(nv, "nvmlClocksThrottleReasonHwThermalSlowdown", 0x40),
+                "sw_thermal_slowdown": getattr(nv, "nvmlClocksThrottleReasonSwThermalSlowdown", 0x20),
+                "sw_power_cap": getattr(nv, "nvmlClocksThrottleReasonSwPowerCap", 0x4),
+                "hw_power_brake": getattr(nv, "nvmlClocksThrottleReasonHwPowerBrakeSlowdown", 0x80),
+            }
+            while not self._stop.is_set():
+                self.samples.append(int(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)))
+                try:
+                    r = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(h))
+                    for k, bit in names.items():
+                        if r & bit:
+                            self.reasons.add(k)
+                except Exception:
+                    pass
+                time.sleep(0.01)
+        except Exception as e:  # NVML unavailable: fall back to one nvidia-smi query
+            self.error = repr(e)
+
+    def stop(self) -> dict:
+        self._stop.set()
+        if self._thread:
+            self._thread.join(timeout=2)
+        if not self.samples:
+            try:
+                import subprocess
+
+                out = subprocess.check_output(
+                    ["nvidia-smi", "-i", str(self.index), "--query-gpu=clocks.sm,clocks.max.sm",
+                     "--format=csv,noheader,nounits"], text=True, timeout=10)
+                a, b = [int(float(v)) for v in out.strip().split(",")]
+                return {"sm_mhz": a, "sm_max_mhz": b, "reasons": [], "samples": 1, "note": "idle nvidia-smi sample"}
+            except Exception:
+                return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0, "note": self.error}
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2], "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(s)}
+
+
+def cpu_reference_fps(frames: int, chunk: int, warmup_frames: int = 8):
+    """The reference's PyTorch CPU path (oracle port: same torchvision module tree, fp32, no_grad,
+    all host threads) on a bounded sample of the workload: u8 -> f32 ingest, forward, decode."""
+    import torch
+
+    from oracle import detector_oracle as do
+
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    sd = do.seeded_state_dict(3, 8, seed=0)
+    model = do.reference_keypoint_cnn(8, 3)
+    model.load_state_dict(sd)
+    model.eval()
+    g = torch.Generator().manual_seed(0)
+    rgb = torch.randint(0, 256, (max(chunk, warmup_frames), H, W, 3), dtype=torch.uint8, generator=g).numpy()
+
+    def run(n):
+        with torch.no_grad():
+            x = torch.from_numpy((rgb[:n].astype("float32").transpose(0, 3, 1, 2)) / 255.0)  # data.py:78,84
+            y = model(x)
+            return do.denormalize_pixel_coordinates(y.reshape(n, 8, 2), H, W)
+
+    run(warmup_frames)
+    t0 = time.perf_counter()
+    done = 0
+    while done < frames:
+        n = min(chunk, frames - done)
+        run(n)
+        done += n
+    dt = time.perf_counter() - t0
+    return done / dt, cores, dt
+
+
+def dist_env():
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    return rank, world, local
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU implementation on the host cores (rank 0 only)."""
+    rank, world, _ = dist_env()
+    if rank != 0:
+        return
+    chunk = 32
+    for _ in range(max(args.warmup, 0)):
+        cpu_reference_fps(chunk, chunk, warmup_frames=8)
+        break  # one warm pass is enough to page everything in (each pass costs seconds)
+    t_total, frames_total, cores = 0.0, 0, os.cpu_count() or 1
+    steps = max(1, args.steps)
+    # bounded: each step is a `chunk`-frame sample of the 256-frame batch; cap the wall time
+    budget_s = 120.0
+    done_steps = 0
+    for _ in range(steps):
+        fps, cores, dt = cpu_reference_fps(chunk, chunk, warmup_frames=1)
+        t_total += dt
+        frames_total += chunk
+        done_steps += 1
+        if t_total > budget_s:
+            break
+    fps = frames_total / t_total
+    line = {
+        "impl": "reference",
+        "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": args.gpus, "steps": done_steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * t_total / done_steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "note": "reference PyTorch CPU path (torchvision resnet18 module tree, "
+                   "fp32, no_grad); each step = a 32-frame sample of the batch"},
+        "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": "port",
+                         "sample": f"{done_steps} steps x {chunk} frames (u8->f32 ingest + forward + decode), fp32"},
+        "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def run_native(args):
+    import torch
+
+    rank, world, local = dist_env()
+    if world > 1:
+        import torch.distributed as dist
+
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", local))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — perseus_b200 has no CPU path (use --impl reference)")
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+
+    from oracle import detector_oracle as do  # weights generator only (seeded random init)
+    from perseus_b200.detector import KeypointCNN
+
+    sd = do.seeded_state_dict(3, 8, seed=0)
+    model = KeypointCNN(num_channels=3, precision="bf16", max_batch=BATCH)
+    model.load_state_dict(sd)
+    model.eval().to(dev)
+
+    # synthetic frames: NBUF distinct batches so consecutive steps never re-read a batch from L2
+    NBUF = 4
+    g = torch.Generator().manual_seed(1234 + rank)
+    host = [torch.randint(0, 256, (BATCH, H, W, 3), dtype=torch.uint8, generator=g).pin_memory() for _ in range(NBUF)]
+    devbuf = [h.to(dev) for h in host]
+    plan = model._plan(dev, BATCH)
+    frames = torch.empty(plan.frames_bytes(BATCH), dtype=torch.uint8, device=dev)
+    px_host = torch.empty((BATCH, 8, 2), dtype=torch.float32).pin_memory()
+
+    def step_resident(i):
+        model.ingest(devbuf[i % NBUF], out=frames)
+        return model.forward_ingested(frames, BATCH)[1]
+
+    dev_in = torch.empty_like(devbuf[0])
+
+    def step_e2e(i):
+        dev_in.copy_(host[i % NBUF], non_blocking=True)
+        model.ingest(dev_in, out=frames)
+        px = model.forward_ingested(frames, BATCH)[1]
+        px_host.copy_(px, non_blocking=True)
+        torch.cuda.current_stream().synchronize()  # the caller consumes the keypoints every step
+        return px_host
+
+    def barrier():
+        if world > 1:
+            import torch.distributed as dist
+
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(steps):
+            fn(i)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            import torch.distributed as dist
+
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        barrier()
+        return ms
+
+    sampler = ClockSampler(local)
+    sampler.start()
+    for i in range(max(args.warmup, 3)):
+        step_resident(i)
+    ms = timed(step_resident, args.steps)
+    for i in range(3):
+        step_e2e(i)
+    ms_e2e = timed(step_e2e, args.steps)
+    clocks = sampler.stop()
+
+    value = world * BATCH * args.steps / (ms * 1e-3)
+    e2e = world * BATCH * args.steps / (ms_e2e * 1e-3)
+
+    line = None
+    if rank == 0:
+        peaks = load_peaks()
+        # roofline of the dominant kernel family (the tcgen05 conv kernels): per-launch CUDA events
+        reps = 5
+        acc = None
+        for _ in range(reps):
+            rows = model.profile_ops(frames, BATCH)
+            acc = rows if acc is None else [(a[0], a[1] + b[1], a[2], a[3]) for a, b in zip(acc, rows)]
+        rows = [(n, t / reps, f, b) for n, t, f, b in acc]
+        conv = [r for r in rows if r[2] > 1e6]
+        conv_ms = sum(r[1] for r in conv)
+        conv_flops = sum(r[2] for r in conv)
+        tot_ms = sum(r[1] for r in rows)
+        achieved = conv_flops / (conv_ms * 1e-3) / 1e12
+        peak = peaks["bf16_tflops_sustained"]
+        roofline = {
+            "bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
+            "traffic": None,
+            "kernel": "conv_umma_kernel (21 launches/step: stem + 20 convs)",
+            "peak_source": peaks["source"] + ", sustained bf16 (kernel timed inside a long step); burst "
+                           f"{peaks['bf16_tflops']}",
+            "share_of_step": conv_ms / tot_ms,
+            "whole_step_frac": (BATCH * FLOPS_PER_FRAME_RGB / (ms / args.steps * 1e-3) / 1e12) / peak,
+            "per_op_ms": {n: round(t, 4) for n, t, _, _ in rows},
+        }
+        cpu_fps, cores, cpu_dt = cpu_reference_fps(256, 32)
+        launches_per_step = 1 + len(rows)
+        line = {
+            "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "global_batch": world * BATCH, "per_gpu_batch": BATCH,
+                       "parallelism": f"batch-sharded x{world}, no collective",
+                       "l2": f"inputs rotate over {NBUF} distinct batches ({NBUF * BATCH * H * W * 3 / 1e6:.0f} MB) "
+                             "and each step streams ~1.4 GB of activations (> 126 MB L2)"},
+            "clocks": clocks,
+            "e2e": {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": BATCH * H * W * 3,
+                    "d2h_bytes_per_step": BATCH * 8 * 2 * 4, "ms_per_step": ms_e2e / args.steps},
+            "gpu_launches": launches_per_step * args.steps,
+            "roofline": roofline,
+            "cpu_baseline": {"value": cpu_fps, "unit": "frames/s", "cores": cores, "kind": "port",
+                             "sample": f"256 frames in 32-frame batches, fp32, {cpu_dt:.1f} s (reference PyTorch "
+                                       "CPU path: u8->f32 ingest + torchvision resnet18 forward + decode)"},
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.barrier()
+        dist.destroy_process_group()
+    return line
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="native", choices=["native", "reference"])
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_native(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -156,6 +156,7 @@ extern "C" int pb200_factors_dynamics(const double* pose1, const double* ang_vel
                                       double* H2, double* H3, int64_t N, pb200_stream stream) {
   if (int rc = require_device()) return rc;
   PB_CHECK(N >= 0, "factors_dynamics: N < 0");
+  if (N == 0) return PB200_OK;  // empty batch: nothing to read or write
   PB_CHECK(pose1 && ang_vel1 && vel1 && pose2 && resid, "factors_dynamics: null input");
   const bool jac = H0 || H1 || H2 || H3;
   PB_CHECK(!jac || (H0 && H1 && H2 && H3), "factors_dynamics: pass all four Jacobians or none");
@@ -188,6 +189,7 @@ extern "C" int pb200_factors_projection(const double* poses, const double* meas,
                                         int P, pb200_stream stream) {
   if (int rc = require_device()) return rc;
   PB_CHECK(N >= 0 && P > 0, "factors_projection: bad N/P");
+  if (N == 0) return PB200_OK;
   PB_CHECK(poses && meas && pts_body && K5 && resid, "factors_projection: null input");
   if (N == 0) return PB200_OK;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -211,6 +213,7 @@ extern "C" int pb200_factors_constvel(const double* vel1, const double* vel2, do
                                       double* H0, double* H1, int64_t N, pb200_stream stream) {
   if (int rc = require_device()) return rc;
   PB_CHECK(N >= 0, "factors_constvel: N < 0");
+  if (N == 0) return PB200_OK;
   PB_CHECK(vel1 && vel2 && resid, "factors_constvel: null input");
   PB_CHECK((H0 == nullptr) == (H1 == nullptr), "factors_constvel: pass both Jacobians or none");
   if (N == 0) return PB200_OK;
