@@ -142,6 +142,15 @@ int pb200_debug_conv_bf16(const void* in_nhwc, int B, int H, int W, int Cin, con
                           const void* residual_nhwc_or_null, int relu, void* out_nhwc,
                           pb200_stream stream);
 
+/* Unit-test entries of the P8-layout kernels (allocate / synchronise — not product entries).
+ * P8 = bf16 [n][C/8][H+2][W+2][8] with a zero border.
+ *   pb200_debug_stem_pool : fused conv1+bn1+relu+maxpool of a loaded bf16 plan: frames -> P8 [B][8][H/4+2][W/4+2][8]
+ *   pb200_debug_conv_p8   : one 3x3/1 64->64 conv (+bias, +residual, ReLU) P8 -> P8 or NHWC; OIHW fp32 HOST weights */
+int pb200_debug_stem_pool(pb200_plan* plan, const void* frames, void* out_p8, int B, pb200_stream stream);
+int pb200_debug_conv_p8(const void* in_p8, int B, int H, int W, const float* w_oihw_host,
+                        const float* bias_host, const void* residual_p8_or_null, int relu, void* out,
+                        int out_nhwc, pb200_stream stream);
+
 /* ---- smoother factors (float64, batched) ---------------------------------------------- */
 
 /* KeypointProjectionFactor over N poses x P body points.

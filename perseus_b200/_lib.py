@@ -56,6 +56,10 @@ SIGNATURES = {
         [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_int,
          c_void_p, c_void_p],
     ),
+    "pb200_debug_stem_pool": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
+    "pb200_debug_conv_p8": (
+        c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p]
+    ),
     "pb200_factors_projection": (
         c_int,
         [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p],

@@ -122,6 +122,20 @@ __device__ __forceinline__ void tma_store_wait() {
   asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory");
 }
 
+
+// 1-D bulk copy global -> shared (TMA engine, no descriptor): dst/src 16-byte aligned, bytes % 16 == 0.
+__device__ __forceinline__ void bulk_load_1d(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+          smem_u32(dst)),
+      "l"(reinterpret_cast<uint64_t>(src)), "r"(bytes), "r"(smem_u32(bar))
+      : "memory");
+}
+// named barrier among `nthreads` threads of the CTA (id 1..15; 0 is __syncthreads)
+__device__ __forceinline__ void named_bar_sync(uint32_t id, uint32_t nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
 // tcgen05 / TMEM -------------------------------------------------------------------------------
 __device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem, uint32_t ncols) {
   asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
@@ -192,6 +206,19 @@ __device__ __forceinline__ uint64_t umma_desc_kmajor(uint32_t smem_addr, uint32_
   d |= static_cast<uint64_t>(1) << 46;  // descriptor version (Blackwell)
   d |= layout << 61;
   return d;
+}
+
+// K-major NO-SWIZZLE ("interleaved") shared-memory matrix descriptor.  The operand is made of
+// 8-row x 16-byte core matrices (128 contiguous bytes: row i at +16*i); LBO = byte distance between
+// core matrices adjacent in K, SBO = byte distance between 8-row groups adjacent in M/N.
+// Element (row m, k): start + (m/8)*SBO + (m%8)*16 + (k/8)*LBO + (k%8)*2.  start needs 16-byte alignment only.
+__device__ __forceinline__ uint64_t umma_desc_interleaved(uint32_t smem_addr, uint32_t lbo, uint32_t sbo) {
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((smem_addr & 0x3FFFFu) >> 4);
+  d |= static_cast<uint64_t>((lbo >> 4) & 0x3FFFu) << 16;
+  d |= static_cast<uint64_t>((sbo >> 4) & 0x3FFFu) << 32;
+  d |= static_cast<uint64_t>(1) << 46;  // descriptor version (Blackwell)
+  return d;                             // layout type 0 = no swizzle
 }
 // Instruction descriptor, kind::f16: D=f32, A=B=bf16, both K-major, M x N tile.
 __host__ __device__ constexpr uint32_t umma_idesc_bf16(uint32_t M, uint32_t N) {

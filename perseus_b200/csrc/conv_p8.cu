@@ -1,0 +1,284 @@
+// 3x3 stride-1 convolution 64 -> 64 channels (+ folded BN, residual add, ReLU) on the P8 layout:
+// layer1 of the detector's ResNet-18 (torchvision BasicBlock.forward, resnet.py:89-105, reached from
+// perseus/detector/models.py:34-40).  tcgen05 implicit GEMM in which NO operand is ever re-read:
+//
+//   * P8 = [n][C/8][H+2][W+2][8] bf16 with a zero border (layout.h).  Over the flattened padded plane
+//     a 3x3 conv is out[q] = sum_{r,s} in[q + r*(W+2) + s] . w[r][s], so one shared-memory patch of
+//     128 + 2(W+2) + 2 positions per 8-channel chunk serves all nine taps of a 128-position M tile: each tap
+//     is the same patch read through a no-swizzle K-major descriptor (row pitch 16 B, LBO = chunk
+//     pitch) whose start address is shifted by (r*(W+2) + s) * 16 bytes.  The two positions per row that
+//     fall on the border produce garbage accumulators and are stored as the zero border itself.
+//   * the whole folded weight tensor (64 x 576 bf16 = 72 KB) stays resident in shared memory.
+//   * L2 -> SM traffic per tile is 33.5 KB (one patch) instead of 9 x (16 KB + 8 KB) for a TMA-im2col
+//     implicit GEMM, which at N = 64 is L2-bandwidth-bound (profiles/README.md, r01 v0).
+//   * warp 0: producer (8 cp.async.bulk per patch, no tensor map); warp 1: 36 x tcgen05.mma
+//     (M128 N64 K16) per tile into one of two TMEM accumulators; warps 2..5: epilogue
+//     (TMEM -> +bias (+residual) -> ReLU -> bf16 -> 16-byte stores, lanes = consecutive positions so
+//     every store instruction of a warp is one contiguous 512-byte run in P8).
+#include "common.cuh"
+#include "layout.h"
+
+namespace pb200 {
+
+namespace {
+
+constexpr int kThreads = 192;
+constexpr int kStages = 4;
+constexpr int kChunks = 8;                       // Cin / 8
+constexpr int kWBytes = 64 * 576 * 2;            // 73728
+constexpr int kWSbo = 72 * 128;                  // 9216: bytes per 8-output-channel group
+
+struct ConvP8Params {
+  const uint8_t* in;        // P8 [B][8][H+2][W+2][8]
+  const uint8_t* wimg;      // 73728-byte shared-memory image
+  const float* bias;        // [64]
+  const uint8_t* residual;  // P8 or null
+  uint8_t* out;             // P8, or NHWC [B][H][W][64] when out_nhwc
+  int H, W, Wp;
+  int tiles_per_img, num_tiles;
+  int npos;                 // patch positions per chunk = 128 + 2*Wp + 2
+  int patch_pitch;          // bytes between chunk planes of a patch in shared memory (multiple of 128)
+  int relu, out_nhwc;
+  long long img_bytes;      // bytes per P8 image
+  long long plane_bytes;    // bytes per P8 chunk plane
+};
+
+__global__ void __launch_bounds__(kThreads, 1) conv_p8_kernel(const ConvP8Params p) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t full_bar[kStages];
+  __shared__ __align__(8) uint64_t empty_bar[kStages];
+  __shared__ __align__(8) uint64_t w_bar;
+  __shared__ __align__(8) uint64_t tmem_full_bar[2];
+  __shared__ __align__(8) uint64_t tmem_empty_bar[2];
+  __shared__ uint32_t tmem_base_slot;
+  __shared__ float s_bias[64];
+
+  const uint32_t raw_addr = smem_u32(smem_raw);
+  uint8_t* smem = smem_raw + (((raw_addr + 127u) & ~127u) - raw_addr);
+  uint8_t* s_w = smem;
+  uint8_t* s_patch = smem + kWBytes;
+  const int stage_bytes = kChunks * p.patch_pitch;
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int i = 0; i < kStages; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+    }
+    mbar_init(&w_bar, 1);
+    mbar_init(&tmem_full_bar[0], 1);
+    mbar_init(&tmem_full_bar[1], 1);
+    mbar_init(&tmem_empty_bar[0], 4);
+    mbar_init(&tmem_empty_bar[1], 4);
+    fence_barrier_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(&tmem_base_slot, 128);
+    tmem_relinquish();
+  }
+  if (threadIdx.x >= 64 && threadIdx.x < 128) s_bias[threadIdx.x - 64] = __ldg(p.bias + threadIdx.x - 64);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_slot;
+
+  if (warp == 0) {
+    // ================================ producer ====================================
+    if (lane == 0) {
+      mbar_expect_tx(&w_bar, kWBytes);
+      bulk_load_1d(s_w, p.wimg, kWBytes, &w_bar);
+      int stage = 0;
+      uint32_t phase = 0;
+      const uint32_t chunk_bytes = static_cast<uint32_t>(p.npos) * 16u;
+      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+        const int n = tile / p.tiles_per_img;
+        const int q0 = (tile - n * p.tiles_per_img) * 128;
+        const uint8_t* src = p.in + n * p.img_bytes + static_cast<long long>(q0) * 16;
+        mbar_wait(&empty_bar[stage], phase ^ 1u);
+        mbar_expect_tx(&full_bar[stage], chunk_bytes * kChunks);
+        uint8_t* dst = s_patch + stage * stage_bytes;
+#pragma unroll
+        for (int j = 0; j < kChunks; ++j)
+          bulk_load_1d(dst + j * p.patch_pitch, src + j * p.plane_bytes, chunk_bytes, &full_bar[stage]);
+        if (++stage == kStages) {
+          stage = 0;
+          phase ^= 1u;
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================================ MMA issuer ==================================
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(128, 64);
+      const uint32_t w_addr = smem_u32(s_w);
+      const uint32_t patch_addr = smem_u32(s_patch);
+      mbar_wait(&w_bar, 0);
+      int stage = 0;
+      uint32_t phase = 0;
+      int it = 0;
+      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+        const int acc = it & 1;
+        mbar_wait(&tmem_empty_bar[acc], ((it >> 1) & 1u) ^ 1u);
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * 64;
+        const uint32_t a_base = patch_addr + stage * stage_bytes;
+#pragma unroll
+        for (int t = 0; t < 9; ++t) {
+          const int r = t / 3, s = t - 3 * r;
+          const uint32_t a_tap = a_base + static_cast<uint32_t>(r * p.Wp + s) * 16u;
+#pragma unroll
+          for (int kk = 0; kk < 4; ++kk) {
+            const uint64_t adesc = umma_desc_interleaved(a_tap + 2 * kk * p.patch_pitch, p.patch_pitch, 128);
+            const uint64_t bdesc = umma_desc_interleaved(w_addr + (t * 8 + 2 * kk) * 128, 128, kWSbo);
+            umma_bf16(d_tmem, adesc, bdesc, idesc, (t | kk) != 0 ? 1u : 0u);
+          }
+        }
+        umma_commit(&empty_bar[stage]);
+        umma_commit(&tmem_full_bar[acc]);
+        if (++stage == kStages) {
+          stage = 0;
+          phase ^= 1u;
+        }
+      }
+    }
+  } else {
+    // ================================ epilogue ====================================
+    const int q = warp & 3;
+    const int m = q * 32 + lane;
+    const long long plane16 = p.plane_bytes / 16;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+      const int n = tile / p.tiles_per_img;
+      const int ti = tile - n * p.tiles_per_img;
+      const int q0 = ti * 128 + m;
+      const int h = q0 / p.Wp;
+      const int w = q0 - h * p.Wp;
+      const bool in_plane = q0 < p.H * p.Wp;
+      const bool valid = in_plane && w < p.W;
+      const int a = it & 1;
+      const long long opos = static_cast<long long>(q0) + p.Wp + 1;  // padded position of this output
+      // residual: issue all eight 16-byte loads BEFORE waiting for the accumulator so their latency hides behind the MMAs
+      uint4 rv[8];
+      const bool has_res = p.residual != nullptr;
+      if (has_res && valid) {
+        const uint4* res = reinterpret_cast<const uint4*>(p.residual + n * p.img_bytes) + opos;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) rv[j] = __ldg(res + j * plane16);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) rv[j] = make_uint4(0, 0, 0, 0);
+      }
+      mbar_wait(&tmem_full_bar[a], (it >> 1) & 1u);
+      tc_fence_after();
+      const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + a * 64;
+      uint32_t x0[32], x1[32];
+      tmem_ld_32x32(t_addr, x0);
+      tmem_ld_32x32(t_addr + 32, x1);
+      tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tmem_empty_bar[a]);
+
+      uint4 o[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const uint32_t* x = j < 4 ? &x0[8 * j] : &x1[8 * (j - 4)];
+        float f[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(x[e]) + s_bias[8 * j + e];
+        if (has_res) {
+          f[0] += bf16_lo(rv[j].x); f[1] += bf16_hi(rv[j].x);
+          f[2] += bf16_lo(rv[j].y); f[3] += bf16_hi(rv[j].y);
+          f[4] += bf16_lo(rv[j].z); f[5] += bf16_hi(rv[j].z);
+          f[6] += bf16_lo(rv[j].w); f[7] += bf16_hi(rv[j].w);
+        }
+        if (p.relu) {
+#pragma unroll
+          for (int e = 0; e < 8; ++e) f[e] = fmaxf(f[e], 0.f);
+        }
+        o[j] = valid ? make_uint4(pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]), pack_bf16x2(f[4], f[5]),
+                                  pack_bf16x2(f[6], f[7]))
+                     : make_uint4(0, 0, 0, 0);
+      }
+      if (p.out_nhwc) {
+        if (valid) {
+          uint4* dst = reinterpret_cast<uint4*>(p.out) + ((static_cast<long long>(n) * p.H + h) * p.W + w) * 8;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) dst[j] = o[j];
+        }
+      } else {
+        uint4* oimg = reinterpret_cast<uint4*>(p.out + n * p.img_bytes);
+        if (in_plane) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) oimg[j * plane16 + opos] = o[j];
+        }
+        // the zero border rows the flattened tiles do not reach
+        if (ti == 0 && m < p.Wp + 1) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) oimg[j * plane16 + m] = make_uint4(0, 0, 0, 0);
+        }
+        if (ti == p.tiles_per_img - 1 && m < p.Wp - 1) {
+          const long long bpos = static_cast<long long>(p.H + 1) * p.Wp + 1 + m;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) oimg[j * plane16 + bpos] = make_uint4(0, 0, 0, 0);
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 128);
+  }
+}
+
+constexpr int kMaxDynSmem = 227 * 1024 - 1024;  // the kernel also has ~400 B of static shared memory
+inline int patch_pitch_for(int Wp) { return ((128 + 2 * Wp + 2) * 16 + 127) / 128 * 128; }
+inline int smem_bytes_for(int Wp) { return kWBytes + kStages * kChunks * patch_pitch_for(Wp) + 128; }
+
+}  // namespace
+
+int conv_p8_init() {
+  static bool done = false;
+  if (done) return PB200_OK;
+  PB_CUDA(cudaFuncSetAttribute(conv_p8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem));
+  done = true;
+  return PB200_OK;
+}
+
+int launch_conv_p8(const void* in_p8, const void* wimg, const float* bias, const void* residual_p8, void* out,
+                   int out_nhwc, int relu, int B, int H, int W, cudaStream_t st) {
+  const int Wp = W + 2;
+  PB_CHECK(smem_bytes_for(Wp) <= kMaxDynSmem, "conv_p8: W = %d too wide for the resident-weight kernel", W);
+  PB_CHECK(Wp - 1 <= 128, "conv_p8: W = %d too wide for the border writer", W);
+  if (B == 0) return PB200_OK;
+  ConvP8Params p;
+  p.in = static_cast<const uint8_t*>(in_p8);
+  p.wimg = static_cast<const uint8_t*>(wimg);
+  p.bias = bias;
+  p.residual = static_cast<const uint8_t*>(residual_p8);
+  p.out = static_cast<uint8_t*>(out);
+  p.H = H;
+  p.W = W;
+  p.Wp = Wp;
+  p.tiles_per_img = (H * Wp + 127) / 128;
+  p.num_tiles = B * p.tiles_per_img;
+  p.npos = 128 + 2 * Wp + 2;
+  p.patch_pitch = patch_pitch_for(Wp);
+  p.relu = relu;
+  p.out_nhwc = out_nhwc;
+  p.plane_bytes = static_cast<long long>(p8_plane_elems(H, W)) * 16;
+  p.img_bytes = p.plane_bytes * 8;
+  const int grid = p.num_tiles < num_sms() ? p.num_tiles : num_sms();
+  conv_p8_kernel<<<grid, kThreads, smem_bytes_for(Wp), st>>>(p);
+  PB_CUDA(cudaGetLastError());
+  return PB200_OK;
+}
+
+}  // namespace pb200

@@ -1,6 +1,7 @@
 // Buffer layouts and internal launch interfaces shared by the kernels and the plan.
 #pragma once
 #include <cuda_runtime.h>
+#include <stddef.h>
 #include <stdint.h>
 
 namespace pb200 {
@@ -38,6 +39,37 @@ struct IngestArgs {
 int launch_ingest(const IngestArgs& a, void* out, bool bf16, cudaStream_t st);
 int launch_repack_nchw(const float* x, int C, int H, int W, int B, void* out, bool bf16,
                        cudaStream_t st);
+
+
+// ---- "P8" activation layout: [n][C/8][H+2][W+2][8] bf16, zero border --------------
+// One 16-byte element = 8 consecutive channels of one pixel; a channel-chunk plane is a dense
+// (H+2) x (W+2) image.  A 3x3/1 conv over the FLATTENED padded plane is out[q] = sum_{r,s} in[q + r*(W+2) + s] . w[r][s]
+// with q = h*(W+2) + w, so every filter tap is the same shared-memory patch read at a 16-byte-granular
+// offset through a no-swizzle K-major UMMA descriptor (row pitch 16 B, LBO = plane pitch).
+// Producers write the whole tensor (interior + zero border) every time.
+inline size_t p8_plane_elems(int H, int W) { return static_cast<size_t>(H + 2) * (W + 2); }
+inline size_t p8_image_bytes(int C, int H, int W) { return static_cast<size_t>(C / 8) * p8_plane_elems(H, W) * 16; }
+constexpr size_t kP8SlackBytes = 4096;  // the last tile of the last image reads 2 elements past the end
+
+// Fused stem: conv1 7x7/2 + folded BN + ReLU + maxpool 3x3/2 on the frames buffer -> P8 [B][8][66][66][8].
+// wimg: 28672-byte shared-memory image of the folded stem weights (no-swizzle K-major core-matrix
+// order, K = r*32 + s8*4 + c): element (co, k) at (co/8)*3584 + (k/8)*128 + (co%8)*16 + (k%8)*2.
+constexpr int kStemWimgBytes = 64 * kStemK * 2;
+inline size_t stem_wimg_offset(int co, int k) {
+  return static_cast<size_t>(co / 8) * (kStemK / 8 * 128) + static_cast<size_t>(k / 8) * 128 + (co % 8) * 16 + (k % 8) * 2;
+}
+int stem_pool_init();
+
+// conv_p8.cu: 3x3/1 conv 64 -> 64 on P8 with the weights resident in shared memory.
+// wimg: 73728-byte image, K = (r*3 + s)*64 + ci: element (co, k) at (co/8)*9216 + (k/8)*128 + (co%8)*16 + (k%8)*2.
+inline size_t conv_p8_wimg_offset(int co, int k) {
+  return static_cast<size_t>(co / 8) * 9216 + static_cast<size_t>(k / 8) * 128 + (co % 8) * 16 + (k % 8) * 2;
+}
+int conv_p8_init();
+int launch_conv_p8(const void* in_p8, const void* wimg, const float* bias, const void* residual_p8, void* out,
+                   int out_nhwc, int relu, int B, int H, int W, cudaStream_t st);
+int launch_stem_pool(const void* frames, const void* wimg, const float* bias, void* out_p8, int B, int H,
+                     int W, cudaStream_t st);
 
 // 3x3 stride-2 pad-1 max pooling, NHWC (C % 8 == 0 for bf16, % 4 for fp32).
 int launch_maxpool(const void* in, void* out, int B, int H, int W, int C, bool bf16, cudaStream_t st);

@@ -20,13 +20,14 @@ struct ConvSpec {
   int Cin, Cout, R, stride, pad;
   int Hin, Win, Ho, Wo;
   bool stem;
+  bool p8 = false;      // bf16 modes: weights packed as the resident shared-memory image of conv_p8.cu
   // device storage (offsets into the weight arena)
   size_t w_off = 0;     // packed weights
   size_t b_off = 0;     // fp32 bias [Cout]
   size_t w_bytes = 0;
 };
 
-enum OpKind { OP_REPACK, OP_CONV, OP_MAXPOOL, OP_HEAD };
+enum OpKind { OP_REPACK, OP_CONV, OP_MAXPOOL, OP_HEAD, OP_STEM_POOL, OP_CONV_P8 };
 
 struct Op {
   OpKind kind;
@@ -34,10 +35,12 @@ struct Op {
   int conv = -1;   // index into convs
   int in_buf = -1, out_buf = -1, res_buf = -1;  // activation buffer ids
   int relu = 0;
+  int out_nhwc = 0;  // OP_CONV_P8: write NHWC (hand-over to the TMA-im2col layers) instead of P8
 };
 
 // activation buffer ids
-enum { BUF_FRAMES = 0, BUF_STEM = 1, BUF_R0 = 2, BUF_R1 = 3, BUF_R2 = 4, BUF_R3 = 5, BUF_COUNT = 6 };
+enum { BUF_FRAMES = 0, BUF_STEM = 1, BUF_R0 = 2, BUF_R1 = 3, BUF_R2 = 4, BUF_R3 = 5, BUF_P8A = 6, BUF_P8B = 7,
+       BUF_P8C = 8, BUF_COUNT = 9 };
 
 }  // namespace pb200
 
@@ -95,20 +98,45 @@ static void build_graph(pb200_plan* pl) {
   add_conv(pl, "conv1", "bn1", pl->C, 64, 7, 2, 3, H, W, true);
   const int H1 = (H + 6 - 7) / 2 + 1, W1 = (W + 6 - 7) / 2 + 1;   // after conv1
   const int H2 = (H1 + 2 - 3) / 2 + 1, W2 = (W1 + 2 - 3) / 2 + 1; // after maxpool
-  if (pl->precision != PB200_PREC_FP32 || true) {
-    Op op;
-    op.kind = OP_CONV; op.name = "conv1+bn1+relu"; op.conv = 0; op.in_buf = BUF_FRAMES; op.out_buf = BUF_STEM; op.relu = 1;
-    pl->ops.push_back(op);
-  }
-  {
-    Op op;
-    op.kind = OP_MAXPOOL; op.name = "maxpool"; op.in_buf = BUF_STEM; op.out_buf = BUF_R0;
-    pl->ops.push_back(op);
-  }
   int cur = 0;  // rotating buffer index holding the block input
   int h = H2, w = W2, cin = 64;
   const int planes[4] = {64, 128, 256, 512};
-  for (int L = 0; L < 4; ++L) {
+  int first_layer = 0;
+  if (pl->bf16) {
+    // fused stem (conv1+bn1+relu+maxpool) and layer1 on the P8 layout (stem_pool.cu, conv_p8.cu)
+    {
+      Op op;
+      op.kind = OP_STEM_POOL; op.name = "conv1+bn1+relu+maxpool"; op.conv = 0; op.in_buf = BUF_FRAMES; op.out_buf = BUF_P8A;
+      pl->ops.push_back(op);
+    }
+    const int seq_in[4] = {BUF_P8A, BUF_P8B, BUF_P8C, BUF_P8B};
+    const int seq_out[4] = {BUF_P8B, BUF_P8C, BUF_P8B, BUF_R0};
+    const int seq_res[4] = {-1, BUF_P8A, -1, BUF_P8C};
+    for (int i = 0; i < 4; ++i) {
+      const std::string pre = "layer1." + std::to_string(i / 2);
+      const std::string cn = (i % 2) ? ".conv2" : ".conv1", bn = (i % 2) ? ".bn2" : ".bn1";
+      add_conv(pl, pre + cn, pre + bn, 64, 64, 3, 1, 1, H2, W2);
+      pl->convs.back().p8 = true;
+      Op op;
+      op.kind = OP_CONV_P8; op.name = pre + cn + "+bn" + ((i % 2) ? "+add+relu" : "+relu");
+      op.conv = static_cast<int>(pl->convs.size()) - 1;
+      op.in_buf = seq_in[i]; op.out_buf = seq_out[i]; op.res_buf = seq_res[i]; op.relu = 1; op.out_nhwc = (i == 3);
+      pl->ops.push_back(op);
+    }
+    first_layer = 1;
+  } else {
+    {
+      Op op;
+      op.kind = OP_CONV; op.name = "conv1+bn1+relu"; op.conv = 0; op.in_buf = BUF_FRAMES; op.out_buf = BUF_STEM; op.relu = 1;
+      pl->ops.push_back(op);
+    }
+    {
+      Op op;
+      op.kind = OP_MAXPOOL; op.name = "maxpool"; op.in_buf = BUF_STEM; op.out_buf = BUF_R0;
+      pl->ops.push_back(op);
+    }
+  }
+  for (int L = first_layer; L < 4; ++L) {
     for (int b = 0; b < 2; ++b) {
       const int cout = planes[L];
       const int stride = (L > 0 && b == 0) ? 2 : 1;
@@ -150,12 +178,20 @@ static void build_graph(pb200_plan* pl) {
   // buffers (bytes per frame)
   const size_t e = pl->elt;
   pl->buf_per_frame[BUF_FRAMES] = static_cast<size_t>(H + 6) * (W + 8) * 4 * e;
-  pl->buf_per_frame[BUF_STEM] = static_cast<size_t>(H1) * W1 * 64 * e;
-  for (int i = 0; i < 4; ++i) pl->buf_per_frame[BUF_R0 + i] = static_cast<size_t>(H2) * W2 * 64 * e;
+  if (pl->bf16) {
+    pl->buf_per_frame[BUF_STEM] = 0;  // the stem output never leaves the SM (fused maxpool)
+    pl->buf_per_frame[BUF_R0] = static_cast<size_t>(H2) * W2 * 64 * e;
+    for (int i = 1; i < 4; ++i) pl->buf_per_frame[BUF_R0 + i] = static_cast<size_t>(H2 / 2) * (W2 / 2) * 128 * e;
+    for (int i = 0; i < 3; ++i) pl->buf_per_frame[BUF_P8A + i] = p8_image_bytes(64, H2, W2);
+  } else {
+    pl->buf_per_frame[BUF_STEM] = static_cast<size_t>(H1) * W1 * 64 * e;
+    for (int i = 0; i < 4; ++i) pl->buf_per_frame[BUF_R0 + i] = static_cast<size_t>(H2) * W2 * 64 * e;
+  }
   size_t off = 0;
   for (int i = 0; i < BUF_COUNT; ++i) {
     pl->buf_off[i] = off;
-    off += align_up(pl->buf_per_frame[i] * pl->max_batch, 1024);
+    if (pl->buf_per_frame[i] == 0) continue;
+    off += align_up(pl->buf_per_frame[i] * pl->max_batch + (i >= BUF_P8A ? kP8SlackBytes : 0), 1024);
   }
   pl->workspace_bytes = off;
   // weight arena
@@ -216,7 +252,10 @@ extern "C" int pb200_plan_create(pb200_plan** out, int device, int max_batch, in
     return cuda_fail(e, "cudaMalloc(weight arena)", __FILE__, __LINE__);
   }
   if (pl->bf16) {
-    if (int rc = umma_conv_init()) {
+    int rc = umma_conv_init();
+    if (rc == PB200_OK) rc = stem_pool_init();
+    if (rc == PB200_OK) rc = conv_p8_init();
+    if (rc) {
       cudaFree(pl->arena);
       delete pl;
       return rc;
@@ -306,8 +345,10 @@ extern "C" int pb200_plan_load_weights(pb200_plan* plan, const float* const* ten
               k = (r * c.R + s) * c.Cin + ci;
             }
             if (plan->bf16) {
-              reinterpret_cast<uint16_t*>(host.data() + c.w_off)[static_cast<size_t>(co) * K + k] =
-                  f32_to_bf16_rne(static_cast<float>(v));
+              size_t off = (static_cast<size_t>(co) * K + k) * 2;  // [Cout][K] K-major rows (TMA-im2col kernels)
+              if (c.stem) off = stem_wimg_offset(co, k);
+              else if (c.p8) off = conv_p8_wimg_offset(co, k);
+              *reinterpret_cast<uint16_t*>(host.data() + c.w_off + off) = f32_to_bf16_rne(static_cast<float>(v));
             } else {
               reinterpret_cast<float*>(host.data() + c.w_off)[static_cast<size_t>(k) * c.Cout + co] =
                   static_cast<float>(v);
@@ -355,19 +396,14 @@ static int prepare(pb200_plan* pl, const void* frames, void* ws, int B) {
   for (const auto& op : pl->ops) {
     if (op.kind != OP_CONV) continue;
     const ConvSpec& c = pl->convs[op.conv];
+    if (c.stem) continue;  // bf16 stem = OP_STEM_POOL (no tensor maps)
     UmmaConvLaunch* L = &pl->umma[op.conv];
     const void* in = buf_ptr(pl, frames, ws, op.in_buf);
     void* out = buf_ptr(pl, frames, ws, op.out_buf);
     const void* res = op.res_buf >= 0 ? buf_ptr(pl, frames, ws, op.res_buf) : nullptr;
     const float* bias = reinterpret_cast<const float*>(pl->arena + c.b_off);
-    int rc;
-    if (c.stem) {
-      rc = build_umma_stem(L, in, B, pl->H, pl->W, pl->arena + c.w_off, bias, out, c.Cout);
-      L->flops = 2.0 * B * c.Ho * c.Wo * c.Cout * 49.0 * c.Cin;
-    } else {
-      rc = build_umma_conv(L, in, B, c.Hin, c.Win, c.Cin, pl->arena + c.w_off, bias, res, out, c.Cout,
-                           c.R, c.stride, c.pad, op.relu, choose_block_n(c, B));
-    }
+    int rc = build_umma_conv(L, in, B, c.Hin, c.Win, c.Cin, pl->arena + c.w_off, bias, res, out, c.Cout,
+                             c.R, c.stride, c.pad, op.relu, choose_block_n(c, B));
     if (rc) {
       pl->cache_B = -1;
       return rc;
@@ -398,6 +434,18 @@ static int run_op(pb200_plan* pl, const Op& op, const void* frames, void* ws, fl
         s.Hin = c.Hin; s.Win = c.Win; s.Cin = c.Cin; s.R = c.R; s.S = c.R; s.stride = c.stride; s.pad = c.pad;
       }
       return launch_conv_simt(s, st);
+    }
+    case OP_STEM_POOL: {
+      const ConvSpec& c = pl->convs[op.conv];
+      return launch_stem_pool(frames, pl->arena + c.w_off, reinterpret_cast<const float*>(pl->arena + c.b_off),
+                              buf_ptr(pl, frames, ws, op.out_buf), B, pl->H, pl->W, st);
+    }
+    case OP_CONV_P8: {
+      const ConvSpec& c = pl->convs[op.conv];
+      return launch_conv_p8(buf_ptr(pl, frames, ws, op.in_buf), pl->arena + c.w_off,
+                            reinterpret_cast<const float*>(pl->arena + c.b_off),
+                            op.res_buf >= 0 ? buf_ptr(pl, frames, ws, op.res_buf) : nullptr,
+                            buf_ptr(pl, frames, ws, op.out_buf), op.out_nhwc, op.relu, B, c.Hin, c.Win, st);
     }
     case OP_MAXPOOL: {
       const ConvSpec& c = pl->convs[0];
@@ -466,7 +514,12 @@ extern "C" int pb200_plan_op_work(const pb200_plan* plan, int i, int B, double* 
   const double e = static_cast<double>(plan->elt);
   *flops = 0.0;
   *bytes = 0.0;
-  if (op.kind == OP_CONV) {
+  if (op.kind == OP_STEM_POOL) {
+    const ConvSpec& c = plan->convs[op.conv];
+    *flops = 2.0 * B * c.Ho * c.Wo * c.Cout * c.R * c.R * c.Cin;
+    *bytes = e * (static_cast<double>(B) * (plan->H + 6) * (plan->W + 8) * 4 + B * (c.Ho / 2.0) * (c.Wo / 2.0) * c.Cout +
+                  static_cast<double>(c.Cout) * c.R * c.R * c.Cin);
+  } else if (op.kind == OP_CONV || op.kind == OP_CONV_P8) {
     const ConvSpec& c = plan->convs[op.conv];
     const double M = static_cast<double>(B) * c.Ho * c.Wo;
     *flops = 2.0 * M * c.Cout * c.R * c.R * c.Cin;
@@ -585,6 +638,45 @@ extern "C" int pb200_debug_conv_bf16(const void* in_nhwc, int B, int H, int W, i
   if (rc == PB200_OK) rc = launch_umma_conv(L, st);
   cudaError_t e = cudaStreamSynchronize(st);
   if (rc == PB200_OK && e != cudaSuccess) rc = cuda_fail(e, "debug_conv sync", __FILE__, __LINE__);
+  cudaFree(dw);
+  cudaFree(db);
+  return rc;
+}
+
+extern "C" int pb200_debug_stem_pool(pb200_plan* plan, const void* frames, void* out_p8, int B,
+                                     pb200_stream stream) {
+  PB_CHECK(plan && frames && out_p8 && plan->bf16 && plan->loaded, "debug_stem_pool: needs a loaded bf16 plan");
+  const ConvSpec& c = plan->convs[0];
+  return launch_stem_pool(frames, plan->arena + c.w_off, reinterpret_cast<const float*>(plan->arena + c.b_off),
+                          out_p8, B, plan->H, plan->W, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int pb200_debug_conv_p8(const void* in_p8, int B, int H, int W, const float* w_oihw_host,
+                                   const float* bias_host, const void* residual_p8_or_null, int relu,
+                                   void* out, int out_nhwc, pb200_stream stream) {
+  if (int rc = require_device()) return rc;
+  if (int rc = conv_p8_init()) return rc;
+  PB_CHECK(in_p8 && w_oihw_host && bias_host && out, "debug_conv_p8: null argument");
+  std::vector<uint8_t> img(64 * 576 * 2);
+  for (int co = 0; co < 64; ++co)
+    for (int ci = 0; ci < 64; ++ci)
+      for (int r = 0; r < 3; ++r)
+        for (int s = 0; s < 3; ++s)
+          *reinterpret_cast<uint16_t*>(img.data() + conv_p8_wimg_offset(co, (r * 3 + s) * 64 + ci)) =
+              f32_to_bf16_rne(w_oihw_host[((static_cast<size_t>(co) * 64 + ci) * 3 + r) * 3 + s]);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  void *dw = nullptr, *db = nullptr;
+  PB_CUDA(cudaMalloc(&dw, img.size()));
+  PB_CUDA(cudaMalloc(&db, sizeof(float) * 64));
+  int rc = PB200_OK;
+  if (cudaMemcpyAsync(dw, img.data(), img.size(), cudaMemcpyHostToDevice, st) != cudaSuccess ||
+      cudaMemcpyAsync(db, bias_host, sizeof(float) * 64, cudaMemcpyHostToDevice, st) != cudaSuccess)
+    rc = PB200_ERR_CUDA;
+  if (rc == PB200_OK)
+    rc = launch_conv_p8(in_p8, dw, static_cast<const float*>(db), residual_p8_or_null, out, out_nhwc, relu, B, H,
+                        W, st);
+  cudaError_t e = cudaStreamSynchronize(st);
+  if (rc == PB200_OK && e != cudaSuccess) rc = cuda_fail(e, "debug_conv_p8 sync", __FILE__, __LINE__);
   cudaFree(dw);
   cudaFree(db);
   return rc;

@@ -1,0 +1,294 @@
+// Fused stem of the detector: conv1 7x7/2 (+ folded BN) + ReLU + maxpool 3x3/2 in ONE tcgen05 kernel.
+// Replaces resnet.conv1 / bn1 / relu / maxpool (torchvision resnet.py:268-271; RGBD conv1 at
+// perseus/detector/models.py:27-28) of KeypointCNN.forward (models.py:34-40).
+//
+// GEMM view per conv output row: D[128 pixels][64 ch] = A[128][224] * Wt[64][224]^T with
+// K = (filter row r) x (8 taps) x (4 frame channels).  The frames buffer is [B][H+6][W+8][4] bf16 with
+// zero margins, so for filter row r the A row of output pixel wo is the 64 contiguous bytes of frames
+// row 2*ho + r starting at pixel 2*wo: consecutive output pixels are 16 B apart and OVERLAP.  That is
+// exactly a no-swizzle K-major UMMA operand whose core matrices (8 rows x 16 B, contiguous) are LBO = 16 B
+// apart along K and SBO = 128 B apart along M: the raw frame row in shared memory IS the im2col
+// operand; nothing is expanded or re-read.
+//
+//   * warp 0 (one thread): streams frame row-PAIRS (4224 contiguous bytes) into a 16-slot ring with
+//     cp.async.bulk (no tensor map); conv row c needs pairs c..c+3, pair c is released after row c.
+//   * warp 1 (one thread): 14 x tcgen05.mma (M128 N64 K16) per conv row into one of two TMEM
+//     accumulators; weights (28 KB image) stay resident in shared memory for the CTA's lifetime.
+//   * warps 2..5: epilogue.  Thread = conv column.  TMEM -> +bias, ReLU, bf16x2 pack -> horizontal
+//     3-max by warp shuffles (one 128-byte shared-memory hand-off per warp boundary) -> vertical
+//     running max in registers -> even lanes store the pooled pixel in the P8 layout (layout.h),
+//     borders included.  Post-ReLU values are >= 0, so the pool's -inf padding can be 0.
+//   * work unit = (image, band of PB pooled rows); a band recomputes one conv row of overlap.
+#include "common.cuh"
+#include "layout.h"
+
+namespace pb200 {
+
+namespace {
+
+constexpr int kThreads = 192;
+constexpr int kRowBytes = 2112;           // (256 + 8) px * 4 ch * 2 B
+constexpr int kPairBytes = 2 * kRowBytes; // 4224
+constexpr int kRing = 16;                 // row-pair slots
+constexpr int kBSbo = kStemK / 8 * 128;   // 3584: 8-channel groups of the weight image
+constexpr int kSmemW = 0;
+constexpr int kSmemRing = kStemWimgBytes;                     // 28672
+constexpr int kSmemXchg = kSmemRing + kRing * kPairBytes;     // + 67584
+constexpr int kSmemBias = kSmemXchg + 2 * 4 * 128;            // + 1024
+constexpr int kSmemTotal = kSmemBias + 64 * 4 + 128;          // + alignment slack
+
+struct StemPoolParams {
+  const uint8_t* frames;
+  const uint8_t* wimg;
+  const float* bias;
+  uint8_t* out;
+  int num_units, bands_per_img, PB, Hpool;  // Hpool = pooled rows per image (64)
+  long long frame_bytes, out_img_bytes;
+};
+
+__device__ __forceinline__ uint32_t hmax2_u32(uint32_t a, uint32_t b) {
+  __nv_bfloat162 r = __hmax2(*reinterpret_cast<__nv_bfloat162*>(&a), *reinterpret_cast<__nv_bfloat162*>(&b));
+  return *reinterpret_cast<uint32_t*>(&r);
+}
+
+__global__ void __launch_bounds__(kThreads, 1) stem_pool_kernel(const StemPoolParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t full_bar[kRing];
+  __shared__ __align__(8) uint64_t empty_bar[kRing];
+  __shared__ __align__(8) uint64_t w_bar;
+  __shared__ __align__(8) uint64_t tmem_full_bar[2];
+  __shared__ __align__(8) uint64_t tmem_empty_bar[2];
+  __shared__ uint32_t tmem_base_slot;
+
+  const uint32_t raw_addr = smem_u32(smem_raw);
+  uint8_t* smem = smem_raw + (((raw_addr + 127u) & ~127u) - raw_addr);
+  uint8_t* s_w = smem + kSmemW;
+  uint8_t* s_ring = smem + kSmemRing;
+  uint32_t* s_xchg = reinterpret_cast<uint32_t*>(smem + kSmemXchg);  // [2][4][32]
+  float* s_bias = reinterpret_cast<float*>(smem + kSmemBias);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int i = 0; i < kRing; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+    }
+    mbar_init(&w_bar, 1);
+    mbar_init(&tmem_full_bar[0], 1);
+    mbar_init(&tmem_full_bar[1], 1);
+    mbar_init(&tmem_empty_bar[0], 4);
+    mbar_init(&tmem_empty_bar[1], 4);
+    fence_barrier_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(&tmem_base_slot, 128);
+    tmem_relinquish();
+  }
+  if (threadIdx.x >= 64 && threadIdx.x < 128) s_bias[threadIdx.x - 64] = __ldg(p.bias + threadIdx.x - 64);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_slot;
+
+  if (warp == 0) {
+    // ================================ producer ====================================
+    if (lane == 0) {
+      mbar_expect_tx(&w_bar, kStemWimgBytes);
+      bulk_load_1d(s_w, p.wimg, kStemWimgBytes, &w_bar);
+      uint32_t G = 0;
+      for (int u = blockIdx.x; u < p.num_units; u += gridDim.x) {
+        const int n = u / p.bands_per_img;
+        const int band = u - n * p.bands_per_img;
+        const int c_start = band == 0 ? 0 : 2 * band * p.PB - 1;
+        const int n_pairs = 2 * p.PB + (band == 0 ? 0 : 1) + 3;
+        const uint8_t* src = p.frames + n * p.frame_bytes + static_cast<long long>(2 * c_start) * kRowBytes;
+        for (int g = 0; g < n_pairs; ++g, ++G) {
+          const uint32_t slot = G % kRing, ph = (G / kRing) & 1u;
+          mbar_wait(&empty_bar[slot], ph ^ 1u);
+          mbar_expect_tx(&full_bar[slot], kPairBytes);
+          bulk_load_1d(s_ring + slot * kPairBytes, src + static_cast<long long>(g) * kPairBytes, kPairBytes,
+                       &full_bar[slot]);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================================ MMA issuer ==================================
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(128, 64);
+      const uint32_t w_addr = smem_u32(s_w);
+      const uint32_t ring_addr = smem_u32(s_ring);
+      mbar_wait(&w_bar, 0);
+      uint32_t G = 0;
+      int it = 0;
+      for (int u = blockIdx.x; u < p.num_units; u += gridDim.x) {
+        const int band = u % p.bands_per_img;
+        const int n_conv = 2 * p.PB + (band == 0 ? 0 : 1);
+        for (uint32_t j = 0; j < 3; ++j) mbar_wait(&full_bar[(G + j) % kRing], ((G + j) / kRing) & 1u);
+        for (int i = 0; i < n_conv; ++i, ++it) {
+          const uint32_t Gi = G + i;
+          mbar_wait(&full_bar[(Gi + 3) % kRing], ((Gi + 3) / kRing) & 1u);
+          const int acc = it & 1;
+          mbar_wait(&tmem_empty_bar[acc], ((it >> 1) & 1u) ^ 1u);
+          tc_fence_after();
+          const uint32_t d_tmem = tmem_base + acc * 64;
+#pragma unroll
+          for (int r = 0; r < 7; ++r) {
+            const uint32_t row = ring_addr + ((Gi + (r >> 1)) % kRing) * kPairBytes + (r & 1) * kRowBytes;
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+              const uint64_t adesc = umma_desc_interleaved(row + h * 32, 16, 128);
+              const uint64_t bdesc = umma_desc_interleaved(w_addr + (r * 4 + h * 2) * 128, 128, kBSbo);
+              umma_bf16(d_tmem, adesc, bdesc, idesc, (r | h) != 0 ? 1u : 0u);
+            }
+          }
+          umma_commit(&tmem_full_bar[acc]);
+          umma_commit(&empty_bar[Gi % kRing]);
+        }
+        for (uint32_t j = 0; j < 3; ++j) umma_commit(&empty_bar[(G + n_conv + j) % kRing]);
+        G += n_conv + 3;
+      }
+    }
+  } else {
+    // ================================ epilogue ====================================
+    const int q = warp & 3;          // TMEM lane quarter
+    const int wo = q * 32 + lane;    // conv output column
+    const int et = wo;               // epilogue thread id 0..127 (for border writes)
+    constexpr int Wp8 = 66;          // padded pooled width
+    const long long plane = static_cast<long long>(p.Hpool + 2) * Wp8;  // elements (16 B) per chunk plane
+    int it = 0;
+    for (int u = blockIdx.x; u < p.num_units; u += gridDim.x) {
+      const int n = u / p.bands_per_img;
+      const int band = u - n * p.bands_per_img;
+      const int c_start = band == 0 ? 0 : 2 * band * p.PB - 1;
+      const int n_conv = 2 * p.PB + (band == 0 ? 0 : 1);
+      uint4* out_img = reinterpret_cast<uint4*>(p.out + n * p.out_img_bytes);
+      // top / bottom zero border rows of the P8 tensor
+      if (band == 0 && et < Wp8) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) out_img[j * plane + et] = make_uint4(0, 0, 0, 0);
+      }
+      if (band == p.bands_per_img - 1 && et < Wp8) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          out_img[j * plane + static_cast<long long>(p.Hpool + 1) * Wp8 + et] = make_uint4(0, 0, 0, 0);
+      }
+      uint32_t accv[32];
+#pragma unroll
+      for (int k = 0; k < 32; ++k) accv[k] = 0u;
+      for (int i = 0; i < n_conv; ++i, ++it) {
+        const int c = c_start + i;
+        const int a = it & 1;
+        mbar_wait(&tmem_full_bar[a], (it >> 1) & 1u);
+        tc_fence_after();
+        const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + a * 64;
+        uint32_t x0[32], x1[32];
+        tmem_ld_32x32(t_addr, x0);
+        tmem_ld_32x32(t_addr + 32, x1);
+        tmem_ld_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tmem_empty_bar[a]);
+        uint32_t v[32];
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+          const float2 b = *reinterpret_cast<const float2*>(s_bias + 2 * k);
+          v[k] = pack_bf16x2(fmaxf(__uint_as_float(x0[2 * k]) + b.x, 0.f),
+                             fmaxf(__uint_as_float(x0[2 * k + 1]) + b.y, 0.f));
+        }
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+          const float2 b = *reinterpret_cast<const float2*>(s_bias + 32 + 2 * k);
+          v[16 + k] = pack_bf16x2(fmaxf(__uint_as_float(x1[2 * k]) + b.x, 0.f),
+                                  fmaxf(__uint_as_float(x1[2 * k + 1]) + b.y, 0.f));
+        }
+        // hand the warp's last column to the next warp
+        uint32_t* xw = s_xchg + ((it & 1) * 4 + q) * 32;
+        if (lane == 31) {
+#pragma unroll
+          for (int k = 0; k < 8; ++k)
+            reinterpret_cast<uint4*>(xw)[k] = make_uint4(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
+        }
+        named_bar_sync(1, 128);
+        const uint32_t* xr = s_xchg + ((it & 1) * 4 + (q > 0 ? q - 1 : 0)) * 32;
+#pragma unroll
+        for (int k = 0; k < 32; ++k) {
+          uint32_t left = __shfl_up_sync(0xffffffffu, v[k], 1);
+          const uint32_t right = __shfl_down_sync(0xffffffffu, v[k], 1);
+          if (lane == 0) left = q > 0 ? xr[k] : 0u;
+          v[k] = hmax2_u32(hmax2_u32(left, v[k]), right);  // lane 31 (odd column) is never a pool centre
+        }
+        if (c & 1) {
+          // conv rows 2po-1, 2po, 2po+1 complete pooled row po = (c-1)/2 (owned by this band unless i == 0)
+          if (i > 0 || band == 0) {
+            const int po = (c - 1) >> 1;
+            uint4* orow = out_img + static_cast<long long>(po + 1) * Wp8;
+            if ((lane & 1) == 0) {
+              const int pw = wo >> 1;
+#pragma unroll
+              for (int j = 0; j < 8; ++j)
+                orow[j * plane + pw + 1] =
+                    make_uint4(hmax2_u32(accv[4 * j], v[4 * j]), hmax2_u32(accv[4 * j + 1], v[4 * j + 1]),
+                               hmax2_u32(accv[4 * j + 2], v[4 * j + 2]), hmax2_u32(accv[4 * j + 3], v[4 * j + 3]));
+            } else if (wo == 1 || wo == 127) {
+              const int col = wo == 1 ? 0 : Wp8 - 1;
+#pragma unroll
+              for (int j = 0; j < 8; ++j) orow[j * plane + col] = make_uint4(0, 0, 0, 0);
+            }
+          }
+#pragma unroll
+          for (int k = 0; k < 32; ++k) accv[k] = v[k];
+        } else {
+#pragma unroll
+          for (int k = 0; k < 32; ++k) accv[k] = hmax2_u32(accv[k], v[k]);
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 128);
+  }
+}
+
+}  // namespace
+
+int stem_pool_init() {
+  static bool done = false;
+  if (done) return PB200_OK;
+  PB_CUDA(cudaFuncSetAttribute(stem_pool_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
+  done = true;
+  return PB200_OK;
+}
+
+int launch_stem_pool(const void* frames, const void* wimg, const float* bias, void* out_p8, int B, int H,
+                     int W, cudaStream_t st) {
+  PB_CHECK(W == 256 && H % 4 == 0 && H >= 8, "stem_pool: needs W = 256 and H %% 4 == 0 (got %dx%d)", H, W);
+  if (B == 0) return PB200_OK;
+  const int Hpool = H / 4;
+  // pooled rows per band: the largest power of two that still gives every SM ~2 units
+  int PB = 16;
+  while (PB > 1 && (Hpool % PB != 0 || static_cast<long long>(B) * (Hpool / PB) < 2LL * num_sms())) PB >>= 1;
+  StemPoolParams p;
+  p.frames = static_cast<const uint8_t*>(frames);
+  p.wimg = static_cast<const uint8_t*>(wimg);
+  p.bias = bias;
+  p.out = static_cast<uint8_t*>(out_p8);
+  p.PB = PB;
+  p.Hpool = Hpool;
+  p.bands_per_img = Hpool / PB;
+  p.num_units = B * p.bands_per_img;
+  p.frame_bytes = static_cast<long long>(H + 6) * kRowBytes;
+  p.out_img_bytes = static_cast<long long>(p8_image_bytes(64, Hpool, 64));
+  const int grid = p.num_units < num_sms() ? p.num_units : num_sms();
+  stem_pool_kernel<<<grid, kThreads, kSmemTotal, st>>>(p);
+  PB_CUDA(cudaGetLastError());
+  return PB200_OK;
+}
+
+}  // namespace pb200

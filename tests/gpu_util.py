@@ -56,3 +56,20 @@ def frames_view(model, buf: torch.Tensor, B: int):
     dt = torch.bfloat16 if model.precision != "fp32" else torch.float32
     n = B * (model.H + 6) * (model.W + 8) * 4
     return buf.view(dt)[:n].view(B, model.H + 6, model.W + 8, 4)
+
+
+def nhwc_to_p8(x: torch.Tensor) -> torch.Tensor:
+    """(B, H, W, C) bf16 -> P8 (B, C/8, H+2, W+2, 8) bf16 with a zero border (csrc/layout.h)."""
+    B, H, W, C = x.shape
+    out = torch.zeros(B, C // 8, H + 2, W + 2, 8, dtype=x.dtype, device=x.device)
+    out[:, :, 1:-1, 1:-1] = x.view(B, H, W, C // 8, 8).permute(0, 3, 1, 2, 4)
+    return out
+
+
+def p8_to_nhwc(p: torch.Tensor):
+    """P8 -> ((B, H, W, C) interior, max |border|)."""
+    B, C8, Hp, Wp, _ = p.shape
+    border = p.clone().float()
+    border[:, :, 1:-1, 1:-1] = 0
+    x = p[:, :, 1:-1, 1:-1].permute(0, 2, 3, 1, 4).reshape(B, Hp - 2, Wp - 2, C8 * 8)
+    return x, float(border.abs().max())
