@@ -220,6 +220,37 @@ __device__ __forceinline__ uint64_t umma_desc_interleaved(uint32_t smem_addr, ui
   d |= static_cast<uint64_t>(1) << 46;  // descriptor version (Blackwell)
   return d;                             // layout type 0 = no swizzle
 }
+
+// ---- split (lo / hi word) descriptor helpers: the MMA-issuing warp keeps every operand warp-uniform
+// (so ptxas holds them in uniform registers and emits bare UTCHMMA, no per-instruction R2UR waterfall)
+// and advances a descriptor by adding (byte offset >> 4) to its low word.
+__device__ __forceinline__ uint32_t desc_lo(uint32_t smem_addr, uint32_t lbo_bytes) {
+  return ((smem_addr & 0x3FFFFu) >> 4) | (((lbo_bytes >> 4) & 0x3FFFu) << 16);
+}
+__device__ __forceinline__ uint32_t desc_hi_interleaved(uint32_t sbo_bytes) {
+  return ((sbo_bytes >> 4) & 0x3FFFu) | (1u << 14);  // SBO | descriptor version 1 | layout 0
+}
+__device__ __forceinline__ uint32_t desc_hi_swizzled(uint32_t swizzle_bytes) {
+  const uint32_t layout = (swizzle_bytes == 128u) ? 2u : (swizzle_bytes == 64u ? 4u : 6u);
+  return (((8u * swizzle_bytes) >> 4) & 0x3FFFu) | (1u << 14) | (layout << 29);
+}
+__device__ __forceinline__ void umma_bf16_split(uint32_t tmem_d, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo,
+                                                uint32_t b_hi, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      ".reg .b64 da, db;\n"
+      "setp.ne.b32 p, %6, 0;\n"
+      "mov.b64 da, {%1, %2};\n"
+      "mov.b64 db, {%3, %4};\n"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, p;\n"
+      "}\n" ::"r"(tmem_d),
+      "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// value of lane 0, provably warp-uniform for the compiler
+__device__ __forceinline__ uint32_t warp_uniform(uint32_t v) { return __shfl_sync(0xffffffffu, v, 0); }
+
 // Instruction descriptor, kind::f16: D=f32, A=B=bf16, both K-major, M x N tile.
 __host__ __device__ constexpr uint32_t umma_idesc_bf16(uint32_t M, uint32_t N) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((N >> 3) << 17) | ((M >> 4) << 24);

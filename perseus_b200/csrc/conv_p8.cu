@@ -87,62 +87,68 @@ __global__ void __launch_bounds__(kThreads, 1) conv_p8_kernel(const ConvP8Params
 
   if (warp == 0) {
     // ================================ producer ====================================
-    if (lane == 0) {
+    // the whole warp runs the loop (operands stay warp-uniform); one elected lane issues the copies
+    if (elect_one()) {
       mbar_expect_tx(&w_bar, kWBytes);
       bulk_load_1d(s_w, p.wimg, kWBytes, &w_bar);
-      int stage = 0;
-      uint32_t phase = 0;
-      const uint32_t chunk_bytes = static_cast<uint32_t>(p.npos) * 16u;
-      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
-        const int n = tile / p.tiles_per_img;
-        const int q0 = (tile - n * p.tiles_per_img) * 128;
-        const uint8_t* src = p.in + n * p.img_bytes + static_cast<long long>(q0) * 16;
-        mbar_wait(&empty_bar[stage], phase ^ 1u);
+    }
+    int stage = 0;
+    uint32_t phase = 0;
+    const uint32_t chunk_bytes = static_cast<uint32_t>(p.npos) * 16u;
+    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+      const int n = tile / p.tiles_per_img;
+      const int q0 = (tile - n * p.tiles_per_img) * 128;
+      const uint8_t* src = p.in + n * p.img_bytes + static_cast<long long>(q0) * 16;
+      mbar_wait(&empty_bar[stage], phase ^ 1u);
+      if (elect_one()) {
         mbar_expect_tx(&full_bar[stage], chunk_bytes * kChunks);
         uint8_t* dst = s_patch + stage * stage_bytes;
 #pragma unroll
         for (int j = 0; j < kChunks; ++j)
           bulk_load_1d(dst + j * p.patch_pitch, src + j * p.plane_bytes, chunk_bytes, &full_bar[stage]);
-        if (++stage == kStages) {
-          stage = 0;
-          phase ^= 1u;
-        }
+      }
+      __syncwarp();
+      if (++stage == kStages) {
+        stage = 0;
+        phase ^= 1u;
       }
     }
   } else if (warp == 1) {
     // ================================ MMA issuer ==================================
-    if (lane == 0) {
-      constexpr uint32_t idesc = umma_idesc_bf16(128, 64);
-      const uint32_t w_addr = smem_u32(s_w);
-      const uint32_t patch_addr = smem_u32(s_patch);
-      mbar_wait(&w_bar, 0);
-      int stage = 0;
-      uint32_t phase = 0;
-      int it = 0;
-      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
-        const int acc = it & 1;
-        mbar_wait(&tmem_empty_bar[acc], ((it >> 1) & 1u) ^ 1u);
-        mbar_wait(&full_bar[stage], phase);
-        tc_fence_after();
-        const uint32_t d_tmem = tmem_base + acc * 64;
-        const uint32_t a_base = patch_addr + stage * stage_bytes;
+    constexpr uint32_t idesc = umma_idesc_bf16(128, 64);
+    const uint32_t tm = warp_uniform(tmem_base);
+    const uint32_t a_hi = desc_hi_interleaved(128);
+    const uint32_t b_hi = desc_hi_interleaved(kWSbo);
+    const uint32_t b_lo0 = desc_lo(smem_u32(s_w), 128);
+    const uint32_t pitch16 = static_cast<uint32_t>(p.patch_pitch) >> 4;
+    mbar_wait(&w_bar, 0);
+    int stage = 0;
+    uint32_t phase = 0;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+      const int acc = it & 1;
+      mbar_wait(&tmem_empty_bar[acc], ((it >> 1) & 1u) ^ 1u);
+      mbar_wait(&full_bar[stage], phase);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint32_t d_tmem = tm + acc * 64;
+        const uint32_t a_lo0 = desc_lo(smem_u32(s_patch) + stage * stage_bytes, p.patch_pitch);
 #pragma unroll
         for (int t = 0; t < 9; ++t) {
           const int r = t / 3, s = t - 3 * r;
-          const uint32_t a_tap = a_base + static_cast<uint32_t>(r * p.Wp + s) * 16u;
+          const uint32_t a_tap = a_lo0 + static_cast<uint32_t>(r * p.Wp + s);  // (r*Wp + s) * 16 B >> 4
 #pragma unroll
-          for (int kk = 0; kk < 4; ++kk) {
-            const uint64_t adesc = umma_desc_interleaved(a_tap + 2 * kk * p.patch_pitch, p.patch_pitch, 128);
-            const uint64_t bdesc = umma_desc_interleaved(w_addr + (t * 8 + 2 * kk) * 128, 128, kWSbo);
-            umma_bf16(d_tmem, adesc, bdesc, idesc, (t | kk) != 0 ? 1u : 0u);
-          }
+          for (int kk = 0; kk < 4; ++kk)
+            umma_bf16_split(d_tmem, a_tap + 2 * kk * pitch16, a_hi, b_lo0 + (t * 8 + 2 * kk) * 8, b_hi, idesc,
+                            (t | kk) != 0 ? 1u : 0u);
         }
         umma_commit(&empty_bar[stage]);
         umma_commit(&tmem_full_bar[acc]);
-        if (++stage == kStages) {
-          stage = 0;
-          phase ^= 1u;
-        }
+      }
+      __syncwarp();
+      if (++stage == kStages) {
+        stage = 0;
+        phase ^= 1u;
       }
     }
   } else {

@@ -9,10 +9,8 @@
 //     lands a 128 x 64 bf16 K-major SWIZZLE_128B operand tile in shared memory; out-of-image
 //     taps are zero-filled by TMA's bounds check (the conv's zero padding).  Stride-2 layers use
 //     four parity-split views of the input (even/odd rows x even/odd cols), one per tap parity.
-//   * the stem reads the zero-margined frames buffer: a K block is one filter row = 8 taps x 4
-//     channels = 32 contiguous bf16 per output pixel, pixels 16 B apart (overlapping TMA rows),
-//     SWIZZLE_64B tiles.
-//   * warp roles (192 threads): warp 0 = TMA producer, warp 1 = MMA issuer (one thread) + TMEM
+//   * (the stem and layer1 do not use this kernel: stem_pool.cu / conv_p8.cu)
+//   * warp roles (192 threads): warp 0 = TMA producer, warp 1 = MMA issuer (one elected lane) + TMEM
 //     owner, warps 2..5 = epilogue (TMEM -> registers -> bias/residual/ReLU -> bf16 NHWC).
 //   * persistent CTAs (grid = #SMs), static tile round-robin, smem ring of kStages stages,
 //     two TMEM accumulators so the epilogue of tile i overlaps the MMAs of tile i+1.
@@ -83,83 +81,82 @@ conv_umma_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams
 
   if (warp == 0) {
     // ================================ TMA producer ================================
-    if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
-        const int m_tile = tile / p.num_n_tiles;
-        const int n_tile = tile - m_tile * p.num_n_tiles;
-        int n0, ho0;
-        if (p.stem) {
-          n0 = m_tile / p.Ho;
-          ho0 = m_tile - n0 * p.Ho;
-        } else if (p.tiles_per_img > 0) {
-          n0 = m_tile / p.tiles_per_img;
-          ho0 = (m_tile - n0 * p.tiles_per_img) * p.bh;
-        } else {
-          n0 = m_tile * p.imgs_per_tile;
-          ho0 = 0;
-        }
-        for (int kb = 0; kb < p.num_kblocks; ++kb) {
-          mbar_wait(&empty_bar[stage], phase ^ 1u);
+    // the whole warp runs the loop so every operand stays warp-uniform; one elected lane issues
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+      const int m_tile = tile / p.num_n_tiles;
+      const int n_tile = tile - m_tile * p.num_n_tiles;
+      int n0, ho0;
+      if (p.tiles_per_img > 0) {
+        n0 = m_tile / p.tiles_per_img;
+        ho0 = (m_tile - n0 * p.tiles_per_img) * p.bh;
+      } else {
+        n0 = m_tile * p.imgs_per_tile;
+        ho0 = 0;
+      }
+      int r = 0, s = 0, cb = 0;
+      for (int kb = 0; kb < p.num_kblocks; ++kb) {
+        mbar_wait(&empty_bar[stage], phase ^ 1u);
+        if (elect_one()) {
           mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
           uint8_t* a_dst = smem_a + stage * Cfg::kABytes;
           uint8_t* b_dst = smem_b + stage * Cfg::kBBytes;
-          if (p.stem) {
-            // one filter row: frames row 2*ho + r, all 128 output columns, 32 elements each
-            tma_load_4d(a_dst, &maps.a[0], &full_bar[stage], 0, 0, 2 * ho0 + kb, n0);
-          } else {
-            const int tap = kb / p.cblocks;
-            const int cb = kb - tap * p.cblocks;
-            const int r = tap / p.S;
-            const int s = tap - r * p.S;
-            int dh = r - p.pad, dw = s - p.pad, mi = 0;
-            if (p.stride == 2) {
-              const int hp = dh & 1, wp = dw & 1;
-              dh = (dh - hp) >> 1;
-              dw = (dw - wp) >> 1;
-              mi = hp * 2 + wp;
-            }
-            tma_load_4d(a_dst, &maps.a[mi], &full_bar[stage], cb * 64, dw, ho0 + dh, n0);
+          int dh = r - p.pad, dw = s - p.pad, mi = 0;
+          if (p.stride == 2) {
+            const int hp = dh & 1, wp = dw & 1;
+            dh = (dh - hp) >> 1;
+            dw = (dw - wp) >> 1;
+            mi = hp * 2 + wp;
           }
+          tma_load_4d(a_dst, &maps.a[mi], &full_bar[stage], cb * 64, dw, ho0 + dh, n0);
           tma_load_2d(b_dst, &maps.b, &full_bar[stage], kb * Cfg::kBlockK, n_tile * BLOCK_N);
-          if (++stage == kStages) {
-            stage = 0;
-            phase ^= 1u;
+        }
+        __syncwarp();
+        if (++cb == p.cblocks) {
+          cb = 0;
+          if (++s == p.S) {
+            s = 0;
+            ++r;
           }
+        }
+        if (++stage == kStages) {
+          stage = 0;
+          phase ^= 1u;
         }
       }
     }
   } else if (warp == 1) {
     // ================================ MMA issuer ==================================
-    if (lane == 0) {
-      constexpr uint32_t idesc = umma_idesc_bf16(kTileM, BLOCK_N);
-      int stage = 0;
-      uint32_t phase = 0;
-      int it = 0;
-      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
-        const int acc = it & 1;
-        const uint32_t acc_phase = (it >> 1) & 1;
-        mbar_wait(&tmem_empty_bar[acc], acc_phase ^ 1u);
+    constexpr uint32_t idesc = umma_idesc_bf16(kTileM, BLOCK_N);
+    const uint32_t tm = warp_uniform(tmem_base);
+    const uint32_t d_hi = desc_hi_swizzled(SW);
+    int stage = 0;
+    uint32_t phase = 0;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+      const int acc = it & 1;
+      const uint32_t acc_phase = (it >> 1) & 1;
+      mbar_wait(&tmem_empty_bar[acc], acc_phase ^ 1u);
+      tc_fence_after();
+      const uint32_t d_tmem = tm + acc * BLOCK_N;
+      for (int kb = 0; kb < p.num_kblocks; ++kb) {
+        mbar_wait(&full_bar[stage], phase);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + acc * BLOCK_N;
-        for (int kb = 0; kb < p.num_kblocks; ++kb) {
-          mbar_wait(&full_bar[stage], phase);
-          tc_fence_after();
-          const uint64_t adesc = umma_desc_kmajor(smem_u32(smem_a + stage * Cfg::kABytes), SW);
-          const uint64_t bdesc = umma_desc_kmajor(smem_u32(smem_b + stage * Cfg::kBBytes), SW);
+        if (elect_one()) {
+          const uint32_t a_lo = desc_lo(smem_u32(smem_a + stage * Cfg::kABytes), 16);
+          const uint32_t b_lo = desc_lo(smem_u32(smem_b + stage * Cfg::kBBytes), 16);
 #pragma unroll
-          for (int k = 0; k < Cfg::kKSteps; ++k) {
+          for (int k = 0; k < Cfg::kKSteps; ++k)
             // advancing K by 16 elements = 32 bytes inside the swizzle span: +2 in the address field
-            umma_bf16(d_tmem, adesc + static_cast<uint64_t>(2 * k), bdesc + static_cast<uint64_t>(2 * k),
-                      idesc, (kb | k) != 0 ? 1u : 0u);
-          }
+            umma_bf16_split(d_tmem, a_lo + 2 * k, d_hi, b_lo + 2 * k, d_hi, idesc, (kb | k) != 0 ? 1u : 0u);
           umma_commit(&empty_bar[stage]);  // frees the smem stage once these MMAs have read it
           if (kb == p.num_kblocks - 1) umma_commit(&tmem_full_bar[acc]);
-          if (++stage == kStages) {
-            stage = 0;
-            phase ^= 1u;
-          }
+        }
+        __syncwarp();
+        if (++stage == kStages) {
+          stage = 0;
+          phase ^= 1u;
         }
       }
     }
@@ -250,7 +247,6 @@ int umma_conv_init() {
   if (int rc = set_attr<64, 128>()) return rc;
   if (int rc = set_attr<128, 128>()) return rc;
   if (int rc = set_attr<256, 128>()) return rc;
-  if (int rc = set_attr<64, 64>()) return rc;
   done = true;
   return PB200_OK;
 }
@@ -334,54 +330,9 @@ int build_umma_conv(UmmaConvLaunch* L, const void* in, int B, int Hin, int Win, 
   return encode_weight_map(&L->maps.b, wpacked, Cout, R * R * Cin, block_n, 128);
 }
 
-int build_umma_stem(UmmaConvLaunch* L, const void* frames, int B, int H, int W, const void* wpacked,
-                    const float* bias, void* out, int Cout) {
-  const int Ho = H / 2, Wo = W / 2;
-  PB_CHECK(Wo == kTileM, "umma stem: needs W = 256 (one 128-pixel output row per tile), got W=%d", W);
-  PB_CHECK(H % 2 == 0, "umma stem: odd H");
-  PB_CHECK(Cout == 64, "umma stem: Cout must be 64");
-  const int Hp = H + 6, Wp = W + 8;
-  memset(L, 0, sizeof(*L));
-  UmmaConvParams& p = L->p;
-  const long long M = static_cast<long long>(B) * Ho * Wo;
-  p.M_total = static_cast<int>(M);
-  p.Cout = Cout;
-  p.stem = 1;
-  p.Ho = Ho;
-  p.Wo = Wo;
-  p.tiles_per_img = Ho;
-  p.imgs_per_tile = 1;
-  p.bh = 1;
-  p.stride = 2;
-  p.pad = 0;
-  p.S = 8;
-  p.cblocks = 1;
-  p.num_kblocks = 7;
-  p.num_n_tiles = 1;
-  p.num_tiles = B * Ho;
-  p.relu = 1;
-  p.bias = bias;
-  p.residual = nullptr;
-  p.out = out;
-  L->block_n = 64;
-  L->sw = 64;
-  L->grid = p.num_tiles < num_sms() ? p.num_tiles : num_sms();
-  L->flops = 0.0;  // filled by the plan (depends on the real channel count)
-  // virtual tensor V[n][row][wo][j] = frames[n][row][2*wo + j/4][j%4], j in [0,32):
-  // element strides (1, 8, Wp*4, Hp*Wp*4) -> overlapping 64-byte rows, 16 bytes apart.
-  const uint64_t dims[4] = {32, (uint64_t)Wo, (uint64_t)Hp, (uint64_t)B};
-  const uint64_t str[3] = {16, (uint64_t)Wp * 8, (uint64_t)Hp * Wp * 8};
-  const uint32_t box[4] = {32, (uint32_t)Wo, 1, 1};
-  if (int rc = encode_tma_bf16(&L->maps.a[0], frames, 4, dims, str, box, 64)) return rc;
-  for (int i = 1; i < 4; ++i) L->maps.a[i] = L->maps.a[0];
-  return encode_weight_map(&L->maps.b, wpacked, Cout, 224, 64, 64);
-}
-
 int launch_umma_conv(const UmmaConvLaunch& L, cudaStream_t st) {
   if (L.p.num_tiles == 0) return PB200_OK;
-  if (L.sw == 64) {
-    conv_umma_kernel<64, 64><<<L.grid, kUmmaThreads, UmmaCfg<64, 64>::kSmemBytes, st>>>(L.maps, L.p);
-  } else if (L.block_n == 64) {
+  if (L.block_n == 64) {
     conv_umma_kernel<64, 128><<<L.grid, kUmmaThreads, UmmaCfg<64, 128>::kSmemBytes, st>>>(L.maps, L.p);
   } else if (L.block_n == 128) {
     conv_umma_kernel<128, 128><<<L.grid, kUmmaThreads, UmmaCfg<128, 128>::kSmemBytes, st>>>(L.maps, L.p);

@@ -15,7 +15,7 @@ struct UmmaConvParams {
   int num_tiles, num_n_tiles, num_kblocks;
   int M_total;  // B*Ho*Wo output pixels
   int Cout;
-  int stem;     // 1: A rows come from the frames buffer (7 k-blocks = 7 filter rows)
+  int stem;     // unused (kept 0)
   int Ho, Wo;
   int tiles_per_img;  // Ho*Wo/128 when >= 1, else 0
   int imgs_per_tile;  // 128/(Ho*Wo) when the image is smaller than a tile, else 1
@@ -41,9 +41,6 @@ struct UmmaConvLaunch {
 int build_umma_conv(UmmaConvLaunch* L, const void* in, int B, int Hin, int Win, int Cin,
                     const void* wpacked, const float* bias, const void* residual, void* out, int Cout,
                     int R, int stride, int pad, int relu, int block_n);
-// Stem 7x7/2 on the frames buffer [B][H+6][W+8][4] bf16.  wpacked: bf16 [64][224], K = r*32+s8*4+c.
-int build_umma_stem(UmmaConvLaunch* L, const void* frames, int B, int H, int W, const void* wpacked,
-                    const float* bias, void* out, int Cout);
 int launch_umma_conv(const UmmaConvLaunch& L, cudaStream_t st);
 int umma_conv_init();  // sets the dynamic shared-memory attributes once per process
 

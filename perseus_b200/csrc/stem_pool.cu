@@ -95,61 +95,71 @@ __global__ void __launch_bounds__(kThreads, 1) stem_pool_kernel(const StemPoolPa
 
   if (warp == 0) {
     // ================================ producer ====================================
-    if (lane == 0) {
+    // whole warp runs the loop (warp-uniform operands); one elected lane issues the copies
+    if (elect_one()) {
       mbar_expect_tx(&w_bar, kStemWimgBytes);
       bulk_load_1d(s_w, p.wimg, kStemWimgBytes, &w_bar);
-      uint32_t G = 0;
-      for (int u = blockIdx.x; u < p.num_units; u += gridDim.x) {
-        const int n = u / p.bands_per_img;
-        const int band = u - n * p.bands_per_img;
-        const int c_start = band == 0 ? 0 : 2 * band * p.PB - 1;
-        const int n_pairs = 2 * p.PB + (band == 0 ? 0 : 1) + 3;
-        const uint8_t* src = p.frames + n * p.frame_bytes + static_cast<long long>(2 * c_start) * kRowBytes;
-        for (int g = 0; g < n_pairs; ++g, ++G) {
-          const uint32_t slot = G % kRing, ph = (G / kRing) & 1u;
-          mbar_wait(&empty_bar[slot], ph ^ 1u);
+    }
+    uint32_t G = 0;
+    for (int u = blockIdx.x; u < p.num_units; u += gridDim.x) {
+      const int n = u / p.bands_per_img;
+      const int band = u - n * p.bands_per_img;
+      const int c_start = band == 0 ? 0 : 2 * band * p.PB - 1;
+      const int n_pairs = 2 * p.PB + (band == 0 ? 0 : 1) + 3;
+      const uint8_t* src = p.frames + n * p.frame_bytes + static_cast<long long>(2 * c_start) * kRowBytes;
+      for (int g = 0; g < n_pairs; ++g, ++G) {
+        const uint32_t slot = G % kRing, ph = (G / kRing) & 1u;
+        mbar_wait(&empty_bar[slot], ph ^ 1u);
+        if (elect_one()) {
           mbar_expect_tx(&full_bar[slot], kPairBytes);
           bulk_load_1d(s_ring + slot * kPairBytes, src + static_cast<long long>(g) * kPairBytes, kPairBytes,
                        &full_bar[slot]);
         }
+        __syncwarp();
       }
     }
   } else if (warp == 1) {
     // ================================ MMA issuer ==================================
-    if (lane == 0) {
-      constexpr uint32_t idesc = umma_idesc_bf16(128, 64);
-      const uint32_t w_addr = smem_u32(s_w);
-      const uint32_t ring_addr = smem_u32(s_ring);
-      mbar_wait(&w_bar, 0);
-      uint32_t G = 0;
-      int it = 0;
-      for (int u = blockIdx.x; u < p.num_units; u += gridDim.x) {
-        const int band = u % p.bands_per_img;
-        const int n_conv = 2 * p.PB + (band == 0 ? 0 : 1);
-        for (uint32_t j = 0; j < 3; ++j) mbar_wait(&full_bar[(G + j) % kRing], ((G + j) / kRing) & 1u);
-        for (int i = 0; i < n_conv; ++i, ++it) {
-          const uint32_t Gi = G + i;
-          mbar_wait(&full_bar[(Gi + 3) % kRing], ((Gi + 3) / kRing) & 1u);
-          const int acc = it & 1;
-          mbar_wait(&tmem_empty_bar[acc], ((it >> 1) & 1u) ^ 1u);
-          tc_fence_after();
-          const uint32_t d_tmem = tmem_base + acc * 64;
+    constexpr uint32_t idesc = umma_idesc_bf16(128, 64);
+    const uint32_t tm = warp_uniform(tmem_base);
+    const uint32_t a_hi = desc_hi_interleaved(128);
+    const uint32_t b_hi = desc_hi_interleaved(kBSbo);
+    const uint32_t b_lo0 = desc_lo(smem_u32(s_w), 128);
+    const uint32_t ring_addr = smem_u32(s_ring);
+    mbar_wait(&w_bar, 0);
+    uint32_t G = 0;
+    int it = 0;
+    for (int u = blockIdx.x; u < p.num_units; u += gridDim.x) {
+      const int band = u % p.bands_per_img;
+      const int n_conv = 2 * p.PB + (band == 0 ? 0 : 1);
+      for (uint32_t j = 0; j < 3; ++j) mbar_wait(&full_bar[(G + j) % kRing], ((G + j) / kRing) & 1u);
+      for (int i = 0; i < n_conv; ++i, ++it) {
+        const uint32_t Gi = G + i;
+        mbar_wait(&full_bar[(Gi + 3) % kRing], ((Gi + 3) / kRing) & 1u);
+        const int acc = it & 1;
+        mbar_wait(&tmem_empty_bar[acc], ((it >> 1) & 1u) ^ 1u);
+        tc_fence_after();
+        if (elect_one()) {
+          const uint32_t d_tmem = tm + acc * 64;
 #pragma unroll
           for (int r = 0; r < 7; ++r) {
             const uint32_t row = ring_addr + ((Gi + (r >> 1)) % kRing) * kPairBytes + (r & 1) * kRowBytes;
+            const uint32_t a_lo = desc_lo(row, 16);
 #pragma unroll
-            for (int h = 0; h < 2; ++h) {
-              const uint64_t adesc = umma_desc_interleaved(row + h * 32, 16, 128);
-              const uint64_t bdesc = umma_desc_interleaved(w_addr + (r * 4 + h * 2) * 128, 128, kBSbo);
-              umma_bf16(d_tmem, adesc, bdesc, idesc, (r | h) != 0 ? 1u : 0u);
-            }
+            for (int h = 0; h < 2; ++h)
+              umma_bf16_split(d_tmem, a_lo + 2 * h, a_hi, b_lo0 + (r * 4 + h * 2) * 8, b_hi, idesc,
+                              (r | h) != 0 ? 1u : 0u);
           }
           umma_commit(&tmem_full_bar[acc]);
           umma_commit(&empty_bar[Gi % kRing]);
         }
-        for (uint32_t j = 0; j < 3; ++j) umma_commit(&empty_bar[(G + n_conv + j) % kRing]);
-        G += n_conv + 3;
+        __syncwarp();
       }
+      if (elect_one()) {
+        for (uint32_t j = 0; j < 3; ++j) umma_commit(&empty_bar[(G + n_conv + j) % kRing]);
+      }
+      __syncwarp();
+      G += n_conv + 3;
     }
   } else {
     // ================================ epilogue ====================================
