@@ -157,6 +157,29 @@ __global__ void __launch_bounds__(kThreads, 1) conv_p8_kernel(const ConvP8Params
     const int m = q * 32 + lane;
     const long long plane16 = p.plane_bytes / 16;
     int it = 0;
+    const bool has_res = p.residual != nullptr;
+    // residual tile of THIS thread's row: loaded one tile ahead (right after the previous tile consumed
+    // its copy) so the DRAM latency hides behind the previous tile's stores and the accumulator wait
+    uint4 rv[8];
+    auto load_residual = [&](int tile) {
+      bool ok = false;
+      if (has_res && tile < p.num_tiles) {
+        const int n = tile / p.tiles_per_img;
+        const int q0 = (tile - n * p.tiles_per_img) * 128 + m;
+        const int h = q0 / p.Wp;
+        if (q0 < p.H * p.Wp && q0 - h * p.Wp < p.W) {
+          const uint4* res = reinterpret_cast<const uint4*>(p.residual + n * p.img_bytes) + q0 + p.Wp + 1;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) rv[j] = __ldg(res + j * plane16);
+          ok = true;
+        }
+      }
+      if (!ok) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) rv[j] = make_uint4(0, 0, 0, 0);
+      }
+    };
+    load_residual(blockIdx.x);
     for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
       const int n = tile / p.tiles_per_img;
       const int ti = tile - n * p.tiles_per_img;
@@ -167,17 +190,6 @@ __global__ void __launch_bounds__(kThreads, 1) conv_p8_kernel(const ConvP8Params
       const bool valid = in_plane && w < p.W;
       const int a = it & 1;
       const long long opos = static_cast<long long>(q0) + p.Wp + 1;  // padded position of this output
-      // residual: issue all eight 16-byte loads BEFORE waiting for the accumulator so their latency hides behind the MMAs
-      uint4 rv[8];
-      const bool has_res = p.residual != nullptr;
-      if (has_res && valid) {
-        const uint4* res = reinterpret_cast<const uint4*>(p.residual + n * p.img_bytes) + opos;
-#pragma unroll
-        for (int j = 0; j < 8; ++j) rv[j] = __ldg(res + j * plane16);
-      } else {
-#pragma unroll
-        for (int j = 0; j < 8; ++j) rv[j] = make_uint4(0, 0, 0, 0);
-      }
       mbar_wait(&tmem_full_bar[a], (it >> 1) & 1u);
       tc_fence_after();
       const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + a * 64;
@@ -210,6 +222,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_p8_kernel(const ConvP8Params
                                   pack_bf16x2(f[6], f[7]))
                      : make_uint4(0, 0, 0, 0);
       }
+      load_residual(tile + gridDim.x);  // rv is dead from here on: prefetch the next tile's residual
       if (p.out_nhwc) {
         if (valid) {
           uint4* dst = reinterpret_cast<uint4*>(p.out) + ((static_cast<long long>(n) * p.H + h) * p.W + w) * 8;

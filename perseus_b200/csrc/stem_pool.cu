@@ -14,10 +14,11 @@
 //     cp.async.bulk (no tensor map); conv row c needs pairs c..c+3, pair c is released after row c.
 //   * warp 1 (one thread): 14 x tcgen05.mma (M128 N64 K16) per conv row into one of two TMEM
 //     accumulators; weights (28 KB image) stay resident in shared memory for the CTA's lifetime.
-//   * warps 2..5: epilogue.  Thread = conv column.  TMEM -> +bias, ReLU, bf16x2 pack -> horizontal
-//     3-max by warp shuffles (one 128-byte shared-memory hand-off per warp boundary) -> vertical
-//     running max in registers -> even lanes store the pooled pixel in the P8 layout (layout.h),
-//     borders included.  Post-ReLU values are >= 0, so the pool's -inf padding can be 0.
+//   * warps 2..9: epilogue.  Thread = conv column x 32 channels.  TMEM -> vertical running 3-max in fp32
+//     registers on the raw accumulators; once per pooled row: +bias, ReLU, bf16x2 pack -> horizontal
+//     3-max by warp shuffles (one 64-byte shared-memory hand-off per warp boundary) -> even lanes store the
+//     pooled pixel in the P8 layout (layout.h), borders included.  Post-ReLU values are >= 0, so the
+//     pool's -inf padding can be 0 horizontally.
 //   * work unit = (image, band of PB pooled rows); a band recomputes one conv row of overlap.
 #include "common.cuh"
 #include "layout.h"
@@ -26,7 +27,7 @@ namespace pb200 {
 
 namespace {
 
-constexpr int kThreads = 192;
+constexpr int kThreads = 320;  // producer warp + MMA warp + 8 epilogue warps
 constexpr int kRowBytes = 2112;           // (256 + 8) px * 4 ch * 2 B
 constexpr int kPairBytes = 2 * kRowBytes; // 4224
 constexpr int kRing = 16;                 // row-pair slots
@@ -79,8 +80,8 @@ __global__ void __launch_bounds__(kThreads, 1) stem_pool_kernel(const StemPoolPa
     mbar_init(&w_bar, 1);
     mbar_init(&tmem_full_bar[0], 1);
     mbar_init(&tmem_full_bar[1], 1);
-    mbar_init(&tmem_empty_bar[0], 4);
-    mbar_init(&tmem_empty_bar[1], 4);
+    mbar_init(&tmem_empty_bar[0], 8);
+    mbar_init(&tmem_empty_bar[1], 8);
     fence_barrier_init();
   }
   if (warp == 1) {
@@ -163,96 +164,94 @@ __global__ void __launch_bounds__(kThreads, 1) stem_pool_kernel(const StemPoolPa
     }
   } else {
     // ================================ epilogue ====================================
-    const int q = warp & 3;          // TMEM lane quarter
-    const int wo = q * 32 + lane;    // conv output column
-    const int et = wo;               // epilogue thread id 0..127 (for border writes)
-    constexpr int Wp8 = 66;          // padded pooled width
+    // 8 warps: warp -> (TMEM lane quarter q, channel half).  Thread = conv column x 32 channels.
+    // Vertical 3-max runs in fp32 on the RAW accumulators (one FMNMX per value and conv row); bias, ReLU,
+    // the bf16 rounding and the horizontal 3-max happen once per POOLED row.  Exact: x -> bf16(relu(x + b))
+    // is monotone, so it commutes with max.
+    const int q = warp & 3;                // TMEM lane quarter
+    const int half = (warp - 2) >> 2;      // channels [32*half, 32*half + 32)
+    const int wo = q * 32 + lane;          // conv output column
+    constexpr int Wp8 = 66;                // padded pooled width
     const long long plane = static_cast<long long>(p.Hpool + 2) * Wp8;  // elements (16 B) per chunk plane
+    const float* bias = s_bias + 32 * half;
     int it = 0;
+    uint32_t fin = 0;
     for (int u = blockIdx.x; u < p.num_units; u += gridDim.x) {
       const int n = u / p.bands_per_img;
       const int band = u - n * p.bands_per_img;
       const int c_start = band == 0 ? 0 : 2 * band * p.PB - 1;
       const int n_conv = 2 * p.PB + (band == 0 ? 0 : 1);
-      uint4* out_img = reinterpret_cast<uint4*>(p.out + n * p.out_img_bytes);
+      uint4* out_img = reinterpret_cast<uint4*>(p.out + n * p.out_img_bytes) + 4 * half * plane;
       // top / bottom zero border rows of the P8 tensor
-      if (band == 0 && et < Wp8) {
+      if (band == 0 && wo < Wp8) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) out_img[j * plane + et] = make_uint4(0, 0, 0, 0);
+        for (int j = 0; j < 4; ++j) out_img[j * plane + wo] = make_uint4(0, 0, 0, 0);
       }
-      if (band == p.bands_per_img - 1 && et < Wp8) {
+      if (band == p.bands_per_img - 1 && wo < Wp8) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
-          out_img[j * plane + static_cast<long long>(p.Hpool + 1) * Wp8 + et] = make_uint4(0, 0, 0, 0);
+        for (int j = 0; j < 4; ++j)
+          out_img[j * plane + static_cast<long long>(p.Hpool + 1) * Wp8 + wo] = make_uint4(0, 0, 0, 0);
       }
-      uint32_t accv[32];
+      float run[32], podd[32];
 #pragma unroll
-      for (int k = 0; k < 32; ++k) accv[k] = 0u;
+      for (int k = 0; k < 32; ++k) podd[k] = -INFINITY;
       for (int i = 0; i < n_conv; ++i, ++it) {
         const int c = c_start + i;
         const int a = it & 1;
         mbar_wait(&tmem_full_bar[a], (it >> 1) & 1u);
         tc_fence_after();
-        const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + a * 64;
-        uint32_t x0[32], x1[32];
-        tmem_ld_32x32(t_addr, x0);
-        tmem_ld_32x32(t_addr + 32, x1);
+        uint32_t x[32];
+        tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + a * 64 + half * 32, x);
         tmem_ld_wait();
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&tmem_empty_bar[a]);
-        uint32_t v[32];
+        if ((c & 1) == 0) {
 #pragma unroll
-        for (int k = 0; k < 16; ++k) {
-          const float2 b = *reinterpret_cast<const float2*>(s_bias + 2 * k);
-          v[k] = pack_bf16x2(fmaxf(__uint_as_float(x0[2 * k]) + b.x, 0.f),
-                             fmaxf(__uint_as_float(x0[2 * k + 1]) + b.y, 0.f));
+          for (int k = 0; k < 32; ++k) run[k] = fmaxf(podd[k], __uint_as_float(x[k]));
+          continue;
+        }
+        // odd conv row: closes the window of pooled row (c-1)/2 and opens the next one
+        const bool owned = i > 0 || band == 0;
+        uint32_t v[16];
+        if (owned) {
+#pragma unroll
+          for (int k = 0; k < 16; ++k) {
+            const float2 b = *reinterpret_cast<const float2*>(bias + 2 * k);
+            v[k] = pack_bf16x2(fmaxf(fmaxf(run[2 * k], __uint_as_float(x[2 * k])) + b.x, 0.f),
+                               fmaxf(fmaxf(run[2 * k + 1], __uint_as_float(x[2 * k + 1])) + b.y, 0.f));
+          }
         }
 #pragma unroll
-        for (int k = 0; k < 16; ++k) {
-          const float2 b = *reinterpret_cast<const float2*>(s_bias + 32 + 2 * k);
-          v[16 + k] = pack_bf16x2(fmaxf(__uint_as_float(x1[2 * k]) + b.x, 0.f),
-                                  fmaxf(__uint_as_float(x1[2 * k + 1]) + b.y, 0.f));
-        }
-        // hand the warp's last column to the next warp
-        uint32_t* xw = s_xchg + ((it & 1) * 4 + q) * 32;
+        for (int k = 0; k < 32; ++k) podd[k] = __uint_as_float(x[k]);
+        if (!owned) continue;
+        // horizontal 3-max: hand the warp's last column to the next warp through shared memory
+        uint32_t* xw = s_xchg + (((fin & 1) * 4 + q) * 2 + half) * 16;
         if (lane == 31) {
 #pragma unroll
-          for (int k = 0; k < 8; ++k)
+          for (int k = 0; k < 4; ++k)
             reinterpret_cast<uint4*>(xw)[k] = make_uint4(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
         }
-        named_bar_sync(1, 128);
-        const uint32_t* xr = s_xchg + ((it & 1) * 4 + (q > 0 ? q - 1 : 0)) * 32;
+        named_bar_sync(1, 256);
+        const uint32_t* xr = s_xchg + (((fin & 1) * 4 + (q > 0 ? q - 1 : 0)) * 2 + half) * 16;
+        ++fin;
 #pragma unroll
-        for (int k = 0; k < 32; ++k) {
+        for (int k = 0; k < 16; ++k) {
           uint32_t left = __shfl_up_sync(0xffffffffu, v[k], 1);
           const uint32_t right = __shfl_down_sync(0xffffffffu, v[k], 1);
-          if (lane == 0) left = q > 0 ? xr[k] : 0u;
+          if (lane == 0) left = q > 0 ? xr[k] : 0u;  // column -1 is the pool's padding (values are >= 0)
           v[k] = hmax2_u32(hmax2_u32(left, v[k]), right);  // lane 31 (odd column) is never a pool centre
         }
-        if (c & 1) {
-          // conv rows 2po-1, 2po, 2po+1 complete pooled row po = (c-1)/2 (owned by this band unless i == 0)
-          if (i > 0 || band == 0) {
-            const int po = (c - 1) >> 1;
-            uint4* orow = out_img + static_cast<long long>(po + 1) * Wp8;
-            if ((lane & 1) == 0) {
-              const int pw = wo >> 1;
+        const int po = (c - 1) >> 1;
+        uint4* orow = out_img + static_cast<long long>(po + 1) * Wp8;
+        if ((lane & 1) == 0) {
+          const int pw = wo >> 1;
 #pragma unroll
-              for (int j = 0; j < 8; ++j)
-                orow[j * plane + pw + 1] =
-                    make_uint4(hmax2_u32(accv[4 * j], v[4 * j]), hmax2_u32(accv[4 * j + 1], v[4 * j + 1]),
-                               hmax2_u32(accv[4 * j + 2], v[4 * j + 2]), hmax2_u32(accv[4 * j + 3], v[4 * j + 3]));
-            } else if (wo == 1 || wo == 127) {
-              const int col = wo == 1 ? 0 : Wp8 - 1;
+          for (int j = 0; j < 4; ++j) orow[j * plane + pw + 1] = make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+        } else if (wo == 1 || wo == 127) {
+          const int col = wo == 1 ? 0 : Wp8 - 1;
 #pragma unroll
-              for (int j = 0; j < 8; ++j) orow[j * plane + col] = make_uint4(0, 0, 0, 0);
-            }
-          }
-#pragma unroll
-          for (int k = 0; k < 32; ++k) accv[k] = v[k];
-        } else {
-#pragma unroll
-          for (int k = 0; k < 32; ++k) accv[k] = hmax2_u32(accv[k], v[k]);
+          for (int j = 0; j < 4; ++j) orow[j * plane + col] = make_uint4(0, 0, 0, 0);
         }
       }
     }
