@@ -196,7 +196,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_p8_kernel(const ConvP8Params
       uint32_t x0[32], x1[32];
       tmem_ld_32x32(t_addr, x0);
       tmem_ld_32x32(t_addr + 32, x1);
-      tmem_ld_wait();
+      tmem_ld_wait_regs(x0);
+      tmem_ld_wait_regs(x1);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tmem_empty_bar[a]);

@@ -184,7 +184,7 @@ conv_umma_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams
       for (int chunk = 0; chunk < BLOCK_N / 32; ++chunk) {
         uint32_t v[32];
         tmem_ld_32x32(t_addr + chunk * 32, v);
-        tmem_ld_wait();
+        tmem_ld_wait_regs(v);
         if (valid) {
           float f[32];
 #pragma unroll

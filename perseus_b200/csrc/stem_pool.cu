@@ -10,16 +10,17 @@
 // apart along K and SBO = 128 B apart along M: the raw frame row in shared memory IS the im2col
 // operand; nothing is expanded or re-read.
 //
-//   * warp 0 (one thread): streams frame row-PAIRS (4224 contiguous bytes) into a 16-slot ring with
-//     cp.async.bulk (no tensor map); conv row c needs pairs c..c+3, pair c is released after row c.
-//   * warp 1 (one thread): 14 x tcgen05.mma (M128 N64 K16) per conv row into one of two TMEM
-//     accumulators; weights (28 KB image) stay resident in shared memory for the CTA's lifetime.
+//   * warp 0 (one elected lane): streams frame row-PAIRS (4224 contiguous bytes) into a 16-slot ring with
+//     cp.async.bulk (no tensor map).
+//   * warp 1 (one elected lane): per iteration 2 x 14 tcgen05.mma (M128 N64 K16) = the conv-row pair
+//     (2k, 2k+1) into one of two 128-column TMEM accumulator stages; the weights (28 KB image) stay
+//     resident in shared memory for the CTA's lifetime.
 //   * warps 2..9: epilogue.  Thread = conv column x 32 channels.  TMEM -> vertical running 3-max in fp32
 //     registers on the raw accumulators; once per pooled row: +bias, ReLU, bf16x2 pack -> horizontal
 //     3-max by warp shuffles (one 64-byte shared-memory hand-off per warp boundary) -> even lanes store the
 //     pooled pixel in the P8 layout (layout.h), borders included.  Post-ReLU values are >= 0, so the
 //     pool's -inf padding can be 0 horizontally.
-//   * work unit = (image, band of PB pooled rows); a band recomputes one conv row of overlap.
+//   * work unit = (image, band of PB pooled rows); a band below the top recomputes one conv-row pair.
 #include "common.cuh"
 #include "layout.h"
 
@@ -85,7 +86,7 @@ __global__ void __launch_bounds__(kThreads, 1) stem_pool_kernel(const StemPoolPa
     fence_barrier_init();
   }
   if (warp == 1) {
-    tmem_alloc(&tmem_base_slot, 128);
+    tmem_alloc(&tmem_base_slot, 256);
     tmem_relinquish();
   }
   if (threadIdx.x >= 64 && threadIdx.x < 128) s_bias[threadIdx.x - 64] = __ldg(p.bias + threadIdx.x - 64);
@@ -94,6 +95,12 @@ __global__ void __launch_bounds__(kThreads, 1) stem_pool_kernel(const StemPoolPa
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_slot;
 
+  // Work decomposition shared by the three roles.  A unit = (image n, band of PB pooled rows).  It runs
+  // `n_it` iterations; iteration k (k0 <= k < k0 + n_it) computes the conv-row pair (2k, 2k+1).  Pooled row k =
+  // max(conv rows 2k-1, 2k, 2k+1), so a band that does not start at the top of the image runs one extra
+  // leading iteration (k0 = p0 - 1) whose only product is conv row 2k+1 (the carried "previous odd row").
+  // Conv rows 2k, 2k+1 read frame rows 4k .. 4k+8, i.e. frame row-pairs 2k .. 2k+4; iteration k releases pairs
+  // 2k and 2k+1.  Per unit the ring therefore sees 2*n_it + 3 pairs.
   if (warp == 0) {
     // ================================ producer ====================================
     // whole warp runs the loop (warp-uniform operands); one elected lane issues the copies
@@ -105,9 +112,9 @@ __global__ void __launch_bounds__(kThreads, 1) stem_pool_kernel(const StemPoolPa
     for (int u = blockIdx.x; u < p.num_units; u += gridDim.x) {
       const int n = u / p.bands_per_img;
       const int band = u - n * p.bands_per_img;
-      const int c_start = band == 0 ? 0 : 2 * band * p.PB - 1;
-      const int n_pairs = 2 * p.PB + (band == 0 ? 0 : 1) + 3;
-      const uint8_t* src = p.frames + n * p.frame_bytes + static_cast<long long>(2 * c_start) * kRowBytes;
+      const int k0 = band == 0 ? 0 : band * p.PB - 1;
+      const int n_pairs = 2 * (p.PB + (band == 0 ? 0 : 1)) + 3;
+      const uint8_t* src = p.frames + n * p.frame_bytes + static_cast<long long>(4 * k0) * kRowBytes;
       for (int g = 0; g < n_pairs; ++g, ++G) {
         const uint32_t slot = G % kRing, ph = (G / kRing) & 1u;
         mbar_wait(&empty_bar[slot], ph ^ 1u);
@@ -132,55 +139,62 @@ __global__ void __launch_bounds__(kThreads, 1) stem_pool_kernel(const StemPoolPa
     int it = 0;
     for (int u = blockIdx.x; u < p.num_units; u += gridDim.x) {
       const int band = u % p.bands_per_img;
-      const int n_conv = 2 * p.PB + (band == 0 ? 0 : 1);
+      const int n_it = p.PB + (band == 0 ? 0 : 1);
       for (uint32_t j = 0; j < 3; ++j) mbar_wait(&full_bar[(G + j) % kRing], ((G + j) / kRing) & 1u);
-      for (int i = 0; i < n_conv; ++i, ++it) {
-        const uint32_t Gi = G + i;
+      for (int i = 0; i < n_it; ++i, ++it) {
+        const uint32_t Gi = G + 2 * i;
         mbar_wait(&full_bar[(Gi + 3) % kRing], ((Gi + 3) / kRing) & 1u);
+        mbar_wait(&full_bar[(Gi + 4) % kRing], ((Gi + 4) / kRing) & 1u);
         const int acc = it & 1;
         mbar_wait(&tmem_empty_bar[acc], ((it >> 1) & 1u) ^ 1u);
         tc_fence_after();
         if (elect_one()) {
-          const uint32_t d_tmem = tm + acc * 64;
 #pragma unroll
-          for (int r = 0; r < 7; ++r) {
-            const uint32_t row = ring_addr + ((Gi + (r >> 1)) % kRing) * kPairBytes + (r & 1) * kRowBytes;
-            const uint32_t a_lo = desc_lo(row, 16);
+          for (int e = 0; e < 2; ++e) {  // e = 0: conv row 2k (columns [0,64)), e = 1: conv row 2k+1 (columns [64,128))
+            const uint32_t d_tmem = tm + acc * 128 + e * 64;
 #pragma unroll
-            for (int h = 0; h < 2; ++h)
-              umma_bf16_split(d_tmem, a_lo + 2 * h, a_hi, b_lo0 + (r * 4 + h * 2) * 8, b_hi, idesc,
-                              (r | h) != 0 ? 1u : 0u);
+            for (int r = 0; r < 7; ++r) {
+              const int fr = 2 * e + r;  // frame row relative to 4k
+              const uint32_t row = ring_addr + ((Gi + (fr >> 1)) % kRing) * kPairBytes + (fr & 1) * kRowBytes;
+              const uint32_t a_lo = desc_lo(row, 16);
+#pragma unroll
+              for (int h = 0; h < 2; ++h)
+                umma_bf16_split(d_tmem, a_lo + 2 * h, a_hi, b_lo0 + (r * 4 + h * 2) * 8, b_hi, idesc,
+                                (r | h) != 0 ? 1u : 0u);
+            }
           }
           umma_commit(&tmem_full_bar[acc]);
           umma_commit(&empty_bar[Gi % kRing]);
+          umma_commit(&empty_bar[(Gi + 1) % kRing]);
         }
         __syncwarp();
       }
       if (elect_one()) {
-        for (uint32_t j = 0; j < 3; ++j) umma_commit(&empty_bar[(G + n_conv + j) % kRing]);
+        for (uint32_t j = 0; j < 3; ++j) umma_commit(&empty_bar[(G + 2 * n_it + j) % kRing]);
       }
       __syncwarp();
-      G += n_conv + 3;
+      G += 2 * n_it + 3;
     }
   } else {
     // ================================ epilogue ====================================
     // 8 warps: warp -> (TMEM lane quarter q, channel half).  Thread = conv column x 32 channels.
-    // Vertical 3-max runs in fp32 on the RAW accumulators (one FMNMX per value and conv row); bias, ReLU,
-    // the bf16 rounding and the horizontal 3-max happen once per POOLED row.  Exact: x -> bf16(relu(x + b))
-    // is monotone, so it commutes with max.
+    // Per iteration: both conv rows of the pair come out of TMEM, the vertical 3-max (with the carried odd
+    // row) runs in fp32 on the RAW accumulators, then bias, ReLU, the bf16 rounding and the horizontal 3-max
+    // happen once per POOLED row.  Exact: x -> bf16(relu(x + b)) is monotone, so it commutes with max.
     const int q = warp & 3;                // TMEM lane quarter
     const int half = (warp - 2) >> 2;      // channels [32*half, 32*half + 32)
     const int wo = q * 32 + lane;          // conv output column
     constexpr int Wp8 = 66;                // padded pooled width
     const long long plane = static_cast<long long>(p.Hpool + 2) * Wp8;  // elements (16 B) per chunk plane
     const float* bias = s_bias + 32 * half;
+    const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + half * 32;
     int it = 0;
     uint32_t fin = 0;
     for (int u = blockIdx.x; u < p.num_units; u += gridDim.x) {
       const int n = u / p.bands_per_img;
       const int band = u - n * p.bands_per_img;
-      const int c_start = band == 0 ? 0 : 2 * band * p.PB - 1;
-      const int n_conv = 2 * p.PB + (band == 0 ? 0 : 1);
+      const int k0 = band == 0 ? 0 : band * p.PB - 1;
+      const int n_it = p.PB + (band == 0 ? 0 : 1);
       uint4* out_img = reinterpret_cast<uint4*>(p.out + n * p.out_img_bytes) + 4 * half * plane;
       // top / bottom zero border rows of the P8 tensor
       if (band == 0 && wo < Wp8) {
@@ -192,38 +206,34 @@ __global__ void __launch_bounds__(kThreads, 1) stem_pool_kernel(const StemPoolPa
         for (int j = 0; j < 4; ++j)
           out_img[j * plane + static_cast<long long>(p.Hpool + 1) * Wp8 + wo] = make_uint4(0, 0, 0, 0);
       }
-      float run[32], podd[32];
+      float podd[32];
 #pragma unroll
       for (int k = 0; k < 32; ++k) podd[k] = -INFINITY;
-      for (int i = 0; i < n_conv; ++i, ++it) {
-        const int c = c_start + i;
+      for (int i = 0; i < n_it; ++i, ++it) {
         const int a = it & 1;
         mbar_wait(&tmem_full_bar[a], (it >> 1) & 1u);
         tc_fence_after();
-        uint32_t x[32];
-        tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + a * 64 + half * 32, x);
-        tmem_ld_wait();
+        uint32_t xe[32], xo[32];
+        tmem_ld_32x32(t_lane + a * 128, xe);
+        tmem_ld_32x32(t_lane + a * 128 + 64, xo);
+        tmem_ld_wait_regs(xe);
+        tmem_ld_wait_regs(xo);
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&tmem_empty_bar[a]);
-        if ((c & 1) == 0) {
-#pragma unroll
-          for (int k = 0; k < 32; ++k) run[k] = fmaxf(podd[k], __uint_as_float(x[k]));
-          continue;
-        }
-        // odd conv row: closes the window of pooled row (c-1)/2 and opens the next one
-        const bool owned = i > 0 || band == 0;
+        const bool owned = i > 0 || band == 0;  // the leading iteration of a lower band only produces podd
         uint32_t v[16];
         if (owned) {
 #pragma unroll
           for (int k = 0; k < 16; ++k) {
             const float2 b = *reinterpret_cast<const float2*>(bias + 2 * k);
-            v[k] = pack_bf16x2(fmaxf(fmaxf(run[2 * k], __uint_as_float(x[2 * k])) + b.x, 0.f),
-                               fmaxf(fmaxf(run[2 * k + 1], __uint_as_float(x[2 * k + 1])) + b.y, 0.f));
+            const float m0 = fmaxf(fmaxf(podd[2 * k], __uint_as_float(xe[2 * k])), __uint_as_float(xo[2 * k]));
+            const float m1 = fmaxf(fmaxf(podd[2 * k + 1], __uint_as_float(xe[2 * k + 1])), __uint_as_float(xo[2 * k + 1]));
+            v[k] = pack_bf16x2(fmaxf(m0 + b.x, 0.f), fmaxf(m1 + b.y, 0.f));
           }
         }
 #pragma unroll
-        for (int k = 0; k < 32; ++k) podd[k] = __uint_as_float(x[k]);
+        for (int k = 0; k < 32; ++k) podd[k] = __uint_as_float(xo[k]);
         if (!owned) continue;
         // horizontal 3-max: hand the warp's last column to the next warp through shared memory
         uint32_t* xw = s_xchg + (((fin & 1) * 4 + q) * 2 + half) * 16;
@@ -242,7 +252,7 @@ __global__ void __launch_bounds__(kThreads, 1) stem_pool_kernel(const StemPoolPa
           if (lane == 0) left = q > 0 ? xr[k] : 0u;  // column -1 is the pool's padding (values are >= 0)
           v[k] = hmax2_u32(hmax2_u32(left, v[k]), right);  // lane 31 (odd column) is never a pool centre
         }
-        const int po = (c - 1) >> 1;
+        const int po = k0 + i;
         uint4* orow = out_img + static_cast<long long>(po + 1) * Wp8;
         if ((lane & 1) == 0) {
           const int pw = wo >> 1;
@@ -261,7 +271,7 @@ __global__ void __launch_bounds__(kThreads, 1) stem_pool_kernel(const StemPoolPa
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, 128);
+    tmem_dealloc(tmem_base, 256);
   }
 }
 

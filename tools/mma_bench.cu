@@ -6,11 +6,11 @@
 namespace pb200 { void set_error(const char*, ...) {} int cuda_fail(cudaError_t, const char*, const char*, int) { return 2; } }
 using namespace pb200;
 
-struct Variant { int n; int a_mode; int a_off; int a_lbo; int a_sbo; int b_mode; const char* name; };
+struct Variant { int n; int a_mode; int a_off; int a_lbo; int a_sbo; int b_mode; const char* name; int vary = 0; };
 // mode 0 = interleaved(no swizzle), 1 = SW128
 
 __global__ void __launch_bounds__(128, 1) bench(int N, int a_mode, uint32_t a_off, uint32_t a_lbo, uint32_t a_sbo,
-                                                 int b_mode, int iters, long long* out) {
+                                                 int b_mode, int iters, long long* out, int vary) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint64_t bar;
   __shared__ uint32_t slot;
@@ -32,7 +32,16 @@ __global__ void __launch_bounds__(128, 1) bench(int N, int a_mode, uint32_t a_of
     for (int i = 0; i < 8; ++i) umma_bf16(tm, ad, bd, idesc, 1);
     umma_commit(&bar); mbar_wait(&bar, 0);
     long long t0 = clock64();
-    for (int i = 0; i < iters; ++i) umma_bf16(tm, ad + (i & 3) * 2 * (a_mode ? 1 : 0), bd, idesc, 1);
+    if (vary == 0) {
+      for (int i = 0; i < iters; ++i) umma_bf16(tm, ad + (i & 3) * 2 * (a_mode ? 1 : 0), bd, idesc, 1);
+    } else {
+      // unrolled, compile-time offsets (no issue-side arithmetic): vary bit0 = move A each MMA, bit1 = move B
+      const uint64_t sa = (vary & 1) ? 132 : 0, sb = (vary & 2) ? 16 : 0;
+      for (int i = 0; i < iters; i += 8) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) umma_bf16(tm, ad + sa * j + (j & 1) * 2, bd + sb * j, idesc, 1);
+      }
+    }
     umma_commit(&bar); mbar_wait(&bar, 1);
     long long t1 = clock64();
     out[blockIdx.x] = t1 - t0;
@@ -59,14 +68,19 @@ int main() {
     {64, 1, 0, 0, 0, 0, "N64  A=SW128           B=nosw"},
     {128, 0, 0, 4224, 128, 0, "N128 A=nosw aligned    B=nosw"},
     {128, 0, 16, 4224, 128, 0, "N128 A=nosw +16B       B=nosw"},
-    {256, 0, 16, 4224, 128, 0, "N256 A=nosw +16B       B=nosw"},
+    {64, 0, 0, 16, 128, 0, "N64  nosw lbo16: A moves", 1},
+    {64, 0, 0, 16, 128, 0, "N64  nosw lbo16: B moves", 2},
+    {64, 0, 0, 16, 128, 0, "N64  nosw lbo16: A and B move", 3},
+    {64, 0, 0, 4224, 128, 0, "N64  nosw lbo4224: A and B move", 3},
+    {128, 0, 0, 16, 128, 0, "N128 nosw lbo16: A and B move", 3},
+    {64, 1, 0, 0, 0, 1, "N64  SW128: A and B move", 3},
     {32, 1, 0, 0, 0, 1, "N32  A=SW128           B=SW128"},
     {16, 1, 0, 0, 0, 1, "N16  A=SW128           B=SW128"},
   };
   const int iters = 2000;
   for (auto& v : vs) {
     for (int grid : {1, 148}) {
-      bench<<<grid, 128, 200 * 1024>>>(v.n, v.a_mode, v.a_off, v.a_lbo, v.a_sbo, v.b_mode, iters, d);
+      bench<<<grid, 128, 200 * 1024>>>(v.n, v.a_mode, v.a_off, v.a_lbo, v.a_sbo, v.b_mode, iters, d, v.vary);
       cudaError_t e = cudaDeviceSynchronize();
       if (e != cudaSuccess) { printf("%s: CUDA error %s\n", v.name, cudaGetErrorString(e)); return 1; }
       long long h[148]; cudaMemcpy(h, d, grid * 8, cudaMemcpyDeviceToHost);
