@@ -83,7 +83,7 @@ class ClockSampler:
                             self.reasons.add(k)
                 except Exception:
                     pass
-                time.sleep(0.01)
+                time.sleep(0.005)
         except Exception as e:  # NVML unavailable: fall back to one nvidia-smi query
             self.error = repr(e)
 
@@ -140,6 +140,100 @@ def cpu_reference_fps(frames: int, chunk: int, warmup_frames: int = 8):
     return done / dt, cores, dt
 
 
+
+def _p50(xs):
+    xs = sorted(xs)
+    return xs[len(xs) // 2]
+
+
+def measure_latency(model, dev, iters=200):
+    """BASELINE.json 'bs1 p50 ms' (configs[4] shape): ZED-shaped 376x672 BGRA frame in PINNED HOST memory ->
+    keypoints in pinned host memory, wall clock around one CUDA-graph replay + stream sync (H2D, ingest, forward,
+    decode, D2H inside).  Also the device-only time of the same graph (CUDA events)."""
+    import torch
+
+    from perseus_b200.detector import StreamingDetector
+
+    out = {}
+    for B in (1, 2):
+        det = StreamingDetector(model, 376, 672, 4, batch=B)
+        g = torch.Generator().manual_seed(B)
+        det.host_rgb.copy_(torch.randint(0, 256, det.host_rgb.shape, dtype=torch.uint8, generator=g))
+        for _ in range(20):
+            det.infer_pinned()
+        wall, devt = [], []
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        for _ in range(iters):
+            t0 = time.perf_counter()
+            det.infer_pinned()
+            wall.append((time.perf_counter() - t0) * 1e3)
+        for _ in range(iters // 4):
+            with torch.cuda.stream(det.stream):
+                e0.record(det.stream)
+                det.graph.replay()
+                e1.record(det.stream)
+            det.stream.synchronize()
+            devt.append(e0.elapsed_time(e1))
+        out[f"bs{B}_p50_ms"] = _p50(wall)
+        out[f"bs{B}_p99_ms"] = sorted(wall)[int(len(wall) * 0.99) - 1]
+        out[f"bs{B}_device_p50_ms"] = _p50(devt)
+    out["what"] = ("pinned-host BGRA 376x672 frame -> pinned-host keypoints, one CUDA-graph replay (H2D + ingest + "
+                   "backbone + head/decode + D2H) + sync; wall clock p50 over %d frames" % iters)
+    return out
+
+
+def measure_factors(dev, peaks, N=10_000, big=1_000_000):
+    """BASELINE.json configs[4]: batched residual + Jacobian evaluation of the smoother factors over 10k cube poses
+    (8 projection factors + 1 dynamics + 1 const-velocity factor per pose), float64; plus 1M poses where the
+    HBM roofline fraction is meaningful (1120 B/pose projection, 1152 B/pair dynamics)."""
+    import numpy as np
+    import torch
+
+    from perseus_b200.smoother import constant_velocity_batch, keypoint_projection_batch, pose_dynamics_batch
+
+    res = {}
+    for n in (N, big):
+        g = torch.Generator().manual_seed(0)
+        def rnd(*shape):
+            return torch.randn(*shape, generator=g, dtype=torch.float64)
+        # rotations from normalised quaternions (any proper rotation will do for timing)
+        qn = torch.nn.functional.normalize(rnd(2, n, 4), dim=-1)
+        w, x, y, z = qn.unbind(-1)
+        R = torch.stack([1 - 2 * (y * y + z * z), 2 * (x * y - z * w), 2 * (x * z + y * w),
+                         2 * (x * y + z * w), 1 - 2 * (x * x + z * z), 2 * (y * z - x * w),
+                         2 * (x * z - y * w), 2 * (y * z + x * w), 1 - 2 * (x * x + y * y)], -1)
+        t = rnd(2, n, 3) * 0.05
+        t[..., 2] += 0.45
+        pose = torch.cat([R, t], -1).to(dev)
+        wv, vv = rnd(n, 3).to(dev), rnd(n, 3).to(dev)
+        K5 = torch.tensor([221.7, 221.7, 0.0, 128.0, 128.0], dtype=torch.float64, device=dev)
+        corners = torch.tensor([[a, b, c] for a in (-1, 1) for b in (-1, 1) for c in (-1, 1)], dtype=torch.float64,
+                               device=dev) * 0.0175
+        meas = (torch.rand(n, 8, 2, generator=g, dtype=torch.float64) * 255).to(dev)
+
+        def step():
+            keypoint_projection_batch(pose[0], K5, meas, corners)
+            pose_dynamics_batch(pose[0], wv, vv, pose[1], 0.1, "world")
+            constant_velocity_batch(vv, wv)
+
+        for _ in range(3):
+            step()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        reps = 20 if n <= N else 5
+        e0.record()
+        for _ in range(reps):
+            step()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / reps
+        nbytes = n * (1120 + 1152 + 72 + 144)
+        res[f"poses_{n}"] = {"ms": ms, "poses_per_s": n / (ms * 1e-3), "algorithmic_GBps": nbytes / (ms * 1e-3) / 1e9,
+                             "hbm_frac": nbytes / (ms * 1e-3) / 1e9 / peaks["hbm_gbs"]}
+    res["what"] = "per pose: 8 projection (resid + 2x6 J) + 1 dynamics (resid + 4 J blocks) + 1 const-vel factor, fp64"
+    return res
+
+
 def dist_env():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -152,7 +246,7 @@ def run_reference(args):
     rank, world, _ = dist_env()
     if rank != 0:
         return
-    chunk = 32
+    chunk = int(os.environ.get("PB200_REF_CHUNK", "32"))  # frames per step (bounded sample of the 256-frame batch)
     for _ in range(max(args.warmup, 0)):
         cpu_reference_fps(chunk, chunk, warmup_frames=8)
         break  # one warm pass is enough to page everything in (each pass costs seconds)
@@ -175,7 +269,7 @@ def run_reference(args):
         "warmup": args.warmup, "ms_per_step": 1e3 * t_total / done_steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": WORKLOAD, "note": "reference PyTorch CPU path (torchvision resnet18 module tree, "
-                   "fp32, no_grad); each step = a 32-frame sample of the batch"},
+                   f"fp32, no_grad); each step = a {chunk}-frame sample of the batch"},
         "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": "port",
                          "sample": f"{done_steps} steps x {chunk} frames (u8->f32 ingest + forward + decode), fp32"},
         "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -324,6 +418,8 @@ def run_native(args):
             "whole_step_frac": (BATCH * FLOPS_PER_FRAME_RGB / (ms / args.steps * 1e-3) / 1e12) / peak,
             "per_op_ms": {n: round(t, 4) for n, t, _, _ in rows},
         }
+        latency = measure_latency(model, dev)
+        factors = measure_factors(dev, peaks)
         cpu_fps, cores, cpu_dt = cpu_reference_fps(256, 32)
         launches_per_step = 1 + len(rows)
         line = {
@@ -339,6 +435,8 @@ def run_native(args):
                     "d2h_bytes_per_step": BATCH * 8 * 2 * 4, "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": launches_per_step * args.steps,
             "roofline": roofline,
+            "latency": latency,
+            "factors": factors,
             "cpu_baseline": {"value": cpu_fps, "unit": "frames/s", "cores": cores, "kind": "port",
                              "sample": f"256 frames in 32-frame batches, fp32, {cpu_dt:.1f} s (reference PyTorch "
                                        "CPU path: u8->f32 ingest + torchvision resnet18 forward + decode)"},
@@ -355,8 +453,8 @@ def run_native(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=50)
-    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     args = ap.parse_args()
     if args.impl == "reference":

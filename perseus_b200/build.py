@@ -68,7 +68,10 @@ def build(force: bool = False, verbose: bool = False) -> str:
             sys.stderr.write(f"--- {src} ---\n{out}\n")
     if failed:
         raise RuntimeError("nvcc failed building libperseus_b200.so")
-    link = [nvcc, "--shared", "-o", LIB] + objs + ["-gencode", "arch=compute_100a,code=sm_100a"]
+    # shared cudart: ONE CUDA runtime per process (the one torch already loaded), so stream capture into CUDA graphs
+    # and the current-device state are shared with PyTorch; rpath = the toolkit copy for torch-free loads
+    link = [nvcc, "--shared", "--cudart", "shared", "-Xlinker", "-rpath=/usr/local/cuda/lib64", "-o", LIB] + objs + [
+        "-gencode", "arch=compute_100a,code=sm_100a"]
     subprocess.check_call(link)
     with open(STAMP, "w") as fh:
         fh.write(want)

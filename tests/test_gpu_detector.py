@@ -293,3 +293,28 @@ def test_full_size_batch256_properties():
     assert px.shape == (256, 8, 2) and torch.isfinite(px).all()
     for i in (0, 127, 254):
         assert torch.equal(model.forward_frames(rgb[i:i + 2]), px[i:i + 2])
+
+
+def test_streaming_detector_graph_matches_eager_path():
+    """BASELINE.json configs[4] shape: ZED-shaped BGRA + depth frames, bs 1 and 2, one CUDA-graph replay per step
+    (H2D + ingest + forward + decode + D2H) == the eager forward_frames result, bit for bit, for changing inputs."""
+    from perseus_b200.detector import StreamingDetector
+
+    for C, B in ((4, 1), (3, 2)):
+        model, sd = gu.native_model(C, "bf16")
+        det = StreamingDetector(model, 376, 672, 4, batch=B)
+        for seed in (1, 2, 3):
+            bgra = gu.synth_u8_frames(B, 376, 672, 4, seed=seed)
+            depth = gu.synth_depth_m(B, 376, 672, seed=seed)
+            got = det.infer(bgra.numpy(), depth.numpy() if C == 4 else None)
+            want = model.forward_frames(bgra.cuda(), depth.cuda() if C == 4 else None, bgr=True, depth_divisor=0.035)
+            assert got.shape == (B, 8, 2)
+            assert torch.equal(torch.from_numpy(got), want.cpu())
+    # fp32 parity mode against the reference on the streaming ingest
+    model, sd = gu.native_model(3, "fp32")
+    det = StreamingDetector(model, 376, 672, 4, batch=1)
+    bgra = gu.synth_u8_frames(1, 376, 672, 4, seed=7)
+    got = torch.from_numpy(det.infer(bgra.numpy()))
+    x = do.streaming_ingest(bgra[0].numpy(), None, 3)[None]
+    want = do.denormalize_pixel_coordinates(do.reference_forward(sd, x).reshape(1, 8, 2), 256, 256)
+    assert (got - want).abs().max() <= 1e-3
