@@ -10,8 +10,8 @@
 //     taps are zero-filled by TMA's bounds check (the conv's zero padding).  Stride-2 layers use
 //     four parity-split views of the input (even/odd rows x even/odd cols), one per tap parity.
 //   * (the stem and layer1 do not use this kernel: stem_pool.cu / conv_p8.cu)
-//   * warp roles (192 threads): warp 0 = TMA producer, warp 1 = MMA issuer (one elected lane) + TMEM
-//     owner, warps 2..5 = epilogue (TMEM -> registers -> bias/residual/ReLU -> bf16 NHWC).
+//   * warp roles (320 threads): warp 0 = TMA producer, warp 1 = MMA issuer (one elected lane) + TMEM
+//     owner, warps 2..9 = epilogue (TMEM -> registers -> bias/residual/ReLU -> bf16 NHWC).
 //   * persistent CTAs (grid = #SMs), static tile round-robin, smem ring of kStages stages,
 //     two TMEM accumulators so the epilogue of tile i overlaps the MMAs of tile i+1.
 #include "common.cuh"
@@ -20,7 +20,7 @@
 
 namespace pb200 {
 
-constexpr int kUmmaThreads = 192;
+constexpr int kUmmaThreads = 320;  // TMA warp + MMA warp + 8 epilogue warps
 constexpr int kTileM = 128;
 
 template <int BLOCK_N, int SW>
@@ -46,6 +46,7 @@ conv_umma_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams
   __shared__ __align__(8) uint64_t tmem_full_bar[2];
   __shared__ __align__(8) uint64_t tmem_empty_bar[2];
   __shared__ uint32_t tmem_base_slot;
+  __shared__ float s_bias[512];  // folded-BN shift of every output channel (Cout <= 512)
 
   const uint32_t raw_addr = smem_u32(smem_raw);
   const uint32_t tiles_addr = (raw_addr + 1023u) & ~1023u;
@@ -66,14 +67,15 @@ conv_umma_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams
     }
     mbar_init(&tmem_full_bar[0], 1);
     mbar_init(&tmem_full_bar[1], 1);
-    mbar_init(&tmem_empty_bar[0], 4);
-    mbar_init(&tmem_empty_bar[1], 4);
+    mbar_init(&tmem_empty_bar[0], 8);
+    mbar_init(&tmem_empty_bar[1], 8);
     fence_barrier_init();
   }
   if (warp == 1) {
     tmem_alloc(&tmem_base_slot, Cfg::kTmemCols);
     tmem_relinquish();
   }
+  for (int i = threadIdx.x; i < p.Cout; i += kUmmaThreads) s_bias[i] = __ldg(p.bias + i);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -162,7 +164,14 @@ conv_umma_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams
     }
   } else {
     // ================================ epilogue ====================================
+    // 8 warps: warp -> (TMEM lane quarter q, column half).  Thread = one output pixel x BLOCK_N/2 channels.
+    // The residual row of the tile (all 16-byte loads of this thread) is requested BEFORE the accumulator
+    // wait so its L2/HBM latency hides behind the MMAs; the bias sits in shared memory.
+    constexpr int kCols = BLOCK_N / 2;            // columns per epilogue thread
+    constexpr int kChunks = kCols / 32;           // 32-column TMEM loads per thread
+    constexpr int kVec = kCols / 8;               // 16-byte vectors of bf16 per thread
     const int q = warp & 3;  // TMEM lane quarter this warp may access
+    const int half = (warp - 2) >> 2;
     const int row = q * 32 + lane;
     int it = 0;
     for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
@@ -170,56 +179,55 @@ conv_umma_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams
       const int n_tile = tile - m_tile * p.num_n_tiles;
       const int acc = it & 1;
       const uint32_t acc_phase = (it >> 1) & 1;
-      mbar_wait(&tmem_full_bar[acc], acc_phase);
-      tc_fence_after();
       const long long gm = static_cast<long long>(m_tile) * kTileM + row;
       const bool valid = gm < p.M_total;
-      const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BLOCK_N;
-      __nv_bfloat16* out_row = static_cast<__nv_bfloat16*>(p.out) + gm * p.Cout + n_tile * BLOCK_N;
-      const __nv_bfloat16* res_row =
-          p.residual ? static_cast<const __nv_bfloat16*>(p.residual) + gm * p.Cout + n_tile * BLOCK_N
-                     : nullptr;
-      const float* bias = p.bias + n_tile * BLOCK_N;
-#pragma unroll 1
-      for (int chunk = 0; chunk < BLOCK_N / 32; ++chunk) {
+      const int col0 = n_tile * BLOCK_N + half * kCols;
+      uint4 rv[kVec];
+      const bool has_res = p.residual != nullptr;
+      if (has_res && valid) {
+        const uint4* res = reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(p.residual) + gm * p.Cout + col0);
+#pragma unroll
+        for (int j = 0; j < kVec; ++j) rv[j] = __ldg(res + j);
+      } else {
+#pragma unroll
+        for (int j = 0; j < kVec; ++j) rv[j] = make_uint4(0, 0, 0, 0);
+      }
+      mbar_wait(&tmem_full_bar[acc], acc_phase);
+      tc_fence_after();
+      const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BLOCK_N + half * kCols;
+      uint4* out_row = reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(p.out) + gm * p.Cout + col0);
+      const float* bias = s_bias + col0;
+#pragma unroll
+      for (int chunk = 0; chunk < kChunks; ++chunk) {
         uint32_t v[32];
         tmem_ld_32x32(t_addr + chunk * 32, v);
         tmem_ld_wait_regs(v);
-        if (valid) {
-          float f[32];
+        if (chunk == kChunks - 1) {  // accumulator fully read: hand it back to the MMA warp
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
+        }
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const float4 bv = __ldg(reinterpret_cast<const float4*>(bias + chunk * 32) + j);
-            f[4 * j] = __uint_as_float(v[4 * j]) + bv.x;
-            f[4 * j + 1] = __uint_as_float(v[4 * j + 1]) + bv.y;
-            f[4 * j + 2] = __uint_as_float(v[4 * j + 2]) + bv.z;
-            f[4 * j + 3] = __uint_as_float(v[4 * j + 3]) + bv.w;
-          }
-          if (res_row != nullptr) {
+        for (int j = 0; j < 4; ++j) {
+          float f[8];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              const uint4 rv = __ldg(reinterpret_cast<const uint4*>(res_row + chunk * 32) + j);
-              f[8 * j] += bf16_lo(rv.x); f[8 * j + 1] += bf16_hi(rv.x);
-              f[8 * j + 2] += bf16_lo(rv.y); f[8 * j + 3] += bf16_hi(rv.y);
-              f[8 * j + 4] += bf16_lo(rv.z); f[8 * j + 5] += bf16_hi(rv.z);
-              f[8 * j + 6] += bf16_lo(rv.w); f[8 * j + 7] += bf16_hi(rv.w);
-            }
+          for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(v[8 * j + e]) + bias[chunk * 32 + 8 * j + e];
+          if (has_res) {
+            const uint4 r4 = rv[chunk * 4 + j];
+            f[0] += bf16_lo(r4.x); f[1] += bf16_hi(r4.x);
+            f[2] += bf16_lo(r4.y); f[3] += bf16_hi(r4.y);
+            f[4] += bf16_lo(r4.z); f[5] += bf16_hi(r4.z);
+            f[6] += bf16_lo(r4.w); f[7] += bf16_hi(r4.w);
           }
           if (p.relu) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
+            for (int e = 0; e < 8; ++e) f[e] = fmaxf(f[e], 0.f);
           }
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const uint4 o = make_uint4(pack_bf16x2(f[8 * j], f[8 * j + 1]), pack_bf16x2(f[8 * j + 2], f[8 * j + 3]),
-                                       pack_bf16x2(f[8 * j + 4], f[8 * j + 5]), pack_bf16x2(f[8 * j + 6], f[8 * j + 7]));
-            reinterpret_cast<uint4*>(out_row + chunk * 32)[j] = o;
-          }
+          if (valid)
+            out_row[chunk * 4 + j] = make_uint4(pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]),
+                                                pack_bf16x2(f[4], f[5]), pack_bf16x2(f[6], f[7]));
         }
       }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
     }
   }
 
@@ -265,6 +273,7 @@ int build_umma_conv(UmmaConvLaunch* L, const void* in, int B, int Hin, int Win, 
   PB_CHECK(Cin % 64 == 0, "umma conv: Cin %d not a multiple of 64", Cin);
   PB_CHECK(block_n == 64 || block_n == 128 || block_n == 256, "umma conv: block_n %d", block_n);
   PB_CHECK(Cout % block_n == 0, "umma conv: Cout %d %% block_n %d", Cout, block_n);
+  PB_CHECK(Cout <= 512, "umma conv: Cout %d > 512 (bias staging)", Cout);
   const int Ho = (Hin + 2 * pad - R) / stride + 1;
   const int Wo = (Win + 2 * pad - R) / stride + 1;
   PB_CHECK(stride == 1 || (Hin % 2 == 0 && Win % 2 == 0), "umma conv: stride 2 needs even H, W");

@@ -381,11 +381,23 @@ static inline uint8_t* buf_ptr(const pb200_plan* pl, const void* frames, void* w
 }
 
 static int choose_block_n(const ConvSpec& c, int B) {
-  // widest N tile that still gives every SM a tile; ties go to the wider tile (less A re-reading)
+  // Persistent CTAs take ceil(tiles / #SMs) equal tiles each, so the kernel time is rounds x (MMA cycles per tile).
+  // An M128 x N x K16 MMA costs max(48, N/2) cycles (tools/mma_bench.cu); ties go to the wider tile (the A tile is
+  // re-read from L2 once per N tile).
   const long long m_tiles = (static_cast<long long>(B) * c.Ho * c.Wo + 127) / 128;
-  int bn = c.Cout < 256 ? c.Cout : 256;
-  while (bn > 64 && m_tiles * (c.Cout / bn) < num_sms()) bn /= 2;
-  return bn;
+  int best = 64;
+  long long best_cost = -1;
+  for (int bn = 64; bn <= 256 && bn <= c.Cout; bn *= 2) {
+    if (c.Cout % bn) continue;
+    const long long tiles = m_tiles * (c.Cout / bn);
+    const long long rounds = (tiles + num_sms() - 1) / num_sms();
+    const long long cost = rounds * (bn / 2 < 48 ? 48 : bn / 2);
+    if (best_cost < 0 || cost <= best_cost) {
+      best = bn;
+      best_cost = cost;
+    }
+  }
+  return best;
 }
 
 // (re)build the TMA descriptors / launch parameters when a pointer or the batch size changed
