@@ -14,6 +14,8 @@
 //     owner, warps 2..9 = epilogue (TMEM -> registers -> bias/residual/ReLU -> bf16 NHWC).
 //   * persistent CTAs (grid = #SMs), static tile round-robin, smem ring of kStages stages,
 //     two TMEM accumulators so the epilogue of tile i overlaps the MMAs of tile i+1.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "conv_umma.cuh"
 #include "tma_host.h"
@@ -63,7 +65,7 @@ conv_umma_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams
 #pragma unroll
     for (int i = 0; i < kStages; ++i) {
       mbar_init(&full_bar[i], 1);
-      mbar_init(&empty_bar[i], 1);
+      mbar_init(&empty_bar[i], p.cl);  // every CTA of the cluster releases a stage (its B slice is multicast)
     }
     mbar_init(&tmem_full_bar[0], 1);
     mbar_init(&tmem_full_bar[1], 1);
@@ -78,17 +80,27 @@ conv_umma_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams
   for (int i = threadIdx.x; i < p.Cout; i += kUmmaThreads) s_bias[i] = __ldg(p.bias + i);
   tc_fence_before();
   __syncthreads();
+  if (p.cl > 1) cluster_sync_all();  // peers' barriers are initialised before anyone multicasts into them
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_slot;
+  // cluster geometry: the CL CTAs of a cluster take CL consecutive M tiles of the same N tile and share its
+  // weight tile: each CTA loads 1/CL of it and TMA-multicasts the slice into every CTA's stage buffer.
+  const int cl = p.cl;
+  const int crank = cl > 1 ? static_cast<int>(cluster_ctarank()) : 0;
+  const int cluster_id = blockIdx.x / cl;
+  const int num_clusters = gridDim.x / cl;
+  const uint16_t cmask = static_cast<uint16_t>((1u << cl) - 1u);
 
   if (warp == 0) {
     // ================================ TMA producer ================================
     // the whole warp runs the loop so every operand stays warp-uniform; one elected lane issues
     int stage = 0;
     uint32_t phase = 0;
-    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
-      const int m_tile = tile / p.num_n_tiles;
-      const int n_tile = tile - m_tile * p.num_n_tiles;
+    const int slice_rows = BLOCK_N / cl;
+    for (int st = cluster_id; st < p.num_super; st += num_clusters) {
+      const int m_super = st / p.num_n_tiles;
+      const int n_tile = st - m_super * p.num_n_tiles;
+      const int m_tile = m_super * cl + crank;
       int n0, ho0;
       if (p.tiles_per_img > 0) {
         n0 = m_tile / p.tiles_per_img;
@@ -112,7 +124,11 @@ conv_umma_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams
             mi = hp * 2 + wp;
           }
           tma_load_4d(a_dst, &maps.a[mi], &full_bar[stage], cb * 64, dw, ho0 + dh, n0);
-          tma_load_2d(b_dst, &maps.b, &full_bar[stage], kb * Cfg::kBlockK, n_tile * BLOCK_N);
+          if (cl == 1)
+            tma_load_2d(b_dst, &maps.b, &full_bar[stage], kb * Cfg::kBlockK, n_tile * BLOCK_N);
+          else
+            tma_load_2d_mcast(b_dst + crank * slice_rows * SW, &maps.b, &full_bar[stage], kb * Cfg::kBlockK,
+                              n_tile * BLOCK_N + crank * slice_rows, cmask);
         }
         __syncwarp();
         if (++cb == p.cblocks) {
@@ -136,7 +152,7 @@ conv_umma_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams
     int stage = 0;
     uint32_t phase = 0;
     int it = 0;
-    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+    for (int st = cluster_id; st < p.num_super; st += num_clusters, ++it) {
       const int acc = it & 1;
       const uint32_t acc_phase = (it >> 1) & 1;
       mbar_wait(&tmem_empty_bar[acc], acc_phase ^ 1u);
@@ -152,7 +168,9 @@ conv_umma_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams
           for (int k = 0; k < Cfg::kKSteps; ++k)
             // advancing K by 16 elements = 32 bytes inside the swizzle span: +2 in the address field
             umma_bf16_split(d_tmem, a_lo + 2 * k, d_hi, b_lo + 2 * k, d_hi, idesc, (kb | k) != 0 ? 1u : 0u);
-          umma_commit(&empty_bar[stage]);  // frees the smem stage once these MMAs have read it
+          // frees the smem stage (in every CTA of the cluster) once these MMAs have read it
+          if (cl == 1) umma_commit(&empty_bar[stage]);
+          else umma_commit_mcast(&empty_bar[stage], cmask);
           if (kb == p.num_kblocks - 1) umma_commit(&tmem_full_bar[acc]);
         }
         __syncwarp();
@@ -174,9 +192,10 @@ conv_umma_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams
     const int half = (warp - 2) >> 2;
     const int row = q * 32 + lane;
     int it = 0;
-    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
-      const int m_tile = tile / p.num_n_tiles;
-      const int n_tile = tile - m_tile * p.num_n_tiles;
+    for (int st = cluster_id; st < p.num_super; st += num_clusters, ++it) {
+      const int m_super = st / p.num_n_tiles;
+      const int n_tile = st - m_super * p.num_n_tiles;
+      const int m_tile = m_super * cl + crank;
       const int acc = it & 1;
       const uint32_t acc_phase = (it >> 1) & 1;
       const long long gm = static_cast<long long>(m_tile) * kTileM + row;
@@ -233,6 +252,7 @@ conv_umma_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams
 
   tc_fence_before();
   __syncthreads();
+  if (cl > 1) cluster_sync_all();  // no CTA leaves while a peer may still multicast into it or signal its barriers
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, Cfg::kTmemCols);
@@ -266,9 +286,39 @@ static int encode_weight_map(CUtensorMap* m, const void* w, int Cout, int Ktot, 
   return encode_tma_bf16(m, w, 2, dims, strides, box, sw);
 }
 
+// persistent grid = as many clusters as can be co-resident (clusters of 4 do not tile all 148 SMs)
+template <int BLOCK_N>
+static int query_clusters(int cl) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(num_sms() / cl * cl);
+  cfg.blockDim = dim3(kUmmaThreads);
+  cfg.dynamicSmemBytes = UmmaCfg<BLOCK_N, 128>::kSmemBytes;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = cl;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  int n = 0;
+  if (cudaOccupancyMaxActiveClusters(&n, conv_umma_kernel<BLOCK_N, 128>, &cfg) != cudaSuccess) {
+    (void)cudaGetLastError();
+    return 0;
+  }
+  return n;
+}
+static int max_active_clusters(int block_n, int cl) {
+  if (cl == 1) return num_sms();
+  static int cache[3][5] = {};
+  const int bi = block_n == 64 ? 0 : (block_n == 128 ? 1 : 2);
+  if (cache[bi][cl] == 0)
+    cache[bi][cl] = block_n == 64 ? query_clusters<64>(cl) : (block_n == 128 ? query_clusters<128>(cl) : query_clusters<256>(cl));
+  return cache[bi][cl];
+}
+
 int build_umma_conv(UmmaConvLaunch* L, const void* in, int B, int Hin, int Win, int Cin,
                     const void* wpacked, const float* bias, const void* residual, void* out, int Cout,
-                    int R, int stride, int pad, int relu, int block_n) {
+                    int R, int stride, int pad, int relu, int block_n, int cluster) {
   PB_CHECK(stride == 1 || stride == 2, "umma conv: stride %d unsupported", stride);
   PB_CHECK(Cin % 64 == 0, "umma conv: Cin %d not a multiple of 64", Cin);
   PB_CHECK(block_n == 64 || block_n == 128 || block_n == 256, "umma conv: block_n %d", block_n);
@@ -316,7 +366,20 @@ int build_umma_conv(UmmaConvLaunch* L, const void* in, int B, int Hin, int Win, 
   p.out = out;
   L->block_n = block_n;
   L->sw = 128;
-  L->grid = p.num_tiles < num_sms() ? p.num_tiles : num_sms();
+  // cluster size: share the weight tile among up to 4 CTAs when there are enough M tiles to keep every SM busy
+  int cl = cluster;
+  if (cl == 0) {
+    const char* force = getenv("PB200_FORCE_CLUSTER");  // tests: exercise the multicast path on small shapes
+    if (force != nullptr && (force[0] == '1' || force[0] == '2' || force[0] == '4') && force[1] == 0) cl = force[0] - '0';
+  }
+  if (cl == 0) cl = 1;  // measured (profiles/README.md r01): multicast halves L2 traffic but not the per-SM smem fill
+                        // (A + whole B still land in every CTA), which is what bounds these layers -> no gain
+  PB_CHECK(cl == 1 || cl == 2 || cl == 4, "umma conv: cluster %d", cl);
+  p.cl = cl;
+  p.num_super = (m_tiles + cl - 1) / cl * p.num_n_tiles;
+  const int max_clusters = max_active_clusters(block_n, cl);
+  PB_CHECK(max_clusters > 0, "umma conv: no resident cluster of %d CTAs", cl);
+  L->grid = (p.num_super < max_clusters ? p.num_super : max_clusters) * cl;
   L->flops = 2.0 * static_cast<double>(M) * Cout * R * R * Cin;
 
   const uint32_t box[4] = {64u, static_cast<uint32_t>(Wo), static_cast<uint32_t>(bh),
@@ -336,20 +399,32 @@ int build_umma_conv(UmmaConvLaunch* L, const void* in, int B, int Hin, int Win, 
         if (int rc = encode_tma_bf16(&L->maps.a[hp * 2 + wp], base, 4, dims, str, box, 128)) return rc;
       }
   }
-  return encode_weight_map(&L->maps.b, wpacked, Cout, R * R * Cin, block_n, 128);
+  return encode_weight_map(&L->maps.b, wpacked, Cout, R * R * Cin, block_n / p.cl, 128);
+}
+
+template <int BLOCK_N>
+static int launch_one(const UmmaConvLaunch& L, cudaStream_t st) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(L.grid);
+  cfg.blockDim = dim3(kUmmaThreads);
+  cfg.dynamicSmemBytes = UmmaCfg<BLOCK_N, 128>::kSmemBytes;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = L.p.cl;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  PB_CUDA(cudaLaunchKernelEx(&cfg, conv_umma_kernel<BLOCK_N, 128>, L.maps, L.p));
+  return PB200_OK;
 }
 
 int launch_umma_conv(const UmmaConvLaunch& L, cudaStream_t st) {
   if (L.p.num_tiles == 0) return PB200_OK;
-  if (L.block_n == 64) {
-    conv_umma_kernel<64, 128><<<L.grid, kUmmaThreads, UmmaCfg<64, 128>::kSmemBytes, st>>>(L.maps, L.p);
-  } else if (L.block_n == 128) {
-    conv_umma_kernel<128, 128><<<L.grid, kUmmaThreads, UmmaCfg<128, 128>::kSmemBytes, st>>>(L.maps, L.p);
-  } else {
-    conv_umma_kernel<256, 128><<<L.grid, kUmmaThreads, UmmaCfg<256, 128>::kSmemBytes, st>>>(L.maps, L.p);
-  }
-  PB_CUDA(cudaGetLastError());
-  return PB200_OK;
+  if (L.block_n == 64) return launch_one<64>(L, st);
+  if (L.block_n == 128) return launch_one<128>(L, st);
+  return launch_one<256>(L, st);
 }
 
 }  // namespace pb200

@@ -13,6 +13,8 @@ struct alignas(64) UmmaConvMaps {
 
 struct UmmaConvParams {
   int num_tiles, num_n_tiles, num_kblocks;
+  int cl;         // thread-block cluster size (1, 2 or 4): CTAs sharing one multicast weight tile
+  int num_super;  // ceil(m_tiles / cl) * num_n_tiles: work items per cluster loop
   int M_total;  // B*Ho*Wo output pixels
   int Cout;
   int stem;     // unused (kept 0)
@@ -40,7 +42,7 @@ struct UmmaConvLaunch {
 // with K order (r, s, c).
 int build_umma_conv(UmmaConvLaunch* L, const void* in, int B, int Hin, int Win, int Cin,
                     const void* wpacked, const float* bias, const void* residual, void* out, int Cout,
-                    int R, int stride, int pad, int relu, int block_n);
+                    int R, int stride, int pad, int relu, int block_n, int cluster = 0 /* 0 = choose */);
 int launch_umma_conv(const UmmaConvLaunch& L, cudaStream_t st);
 int umma_conv_init();  // sets the dynamic shared-memory attributes once per process
 
