@@ -369,15 +369,27 @@ int build_umma_conv(UmmaConvLaunch* L, const void* in, int B, int Hin, int Win, 
   // cluster size: share the weight tile among up to 4 CTAs when there are enough M tiles to keep every SM busy
   int cl = cluster;
   if (cl == 0) {
-    const char* force = getenv("PB200_FORCE_CLUSTER");  // tests: exercise the multicast path on small shapes
-    if (force != nullptr && (force[0] == '1' || force[0] == '2' || force[0] == '4') && force[1] == 0) cl = force[0] - '0';
+    const char* force = getenv("PB200_FORCE_CLUSTER");  // tests: exercise the cluster paths on small shapes
+    if (force != nullptr && force[1] == 0) {
+      if (force[0] == '1' || force[0] == '2' || force[0] == '4') cl = force[0] - '0';
+      if (force[0] == 'p') cl = -2;
+    }
   }
-  if (cl == 0) cl = 1;  // measured (profiles/README.md r01): multicast halves L2 traffic but not the per-SM smem fill
-                        // (A + whole B still land in every CTA), which is what bounds these layers -> no gain
-  PB_CHECK(cl == 1 || cl == 2 || cl == 4, "umma conv: cluster %d", cl);
+  // default: CTA pairs (halves the weight bytes landing in each SM) whenever there is a whole wave of pair tiles;
+  // plain multicast clusters measured no gain (profiles/README.md) and stay opt-in
+  if (cl == 0) cl = (static_cast<long long>(m_tiles) * p.num_n_tiles >= 2LL * num_sms()) ? -2 : 1;
+  PB_CHECK(cl == 1 || cl == 2 || cl == 4 || cl == -2, "umma conv: cluster %d", cl);
+  L->pair = cl == -2;
+  if (L->pair) cl = 2;
   p.cl = cl;
   p.num_super = (m_tiles + cl - 1) / cl * p.num_n_tiles;
-  const int max_clusters = max_active_clusters(block_n, cl);
+  int max_clusters;
+  if (L->pair) {
+    if (int rc = umma_pair_init()) return rc;
+    max_clusters = umma_pair_max_pairs(block_n);
+  } else {
+    max_clusters = max_active_clusters(block_n, cl);
+  }
   PB_CHECK(max_clusters > 0, "umma conv: no resident cluster of %d CTAs", cl);
   L->grid = (p.num_super < max_clusters ? p.num_super : max_clusters) * cl;
   L->flops = 2.0 * static_cast<double>(M) * Cout * R * R * Cin;
@@ -422,6 +434,7 @@ static int launch_one(const UmmaConvLaunch& L, cudaStream_t st) {
 
 int launch_umma_conv(const UmmaConvLaunch& L, cudaStream_t st) {
   if (L.p.num_tiles == 0) return PB200_OK;
+  if (L.pair) return launch_umma_pair(L, st);
   if (L.block_n == 64) return launch_one<64>(L, st);
   if (L.block_n == 128) return launch_one<128>(L, st);
   return launch_one<256>(L, st);

@@ -35,6 +35,7 @@ struct UmmaConvLaunch {
   int block_n;  // 64 / 128 / 256
   int sw;       // swizzle bytes = bytes of K per smem row: 128 (generic) or 64 (stem)
   int grid;
+  int pair;     // 1: CTA-pair kernel (conv_umma2.cu, tcgen05 cta_group::2), p.cl == 2
   double flops;  // algorithmic 2*MAC (unpadded)
 };
 
@@ -42,8 +43,12 @@ struct UmmaConvLaunch {
 // with K order (r, s, c).
 int build_umma_conv(UmmaConvLaunch* L, const void* in, int B, int Hin, int Win, int Cin,
                     const void* wpacked, const float* bias, const void* residual, void* out, int Cout,
-                    int R, int stride, int pad, int relu, int block_n, int cluster = 0 /* 0 = choose */);
-int launch_umma_conv(const UmmaConvLaunch& L, cudaStream_t st);
+                    int R, int stride, int pad, int relu, int block_n, int cluster = 0 /* 0 = choose; 1/2/4 = multicast cluster; -2 = CTA pair */);
+int launch_umma_conv(const UmmaConvLaunch& L, cudaStream_t st);  // dispatches on L.pair
+// conv_umma2.cu
+int umma_pair_init();
+int umma_pair_max_pairs(int block_n);
+int launch_umma_pair(const UmmaConvLaunch& L, cudaStream_t st);
 int umma_conv_init();  // sets the dynamic shared-memory attributes once per process
 
 }  // namespace pb200

@@ -1,0 +1,303 @@
+// CTA-pair (tcgen05 cta_group::2) variant of the TMA-im2col implicit-GEMM convolution of conv_umma.cu.
+// Same GEMM view, tensor maps and epilogue; what changes is who holds what:
+//   * a cluster of two CTAs computes a 256 x BLOCK_N tile.  Each CTA TMA-loads the activation tile of ITS 128
+//     output pixels and only HALF of the weight tile (BLOCK_N/2 rows) into its own shared memory; one
+//     tcgen05.mma.cta_group::2 issued by the pair leader reads A and the B halves from both CTAs and writes
+//     the accumulator rows of each CTA into that CTA's TMEM.
+//   * why: these layers are bound by the bytes that must LAND in each SM's shared memory per MMA cycle
+//     (smem capacity / L2 latency, tools/tma_bench.cu): per 64-deep k-block a CTA now receives 16 KB + BLOCK_N/2 rows
+//     instead of 16 KB + BLOCK_N rows, and the smaller stage buys two more pipeline stages.
+//   * barriers: both producers credit the LEADER's full barrier (remote arrive.expect_tx + TMA completion bytes);
+//     the leader's tcgen05.commit multicasts the "stage free" / "accumulator ready" arrivals to both CTAs; the
+//     peer's epilogue warps release the accumulator on the leader's barrier through its cluster address.
+#include <stdlib.h>
+
+#include "common.cuh"
+#include "conv_umma.cuh"
+
+namespace pb200 {
+
+constexpr int kPairThreads = 320;  // TMA warp + MMA warp + 8 epilogue warps (per CTA)
+
+template <int BLOCK_N>
+struct PairCfg {
+  static constexpr int kABytes = 128 * 128;
+  static constexpr int kBBytes = BLOCK_N / 2 * 128;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kStages = (192 * 1024 / kStageBytes) > 8 ? 8 : (192 * 1024 / kStageBytes);
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024;
+  static constexpr int kTmemCols = 2 * BLOCK_N;
+};
+
+template <int BLOCK_N>
+__global__ void __launch_bounds__(kPairThreads, 1)
+conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams p) {
+  using Cfg = PairCfg<BLOCK_N>;
+  constexpr int kStages = Cfg::kStages;
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t full_bar[kStages];   // used in the leader CTA only
+  __shared__ __align__(8) uint64_t empty_bar[kStages];  // per CTA: its stage buffers are free again
+  __shared__ __align__(8) uint64_t tmem_full_bar[2];    // per CTA: accumulator stage complete
+  __shared__ __align__(8) uint64_t tmem_empty_bar[2];   // leader only: both CTAs' epilogues drained the stage
+  __shared__ uint32_t tmem_base_slot;
+  __shared__ float s_bias[512];
+
+  const uint32_t raw_addr = smem_u32(smem_raw);
+  uint8_t* tiles = smem_raw + (((raw_addr + 1023u) & ~1023u) - raw_addr);
+  uint8_t* smem_a = tiles;
+  uint8_t* smem_b = tiles + kStages * Cfg::kABytes;
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int crank = static_cast<int>(cluster_ctarank());
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&maps.a[0]);
+    tma_prefetch_desc(&maps.b);
+#pragma unroll
+    for (int i = 0; i < kStages; ++i) {
+      mbar_init(&full_bar[i], 2);   // one arrive.expect_tx per producer of the pair
+      mbar_init(&empty_bar[i], 1);  // the leader's multicast commit
+    }
+    mbar_init(&tmem_full_bar[0], 1);
+    mbar_init(&tmem_full_bar[1], 1);
+    mbar_init(&tmem_empty_bar[0], 16);  // 8 epilogue warps x 2 CTAs
+    mbar_init(&tmem_empty_bar[1], 16);
+    fence_barrier_init();
+  }
+  if (warp == 1) {
+    tmem_alloc2(&tmem_base_slot, Cfg::kTmemCols);
+    tmem_relinquish2();
+  }
+  for (int i = threadIdx.x; i < p.Cout; i += kPairThreads) s_bias[i] = __ldg(p.bias + i);
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_slot;
+  const int pair_id = blockIdx.x >> 1;
+  const int num_pairs = gridDim.x >> 1;
+
+  if (warp == 0) {
+    // ================================ TMA producer (both CTAs) ====================
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int st = pair_id; st < p.num_super; st += num_pairs) {
+      const int m_super = st / p.num_n_tiles;
+      const int n_tile = st - m_super * p.num_n_tiles;
+      const int m_tile = m_super * 2 + crank;
+      int n0, ho0;
+      if (p.tiles_per_img > 0) {
+        n0 = m_tile / p.tiles_per_img;
+        ho0 = (m_tile - n0 * p.tiles_per_img) * p.bh;
+      } else {
+        n0 = m_tile * p.imgs_per_tile;
+        ho0 = 0;
+      }
+      int r = 0, s = 0, cb = 0;
+      for (int kb = 0; kb < p.num_kblocks; ++kb) {
+        mbar_wait(&empty_bar[stage], phase ^ 1u);
+        if (elect_one()) {
+          const uint32_t lfull = mapa_u32(&full_bar[stage], 0);  // the leader's barrier for this stage
+          mbar_expect_tx_cluster(lfull, Cfg::kStageBytes);
+          int dh = r - p.pad, dw = s - p.pad, mi = 0;
+          if (p.stride == 2) {
+            const int hp = dh & 1, wp = dw & 1;
+            dh = (dh - hp) >> 1;
+            dw = (dw - wp) >> 1;
+            mi = hp * 2 + wp;
+          }
+          tma_load_4d_2sm(smem_a + stage * Cfg::kABytes, &maps.a[mi], lfull, cb * 64, dw, ho0 + dh, n0);
+          tma_load_2d_2sm(smem_b + stage * Cfg::kBBytes, &maps.b, lfull, kb * 64,
+                          n_tile * BLOCK_N + crank * (BLOCK_N / 2));
+        }
+        __syncwarp();
+        if (++cb == p.cblocks) {
+          cb = 0;
+          if (++s == p.S) {
+            s = 0;
+            ++r;
+          }
+        }
+        if (++stage == kStages) {
+          stage = 0;
+          phase ^= 1u;
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================================ MMA issuer (pair leader only) ===============
+    if (crank == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(256, BLOCK_N);
+      const uint32_t tm = warp_uniform(tmem_base);
+      const uint32_t d_hi = desc_hi_swizzled(128);
+      int stage = 0;
+      uint32_t phase = 0;
+      int it = 0;
+      for (int st = pair_id; st < p.num_super; st += num_pairs, ++it) {
+        const int acc = it & 1;
+        mbar_wait(&tmem_empty_bar[acc], ((it >> 1) & 1u) ^ 1u);
+        tc_fence_after();
+        const uint32_t d_tmem = tm + acc * BLOCK_N;
+        for (int kb = 0; kb < p.num_kblocks; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          if (elect_one()) {
+            const uint32_t a_lo = desc_lo(smem_u32(smem_a + stage * Cfg::kABytes), 16);
+            const uint32_t b_lo = desc_lo(smem_u32(smem_b + stage * Cfg::kBBytes), 16);
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+              umma2_bf16_split(d_tmem, a_lo + 2 * k, d_hi, b_lo + 2 * k, d_hi, idesc, (kb | k) != 0 ? 1u : 0u);
+            umma2_commit_mcast(&empty_bar[stage], 3);  // both CTAs may refill this stage
+            if (kb == p.num_kblocks - 1) umma2_commit_mcast(&tmem_full_bar[acc], 3);
+          }
+          __syncwarp();
+          if (++stage == kStages) {
+            stage = 0;
+            phase ^= 1u;
+          }
+        }
+      }
+    }
+  } else {
+    // ================================ epilogue (both CTAs) =========================
+    constexpr int kCols = BLOCK_N / 2;
+    constexpr int kChunks = kCols / 32;
+    constexpr int kVec = kCols / 8;
+    const int q = warp & 3;
+    const int half = (warp - 2) >> 2;
+    const int row = q * 32 + lane;
+    int it = 0;
+    for (int st = pair_id; st < p.num_super; st += num_pairs, ++it) {
+      const int m_super = st / p.num_n_tiles;
+      const int n_tile = st - m_super * p.num_n_tiles;
+      const int m_tile = m_super * 2 + crank;
+      const int acc = it & 1;
+      const long long gm = static_cast<long long>(m_tile) * 128 + row;
+      const bool valid = gm < p.M_total;
+      const int col0 = n_tile * BLOCK_N + half * kCols;
+      uint4 rv[kVec];
+      const bool has_res = p.residual != nullptr;
+      if (has_res && valid) {
+        const uint4* res = reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(p.residual) + gm * p.Cout + col0);
+#pragma unroll
+        for (int j = 0; j < kVec; ++j) rv[j] = __ldg(res + j);
+      } else {
+#pragma unroll
+        for (int j = 0; j < kVec; ++j) rv[j] = make_uint4(0, 0, 0, 0);
+      }
+      mbar_wait(&tmem_full_bar[acc], (it >> 1) & 1u);
+      tc_fence_after();
+      const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BLOCK_N + half * kCols;
+      uint4* out_row = reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(p.out) + gm * p.Cout + col0);
+      const float* bias = s_bias + col0;
+#pragma unroll
+      for (int chunk = 0; chunk < kChunks; ++chunk) {
+        uint32_t v[32];
+        tmem_ld_32x32(t_addr + chunk * 32, v);
+        tmem_ld_wait_regs(v);
+        if (chunk == kChunks - 1) {  // accumulator stage fully read by this warp: tell the leader's MMA warp
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) {
+            if (crank == 0) mbar_arrive(&tmem_empty_bar[acc]);
+            else mbar_arrive_cluster(mapa_u32(&tmem_empty_bar[acc], 0));
+          }
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          float f[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(v[8 * j + e]) + bias[chunk * 32 + 8 * j + e];
+          if (has_res) {
+            const uint4 r4 = rv[chunk * 4 + j];
+            f[0] += bf16_lo(r4.x); f[1] += bf16_hi(r4.x);
+            f[2] += bf16_lo(r4.y); f[3] += bf16_hi(r4.y);
+            f[4] += bf16_lo(r4.z); f[5] += bf16_hi(r4.z);
+            f[6] += bf16_lo(r4.w); f[7] += bf16_hi(r4.w);
+          }
+          if (p.relu) {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) f[e] = fmaxf(f[e], 0.f);
+          }
+          if (valid)
+            out_row[chunk * 4 + j] = make_uint4(pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]),
+                                                pack_bf16x2(f[4], f[5]), pack_bf16x2(f[6], f[7]));
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();  // the peer's TMEM / barriers stay alive until the leader's last MMA and commit are done
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc2(tmem_base, Cfg::kTmemCols);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------
+template <int BLOCK_N>
+static int pair_cfg(cudaLaunchConfig_t* cfg, cudaLaunchAttribute* attr, int grid, cudaStream_t st) {
+  *cfg = cudaLaunchConfig_t{};
+  cfg->gridDim = dim3(grid);
+  cfg->blockDim = dim3(kPairThreads);
+  cfg->dynamicSmemBytes = PairCfg<BLOCK_N>::kSmemBytes;
+  cfg->stream = st;
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg->attrs = attr;
+  cfg->numAttrs = 1;
+  return PB200_OK;
+}
+
+template <int BLOCK_N>
+static int pair_init_one(int* max_pairs) {
+  PB_CUDA(cudaFuncSetAttribute(conv_umma2_kernel<BLOCK_N>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               PairCfg<BLOCK_N>::kSmemBytes));
+  cudaLaunchConfig_t cfg;
+  cudaLaunchAttribute attr[1];
+  pair_cfg<BLOCK_N>(&cfg, attr, num_sms() / 2 * 2, nullptr);
+  int n = 0;
+  PB_CUDA(cudaOccupancyMaxActiveClusters(&n, conv_umma2_kernel<BLOCK_N>, &cfg));
+  *max_pairs = n;
+  return PB200_OK;
+}
+
+static int g_max_pairs[3] = {0, 0, 0};  // BLOCK_N = 64, 128, 256
+
+int umma_pair_init() {
+  static bool done = false;
+  if (done) return PB200_OK;
+  if (int rc = pair_init_one<64>(&g_max_pairs[0])) return rc;
+  if (int rc = pair_init_one<128>(&g_max_pairs[1])) return rc;
+  if (int rc = pair_init_one<256>(&g_max_pairs[2])) return rc;
+  done = true;
+  return PB200_OK;
+}
+
+int umma_pair_max_pairs(int block_n) { return g_max_pairs[block_n == 64 ? 0 : (block_n == 128 ? 1 : 2)]; }
+
+int launch_umma_pair(const UmmaConvLaunch& L, cudaStream_t st) {
+  if (L.p.num_tiles == 0) return PB200_OK;
+  cudaLaunchConfig_t cfg;
+  cudaLaunchAttribute attr[1];
+  if (L.block_n == 64) {
+    pair_cfg<64>(&cfg, attr, L.grid, st);
+    PB_CUDA(cudaLaunchKernelEx(&cfg, conv_umma2_kernel<64>, L.maps, L.p));
+  } else if (L.block_n == 128) {
+    pair_cfg<128>(&cfg, attr, L.grid, st);
+    PB_CUDA(cudaLaunchKernelEx(&cfg, conv_umma2_kernel<128>, L.maps, L.p));
+  } else {
+    pair_cfg<256>(&cfg, attr, L.grid, st);
+    PB_CUDA(cudaLaunchKernelEx(&cfg, conv_umma2_kernel<256>, L.maps, L.p));
+  }
+  return PB200_OK;
+}
+
+}  // namespace pb200

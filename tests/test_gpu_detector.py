@@ -93,16 +93,16 @@ CONV_CASES = [
 ]
 
 
-@pytest.mark.parametrize("cluster", ["auto", "2", "4"])
+@pytest.mark.parametrize("cluster", ["1", "p", "2", "4"])
 @pytest.mark.parametrize("case", CONV_CASES, ids=[str(c) for c in CONV_CASES])
 def test_umma_conv_layer_vs_exact_operand_reference(case, cluster, monkeypatch):
     """tcgen05 implicit GEMM vs F.conv2d in fp64 on the SAME bf16-rounded operands: only fp32
     accumulation order and the final bf16 rounding differ (tolerance 2 bf16 ulps of the value)."""
     from perseus_b200 import _lib
 
-    # cluster 2 / 4: the weight tile is split across the CTAs of a thread-block cluster and TMA-multicast
+    # cluster p: CTA pair (cta_group::2, M = 256); 2 / 4: the weight tile is split across the CTAs of a thread-block cluster and TMA-multicast
     # (ragged M-tile counts leave some CTAs of the last cluster without a valid tile)
-    if cluster != "auto":
+    if True:
         monkeypatch.setenv("PB200_FORCE_CLUSTER", cluster)
     B, H, W, Cin, Cout, R, stride, pad, use_res, relu = case
     g = torch.Generator().manual_seed(hash(case) % 1000)

@@ -81,6 +81,19 @@ int main() {
     encode_tma_bf16(&m.m, buf, 2, dims, str, box, 128);
     run("B tile [256][2304]: box{64,256} 32 KB", m, 1, buf, 32768, 30);
   }
+  {
+    uint64_t dims[4] = {128, 32, 32, 256}, str[3] = {256, 32 * 256, 32 * 32 * 256}; uint32_t box[4] = {64, 32, 4, 1};
+    encode_tma_bf16(&m.m, buf, 4, dims, str, box, 128);
+    run("L2-hot A tile NHWC C=128: box{64,32,4} 16 KB", m, 0, buf, 16384, 8);
+    uint64_t dims2[2] = {2304, 256}, str2[1] = {4608}; uint32_t box2[2] = {64, 256};
+    encode_tma_bf16(&m.m, buf, 2, dims2, str2, box2, 128);
+    run("L2-hot B tile box{64,256} 32 KB", m, 1, buf, 32768, 4);
+    uint32_t box3[2] = {64, 128};
+    encode_tma_bf16(&m.m, buf, 2, dims2, str2, box3, 128);
+    run("L2-hot B tile box{64,128} 16 KB", m, 1, buf, 16384, 4);
+  }
+  run("L2-hot 1-D bulk copy 32 KB", m, 2, buf, 32768, 16);
+  run("L2-hot 1-D bulk copy 16 KB", m, 2, buf, 16384, 16);
   run("1-D bulk copy 16 KB", m, 2, buf, 16384, 4000);
   run("1-D bulk copy 32 KB", m, 2, buf, 32768, 4000);
   run("1-D bulk copy 4 KB", m, 2, buf, 4096, 4000);
