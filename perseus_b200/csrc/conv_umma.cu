@@ -22,7 +22,7 @@
 
 namespace pb200 {
 
-constexpr int kUmmaThreads = 320;  // TMA warp + MMA warp + 8 epilogue warps
+constexpr int kUmmaThreads = 352;  // 2 TMA warps + MMA warp + 8 epilogue warps
 constexpr int kTileM = 128;
 
 template <int BLOCK_N, int SW>
@@ -91,7 +91,11 @@ conv_umma_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams
   const int num_clusters = gridDim.x / cl;
   const uint16_t cmask = static_cast<uint16_t>((1u << cl) - 1u);
 
-  if (warp == 0) {
+  if (warp == 0 || warp == 10) {
+    // two producer warps take alternate k-blocks: one warp's issue loop (barrier wait + expect_tx + 2 TMA issues)
+    // costs about as many cycles as a 256-cycle k-block of MMAs (profiles/README.md r01)
+    const int pi = warp == 0 ? 0 : 1;
+    uint32_t g = 0;  // k-block counter of this CTA across all its tiles
     // ================================ TMA producer ================================
     // the whole warp runs the loop so every operand stays warp-uniform; one elected lane issues
     int stage = 0;
@@ -109,38 +113,38 @@ conv_umma_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams
         n0 = m_tile * p.imgs_per_tile;
         ho0 = 0;
       }
-      int r = 0, s = 0, cb = 0;
-      for (int kb = 0; kb < p.num_kblocks; ++kb) {
-        mbar_wait(&empty_bar[stage], phase ^ 1u);
-        if (elect_one()) {
-          mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
-          uint8_t* a_dst = smem_a + stage * Cfg::kABytes;
-          uint8_t* b_dst = smem_b + stage * Cfg::kBBytes;
-          int dh = r - p.pad, dw = s - p.pad, mi = 0;
-          if (p.stride == 2) {
-            const int hp = dh & 1, wp = dw & 1;
-            dh = (dh - hp) >> 1;
-            dw = (dw - wp) >> 1;
-            mi = hp * 2 + wp;
-          }
-          tma_load_4d(a_dst, &maps.a[mi], &full_bar[stage], cb * 64, dw, ho0 + dh, n0);
-          if (cl == 1)
-            tma_load_2d(b_dst, &maps.b, &full_bar[stage], kb * Cfg::kBlockK, n_tile * BLOCK_N);
-          else
-            tma_load_2d_mcast(b_dst + crank * slice_rows * SW, &maps.b, &full_bar[stage], kb * Cfg::kBlockK,
-                              n_tile * BLOCK_N + crank * slice_rows, cmask);
+      // the issue loop is kept as light as possible: one warp must feed a k-block every 128-512 MMA cycles
+      const int taps = p.S * p.S;
+      int kcol = 0;
+      for (int tap = 0; tap < taps; ++tap) {
+        const int r = tap / p.S, s = tap - r * p.S;
+        int dh = r - p.pad, dw = s - p.pad, mi = 0;
+        if (p.stride == 2) {
+          const int hp = dh & 1, wp = dw & 1;
+          dh = (dh - hp) >> 1;
+          dw = (dw - wp) >> 1;
+          mi = hp * 2 + wp;
         }
-        __syncwarp();
-        if (++cb == p.cblocks) {
-          cb = 0;
-          if (++s == p.S) {
-            s = 0;
-            ++r;
+        const CUtensorMap* amap = &maps.a[mi];
+        const int hrow = ho0 + dh;
+        for (int cb = 0; cb < p.cblocks; ++cb, kcol += Cfg::kBlockK) {
+          if ((g++ & 1u) == static_cast<uint32_t>(pi)) {
+          mbar_wait(&empty_bar[stage], phase ^ 1u);
+          if (elect_one()) {
+            mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+            tma_load_4d(smem_a + stage * Cfg::kABytes, amap, &full_bar[stage], cb * 64, dw, hrow, n0);
+            if (cl == 1)
+              tma_load_2d(smem_b + stage * Cfg::kBBytes, &maps.b, &full_bar[stage], kcol, n_tile * BLOCK_N);
+            else
+              tma_load_2d_mcast(smem_b + stage * Cfg::kBBytes + crank * slice_rows * SW, &maps.b, &full_bar[stage], kcol,
+                                n_tile * BLOCK_N + crank * slice_rows, cmask);
           }
-        }
-        if (++stage == kStages) {
-          stage = 0;
-          phase ^= 1u;
+          __syncwarp();
+          }
+          if (++stage == kStages) {
+            stage = 0;
+            phase ^= 1u;
+          }
         }
       }
     }

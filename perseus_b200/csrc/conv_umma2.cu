@@ -17,7 +17,7 @@
 
 namespace pb200 {
 
-constexpr int kPairThreads = 320;  // TMA warp + MMA warp + 8 epilogue warps (per CTA)
+constexpr int kPairThreads = 352;  // 2 TMA warps + MMA warp + 8 epilogue warps (per CTA)
 
 template <int BLOCK_N>
 struct PairCfg {
@@ -78,10 +78,15 @@ conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParam
   const int pair_id = blockIdx.x >> 1;
   const int num_pairs = gridDim.x >> 1;
 
-  if (warp == 0) {
+  if (warp == 0 || warp == 10) {
+    // two producer warps take alternate k-blocks: one warp's issue loop (barrier wait + expect_tx + 2 TMA issues)
+    // costs about as many cycles as a 256-cycle k-block of MMAs (profiles/README.md r01)
+    const int pi = warp == 0 ? 0 : 1;
+    uint32_t g = 0;  // k-block counter of this CTA across all its tiles
     // ================================ TMA producer (both CTAs) ====================
     int stage = 0;
     uint32_t phase = 0;
+    const uint32_t lfull0 = mapa_u32(&full_bar[0], 0);
     for (int st = pair_id; st < p.num_super; st += num_pairs) {
       const int m_super = st / p.num_n_tiles;
       const int n_tile = st - m_super * p.num_n_tiles;
@@ -94,34 +99,36 @@ conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParam
         n0 = m_tile * p.imgs_per_tile;
         ho0 = 0;
       }
-      int r = 0, s = 0, cb = 0;
-      for (int kb = 0; kb < p.num_kblocks; ++kb) {
-        mbar_wait(&empty_bar[stage], phase ^ 1u);
-        if (elect_one()) {
-          const uint32_t lfull = mapa_u32(&full_bar[stage], 0);  // the leader's barrier for this stage
-          mbar_expect_tx_cluster(lfull, Cfg::kStageBytes);
-          int dh = r - p.pad, dw = s - p.pad, mi = 0;
-          if (p.stride == 2) {
-            const int hp = dh & 1, wp = dw & 1;
-            dh = (dh - hp) >> 1;
-            dw = (dw - wp) >> 1;
-            mi = hp * 2 + wp;
-          }
-          tma_load_4d_2sm(smem_a + stage * Cfg::kABytes, &maps.a[mi], lfull, cb * 64, dw, ho0 + dh, n0);
-          tma_load_2d_2sm(smem_b + stage * Cfg::kBBytes, &maps.b, lfull, kb * 64,
-                          n_tile * BLOCK_N + crank * (BLOCK_N / 2));
+      // the issue loop is kept as light as possible: one warp must feed a k-block every 256-512 MMA cycles
+      const int n_row = n_tile * BLOCK_N + crank * (BLOCK_N / 2);
+      const int taps = p.S * p.S;
+      int kcol = 0;
+      for (int tap = 0; tap < taps; ++tap) {
+        const int r = tap / p.S, s = tap - r * p.S;
+        int dh = r - p.pad, dw = s - p.pad, mi = 0;
+        if (p.stride == 2) {
+          const int hp = dh & 1, wp = dw & 1;
+          dh = (dh - hp) >> 1;
+          dw = (dw - wp) >> 1;
+          mi = hp * 2 + wp;
         }
-        __syncwarp();
-        if (++cb == p.cblocks) {
-          cb = 0;
-          if (++s == p.S) {
-            s = 0;
-            ++r;
+        const CUtensorMap* amap = &maps.a[mi];
+        const int hrow = ho0 + dh;
+        for (int cb = 0; cb < p.cblocks; ++cb, kcol += 64) {
+          if ((g++ & 1u) == static_cast<uint32_t>(pi)) {
+          mbar_wait(&empty_bar[stage], phase ^ 1u);
+          if (elect_one()) {
+            const uint32_t lfull = lfull0 + stage * 8;  // the leader's full barrier of this stage
+            mbar_expect_tx_cluster(lfull, Cfg::kStageBytes);
+            tma_load_4d_2sm(smem_a + stage * Cfg::kABytes, amap, lfull, cb * 64, dw, hrow, n0);
+            tma_load_2d_2sm(smem_b + stage * Cfg::kBBytes, &maps.b, lfull, kcol, n_row);
           }
-        }
-        if (++stage == kStages) {
-          stage = 0;
-          phase ^= 1u;
+          __syncwarp();
+          }
+          if (++stage == kStages) {
+            stage = 0;
+            phase ^= 1u;
+          }
         }
       }
     }

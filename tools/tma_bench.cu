@@ -31,7 +31,14 @@ __global__ void __launch_bounds__(32, 1) bench(const __grid_constant__ Maps maps
         const int j = (i * 7 + blockIdx.x * 13) % span;  // walk over the tensor so loads are not the same lines
         if (mode == 0) tma_load_4d(base + s * 32768, &maps.m, &full[s], 0, -1 + (j & 1), (j >> 1) % 28, j % 200);
         else if (mode == 1) tma_load_2d(base + s * 32768, &maps.m, &full[s], (j % 30) * 64, (j % 2) * 128);
-        else bulk_load_1d(base + s * 32768, src + (size_t)j * bytes, bytes, &full[s]);
+        else if (mode == 2) bulk_load_1d(base + s * 32768, src + (size_t)j * bytes, bytes, &full[s]);
+        else if (mode == 3) {  // two 1-D copies of bytes/2 per iteration on one barrier
+          bulk_load_1d(base + s * 32768, src + (size_t)j * bytes, bytes / 2, &full[s]);
+          bulk_load_1d(base + s * 32768 + bytes / 2, src + (size_t)j * bytes + bytes / 2, bytes / 2, &full[s]);
+        } else {  // mode 4: four copies
+          for (int q = 0; q < 4; ++q)
+            bulk_load_1d(base + s * 32768 + q * (bytes / 4), src + (size_t)j * bytes + q * (bytes / 4), bytes / 4, &full[s]);
+        }
       }
     }
     out[blockIdx.x] = clock64() - t0;
@@ -93,6 +100,9 @@ int main() {
     run("L2-hot B tile box{64,128} 16 KB", m, 1, buf, 16384, 4);
   }
   run("L2-hot 1-D bulk copy 32 KB", m, 2, buf, 32768, 16);
+  run("L2-hot 2 x 16 KB per iteration", m, 3, buf, 32768, 16);
+  run("L2-hot 4 x 8 KB per iteration", m, 4, buf, 32768, 16);
+  run("L2-hot 4 x 2 KB per iteration", m, 4, buf, 8192, 16);
   run("L2-hot 1-D bulk copy 16 KB", m, 2, buf, 16384, 16);
   run("1-D bulk copy 16 KB", m, 2, buf, 16384, 4000);
   run("1-D bulk copy 32 KB", m, 2, buf, 32768, 4000);
