@@ -395,28 +395,49 @@ def run_native(args):
     line = None
     if rank == 0:
         peaks = load_peaks()
-        # roofline of the dominant kernel family (the tcgen05 conv kernels): per-launch CUDA events
+        # roofline of the dominant kernel (largest share of the step): per-launch CUDA events on the launching stream
         reps = 5
         acc = None
         for _ in range(reps):
             rows = model.profile_ops(frames, BATCH)
-            acc = rows if acc is None else [(a[0], a[1] + b[1], a[2], a[3]) for a, b in zip(acc, rows)]
-        rows = [(n, t / reps, f, b) for n, t, f, b in acc]
-        conv = [r for r in rows if r[2] > 1e6]
-        conv_ms = sum(r[1] for r in conv)
-        conv_flops = sum(r[2] for r in conv)
+            acc = rows if acc is None else [(a[0], a[1] + b[1], a[2], a[3], a[4]) for a, b in zip(acc, rows)]
+        rows = [(n, t / reps, f, b, k) for n, t, f, b, k in acc]
         tot_ms = sum(r[1] for r in rows)
-        achieved = conv_flops / (conv_ms * 1e-3) / 1e12
+        by_kernel = {}
+        for n, t, f, b, k in rows:
+            e = by_kernel.setdefault(k, {"ms": 0.0, "flops": 0.0, "bytes": 0.0, "launches": 0})
+            e["ms"] += t
+            e["flops"] += f
+            e["bytes"] += b
+            e["launches"] += 1
+        dom = max((k for k in by_kernel if by_kernel[k]["flops"] > 1e6), key=lambda k: by_kernel[k]["ms"])
+        conv_ms = sum(e["ms"] for e in by_kernel.values() if e["flops"] > 1e6)
+        conv_flops = sum(e["flops"] for e in by_kernel.values() if e["flops"] > 1e6)
         peak = peaks["bf16_tflops_sustained"]
+        try:
+            with open(os.path.join(ROOT, "profiles", "traffic.json")) as fh:
+                traffic = json.load(fh)
+        except Exception:
+            traffic = {}
+        d = by_kernel[dom]
+        achieved = d["flops"] / (d["ms"] * 1e-3) / 1e12
         roofline = {
             "bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
-            "traffic": None,
-            "kernel": "conv_umma_kernel (21 launches/step: stem + 20 convs)",
+            "traffic": traffic.get(dom, {}).get("dram_bytes_per_launch"),
+            "kernel": dom, "launches_per_step": d["launches"],
+            "algorithmic_flops_per_launch": d["flops"] / d["launches"], "avg_launch_ms": d["ms"] / d["launches"],
             "peak_source": peaks["source"] + ", sustained bf16 (kernel timed inside a long step); burst "
                            f"{peaks['bf16_tflops']}",
-            "share_of_step": conv_ms / tot_ms,
+            "share_of_step": d["ms"] / tot_ms,
+            "all_tcgen05_conv_kernels": {"achieved": conv_flops / (conv_ms * 1e-3) / 1e12,
+                                         "frac": conv_flops / (conv_ms * 1e-3) / 1e12 / peak, "share_of_step": conv_ms / tot_ms},
             "whole_step_frac": (BATCH * FLOPS_PER_FRAME_RGB / (ms / args.steps * 1e-3) / 1e12) / peak,
-            "per_op_ms": {n: round(t, 4) for n, t, _, _ in rows},
+            "per_kernel": {k: {"ms": round(e["ms"], 4), "launches": e["launches"],
+                               "TFLOPs": round(e["flops"] / (e["ms"] * 1e-3) / 1e12, 1) if e["flops"] > 1e6 else None,
+                               "GBps": round(e["bytes"] / (e["ms"] * 1e-3) / 1e9, 1),
+                               "dram_bytes_per_launch_ncu": traffic.get(k, {}).get("dram_bytes_per_launch")}
+                           for k, e in by_kernel.items()},
+            "per_op_ms": {n: round(t, 4) for n, t, _, _, _ in rows},
         }
         latency = measure_latency(model, dev)
         factors = measure_factors(dev, peaks)

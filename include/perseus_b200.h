@@ -122,6 +122,8 @@ int pb200_forward_nchw_f32(pb200_plan* plan, const float* x_nchw, void* workspac
  * ms has room for pb200_plan_num_ops() floats. */
 int pb200_plan_num_ops(const pb200_plan* plan);
 const char* pb200_plan_op_name(const pb200_plan* plan, int i);
+/* name of the kernel op i launches (depends on the batch size of the last forward for the tcgen05 convs) */
+const char* pb200_plan_op_kernel(const pb200_plan* plan, int i);
 /* algorithmic FLOPs (2*MAC, unpadded) and algorithmic HBM bytes of op i for B frames */
 int pb200_plan_op_work(const pb200_plan* plan, int i, int B, double* flops, double* bytes);
 int pb200_forward_profile(pb200_plan* plan, const void* frames, void* workspace, float* out_norm,

@@ -45,6 +45,7 @@ SIGNATURES = {
     "pb200_forward_nchw_f32": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
     "pb200_plan_num_ops": (c_int, [c_void_p]),
     "pb200_plan_op_name": (c_char_p, [c_void_p, c_int]),
+    "pb200_plan_op_kernel": (c_char_p, [c_void_p, c_int]),
     "pb200_plan_op_work": (c_int, [c_void_p, c_int, c_int, POINTER(c_double), POINTER(c_double)]),
     "pb200_forward_profile": (
         c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, POINTER(c_float)]

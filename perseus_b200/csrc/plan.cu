@@ -64,6 +64,7 @@ struct pb200_plan {
   int cache_B = -1;
   std::vector<pb200::UmmaConvLaunch> umma;  // per conv
   std::vector<std::string> op_names;
+  std::vector<std::string> op_kernels;  // kernel each op launches (known after the first forward at a batch size)
 };
 
 namespace pb200 {
@@ -515,6 +516,29 @@ extern "C" int pb200_plan_num_ops(const pb200_plan* plan) {
 extern "C" const char* pb200_plan_op_name(const pb200_plan* plan, int i) {
   if (!plan || i < 0 || i >= static_cast<int>(plan->ops.size())) return "";
   return plan->op_names[i].c_str();
+}
+extern "C" const char* pb200_plan_op_kernel(const pb200_plan* plan, int i) {
+  if (!plan || i < 0 || i >= static_cast<int>(plan->ops.size())) return "";
+  const Op& op = plan->ops[i];
+  pb200_plan* pl = const_cast<pb200_plan*>(plan);
+  if (pl->op_kernels.size() != plan->ops.size()) pl->op_kernels.assign(plan->ops.size(), "");
+  std::string& k = pl->op_kernels[i];
+  switch (op.kind) {
+    case OP_STEM_POOL: k = "stem_pool_kernel"; break;
+    case OP_CONV_P8: k = "conv_p8_kernel"; break;
+    case OP_MAXPOOL: k = plan->bf16 ? "maxpool_bf16_kernel" : "maxpool_f32_kernel"; break;
+    case OP_HEAD: k = "head_kernel"; break;
+    case OP_CONV:
+      if (!plan->bf16) k = "conv_simt_kernel";
+      else if (plan->cache_B < 0 || plan->umma.size() != plan->convs.size()) k = "conv_umma*";
+      else {
+        const UmmaConvLaunch& L = plan->umma[op.conv];
+        k = std::string(L.pair ? "conv_umma2_kernel<" : "conv_umma_kernel<") + std::to_string(L.block_n) + ">";
+      }
+      break;
+    default: k = ""; break;
+  }
+  return k.c_str();
 }
 extern "C" int pb200_plan_launches_per_forward(const pb200_plan* plan) {
   return plan ? static_cast<int>(plan->ops.size()) : 0;

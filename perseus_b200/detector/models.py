@@ -277,7 +277,7 @@ class KeypointCNN(nn.Module):
         return px
 
     def profile_ops(self, frames: torch.Tensor, B: int):
-        """Per-kernel CUDA-event times of one forward: list of (name, ms, flops, bytes)."""
+        """Per-kernel CUDA-event times of one forward: list of (name, ms, flops, bytes, kernel)."""
         plan = self._plan(frames.device, B)
         n = plan.lib.pb200_plan_num_ops(plan.handle)
         ms = (ctypes.c_float * n)()
@@ -293,5 +293,6 @@ class KeypointCNN(nn.Module):
         for i in range(n):
             fl, by = ctypes.c_double(), ctypes.c_double()
             _lib.check(plan.lib.pb200_plan_op_work(plan.handle, i, B, ctypes.byref(fl), ctypes.byref(by)))
-            rows.append((plan.lib.pb200_plan_op_name(plan.handle, i).decode(), float(ms[i]), fl.value, by.value))
+            rows.append((plan.lib.pb200_plan_op_name(plan.handle, i).decode(), float(ms[i]), fl.value, by.value,
+                         plan.lib.pb200_plan_op_kernel(plan.handle, i).decode()))
         return rows
