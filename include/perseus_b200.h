@@ -144,6 +144,13 @@ int pb200_debug_conv_bf16(const void* in_nhwc, int B, int H, int W, int Cin, con
                           const void* residual_nhwc_or_null, int relu, void* out_nhwc,
                           pb200_stream stream);
 
+/* Same for the split-bf16 ("bf16x3") mode: activations, residual and output are NHWC bf16 with 2*C
+ * channels per pixel, [hi(C) | lo(C)], value = hi + lo. */
+int pb200_debug_conv_split(const void* in_nhwc2, int B, int H, int W, int Cin, const float* w_oihw_host,
+                           const float* bias_host, int Cout, int R, int stride, int pad,
+                           const void* residual_nhwc2_or_null, int relu, void* out_nhwc2,
+                           pb200_stream stream);
+
 /* Unit-test entries of the P8-layout kernels (allocate / synchronise — not product entries).
  * P8 = bf16 [n][C/8][H+2][W+2][8] with a zero border.
  *   pb200_debug_stem_pool : fused conv1+bn1+relu+maxpool of a loaded bf16 plan: frames -> P8 [B][8][H/4+2][W/4+2][8]

@@ -13,7 +13,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libperseus_b200.so")
 
 PREC_FP32, PREC_BF16, PREC_BF16X3 = 0, 1, 2
-PRECISIONS = {"fp32": PREC_FP32, "bf16": PREC_BF16}
+PRECISIONS = {"fp32": PREC_FP32, "bf16": PREC_BF16, "bf16x3": PREC_BF16X3}
 
 ERR_NO_DEVICE = 3
 
@@ -53,6 +53,11 @@ SIGNATURES = {
     "pb200_plan_launches_per_forward": (c_int, [c_void_p]),
     "pb200_decode_pixels": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p]),
     "pb200_debug_conv_bf16": (
+        c_int,
+        [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_int,
+         c_void_p, c_void_p],
+    ),
+    "pb200_debug_conv_split": (
         c_int,
         [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_int,
          c_void_p, c_void_p],

@@ -37,7 +37,7 @@ struct UmmaCfg {
   static constexpr int kTmemCols = 2 * BLOCK_N;                      // double-buffered accumulator
 };
 
-template <int BLOCK_N, int SW>
+template <int BLOCK_N, int SW, bool SPLIT>
 __global__ void __launch_bounds__(kUmmaThreads, 1)
 conv_umma_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams p) {
   using Cfg = UmmaCfg<BLOCK_N, SW>;
@@ -128,15 +128,22 @@ conv_umma_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams
         const CUtensorMap* amap = &maps.a[mi];
         const int hrow = ho0 + dh;
         for (int cb = 0; cb < p.cblocks; ++cb, kcol += Cfg::kBlockK) {
+          // SPLIT ("bf16x3"): a = a_hi + a_lo (channels [0,Cin) and [Cin,2Cin) of the activation tensor),
+          // w = w_hi + w_lo (columns [0,Ktot) and [Ktot,2Ktot) of the packed weights); three k-blocks per
+          // (tap, channel block): a_hi*w_hi, a_lo*w_hi, a_hi*w_lo (lo*lo is below fp32 resolution)
+#pragma unroll
+          for (int ps = 0; ps < (SPLIT ? 3 : 1); ++ps) {
           if ((g++ & 1u) == static_cast<uint32_t>(pi)) {
+          const int a_ch = cb * 64 + ((SPLIT && ps == 1) ? p.cin : 0);
+          const int b_col = kcol + ((SPLIT && ps == 2) ? p.ktot : 0);
           mbar_wait(&empty_bar[stage], phase ^ 1u);
           if (elect_one()) {
             mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
-            tma_load_4d(smem_a + stage * Cfg::kABytes, amap, &full_bar[stage], cb * 64, dw, hrow, n0);
+            tma_load_4d(smem_a + stage * Cfg::kABytes, amap, &full_bar[stage], a_ch, dw, hrow, n0);
             if (cl == 1)
-              tma_load_2d(smem_b + stage * Cfg::kBBytes, &maps.b, &full_bar[stage], kcol, n_tile * BLOCK_N);
+              tma_load_2d(smem_b + stage * Cfg::kBBytes, &maps.b, &full_bar[stage], b_col, n_tile * BLOCK_N);
             else
-              tma_load_2d_mcast(smem_b + stage * Cfg::kBBytes + crank * slice_rows * SW, &maps.b, &full_bar[stage], kcol,
+              tma_load_2d_mcast(smem_b + stage * Cfg::kBBytes + crank * slice_rows * SW, &maps.b, &full_bar[stage], b_col,
                                 n_tile * BLOCK_N + crank * slice_rows, cmask);
           }
           __syncwarp();
@@ -144,6 +151,7 @@ conv_umma_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams
           if (++stage == kStages) {
             stage = 0;
             phase ^= 1u;
+          }
           }
         }
       }
@@ -205,8 +213,60 @@ conv_umma_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams
       const long long gm = static_cast<long long>(m_tile) * kTileM + row;
       const bool valid = gm < p.M_total;
       const int col0 = n_tile * BLOCK_N + half * kCols;
-      uint4 rv[kVec];
       const bool has_res = p.residual != nullptr;
+      if constexpr (SPLIT) {
+        // rows of the split tensors are [hi(Cout) | lo(Cout)]; the residual is hi + lo; the result is stored as
+        // hi = bf16(f), lo = bf16(f - hi)
+        mbar_wait(&tmem_full_bar[acc], acc_phase);
+        tc_fence_after();
+        const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BLOCK_N + half * kCols;
+        const long long rowoff = gm * (2LL * p.Cout) + col0;
+        uint4* out_hi = reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(p.out) + rowoff);
+        uint4* out_lo = reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(p.out) + rowoff + p.Cout);
+        const uint4* res_hi = reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(p.residual) + rowoff);
+        const uint4* res_lo = reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(p.residual) + rowoff + p.Cout);
+        const float* bias = s_bias + col0;
+#pragma unroll 1
+        for (int chunk = 0; chunk < kChunks; ++chunk) {
+          uint32_t v[32];
+          tmem_ld_32x32(t_addr + chunk * 32, v);
+          tmem_ld_wait_regs(v);
+          if (chunk == kChunks - 1) {
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
+          }
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            float f[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(v[8 * j + e]) + bias[chunk * 32 + 8 * j + e];
+            if (has_res && valid) {
+              const uint4 h4 = __ldg(res_hi + chunk * 4 + j), l4 = __ldg(res_lo + chunk * 4 + j);
+              f[0] += bf16_lo(h4.x) + bf16_lo(l4.x); f[1] += bf16_hi(h4.x) + bf16_hi(l4.x);
+              f[2] += bf16_lo(h4.y) + bf16_lo(l4.y); f[3] += bf16_hi(h4.y) + bf16_hi(l4.y);
+              f[4] += bf16_lo(h4.z) + bf16_lo(l4.z); f[5] += bf16_hi(h4.z) + bf16_hi(l4.z);
+              f[6] += bf16_lo(h4.w) + bf16_lo(l4.w); f[7] += bf16_hi(h4.w) + bf16_hi(l4.w);
+            }
+            if (p.relu) {
+#pragma unroll
+              for (int e = 0; e < 8; ++e) f[e] = fmaxf(f[e], 0.f);
+            }
+            uint32_t hi[4], lo[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              hi[e] = pack_bf16x2(f[2 * e], f[2 * e + 1]);
+              lo[e] = pack_bf16x2(f[2 * e] - bf16_lo(hi[e]), f[2 * e + 1] - bf16_hi(hi[e]));
+            }
+            if (valid) {
+              out_hi[chunk * 4 + j] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+              out_lo[chunk * 4 + j] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+            }
+          }
+        }
+        continue;
+      }
+      uint4 rv[kVec];
       if (has_res && valid) {
         const uint4* res = reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(p.residual) + gm * p.Cout + col0);
 #pragma unroll
@@ -268,7 +328,9 @@ conv_umma_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams
 // ------------------------------------------------------------------------------------------
 template <int BLOCK_N, int SW>
 static int set_attr() {
-  PB_CUDA(cudaFuncSetAttribute(conv_umma_kernel<BLOCK_N, SW>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  PB_CUDA(cudaFuncSetAttribute(conv_umma_kernel<BLOCK_N, SW, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               UmmaCfg<BLOCK_N, SW>::kSmemBytes));
+  PB_CUDA(cudaFuncSetAttribute(conv_umma_kernel<BLOCK_N, SW, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                UmmaCfg<BLOCK_N, SW>::kSmemBytes));
   return PB200_OK;
 }
@@ -305,7 +367,7 @@ static int query_clusters(int cl) {
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   int n = 0;
-  if (cudaOccupancyMaxActiveClusters(&n, conv_umma_kernel<BLOCK_N, 128>, &cfg) != cudaSuccess) {
+  if (cudaOccupancyMaxActiveClusters(&n, conv_umma_kernel<BLOCK_N, 128, false>, &cfg) != cudaSuccess) {
     (void)cudaGetLastError();
     return 0;
   }
@@ -322,7 +384,7 @@ static int max_active_clusters(int block_n, int cl) {
 
 int build_umma_conv(UmmaConvLaunch* L, const void* in, int B, int Hin, int Win, int Cin,
                     const void* wpacked, const float* bias, const void* residual, void* out, int Cout,
-                    int R, int stride, int pad, int relu, int block_n, int cluster) {
+                    int R, int stride, int pad, int relu, int block_n, int cluster, int split) {
   PB_CHECK(stride == 1 || stride == 2, "umma conv: stride %d unsupported", stride);
   PB_CHECK(Cin % 64 == 0, "umma conv: Cin %d not a multiple of 64", Cin);
   PB_CHECK(block_n == 64 || block_n == 128 || block_n == 256, "umma conv: block_n %d", block_n);
@@ -360,7 +422,11 @@ int build_umma_conv(UmmaConvLaunch* L, const void* in, int B, int Hin, int Win, 
   p.pad = pad;
   p.S = R;
   p.cblocks = Cin / 64;
-  p.num_kblocks = R * R * p.cblocks;
+  p.num_kblocks = R * R * p.cblocks * (split ? 3 : 1);
+  p.cin = Cin;
+  p.ktot = R * R * Cin;
+  L->split = split ? 1 : 0;
+  if (split) cluster = 1;  // the split-bf16 mode runs on the single-CTA kernel
   p.num_n_tiles = Cout / block_n;
   const int m_tiles = static_cast<int>((M + kTileM - 1) / kTileM);
   p.num_tiles = m_tiles * p.num_n_tiles;
@@ -401,24 +467,25 @@ int build_umma_conv(UmmaConvLaunch* L, const void* in, int B, int Hin, int Win, 
   const uint32_t box[4] = {64u, static_cast<uint32_t>(Wo), static_cast<uint32_t>(bh),
                            static_cast<uint32_t>(imgs)};
   const uint64_t e = 2;  // bytes per element
+  const uint64_t Cs = static_cast<uint64_t>(Cin) * (split ? 2 : 1);  // stored channels per pixel: [hi | lo] when split
   if (stride == 1) {
-    const uint64_t dims[4] = {(uint64_t)Cin, (uint64_t)Win, (uint64_t)Hin, (uint64_t)B};
-    const uint64_t str[3] = {Cin * e, (uint64_t)Win * Cin * e, (uint64_t)Hin * Win * Cin * e};
+    const uint64_t dims[4] = {Cs, (uint64_t)Win, (uint64_t)Hin, (uint64_t)B};
+    const uint64_t str[3] = {Cs * e, (uint64_t)Win * Cs * e, (uint64_t)Hin * Win * Cs * e};
     if (int rc = encode_tma_bf16(&L->maps.a[0], in, 4, dims, str, box, 128)) return rc;
     for (int i = 1; i < 4; ++i) L->maps.a[i] = L->maps.a[0];
   } else {
     for (int hp = 0; hp < 2; ++hp)
       for (int wp = 0; wp < 2; ++wp) {
-        const uint8_t* base = static_cast<const uint8_t*>(in) + (static_cast<uint64_t>(hp) * Win + wp) * Cin * e;
-        const uint64_t dims[4] = {(uint64_t)Cin, (uint64_t)Win / 2, (uint64_t)Hin / 2, (uint64_t)B};
-        const uint64_t str[3] = {2 * Cin * e, 2 * (uint64_t)Win * Cin * e, (uint64_t)Hin * Win * Cin * e};
+        const uint8_t* base = static_cast<const uint8_t*>(in) + (static_cast<uint64_t>(hp) * Win + wp) * Cs * e;
+        const uint64_t dims[4] = {Cs, (uint64_t)Win / 2, (uint64_t)Hin / 2, (uint64_t)B};
+        const uint64_t str[3] = {2 * Cs * e, 2 * (uint64_t)Win * Cs * e, (uint64_t)Hin * Win * Cs * e};
         if (int rc = encode_tma_bf16(&L->maps.a[hp * 2 + wp], base, 4, dims, str, box, 128)) return rc;
       }
   }
-  return encode_weight_map(&L->maps.b, wpacked, Cout, R * R * Cin, block_n / p.cl, 128);
+  return encode_weight_map(&L->maps.b, wpacked, Cout, R * R * Cin * (split ? 2 : 1), block_n / p.cl, 128);
 }
 
-template <int BLOCK_N>
+template <int BLOCK_N, bool SPLIT>
 static int launch_one(const UmmaConvLaunch& L, cudaStream_t st) {
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(L.grid);
@@ -432,16 +499,21 @@ static int launch_one(const UmmaConvLaunch& L, cudaStream_t st) {
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  PB_CUDA(cudaLaunchKernelEx(&cfg, conv_umma_kernel<BLOCK_N, 128>, L.maps, L.p));
+  PB_CUDA(cudaLaunchKernelEx(&cfg, conv_umma_kernel<BLOCK_N, 128, SPLIT>, L.maps, L.p));
   return PB200_OK;
 }
 
 int launch_umma_conv(const UmmaConvLaunch& L, cudaStream_t st) {
   if (L.p.num_tiles == 0) return PB200_OK;
   if (L.pair) return launch_umma_pair(L, st);
-  if (L.block_n == 64) return launch_one<64>(L, st);
-  if (L.block_n == 128) return launch_one<128>(L, st);
-  return launch_one<256>(L, st);
+  if (L.split) {
+    if (L.block_n == 64) return launch_one<64, true>(L, st);
+    if (L.block_n == 128) return launch_one<128, true>(L, st);
+    return launch_one<256, true>(L, st);
+  }
+  if (L.block_n == 64) return launch_one<64, false>(L, st);
+  if (L.block_n == 128) return launch_one<128, false>(L, st);
+  return launch_one<256, false>(L, st);
 }
 
 }  // namespace pb200

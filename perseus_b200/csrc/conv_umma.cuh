@@ -18,6 +18,8 @@ struct UmmaConvParams {
   int M_total;  // B*Ho*Wo output pixels
   int Cout;
   int stem;     // unused (kept 0)
+  int cin;      // split-bf16 mode: channel offset of the lo halves in the activation tensor (= Cin)
+  int ktot;     // split-bf16 mode: column offset of the lo halves in the packed weights (= R*R*Cin)
   int Ho, Wo;
   int tiles_per_img;  // Ho*Wo/128 when >= 1, else 0
   int imgs_per_tile;  // 128/(Ho*Wo) when the image is smaller than a tile, else 1
@@ -35,6 +37,7 @@ struct UmmaConvLaunch {
   int block_n;  // 64 / 128 / 256
   int sw;       // swizzle bytes = bytes of K per smem row: 128 (generic) or 64 (stem)
   int grid;
+  int split;    // 1: split-bf16 ("bf16x3") operands, conv_umma_kernel<.., true>
   int pair;     // 1: CTA-pair kernel (conv_umma2.cu, tcgen05 cta_group::2), p.cl == 2
   double flops;  // algorithmic 2*MAC (unpadded)
 };
@@ -43,7 +46,8 @@ struct UmmaConvLaunch {
 // with K order (r, s, c).
 int build_umma_conv(UmmaConvLaunch* L, const void* in, int B, int Hin, int Win, int Cin,
                     const void* wpacked, const float* bias, const void* residual, void* out, int Cout,
-                    int R, int stride, int pad, int relu, int block_n, int cluster = 0 /* 0 = choose; 1/2/4 = multicast cluster; -2 = CTA pair */);
+                    int R, int stride, int pad, int relu, int block_n, int cluster = 0 /* 0 = choose; 1/2/4 = multicast cluster; -2 = CTA pair */,
+                    int split = 0 /* 1: activations [hi|lo] (2*Cin channels), weights [Cout][hi K | lo K], out/residual [hi|lo] */);
 int launch_umma_conv(const UmmaConvLaunch& L, cudaStream_t st);  // dispatches on L.pair
 // conv_umma2.cu
 int umma_pair_init();

@@ -74,8 +74,11 @@ int launch_stem_pool(const void* frames, const void* wimg, const float* bias, vo
 // 3x3 stride-2 pad-1 max pooling, NHWC (C % 8 == 0 for bf16, % 4 for fp32).
 int launch_maxpool(const void* in, void* out, int B, int H, int W, int C, bool bf16, cudaStream_t st);
 // global average pool + Linear(C -> n_out) + pixel decode; in is NHWC [B][HW][C].
+// mode: 0 = fp32 input, 1 = bf16, 2 = split bf16 rows [hi(C) | lo(C)]
 int launch_head(const void* in, const float* fc_w, const float* fc_b, float* out_norm, float* out_px,
-                int B, int HW, int C, int n_out, int imgH, int imgW, bool bf16, cudaStream_t st);
+                int B, int HW, int C, int n_out, int imgH, int imgW, int mode, cudaStream_t st);
+// split-bf16 mode: fp32 NHWC in -> [hi(C) | lo(C)] bf16 NHWC out
+int launch_maxpool_split(const void* in, void* out, int B, int H, int W, int C, cudaStream_t st);
 int launch_decode(const float* xy_norm, float* xy_px, long long n_points, int H, int W,
                   cudaStream_t st);
 

@@ -46,7 +46,8 @@ enum { BUF_FRAMES = 0, BUF_STEM = 1, BUF_R0 = 2, BUF_R1 = 3, BUF_R2 = 4, BUF_R3 
 
 struct pb200_plan {
   int device = 0, max_batch = 0, C = 3, H = 256, W = 256, n_kp = 8, precision = PB200_PREC_BF16;
-  bool bf16 = true;
+  bool bf16 = true;    // single-pass bf16 tcgen05 mode (fused stem, P8 layer1)
+  bool split = false;  // split-bf16 "bf16x3" mode: fp32 SIMT stem + maxpool, every later conv on tcgen05 with [hi|lo] operands
   size_t elt = 2;
   std::vector<pb200::ConvSpec> convs;
   std::vector<pb200::Op> ops;
@@ -228,8 +229,8 @@ extern "C" int pb200_plan_create(pb200_plan** out, int device, int max_batch, in
   PB_CHECK(in_channels >= 1 && in_channels <= 4,
            "plan_create: in_channels %d (the frames layout carries up to 4: R,G,B,D)", in_channels);
   PB_CHECK(n_keypoints >= 1, "plan_create: n_keypoints %d", n_keypoints);
-  PB_CHECK(precision == PB200_PREC_FP32 || precision == PB200_PREC_BF16,
-           "plan_create: precision %d not available (0 = fp32 SIMT, 1 = bf16 tcgen05)", precision);
+  PB_CHECK(precision == PB200_PREC_FP32 || precision == PB200_PREC_BF16 || precision == PB200_PREC_BF16X3,
+           "plan_create: precision %d not available (0 = fp32 SIMT, 1 = bf16 tcgen05, 2 = split-bf16 tcgen05)", precision);
   PB_CHECK(H % 32 == 0 && W % 32 == 0 && H >= 32 && W >= 32, "plan_create: H, W must be multiples of 32");
   if (precision != PB200_PREC_FP32)
     PB_CHECK(H == 256 && W == 256, "plan_create: the tcgen05 path is tiled for 256x256 frames (got %dx%d); "
@@ -244,7 +245,9 @@ extern "C" int pb200_plan_create(pb200_plan** out, int device, int max_batch, in
   pl->W = W;
   pl->n_kp = n_keypoints;
   pl->precision = precision;
-  pl->bf16 = precision != PB200_PREC_FP32;
+  pl->bf16 = precision == PB200_PREC_BF16;
+  pl->split = precision == PB200_PREC_BF16X3;
+  // split mode: fp32 frames / stem output, later activations are [hi | lo] bf16 pairs = 4 bytes per value as well
   pl->elt = pl->bf16 ? 2 : 4;
   build_graph(pl);
   cudaError_t e = cudaMalloc(reinterpret_cast<void**>(&pl->arena), pl->arena_bytes);
@@ -252,10 +255,10 @@ extern "C" int pb200_plan_create(pb200_plan** out, int device, int max_batch, in
     delete pl;
     return cuda_fail(e, "cudaMalloc(weight arena)", __FILE__, __LINE__);
   }
-  if (pl->bf16) {
+  if (pl->bf16 || pl->split) {
     int rc = umma_conv_init();
-    if (rc == PB200_OK) rc = stem_pool_init();
-    if (rc == PB200_OK) rc = conv_p8_init();
+    if (rc == PB200_OK && pl->bf16) rc = stem_pool_init();
+    if (rc == PB200_OK && pl->bf16) rc = conv_p8_init();
     if (rc) {
       cudaFree(pl->arena);
       delete pl;
@@ -345,7 +348,17 @@ extern "C" int pb200_plan_load_weights(pb200_plan* plan, const float* const* ten
             } else {
               k = (r * c.R + s) * c.Cin + ci;
             }
-            if (plan->bf16) {
+            if (plan->split && !c.stem) {
+              // [Cout][hi K | lo K] bf16 rows: w = hi + lo, hi = bf16(w), lo = bf16(w - hi)
+              const float wf = static_cast<float>(v);
+              const uint16_t hi = f32_to_bf16_rne(wf);
+              uint32_t hbits = static_cast<uint32_t>(hi) << 16;
+              float hf;
+              memcpy(&hf, &hbits, 4);
+              uint16_t* row = reinterpret_cast<uint16_t*>(host.data() + c.w_off) + static_cast<size_t>(co) * 2 * K;
+              row[k] = hi;
+              row[K + k] = f32_to_bf16_rne(wf - hf);
+            } else if (plan->bf16) {
               size_t off = (static_cast<size_t>(co) * K + k) * 2;  // [Cout][K] K-major rows (TMA-im2col kernels)
               if (c.stem) off = stem_wimg_offset(co, k);
               else if (c.p8) off = conv_p8_wimg_offset(co, k);
@@ -403,20 +416,20 @@ static int choose_block_n(const ConvSpec& c, int B) {
 
 // (re)build the TMA descriptors / launch parameters when a pointer or the batch size changed
 static int prepare(pb200_plan* pl, const void* frames, void* ws, int B) {
-  if (!pl->bf16) return PB200_OK;
+  if (!pl->bf16 && !pl->split) return PB200_OK;
   if (pl->cache_frames == frames && pl->cache_ws == ws && pl->cache_B == B) return PB200_OK;
   pl->umma.assign(pl->convs.size(), UmmaConvLaunch());
   for (const auto& op : pl->ops) {
     if (op.kind != OP_CONV) continue;
     const ConvSpec& c = pl->convs[op.conv];
-    if (c.stem) continue;  // bf16 stem = OP_STEM_POOL (no tensor maps)
+    if (c.stem) continue;  // bf16 stem = OP_STEM_POOL (no tensor maps); split stem = fp32 SIMT
     UmmaConvLaunch* L = &pl->umma[op.conv];
     const void* in = buf_ptr(pl, frames, ws, op.in_buf);
     void* out = buf_ptr(pl, frames, ws, op.out_buf);
     const void* res = op.res_buf >= 0 ? buf_ptr(pl, frames, ws, op.res_buf) : nullptr;
     const float* bias = reinterpret_cast<const float*>(pl->arena + c.b_off);
     int rc = build_umma_conv(L, in, B, c.Hin, c.Win, c.Cin, pl->arena + c.w_off, bias, res, out, c.Cout,
-                             c.R, c.stride, c.pad, op.relu, choose_block_n(c, B));
+                             c.R, c.stride, c.pad, op.relu, choose_block_n(c, B), 0, pl->split ? 1 : 0);
     if (rc) {
       pl->cache_B = -1;
       return rc;
@@ -433,7 +446,7 @@ static int run_op(pb200_plan* pl, const Op& op, const void* frames, void* ws, fl
   switch (op.kind) {
     case OP_CONV: {
       const ConvSpec& c = pl->convs[op.conv];
-      if (pl->bf16) return launch_umma_conv(pl->umma[op.conv], st);
+      if (pl->bf16 || (pl->split && !c.stem)) return launch_umma_conv(pl->umma[op.conv], st);
       SimtConv s;
       s.in = reinterpret_cast<const float*>(buf_ptr(pl, frames, ws, op.in_buf));
       s.w = reinterpret_cast<const float*>(pl->arena + c.w_off);
@@ -462,6 +475,9 @@ static int run_op(pb200_plan* pl, const Op& op, const void* frames, void* ws, fl
     }
     case OP_MAXPOOL: {
       const ConvSpec& c = pl->convs[0];
+      if (pl->split)
+        return launch_maxpool_split(buf_ptr(pl, frames, ws, op.in_buf), buf_ptr(pl, frames, ws, op.out_buf), B,
+                                    c.Ho, c.Wo, c.Cout, st);
       return launch_maxpool(buf_ptr(pl, frames, ws, op.in_buf), buf_ptr(pl, frames, ws, op.out_buf), B,
                             c.Ho, c.Wo, c.Cout, pl->bf16, st);
     }
@@ -470,7 +486,7 @@ static int run_op(pb200_plan* pl, const Op& op, const void* frames, void* ws, fl
       return launch_head(buf_ptr(pl, frames, ws, op.in_buf),
                          reinterpret_cast<const float*>(pl->arena + pl->fc_w_off),
                          reinterpret_cast<const float*>(pl->arena + pl->fc_b_off), out_norm, out_px, B,
-                         c.Ho * c.Wo, c.Cout, 2 * pl->n_kp, pl->H, pl->W, pl->bf16, st);
+                         c.Ho * c.Wo, c.Cout, 2 * pl->n_kp, pl->H, pl->W, pl->split ? 2 : (pl->bf16 ? 1 : 0), st);
     }
     default:
       return PB200_OK;
@@ -526,14 +542,14 @@ extern "C" const char* pb200_plan_op_kernel(const pb200_plan* plan, int i) {
   switch (op.kind) {
     case OP_STEM_POOL: k = "stem_pool_kernel"; break;
     case OP_CONV_P8: k = "conv_p8_kernel"; break;
-    case OP_MAXPOOL: k = plan->bf16 ? "maxpool_bf16_kernel" : "maxpool_f32_kernel"; break;
+    case OP_MAXPOOL: k = plan->split ? "maxpool_split_kernel" : (plan->bf16 ? "maxpool_bf16_kernel" : "maxpool_f32_kernel"); break;
     case OP_HEAD: k = "head_kernel"; break;
     case OP_CONV:
-      if (!plan->bf16) k = "conv_simt_kernel";
+      if (!plan->bf16 && !(plan->split && !plan->convs[op.conv].stem)) k = "conv_simt_kernel";
       else if (plan->cache_B < 0 || plan->umma.size() != plan->convs.size()) k = "conv_umma*";
       else {
         const UmmaConvLaunch& L = plan->umma[op.conv];
-        k = std::string(L.pair ? "conv_umma2_kernel<" : "conv_umma_kernel<") + std::to_string(L.block_n) + ">";
+        k = std::string(L.pair ? "conv_umma2_kernel<" : "conv_umma_kernel<") + std::to_string(L.block_n) + (L.split ? ",split>" : ">");
       }
       break;
     default: k = ""; break;
@@ -674,6 +690,50 @@ extern "C" int pb200_debug_conv_bf16(const void* in_nhwc, int B, int H, int W, i
   if (rc == PB200_OK) rc = launch_umma_conv(L, st);
   cudaError_t e = cudaStreamSynchronize(st);
   if (rc == PB200_OK && e != cudaSuccess) rc = cuda_fail(e, "debug_conv sync", __FILE__, __LINE__);
+  cudaFree(dw);
+  cudaFree(db);
+  return rc;
+}
+
+extern "C" int pb200_debug_conv_split(const void* in_nhwc2, int B, int H, int W, int Cin,
+                                      const float* w_oihw_host, const float* bias_host, int Cout, int R,
+                                      int stride, int pad, const void* residual_nhwc2_or_null, int relu,
+                                      void* out_nhwc2, pb200_stream stream) {
+  if (int rc = require_device()) return rc;
+  if (int rc = umma_conv_init()) return rc;
+  PB_CHECK(in_nhwc2 && w_oihw_host && bias_host && out_nhwc2, "debug_conv_split: null argument");
+  const size_t K = static_cast<size_t>(R) * R * Cin;
+  std::vector<uint16_t> wp(2 * K * Cout);
+  for (int co = 0; co < Cout; ++co)
+    for (int ci = 0; ci < Cin; ++ci)
+      for (int r = 0; r < R; ++r)
+        for (int s = 0; s < R; ++s) {
+          const float wf = w_oihw_host[((static_cast<size_t>(co) * Cin + ci) * R + r) * R + s];
+          const uint16_t hi = f32_to_bf16_rne(wf);
+          const uint32_t hbits = static_cast<uint32_t>(hi) << 16;
+          float hf;
+          memcpy(&hf, &hbits, 4);
+          const size_t k = (static_cast<size_t>(r) * R + s) * Cin + ci;
+          wp[co * 2 * K + k] = hi;
+          wp[co * 2 * K + K + k] = f32_to_bf16_rne(wf - hf);
+        }
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  void *dw = nullptr, *db = nullptr;
+  PB_CUDA(cudaMalloc(&dw, wp.size() * 2));
+  PB_CUDA(cudaMalloc(&db, sizeof(float) * Cout));
+  int rc = PB200_OK;
+  if (cudaMemcpyAsync(dw, wp.data(), wp.size() * 2, cudaMemcpyHostToDevice, st) != cudaSuccess ||
+      cudaMemcpyAsync(db, bias_host, sizeof(float) * Cout, cudaMemcpyHostToDevice, st) != cudaSuccess)
+    rc = PB200_ERR_CUDA;
+  UmmaConvLaunch L;
+  if (rc == PB200_OK) {
+    int bn = Cout < 256 ? Cout : 256;
+    rc = build_umma_conv(&L, in_nhwc2, B, H, W, Cin, dw, static_cast<const float*>(db),
+                         residual_nhwc2_or_null, out_nhwc2, Cout, R, stride, pad, relu, bn, 0, 1);
+  }
+  if (rc == PB200_OK) rc = launch_umma_conv(L, st);
+  cudaError_t e = cudaStreamSynchronize(st);
+  if (rc == PB200_OK && e != cudaSuccess) rc = cuda_fail(e, "debug_conv_split sync", __FILE__, __LINE__);
   cudaFree(dw);
   cudaFree(db);
   return rc;

@@ -83,6 +83,50 @@ maxpool_f32_kernel(const float4* __restrict__ in, float4* __restrict__ out, int 
   out[gid] = m;
 }
 
+// split-bf16 ("bf16x3") mode: fp32 NHWC in, [hi(C) | lo(C)] bf16 NHWC out (hi = bf16(m), lo = bf16(m - hi))
+__global__ void __launch_bounds__(256)
+maxpool_split_kernel(const float4* __restrict__ in, uint2* __restrict__ out, int B, int H, int W,
+                     int C4, int Ho, int Wo) {
+  const long long total = static_cast<long long>(B) * Ho * Wo * C4;
+  const long long gid = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (gid >= total) return;
+  const int c = static_cast<int>(gid % C4);
+  long long p = gid / C4;
+  const long long pix = p;
+  const int wo = static_cast<int>(p % Wo);
+  p /= Wo;
+  const int ho = static_cast<int>(p % Ho);
+  const int b = static_cast<int>(p / Ho);
+  float4 m = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+#pragma unroll
+  for (int r = 0; r < 3; ++r) {
+    const int hi = 2 * ho + r - 1;
+    if (hi < 0 || hi >= H) continue;
+#pragma unroll
+    for (int s = 0; s < 3; ++s) {
+      const int wi = 2 * wo + s - 1;
+      if (wi < 0 || wi >= W) continue;
+      const float4 v = __ldg(in + ((static_cast<long long>(b) * H + hi) * W + wi) * C4 + c);
+      m.x = fmaxf(m.x, v.x); m.y = fmaxf(m.y, v.y); m.z = fmaxf(m.z, v.z); m.w = fmaxf(m.w, v.w);
+    }
+  }
+  const uint32_t h0 = pack_bf16x2(m.x, m.y), h1 = pack_bf16x2(m.z, m.w);
+  const uint32_t l0 = pack_bf16x2(m.x - bf16_lo(h0), m.y - bf16_hi(h0));
+  const uint32_t l1 = pack_bf16x2(m.z - bf16_lo(h1), m.w - bf16_hi(h1));
+  out[pix * (2 * C4) + c] = make_uint2(h0, h1);
+  out[pix * (2 * C4) + C4 + c] = make_uint2(l0, l1);
+}
+
+int launch_maxpool_split(const void* in, void* out, int B, int H, int W, int C, cudaStream_t st) {
+  const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1;
+  PB_CHECK(C % 4 == 0, "maxpool: C %% 4 != 0");
+  const long long total = static_cast<long long>(B) * Ho * Wo * (C / 4);
+  maxpool_split_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, st>>>(
+      static_cast<const float4*>(in), static_cast<uint2*>(out), B, H, W, C / 4, Ho, Wo);
+  PB_CUDA(cudaGetLastError());
+  return PB200_OK;
+}
+
 int launch_maxpool(const void* in, void* out, int B, int H, int W, int C, bool bf16, cudaStream_t st) {
   const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1;
   if (bf16) {
@@ -105,7 +149,7 @@ int launch_maxpool(const void* in, void* out, int B, int H, int W, int C, bool b
 // them over the HW pixels with coalesced 4-byte (bf16x2) / 8-byte (float2) loads; the means go to
 // shared memory.  Phase 2: each warp produces outputs o = warp, warp+8, ...: lanes stride over
 // the channels, then a 5-step shuffle tree.  Everything after the loads is fp32.
-template <bool BF16>
+template <int MODE>  // 0: fp32 input, 1: bf16, 2: split bf16 rows [hi(C) | lo(C)]
 __global__ void __launch_bounds__(256)
 head_kernel(const void* __restrict__ in, const float* __restrict__ fc_w,
             const float* __restrict__ fc_b, float* __restrict__ out_norm, float* __restrict__ out_px,
@@ -115,7 +159,16 @@ head_kernel(const void* __restrict__ in, const float* __restrict__ fc_w,
   const float inv = 1.0f / static_cast<float>(HW);
   for (int c2 = threadIdx.x; c2 < C / 2; c2 += blockDim.x) {
     float a0 = 0.f, a1 = 0.f;
-    if (BF16) {
+    if (MODE == 2) {
+      const uint32_t* p = static_cast<const uint32_t*>(in) + static_cast<long long>(b) * HW * C + c2;
+#pragma unroll 8
+      for (int i = 0; i < HW; ++i) {
+        const uint32_t h = __ldg(p + static_cast<long long>(i) * C);
+        const uint32_t l = __ldg(p + static_cast<long long>(i) * C + C / 2);
+        a0 += bf16_lo(h) + bf16_lo(l);
+        a1 += bf16_hi(h) + bf16_hi(l);
+      }
+    } else if (MODE == 1) {
       const uint32_t* p = static_cast<const uint32_t*>(in) + static_cast<long long>(b) * HW * (C / 2) + c2;
 #pragma unroll 8
       for (int i = 0; i < HW; ++i) {
@@ -152,14 +205,16 @@ head_kernel(const void* __restrict__ in, const float* __restrict__ fc_w,
 }
 
 int launch_head(const void* in, const float* fc_w, const float* fc_b, float* out_norm, float* out_px,
-                int B, int HW, int C, int n_out, int imgH, int imgW, bool bf16, cudaStream_t st) {
+                int B, int HW, int C, int n_out, int imgH, int imgW, int mode, cudaStream_t st) {
   PB_CHECK(C % 2 == 0, "head: odd channel count");
   const float hw = denorm_scale(imgW), hh = denorm_scale(imgH);
   const size_t smem = sizeof(float) * C;
-  if (bf16)
-    head_kernel<true><<<B, 256, smem, st>>>(in, fc_w, fc_b, out_norm, out_px, HW, C, n_out, hw, hh);
+  if (mode == 2)
+    head_kernel<2><<<B, 256, smem, st>>>(in, fc_w, fc_b, out_norm, out_px, HW, C, n_out, hw, hh);
+  else if (mode == 1)
+    head_kernel<1><<<B, 256, smem, st>>>(in, fc_w, fc_b, out_norm, out_px, HW, C, n_out, hw, hh);
   else
-    head_kernel<false><<<B, 256, smem, st>>>(in, fc_w, fc_b, out_norm, out_px, HW, C, n_out, hw, hh);
+    head_kernel<0><<<B, 256, smem, st>>>(in, fc_w, fc_b, out_norm, out_px, HW, C, n_out, hw, hh);
   PB_CUDA(cudaGetLastError());
   return PB200_OK;
 }

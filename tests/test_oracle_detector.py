@@ -122,3 +122,15 @@ def test_bf16_emulation_tracks_fp32_reference():
     emu = do.bf16_emulated_forward(sd, x)
     # bf16 noise on random-init weights: ~1e-2 relative, far from an indexing bug
     assert (emu - ref).abs().max() < 0.05 * ref.abs().max()
+
+
+@pytest.mark.parametrize("C", [3, 4])
+def test_bf16x3_emulation_meets_the_bf16_tolerance_on_the_golden_vectors(C):
+    """The split-bf16 operand model (a_hi*w_hi + a_lo*w_hi + a_hi*w_lo) stays within north_star's 0.05 px of the
+    reference's golden outputs — the bound the GPU bf16x3 mode is tested against."""
+    g = np.load(GOLD)
+    sd = do.seeded_state_dict(C, 8, seed=0, randomize_bn=True)
+    x = golden_input(C)
+    y = do.bf16x3_emulated_forward(sd, x)
+    err = float(((y.double() - torch.from_numpy(g[f"c{C}_bn1_out32"]).double()).abs() * 127.5).max())
+    assert err <= 0.05, err
