@@ -189,6 +189,28 @@ int pb200_factors_dynamics(const double* pose1, const double* ang_vel1, const do
 int pb200_factors_constvel(const double* vel1, const double* vel2, double* resid, double* H0,
                            double* H1, int64_t N, pb200_stream stream);
 
+/* ---- training-step operators (train.py:259-304) -----------------------------------------------
+ * Hand-written kernels for the data-parallel training step: tcgen05 forward / data-gradient / weight-gradient
+ * convolutions on NHWC bf16, batch-statistics BatchNorm forward + backward, max-pool backward, the regression
+ * head, SmoothL1 loss, and the fused gradient-norm + clip + AdamW update.  Every entry is asynchronous on
+ * `stream`, allocates nothing, and takes DEVICE pointers.  Replaces loss.backward() through the torchvision
+ * module tree + torch.optim.AdamW (train.py:287-303). */
+
+/* fp32 OIHW parameter -> bf16 GEMM operand.  mode 0: forward [Cout][(r,s,ci)];
+ * mode 1: data-gradient [Cin][(R-1-r,R-1-s,co)] (flipped + transposed filter). */
+int pb200_train_pack_weights(const float* w_oihw, int Cout, int Cin, int R, int mode, void* out_bf16,
+                             pb200_stream stream);
+/* convolution on NHWC bf16 with device-packed weights; out = [relu](conv + bias [+ residual]). */
+int pb200_train_conv(const void* in_nhwc, int B, int H, int W, int Cin, const void* wpacked, const float* bias,
+                     int Cout, int R, int stride, int pad, const void* residual_or_null, int relu,
+                     void* out_nhwc, pb200_stream stream);
+/* weight gradient: scratch[R*R][Cin][Cout] (fp32, zeroed by the caller) += x^T (*) dz over all pixels. */
+int pb200_train_wgrad(const void* x_nhwc, const void* dz_nhwc, int B, int H, int W, int Cin, int Cout, int R,
+                      int stride, int pad, float* scratch, pb200_stream stream);
+/* scratch [R*R][Cin][Cout] -> OIHW fp32 [Cout][cin_real][R][R] (cin_real <= Cin drops padded channels). */
+int pb200_train_unpack_wgrad(const float* scratch, int Cout, int Cin, int R, int cin_real, float* dw_oihw,
+                             pb200_stream stream);
+
 #ifdef __cplusplus
 }
 #endif
