@@ -211,6 +211,46 @@ int pb200_train_wgrad(const void* x_nhwc, const void* dz_nhwc, int B, int H, int
 int pb200_train_unpack_wgrad(const float* scratch, int Cout, int Cin, int R, int cin_real, float* dw_oihw,
                              pb200_stream stream);
 
+/* Batch-statistics BatchNorm on NHWC bf16 [M][C] (nn.BatchNorm2d in train mode; C % 8 == 0, C <= 512).
+ * bn_stats: sums[2*C] (fp64; zeroed here) = per-channel sum and sum of squares of z.
+ * bn_apply: y = [relu](gamma * (z - mean) * invstd + beta [+ residual]); stores mean / invstd for the backward
+ *           and updates running_mean / running_var (momentum, unbiased variance) when they are non-null. */
+int pb200_train_bn_stats(const void* z, int64_t M, int C, double* sums, pb200_stream stream);
+int pb200_train_bn_apply(const void* z, const double* sums, const float* gamma, const float* beta,
+                         float* running_mean, float* running_var, float momentum, float eps, float* save_mean,
+                         float* save_invstd, const void* residual_or_null, int relu, void* y, int64_t M, int C,
+                         pb200_stream stream);
+/* BatchNorm backward fused with the ReLU mask of the layer output: g = dy * [y_mask > 0] (y_mask null: g = dy);
+ * dz = gamma * invstd * (g - mean(g) - xhat * mean(g * xhat)); dgamma = sum g * xhat; dbeta = sum g.
+ * Optionally also writes g (the gradient the identity branch receives) and a zero-stuffed copy of dz,
+ * [B][2*Ho][2*Wo][C] with dz at the even positions, which a stride-2 data gradient convolves at stride 1. */
+int pb200_train_bn_backward(const void* dy, const void* y_mask_or_null, const void* z, const float* save_mean,
+                            const float* save_invstd, const float* gamma, double* sums, int64_t M, int C, void* dz,
+                            void* g_out_or_null, void* stuffed_out_or_null, int Ho, int Wo, float* dgamma,
+                            float* dbeta, pb200_stream stream);
+/* conv1 (7x7/2) as a GEMM: im2col of the NCHW fp32 batch into bf16 [B*H/2*W/2][256] (k = (r*7+s)*C + c, zero
+ * tail), the matching weight pack [64][256] and the gradient unpack from the wgrad scratch [256][64]. */
+int pb200_train_stem_im2col(const float* x_nchw, int B, int C, int H, int W, void* A_bf16, pb200_stream stream);
+int pb200_train_stem_pack(const float* w_oihw, int C, void* out_bf16, pb200_stream stream);
+int pb200_train_stem_unpack(const float* scratch, int C, float* dw_oihw, pb200_stream stream);
+/* 3x3/2 pad-1 max pool on NHWC bf16 with the argmax (one byte per element) kept for the backward. */
+int pb200_train_maxpool(const void* in, void* out, void* idx, int B, int H, int W, int C, pb200_stream stream);
+int pb200_train_maxpool_backward(const void* dout, const void* idx, void* din, int B, int H, int W, int C,
+                                 pb200_stream stream);
+/* avgpool + fc forward keeping the pooled features; SmoothL1Loss(beta, mean) with d loss / d pred; the head's
+ * backward (fc gradients + the gradient of the last activation, broadcast over its HW pixels). */
+int pb200_train_head_forward(const void* y_nhwc, const float* fc_w, const float* fc_b, float* feat, float* pred,
+                             int B, int HW, int C, int n_out, pb200_stream stream);
+int pb200_train_smooth_l1(const float* pred, const float* target, int n, float beta, float* loss, float* dpred,
+                          pb200_stream stream);
+int pb200_train_head_backward(const float* dpred, const float* feat, const float* fc_w, int B, int HW, int C,
+                              int n_out, float* d_fc_w, float* d_fc_b, void* dy_nhwc, pb200_stream stream);
+/* clip_grad_norm_(max_norm) + AdamW on flat fp32 buffers: grads are first scaled by grad_scale (1/world after a
+ * sum all-reduce), the global norm of the scaled gradient is reduced into sqnorm_scratch, then one fused update. */
+int pb200_train_adamw_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n,
+                           float lr, float beta1, float beta2, float eps, float weight_decay, int step,
+                           float grad_scale, float max_norm, double* sqnorm_scratch, pb200_stream stream);
+
 #ifdef __cplusplus
 }
 #endif

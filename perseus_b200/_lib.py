@@ -76,6 +76,34 @@ SIGNATURES = {
         c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p]
     ),
     "pb200_train_unpack_wgrad": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "pb200_train_bn_stats": (c_int, [c_void_p, c_int64, c_int, c_void_p, c_void_p]),
+    "pb200_train_bn_apply": (
+        c_int,
+        [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_float, c_void_p, c_void_p, c_void_p,
+         c_int, c_void_p, c_int64, c_int, c_void_p],
+    ),
+    "pb200_train_bn_backward": (
+        c_int,
+        [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p, c_void_p,
+         c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p],
+    ),
+    "pb200_train_stem_im2col": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "pb200_train_stem_pack": (c_int, [c_void_p, c_int, c_void_p, c_void_p]),
+    "pb200_train_stem_unpack": (c_int, [c_void_p, c_int, c_void_p, c_void_p]),
+    "pb200_train_maxpool": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
+    "pb200_train_maxpool_backward": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
+    "pb200_train_head_forward": (
+        c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]
+    ),
+    "pb200_train_smooth_l1": (c_int, [c_void_p, c_void_p, c_int, c_float, c_void_p, c_void_p, c_void_p]),
+    "pb200_train_head_backward": (
+        c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]
+    ),
+    "pb200_train_adamw_step": (
+        c_int,
+        [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_float, c_float, c_float, c_float, c_float, c_int, c_float,
+         c_float, c_void_p, c_void_p],
+    ),
     "pb200_factors_projection": (
         c_int,
         [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p],

@@ -124,3 +124,660 @@ extern "C" int pb200_train_unpack_wgrad(const float* scratch, int Cout, int Cin,
   PB_CUDA(cudaGetLastError());
   return PB200_OK;
 }
+
+// =================================================================================================================
+// Batch-statistics BatchNorm on NHWC bf16 [M][C] (train-mode nn.BatchNorm2d, resnet.py:93-99 / 269; eps 1e-5,
+// momentum 0.1).  Memory-bound: a thread owns 8 adjacent channels (one 16-byte load) of a strided set of rows.
+//   forward : bn_stats (sum, sum of squares -> fp64 atomics)  +  bn_apply (scale/shift derived from the sums in
+//             every CTA's prologue; y = [relu](z * scale + shift [+ residual]); CTA 0 stores mean / invstd and updates
+//             the running statistics)
+//   backward: bn_bwd_reduce (sum g, sum g * xhat with g = dy * [y > 0])  +  bn_bwd_apply
+//             (dz = gamma * invstd * (g - mean(g) - xhat * mean(g * xhat)); also g itself for the identity branch, the
+//             zero-stuffed copy a stride-2 data gradient convolves, and dgamma / dbeta)
+// =================================================================================================================
+namespace pb200 {
+
+constexpr int kBnThreads = 256;
+
+__device__ __forceinline__ void unpack8(const uint4& v, float (&f)[8]) {
+  f[0] = bf16_lo(v.x); f[1] = bf16_hi(v.x); f[2] = bf16_lo(v.y); f[3] = bf16_hi(v.y);
+  f[4] = bf16_lo(v.z); f[5] = bf16_hi(v.z); f[6] = bf16_lo(v.w); f[7] = bf16_hi(v.w);
+}
+__device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
+  return make_uint4(pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]), pack_bf16x2(f[4], f[5]), pack_bf16x2(f[6], f[7]));
+}
+
+// rows [row0, row1) of this CTA; thread -> (channel group cg, row lane rl)
+struct RowSplit {
+  long long row0, row1;
+  int cg, rl, lanes;
+};
+__device__ __forceinline__ RowSplit row_split(long long M, int C8) {
+  RowSplit s;
+  const long long per = (M + gridDim.x - 1) / gridDim.x;
+  s.row0 = per * blockIdx.x;
+  s.row1 = s.row0 + per < M ? s.row0 + per : M;
+  s.cg = threadIdx.x % C8;
+  s.rl = threadIdx.x / C8;
+  s.lanes = kBnThreads / C8;
+  return s;
+}
+
+__global__ void __launch_bounds__(kBnThreads)
+bn_stats_kernel(const uint4* __restrict__ z, long long M, int C, double* __restrict__ sums /* [2][C] */) {
+  __shared__ float s_acc[2 * 512];
+  const int C8 = C / 8;
+  for (int i = threadIdx.x; i < 2 * C; i += kBnThreads) s_acc[i] = 0.f;
+  __syncthreads();
+  const RowSplit rs = row_split(M, C8);
+  float a[8] = {0, 0, 0, 0, 0, 0, 0, 0}, q[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  for (long long r = rs.row0 + rs.rl; r < rs.row1; r += rs.lanes) {
+    float f[8];
+    unpack8(__ldg(z + r * C8 + rs.cg), f);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      a[e] += f[e];
+      q[e] = fmaf(f[e], f[e], q[e]);
+    }
+  }
+#pragma unroll
+  for (int e = 0; e < 8; ++e) {
+    atomicAdd(&s_acc[rs.cg * 8 + e], a[e]);
+    atomicAdd(&s_acc[C + rs.cg * 8 + e], q[e]);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < 2 * C; i += kBnThreads) atomicAdd(&sums[i], static_cast<double>(s_acc[i]));
+}
+
+__global__ void __launch_bounds__(kBnThreads)
+bn_apply_kernel(const uint4* __restrict__ z, const double* __restrict__ sums, const float* __restrict__ gamma,
+                const float* __restrict__ beta, float* __restrict__ running_mean, float* __restrict__ running_var,
+                float momentum, float eps, float* __restrict__ save_mean, float* __restrict__ save_invstd,
+                const uint4* __restrict__ residual, int relu, uint4* __restrict__ y, long long M, int C) {
+  __shared__ float s_scale[512], s_shift[512];
+  for (int c = threadIdx.x; c < C; c += kBnThreads) {
+    const double mean = sums[c] / static_cast<double>(M);
+    double var = sums[C + c] / static_cast<double>(M) - mean * mean;
+    if (var < 0.0) var = 0.0;
+    const float invstd = static_cast<float>(1.0 / sqrt(var + static_cast<double>(eps)));
+    const float sc = gamma[c] * invstd;
+    s_scale[c] = sc;
+    s_shift[c] = beta[c] - static_cast<float>(mean) * sc;
+    if (blockIdx.x == 0) {
+      save_mean[c] = static_cast<float>(mean);
+      save_invstd[c] = invstd;
+      if (running_mean != nullptr) {  // nn.BatchNorm2d: unbiased variance in the running estimate
+        const double unb = M > 1 ? var * static_cast<double>(M) / static_cast<double>(M - 1) : var;
+        running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * static_cast<float>(mean);
+        running_var[c] = (1.f - momentum) * running_var[c] + momentum * static_cast<float>(unb);
+      }
+    }
+  }
+  __syncthreads();
+  const int C8 = C / 8;
+  const long long total = M * C8;
+  for (long long i = static_cast<long long>(blockIdx.x) * kBnThreads + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * kBnThreads) {
+    const int c0 = static_cast<int>(i % C8) * 8;
+    float f[8];
+    unpack8(__ldg(z + i), f);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) f[e] = fmaf(f[e], s_scale[c0 + e], s_shift[c0 + e]);
+    if (residual != nullptr) {
+      float r[8];
+      unpack8(__ldg(residual + i), r);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) f[e] += r[e];
+    }
+    if (relu) {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) f[e] = fmaxf(f[e], 0.f);
+    }
+    y[i] = pack8(f);
+  }
+}
+
+__global__ void __launch_bounds__(kBnThreads)
+bn_bwd_reduce_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ y_mask, const uint4* __restrict__ z,
+                     const float* __restrict__ mean, const float* __restrict__ invstd, long long M, int C,
+                     double* __restrict__ sums /* [2][C]: sum g, sum g*xhat */) {
+  __shared__ float s_acc[2 * 512];
+  const int C8 = C / 8;
+  for (int i = threadIdx.x; i < 2 * C; i += kBnThreads) s_acc[i] = 0.f;
+  __syncthreads();
+  const RowSplit rs = row_split(M, C8);
+  float mu[8], is[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) {
+    mu[e] = mean[rs.cg * 8 + e];
+    is[e] = invstd[rs.cg * 8 + e];
+  }
+  float a[8] = {0, 0, 0, 0, 0, 0, 0, 0}, q[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  for (long long r = rs.row0 + rs.rl; r < rs.row1; r += rs.lanes) {
+    const long long i = r * C8 + rs.cg;
+    float g[8], zz[8];
+    unpack8(__ldg(dy + i), g);
+    unpack8(__ldg(z + i), zz);
+    if (y_mask != nullptr) {
+      float m[8];
+      unpack8(__ldg(y_mask + i), m);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) g[e] = m[e] > 0.f ? g[e] : 0.f;
+    }
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      a[e] += g[e];
+      q[e] = fmaf(g[e], (zz[e] - mu[e]) * is[e], q[e]);
+    }
+  }
+#pragma unroll
+  for (int e = 0; e < 8; ++e) {
+    atomicAdd(&s_acc[rs.cg * 8 + e], a[e]);
+    atomicAdd(&s_acc[C + rs.cg * 8 + e], q[e]);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < 2 * C; i += kBnThreads) atomicAdd(&sums[i], static_cast<double>(s_acc[i]));
+}
+
+// stuffed_out: [B][2*Ho][2*Wo][C] with dz at the even positions (the caller zeroes it); Wo / HoWo describe dz's rows
+__global__ void __launch_bounds__(kBnThreads)
+bn_bwd_apply_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ y_mask, const uint4* __restrict__ z,
+                    const float* __restrict__ mean, const float* __restrict__ invstd, const float* __restrict__ gamma,
+                    const double* __restrict__ sums, long long M, int C, uint4* __restrict__ dz,
+                    uint4* __restrict__ g_out, uint4* __restrict__ stuffed_out, int Ho, int Wo,
+                    float* __restrict__ dgamma, float* __restrict__ dbeta) {
+  __shared__ float s_k[512], s_mg[512], s_mgx[512], s_mu[512], s_is[512];
+  const float invM = 1.0f / static_cast<float>(M);
+  for (int c = threadIdx.x; c < C; c += kBnThreads) {
+    const float sg = static_cast<float>(sums[c]), sgx = static_cast<float>(sums[C + c]);
+    s_k[c] = gamma[c] * invstd[c];
+    s_mg[c] = sg * invM;
+    s_mgx[c] = sgx * invM;
+    s_mu[c] = mean[c];
+    s_is[c] = invstd[c];
+    if (blockIdx.x == 0) {
+      dgamma[c] = sgx;
+      dbeta[c] = sg;
+    }
+  }
+  __syncthreads();
+  const int C8 = C / 8;
+  const long long total = M * C8;
+  for (long long i = static_cast<long long>(blockIdx.x) * kBnThreads + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * kBnThreads) {
+    const int c0 = static_cast<int>(i % C8) * 8;
+    float g[8], zz[8], o[8];
+    unpack8(__ldg(dy + i), g);
+    unpack8(__ldg(z + i), zz);
+    if (y_mask != nullptr) {
+      float m[8];
+      unpack8(__ldg(y_mask + i), m);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) g[e] = m[e] > 0.f ? g[e] : 0.f;
+    }
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const int c = c0 + e;
+      const float xhat = (zz[e] - s_mu[c]) * s_is[c];
+      o[e] = s_k[c] * (g[e] - s_mg[c] - xhat * s_mgx[c]);
+    }
+    const uint4 ov = pack8(o);
+    dz[i] = ov;
+    if (g_out != nullptr) g_out[i] = pack8(g);
+    if (stuffed_out != nullptr) {
+      const long long row = i / C8;
+      const int wo = static_cast<int>(row % Wo);
+      const long long t = row / Wo;
+      const int ho = static_cast<int>(t % Ho);
+      const long long b = t / Ho;
+      stuffed_out[((b * (2 * Ho) + 2 * ho) * (2LL * Wo) + 2 * wo) * C8 + (i % C8)] = ov;
+    }
+  }
+}
+
+static inline int bn_grid(long long M, int C) {
+  const long long vec = M * (C / 8);
+  long long g = (vec + kBnThreads * 4 - 1) / (kBnThreads * 4);
+  const long long cap = static_cast<long long>(num_sms()) * 8;
+  if (g > cap) g = cap;
+  if (g < 1) g = 1;
+  return static_cast<int>(g);
+}
+
+}  // namespace pb200
+
+#define PB_BN_CHECK(C) PB_CHECK((C) % 8 == 0 && (C) <= 512 && kBnThreads % ((C) / 8) == 0, "bn: C = %d unsupported", (C))
+
+extern "C" int pb200_train_bn_stats(const void* z, int64_t M, int C, double* sums, pb200_stream stream) {
+  if (int rc = require_device()) return rc;
+  PB_CHECK(z && sums && M >= 1, "train_bn_stats: bad argument");
+  PB_BN_CHECK(C);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  PB_CUDA(cudaMemsetAsync(sums, 0, sizeof(double) * 2 * C, st));
+  bn_stats_kernel<<<bn_grid(M, C), kBnThreads, 0, st>>>(static_cast<const uint4*>(z), M, C, sums);
+  PB_CUDA(cudaGetLastError());
+  return PB200_OK;
+}
+
+extern "C" int pb200_train_bn_apply(const void* z, const double* sums, const float* gamma, const float* beta,
+                                    float* running_mean, float* running_var, float momentum, float eps,
+                                    float* save_mean, float* save_invstd, const void* residual_or_null, int relu,
+                                    void* y, int64_t M, int C, pb200_stream stream) {
+  if (int rc = require_device()) return rc;
+  PB_CHECK(z && sums && gamma && beta && save_mean && save_invstd && y, "train_bn_apply: null argument");
+  PB_BN_CHECK(C);
+  bn_apply_kernel<<<bn_grid(M, C), kBnThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const uint4*>(z), sums, gamma, beta, running_mean, running_var, momentum, eps, save_mean, save_invstd,
+      static_cast<const uint4*>(residual_or_null), relu, static_cast<uint4*>(y), M, C);
+  PB_CUDA(cudaGetLastError());
+  return PB200_OK;
+}
+
+extern "C" int pb200_train_bn_backward(const void* dy, const void* y_mask_or_null, const void* z, const float* save_mean,
+                                       const float* save_invstd, const float* gamma, double* sums, int64_t M, int C,
+                                       void* dz, void* g_out_or_null, void* stuffed_out_or_null, int Ho, int Wo,
+                                       float* dgamma, float* dbeta, pb200_stream stream) {
+  if (int rc = require_device()) return rc;
+  PB_CHECK(dy && z && save_mean && save_invstd && gamma && sums && dz && dgamma && dbeta, "train_bn_backward: null argument");
+  PB_BN_CHECK(C);
+  PB_CHECK(stuffed_out_or_null == nullptr || (Ho > 0 && Wo > 0 && M % (static_cast<int64_t>(Ho) * Wo) == 0),
+           "train_bn_backward: bad zero-stuffing geometry");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  PB_CUDA(cudaMemsetAsync(sums, 0, sizeof(double) * 2 * C, st));
+  if (stuffed_out_or_null != nullptr)
+    PB_CUDA(cudaMemsetAsync(stuffed_out_or_null, 0, static_cast<size_t>(M) * 4 * C * 2, st));
+  const int grid = bn_grid(M, C);
+  bn_bwd_reduce_kernel<<<grid, kBnThreads, 0, st>>>(static_cast<const uint4*>(dy), static_cast<const uint4*>(y_mask_or_null),
+                                                    static_cast<const uint4*>(z), save_mean, save_invstd, M, C, sums);
+  bn_bwd_apply_kernel<<<grid, kBnThreads, 0, st>>>(static_cast<const uint4*>(dy), static_cast<const uint4*>(y_mask_or_null),
+                                                   static_cast<const uint4*>(z), save_mean, save_invstd, gamma, sums, M, C,
+                                                   static_cast<uint4*>(dz), static_cast<uint4*>(g_out_or_null),
+                                                   static_cast<uint4*>(stuffed_out_or_null), Ho, Wo, dgamma, dbeta);
+  PB_CUDA(cudaGetLastError());
+  return PB200_OK;
+}
+
+// =================================================================================================================
+// Stem im2col, max-pool forward (with argmax) / backward
+// =================================================================================================================
+namespace pb200 {
+
+// conv1 (7x7 / 2, pad 3) as a GEMM: A[m][k], m = (b, ho, wo), k = (r*7 + s)*C + c for k < 49*C, zero up to K = 256.
+// x is the reference-style NCHW fp32 batch (train.py:266-268).  One thread = one (m, tap) -> C bf16 values.
+__global__ void __launch_bounds__(256)
+stem_im2col_kernel(const float* __restrict__ x, int B, int C, int H, int W, int Ho, int Wo,
+                   __nv_bfloat16* __restrict__ A) {
+  constexpr int K = 256;
+  const long long total = static_cast<long long>(B) * Ho * Wo * 64;  // 64 slots per row: 49 taps + 15 zero slots
+  const long long gid = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (gid >= total) return;
+  const int slot = static_cast<int>(gid & 63);
+  const long long m = gid >> 6;
+  const int wo = static_cast<int>(m % Wo);
+  const long long t = m / Wo;
+  const int ho = static_cast<int>(t % Ho);
+  const int b = static_cast<int>(t / Ho);
+  __nv_bfloat16* row = A + m * K;
+  if (slot >= 49) {
+    // zero tail: columns [49*C, 256) split over the 15 spare slots
+    const int tail0 = 49 * C, tail = K - tail0;
+    const int per = (tail + 14) / 15;
+    const int k0 = tail0 + (slot - 49) * per;
+    for (int k = k0; k < k0 + per && k < K; ++k) row[k] = __float2bfloat16_rn(0.f);
+    return;
+  }
+  const int r = slot / 7, s = slot - r * 7;
+  const int hi = 2 * ho + r - 3, wi = 2 * wo + s - 3;
+  const bool in = hi >= 0 && hi < H && wi >= 0 && wi < W;
+  for (int c = 0; c < C; ++c) {
+    const float v = in ? __ldg(x + ((static_cast<long long>(b) * C + c) * H + hi) * W + wi) : 0.f;
+    row[slot * C + c] = __float2bfloat16_rn(v);
+  }
+}
+
+// conv1.weight fp32 [64][C][7][7] -> bf16 [64][256] with k = (r*7+s)*C + c (zero tail)
+__global__ void stem_pack_kernel(const float* __restrict__ w, int C, __nv_bfloat16* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= 64 * 256) return;
+  const int co = i >> 8, k = i & 255;
+  float v = 0.f;
+  if (k < 49 * C) {
+    const int tap = k / C, c = k - tap * C;
+    v = w[(co * C + c) * 49 + tap];
+  }
+  out[i] = __float2bfloat16_rn(v);
+}
+
+// scratch [1][256][64] -> conv1.weight.grad [64][C][7][7]
+__global__ void stem_unpack_kernel(const float* __restrict__ scratch, int C, float* __restrict__ dw) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= 64 * C * 49) return;
+  const int tap = i % 49;
+  const int t = i / 49;
+  const int c = t % C, co = t / C;
+  dw[i] = scratch[(tap * C + c) * 64 + co];
+}
+
+// 3x3 / 2 pad 1 max pool, NHWC bf16, 8 channels per thread; idx = position (r*3+s) of the FIRST maximum in scan order
+// (torch's tie rule), one byte per channel
+__global__ void __launch_bounds__(256)
+maxpool_train_kernel(const uint4* __restrict__ in, uint4* __restrict__ out, uint2* __restrict__ idx, int B, int H, int W,
+                     int C8, int Ho, int Wo) {
+  const long long total = static_cast<long long>(B) * Ho * Wo * C8;
+  const long long gid = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (gid >= total) return;
+  const int c = static_cast<int>(gid % C8);
+  long long p = gid / C8;
+  const int wo = static_cast<int>(p % Wo);
+  p /= Wo;
+  const int ho = static_cast<int>(p % Ho);
+  const int b = static_cast<int>(p / Ho);
+  float m[8];
+  uint32_t am[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) {
+    m[e] = -INFINITY;
+    am[e] = 0;
+  }
+#pragma unroll
+  for (int r = 0; r < 3; ++r) {
+    const int hi = 2 * ho + r - 1;
+    if (hi < 0 || hi >= H) continue;
+#pragma unroll
+    for (int s = 0; s < 3; ++s) {
+      const int wi = 2 * wo + s - 1;
+      if (wi < 0 || wi >= W) continue;
+      float f[8];
+      unpack8(__ldg(in + ((static_cast<long long>(b) * H + hi) * W + wi) * C8 + c), f);
+#pragma unroll
+      for (int e = 0; e < 8; ++e)
+        if (f[e] > m[e]) {
+          m[e] = f[e];
+          am[e] = r * 3 + s;
+        }
+    }
+  }
+  out[gid] = pack8(m);
+  idx[gid] = make_uint2(am[0] | (am[1] << 8) | (am[2] << 16) | (am[3] << 24),
+                        am[4] | (am[5] << 8) | (am[6] << 16) | (am[7] << 24));
+}
+
+// gather form: every input pixel sums the gradients of the (<= 4) windows whose argmax it is
+__global__ void __launch_bounds__(256)
+maxpool_bwd_kernel(const uint4* __restrict__ dout, const uint2* __restrict__ idx, uint4* __restrict__ din, int B, int H,
+                   int W, int C8, int Ho, int Wo) {
+  const long long total = static_cast<long long>(B) * H * W * C8;
+  const long long gid = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (gid >= total) return;
+  const int c = static_cast<int>(gid % C8);
+  long long p = gid / C8;
+  const int w = static_cast<int>(p % W);
+  p /= W;
+  const int h = static_cast<int>(p % H);
+  const int b = static_cast<int>(p / H);
+  float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  // windows (ho, wo) with 2*ho - 1 <= h <= 2*ho + 1
+  const int ho_lo = h / 2, ho_hi = (h + 1) / 2;
+  const int wo_lo = w / 2, wo_hi = (w + 1) / 2;
+  for (int ho = ho_lo; ho <= ho_hi; ++ho) {
+    if (ho >= Ho) continue;
+    const int r = h - (2 * ho - 1);
+    for (int wo = wo_lo; wo <= wo_hi; ++wo) {
+      if (wo >= Wo) continue;
+      const int s = w - (2 * wo - 1);
+      const uint32_t me = r * 3 + s;
+      const long long o = ((static_cast<long long>(b) * Ho + ho) * Wo + wo) * C8 + c;
+      const uint2 iv = __ldg(idx + o);
+      float g[8];
+      unpack8(__ldg(dout + o), g);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        const uint32_t word = e < 4 ? iv.x : iv.y;
+        if (((word >> (8 * (e & 3))) & 0xffu) == me) acc[e] += g[e];
+      }
+    }
+  }
+  din[gid] = pack8(acc);
+}
+
+}  // namespace pb200
+
+extern "C" int pb200_train_stem_im2col(const float* x_nchw, int B, int C, int H, int W, void* A_bf16, pb200_stream stream) {
+  if (int rc = require_device()) return rc;
+  PB_CHECK(x_nchw && A_bf16 && C >= 1 && C <= 4 && H % 2 == 0 && W % 2 == 0, "train_stem_im2col: bad argument");
+  const int Ho = H / 2, Wo = W / 2;
+  const long long total = static_cast<long long>(B) * Ho * Wo * 64;
+  stem_im2col_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      x_nchw, B, C, H, W, Ho, Wo, static_cast<__nv_bfloat16*>(A_bf16));
+  PB_CUDA(cudaGetLastError());
+  return PB200_OK;
+}
+
+extern "C" int pb200_train_stem_pack(const float* w_oihw, int C, void* out_bf16, pb200_stream stream) {
+  if (int rc = require_device()) return rc;
+  PB_CHECK(w_oihw && out_bf16 && C >= 1 && C <= 4, "train_stem_pack: bad argument");
+  stem_pack_kernel<<<64, 256, 0, static_cast<cudaStream_t>(stream)>>>(w_oihw, C, static_cast<__nv_bfloat16*>(out_bf16));
+  PB_CUDA(cudaGetLastError());
+  return PB200_OK;
+}
+
+extern "C" int pb200_train_stem_unpack(const float* scratch, int C, float* dw_oihw, pb200_stream stream) {
+  if (int rc = require_device()) return rc;
+  PB_CHECK(scratch && dw_oihw && C >= 1 && C <= 4, "train_stem_unpack: bad argument");
+  const int total = 64 * C * 49;
+  stem_unpack_kernel<<<(total + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(scratch, C, dw_oihw);
+  PB_CUDA(cudaGetLastError());
+  return PB200_OK;
+}
+
+extern "C" int pb200_train_maxpool(const void* in, void* out, void* idx, int B, int H, int W, int C, pb200_stream stream) {
+  if (int rc = require_device()) return rc;
+  PB_CHECK(in && out && idx && C % 8 == 0 && H % 2 == 0 && W % 2 == 0, "train_maxpool: bad argument");
+  const int Ho = H / 2, Wo = W / 2;
+  const long long total = static_cast<long long>(B) * Ho * Wo * (C / 8);
+  maxpool_train_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const uint4*>(in), static_cast<uint4*>(out), static_cast<uint2*>(idx), B, H, W, C / 8, Ho, Wo);
+  PB_CUDA(cudaGetLastError());
+  return PB200_OK;
+}
+
+extern "C" int pb200_train_maxpool_backward(const void* dout, const void* idx, void* din, int B, int H, int W, int C,
+                                            pb200_stream stream) {
+  if (int rc = require_device()) return rc;
+  PB_CHECK(dout && idx && din && C % 8 == 0 && H % 2 == 0 && W % 2 == 0, "train_maxpool_backward: bad argument");
+  const int Ho = H / 2, Wo = W / 2;
+  const long long total = static_cast<long long>(B) * H * W * (C / 8);
+  maxpool_bwd_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const uint4*>(dout), static_cast<const uint2*>(idx), static_cast<uint4*>(din), B, H, W, C / 8, Ho, Wo);
+  PB_CUDA(cudaGetLastError());
+  return PB200_OK;
+}
+
+// =================================================================================================================
+// Regression head (avgpool + fc), SmoothL1 loss, their backward, and the fused optimizer
+// =================================================================================================================
+namespace pb200 {
+
+// forward: feat[b][c] = mean over HW of y[b][hw][c]; pred[b][o] = feat . W[o] + bias[o]   (one CTA per frame)
+__global__ void __launch_bounds__(256)
+head_train_fwd_kernel(const __nv_bfloat16* __restrict__ y, const float* __restrict__ fc_w, const float* __restrict__ fc_b,
+                      float* __restrict__ feat, float* __restrict__ pred, int HW, int C, int n_out) {
+  extern __shared__ float s_mean[];
+  const int b = blockIdx.x;
+  const float inv = 1.0f / static_cast<float>(HW);
+  for (int c2 = threadIdx.x; c2 < C / 2; c2 += blockDim.x) {
+    const uint32_t* p = reinterpret_cast<const uint32_t*>(y) + static_cast<long long>(b) * HW * (C / 2) + c2;
+    float a0 = 0.f, a1 = 0.f;
+    for (int i = 0; i < HW; ++i) {
+      const uint32_t v = __ldg(p + static_cast<long long>(i) * (C / 2));
+      a0 += bf16_lo(v);
+      a1 += bf16_hi(v);
+    }
+    s_mean[2 * c2] = a0 * inv;
+    s_mean[2 * c2 + 1] = a1 * inv;
+    feat[static_cast<long long>(b) * C + 2 * c2] = a0 * inv;
+    feat[static_cast<long long>(b) * C + 2 * c2 + 1] = a1 * inv;
+  }
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int o = warp; o < n_out; o += (blockDim.x >> 5)) {
+    float acc = 0.f;
+    for (int c = lane; c < C; c += 32) acc = fmaf(s_mean[c], __ldg(fc_w + o * C + c), acc);
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
+    if (lane == 0) pred[static_cast<long long>(b) * n_out + o] = acc + __ldg(fc_b + o);
+  }
+}
+
+// SmoothL1Loss(beta, reduction = mean) (train.py:119,290) and d loss / d pred, one CTA
+__global__ void __launch_bounds__(256)
+smooth_l1_kernel(const float* __restrict__ pred, const float* __restrict__ target, int n, float beta,
+                 float* __restrict__ loss, float* __restrict__ dpred) {
+  __shared__ float s_part[256];
+  float acc = 0.f;
+  const float invn = 1.0f / static_cast<float>(n);
+  for (int i = threadIdx.x; i < n; i += 256) {
+    const float d = pred[i] - target[i];
+    const float ad = fabsf(d);
+    if (ad < beta) {
+      acc += 0.5f * d * d / beta;
+      dpred[i] = d / beta * invn;
+    } else {
+      acc += ad - 0.5f * beta;
+      dpred[i] = (d > 0.f ? 1.f : -1.f) * invn;
+    }
+  }
+  s_part[threadIdx.x] = acc;
+  __syncthreads();
+  for (int s = 128; s > 0; s >>= 1) {
+    if (threadIdx.x < s) s_part[threadIdx.x] += s_part[threadIdx.x + s];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *loss = s_part[0] * invn;
+}
+
+// d fc.weight[o][c] = sum_b dpred[b][o] feat[b][c]; d fc.bias[o] = sum_b dpred[b][o]   (grid = n_out CTAs)
+__global__ void __launch_bounds__(256)
+head_bwd_params_kernel(const float* __restrict__ dpred, const float* __restrict__ feat, int B, int C, int n_out,
+                       float* __restrict__ dW, float* __restrict__ db) {
+  const int o = blockIdx.x;
+  for (int c = threadIdx.x; c < C; c += 256) {
+    float acc = 0.f;
+    for (int b = 0; b < B; ++b) acc = fmaf(dpred[b * n_out + o], feat[static_cast<long long>(b) * C + c], acc);
+    dW[o * C + c] = acc;
+  }
+  if (threadIdx.x == 0) {
+    float acc = 0.f;
+    for (int b = 0; b < B; ++b) acc += dpred[b * n_out + o];
+    db[o] = acc;
+  }
+}
+
+// dy[b][hw][c] = (sum_o dpred[b][o] W[o][c]) / HW, broadcast over the pixels (one CTA per frame)
+__global__ void __launch_bounds__(256)
+head_bwd_input_kernel(const float* __restrict__ dpred, const float* __restrict__ fc_w, int HW, int C, int n_out,
+                      __nv_bfloat16* __restrict__ dy) {
+  extern __shared__ float s_df[];
+  const int b = blockIdx.x;
+  const float inv = 1.0f / static_cast<float>(HW);
+  for (int c = threadIdx.x; c < C; c += 256) {
+    float acc = 0.f;
+    for (int o = 0; o < n_out; ++o) acc = fmaf(dpred[b * n_out + o], __ldg(fc_w + o * C + c), acc);
+    s_df[c] = acc * inv;
+  }
+  __syncthreads();
+  __nv_bfloat16* out = dy + static_cast<long long>(b) * HW * C;
+  for (int i = threadIdx.x; i < HW * C; i += 256) out[i] = __float2bfloat16_rn(s_df[i % C]);
+}
+
+// ---- optimizer: global gradient norm, clip, AdamW (train.py:301-303; torch.optim.AdamW defaults) ----------------
+__global__ void __launch_bounds__(256)
+grad_sqnorm_kernel(const float* __restrict__ g, long long n, float grad_scale, double* __restrict__ out) {
+  __shared__ float s_part[256];
+  float acc = 0.f;
+  for (long long i = static_cast<long long>(blockIdx.x) * 256 + threadIdx.x; i < n; i += static_cast<long long>(gridDim.x) * 256) {
+    const float v = g[i] * grad_scale;
+    acc = fmaf(v, v, acc);
+  }
+  s_part[threadIdx.x] = acc;
+  __syncthreads();
+  for (int s = 128; s > 0; s >>= 1) {
+    if (threadIdx.x < s) s_part[threadIdx.x] += s_part[threadIdx.x + s];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) atomicAdd(out, static_cast<double>(s_part[0]));
+}
+
+// decay[i] (0/1 per element would cost a byte per parameter): torch's AdamW applies weight decay to EVERY parameter of
+// the group (train.py:199 passes model.parameters()), so one scalar wd is exact.
+__global__ void __launch_bounds__(256)
+adamw_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
+             long long n, float lr, float b1, float b2, float eps, float wd, float bc1, float bc2_sqrt, float grad_scale,
+             float max_norm, const double* __restrict__ sqnorm) {
+  float clip = 1.f;
+  if (max_norm > 0.f) {  // clip_grad_norm_: coef = max_norm / (total_norm + 1e-6), clamped to 1
+    const float total = static_cast<float>(sqrt(*sqnorm));
+    clip = fminf(max_norm / (total + 1e-6f), 1.f);
+  }
+  const float gs = grad_scale * clip;
+  for (long long i = static_cast<long long>(blockIdx.x) * 256 + threadIdx.x; i < n; i += static_cast<long long>(gridDim.x) * 256) {
+    const float gi = g[i] * gs;
+    float pi = p[i];
+    pi -= lr * wd * pi;
+    const float mi = b1 * m[i] + (1.f - b1) * gi;
+    const float vi = b2 * v[i] + (1.f - b2) * gi * gi;
+    m[i] = mi;
+    v[i] = vi;
+    const float denom = sqrtf(vi) / bc2_sqrt + eps;
+    p[i] = pi - (lr / bc1) * (mi / denom);
+  }
+}
+
+}  // namespace pb200
+
+extern "C" int pb200_train_head_forward(const void* y_nhwc, const float* fc_w, const float* fc_b, float* feat, float* pred,
+                                        int B, int HW, int C, int n_out, pb200_stream stream) {
+  if (int rc = require_device()) return rc;
+  PB_CHECK(y_nhwc && fc_w && fc_b && feat && pred && C % 2 == 0, "train_head_forward: bad argument");
+  head_train_fwd_kernel<<<B, 256, sizeof(float) * C, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(y_nhwc), fc_w, fc_b, feat, pred, HW, C, n_out);
+  PB_CUDA(cudaGetLastError());
+  return PB200_OK;
+}
+
+extern "C" int pb200_train_smooth_l1(const float* pred, const float* target, int n, float beta, float* loss, float* dpred,
+                                     pb200_stream stream) {
+  if (int rc = require_device()) return rc;
+  PB_CHECK(pred && target && loss && dpred && n >= 1 && beta > 0.f, "train_smooth_l1: bad argument");
+  smooth_l1_kernel<<<1, 256, 0, static_cast<cudaStream_t>(stream)>>>(pred, target, n, beta, loss, dpred);
+  PB_CUDA(cudaGetLastError());
+  return PB200_OK;
+}
+
+extern "C" int pb200_train_head_backward(const float* dpred, const float* feat, const float* fc_w, int B, int HW, int C,
+                                         int n_out, float* d_fc_w, float* d_fc_b, void* dy_nhwc, pb200_stream stream) {
+  if (int rc = require_device()) return rc;
+  PB_CHECK(dpred && feat && fc_w && d_fc_w && d_fc_b && dy_nhwc, "train_head_backward: null argument");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  head_bwd_params_kernel<<<n_out, 256, 0, st>>>(dpred, feat, B, C, n_out, d_fc_w, d_fc_b);
+  head_bwd_input_kernel<<<B, 256, sizeof(float) * C, st>>>(dpred, fc_w, HW, C, n_out, static_cast<__nv_bfloat16*>(dy_nhwc));
+  PB_CUDA(cudaGetLastError());
+  return PB200_OK;
+}
+
+extern "C" int pb200_train_adamw_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n,
+                                      float lr, float beta1, float beta2, float eps, float weight_decay, int step,
+                                      float grad_scale, float max_norm, double* sqnorm_scratch, pb200_stream stream) {
+  if (int rc = require_device()) return rc;
+  PB_CHECK(params && grads && exp_avg && exp_avg_sq && sqnorm_scratch && n >= 1 && step >= 1, "train_adamw_step: bad argument");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int grid = num_sms() * 4;
+  PB_CUDA(cudaMemsetAsync(sqnorm_scratch, 0, sizeof(double), st));
+  if (max_norm > 0.f) grad_sqnorm_kernel<<<grid, 256, 0, st>>>(grads, n, grad_scale, sqnorm_scratch);
+  const float bc1 = 1.f - powf(beta1, static_cast<float>(step));
+  const float bc2_sqrt = sqrtf(1.f - powf(beta2, static_cast<float>(step)));
+  adamw_kernel<<<grid, 256, 0, st>>>(params, grads, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps, weight_decay, bc1,
+                                     bc2_sqrt, grad_scale, max_norm, sqnorm_scratch);
+  PB_CUDA(cudaGetLastError());
+  return PB200_OK;
+}

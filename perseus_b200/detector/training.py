@@ -1,0 +1,291 @@
+"""Native data-parallel training step of the keypoint detector (reference: perseus/detector/train.py:259-304).
+
+One `NativeTrainer.step(x, target)` = forward with batch-statistics BatchNorm -> SmoothL1Loss(beta=1) -> backward ->
+(NCCL all-reduce of the flat gradient when a process group is given) -> clip_grad_norm_(1.0) -> AdamW, all on
+hand-written sm_100a kernels through the C ABI (`pb200_train_*`):
+
+  * convolutions: forward and data gradient on the tcgen05 implicit-GEMM kernels (the data gradient is the same
+    kernel fed with the flipped/transposed filter; stride-2 layers convolve a zero-stuffed gradient), weight gradient
+    on the MN-major tcgen05 GEMM of csrc/wgrad_umma.cu; conv1 is an explicit im2col GEMM;
+  * BatchNorm statistics / apply / backward, ReLU masks, max-pool, head, loss and the fused optimizer: memory-bound
+    SIMT kernels of csrc/train.cu.
+
+Activations are NHWC bf16 (the reference trains under fp16 autocast, train.py:259-261; north_star asks for bf16),
+parameters, gradients and optimizer state are fp32 in ONE flat buffer each, so the all-reduce is a single NCCL call
+over NVLink and the optimizer a single kernel.  The module's parameters are re-pointed at views of the flat buffer:
+`state_dict()`, checkpoints and the eval-mode native forward keep working on the trained weights.
+
+There is no autograd and no PyTorch fallback on this path; torch is used for memory and `torch.distributed`.
+"""
+from __future__ import annotations
+
+import torch
+import torch.distributed as dist
+
+from .. import _lib
+
+
+class _Conv:
+    """One conv + its BatchNorm: parameter views, packed operands and saved tensors of a step."""
+
+    def __init__(self, name, conv, bn, Hin, Win, stem=False):
+        self.name = name
+        self.conv, self.bn = conv, bn
+        self.Cout, self.Cin_real = conv.weight.shape[0], conv.weight.shape[1]
+        self.R = conv.weight.shape[2]
+        self.stride, self.pad = conv.stride[0], conv.padding[0]
+        self.Hin, self.Win = Hin, Win
+        self.Ho = (Hin + 2 * self.pad - self.R) // self.stride + 1
+        self.Wo = (Win + 2 * self.pad - self.R) // self.stride + 1
+        self.stem = stem
+        self.Cin = 256 if stem else self.Cin_real  # the stem runs as a 1x1 conv over its im2col matrix (K = 256)
+
+
+class NativeTrainer:
+    def __init__(self, model, batch: int, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8,
+                 weight_decay: float = 1e-2, max_norm: float = 1.0, l1_beta: float = 1.0, process_group=None):
+        p0 = next(model.parameters())
+        if not p0.is_cuda:
+            raise RuntimeError("NativeTrainer: the model must be on a B200 (cuda); there is no CPU training path")
+        if model.H != 256 or model.W != 256:
+            raise ValueError("NativeTrainer: the tcgen05 kernels are tiled for 256x256 frames")
+        self.lib = _lib.lib()
+        self.model = model
+        self.dev = p0.device
+        self.B = batch
+        self.lr, self.betas, self.eps, self.wd = lr, betas, eps, weight_decay
+        self.max_norm, self.l1_beta = max_norm, l1_beta
+        self.pg = process_group
+        self.world = dist.get_world_size(process_group) if (process_group is not None or dist.is_initialized()) else 1
+        self.step_count = 0
+        self._flatten()
+        self._build_graph()
+        self._allocate()
+
+    # ---- flat parameter / gradient / optimizer-state buffers ------------------------------------------------------
+    def _flatten(self):
+        params = list(self.model.parameters())
+        n = sum(p.numel() for p in params)
+        f32 = dict(dtype=torch.float32, device=self.dev)
+        self.flat_p = torch.empty(n, **f32)
+        self.flat_g = torch.zeros(n, **f32)
+        self.flat_m = torch.zeros(n, **f32)
+        self.flat_v = torch.zeros(n, **f32)
+        self.grad_of = {}
+        off = 0
+        for p in params:
+            k = p.numel()
+            self.flat_p[off:off + k].copy_(p.detach().reshape(-1).float())
+            p.data = self.flat_p[off:off + k].view(p.shape)
+            gview = self.flat_g[off:off + k].view(p.shape)
+            p.grad = gview
+            self.grad_of[id(p)] = gview
+            off += k
+        self.n_params = n
+        if self.world > 1:  # DDP's initial parameter broadcast (train.py:152)
+            dist.broadcast(self.flat_p, src=0, group=self.pg)
+
+    def _g(self, p):
+        return self.grad_of[id(p)]
+
+    # ---- layer graph (torchvision resnet18, resnet.py:266-282) ----------------------------------------------------
+    def _build_graph(self):
+        r = self.model.resnet
+        H = self.model.H
+        self.stem = _Conv("conv1", r.conv1, r.bn1, H, H, stem=True)
+        self.blocks = []
+        h = H // 4
+        for li, layer in enumerate((r.layer1, r.layer2, r.layer3, r.layer4)):
+            for bi, blk in enumerate(layer):
+                c1 = _Conv(f"layer{li + 1}.{bi}.conv1", blk.conv1, blk.bn1, h, h)
+                c2 = _Conv(f"layer{li + 1}.{bi}.conv2", blk.conv2, blk.bn2, c1.Ho, c1.Wo)
+                ds = None
+                if blk.downsample is not None:
+                    ds = _Conv(f"layer{li + 1}.{bi}.downsample", blk.downsample[0], blk.downsample[1], h, h)
+                self.blocks.append((c1, c2, ds))
+                h = c1.Ho
+        self.convs = [self.stem] + [c for b in self.blocks for c in b if c is not None]
+
+    def _allocate(self):
+        B, dev = self.B, self.dev
+        bf = dict(dtype=torch.bfloat16, device=dev)
+        f32 = dict(dtype=torch.float32, device=dev)
+        H = self.model.H
+        self.A = torch.empty(B * (H // 2) * (H // 2), 256, **bf)  # conv1 im2col
+        max_act = 0
+        for c in self.convs:
+            M = B * c.Ho * c.Wo
+            c.M = M
+            c.z = torch.empty(M, c.Cout, **bf)
+            c.y = torch.empty(M, c.Cout, **bf)
+            c.mean = torch.empty(c.Cout, **f32)
+            c.invstd = torch.empty(c.Cout, **f32)
+            c.w_fwd = torch.empty(c.Cout * c.R * c.R * c.Cin, **bf)
+            c.w_dgrad = None if c.stem else torch.empty(c.Cout * c.R * c.R * c.Cin, **bf)
+            max_act = max(max_act, M * c.Cout)
+        s = self.stem
+        self.pool = torch.empty(B * (s.Ho // 2) * (s.Wo // 2), 64, **bf)
+        self.pool_idx = torch.empty(B * (s.Ho // 2) * (s.Wo // 2) * 64, dtype=torch.uint8, device=dev)
+        # backward work buffers: gradients w.r.t. activations (ping-pong), conv outputs, identity branch, zero-stuffed
+        act1 = max(c.M * c.Cout for c in self.convs if not c.stem)   # largest non-stem activation (layer1)
+        self.dY = [torch.empty(act1, **bf) for _ in range(2)]
+        self.dT = torch.empty(act1, **bf)
+        self.dz = torch.empty(act1, **bf)
+        self.dzd = torch.empty(act1, **bf)
+        self.g_idn = torch.empty(act1, **bf)
+        self.tmp = torch.empty(act1, **bf)
+        stuffed = max([4 * c.M * c.Cout for c in self.convs if c.stride == 2 and not c.stem] + [8])
+        self.stuffed = [torch.empty(stuffed, **bf) for _ in range(2)]
+        self.dy0 = torch.empty(s.M * 64, **bf)   # gradient w.r.t. the stem activation (after max-pool backward)
+        self.dz0 = torch.empty(s.M * 64, **bf)
+        self.scratch = torch.zeros(9 * 512 * 512, **f32)   # wgrad partial sums [R*R][Cin][Cout]
+        self.sums = torch.zeros(2 * 512, dtype=torch.float64, device=dev)
+        self.sqnorm = torch.zeros(1, dtype=torch.float64, device=dev)
+        self.zero_bias = torch.zeros(512, **f32)
+        nk = 2 * self.model.n_keypoints
+        self.feat = torch.empty(B, 512, **f32)
+        self.pred = torch.empty(B, nk, **f32)
+        self.dpred = torch.empty(B, nk, **f32)
+        self.loss = torch.zeros(1, **f32)
+
+    # ---- thin wrappers over the C ABI --------------------------------------------------------------------------
+    def _s(self):
+        return _lib.current_stream_ptr()
+
+    def _conv(self, x, B, H, W, Cin, w, Cout, R, stride, pad, out, residual=None, relu=0):
+        _lib.check(self.lib.pb200_train_conv(x.data_ptr(), B, H, W, Cin, w.data_ptr(), self.zero_bias.data_ptr(), Cout, R,
+                                             stride, pad, _lib.ptr(residual), relu, out.data_ptr(), self._s()))
+
+    def _bn_forward(self, c, residual=None, relu=1):
+        bn = c.bn
+        _lib.check(self.lib.pb200_train_bn_stats(c.z.data_ptr(), c.M, c.Cout, self.sums.data_ptr(), self._s()))
+        _lib.check(self.lib.pb200_train_bn_apply(
+            c.z.data_ptr(), self.sums.data_ptr(), bn.weight.data_ptr(), bn.bias.data_ptr(), bn.running_mean.data_ptr(),
+            bn.running_var.data_ptr(), float(bn.momentum), float(bn.eps), c.mean.data_ptr(), c.invstd.data_ptr(),
+            _lib.ptr(residual), relu, c.y.data_ptr(), c.M, c.Cout, self._s()))
+        bn.num_batches_tracked += 1
+
+    def _bn_backward(self, c, dy, mask, dz, g_out=None, stuffed=None):
+        bn = c.bn
+        _lib.check(self.lib.pb200_train_bn_backward(
+            dy.data_ptr(), _lib.ptr(mask), c.z.data_ptr(), c.mean.data_ptr(), c.invstd.data_ptr(), bn.weight.data_ptr(),
+            self.sums.data_ptr(), c.M, c.Cout, dz.data_ptr(), _lib.ptr(g_out), _lib.ptr(stuffed), c.Ho, c.Wo,
+            self._g(bn.weight).data_ptr(), self._g(bn.bias).data_ptr(), self._s()))
+
+    def _wgrad(self, c, x, dz):
+        n = c.R * c.R * c.Cin * c.Cout
+        self.scratch[:n].zero_()
+        if c.stem:  # 1x1 "conv" over the im2col matrix
+            H = self.model.H // 2
+            _lib.check(self.lib.pb200_train_wgrad(x.data_ptr(), dz.data_ptr(), self.B, H, H, 256, 64, 1, 1, 0,
+                                                  self.scratch.data_ptr(), self._s()))
+            _lib.check(self.lib.pb200_train_stem_unpack(self.scratch.data_ptr(), c.Cin_real,
+                                                        self._g(c.conv.weight).data_ptr(), self._s()))
+            return
+        _lib.check(self.lib.pb200_train_wgrad(x.data_ptr(), dz.data_ptr(), self.B, c.Hin, c.Win, c.Cin, c.Cout, c.R, c.stride,
+                                              c.pad, self.scratch.data_ptr(), self._s()))
+        _lib.check(self.lib.pb200_train_unpack_wgrad(self.scratch.data_ptr(), c.Cout, c.Cin, c.R, c.Cin,
+                                                     self._g(c.conv.weight).data_ptr(), self._s()))
+
+    def _dgrad(self, c, dz_or_stuffed, out, residual=None):
+        """gradient w.r.t. the conv input: stride-1 conv of dz (zero-stuffed for stride-2 layers) with the flipped filter"""
+        _lib.check(self.lib.pb200_train_conv(dz_or_stuffed.data_ptr(), self.B, c.Hin, c.Win, c.Cout, c.w_dgrad.data_ptr(),
+                                             self.zero_bias.data_ptr(), c.Cin, c.R, 1, c.R // 2, _lib.ptr(residual), 0,
+                                             out.data_ptr(), self._s()))
+
+    def _pack_weights(self):
+        for c in self.convs:
+            w = c.conv.weight
+            if c.stem:
+                _lib.check(self.lib.pb200_train_stem_pack(w.data_ptr(), c.Cin_real, c.w_fwd.data_ptr(), self._s()))
+            else:
+                _lib.check(self.lib.pb200_train_pack_weights(w.data_ptr(), c.Cout, c.Cin, c.R, 0, c.w_fwd.data_ptr(), self._s()))
+                _lib.check(self.lib.pb200_train_pack_weights(w.data_ptr(), c.Cout, c.Cin, c.R, 1, c.w_dgrad.data_ptr(), self._s()))
+
+    # ---- the step ---------------------------------------------------------------------------------------------------
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        """x: (B, C, 256, 256) float32 cuda, NCHW as train.py:266-268 builds it -> predictions (B, 2K) float32."""
+        B, m = self.B, self.model
+        if tuple(x.shape) != (B, m.num_channels, m.H, m.W) or not x.is_cuda:
+            raise ValueError(f"NativeTrainer.forward: expected a cuda ({B}, {m.num_channels}, {m.H}, {m.W}) batch")
+        x = x.detach().to(torch.float32).contiguous()
+        self._pack_weights()
+        s = self.stem
+        _lib.check(self.lib.pb200_train_stem_im2col(x.data_ptr(), B, m.num_channels, m.H, m.W, self.A.data_ptr(), self._s()))
+        self._conv(self.A, B, s.Ho, s.Wo, 256, s.w_fwd, 64, 1, 1, 0, s.z)
+        self._bn_forward(s, relu=1)
+        _lib.check(self.lib.pb200_train_maxpool(s.y.data_ptr(), self.pool.data_ptr(), self.pool_idx.data_ptr(), B, s.Ho, s.Wo,
+                                                64, self._s()))
+        cur = self.pool
+        for c1, c2, ds in self.blocks:
+            self._conv(cur, B, c1.Hin, c1.Win, c1.Cin, c1.w_fwd, c1.Cout, c1.R, c1.stride, c1.pad, c1.z)
+            self._bn_forward(c1, relu=1)
+            self._conv(c1.y, B, c2.Hin, c2.Win, c2.Cin, c2.w_fwd, c2.Cout, c2.R, 1, c2.pad, c2.z)
+            idn = cur
+            if ds is not None:
+                self._conv(cur, B, ds.Hin, ds.Win, ds.Cin, ds.w_fwd, ds.Cout, 1, ds.stride, 0, ds.z)
+                self._bn_forward(ds, relu=0)
+                idn = ds.y
+            self._bn_forward(c2, residual=idn, relu=1)
+            c1.x_in = cur
+            cur = c2.y
+        last = self.blocks[-1][1]
+        fc = m.resnet.fc
+        _lib.check(self.lib.pb200_train_head_forward(cur.data_ptr(), fc.weight.data_ptr(), fc.bias.data_ptr(), self.feat.data_ptr(),
+                                                     self.pred.data_ptr(), B, last.Ho * last.Wo, last.Cout, fc.weight.shape[0],
+                                                     self._s()))
+        return self.pred
+
+    def backward(self, target: torch.Tensor) -> torch.Tensor:
+        """SmoothL1Loss(pred, target) (train.py:119,290) and the gradient of every parameter into the flat buffer."""
+        B, m = self.B, self.model
+        fc = m.resnet.fc
+        n_out = fc.weight.shape[0]
+        t = target.detach().to(torch.float32).reshape(B, n_out).contiguous()
+        _lib.check(self.lib.pb200_train_smooth_l1(self.pred.data_ptr(), t.data_ptr(), B * n_out, float(self.l1_beta),
+                                                  self.loss.data_ptr(), self.dpred.data_ptr(), self._s()))
+        last = self.blocks[-1][1]
+        dY, other = self.dY
+        _lib.check(self.lib.pb200_train_head_backward(self.dpred.data_ptr(), self.feat.data_ptr(), fc.weight.data_ptr(), B,
+                                                      last.Ho * last.Wo, last.Cout, n_out, self._g(fc.weight).data_ptr(),
+                                                      self._g(fc.bias).data_ptr(), dY.data_ptr(), self._s()))
+        for c1, c2, ds in reversed(self.blocks):
+            # out = relu(bn2(z2) + idn): g = dY * [out > 0] feeds bn2's backward and the identity branch
+            self._bn_backward(c2, dY, c2.y, self.dz, g_out=self.g_idn)
+            self._wgrad(c2, c1.y, self.dz)
+            self._dgrad(c2, self.dz, self.dT)                      # gradient w.r.t. y1 (before its ReLU mask)
+            st = c1.stride == 2
+            self._bn_backward(c1, self.dT, c1.y, self.dz, stuffed=self.stuffed[0] if st else None)
+            self._wgrad(c1, c1.x_in, self.dz)
+            if ds is not None:
+                self._bn_backward(ds, self.g_idn, None, self.dzd, stuffed=self.stuffed[1] if ds.stride == 2 else None)
+                self._wgrad(ds, c1.x_in, self.dzd)
+                self._dgrad(ds, self.stuffed[1] if ds.stride == 2 else self.dzd, self.tmp)
+                self._dgrad(c1, self.stuffed[0] if st else self.dz, other, residual=self.tmp)
+            else:
+                self._dgrad(c1, self.dz, other, residual=self.g_idn)
+            dY, other = other, dY
+        s = self.stem
+        _lib.check(self.lib.pb200_train_maxpool_backward(dY.data_ptr(), self.pool_idx.data_ptr(), self.dy0.data_ptr(), B, s.Ho,
+                                                         s.Wo, 64, self._s()))
+        self._bn_backward(s, self.dy0, s.y, self.dz0)
+        self._wgrad(s, self.A, self.dz0)
+        return self.loss
+
+    def optimizer_step(self):
+        """gradient all-reduce (NCCL, one call on the flat buffer) + clip_grad_norm_ + AdamW (train.py:300-303)."""
+        if self.world > 1:
+            dist.all_reduce(self.flat_g, op=dist.ReduceOp.SUM, group=self.pg)
+        self.step_count += 1
+        _lib.check(self.lib.pb200_train_adamw_step(
+            self.flat_p.data_ptr(), self.flat_g.data_ptr(), self.flat_m.data_ptr(), self.flat_v.data_ptr(), self.n_params,
+            float(self.lr), float(self.betas[0]), float(self.betas[1]), float(self.eps), float(self.wd), self.step_count,
+            1.0 / self.world, float(self.max_norm), self.sqnorm.data_ptr(), self._s()))
+        self.model.refresh_weights()  # the eval-mode native forward re-folds BN from the updated parameters
+
+    def step(self, x: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
+        with torch.cuda.device(self.dev):
+            self.forward(x)
+            loss = self.backward(target)
+            self.optimizer_step()
+        return loss

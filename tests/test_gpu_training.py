@@ -90,3 +90,191 @@ def test_dgrad_stride1_is_a_conv_with_the_flipped_transposed_filter(case):
     err = (got - want).abs()
     tol = 2.0 ** -7 * want.abs() + 1e-2
     assert (err <= tol).all(), f"max err {float(err.max()):.4f}"
+
+
+# ---- memory-bound training kernels ------------------------------------------------------------------------------
+@pytest.mark.parametrize("M,C,use_res,relu", [(4096, 64, False, True), (1000, 128, True, True), (257, 512, False, False)])
+def test_bn_forward_and_backward_vs_autograd(M, C, use_res, relu):
+    L = _lib()
+    g = torch.Generator().manual_seed(M + C)
+    z = (torch.randn(M, C, generator=g) * 1.5 + 0.3).bfloat16()
+    res = torch.randn(M, C, generator=g).bfloat16() if use_res else None
+    gamma, beta = torch.rand(C, generator=g) + 0.5, torch.randn(C, generator=g) * 0.1
+    rm, rv = torch.randn(C, generator=g) * 0.1, torch.rand(C, generator=g) + 0.5
+    dy = torch.randn(M, C, generator=g).bfloat16()
+    # reference in fp64 on the same bf16 inputs
+    zr = z.double().requires_grad_(True)
+    gr, br = gamma.double().requires_grad_(True), beta.double().requires_grad_(True)
+    rm_ref, rv_ref = rm.double().clone(), rv.double().clone()
+    pre = F.batch_norm(zr, rm_ref, rv_ref, gr, br, training=True, momentum=0.1, eps=1e-5)
+    if use_res:
+        pre = pre + res.double()
+    y_ref = pre.relu() if relu else pre
+    zd, dyd = z.cuda(), dy.cuda()
+    resd = res.cuda() if use_res else None
+    gd, bd, rmd, rvd = gamma.cuda(), beta.cuda(), rm.cuda(), rv.cuda()
+    sums = torch.zeros(2 * C, dtype=torch.float64, device="cuda")
+    mean, invstd = torch.empty(C, device="cuda"), torch.empty(C, device="cuda")
+    y = torch.full((M, C), float("nan"), dtype=torch.bfloat16, device="cuda")
+    L.check(L.lib().pb200_train_bn_stats(zd.data_ptr(), M, C, sums.data_ptr(), _stream()))
+    L.check(L.lib().pb200_train_bn_apply(zd.data_ptr(), sums.data_ptr(), gd.data_ptr(), bd.data_ptr(), rmd.data_ptr(),
+                                         rvd.data_ptr(), 0.1, 1e-5, mean.data_ptr(), invstd.data_ptr(),
+                                         None if resd is None else resd.data_ptr(), int(relu), y.data_ptr(), M, C, _stream()))
+    torch.cuda.synchronize()
+    assert torch.allclose(rmd.double().cpu(), rm_ref, atol=1e-5) and torch.allclose(rvd.double().cpu(), rv_ref, rtol=1e-5, atol=1e-5)
+    err = (y.double().cpu() - y_ref.detach()).abs()
+    assert (err <= 2.0 ** -7 * y_ref.detach().abs() + 1e-3).all(), float(err.max())
+    # backward: the kernel masks with ITS OWN stored output, as the trainer does
+    y_mask = y if relu else None
+    g_masked = dy.double() * ((y.double().cpu() > 0) if relu else 1.0)
+    pre.backward(g_masked)
+    dz = torch.full((M, C), float("nan"), dtype=torch.bfloat16, device="cuda")
+    g_out = torch.full((M, C), float("nan"), dtype=torch.bfloat16, device="cuda")
+    dgam, dbet = torch.empty(C, device="cuda"), torch.empty(C, device="cuda")
+    L.check(L.lib().pb200_train_bn_backward(dyd.data_ptr(), None if y_mask is None else y_mask.data_ptr(), zd.data_ptr(),
+                                            mean.data_ptr(), invstd.data_ptr(), gd.data_ptr(), sums.data_ptr(), M, C,
+                                            dz.data_ptr(), g_out.data_ptr(), None, 0, 0, dgam.data_ptr(), dbet.data_ptr(),
+                                            _stream()))
+    torch.cuda.synchronize()
+    assert torch.equal(g_out.double().cpu(), g_masked.bfloat16().double())
+    e = (dz.double().cpu() - zr.grad).abs()
+    assert (e <= 2.0 ** -7 * zr.grad.abs() + 2e-3).all(), float(e.max())
+    assert torch.allclose(dgam.double().cpu(), gr.grad, rtol=2e-3, atol=2e-2)
+    assert torch.allclose(dbet.double().cpu(), br.grad, rtol=2e-3, atol=2e-2)
+
+
+def test_bn_backward_zero_stuffed_copy():
+    L = _lib()
+    B, Ho, Wo, C = 2, 4, 8, 64
+    M = B * Ho * Wo
+    g = torch.Generator().manual_seed(1)
+    z, dy = torch.randn(M, C, generator=g).bfloat16().cuda(), torch.randn(M, C, generator=g).bfloat16().cuda()
+    mean, invstd = torch.zeros(C, device="cuda"), torch.ones(C, device="cuda")
+    gamma = torch.ones(C, device="cuda")
+    sums = torch.zeros(2 * C, dtype=torch.float64, device="cuda")
+    dz = torch.empty(M, C, dtype=torch.bfloat16, device="cuda")
+    stuffed = torch.full((B, 2 * Ho, 2 * Wo, C), float("nan"), dtype=torch.bfloat16, device="cuda")
+    dg, db = torch.empty(C, device="cuda"), torch.empty(C, device="cuda")
+    L.check(L.lib().pb200_train_bn_backward(dy.data_ptr(), None, z.data_ptr(), mean.data_ptr(), invstd.data_ptr(),
+                                            gamma.data_ptr(), sums.data_ptr(), M, C, dz.data_ptr(), None, stuffed.data_ptr(),
+                                            Ho, Wo, dg.data_ptr(), db.data_ptr(), _stream()))
+    torch.cuda.synchronize()
+    want = torch.zeros_like(stuffed)
+    want[:, ::2, ::2] = dz.view(B, Ho, Wo, C)
+    assert torch.equal(stuffed, want)
+
+
+def test_maxpool_forward_backward_vs_autograd():
+    L = _lib()
+    B, H, W, C = 3, 16, 32, 64
+    g = torch.Generator().manual_seed(2)
+    x = torch.randn(B, H, W, C, generator=g).relu().bfloat16()  # many exact ties at 0 and some at equal bf16 values
+    dout = torch.randn(B, H // 2, W // 2, C, generator=g).bfloat16()
+    xr = x.double().permute(0, 3, 1, 2).requires_grad_(True)
+    yr = F.max_pool2d(xr, 3, 2, 1)
+    yr.backward(dout.double().permute(0, 3, 1, 2))
+    xd, dd = x.cuda(), dout.cuda()
+    out = torch.empty(B, H // 2, W // 2, C, dtype=torch.bfloat16, device="cuda")
+    idx = torch.empty(B * (H // 2) * (W // 2) * C, dtype=torch.uint8, device="cuda")
+    din = torch.full((B, H, W, C), float("nan"), dtype=torch.bfloat16, device="cuda")
+    L.check(L.lib().pb200_train_maxpool(xd.data_ptr(), out.data_ptr(), idx.data_ptr(), B, H, W, C, _stream()))
+    L.check(L.lib().pb200_train_maxpool_backward(dd.data_ptr(), idx.data_ptr(), din.data_ptr(), B, H, W, C, _stream()))
+    torch.cuda.synchronize()
+    assert torch.equal(out.double().cpu(), yr.detach().permute(0, 2, 3, 1))
+    want = xr.grad.permute(0, 2, 3, 1)
+    e = (din.double().cpu() - want).abs()
+    assert (e <= 2.0 ** -7 * want.abs() + 1e-6).all(), float(e.max())
+
+
+def test_adamw_clip_step_vs_torch():
+    L = _lib()
+    n = 100_003
+    g = torch.Generator().manual_seed(3)
+    p0 = torch.randn(n, generator=g)
+    p = torch.nn.Parameter(p0.clone().cuda())
+    opt = torch.optim.AdamW([p], lr=1e-3)
+    mine_p = p0.clone().cuda()
+    m, v = torch.zeros(n, device="cuda"), torch.zeros(n, device="cuda")
+    sq = torch.zeros(1, dtype=torch.float64, device="cuda")
+    for step in range(1, 4):
+        grad = (torch.randn(n, generator=g) * (3.0 if step == 1 else 0.001)).cuda()  # clipped, then not clipped
+        p.grad = grad.clone()
+        torch.nn.utils.clip_grad_norm_([p], 1.0)
+        opt.step()
+        L.check(L.lib().pb200_train_adamw_step(mine_p.data_ptr(), grad.data_ptr(), m.data_ptr(), v.data_ptr(), n, 1e-3, 0.9, 0.999,
+                                               1e-8, 1e-2, step, 1.0, 1.0, sq.data_ptr(), _stream()))
+        torch.cuda.synchronize()
+        assert torch.allclose(mine_p, p.detach(), rtol=1e-5, atol=1e-6), float((mine_p - p.detach()).abs().max())
+
+
+# ---- the whole step ----------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("C", [4, 3])
+def test_native_train_step_matches_autograd(C):
+    """forward + SmoothL1 + backward + clip + AdamW through pb200_train_* vs the torch module tree under bf16
+    autocast (what stage A / the reference's train.py:259-304 runs) and vs the same in fp32."""
+    import copy
+
+    from perseus_b200.detector import KeypointCNN
+    from perseus_b200.detector.training import NativeTrainer
+
+    torch.manual_seed(0)
+    B = 8
+    model = KeypointCNN(num_channels=C).cuda()
+    ref = copy.deepcopy(model.resnet).float().train()
+    g = torch.Generator(device="cuda").manual_seed(1)
+    x = torch.rand(B, C, 256, 256, device="cuda", generator=g)
+    if C == 4:
+        x[:, 3] = x[:, 3] * 8 + 3  # depth in data units
+    tgt = torch.rand(B, 8, 2, device="cuda", generator=g) * 2 - 1
+    tr = NativeTrainer(model, B)
+    pred = tr.forward(x).clone()
+    loss = float(tr.backward(tgt))
+
+    def run_ref(autocast):
+        r = copy.deepcopy(ref)
+        with torch.autocast("cuda", dtype=torch.bfloat16, enabled=autocast):
+            out = r(x).float()
+            ls = F.smooth_l1_loss(out.reshape(-1, 8, 2), tgt, beta=1.0)
+        ls.backward()
+        return r, out.detach(), float(ls)
+
+    r32, out32, loss32 = run_ref(False)
+    r16, out16, loss16 = run_ref(True)
+    e_pred = float((pred - out32).abs().max())
+    e_pred16 = float((out16 - out32).abs().max())
+    print(f"[train C={C}] pred err vs fp32 {e_pred:.4f} (autocast's own {e_pred16:.4f}); loss {loss:.5f} / {loss32:.5f} / {loss16:.5f}")
+    assert e_pred <= 3 * e_pred16 + 0.02
+    assert abs(loss - loss32) <= 0.02 * abs(loss32) + 3 * abs(loss16 - loss32)
+    worst = 0.0
+    for (name, p32), (_, p16) in zip(r32.named_parameters(), r16.named_parameters()):
+        mine = tr._g(dict(model.resnet.named_parameters())[name])
+        den = float(p32.grad.norm()) + 1e-12
+        rel = float((mine - p32.grad).norm()) / den
+        rel16 = float((p16.grad.float() - p32.grad).norm()) / den
+        worst = max(worst, rel)
+        assert rel <= 3 * rel16 + 0.05, f"{name}: rel err {rel:.3f} vs fp32 autograd (autocast's own {rel16:.3f})"
+    print(f"[train C={C}] worst per-tensor gradient rel err {worst:.3f}")
+    # optimizer: same update as clip_grad_norm_ + AdamW on OUR gradients
+    params = [p for p in model.parameters()]
+    before = [p.detach().clone() for p in params]
+    grads = [tr._g(p).clone() for p in params]
+    tr.optimizer_step()
+    torch.cuda.synchronize()
+    shadow = [torch.nn.Parameter(b.clone()) for b in before]
+    for s, gr in zip(shadow, grads):
+        s.grad = gr
+    torch.nn.utils.clip_grad_norm_(shadow, 1.0)
+    torch.optim.AdamW(shadow, lr=1e-3).step()
+    for p, s in zip(params, shadow):
+        assert torch.allclose(p.detach(), s.detach(), rtol=1e-5, atol=1e-6)
+    # BN running statistics follow nn.BatchNorm2d
+    for (n1, b1), (n2, b2) in zip(model.resnet.named_buffers(), r32.named_buffers()):
+        if n1.endswith("num_batches_tracked"):
+            assert int(b1) == int(b2)
+        else:
+            assert torch.allclose(b1, b2, rtol=2e-2, atol=2e-2), n1
+    # the eval-mode native forward sees the updated weights
+    model.eval()
+    with torch.no_grad():
+        y = model(x)
+    assert torch.isfinite(y).all()
