@@ -200,6 +200,10 @@ int pb200_factors_constvel(const double* vel1, const double* vel2, double* resid
  * mode 1: data-gradient [Cin][(R-1-r,R-1-s,co)] (flipped + transposed filter). */
 int pb200_train_pack_weights(const float* w_oihw, int Cout, int Cin, int R, int mode, void* out_bf16,
                              pb200_stream stream);
+/* every weight pack of a step in one launch.  table_dev: int64 [n][8] on the device, one row per conv:
+ * {w fp32 OIHW ptr, forward operand ptr, data-gradient operand ptr or 0, Cout, Cin, R, first element index,
+ *  kind (0 conv, 1 conv1 -> [64][256] im2col operand)}; total = sum of the element counts. */
+int pb200_train_pack_all(const int64_t* table_dev, int n, int64_t total, pb200_stream stream);
 /* convolution on NHWC bf16 with device-packed weights; out = [relu](conv + bias [+ residual]). */
 int pb200_train_conv(const void* in_nhwc, int B, int H, int W, int Cin, const void* wpacked, const float* bias,
                      int Cout, int R, int stride, int pad, const void* residual_or_null, int relu,

@@ -67,6 +67,7 @@ SIGNATURES = {
         c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p]
     ),
     "pb200_train_pack_weights": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "pb200_train_pack_all": (c_int, [c_void_p, c_int, c_int64, c_void_p]),
     "pb200_train_conv": (
         c_int,
         [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_int,

@@ -403,35 +403,41 @@ extern "C" int pb200_train_bn_backward(const void* dy, const void* y_mask_or_nul
 namespace pb200 {
 
 // conv1 (7x7 / 2, pad 3) as a GEMM: A[m][k], m = (b, ho, wo), k = (r*7 + s)*C + c for k < 49*C, zero up to K = 256.
-// x is the reference-style NCHW fp32 batch (train.py:266-268).  One thread = one (m, tap) -> C bf16 values.
+// x is the reference-style NCHW fp32 batch (train.py:266-268).  One CTA = one output row (b, ho): the 7 input rows it
+// touches are staged in shared memory with coalesced loads (zero padded), then every thread emits 16-byte chunks
+// (8 consecutive k) of the 128 A rows, so the 2 GB write is fully coalesced.
+template <int C>
 __global__ void __launch_bounds__(256)
-stem_im2col_kernel(const float* __restrict__ x, int B, int C, int H, int W, int Ho, int Wo,
-                   __nv_bfloat16* __restrict__ A) {
-  constexpr int K = 256;
-  const long long total = static_cast<long long>(B) * Ho * Wo * 64;  // 64 slots per row: 49 taps + 15 zero slots
-  const long long gid = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (gid >= total) return;
-  const int slot = static_cast<int>(gid & 63);
-  const long long m = gid >> 6;
-  const int wo = static_cast<int>(m % Wo);
-  const long long t = m / Wo;
-  const int ho = static_cast<int>(t % Ho);
-  const int b = static_cast<int>(t / Ho);
-  __nv_bfloat16* row = A + m * K;
-  if (slot >= 49) {
-    // zero tail: columns [49*C, 256) split over the 15 spare slots
-    const int tail0 = 49 * C, tail = K - tail0;
-    const int per = (tail + 14) / 15;
-    const int k0 = tail0 + (slot - 49) * per;
-    for (int k = k0; k < k0 + per && k < K; ++k) row[k] = __float2bfloat16_rn(0.f);
-    return;
+stem_im2col_kernel(const float* __restrict__ x, int H, int W, int Ho, int Wo, uint4* __restrict__ A) {
+  extern __shared__ float s_in[];  // [C][7][W + 6]
+  const int Wp = W + 6;
+  const int b = blockIdx.x / Ho, ho = blockIdx.x - b * Ho;
+  for (int i = threadIdx.x; i < C * 7 * Wp; i += 256) {
+    const int wi = i % Wp - 3;
+    const int t = i / Wp;
+    const int r = t % 7, c = t / 7;
+    const int hi = 2 * ho + r - 3;
+    float v = 0.f;
+    if (hi >= 0 && hi < H && wi >= 0 && wi < W) v = __ldg(x + ((static_cast<long long>(b) * C + c) * H + hi) * W + wi);
+    s_in[i] = v;
   }
-  const int r = slot / 7, s = slot - r * 7;
-  const int hi = 2 * ho + r - 3, wi = 2 * wo + s - 3;
-  const bool in = hi >= 0 && hi < H && wi >= 0 && wi < W;
-  for (int c = 0; c < C; ++c) {
-    const float v = in ? __ldg(x + ((static_cast<long long>(b) * C + c) * H + hi) * W + wi) : 0.f;
-    row[slot * C + c] = __float2bfloat16_rn(v);
+  __syncthreads();
+  uint4* rowbase = A + static_cast<long long>(blockIdx.x) * Wo * 32;  // 32 chunks of 16 B per A row
+  for (int i = threadIdx.x; i < Wo * 32; i += 256) {
+    const int j = i & 31, wo = i >> 5;
+    float f[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const int k = 8 * j + e;
+      float v = 0.f;
+      if (k < 49 * C) {
+        const int tap = k / C, c = k - tap * C;
+        const int r = tap / 7, sx = tap - r * 7;
+        v = s_in[(c * 7 + r) * Wp + 2 * wo + sx];
+      }
+      f[e] = v;
+    }
+    rowbase[i] = make_uint4(pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]), pack_bf16x2(f[4], f[5]), pack_bf16x2(f[6], f[7]));
   }
 }
 
@@ -546,9 +552,16 @@ extern "C" int pb200_train_stem_im2col(const float* x_nchw, int B, int C, int H,
   if (int rc = require_device()) return rc;
   PB_CHECK(x_nchw && A_bf16 && C >= 1 && C <= 4 && H % 2 == 0 && W % 2 == 0, "train_stem_im2col: bad argument");
   const int Ho = H / 2, Wo = W / 2;
-  const long long total = static_cast<long long>(B) * Ho * Wo * 64;
-  stem_im2col_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      x_nchw, B, C, H, W, Ho, Wo, static_cast<__nv_bfloat16*>(A_bf16));
+  const size_t smem = sizeof(float) * C * 7 * (W + 6);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  uint4* A = static_cast<uint4*>(A_bf16);
+  const unsigned grid = static_cast<unsigned>(B) * Ho;
+  switch (C) {
+    case 1: stem_im2col_kernel<1><<<grid, 256, smem, st>>>(x_nchw, H, W, Ho, Wo, A); break;
+    case 2: stem_im2col_kernel<2><<<grid, 256, smem, st>>>(x_nchw, H, W, Ho, Wo, A); break;
+    case 3: stem_im2col_kernel<3><<<grid, 256, smem, st>>>(x_nchw, H, W, Ho, Wo, A); break;
+    default: stem_im2col_kernel<4><<<grid, 256, smem, st>>>(x_nchw, H, W, Ho, Wo, A); break;
+  }
   PB_CUDA(cudaGetLastError());
   return PB200_OK;
 }
@@ -778,6 +791,65 @@ extern "C" int pb200_train_adamw_step(float* params, const float* grads, float* 
   const float bc2_sqrt = sqrtf(1.f - powf(beta2, static_cast<float>(step)));
   adamw_kernel<<<grid, 256, 0, st>>>(params, grads, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps, weight_decay, bc1,
                                      bc2_sqrt, grad_scale, max_norm, sqnorm_scratch);
+  PB_CUDA(cudaGetLastError());
+  return PB200_OK;
+}
+
+// ---- all weight packs of a step in ONE launch -----------------------------------------------------------------
+// table[n][8] (int64, device): {w fp32 OIHW, out forward bf16, out data-gradient bf16 (0: none), Cout, Cin, R,
+// first element index, kind (0: conv, 1: conv1 as [64][256] im2col GEMM operand with Cin real channels)}
+namespace pb200 {
+__global__ void __launch_bounds__(256)
+pack_all_kernel(const long long* __restrict__ table, int n, long long total) {
+  __shared__ long long s_t[32 * 8];
+  for (int i = threadIdx.x; i < n * 8; i += 256) s_t[i] = table[i];
+  __syncthreads();
+  const long long gid = static_cast<long long>(blockIdx.x) * 256 + threadIdx.x;
+  if (gid >= total) return;
+  int e = 0;
+  while (e + 1 < n && gid >= s_t[(e + 1) * 8 + 6]) ++e;
+  const long long* d = s_t + e * 8;
+  const float* w = reinterpret_cast<const float*>(d[0]);
+  __nv_bfloat16* of = reinterpret_cast<__nv_bfloat16*>(d[1]);
+  __nv_bfloat16* od = reinterpret_cast<__nv_bfloat16*>(d[2]);
+  const int Cout = static_cast<int>(d[3]), Cin = static_cast<int>(d[4]), R = static_cast<int>(d[5]);
+  const long long i = gid - d[6];
+  if (d[7] == 1) {  // conv1: i in [0, 64*256)
+    const int co = static_cast<int>(i >> 8), k = static_cast<int>(i & 255);
+    float v = 0.f;
+    if (k < 49 * Cin) {
+      const int tap = k / Cin, c = k - tap * Cin;
+      v = w[(co * Cin + c) * 49 + tap];
+    }
+    of[i] = __float2bfloat16_rn(v);
+    return;
+  }
+  {
+    const int ci = static_cast<int>(i % Cin);
+    long long t = i / Cin;
+    const int s = static_cast<int>(t % R);
+    t /= R;
+    const int r = static_cast<int>(t % R);
+    const int co = static_cast<int>(t / R);
+    of[i] = __float2bfloat16_rn(w[((static_cast<long long>(co) * Cin + ci) * R + r) * R + s]);
+  }
+  if (od != nullptr) {
+    const int co = static_cast<int>(i % Cout);
+    long long t = i / Cout;
+    const int s2 = static_cast<int>(t % R);
+    t /= R;
+    const int r2 = static_cast<int>(t % R);
+    const int ci = static_cast<int>(t / R);
+    od[i] = __float2bfloat16_rn(w[((static_cast<long long>(co) * Cin + ci) * R + (R - 1 - r2)) * R + (R - 1 - s2)]);
+  }
+}
+}  // namespace pb200
+
+extern "C" int pb200_train_pack_all(const int64_t* table_dev, int n, int64_t total, pb200_stream stream) {
+  if (int rc = require_device()) return rc;
+  PB_CHECK(table_dev && n >= 1 && n <= 32 && total >= 1, "train_pack_all: bad argument");
+  pack_all_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const long long*>(table_dev), n, total);
   PB_CUDA(cudaGetLastError());
   return PB200_OK;
 }

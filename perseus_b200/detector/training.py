@@ -43,7 +43,8 @@ class _Conv:
 
 class NativeTrainer:
     def __init__(self, model, batch: int, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8,
-                 weight_decay: float = 1e-2, max_norm: float = 1.0, l1_beta: float = 1.0, process_group=None):
+                 weight_decay: float = 1e-2, max_norm: float = 1.0, l1_beta: float = 1.0, process_group=None,
+                 use_graph: bool = True):
         p0 = next(model.parameters())
         if not p0.is_cuda:
             raise RuntimeError("NativeTrainer: the model must be on a B200 (cuda); there is no CPU training path")
@@ -58,6 +59,8 @@ class NativeTrainer:
         self.pg = process_group
         self.world = dist.get_world_size(process_group) if (process_group is not None or dist.is_initialized()) else 1
         self.step_count = 0
+        self.use_graph = use_graph   # forward + backward captured once into a CUDA graph (~250 launches per step)
+        self._graph, self._eager_steps = None, 0
         self._flatten()
         self._build_graph()
         self._allocate()
@@ -147,10 +150,42 @@ class NativeTrainer:
         self.pred = torch.empty(B, nk, **f32)
         self.dpred = torch.empty(B, nk, **f32)
         self.loss = torch.zeros(1, **f32)
+        self.x_static = torch.zeros(B, self.model.num_channels, H, H, **f32)
+        self.t_static = torch.zeros(B, nk, **f32)
 
     # ---- thin wrappers over the C ABI --------------------------------------------------------------------------
     def _s(self):
         return _lib.current_stream_ptr()
+
+    _pack_table = None
+    _prof = None  # when a list: (label, start event, end event) per wrapper call (see profile_step)
+
+    def _mark(self, label):
+        if self._prof is None:
+            return None
+        e0 = torch.cuda.Event(enable_timing=True)
+        e0.record()
+        return (label, e0)
+
+    def _done(self, tok):
+        if tok is not None:
+            e1 = torch.cuda.Event(enable_timing=True)
+            e1.record()
+            self._prof.append((tok[0], tok[1], e1))
+
+    def profile_step(self, x, target):
+        """One step with CUDA events around every operator class -> {label: ms} (adds event overhead; not a bench)."""
+        self._prof = []
+        with torch.cuda.device(self.dev):
+            self.forward(x)
+            self.backward(target)
+            self.optimizer_step()
+            torch.cuda.synchronize()
+        out = {}
+        for label, e0, e1 in self._prof:
+            out[label] = out.get(label, 0.0) + e0.elapsed_time(e1)
+        self._prof = None
+        return out
 
     def _conv(self, x, B, H, W, Cin, w, Cout, R, stride, pad, out, residual=None, relu=0):
         _lib.check(self.lib.pb200_train_conv(x.data_ptr(), B, H, W, Cin, w.data_ptr(), self.zero_bias.data_ptr(), Cout, R,
@@ -194,13 +229,16 @@ class NativeTrainer:
                                              out.data_ptr(), self._s()))
 
     def _pack_weights(self):
-        for c in self.convs:
-            w = c.conv.weight
-            if c.stem:
-                _lib.check(self.lib.pb200_train_stem_pack(w.data_ptr(), c.Cin_real, c.w_fwd.data_ptr(), self._s()))
-            else:
-                _lib.check(self.lib.pb200_train_pack_weights(w.data_ptr(), c.Cout, c.Cin, c.R, 0, c.w_fwd.data_ptr(), self._s()))
-                _lib.check(self.lib.pb200_train_pack_weights(w.data_ptr(), c.Cout, c.Cin, c.R, 1, c.w_dgrad.data_ptr(), self._s()))
+        if self._pack_table is None:
+            rows, start = [], 0
+            for c in self.convs:
+                n = 64 * 256 if c.stem else c.Cout * c.Cin * c.R * c.R
+                rows.append([c.conv.weight.data_ptr(), c.w_fwd.data_ptr(), 0 if c.stem else c.w_dgrad.data_ptr(), c.Cout,
+                             c.Cin_real if c.stem else c.Cin, c.R, start, 1 if c.stem else 0])
+                start += n
+            self._pack_table = torch.tensor(rows, dtype=torch.int64, device=self.dev)
+            self._pack_total = start
+        _lib.check(self.lib.pb200_train_pack_all(self._pack_table.data_ptr(), len(self.convs), self._pack_total, self._s()))
 
     # ---- the step ---------------------------------------------------------------------------------------------------
     def forward(self, x: torch.Tensor) -> torch.Tensor:
@@ -284,8 +322,50 @@ class NativeTrainer:
         self.model.refresh_weights()  # the eval-mode native forward re-folds BN from the updated parameters
 
     def step(self, x: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
+        """One training step; returns the (device) loss of this batch."""
         with torch.cuda.device(self.dev):
-            self.forward(x)
-            loss = self.backward(target)
+            if not self.use_graph:
+                self.forward(x)
+                loss = self.backward(target)
+            else:
+                self.x_static.copy_(x, non_blocking=True)
+                self.t_static.copy_(target.reshape(self.B, -1), non_blocking=True)
+                if self._graph is not None:
+                    self._graph.replay()
+                elif self._eager_steps < 2:  # first steps eagerly: one-off attribute / occupancy queries happen here
+                    self.forward(self.x_static)
+                    self.backward(self.t_static)
+                    self._eager_steps += 1
+                else:
+                    graph = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(graph):
+                        self.forward(self.x_static)
+                        self.backward(self.t_static)
+                    self._graph = graph
+                    graph.replay()
+                loss = self.loss
             self.optimizer_step()
         return loss
+
+
+def _profiled(label_fn, fn):
+    def wrapper(self, *a, **k):
+        tok = self._mark(label_fn(*a, **k))
+        out = fn(self, *a, **k)
+        self._done(tok)
+        return out
+    wrapper.__doc__ = fn.__doc__
+    return wrapper
+
+
+def _layer_class(c):
+    return "stem" if c.stem else c.name.split(".")[0]
+
+
+NativeTrainer._conv = _profiled(lambda x, B, H, W, Cin, *a, **k: f"conv_fwd[{'stem' if Cin == 256 and H == 128 else str(H)}]",
+                                NativeTrainer._conv)
+NativeTrainer._bn_forward = _profiled(lambda c, **k: f"bn_fwd[{_layer_class(c)}]", NativeTrainer._bn_forward)
+NativeTrainer._bn_backward = _profiled(lambda c, *a, **k: f"bn_bwd[{_layer_class(c)}]", NativeTrainer._bn_backward)
+NativeTrainer._wgrad = _profiled(lambda c, *a, **k: f"wgrad[{_layer_class(c)}]", NativeTrainer._wgrad)
+NativeTrainer._dgrad = _profiled(lambda c, *a, **k: f"dgrad[{_layer_class(c)}]", NativeTrainer._dgrad)
+NativeTrainer._pack_weights = _profiled(lambda: "pack_weights", NativeTrainer._pack_weights)

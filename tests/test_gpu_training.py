@@ -251,9 +251,10 @@ def test_native_train_step_matches_autograd(C):
         den = float(p32.grad.norm()) + 1e-12
         rel = float((mine - p32.grad).norm()) / den
         rel16 = float((p16.grad.float() - p32.grad).norm()) / den
-        worst = max(worst, rel)
+        if rel > worst:
+            worst, worst_name, worst16 = rel, name, rel16
         assert rel <= 3 * rel16 + 0.05, f"{name}: rel err {rel:.3f} vs fp32 autograd (autocast's own {rel16:.3f})"
-    print(f"[train C={C}] worst per-tensor gradient rel err {worst:.3f}")
+    print(f"[train C={C}] worst per-tensor gradient rel err {worst:.3f} ({worst_name}; autocast's own {worst16:.3f})")
     # optimizer: same update as clip_grad_norm_ + AdamW on OUR gradients
     params = [p for p in model.parameters()]
     before = [p.detach().clone() for p in params]
@@ -278,3 +279,35 @@ def test_native_train_step_matches_autograd(C):
     with torch.no_grad():
         y = model(x)
     assert torch.isfinite(y).all()
+
+
+def test_graph_replayed_steps_match_eager_steps():
+    """step() captures forward + backward into one CUDA graph after two eager steps.  The split-K wgrad and the BN
+    statistics use atomics, so two runs differ by rounding noise that Adam's sign-like first updates amplify; the
+    graphed trainer must stay as close to an eager trainer as a second eager trainer does."""
+    import copy
+
+    from perseus_b200.detector import KeypointCNN
+    from perseus_b200.detector.training import NativeTrainer
+
+    torch.manual_seed(0)
+    B = 4
+    models = [KeypointCNN(num_channels=4).cuda()]
+    models += [copy.deepcopy(models[0]) for _ in range(2)]
+    trainers = [NativeTrainer(models[0], B, use_graph=False), NativeTrainer(models[1], B, use_graph=False),
+                NativeTrainer(models[2], B, use_graph=True)]
+    g = torch.Generator(device="cuda").manual_seed(5)
+    for i in range(5):
+        x = torch.rand(B, 4, 256, 256, device="cuda", generator=g)
+        y = torch.rand(B, 8, 2, device="cuda", generator=g) * 2 - 1
+        ls = [float(t.step(x, y)) for t in trainers]
+        print(f"[graph] step {i}: losses {ls}")
+        assert abs(ls[0] - ls[2]) <= 5 * abs(ls[0] - ls[1]) + 3e-2 * abs(ls[0]) + 1e-4, ls
+    assert trainers[2]._graph is not None
+    worst = 0.0
+    for (n, a), (_, b), (_, c) in zip(*[m.named_parameters() for m in models]):
+        noise = float((a - b).abs().mean())
+        d = float((a - c).abs().mean())
+        worst = max(worst, d / (noise + 1e-7))
+        assert d <= 3 * noise + 1e-4, (n, d, noise)
+    print(f"[graph] worst graph-vs-eager / eager-vs-eager mean |dw| ratio {worst:.2f}")

@@ -24,12 +24,71 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
 
+def run_native(args, rank, world, local, dev):
+    """STAGE B: the whole step on this repo's kernels (perseus_b200/detector/training.py)."""
+    import time
+
+    from perseus_b200.detector import KeypointCNN
+    from perseus_b200.detector.training import NativeTrainer
+
+    torch.manual_seed(0)
+    model = KeypointCNN(num_channels=args.channels).to(dev)
+    tr = NativeTrainer(model, args.batch)
+    g = torch.Generator(device=dev).manual_seed(rank)
+    xs = [torch.rand(args.batch, args.channels, 256, 256, device=dev, generator=g) for _ in range(2)]
+    y = torch.rand(args.batch, 8, 2, device=dev, generator=g) * 2 - 1
+    for i in range(args.warmup):
+        tr.step(xs[i % 2], y)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
+    e0.record()
+    for i in range(args.steps):
+        loss = tr.step(xs[i % 2], y)
+    e1.record()
+    host_ms = (time.perf_counter() - t0) * 1e3
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    if world > 1:
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    prof = None
+    if args.profile and rank == 0:
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+        ev[0].record(); tr.forward(xs[0]); ev[1].record(); tr.backward(y); ev[2].record(); tr.optimizer_step(); ev[3].record()
+        torch.cuda.synchronize()
+        prof = {"forward_ms": ev[0].elapsed_time(ev[1]), "backward_ms": ev[1].elapsed_time(ev[2]),
+                "allreduce_clip_adamw_ms": ev[2].elapsed_time(ev[3])}
+        ops = tr.profile_step(xs[0], y)
+        prof["per_operator_ms"] = {k: round(v, 3) for k, v in sorted(ops.items(), key=lambda kv: -kv[1])}
+    model.eval()
+    with torch.no_grad():
+        out = model(xs[0][:8])
+    if rank == 0:
+        print(json.dumps({
+            "metric": "train_step_frames_per_sec (stage B: native sm_100a kernels, fwd+loss+bwd+allreduce+clip+AdamW)",
+            "value": world * args.batch * args.steps / (ms * 1e-3), "unit": "frames/s", "n_gpus": world,
+            "ms_per_step": ms / args.steps, "host_enqueue_ms_per_step": host_ms / args.steps, "per_gpu_batch": args.batch,
+            "dtype": "bf16 activations, fp32 params/grads/optimizer", "channels": args.channels,
+            "allreduce_bytes_per_step": 4 * tr.n_params, "loss": float(loss), "scaling": "weak", "phases": prof,
+            "native_eval_forward_ok": bool(torch.isfinite(out).all()),
+        }), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--batch", type=int, default=256)  # per GPU, train.py:39
     ap.add_argument("--channels", type=int, default=4)  # train.py default is RGBD
+    ap.add_argument("--impl", default="native", choices=["native", "library"])
+    ap.add_argument("--profile", action="store_true", help="native: per-kernel-class CUDA-event times of one step")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -41,6 +100,9 @@ def main():
         dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
 
     from perseus_b200.detector import KeypointCNN
+
+    if args.impl == "native":
+        return run_native(args, rank, world, local, dev)
 
     torch.manual_seed(0)
     model = KeypointCNN(num_channels=args.channels).to(dev).to(memory_format=torch.channels_last)
