@@ -224,12 +224,15 @@ int pb200_train_bn_apply(const void* z, const double* sums, const float* gamma, 
                          float* running_mean, float* running_var, float momentum, float eps, float* save_mean,
                          float* save_invstd, const void* residual_or_null, int relu, void* y, int64_t M, int C,
                          pb200_stream stream);
-/* BatchNorm backward fused with the ReLU mask of the layer output: g = dy * [y_mask > 0] (y_mask null: g = dy);
+/* BatchNorm backward fused with the ReLU mask of the layer output: g = dy * [y_mask > 0]; y_mask null and beta
+ * given: the mask is recomputed from z with the forward's affine map (layers without a residual input) — one
+ * tensor less to read per pass; both null: g = dy;
  * dz = gamma * invstd * (g - mean(g) - xhat * mean(g * xhat)); dgamma = sum g * xhat; dbeta = sum g.
  * Optionally also writes g (the gradient the identity branch receives) and a zero-stuffed copy of dz,
  * [B][2*Ho][2*Wo][C] with dz at the even positions, which a stride-2 data gradient convolves at stride 1. */
 int pb200_train_bn_backward(const void* dy, const void* y_mask_or_null, const void* z, const float* save_mean,
-                            const float* save_invstd, const float* gamma, double* sums, int64_t M, int C, void* dz,
+                            const float* save_invstd, const float* gamma, const float* beta_or_null, double* sums,
+                            int64_t M, int C, void* dz,
                             void* g_out_or_null, void* stuffed_out_or_null, int Ho, int Wo, float* dgamma,
                             float* dbeta, pb200_stream stream);
 /* conv1 (7x7/2) as a GEMM: im2col of the NCHW fp32 batch into bf16 [B*H/2*W/2][256] (k = (r*7+s)*C + c, zero

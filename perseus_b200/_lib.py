@@ -85,8 +85,8 @@ SIGNATURES = {
     ),
     "pb200_train_bn_backward": (
         c_int,
-        [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p, c_void_p,
-         c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p],
+        [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p,
+         c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p],
     ),
     "pb200_train_stem_im2col": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
     "pb200_train_stem_pack": (c_int, [c_void_p, c_int, c_void_p, c_void_p]),

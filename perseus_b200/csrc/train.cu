@@ -163,7 +163,7 @@ __device__ __forceinline__ RowSplit row_split(long long M, int C8) {
   return s;
 }
 
-__global__ void __launch_bounds__(kBnThreads)
+__global__ void __launch_bounds__(kBnThreads, 4)
 bn_stats_kernel(const uint4* __restrict__ z, long long M, int C, double* __restrict__ sums /* [2][C] */) {
   __shared__ float s_acc[2 * 512];
   const int C8 = C / 8;
@@ -171,6 +171,7 @@ bn_stats_kernel(const uint4* __restrict__ z, long long M, int C, double* __restr
   __syncthreads();
   const RowSplit rs = row_split(M, C8);
   float a[8] = {0, 0, 0, 0, 0, 0, 0, 0}, q[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll 4
   for (long long r = rs.row0 + rs.rl; r < rs.row1; r += rs.lanes) {
     float f[8];
     unpack8(__ldg(z + r * C8 + rs.cg), f);
@@ -189,7 +190,7 @@ bn_stats_kernel(const uint4* __restrict__ z, long long M, int C, double* __restr
   for (int i = threadIdx.x; i < 2 * C; i += kBnThreads) atomicAdd(&sums[i], static_cast<double>(s_acc[i]));
 }
 
-__global__ void __launch_bounds__(kBnThreads)
+__global__ void __launch_bounds__(kBnThreads, 4)
 bn_apply_kernel(const uint4* __restrict__ z, const double* __restrict__ sums, const float* __restrict__ gamma,
                 const float* __restrict__ beta, float* __restrict__ running_mean, float* __restrict__ running_var,
                 float momentum, float eps, float* __restrict__ save_mean, float* __restrict__ save_invstd,
@@ -215,14 +216,23 @@ bn_apply_kernel(const uint4* __restrict__ z, const double* __restrict__ sums, co
   }
   __syncthreads();
   const int C8 = C / 8;
+  // C8 is a power of two <= 64 (host check) and both the CTA size and the grid stride are multiples of it, so a thread
+  // keeps ONE channel group for the whole loop: its 8 scales / shifts live in registers
+  const int c0 = (static_cast<int>(threadIdx.x) & (C8 - 1)) * 8;
+  float sc[8], sh[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) {
+    sc[e] = s_scale[c0 + e];
+    sh[e] = s_shift[c0 + e];
+  }
   const long long total = M * C8;
-  for (long long i = static_cast<long long>(blockIdx.x) * kBnThreads + threadIdx.x; i < total;
-       i += static_cast<long long>(gridDim.x) * kBnThreads) {
-    const int c0 = static_cast<int>(i % C8) * 8;
+  const long long step = static_cast<long long>(gridDim.x) * kBnThreads;
+#pragma unroll 4
+  for (long long i = static_cast<long long>(blockIdx.x) * kBnThreads + threadIdx.x; i < total; i += step) {
     float f[8];
     unpack8(__ldg(z + i), f);
 #pragma unroll
-    for (int e = 0; e < 8; ++e) f[e] = fmaf(f[e], s_scale[c0 + e], s_shift[c0 + e]);
+    for (int e = 0; e < 8; ++e) f[e] = fmaf(f[e], sc[e], sh[e]);
     if (residual != nullptr) {
       float r[8];
       unpack8(__ldg(residual + i), r);
@@ -237,28 +247,39 @@ bn_apply_kernel(const uint4* __restrict__ z, const double* __restrict__ sums, co
   }
 }
 
-__global__ void __launch_bounds__(kBnThreads)
+// sums[0..C) = sum g, sums[C..2C) = sum g * (z - mean)   (g = dy under the layer's ReLU mask); the consumer multiplies
+// the second by invstd to get sum g * xhat
+__global__ void __launch_bounds__(kBnThreads, 3)
 bn_bwd_reduce_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ y_mask, const uint4* __restrict__ z,
-                     const float* __restrict__ mean, const float* __restrict__ invstd, long long M, int C,
-                     double* __restrict__ sums /* [2][C]: sum g, sum g*xhat */) {
+                     const float* __restrict__ mean, const float* __restrict__ invstd, const float* __restrict__ gamma,
+                     const float* __restrict__ beta, int mask_from_z, long long M, int C,
+                     double* __restrict__ sums /* [2][C] */) {
   __shared__ float s_acc[2 * 512];
   const int C8 = C / 8;
   for (int i = threadIdx.x; i < 2 * C; i += kBnThreads) s_acc[i] = 0.f;
   __syncthreads();
   const RowSplit rs = row_split(M, C8);
-  float mu[8], is[8];
+  // mask_from_z: the ReLU mask of a layer without a residual input is [z*sc + sh > 0] = [(z - mu) * sc > -beta]
+  // (the forward's affine map, bn_apply_kernel); thr = -beta / sc folded per sign of sc
+  float mu[8], sc[8], nb[8];
 #pragma unroll
   for (int e = 0; e < 8; ++e) {
-    mu[e] = mean[rs.cg * 8 + e];
-    is[e] = invstd[rs.cg * 8 + e];
+    const int c = rs.cg * 8 + e;
+    mu[e] = mean[c];
+    sc[e] = mask_from_z ? gamma[c] * invstd[c] : 0.f;
+    nb[e] = mask_from_z ? beta[c] - mu[e] * sc[e] : 0.f;
   }
   float a[8] = {0, 0, 0, 0, 0, 0, 0, 0}, q[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll 2
   for (long long r = rs.row0 + rs.rl; r < rs.row1; r += rs.lanes) {
     const long long i = r * C8 + rs.cg;
     float g[8], zz[8];
     unpack8(__ldg(dy + i), g);
     unpack8(__ldg(z + i), zz);
-    if (y_mask != nullptr) {
+    if (mask_from_z) {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) g[e] = fmaf(zz[e], sc[e], nb[e]) > 0.f ? g[e] : 0.f;
+    } else if (y_mask != nullptr) {
       float m[8];
       unpack8(__ldg(y_mask + i), m);
 #pragma unroll
@@ -267,7 +288,7 @@ bn_bwd_reduce_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ y_m
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
       a[e] += g[e];
-      q[e] = fmaf(g[e], (zz[e] - mu[e]) * is[e], q[e]);
+      q[e] = fmaf(g[e], zz[e] - mu[e], q[e]);
     }
   }
 #pragma unroll
@@ -279,58 +300,72 @@ bn_bwd_reduce_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ y_m
   for (int i = threadIdx.x; i < 2 * C; i += kBnThreads) atomicAdd(&sums[i], static_cast<double>(s_acc[i]));
 }
 
+// dz = k * (g - mean(g) - xhat * mean(g * xhat)), k = gamma * invstd, evaluated as k*g + A*z + B with per-channel
+// constants (A = -k * invstd * mean(g*xhat), B = -k * mean(g) - A * mean) held in registers.
 // stuffed_out: [B][2*Ho][2*Wo][C] with dz at the even positions (the caller zeroes it); Wo / HoWo describe dz's rows
-__global__ void __launch_bounds__(kBnThreads)
+__global__ void __launch_bounds__(kBnThreads, 3)
 bn_bwd_apply_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ y_mask, const uint4* __restrict__ z,
                     const float* __restrict__ mean, const float* __restrict__ invstd, const float* __restrict__ gamma,
-                    const double* __restrict__ sums, long long M, int C, uint4* __restrict__ dz,
+                    const float* __restrict__ beta, int mask_from_z, const double* __restrict__ sums, long long M, int C,
+                    uint4* __restrict__ dz,
                     uint4* __restrict__ g_out, uint4* __restrict__ stuffed_out, int Ho, int Wo,
                     float* __restrict__ dgamma, float* __restrict__ dbeta) {
-  __shared__ float s_k[512], s_mg[512], s_mgx[512], s_mu[512], s_is[512];
-  const float invM = 1.0f / static_cast<float>(M);
+  __shared__ float s_k[512], s_a[512], s_b[512], s_sh[512];
+  const double invM = 1.0 / static_cast<double>(M);
   for (int c = threadIdx.x; c < C; c += kBnThreads) {
-    const float sg = static_cast<float>(sums[c]), sgx = static_cast<float>(sums[C + c]);
-    s_k[c] = gamma[c] * invstd[c];
-    s_mg[c] = sg * invM;
-    s_mgx[c] = sgx * invM;
-    s_mu[c] = mean[c];
-    s_is[c] = invstd[c];
+    const double is = static_cast<double>(invstd[c]), mu = static_cast<double>(mean[c]);
+    const double sg = sums[c], sgx = sums[C + c] * is;  // sum g, sum g * xhat
+    const double k = static_cast<double>(gamma[c]) * is;
+    const double A = -k * is * (sgx * invM);
+    s_k[c] = static_cast<float>(k);
+    s_a[c] = static_cast<float>(A);
+    s_b[c] = static_cast<float>(-k * (sg * invM) - A * mu);
+    s_sh[c] = mask_from_z ? beta[c] - mean[c] * (gamma[c] * invstd[c]) : 0.f;
     if (blockIdx.x == 0) {
-      dgamma[c] = sgx;
-      dbeta[c] = sg;
+      dgamma[c] = static_cast<float>(sgx);
+      dbeta[c] = static_cast<float>(sg);
     }
   }
   __syncthreads();
   const int C8 = C / 8;
+  const int cg = static_cast<int>(threadIdx.x) & (C8 - 1);  // fixed per thread (see bn_apply_kernel)
+  float k[8], A[8], Bc[8], sh[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) {
+    k[e] = s_k[cg * 8 + e];
+    A[e] = s_a[cg * 8 + e];
+    Bc[e] = s_b[cg * 8 + e];
+    sh[e] = s_sh[cg * 8 + e];
+  }
+  const int c8_shift = __ffs(C8) - 1;
   const long long total = M * C8;
-  for (long long i = static_cast<long long>(blockIdx.x) * kBnThreads + threadIdx.x; i < total;
-       i += static_cast<long long>(gridDim.x) * kBnThreads) {
-    const int c0 = static_cast<int>(i % C8) * 8;
+  const long long step = static_cast<long long>(gridDim.x) * kBnThreads;
+#pragma unroll 2
+  for (long long i = static_cast<long long>(blockIdx.x) * kBnThreads + threadIdx.x; i < total; i += step) {
     float g[8], zz[8], o[8];
     unpack8(__ldg(dy + i), g);
     unpack8(__ldg(z + i), zz);
-    if (y_mask != nullptr) {
+    if (mask_from_z) {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) g[e] = fmaf(zz[e], k[e], sh[e]) > 0.f ? g[e] : 0.f;
+    } else if (y_mask != nullptr) {
       float m[8];
       unpack8(__ldg(y_mask + i), m);
 #pragma unroll
       for (int e = 0; e < 8; ++e) g[e] = m[e] > 0.f ? g[e] : 0.f;
     }
 #pragma unroll
-    for (int e = 0; e < 8; ++e) {
-      const int c = c0 + e;
-      const float xhat = (zz[e] - s_mu[c]) * s_is[c];
-      o[e] = s_k[c] * (g[e] - s_mg[c] - xhat * s_mgx[c]);
-    }
+    for (int e = 0; e < 8; ++e) o[e] = fmaf(k[e], g[e], fmaf(A[e], zz[e], Bc[e]));
     const uint4 ov = pack8(o);
     dz[i] = ov;
     if (g_out != nullptr) g_out[i] = pack8(g);
     if (stuffed_out != nullptr) {
-      const long long row = i / C8;
-      const int wo = static_cast<int>(row % Wo);
-      const long long t = row / Wo;
-      const int ho = static_cast<int>(t % Ho);
-      const long long b = t / Ho;
-      stuffed_out[((b * (2 * Ho) + 2 * ho) * (2LL * Wo) + 2 * wo) * C8 + (i % C8)] = ov;
+      const unsigned row = static_cast<unsigned>(i >> c8_shift);  // < 2^31 rows
+      const unsigned wo = row % static_cast<unsigned>(Wo);
+      const unsigned t = row / static_cast<unsigned>(Wo);
+      const unsigned ho = t % static_cast<unsigned>(Ho);
+      const long long b = t / static_cast<unsigned>(Ho);
+      stuffed_out[((b * (2 * Ho) + 2 * ho) * (2LL * Wo) + 2 * wo) * C8 + cg] = ov;
     }
   }
 }
@@ -346,7 +381,7 @@ static inline int bn_grid(long long M, int C) {
 
 }  // namespace pb200
 
-#define PB_BN_CHECK(C) PB_CHECK((C) % 8 == 0 && (C) <= 512 && kBnThreads % ((C) / 8) == 0, "bn: C = %d unsupported", (C))
+#define PB_BN_CHECK(C) PB_CHECK((C) >= 8 && (C) <= 512 && ((C) & ((C) - 1)) == 0, "bn: C = %d unsupported (power of two in [8, 512])", (C))
 
 extern "C" int pb200_train_bn_stats(const void* z, int64_t M, int C, double* sums, pb200_stream stream) {
   if (int rc = require_device()) return rc;
@@ -374,7 +409,8 @@ extern "C" int pb200_train_bn_apply(const void* z, const double* sums, const flo
 }
 
 extern "C" int pb200_train_bn_backward(const void* dy, const void* y_mask_or_null, const void* z, const float* save_mean,
-                                       const float* save_invstd, const float* gamma, double* sums, int64_t M, int C,
+                                       const float* save_invstd, const float* gamma, const float* beta_or_null,
+                                       double* sums, int64_t M, int C,
                                        void* dz, void* g_out_or_null, void* stuffed_out_or_null, int Ho, int Wo,
                                        float* dgamma, float* dbeta, pb200_stream stream) {
   if (int rc = require_device()) return rc;
@@ -387,10 +423,15 @@ extern "C" int pb200_train_bn_backward(const void* dy, const void* y_mask_or_nul
   if (stuffed_out_or_null != nullptr)
     PB_CUDA(cudaMemsetAsync(stuffed_out_or_null, 0, static_cast<size_t>(M) * 4 * C * 2, st));
   const int grid = bn_grid(M, C);
+  // beta given (and no y tensor): the layer had no residual input, so its ReLU mask is recomputed from z with the
+  // forward's own affine map instead of reading y (one tensor less per pass)
+  const int mask_from_z = (beta_or_null != nullptr && y_mask_or_null == nullptr) ? 1 : 0;
   bn_bwd_reduce_kernel<<<grid, kBnThreads, 0, st>>>(static_cast<const uint4*>(dy), static_cast<const uint4*>(y_mask_or_null),
-                                                    static_cast<const uint4*>(z), save_mean, save_invstd, M, C, sums);
+                                                    static_cast<const uint4*>(z), save_mean, save_invstd, gamma, beta_or_null,
+                                                    mask_from_z, M, C, sums);
   bn_bwd_apply_kernel<<<grid, kBnThreads, 0, st>>>(static_cast<const uint4*>(dy), static_cast<const uint4*>(y_mask_or_null),
-                                                   static_cast<const uint4*>(z), save_mean, save_invstd, gamma, sums, M, C,
+                                                   static_cast<const uint4*>(z), save_mean, save_invstd, gamma, beta_or_null,
+                                                   mask_from_z, sums, M, C,
                                                    static_cast<uint4*>(dz), static_cast<uint4*>(g_out_or_null),
                                                    static_cast<uint4*>(stuffed_out_or_null), Ho, Wo, dgamma, dbeta);
   PB_CUDA(cudaGetLastError());

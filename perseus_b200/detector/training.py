@@ -201,10 +201,12 @@ class NativeTrainer:
         bn.num_batches_tracked += 1
 
     def _bn_backward(self, c, dy, mask, dz, g_out=None, stuffed=None):
+        """mask: the layer output y (ReLU mask read from it), "z" (no residual input: mask recomputed from z), or None"""
         bn = c.bn
+        from_z = isinstance(mask, str)
         _lib.check(self.lib.pb200_train_bn_backward(
-            dy.data_ptr(), _lib.ptr(mask), c.z.data_ptr(), c.mean.data_ptr(), c.invstd.data_ptr(), bn.weight.data_ptr(),
-            self.sums.data_ptr(), c.M, c.Cout, dz.data_ptr(), _lib.ptr(g_out), _lib.ptr(stuffed), c.Ho, c.Wo,
+            dy.data_ptr(), None if from_z else _lib.ptr(mask), c.z.data_ptr(), c.mean.data_ptr(), c.invstd.data_ptr(),
+            bn.weight.data_ptr(), bn.bias.data_ptr() if from_z else None, self.sums.data_ptr(), c.M, c.Cout, dz.data_ptr(), _lib.ptr(g_out), _lib.ptr(stuffed), c.Ho, c.Wo,
             self._g(bn.weight).data_ptr(), self._g(bn.bias).data_ptr(), self._s()))
 
     def _wgrad(self, c, x, dz):
@@ -293,7 +295,7 @@ class NativeTrainer:
             self._wgrad(c2, c1.y, self.dz)
             self._dgrad(c2, self.dz, self.dT)                      # gradient w.r.t. y1 (before its ReLU mask)
             st = c1.stride == 2
-            self._bn_backward(c1, self.dT, c1.y, self.dz, stuffed=self.stuffed[0] if st else None)
+            self._bn_backward(c1, self.dT, "z", self.dz, stuffed=self.stuffed[0] if st else None)
             self._wgrad(c1, c1.x_in, self.dz)
             if ds is not None:
                 self._bn_backward(ds, self.g_idn, None, self.dzd, stuffed=self.stuffed[1] if ds.stride == 2 else None)
@@ -306,7 +308,7 @@ class NativeTrainer:
         s = self.stem
         _lib.check(self.lib.pb200_train_maxpool_backward(dY.data_ptr(), self.pool_idx.data_ptr(), self.dy0.data_ptr(), B, s.Ho,
                                                          s.Wo, 64, self._s()))
-        self._bn_backward(s, self.dy0, s.y, self.dz0)
+        self._bn_backward(s, self.dy0, "z", self.dz0)
         self._wgrad(s, self.A, self.dz0)
         return self.loss
 

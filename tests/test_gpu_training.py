@@ -132,10 +132,18 @@ def test_bn_forward_and_backward_vs_autograd(M, C, use_res, relu):
     g_out = torch.full((M, C), float("nan"), dtype=torch.bfloat16, device="cuda")
     dgam, dbet = torch.empty(C, device="cuda"), torch.empty(C, device="cuda")
     L.check(L.lib().pb200_train_bn_backward(dyd.data_ptr(), None if y_mask is None else y_mask.data_ptr(), zd.data_ptr(),
-                                            mean.data_ptr(), invstd.data_ptr(), gd.data_ptr(), sums.data_ptr(), M, C,
+                                            mean.data_ptr(), invstd.data_ptr(), gd.data_ptr(), None, sums.data_ptr(), M, C,
                                             dz.data_ptr(), g_out.data_ptr(), None, 0, 0, dgam.data_ptr(), dbet.data_ptr(),
                                             _stream()))
     torch.cuda.synchronize()
+    if relu and not use_res:  # the mask recomputed from z must be the mask read from y
+        dz2 = torch.full((M, C), float("nan"), dtype=torch.bfloat16, device="cuda")
+        L.check(L.lib().pb200_train_bn_backward(dyd.data_ptr(), None, zd.data_ptr(), mean.data_ptr(), invstd.data_ptr(),
+                                                gd.data_ptr(), bd.data_ptr(), sums.data_ptr(), M, C, dz2.data_ptr(), None, None,
+                                                0, 0, dgam.data_ptr(), dbet.data_ptr(), _stream()))
+        torch.cuda.synchronize()
+        d2 = (dz2.double() - dz.double()).abs()  # the two calls reduce with different atomic orders: 1 bf16 ulp
+        assert (d2 <= 2.0 ** -7 * dz.double().abs() + 1e-5).all() and torch.equal(dz2 == 0, dz == 0)
     assert torch.equal(g_out.double().cpu(), g_masked.bfloat16().double())
     e = (dz.double().cpu() - zr.grad).abs()
     assert (e <= 2.0 ** -7 * zr.grad.abs() + 2e-3).all(), float(e.max())
@@ -156,7 +164,7 @@ def test_bn_backward_zero_stuffed_copy():
     stuffed = torch.full((B, 2 * Ho, 2 * Wo, C), float("nan"), dtype=torch.bfloat16, device="cuda")
     dg, db = torch.empty(C, device="cuda"), torch.empty(C, device="cuda")
     L.check(L.lib().pb200_train_bn_backward(dy.data_ptr(), None, z.data_ptr(), mean.data_ptr(), invstd.data_ptr(),
-                                            gamma.data_ptr(), sums.data_ptr(), M, C, dz.data_ptr(), None, stuffed.data_ptr(),
+                                            gamma.data_ptr(), None, sums.data_ptr(), M, C, dz.data_ptr(), None, stuffed.data_ptr(),
                                             Ho, Wo, dg.data_ptr(), db.data_ptr(), _stream()))
     torch.cuda.synchronize()
     want = torch.zeros_like(stuffed)
