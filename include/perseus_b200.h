@@ -258,6 +258,53 @@ int pb200_train_adamw_step(float* params, const float* grads, float* exp_avg, fl
                            float lr, float beta1, float beta2, float eps, float weight_decay, int step,
                            float grad_scale, float max_norm, double* sqnorm_scratch, pb200_stream stream);
 
+/* ---- train-time augmentation -----------------------------------------------------------
+ *   pb200_augment <- KeypointAugmentation.forward      perseus/detector/augmentations.py:434-488
+ *                    RandomTransplantationWithDepth    :172-251
+ *                    kornia RandomAffine / RandomErasing x2 / RandomPlanckianJitter / ColorJiggle /
+ *                    RandomGaussianBlur / RandomPlasmaShadow as configured at :351-392
+ *                    DepthBias / DepthGaussianNoise / DepthPlane augmentations :17-169, 395-431
+ *                    normalize_pixel_coordinates       :481
+ * Per-sample draws are inputs (the host samples them); per-pixel depth noise is Philox4x32-10(seed; pixel, image).
+ *   iparams [B][PB200_AUG_IPARAMS] int32:  0 donor image (-1 none); 1-4 / 5-8 erase rectangles x, y, w, h (w = 0: none);
+ *            9 colour-jiggle order, operator k in nibble k (0 brightness 1 contrast 2 saturation 3 hue);
+ *            10 PB200_AUG_* flags; 11 reserved
+ *   fparams [B][PB200_AUG_FPARAMS] float:  0-5 forward affine matrix M (2x3, pixels; key points);  6-11 sampling map S
+ *            (2x3: source position of output pixel (x, y), kornia warp_affine conventions folded in);
+ *            12,13 Planckian red / blue gains; 14 brightness, 15 contrast, 16 saturation factors, 17 hue shift (rad);
+ *            18-22 the 5 Gaussian blur taps; 23 shadow intensity, 24 shadow quantity; rest reserved
+ *   plasma  [B][H][W] float fractal map in [0,1] for the shadow, or NULL
+ *   counts  [B] int32 scratch (transplanted cube-pixel counts; written by the call)
+ *   images  float [B][C_in][H][W], C_in 3..5 (R,G,B[,depth[,segmentation]]); out_images float [B][C_out][H][W]
+ *   keypoints float [B][K][2] pixels -> out_keypoints normalised to [-1, 1]; both may be NULL */
+#define PB200_AUG_IPARAMS 12
+#define PB200_AUG_FPARAMS 32
+#define PB200_AUG_AFFINE 1
+#define PB200_AUG_PLANCKIAN 2
+#define PB200_AUG_JIGGLE 4
+#define PB200_AUG_BLUR 8
+#define PB200_AUG_SHADOW 16
+typedef struct pb200_aug_config {
+  float cube_scale;        /* AugmentationConfig.cube_scale (0.035) */
+  float noise_cube_scale;  /* DepthGaussianNoiseAugmentation keeps its own default (0.035), augmentations.py:396 */
+  float lb_seg_ratio, ub_seg_ratio; /* transplantation acceptance bounds (0.02, 0.7) */
+  int training;            /* F.dropout active (nn.Module.training) */
+  int depth_bias;   float dev_bias, p_bias;
+  int depth_noise;  float std_noise;
+  int near_plane;   float near_mean, near_dev, p_near, near_value;
+  int far_plane;    float far_mean, far_dev, p_far, far_value;
+} pb200_aug_config;
+int pb200_augment(const float* images, const int32_t* iparams, const float* fparams, const float* plasma_or_null,
+                  const pb200_aug_config* cfg /* host */, uint64_t seed, int32_t* counts,
+                  const float* keypoints_or_null, float* out_images, float* out_keypoints_or_null, int B, int C_in,
+                  int C_out, int H, int W, int K, pb200_stream stream);
+/* Diamond-square plasma fractal (kornia.contrib.diamond_square as RandomPlasmaShadow uses it): float [B][H][W]
+ * in [0,1] (per-image min-max normalised); roughness float [B]; scratch float [B][S][S], S = 2^k + 1 >= max(H, W)
+ * (pb200_plasma_side). */
+int pb200_plasma_side(int H, int W);
+int pb200_plasma(const float* roughness, uint64_t seed, float* scratch, float* out, int B, int H, int W,
+                 pb200_stream stream);
+
 #ifdef __cplusplus
 }
 #endif
