@@ -39,6 +39,7 @@ struct AugArgs {
   int B, C_in, C_out, H, W;
   unsigned long long seed;
   pb200_aug_config cfg;
+  float drop[6];  // (p, keep) of the bias / near / far dropout masks
 };
 
 // ---- Philox4x32-10 (Salmon et al. 2011), the same generator family torch.cuda uses -----------------------------
@@ -120,24 +121,24 @@ __device__ __forceinline__ void rgb_to_hsv(float r, float g, float b, float& h, 
   const float mx = fmaxf(r, fmaxf(g, b)), mn = fminf(r, fminf(g, b));
   float delta = mx - mn;
   v = mx;
-  s = delta / (mx + 1e-8f);
+  s = __fdividef(delta, mx + 1e-8f);
   if (delta == 0.f) delta = 1.f;
   const float rc = mx - r, gc = mx - g, bc = mx - b;
   float hh;
-  if (r == mx) hh = (bc - gc) / delta;
-  else if (g == mx) hh = ((rc - bc) + 2.f * delta) / delta;
-  else hh = ((gc - rc) + 4.f * delta) / delta;
-  hh = hh / 6.f;
+  if (r == mx) hh = bc - gc;
+  else if (g == mx) hh = (rc - bc) + 2.f * delta;
+  else hh = (gc - rc) + 4.f * delta;
+  hh = __fdividef(hh, delta) * (1.f / 6.f);
   hh = hh - floorf(hh);  // python-style % 1.0
   h = kTwoPi * hh;
 }
 
 // kornia.color.hsv_to_rgb
 __device__ __forceinline__ void hsv_to_rgb(float h, float s, float v, float& r, float& g, float& b) {
-  const float h6 = (h / kTwoPi) * 6.f;
+  const float h6 = (h * (1.f / kTwoPi)) * 6.f;
   float hi = floorf(h6);
-  hi = hi - 6.f * floorf(hi / 6.f);        // floor(h*6) % 6
-  const float m6 = h6 - 6.f * floorf(h6 / 6.f);  // (h*6) % 6
+  hi = hi - 6.f * floorf(hi * (1.f / 6.f));        // floor(h*6) % 6  (hi is a small integer: exact)
+  const float m6 = h6 - 6.f * floorf(h6 * (1.f / 6.f));  // (h*6) % 6
   const float f = m6 - hi;
   const float p = v * (1.f - s), q = v * (1.f - f * s), t = v * (1.f - (1.f - f) * s);
   switch (static_cast<int>(hi)) {
@@ -185,40 +186,43 @@ __device__ __forceinline__ void colour_ops(float& r, float& g, float& b, int fla
 }
 
 // ---- depth operators (augmentations.py:17-169), fp32 in the reference's own operation order ---------------------
-__device__ __forceinline__ float dropout_mask(float u, float p, int training) {
-  // F.dropout(ones, p, training): 0 with probability p, else 1/(1-p)
-  if (!training || p <= 0.f) return 1.f;
-  if (p >= 1.f) return 0.f;
-  return u >= p ? __fdiv_rn(1.f, __fsub_rn(1.f, p)) : 0.f;
+__device__ __forceinline__ float dropout_mask(float u, float p, float keep) {
+  // F.dropout(ones, p, training): 0 with probability p, else keep = 1/(1-p); the host passes p = 0, keep = 1 when the
+  // dropout is inactive and keep = 0 for p >= 1
+  return u >= p ? keep : 0.f;
 }
 __device__ __forceinline__ float centred(float dev, float mask, float u) {  // dev * mask * 2 * (U - 0.5)
   return __fmul_rn(__fmul_rn(__fmul_rn(dev, mask), 2.f), __fsub_rn(u, 0.5f));
 }
 
-__device__ __forceinline__ float depth_ops(float d, const pb200_aug_config& c, unsigned long long seed, unsigned pix,
-                                           unsigned b) {
+struct DropKeep {
+  float p_bias, keep_bias, p_near, keep_near, p_far, keep_far;
+};
+
+__device__ __forceinline__ float depth_ops(float d, const pb200_aug_config& c, const DropKeep& K, unsigned long long seed,
+                                           unsigned pix, unsigned b) {
   const uint2 key = make_uint2(static_cast<unsigned>(seed), static_cast<unsigned>(seed >> 32));
   const uint4 w0 = philox4x32_10(make_uint4(pix, b, 0u, 0u), key);
   const uint4 w1 = philox4x32_10(make_uint4(pix, b, 1u, 0u), key);
   if (c.depth_bias) {  // DepthBiasAugmentation.forward :42-50
     const float s = __fmul_rn(c.cube_scale, d);
-    const float bias = centred(c.dev_bias, dropout_mask(u01(w0.x), c.p_bias, c.training), u01(w0.y));
+    const float bias = centred(c.dev_bias, dropout_mask(u01(w0.x), K.p_bias, K.keep_bias), u01(w0.y));
     d = __fdiv_rn(__fadd_rn(s, bias), c.cube_scale);
   }
   if (c.depth_noise) {  // DepthGaussianNoiseAugmentation.forward :76-78 (its own cube_scale = 0.035)
     const float s = __fmul_rn(c.noise_cube_scale, d);
     const float u1 = 1.f - u01(w0.z);  // (0, 1]
-    const float z = sqrtf(-2.f * logf(u1)) * cosf(kTwoPi * u01(w0.w));
+    const float z = sqrtf(-2.f * __logf(u1)) * cospif(2.f * u01(w0.w));
     d = __fdiv_rn(__fadd_rn(s, __fmul_rn(c.std_noise, z)), c.noise_cube_scale);
   }
   if (c.near_plane || c.far_plane) {  // DepthPlaneAugmentation.forward :137-168
     float s = __fmul_rn(c.cube_scale, d);
     if (c.near_plane) {
-      const float plane = __fadd_rn(c.near_mean, centred(c.near_dev, dropout_mask(u01(w1.x), c.p_near, c.training), u01(w1.y)));
+      const float plane = __fadd_rn(c.near_mean, centred(c.near_dev, dropout_mask(u01(w1.x), K.p_near, K.keep_near), u01(w1.y)));
       if (s < plane) s = c.near_value;
     }
     if (c.far_plane) {
-      const float plane = __fadd_rn(c.far_mean, centred(c.far_dev, dropout_mask(u01(w1.z), c.p_far, c.training), u01(w1.w)));
+      const float plane = __fadd_rn(c.far_mean, centred(c.far_dev, dropout_mask(u01(w1.z), K.p_far, K.keep_far), u01(w1.w)));
       if (s > plane) s = c.far_value;
     }
     d = __fdiv_rn(s, c.cube_scale);
@@ -264,6 +268,7 @@ __global__ void __launch_bounds__(kAugThreads) augment_kernel(AugArgs A) {
   const float* don = donor >= 0 ? A.images + static_cast<long long>(donor) * C * plane : nullptr;
   const int ty0 = blockIdx.y * kAugTile, tx0 = blockIdx.x * kAugTile;
   const bool blur = (flags & PB200_AUG_BLUR) != 0;
+  const DropKeep dk = {A.drop[0], A.drop[1], A.drop[2], A.drop[3], A.drop[4], A.drop[5]};
 
   // phase 1: warp + erase + colour for the tile (and its halo when the sample is blurred)
   for (int t = threadIdx.x; t < kAugSpan * kAugSpan; t += kAugThreads) {
@@ -349,7 +354,7 @@ __global__ void __launch_bounds__(kAugThreads) augment_kernel(AugArgs A) {
     for (int c = 0; c < 3; ++c) out[c * plane] = rgb[c];
     if (A.C_out > 3) {
       const float d = s_px[3][ly + kAugHalo][lx + kAugHalo];
-      out[3 * plane] = depth_ops(d, A.cfg, A.seed, static_cast<unsigned>(o), static_cast<unsigned>(b));
+      out[3 * plane] = depth_ops(d, A.cfg, dk, A.seed, static_cast<unsigned>(o), static_cast<unsigned>(b));
     }
     if (A.C_out > 4) out[4 * plane] = s_px[4][ly + kAugHalo][lx + kAugHalo];
   }
@@ -399,6 +404,13 @@ extern "C" int pb200_augment(const float* images, const int32_t* iparams, const 
   }
   AugArgs A;
   A.images = images; A.iparams = iparams; A.fparams = fparams; A.counts = counts; A.plasma = plasma_or_null;
+  const float ps[3] = {cfg->p_bias, cfg->p_near, cfg->p_far};
+  for (int i = 0; i < 3; ++i) {  // F.dropout(ones, p, training): keep = 1/(1-p) in fp32
+    const bool active = cfg->training && ps[i] > 0.f;
+    A.drop[2 * i] = active ? ps[i] : 0.f;
+    A.drop[2 * i + 1] = !active ? 1.f : (ps[i] >= 1.f ? 0.f : 1.f / (1.f - ps[i]));
+    if (active && ps[i] >= 1.f) A.drop[2 * i] = 2.f;  // u01 < 1 always: every element dropped
+  }
   A.out = out_images; A.B = B; A.C_in = C_in; A.C_out = C_out; A.H = H; A.W = W; A.seed = seed; A.cfg = *cfg;
   dim3 grid((W + kAugTile - 1) / kAugTile, (H + kAugTile - 1) / kAugTile, B);
   augment_kernel<<<grid, kAugThreads, 0, st>>>(A);

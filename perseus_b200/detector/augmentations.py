@@ -12,6 +12,7 @@ drawn inside the kernel (Philox4x32-10).  The distributions follow the kornia ge
 from __future__ import annotations
 
 import ctypes
+import functools
 import math
 from dataclasses import dataclass
 from typing import Optional, Tuple
@@ -125,12 +126,38 @@ def sampling_map(M: np.ndarray, H: int, W: int) -> np.ndarray:
     return D2 @ np.linalg.inv(M) @ D1
 
 
+def affine_matrices(ang, tx, ty, sc, shx, shy, H, W) -> np.ndarray:
+    """affine_matrix over arrays -> (B, 3, 3)."""
+    B = len(ang)
+    cx, cy = (W - 1) / 2.0, (H - 1) / 2.0
+    a = np.radians(-np.asarray(ang, dtype=np.float64))
+    al, be = sc * np.cos(a), sc * np.sin(a)
+    T = np.zeros((B, 3, 3))
+    T[:, 0, 0], T[:, 0, 1], T[:, 0, 2] = al, be, (1 - al) * cx - be * cy + tx
+    T[:, 1, 0], T[:, 1, 1], T[:, 1, 2] = -be, al, be * cx + (1 - al) * cy + ty
+    T[:, 2, 2] = 1
+    sx, sy = np.tan(np.radians(shx)), np.tan(np.radians(shy))
+    Sh = np.zeros((B, 3, 3))
+    Sh[:, 0, 0], Sh[:, 0, 1], Sh[:, 0, 2] = 1, -sx, sx * cy
+    Sh[:, 1, 0], Sh[:, 1, 1], Sh[:, 1, 2] = -sy, 1 + sx * sy, sy * (cx - sx * cy)
+    Sh[:, 2, 2] = 1
+    return T @ Sh
+
+
+def sampling_maps(M: np.ndarray, H: int, W: int) -> np.ndarray:
+    """sampling_map over a (B, 3, 3) stack."""
+    D1 = np.array([[(W - 1) / W, 0, 0.5 * (W - 1) / W], [0, (H - 1) / H, 0.5 * (H - 1) / H], [0, 0, 1]])
+    D2 = np.array([[W / (W - 1), 0, -0.5], [0, H / (H - 1), -0.5], [0, 0, 1]])
+    return D2 @ np.linalg.inv(M) @ D1
+
+
 def gaussian_taps(sigma: float, ksize: int = 5) -> np.ndarray:
     x = np.arange(ksize, dtype=np.float64) - ksize // 2
     g = np.exp(-(x ** 2) / (2.0 * sigma ** 2))
     return (g / g.sum()).astype(np.float32)
 
 
+@functools.lru_cache(maxsize=1)
 def planckian_table() -> np.ndarray:
     """(25, 2) red / blue gains relative to green for black bodies at 3000..15000 K (RandomPlanckianJitter
     mode='blackbody' picks one row per sample).  kornia's literal coefficient table is not available offline; these
@@ -148,14 +175,28 @@ def planckian_table() -> np.ndarray:
 
 
 # ---- per-sample draws (the kornia parameter generators the reference configures) -----------------------------------
-def _uniform(g: torch.Generator, n: int, lo: float, hi: float) -> np.ndarray:
-    return (lo + (hi - lo) * torch.rand(n, generator=g, dtype=torch.float64)).numpy()
+class _Pool:
+    """All of a batch's per-sample uniforms in ONE generator call (rows are consumed in a fixed order)."""
+
+    ROWS = 40
+
+    def __init__(self, g: torch.Generator, n: int):
+        self.u = torch.rand(self.ROWS, n, generator=g, dtype=torch.float64).numpy()
+        self.i = 0
+
+    def next(self) -> np.ndarray:
+        self.i += 1
+        return self.u[self.i - 1]
+
+
+def _uniform(g: "_Pool", n: int, lo: float, hi: float) -> np.ndarray:
+    return lo + (hi - lo) * g.next()
 
 
 def _erase_rects(g, B, H, W, p, scale, ratio):
     """kornia RectangleEraseGenerator: area ~ U(scale) * H * W; aspect ~ U(ratio) (two-sided when ratio spans 1);
     h = round(sqrt(area * aspect)), w = round(sqrt(area / aspect)) clamped to [1, size]; corner ~ U * (size - len + 1)."""
-    on = torch.rand(B, generator=g, dtype=torch.float64).numpy() < p
+    on = g.next() < p
     area = _uniform(g, B, scale[0], scale[1]) * H * W
     if ratio[0] < 1.0 < ratio[1]:
         a1, a2 = _uniform(g, B, ratio[0], 1.0), _uniform(g, B, 1.0, ratio[1])
@@ -182,29 +223,29 @@ def sample_params(cfg: AugmentationConfig, train: bool, B: int, C: int, H: int, 
     rough = np.full(B, 0.5, dtype=np.float32)
     if not train:
         return ip, fp, rough
+    g = _Pool(g, B)
     if cfg.random_transplantation_with_depth and C == 5 and B > 1:  # augmentations.py:201-208
-        donors = (torch.arange(B) + torch.randint(1, B, (B,), generator=g)) % B
-        ip[:, 0] = donors.numpy()
+        shift = 1 + np.minimum((g.next() * (B - 1)).astype(np.int64), B - 2)  # randint(1, B)
+        ip[:, 0] = (np.arange(B) + shift) % B
     if cfg.random_affine:  # RandomAffine(degrees, translate, scale, shear), p = 0.5
-        on = torch.rand(B, generator=g, dtype=torch.float64).numpy() < 0.5
+        on = g.next() < 0.5
         ang = _uniform(g, B, -cfg.degrees, cfg.degrees)
         tx = _uniform(g, B, -cfg.translate[0] * W, cfg.translate[0] * W)
         ty = _uniform(g, B, -cfg.translate[1] * H, cfg.translate[1] * H)
         sc = _uniform(g, B, cfg.scale[0], cfg.scale[1])
         shx = _uniform(g, B, -cfg.shear, cfg.shear)  # a scalar shear gives x-shear only
-        for b in range(B):
-            if on[b]:
-                M = affine_matrix(ang[b], tx[b], ty[b], sc[b], shx[b], 0.0, H, W)
-                fp[b, 0:6] = M[:2].reshape(-1)
-                fp[b, 6:12] = sampling_map(M, H, W)[:2].reshape(-1)
-                ip[b, 10] |= AFFINE
+        M = affine_matrices(ang, tx, ty, sc, shx, np.zeros(B), H, W)  # (B, 3, 3)
+        S = sampling_maps(M, H, W)
+        fp[on, 0:6] = M[on, :2].reshape(-1, 6)
+        fp[on, 6:12] = S[on, :2].reshape(-1, 6)
+        ip[:, 10] |= np.where(on, AFFINE, 0).astype(np.int32)
     if cfg.random_erasing:  # :361-372
         ip[:, 1:5] = _erase_rects(g, B, H, W, 0.5, (0.02, 0.1), (2.0, 3.0))
         ip[:, 5:9] = _erase_rects(g, B, H, W, 0.5, (0.02, 0.05), (0.8, 1.2))
     if cfg.planckian_jitter:  # RandomPlanckianJitter(mode="blackbody"), p = 0.5
         table = planckian_table() if planck is None else np.asarray(planck, dtype=np.float32)
-        on = torch.rand(B, generator=g, dtype=torch.float64).numpy() < 0.5
-        idx = torch.randint(0, len(table), (B,), generator=g).numpy()
+        on = g.next() < 0.5
+        idx = np.minimum((g.next() * len(table)).astype(np.int64), len(table) - 1)
         fp[:, 12:14] = table[idx]
         ip[:, 10] |= np.where(on, PLANCKIAN, 0).astype(np.int32)
     if cfg.color_jiggle:  # ColorJiggle(brightness, contrast, saturation, hue), p = 1, operator order = randperm(4)
@@ -212,18 +253,17 @@ def sample_params(cfg: AugmentationConfig, train: bool, B: int, C: int, H: int, 
         fp[:, 15] = _uniform(g, B, 1 - cfg.contrast, 1 + cfg.contrast)
         fp[:, 16] = _uniform(g, B, 1 - cfg.saturation, 1 + cfg.saturation)
         fp[:, 17] = _uniform(g, B, -cfg.hue, cfg.hue) * 2.0 * math.pi
-        for b in range(B):
-            perm = torch.randperm(4, generator=g).tolist()
-            ip[b, 9] = sum(op << (4 * k) for k, op in enumerate(perm))
+        perm = np.argsort(np.stack([g.next() for _ in range(4)], axis=1), axis=1).astype(np.int32)  # uniform random permutation
+        ip[:, 9] = perm[:, 0] | (perm[:, 1] << 4) | (perm[:, 2] << 8) | (perm[:, 3] << 12)
         ip[:, 10] |= JIGGLE
     if cfg.blur:  # RandomGaussianBlur((5, 5), (3.0, 8.0), p=0.5)
-        on = torch.rand(B, generator=g, dtype=torch.float64).numpy() < 0.5
+        on = g.next() < 0.5
         sig = _uniform(g, B, 3.0, 8.0)
-        for b in range(B):
-            fp[b, 18:23] = gaussian_taps(sig[b])
+        taps = np.exp(-((np.arange(5.0) - 2.0)[None, :] ** 2) / (2.0 * sig[:, None] ** 2))
+        fp[:, 18:23] = taps / taps.sum(axis=1, keepdims=True)
         ip[:, 10] |= np.where(on, BLUR, 0).astype(np.int32)
     if cfg.random_plasma_shadow:  # RandomPlasmaShadow(): roughness (0.1, 0.7), intensity (-1, 0), quantity (0, 1), p = 0.5
-        on = torch.rand(B, generator=g, dtype=torch.float64).numpy() < 0.5
+        on = g.next() < 0.5
         rough = _uniform(g, B, 0.1, 0.7).astype(np.float32)
         fp[:, 23] = _uniform(g, B, -1.0, 0.0)
         fp[:, 24] = _uniform(g, B, 0.0, 1.0)
@@ -272,8 +312,11 @@ class KeypointAugmentation(nn.Module):
     """Drop-in for the reference class (augmentations.py:327-488)."""
 
     def __init__(self, cfg: AugmentationConfig, train: bool = True, seed: int = 0,
-                 planckian_table: Optional[np.ndarray] = None) -> None:
+                 planckian_table: Optional[np.ndarray] = None, out_channels: Optional[int] = None) -> None:
+        """cfg, train: as the reference.  Additive: seed (host generator + Philox key), planckian_table, and
+        out_channels = write only the first k channels (what train.py:284 slices afterwards anyway)."""
         super().__init__()
+        self.out_channels = out_channels
         self.cfg = cfg
         self.train_mode = train  # the reference stores this as .train, shadowing nn.Module.train()
         self.generator = torch.Generator().manual_seed(seed)
@@ -297,5 +340,5 @@ class KeypointAugmentation(nn.Module):
         if self.train_mode and self.cfg.random_plasma_shadow and (ip[:, 10] & SHADOW).any():
             plasma = plasma_map(torch.from_numpy(rough).to(dev), seed, H, W)
         out, kp_out = augment_batch(x, ip_d, fp_d, plasma, kernel_config(self.cfg, self.train_mode, self.training),
-                                    seed, kp)
+                                    seed, kp, self.out_channels)
         return out, kp_out.reshape(*leading, -1)  # :488

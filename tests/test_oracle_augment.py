@@ -185,3 +185,15 @@ def test_oracle_pipeline_identity_and_kornia_warp_agree():
     b_, _ = ao.augment(x, ip2, fp2, None, cfg, 1, kp, kornia_warp=True)
     # colour operators are discontinuous in places (hue wrap, first-max ties): compare where both are smooth
     assert float((a - b_).abs().median()) < 1e-5 and float(((a - b_).abs() > 1e-2).float().mean()) < 5e-3
+
+
+def test_batched_host_geometry_equals_scalar():
+    rng = np.random.default_rng(4)
+    B, H, W = 7, 48, 80
+    ps = [_random_affine(rng, H, W) for _ in range(B)]
+    M = host.affine_matrices(*(np.array([p[k] for p in ps]) for k in ("angle_deg", "tx", "ty", "scale", "shear_x_deg",
+                                                                      "shear_y_deg")), H, W)
+    S = host.sampling_maps(M, H, W)
+    for b, p in enumerate(ps):
+        np.testing.assert_allclose(M[b], host.affine_matrix(**p), atol=1e-12)
+        np.testing.assert_allclose(S[b], host.sampling_map(M[b], H, W), atol=1e-12)

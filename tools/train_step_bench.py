@@ -37,6 +37,22 @@ def run_native(args, rank, world, local, dev):
     g = torch.Generator(device=dev).manual_seed(rank)
     xs = [torch.rand(args.batch, args.channels, 256, 256, device=dev, generator=g) for _ in range(2)]
     y = torch.rand(args.batch, 8, 2, device=dev, generator=g) * 2 - 1
+    aug = None
+    if args.augment:  # train.py:270-284: 5-channel batch (RGB, depth, segmentation) -> augmentation -> model channels
+        from perseus_b200.detector.augmentations import AugmentationConfig, KeypointAugmentation
+
+        aug = KeypointAugmentation(AugmentationConfig(), train=True, seed=rank, out_channels=args.channels)
+        seg = (torch.rand(args.batch, 1, 256, 256, device=dev, generator=g) < 0.2).float()
+        xs5 = [torch.cat([x[:, :3], 4 + 10 * x[:, 3:4] if args.channels > 3 else 4 + 10 * x[:, :1], seg], dim=1).contiguous()
+               for x in xs]
+        kp_px = (y + 1) * 127.5
+        step_plain = tr.step
+
+        def step_aug(x, _y):
+            xa, ya = aug(xs5[0] if x is xs[0] else xs5[1], kp_px)
+            return step_plain(xa, ya.reshape(args.batch, 8, 2))
+
+        tr.step = step_aug
     for i in range(args.warmup):
         tr.step(xs[i % 2], y)
     if world > 1:
@@ -73,7 +89,7 @@ def run_native(args, rank, world, local, dev):
             "value": world * args.batch * args.steps / (ms * 1e-3), "unit": "frames/s", "n_gpus": world,
             "ms_per_step": ms / args.steps, "host_enqueue_ms_per_step": host_ms / args.steps, "per_gpu_batch": args.batch,
             "dtype": "bf16 activations, fp32 params/grads/optimizer", "channels": args.channels,
-            "allreduce_bytes_per_step": 4 * tr.n_params, "loss": float(loss), "scaling": "weak", "phases": prof,
+            "allreduce_bytes_per_step": 4 * tr.n_params, "loss": float(loss), "scaling": "weak", "phases": prof, "augmentation_in_step": bool(args.augment),
             "native_eval_forward_ok": bool(torch.isfinite(out).all()),
         }), flush=True)
     if world > 1:
@@ -88,6 +104,7 @@ def main():
     ap.add_argument("--batch", type=int, default=256)  # per GPU, train.py:39
     ap.add_argument("--channels", type=int, default=4)  # train.py default is RGBD
     ap.add_argument("--impl", default="native", choices=["native", "library"])
+    ap.add_argument("--augment", action="store_true", help="native: fused train-time augmentation inside the timed step")
     ap.add_argument("--profile", action="store_true", help="native: per-kernel-class CUDA-event times of one step")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
