@@ -345,6 +345,66 @@ def measure_library_bar(dev, devbuf, iters=20):
         return {"error": repr(e)[:300]}
 
 
+def measure_training(dev, rank, world, steps=12, warmup=4):
+    """BASELINE.json configs[3]: the data-parallel training step (train.py:259-304: augmentation, forward, SmoothL1,
+    backward, gradient all-reduce over NCCL, clip, AdamW) on this repo's kernels, RGBD bs 256 per GPU, weak scaling.
+    Every rank runs it (the all-reduce is a collective); CUDA events, max over ranks."""
+    import torch
+    import torch.distributed as dist
+
+    from perseus_b200.detector import KeypointCNN
+    from perseus_b200.detector.augmentations import AugmentationConfig, KeypointAugmentation
+    from perseus_b200.detector.training import NativeTrainer
+
+    torch.manual_seed(0)
+    model = KeypointCNN(num_channels=4).to(dev)
+    tr = NativeTrainer(model, BATCH)
+    aug = KeypointAugmentation(AugmentationConfig(), train=True, seed=rank, out_channels=4)
+    g = torch.Generator(device=dev).manual_seed(100 + rank)
+    xs5 = []
+    for _ in range(2):  # (RGB, depth in data units, cube segmentation): what train.py:266-282 assembles
+        x = torch.rand(BATCH, 5, H, W, device=dev, generator=g)
+        x[:, 3] = 4 + 10 * x[:, 3]
+        x[:, 4] = (x[:, 4] < 0.2).float()
+        xs5.append(x)
+    kp = torch.rand(BATCH, 16, device=dev, generator=g) * 255
+
+    def step(i, with_aug):
+        if with_aug:
+            xa, ya = aug(xs5[i % 2], kp)
+        else:
+            xa, ya = xs5[i % 2][:, :4], kp / 127.5 - 1
+        return tr.step(xa, ya.reshape(BATCH, 8, 2))
+
+    out = {}
+    for name, with_aug in (("step", False), ("augment_plus_step", True)):
+        for i in range(warmup):
+            step(i, with_aug)
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(steps):
+            loss = step(i, with_aug)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        out[name] = {"frames_per_s": world * BATCH * steps / (ms * 1e-3), "ms_per_step": ms / steps}
+    out["loss_finite"] = bool(torch.isfinite(loss).all())
+    out["what"] = ("RGBD bs256/GPU, bf16 activations + fp32 master weights, tcgen05 fwd/dgrad/wgrad, batch-stat BatchNorm, "
+                   f"one NCCL all-reduce of {4 * tr.n_params} gradient bytes per step, clip 1.0 + AdamW; weak scaling; "
+                   "augment_plus_step adds the fused train-time augmentation (5-channel batch -> RGBD + key points)")
+    out["steps"] = steps
+    del tr, model, aug, xs5
+    torch.cuda.empty_cache()
+    return out
+
+
 def dist_env():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -502,6 +562,7 @@ def run_native(args):
 
     value = world * BATCH * args.steps / (ms * 1e-3)
     e2e = world * BATCH * args.steps / (ms_e2e * 1e-3)
+    training = measure_training(dev, rank, world) if not args.no_training else None
 
     line = None
     if rank == 0:
@@ -572,6 +633,7 @@ def run_native(args):
             "latency": latency,
             "factors": factors,
             "other_modes": other,
+            "training_step": training,
             "library_bar": library_bar,
             "cpu_baseline": {"value": cpu_fps, "unit": "frames/s", "cores": cores, "kind": "port",
                              "sample": f"256 frames in 32-frame batches, fp32, {cpu_dt:.1f} s (reference PyTorch "
@@ -592,6 +654,7 @@ def main():
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
+    ap.add_argument("--no-training", action="store_true", help="skip the configs[3] training-step section")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -305,6 +305,26 @@ int pb200_plasma_side(int H, int W);
 int pb200_plasma(const float* roughness, uint64_t seed, float* scratch, float* out, int B, int H, int W,
                  pb200_stream stream);
 
+/* ---- fixed-lag smoother linearisation -----------------------------------------------------
+ * The consumer of the factor entries above: GTSAM's whitening (noiseModel.Diagonal sigmas, factors.py:42,49) +
+ * Gauss-Newton system + solve, specialised to the tracking chain.  W independent windows of T states; state k =
+ * [pose tangent (rot, trans); ang_vel; vel] (12).  Inputs are the factor entries' outputs in place:
+ *   proj_resid [W*T][P][2], proj_jac [W*T][P][12]      (pb200_factors_projection on the W*T poses)
+ *   dyn_resid [W*(T-1)][6], H0..H3                     (pb200_factors_dynamics on (k, k+1) pairs, window-major)
+ *   cv_*_resid [W*(T-1)][3]                            (pb200_factors_constvel on consecutive ang_vel / vel)
+ *   sigmas13 (HOST): pixel, dynamics[6], const ang_vel[3], const vel[3]
+ *   D [W][T][12][12] row-major diagonal blocks of H = sum J^T W J (+ lambda I, + prior I on state 0),
+ *   O [W][T-1][12][12] blocks H[k+1][k],  g [W][T][12] = sum J^T W r
+ * pb200_smoother_solve: block-tridiagonal Cholesky, H delta = -g; work double [W][T][2][144]; delta [W][T][12];
+ * status int32 [W] (1 = a non-positive pivot was met) or NULL. */
+int pb200_smoother_normal_equations(const double* proj_resid, const double* proj_jac, const double* dyn_resid,
+                                    const double* H0, const double* H1, const double* H2, const double* H3,
+                                    const double* cv_angvel_resid, const double* cv_vel_resid,
+                                    const double* sigmas13 /* host */, double lambda, double prior, double* D,
+                                    double* O, double* g, int W, int T, int P, pb200_stream stream);
+int pb200_smoother_solve(const double* D, const double* O, const double* g, double* work, double* delta,
+                         int32_t* status_or_null, int W, int T, pb200_stream stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -88,6 +88,11 @@ SIGNATURES = {
         [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p,
          c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p],
     ),
+    "pb200_smoother_normal_equations": (
+        c_int,
+        [c_void_p] * 9 + [POINTER(c_double), c_double, c_double, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p],
+    ),
+    "pb200_smoother_solve": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p]),
     "pb200_augment": (
         c_int,
         [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, ctypes.c_uint64, c_void_p, c_void_p, c_void_p, c_void_p, c_int,

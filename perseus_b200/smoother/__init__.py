@@ -3,3 +3,12 @@ from .factors import (  # noqa: F401
     keypoint_projection_batch,
     pose_dynamics_batch,
 )
+from .linearize import (  # noqa: F401,E402
+    ChainSigmas,
+    chain_cost,
+    chain_factors,
+    chain_solve,
+    gauss_newton_step,
+    normal_equations,
+    pose_retract,
+)
