@@ -62,6 +62,7 @@ conv_umma_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&maps.a[0]);
     tma_prefetch_desc(&maps.b);
+    if (p.ds_cblocks > 0) tma_prefetch_desc(&maps.ds);
 #pragma unroll
     for (int i = 0; i < kStages; ++i) {
       mbar_init(&full_bar[i], 1);
@@ -153,6 +154,26 @@ conv_umma_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams
             phase ^= 1u;
           }
           }
+        }
+      }
+      // fused 1x1/2 projection of the block input: extra k-blocks whose A tile is the (2 ho, 2 wo) pixel of ds_in
+      for (int cb = 0; cb < p.ds_cblocks; ++cb, kcol += Cfg::kBlockK) {
+        if ((g++ & 1u) == static_cast<uint32_t>(pi)) {
+          mbar_wait(&empty_bar[stage], phase ^ 1u);
+          if (elect_one()) {
+            mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+            tma_load_4d(smem_a + stage * Cfg::kABytes, &maps.ds, &full_bar[stage], cb * 64, 0, ho0, n0);
+            if (cl == 1)
+              tma_load_2d(smem_b + stage * Cfg::kBBytes, &maps.b, &full_bar[stage], kcol, n_tile * BLOCK_N);
+            else
+              tma_load_2d_mcast(smem_b + stage * Cfg::kBBytes + crank * slice_rows * SW, &maps.b, &full_bar[stage], kcol,
+                                n_tile * BLOCK_N + crank * slice_rows, cmask);
+          }
+          __syncwarp();
+        }
+        if (++stage == kStages) {
+          stage = 0;
+          phase ^= 1u;
         }
       }
     }
@@ -384,7 +405,8 @@ static int max_active_clusters(int block_n, int cl) {
 
 int build_umma_conv(UmmaConvLaunch* L, const void* in, int B, int Hin, int Win, int Cin,
                     const void* wpacked, const float* bias, const void* residual, void* out, int Cout,
-                    int R, int stride, int pad, int relu, int block_n, int cluster, int split) {
+                    int R, int stride, int pad, int relu, int block_n, int cluster, int split, const void* ds_in,
+                    int ds_Hin, int ds_Win, int ds_Cin) {
   PB_CHECK(stride == 1 || stride == 2, "umma conv: stride %d unsupported", stride);
   PB_CHECK(Cin % 64 == 0, "umma conv: Cin %d not a multiple of 64", Cin);
   PB_CHECK(block_n == 64 || block_n == 128 || block_n == 256, "umma conv: block_n %d", block_n);
@@ -423,6 +445,13 @@ int build_umma_conv(UmmaConvLaunch* L, const void* in, int B, int Hin, int Win, 
   p.S = R;
   p.cblocks = Cin / 64;
   p.num_kblocks = R * R * p.cblocks * (split ? 3 : 1);
+  p.ds_cblocks = 0;
+  if (ds_in != nullptr) {
+    PB_CHECK(!split && ds_Cin % 64 == 0 && ds_Hin == 2 * Ho && ds_Win == 2 * Wo,
+             "umma conv: fused projection needs a bf16 [B][2Ho][2Wo][64k] input (got %dx%dx%d)", ds_Hin, ds_Win, ds_Cin);
+    p.ds_cblocks = ds_Cin / 64;
+    p.num_kblocks += p.ds_cblocks;
+  }
   p.cin = Cin;
   p.ktot = R * R * Cin;
   L->split = split ? 1 : 0;
@@ -462,7 +491,7 @@ int build_umma_conv(UmmaConvLaunch* L, const void* in, int B, int Hin, int Win, 
   }
   PB_CHECK(max_clusters > 0, "umma conv: no resident cluster of %d CTAs", cl);
   L->grid = (p.num_super < max_clusters ? p.num_super : max_clusters) * cl;
-  L->flops = 2.0 * static_cast<double>(M) * Cout * R * R * Cin;
+  L->flops = 2.0 * static_cast<double>(M) * Cout * (R * R * Cin + (ds_in != nullptr ? ds_Cin : 0));
 
   const uint32_t box[4] = {64u, static_cast<uint32_t>(Wo), static_cast<uint32_t>(bh),
                            static_cast<uint32_t>(imgs)};
@@ -482,7 +511,15 @@ int build_umma_conv(UmmaConvLaunch* L, const void* in, int B, int Hin, int Win, 
         if (int rc = encode_tma_bf16(&L->maps.a[hp * 2 + wp], base, 4, dims, str, box, 128)) return rc;
       }
   }
-  return encode_weight_map(&L->maps.b, wpacked, Cout, R * R * Cin * (split ? 2 : 1), block_n / p.cl, 128);
+  L->maps.ds = L->maps.a[0];
+  if (ds_in != nullptr) {  // parity (0, 0) of the block input: pixel (2 ho, 2 wo), same box as the conv's own tiles
+    const uint64_t dC = static_cast<uint64_t>(ds_Cin);
+    const uint64_t dims[4] = {dC, (uint64_t)ds_Win / 2, (uint64_t)ds_Hin / 2, (uint64_t)B};
+    const uint64_t str[3] = {2 * dC * e, 2 * (uint64_t)ds_Win * dC * e, (uint64_t)ds_Hin * ds_Win * dC * e};
+    if (int rc = encode_tma_bf16(&L->maps.ds, ds_in, 4, dims, str, box, 128)) return rc;
+  }
+  return encode_weight_map(&L->maps.b, wpacked, Cout, (R * R * Cin + (ds_in != nullptr ? ds_Cin : 0)) * (split ? 2 : 1),
+                           block_n / p.cl, 128);
 }
 
 template <int BLOCK_N, bool SPLIT>

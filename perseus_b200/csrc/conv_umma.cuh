@@ -9,6 +9,7 @@ namespace pb200 {
 struct alignas(64) UmmaConvMaps {
   CUtensorMap a[4];  // activation maps: [0] for stride 1 / the stem, [hp*2+wp] parity maps for stride 2
   CUtensorMap b;     // packed weights [Cout][Kpad]
+  CUtensorMap ds;    // fused 1x1/2 projection of the block input (extra K columns), parity (0,0) map; unused otherwise
 };
 
 struct UmmaConvParams {
@@ -25,6 +26,7 @@ struct UmmaConvParams {
   int imgs_per_tile;  // 128/(Ho*Wo) when the image is smaller than a tile, else 1
   int bh;             // output rows per tile
   int stride, pad, S, cblocks;
+  int ds_cblocks;  // fused downsample: extra 64-channel k-blocks read through maps.ds after the R*S taps (0 = none)
   int relu;
   const float* bias;            // [Cout] (folded BN shift)
   const void* residual;         // bf16 [M_total][Cout] or null
@@ -47,7 +49,10 @@ struct UmmaConvLaunch {
 int build_umma_conv(UmmaConvLaunch* L, const void* in, int B, int Hin, int Win, int Cin,
                     const void* wpacked, const float* bias, const void* residual, void* out, int Cout,
                     int R, int stride, int pad, int relu, int block_n, int cluster = 0 /* 0 = choose; 1/2/4 = multicast cluster; -2 = CTA pair */,
-                    int split = 0 /* 1: activations [hi|lo] (2*Cin channels), weights [Cout][hi K | lo K], out/residual [hi|lo] */);
+                    int split = 0 /* 1: activations [hi|lo] (2*Cin channels), weights [Cout][hi K | lo K], out/residual [hi|lo] */,
+                    // fused 1x1 stride-2 projection (resnet.py:240-243) of `ds_in` [B][ds_Hin][ds_Win][ds_Cin] accumulated into
+                    // the same tile: the packed weight rows carry ds_Cin extra columns after R*R*Cin (K-extension)
+                    const void* ds_in = nullptr, int ds_Hin = 0, int ds_Win = 0, int ds_Cin = 0);
 int launch_umma_conv(const UmmaConvLaunch& L, cudaStream_t st);  // dispatches on L.pair
 // conv_umma2.cu
 int umma_pair_init();

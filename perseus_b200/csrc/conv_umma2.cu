@@ -131,6 +131,23 @@ conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParam
           }
         }
       }
+      // fused 1x1/2 projection of the block input: extra k-blocks whose A tile is the (2 ho, 2 wo) pixel of ds_in
+      for (int cb = 0; cb < p.ds_cblocks; ++cb, kcol += 64) {
+        if ((g++ & 1u) == static_cast<uint32_t>(pi)) {
+          mbar_wait(&empty_bar[stage], phase ^ 1u);
+          if (elect_one()) {
+            const uint32_t lfull = lfull0 + stage * 8;
+            mbar_expect_tx_cluster(lfull, Cfg::kStageBytes);
+            tma_load_4d_2sm(smem_a + stage * Cfg::kABytes, &maps.ds, lfull, cb * 64, 0, ho0, n0);
+            tma_load_2d_2sm(smem_b + stage * Cfg::kBBytes, &maps.b, lfull, kcol, n_row);
+          }
+          __syncwarp();
+        }
+        if (++stage == kStages) {
+          stage = 0;
+          phase ^= 1u;
+        }
+      }
     }
   } else if (warp == 1) {
     // ================================ MMA issuer (pair leader only) ===============

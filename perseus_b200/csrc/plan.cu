@@ -2,6 +2,7 @@
 // Mirrors KeypointCNN (perseus/detector/models.py:6-40) = torchvision resnet18 with conv1 swapped
 // for RGBD and fc -> Linear(512, 2*n_keypoints); forward = ResNet._forward_impl (resnet.py:266-282).
 #include <math.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <map>
@@ -21,6 +22,8 @@ struct ConvSpec {
   int Hin, Win, Ho, Wo;
   bool stem;
   bool p8 = false;      // bf16 modes: weights packed as the resident shared-memory image of conv_p8.cu
+  int ds_conv = -1;     // bf16 mode, conv2 of a projection block: index of the 1x1/2 downsample conv fused into this one as
+                        // extra K columns (its own op is not launched)
   // device storage (offsets into the weight arena)
   size_t w_off = 0;     // packed weights
   size_t b_off = 0;     // fp32 bias [Cout]
@@ -36,6 +39,7 @@ struct Op {
   int in_buf = -1, out_buf = -1, res_buf = -1;  // activation buffer ids
   int relu = 0;
   int out_nhwc = 0;  // OP_CONV_P8: write NHWC (hand-over to the TMA-im2col layers) instead of P8
+  int ds_buf = -1;   // OP_CONV with a fused downsample: the block input the projection reads
 };
 
 // activation buffer ids
@@ -145,13 +149,19 @@ static void build_graph(pb200_plan* pl) {
       const std::string pre = "layer" + std::to_string(L + 1) + "." + std::to_string(b);
       const int t = (cur + 1) % 4, y = (cur + 2) % 4, ds = (cur + 3) % 4;
       int res = cur;
+      int fused_ds = -1;  // bf16 mode: the projection is accumulated inside conv2 (K-extension), never materialised
       if (stride != 1 || cin != cout) {  // resnet.py:240-243
         add_conv(pl, pre + ".downsample.0", pre + ".downsample.1", cin, cout, 1, stride, 0, h, w);
-        Op op;
-        op.kind = OP_CONV; op.name = pre + ".downsample"; op.conv = static_cast<int>(pl->convs.size()) - 1;
-        op.in_buf = BUF_R0 + cur; op.out_buf = BUF_R0 + ds; op.relu = 0;
-        pl->ops.push_back(op);
-        res = ds;
+        if (pl->bf16 && stride == 2 && !getenv("PB200_NO_DS_FUSION")) {
+          fused_ds = static_cast<int>(pl->convs.size()) - 1;
+          res = -1;
+        } else {
+          Op op;
+          op.kind = OP_CONV; op.name = pre + ".downsample"; op.conv = static_cast<int>(pl->convs.size()) - 1;
+          op.in_buf = BUF_R0 + cur; op.out_buf = BUF_R0 + ds; op.relu = 0;
+          pl->ops.push_back(op);
+          res = ds;
+        }
       }
       add_conv(pl, pre + ".conv1", pre + ".bn1", cin, cout, 3, stride, 1, h, w);
       {
@@ -164,8 +174,13 @@ static void build_graph(pb200_plan* pl) {
       add_conv(pl, pre + ".conv2", pre + ".bn2", cout, cout, 3, 1, 1, ho, wo);
       {
         Op op;
-        op.kind = OP_CONV; op.name = pre + ".conv2+bn2+add+relu"; op.conv = static_cast<int>(pl->convs.size()) - 1;
-        op.in_buf = BUF_R0 + t; op.out_buf = BUF_R0 + y; op.res_buf = BUF_R0 + res; op.relu = 1;
+        op.kind = OP_CONV; op.name = pre + (fused_ds >= 0 ? ".conv2+bn2+downsample+add+relu" : ".conv2+bn2+add+relu");
+        op.conv = static_cast<int>(pl->convs.size()) - 1;
+        op.in_buf = BUF_R0 + t; op.out_buf = BUF_R0 + y; op.res_buf = res >= 0 ? BUF_R0 + res : -1; op.relu = 1;
+        if (fused_ds >= 0) {
+          pl->convs.back().ds_conv = fused_ds;
+          op.ds_buf = BUF_R0 + cur;
+        }
         pl->ops.push_back(op);
       }
       cur = y;
@@ -199,7 +214,8 @@ static void build_graph(pb200_plan* pl) {
   // weight arena
   size_t woff = 0;
   for (auto& c : pl->convs) {
-    const size_t K = c.stem ? kStemK : static_cast<size_t>(c.R) * c.R * c.Cin;
+    const size_t K = (c.stem ? kStemK : static_cast<size_t>(c.R) * c.R * c.Cin) +
+                     (c.ds_conv >= 0 ? static_cast<size_t>(pl->convs[c.ds_conv].Cin) : 0);
     c.w_bytes = K * c.Cout * e;
     c.w_off = woff;
     woff = align_up(woff + c.w_bytes, 1024);
@@ -333,6 +349,7 @@ extern "C" int pb200_plan_load_weights(pb200_plan* plan, const float* const* ten
     if (int rc = need(bp + ".running_var", {c.Cout}, &var)) return rc;
     float* bias = reinterpret_cast<float*>(host.data() + c.b_off);
     const int K = c.stem ? kStemK : c.R * c.R * c.Cin;
+    const int Krow = K + (c.ds_conv >= 0 ? plan->convs[c.ds_conv].Cin : 0);  // K-major row length incl. a fused projection
     for (int co = 0; co < c.Cout; ++co) {
       // eval-mode BatchNorm2d, eps = 1e-5: y = (x - mean) / sqrt(var + eps) * gamma + beta
       const double sc = static_cast<double>(g->data[co]) / sqrt(static_cast<double>(var->data[co]) + 1e-5);
@@ -359,7 +376,7 @@ extern "C" int pb200_plan_load_weights(pb200_plan* plan, const float* const* ten
               row[k] = hi;
               row[K + k] = f32_to_bf16_rne(wf - hf);
             } else if (plan->bf16) {
-              size_t off = (static_cast<size_t>(co) * K + k) * 2;  // [Cout][K] K-major rows (TMA-im2col kernels)
+              size_t off = (static_cast<size_t>(co) * Krow + k) * 2;  // [Cout][K] K-major rows (TMA-im2col kernels)
               if (c.stem) off = stem_wimg_offset(co, k);
               else if (c.p8) off = conv_p8_wimg_offset(co, k);
               *reinterpret_cast<uint16_t*>(host.data() + c.w_off + off) = f32_to_bf16_rne(static_cast<float>(v));
@@ -368,6 +385,29 @@ extern "C" int pb200_plan_load_weights(pb200_plan* plan, const float* const* ten
                   static_cast<float>(v);
             }
           }
+    }
+  }
+  // fused projections: the downsample's folded weights become columns [R*R*Cin, +Cin_ds) of conv2's rows, its folded
+  // shift is added to conv2's (out = conv2(y1) + b2 + ds(x) + b_ds, resnet.py:99-103)
+  for (const auto& c : plan->convs) {
+    if (c.ds_conv < 0) continue;
+    const ConvSpec& d = plan->convs[c.ds_conv];
+    const HostTensor *w, *g, *b, *mu, *var;
+    const std::string bp = "resnet." + d.bn;
+    if (int rc = need("resnet." + d.name + ".weight", {d.Cout, d.Cin, 1, 1}, &w)) return rc;
+    if (int rc = need(bp + ".weight", {d.Cout}, &g)) return rc;
+    if (int rc = need(bp + ".bias", {d.Cout}, &b)) return rc;
+    if (int rc = need(bp + ".running_mean", {d.Cout}, &mu)) return rc;
+    if (int rc = need(bp + ".running_var", {d.Cout}, &var)) return rc;
+    const int K = c.R * c.R * c.Cin, Krow = K + d.Cin;
+    float* bias = reinterpret_cast<float*>(host.data() + c.b_off);
+    for (int co = 0; co < c.Cout; ++co) {
+      const double sc = static_cast<double>(g->data[co]) / sqrt(static_cast<double>(var->data[co]) + 1e-5);
+      bias[co] = static_cast<float>(static_cast<double>(bias[co]) + static_cast<double>(b->data[co]) -
+                                    static_cast<double>(mu->data[co]) * sc);
+      uint16_t* row = reinterpret_cast<uint16_t*>(host.data() + c.w_off) + static_cast<size_t>(co) * Krow + K;
+      for (int ci = 0; ci < d.Cin; ++ci)
+        row[ci] = f32_to_bf16_rne(static_cast<float>(static_cast<double>(w->data[static_cast<size_t>(co) * d.Cin + ci]) * sc));
     }
   }
   const HostTensor *fw, *fb;
@@ -428,8 +468,11 @@ static int prepare(pb200_plan* pl, const void* frames, void* ws, int B) {
     void* out = buf_ptr(pl, frames, ws, op.out_buf);
     const void* res = op.res_buf >= 0 ? buf_ptr(pl, frames, ws, op.res_buf) : nullptr;
     const float* bias = reinterpret_cast<const float*>(pl->arena + c.b_off);
+    const void* ds_in = op.ds_buf >= 0 ? buf_ptr(pl, frames, ws, op.ds_buf) : nullptr;
+    const ConvSpec* d = c.ds_conv >= 0 ? &pl->convs[c.ds_conv] : nullptr;
     int rc = build_umma_conv(L, in, B, c.Hin, c.Win, c.Cin, pl->arena + c.w_off, bias, res, out, c.Cout,
-                             c.R, c.stride, c.pad, op.relu, choose_block_n(c, B), 0, pl->split ? 1 : 0);
+                             c.R, c.stride, c.pad, op.relu, choose_block_n(c, B), 0, pl->split ? 1 : 0,
+                             d != nullptr ? ds_in : nullptr, d ? d->Hin : 0, d ? d->Win : 0, d ? d->Cin : 0);
     if (rc) {
       pl->cache_B = -1;
       return rc;
@@ -574,11 +617,12 @@ extern "C" int pb200_plan_op_work(const pb200_plan* plan, int i, int B, double* 
   } else if (op.kind == OP_CONV || op.kind == OP_CONV_P8) {
     const ConvSpec& c = plan->convs[op.conv];
     const double M = static_cast<double>(B) * c.Ho * c.Wo;
-    *flops = 2.0 * M * c.Cout * c.R * c.R * c.Cin;
+    const double ds_cin = c.ds_conv >= 0 ? plan->convs[c.ds_conv].Cin : 0.0;  // fused projection: K-extension
+    *flops = 2.0 * M * c.Cout * (c.R * c.R * c.Cin + ds_cin);
     const double in_el = c.stem ? static_cast<double>(B) * (plan->H + 6) * (plan->W + 8) * 4
                                 : static_cast<double>(B) * c.Hin * c.Win * c.Cin;
-    *bytes = e * (in_el + M * c.Cout * (op.res_buf >= 0 ? 2.0 : 1.0) +
-                  static_cast<double>(c.Cout) * c.R * c.R * c.Cin);
+    *bytes = e * (in_el + M * ds_cin + M * c.Cout * (op.res_buf >= 0 ? 2.0 : 1.0) +
+                  static_cast<double>(c.Cout) * (c.R * c.R * c.Cin + ds_cin));
   } else if (op.kind == OP_MAXPOOL) {
     const ConvSpec& c = plan->convs[0];
     *bytes = e * static_cast<double>(B) * c.Cout * (c.Ho * c.Wo + (c.Ho / 2) * (c.Wo / 2));
