@@ -29,10 +29,23 @@ int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
   } while (0)
 
 int require_device();  // PB200_OK if the current device is sm_100, else PB200_ERR_NO_DEVICE
+// Programmatic dependent launch (PDL): the kernels of the forward chain are launched with
+// cudaLaunchAttributeProgrammaticStreamSerialization so that the next kernel's CTAs are scheduled, and run their
+// prologue (barrier init, TMEM allocation, descriptor prefetch, resident-weight load), on SMs the previous kernel has
+// already left; each kernel executes griddepcontrol.wait before it touches anything the previous kernel produced.
+// PB200_NO_PDL=1 in the environment launches them fully serialised (A/B measurements).
+bool pdl_enabled();
+// fills attrs[0] (PDL, if enabled) and returns the attribute count; attrs must have room for 1 entry
+int pdl_launch_attrs(cudaLaunchAttribute* attrs);
 int num_sms();
 
 // ---- device-side PTX wrappers ------------------------------------------------------------
 #ifdef __CUDACC__
+
+// PDL: let the dependent grid start being scheduled / wait for the prerequisite grid's results (no-ops when the
+// kernel was launched without the programmatic-serialization attribute)
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));

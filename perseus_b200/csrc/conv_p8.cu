@@ -84,14 +84,16 @@ __global__ void __launch_bounds__(kThreads, 1) conv_p8_kernel(const ConvP8Params
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_slot;
+  pdl_launch_dependents();
 
   if (warp == 0) {
     // ================================ producer ====================================
     // the whole warp runs the loop (operands stay warp-uniform); one elected lane issues the copies
     if (elect_one()) {
       mbar_expect_tx(&w_bar, kWBytes);
-      bulk_load_1d(s_w, p.wimg, kWBytes, &w_bar);
+      bulk_load_1d(s_w, p.wimg, kWBytes, &w_bar);  // plan constant: fetched while the previous kernel drains (PDL)
     }
+    pdl_wait();  // the input patches are the previous kernel's output
     int stage = 0;
     uint32_t phase = 0;
     const uint32_t chunk_bytes = static_cast<uint32_t>(p.npos) * 16u;
@@ -153,6 +155,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_p8_kernel(const ConvP8Params
     }
   } else {
     // ================================ epilogue ====================================
+    pdl_wait();  // residual reads / output writes must follow the previous kernel (the output buffer may be its input)
     const int q = warp & 3;
     const int m = q * 32 + lane;
     const long long plane16 = p.plane_bytes / 16;
@@ -296,8 +299,15 @@ int launch_conv_p8(const void* in_p8, const void* wimg, const float* bias, const
   p.plane_bytes = static_cast<long long>(p8_plane_elems(H, W)) * 16;
   p.img_bytes = p.plane_bytes * 8;
   const int grid = p.num_tiles < num_sms() ? p.num_tiles : num_sms();
-  conv_p8_kernel<<<grid, kThreads, smem_bytes_for(Wp), st>>>(p);
-  PB_CUDA(cudaGetLastError());
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = smem_bytes_for(Wp);
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_launch_attrs(attr);
+  PB_CUDA(cudaLaunchKernelEx(&cfg, conv_p8_kernel, p));
   return PB200_OK;
 }
 

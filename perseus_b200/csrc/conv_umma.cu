@@ -78,6 +78,10 @@ conv_umma_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams
     tmem_alloc(&tmem_base_slot, Cfg::kTmemCols);
     tmem_relinquish();
   }
+  // PDL: everything above overlaps the previous kernel's tail; nothing below may run before it has completed (its
+  // output is this kernel's input; in the training step the bias / packed weights are written by earlier kernels too)
+  pdl_launch_dependents();
+  pdl_wait();
   for (int i = threadIdx.x; i < p.Cout; i += kUmmaThreads) s_bias[i] = __ldg(p.bias + i);
   tc_fence_before();
   __syncthreads();
@@ -529,13 +533,13 @@ static int launch_one(const UmmaConvLaunch& L, cudaStream_t st) {
   cfg.blockDim = dim3(kUmmaThreads);
   cfg.dynamicSmemBytes = UmmaCfg<BLOCK_N, 128>::kSmemBytes;
   cfg.stream = st;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = L.p.cl;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = 1 + pdl_launch_attrs(attr + 1);
   PB_CUDA(cudaLaunchKernelEx(&cfg, conv_umma_kernel<BLOCK_N, 128, SPLIT>, L.maps, L.p));
   return PB200_OK;
 }

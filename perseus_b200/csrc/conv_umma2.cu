@@ -69,6 +69,9 @@ conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParam
     tmem_alloc2(&tmem_base_slot, Cfg::kTmemCols);
     tmem_relinquish2();
   }
+  // PDL: the prologue above overlaps the previous kernel's tail; nothing below may run before it has completed
+  pdl_launch_dependents();
+  pdl_wait();
   for (int i = threadIdx.x; i < p.Cout; i += kPairThreads) s_bias[i] = __ldg(p.bias + i);
   tc_fence_before();
   __syncthreads();
@@ -265,7 +268,7 @@ conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParam
 // host side
 // ------------------------------------------------------------------------------------------
 template <int BLOCK_N>
-static int pair_cfg(cudaLaunchConfig_t* cfg, cudaLaunchAttribute* attr, int grid, cudaStream_t st) {
+static int pair_cfg(cudaLaunchConfig_t* cfg, cudaLaunchAttribute* attr, int grid, cudaStream_t st, bool pdl = false) {
   *cfg = cudaLaunchConfig_t{};
   cfg->gridDim = dim3(grid);
   cfg->blockDim = dim3(kPairThreads);
@@ -276,7 +279,7 @@ static int pair_cfg(cudaLaunchConfig_t* cfg, cudaLaunchAttribute* attr, int grid
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
   cfg->attrs = attr;
-  cfg->numAttrs = 1;
+  cfg->numAttrs = 1 + (pdl ? pdl_launch_attrs(attr + 1) : 0);
   return PB200_OK;
 }
 
@@ -310,15 +313,15 @@ int umma_pair_max_pairs(int block_n) { return g_max_pairs[block_n == 64 ? 0 : (b
 int launch_umma_pair(const UmmaConvLaunch& L, cudaStream_t st) {
   if (L.p.num_tiles == 0) return PB200_OK;
   cudaLaunchConfig_t cfg;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   if (L.block_n == 64) {
-    pair_cfg<64>(&cfg, attr, L.grid, st);
+    pair_cfg<64>(&cfg, attr, L.grid, st, true);
     PB_CUDA(cudaLaunchKernelEx(&cfg, conv_umma2_kernel<64>, L.maps, L.p));
   } else if (L.block_n == 128) {
-    pair_cfg<128>(&cfg, attr, L.grid, st);
+    pair_cfg<128>(&cfg, attr, L.grid, st, true);
     PB_CUDA(cudaLaunchKernelEx(&cfg, conv_umma2_kernel<128>, L.maps, L.p));
   } else {
-    pair_cfg<256>(&cfg, attr, L.grid, st);
+    pair_cfg<256>(&cfg, attr, L.grid, st, true);
     PB_CUDA(cudaLaunchKernelEx(&cfg, conv_umma2_kernel<256>, L.maps, L.p));
   }
   return PB200_OK;

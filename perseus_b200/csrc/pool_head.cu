@@ -155,6 +155,7 @@ head_kernel(const void* __restrict__ in, const float* __restrict__ fc_w,
             const float* __restrict__ fc_b, float* __restrict__ out_norm, float* __restrict__ out_px,
             int HW, int C, int n_out, float half_wm1, float half_hm1) {
   extern __shared__ float s_mean[];  // C floats
+  pdl_wait();  // launched with programmatic serialization: the last conv's output must be complete
   const int b = blockIdx.x;
   const float inv = 1.0f / static_cast<float>(HW);
   for (int c2 = threadIdx.x; c2 < C / 2; c2 += blockDim.x) {
@@ -209,13 +210,20 @@ int launch_head(const void* in, const float* fc_w, const float* fc_b, float* out
   PB_CHECK(C % 2 == 0, "head: odd channel count");
   const float hw = denorm_scale(imgW), hh = denorm_scale(imgH);
   const size_t smem = sizeof(float) * C;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(B);
+  cfg.blockDim = dim3(256);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_launch_attrs(attr);
   if (mode == 2)
-    head_kernel<2><<<B, 256, smem, st>>>(in, fc_w, fc_b, out_norm, out_px, HW, C, n_out, hw, hh);
+    PB_CUDA(cudaLaunchKernelEx(&cfg, head_kernel<2>, in, fc_w, fc_b, out_norm, out_px, HW, C, n_out, hw, hh));
   else if (mode == 1)
-    head_kernel<1><<<B, 256, smem, st>>>(in, fc_w, fc_b, out_norm, out_px, HW, C, n_out, hw, hh);
+    PB_CUDA(cudaLaunchKernelEx(&cfg, head_kernel<1>, in, fc_w, fc_b, out_norm, out_px, HW, C, n_out, hw, hh));
   else
-    head_kernel<0><<<B, 256, smem, st>>>(in, fc_w, fc_b, out_norm, out_px, HW, C, n_out, hw, hh);
-  PB_CUDA(cudaGetLastError());
+    PB_CUDA(cudaLaunchKernelEx(&cfg, head_kernel<0>, in, fc_w, fc_b, out_norm, out_px, HW, C, n_out, hw, hh));
   return PB200_OK;
 }
 

@@ -2,6 +2,8 @@
 #include <stdarg.h>
 #include <string.h>
 
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "tma_host.h"
 
@@ -48,6 +50,18 @@ int require_device() {
     return PB200_ERR_NO_DEVICE;
   }
   return PB200_OK;
+}
+
+bool pdl_enabled() {
+  static const bool on = getenv("PB200_NO_PDL") == nullptr;
+  return on;
+}
+
+int pdl_launch_attrs(cudaLaunchAttribute* attrs) {
+  if (!pdl_enabled()) return 0;
+  attrs[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attrs[0].val.programmaticStreamSerializationAllowed = 1;
+  return 1;
 }
 
 int num_sms() {

@@ -94,6 +94,8 @@ __global__ void __launch_bounds__(kThreads, 1) stem_pool_kernel(const StemPoolPa
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_slot;
+  pdl_launch_dependents();  // layer1's first kernel may start its prologue on SMs this grid has left
+  pdl_wait();               // the frames come from the ingest kernel (weights / bias above are plan constants)
 
   // Work decomposition shared by the three roles.  A unit = (image n, band of PB pooled rows).  It runs
   // `n_it` iterations; iteration k (k0 <= k < k0 + n_it) computes the conv-row pair (2k, 2k+1).  Pooled row k =
@@ -305,8 +307,15 @@ int launch_stem_pool(const void* frames, const void* wimg, const float* bias, vo
   p.frame_bytes = static_cast<long long>(H + 6) * kRowBytes;
   p.out_img_bytes = static_cast<long long>(p8_image_bytes(64, Hpool, 64));
   const int grid = p.num_units < num_sms() ? p.num_units : num_sms();
-  stem_pool_kernel<<<grid, kThreads, kSmemTotal, st>>>(p);
-  PB_CUDA(cudaGetLastError());
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = kSmemTotal;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_launch_attrs(attr);
+  PB_CUDA(cudaLaunchKernelEx(&cfg, stem_pool_kernel, p));
   return PB200_OK;
 }
 
