@@ -228,10 +228,33 @@ __global__ void __launch_bounds__(kThreads, 1) conv_p8_kernel(const ConvP8Params
       }
       load_residual(tile + gridDim.x);  // rv is dead from here on: prefetch the next tile's residual
       if (p.out_nhwc) {
-        if (valid) {
-          uint4* dst = reinterpret_cast<uint4*>(p.out) + ((static_cast<long long>(n) * p.H + h) * p.W + w) * 8;
+        // NHWC pixel = 8 chunks = one 128-byte line.  A lane holds the 8 chunks of ITS position; storing them directly
+        // makes every store instruction touch 32 different lines with 16 bytes each.  An 8x8 transpose inside each
+        // group of 8 lanes (3 butterfly stages of 16-byte shuffles) turns lane l into the owner of chunk l%8 of the
+        // group's 8 positions, so one instruction writes 4 complete lines.
+        const int l8 = lane & 7;
 #pragma unroll
-          for (int j = 0; j < 8; ++j) dst[j] = o[j];
+        for (int sft = 4; sft >= 1; sft >>= 1) {
+          const bool up = (l8 & sft) != 0;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            if (j & sft) continue;
+            const uint4 send = up ? o[j] : o[j | sft];
+            uint4 recv;
+            recv.x = __shfl_xor_sync(0xffffffffu, send.x, sft);
+            recv.y = __shfl_xor_sync(0xffffffffu, send.y, sft);
+            recv.z = __shfl_xor_sync(0xffffffffu, send.z, sft);
+            recv.w = __shfl_xor_sync(0xffffffffu, send.w, sft);
+            if (up) o[j] = recv;
+            else o[j | sft] = recv;
+          }
+        }
+        // pixel index of this lane's own position (-1: not an output); position 8g + j lives in lane 8g + j
+        const long long own = valid ? (static_cast<long long>(n) * p.H + h) * p.W + w : -1;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const long long pix = __shfl_sync(0xffffffffu, own, (lane & 24) + j);
+          if (pix >= 0) reinterpret_cast<uint4*>(p.out)[pix * 8 + l8] = o[j];
         }
       } else {
         uint4* oimg = reinterpret_cast<uint4*>(p.out + n * p.img_bytes);
