@@ -19,6 +19,7 @@
 #include "common.cuh"
 #include "conv_umma.cuh"
 #include "tma_host.h"
+#include "umma_epilogue.cuh"
 
 namespace pb200 {
 
@@ -292,6 +293,26 @@ conv_umma_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams
         continue;
       }
       uint4 rv[kVec];
+      if constexpr (kCols % 64 == 0) {
+        // line-granular path (umma_epilogue.cuh): residual and output move as complete 128-byte lines
+        const long long gm_group = static_cast<long long>(m_tile) * kTileM + q * 32;
+        if (has_res) {
+          load_residual_lines<kCols>(static_cast<const __nv_bfloat16*>(p.residual), gm_group, p.M_total, p.Cout, col0, lane, rv);
+        } else {
+#pragma unroll
+          for (int j = 0; j < kVec; ++j) rv[j] = make_uint4(0, 0, 0, 0);
+        }
+        mbar_wait(&tmem_full_bar[acc], acc_phase);
+        tc_fence_after();
+        const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BLOCK_N + half * kCols;
+        epilogue_lines<kCols>(t_addr, s_bias + col0, has_res, rv, static_cast<__nv_bfloat16*>(p.out), gm_group, p.M_total,
+                              p.Cout, col0, p.relu, lane, [&]() {
+                                tc_fence_before();
+                                __syncwarp();
+                                if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
+                              });
+        continue;
+      }
       if (has_res && valid) {
         const uint4* res = reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(p.residual) + gm * p.Cout + col0);
 #pragma unroll

@@ -1,0 +1,109 @@
+// Shared epilogue of the TMA-im2col tcgen05 convolutions (conv_umma.cu, conv_umma2.cu): TMEM accumulator ->
+// + bias (+ residual) -> ReLU -> bf16 NHWC, with every global access of a warp made of COMPLETE 128-byte lines.
+//
+// An epilogue thread owns one output pixel (TMEM lane) and kCols consecutive channels, i.e. kCols/8 16-byte chunks of
+// that pixel's NHWC row.  Loading / storing those chunks directly makes each instruction of a warp touch 32 different
+// lines with 16 bytes each (4x the L2 transactions, and the residual read fetches twice the sectors it uses).  Instead,
+// inside every group of 8 lanes the 8 chunks of a 64-channel group are transposed with 16-byte shuffles (3 butterfly
+// stages), so lane l of the group handles chunk l of the group's 8 pixels: one instruction = 4 complete lines.
+#pragma once
+#include "common.cuh"
+
+namespace pb200 {
+
+// In-place 8x8 transpose of 16-byte elements across the 8 lanes of a group: before, lane l holds o[j] = element (l, j);
+// after, o[j] = element (j, l).  An involution: the same call maps back.
+__device__ __forceinline__ void transpose8x8_u4(uint4 (&o)[8], int l8) {
+#pragma unroll
+  for (int sft = 4; sft >= 1; sft >>= 1) {
+    const bool up = (l8 & sft) != 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      if (j & sft) continue;
+      const uint4 send = up ? o[j] : o[j | sft];
+      uint4 recv;
+      recv.x = __shfl_xor_sync(0xffffffffu, send.x, sft);
+      recv.y = __shfl_xor_sync(0xffffffffu, send.y, sft);
+      recv.z = __shfl_xor_sync(0xffffffffu, send.z, sft);
+      recv.w = __shfl_xor_sync(0xffffffffu, send.w, sft);
+      if (up) o[j] = recv;
+      else o[j | sft] = recv;
+    }
+  }
+}
+
+// Residual rows of this thread's tile slice, fetched line by line and transposed back to pixel ownership:
+// rv[g * 8 + c] = chunk c of 64-channel group g of THIS lane's pixel.  gm_group = global pixel index of lane (lane & 24)
+// of the warp; rows >= M_total read as zero.
+template <int kCols>
+__device__ __forceinline__ void load_residual_lines(const __nv_bfloat16* __restrict__ residual, long long gm_group,
+                                                    long long M_total, int Cout, int col0, int lane,
+                                                    uint4 (&rv)[kCols / 8]) {
+  static_assert(kCols % 64 == 0, "line-granular epilogue needs 64-channel groups");
+  const int l8 = lane & 7;
+  const long long gbase = gm_group + (lane & 24);
+#pragma unroll
+  for (int g = 0; g < kCols / 64; ++g) {
+    uint4 t[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const long long gmj = gbase + j;
+      t[j] = gmj < M_total ? __ldg(reinterpret_cast<const uint4*>(residual + gmj * Cout + col0 + g * 64) + l8)
+                           : make_uint4(0, 0, 0, 0);
+    }
+    transpose8x8_u4(t, l8);
+#pragma unroll
+    for (int c = 0; c < 8; ++c) rv[g * 8 + c] = t[c];
+  }
+}
+
+// One tile slice: kCols accumulator columns of this thread's pixel.  `release()` is called once the accumulator has been
+// read completely (hands the TMEM stage back to the MMA warp).
+template <int kCols, typename Release>
+__device__ __forceinline__ void epilogue_lines(uint32_t t_addr, const float* __restrict__ bias, bool has_res,
+                                               const uint4 (&rv)[kCols / 8], __nv_bfloat16* __restrict__ out,
+                                               long long gm_group, long long M_total, int Cout, int col0, int relu,
+                                               int lane, Release release) {
+  static_assert(kCols % 64 == 0, "line-granular epilogue needs 64-channel groups");
+  const int l8 = lane & 7;
+  const long long gbase = gm_group + (lane & 24);
+#pragma unroll
+  for (int g = 0; g < kCols / 64; ++g) {
+    uint4 o[8];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int chunk = 2 * g + h;
+      uint32_t v[32];
+      tmem_ld_32x32(t_addr + chunk * 32, v);
+      tmem_ld_wait_regs(v);
+      if (chunk == kCols / 32 - 1) release();
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float f[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(v[8 * j + e]) + bias[chunk * 32 + 8 * j + e];
+        if (has_res) {
+          const uint4 r4 = rv[chunk * 4 + j];
+          f[0] += bf16_lo(r4.x); f[1] += bf16_hi(r4.x);
+          f[2] += bf16_lo(r4.y); f[3] += bf16_hi(r4.y);
+          f[4] += bf16_lo(r4.z); f[5] += bf16_hi(r4.z);
+          f[6] += bf16_lo(r4.w); f[7] += bf16_hi(r4.w);
+        }
+        if (relu) {
+#pragma unroll
+          for (int e = 0; e < 8; ++e) f[e] = fmaxf(f[e], 0.f);
+        }
+        o[h * 4 + j] = make_uint4(pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]), pack_bf16x2(f[4], f[5]),
+                                  pack_bf16x2(f[6], f[7]));
+      }
+    }
+    transpose8x8_u4(o, l8);  // o[j] = chunk l8 of the group's pixel j
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const long long gmj = gbase + j;
+      if (gmj < M_total) reinterpret_cast<uint4*>(out + gmj * Cout + col0 + g * 64)[l8] = o[j];
+    }
+  }
+}
+
+}  // namespace pb200
