@@ -204,10 +204,12 @@ int pb200_train_pack_weights(const float* w_oihw, int Cout, int Cin, int R, int 
  * {w fp32 OIHW ptr, forward operand ptr, data-gradient operand ptr or 0, Cout, Cin, R, first element index,
  *  kind (0 conv, 1 conv1 -> [64][256] im2col operand)}; total = sum of the element counts. */
 int pb200_train_pack_all(const int64_t* table_dev, int n, int64_t total, pb200_stream stream);
-/* convolution on NHWC bf16 with device-packed weights; out = [relu](conv + bias [+ residual]). */
+/* convolution on NHWC bf16 with device-packed weights; out = [relu](conv + bias [+ residual]).
+ * stats_or_null: double [2][Cout], ZEROED BY THE CALLER: the epilogue adds the per-channel sum and sum of squares of the
+ * bf16 outputs (the batch statistics pb200_train_bn_apply consumes) — no separate statistics pass over the tensor. */
 int pb200_train_conv(const void* in_nhwc, int B, int H, int W, int Cin, const void* wpacked, const float* bias,
                      int Cout, int R, int stride, int pad, const void* residual_or_null, int relu,
-                     void* out_nhwc, pb200_stream stream);
+                     void* out_nhwc, double* stats_or_null, pb200_stream stream);
 /* weight gradient: scratch[R*R][Cin][Cout] (fp32, zeroed by the caller) += x^T (*) dz over all pixels. */
 int pb200_train_wgrad(const void* x_nhwc, const void* dz_nhwc, int B, int H, int W, int Cin, int Cout, int R,
                       int stride, int pad, float* scratch, pb200_stream stream);

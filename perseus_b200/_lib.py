@@ -71,7 +71,7 @@ SIGNATURES = {
     "pb200_train_conv": (
         c_int,
         [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_int,
-         c_void_p, c_void_p],
+         c_void_p, c_void_p, c_void_p],
     ),
     "pb200_train_wgrad": (
         c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p]

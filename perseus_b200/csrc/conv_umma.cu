@@ -49,7 +49,8 @@ conv_umma_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams
   __shared__ __align__(8) uint64_t tmem_full_bar[2];
   __shared__ __align__(8) uint64_t tmem_empty_bar[2];
   __shared__ uint32_t tmem_base_slot;
-  __shared__ float s_bias[512];  // folded-BN shift of every output channel (Cout <= 512)
+  __shared__ float s_bias[512];
+  __shared__ float s_stat[2 * 512];  // training forward: per-CTA partial sum / sum of squares per output channel  // folded-BN shift of every output channel (Cout <= 512)
 
   const uint32_t raw_addr = smem_u32(smem_raw);
   const uint32_t tiles_addr = (raw_addr + 1023u) & ~1023u;
@@ -84,6 +85,8 @@ conv_umma_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams
   pdl_launch_dependents();
   pdl_wait();
   for (int i = threadIdx.x; i < p.Cout; i += kUmmaThreads) s_bias[i] = __ldg(p.bias + i);
+  if (p.stats != nullptr)
+    for (int i = threadIdx.x; i < 2 * p.Cout; i += kUmmaThreads) s_stat[i] = 0.f;
   tc_fence_before();
   __syncthreads();
   if (p.cl > 1) cluster_sync_all();  // peers' barriers are initialised before anyone multicasts into them
@@ -310,7 +313,7 @@ conv_umma_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams
                                 tc_fence_before();
                                 __syncwarp();
                                 if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
-                              });
+                              }, p.stats != nullptr ? s_stat : nullptr);
         continue;
       }
       if (has_res && valid) {
@@ -328,6 +331,7 @@ conv_umma_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams
       const float* bias = s_bias + col0;
 #pragma unroll
       for (int chunk = 0; chunk < kChunks; ++chunk) {
+        uint4 oc[4];
         uint32_t v[32];
         tmem_ld_32x32(t_addr + chunk * 32, v);
         tmem_ld_wait_regs(v);
@@ -352,16 +356,21 @@ conv_umma_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams
 #pragma unroll
             for (int e = 0; e < 8; ++e) f[e] = fmaxf(f[e], 0.f);
           }
-          if (valid)
-            out_row[chunk * 4 + j] = make_uint4(pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]),
-                                                pack_bf16x2(f[4], f[5]), pack_bf16x2(f[6], f[7]));
+          const uint4 ov = make_uint4(pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]), pack_bf16x2(f[4], f[5]),
+                                      pack_bf16x2(f[6], f[7]));
+          if (valid) out_row[chunk * 4 + j] = ov;
+          oc[j] = ov;
         }
+        if (p.stats != nullptr) accumulate_stats32(oc, valid, s_stat, p.Cout, col0 + chunk * 32, lane);
       }
     }
   }
 
   tc_fence_before();
   __syncthreads();
+  if (p.stats != nullptr)  // fused batch statistics: one fp64 atomic per channel and CTA
+    for (int i = threadIdx.x; i < 2 * p.Cout; i += kUmmaThreads)
+      if (s_stat[i] != 0.f) atomicAdd(&p.stats[i], static_cast<double>(s_stat[i]));
   if (cl > 1) cluster_sync_all();  // no CTA leaves while a peer may still multicast into it or signal its barriers
   if (warp == 1) {
     tc_fence_after();
@@ -431,7 +440,7 @@ static int max_active_clusters(int block_n, int cl) {
 int build_umma_conv(UmmaConvLaunch* L, const void* in, int B, int Hin, int Win, int Cin,
                     const void* wpacked, const float* bias, const void* residual, void* out, int Cout,
                     int R, int stride, int pad, int relu, int block_n, int cluster, int split, const void* ds_in,
-                    int ds_Hin, int ds_Win, int ds_Cin) {
+                    int ds_Hin, int ds_Win, int ds_Cin, double* stats) {
   PB_CHECK(stride == 1 || stride == 2, "umma conv: stride %d unsupported", stride);
   PB_CHECK(Cin % 64 == 0, "umma conv: Cin %d not a multiple of 64", Cin);
   PB_CHECK(block_n == 64 || block_n == 128 || block_n == 256, "umma conv: block_n %d", block_n);
@@ -471,6 +480,7 @@ int build_umma_conv(UmmaConvLaunch* L, const void* in, int B, int Hin, int Win, 
   p.cblocks = Cin / 64;
   p.num_kblocks = R * R * p.cblocks * (split ? 3 : 1);
   p.ds_cblocks = 0;
+  PB_CHECK(stats == nullptr || !split, "umma conv: fused statistics are not available in split mode");
   if (ds_in != nullptr) {
     PB_CHECK(!split && ds_Cin % 64 == 0 && ds_Hin == 2 * Ho && ds_Win == 2 * Wo,
              "umma conv: fused projection needs a bf16 [B][2Ho][2Wo][64k] input (got %dx%dx%d)", ds_Hin, ds_Win, ds_Cin);
@@ -488,6 +498,7 @@ int build_umma_conv(UmmaConvLaunch* L, const void* in, int B, int Hin, int Win, 
   p.bias = bias;
   p.residual = residual;
   p.out = out;
+  p.stats = stats;
   L->block_n = block_n;
   L->sw = 128;
   // cluster size: share the weight tile among up to 4 CTAs when there are enough M tiles to keep every SM busy

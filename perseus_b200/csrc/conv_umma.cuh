@@ -31,6 +31,7 @@ struct UmmaConvParams {
   const float* bias;            // [Cout] (folded BN shift)
   const void* residual;         // bf16 [M_total][Cout] or null
   void* out;                    // bf16 [M_total][Cout]
+  double* stats;                // training forward: [2][Cout] += per-channel sum / sum of squares of the bf16 outputs, or null
 };
 
 struct UmmaConvLaunch {
@@ -52,7 +53,8 @@ int build_umma_conv(UmmaConvLaunch* L, const void* in, int B, int Hin, int Win, 
                     int split = 0 /* 1: activations [hi|lo] (2*Cin channels), weights [Cout][hi K | lo K], out/residual [hi|lo] */,
                     // fused 1x1 stride-2 projection (resnet.py:240-243) of `ds_in` [B][ds_Hin][ds_Win][ds_Cin] accumulated into
                     // the same tile: the packed weight rows carry ds_Cin extra columns after R*R*Cin (K-extension)
-                    const void* ds_in = nullptr, int ds_Hin = 0, int ds_Win = 0, int ds_Cin = 0);
+                    const void* ds_in = nullptr, int ds_Hin = 0, int ds_Win = 0, int ds_Cin = 0,
+                    double* stats = nullptr /* fused batch statistics of the output (non-split) */);
 int launch_umma_conv(const UmmaConvLaunch& L, cudaStream_t st);  // dispatches on L.pair
 // conv_umma2.cu
 int umma_pair_init();

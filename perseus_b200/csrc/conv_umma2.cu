@@ -42,6 +42,7 @@ conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParam
   __shared__ __align__(8) uint64_t tmem_empty_bar[2];   // leader only: both CTAs' epilogues drained the stage
   __shared__ uint32_t tmem_base_slot;
   __shared__ float s_bias[512];
+  __shared__ float s_stat[2 * 512];  // training forward: per-CTA partial sum / sum of squares per output channel
 
   const uint32_t raw_addr = smem_u32(smem_raw);
   uint8_t* tiles = smem_raw + (((raw_addr + 1023u) & ~1023u) - raw_addr);
@@ -74,6 +75,8 @@ conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParam
   pdl_launch_dependents();
   pdl_wait();
   for (int i = threadIdx.x; i < p.Cout; i += kPairThreads) s_bias[i] = __ldg(p.bias + i);
+  if (p.stats != nullptr)
+    for (int i = threadIdx.x; i < 2 * p.Cout; i += kPairThreads) s_stat[i] = 0.f;
   tc_fence_before();
   __syncthreads();
   cluster_sync_all();
@@ -226,7 +229,7 @@ conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParam
                                   if (crank == 0) mbar_arrive(&tmem_empty_bar[acc]);
                                   else mbar_arrive_cluster(mapa_u32(&tmem_empty_bar[acc], 0));
                                 }
-                              });
+                              }, p.stats != nullptr ? s_stat : nullptr);
         continue;
       }
       if (has_res && valid) {
@@ -244,6 +247,7 @@ conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParam
       const float* bias = s_bias + col0;
 #pragma unroll
       for (int chunk = 0; chunk < kChunks; ++chunk) {
+        uint4 oc[4];
         uint32_t v[32];
         tmem_ld_32x32(t_addr + chunk * 32, v);
         tmem_ld_wait_regs(v);
@@ -271,16 +275,21 @@ conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParam
 #pragma unroll
             for (int e = 0; e < 8; ++e) f[e] = fmaxf(f[e], 0.f);
           }
-          if (valid)
-            out_row[chunk * 4 + j] = make_uint4(pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]),
-                                                pack_bf16x2(f[4], f[5]), pack_bf16x2(f[6], f[7]));
+          const uint4 ov = make_uint4(pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]), pack_bf16x2(f[4], f[5]),
+                                      pack_bf16x2(f[6], f[7]));
+          if (valid) out_row[chunk * 4 + j] = ov;
+          oc[j] = ov;
         }
+        if (p.stats != nullptr) accumulate_stats32(oc, valid, s_stat, p.Cout, col0 + chunk * 32, lane);
       }
     }
   }
 
   tc_fence_before();
   __syncthreads();
+  if (p.stats != nullptr)  // fused batch statistics: one fp64 atomic per channel and CTA
+    for (int i = threadIdx.x; i < 2 * p.Cout; i += kPairThreads)
+      if (s_stat[i] != 0.f) atomicAdd(&p.stats[i], static_cast<double>(s_stat[i]));
   cluster_sync_all();  // the peer's TMEM / barriers stay alive until the leader's last MMA and commit are done
   if (warp == 1) {
     tc_fence_after();

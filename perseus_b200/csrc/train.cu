@@ -76,7 +76,8 @@ extern "C" int pb200_train_pack_weights(const float* w_oihw, int Cout, int Cin, 
 
 extern "C" int pb200_train_conv(const void* in_nhwc, int B, int H, int W, int Cin, const void* wpacked,
                                 const float* bias, int Cout, int R, int stride, int pad,
-                                const void* residual_or_null, int relu, void* out_nhwc, pb200_stream stream) {
+                                const void* residual_or_null, int relu, void* out_nhwc, double* stats_or_null,
+                                pb200_stream stream) {
   if (int rc = require_device()) return rc;
   if (int rc = umma_conv_init()) return rc;
   PB_CHECK(in_nhwc && wpacked && bias && out_nhwc, "train_conv: null argument");
@@ -99,7 +100,7 @@ extern "C" int pb200_train_conv(const void* in_nhwc, int B, int H, int W, int Ci
     }
   }
   if (int rc = build_umma_conv(&L, in_nhwc, B, H, W, Cin, wpacked, bias, residual_or_null, out_nhwc, Cout, R, stride,
-                               pad, relu, bn))
+                               pad, relu, bn, 0, 0, nullptr, 0, 0, 0, stats_or_null))
     return rc;
   return launch_umma_conv(L, static_cast<cudaStream_t>(stream));
 }

@@ -32,6 +32,78 @@ __device__ __forceinline__ void transpose8x8_u4(uint4 (&o)[8], int l8) {
   }
 }
 
+// Column sums over the 32 lanes of a warp of N per-lane values (N = 32 or 64) by recursive halving: at each step a lane
+// hands half of its columns to its partner and adds the partner's contribution to the half it keeps (N - N/32 shuffles
+// instead of 5 N for a butterfly per column).  Afterwards a[0 .. N/32) hold the sums of columns col_of(lane) + i.
+template <int N>
+__device__ __forceinline__ void warp_column_sums(float (&a)[N], int lane) {
+#pragma unroll
+  for (int sft = 16, n = N / 2; sft >= 1; sft >>= 1, n >>= 1) {
+    const bool up = (lane & sft) != 0;
+#pragma unroll
+    for (int i = 0; i < N / 2; ++i) {
+      if (i < n) {
+        const float send = up ? a[i] : a[i + n];
+        const float recv = __shfl_xor_sync(0xffffffffu, send, sft);
+        a[i] = (up ? a[i + n] : a[i]) + recv;
+      }
+    }
+  }
+}
+template <int N>
+__device__ __forceinline__ int warp_column_of(int lane) {  // first column a lane owns after warp_column_sums<N>
+  int c = 0;
+#pragma unroll
+  for (int sft = 16, n = N / 2; sft >= 1; sft >>= 1, n >>= 1) c += (lane & sft) ? n : 0;
+  return c;
+}
+
+// Batch-statistics BatchNorm fused into the conv epilogue (training forward): per-channel sum and sum of squares of
+// the bf16-ROUNDED outputs (what the separate bn_stats pass used to read back) of one 8-chunk group of this warp's 32
+// pixels, added to the CTA's shared-memory accumulators s_stat[0..C) / s_stat[C..2C).
+__device__ __forceinline__ void accumulate_stats64(const uint4 (&o)[8], bool row_valid, float* s_stat, int C, int col,
+                                                   int lane) {
+#pragma unroll
+  for (int pass = 0; pass < 2; ++pass) {
+    float a[64];
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+      const uint32_t w[4] = {o[c].x, o[c].y, o[c].z, o[c].w};
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float lo = row_valid ? bf16_lo(w[e]) : 0.f, hi = row_valid ? bf16_hi(w[e]) : 0.f;
+        a[c * 8 + 2 * e] = pass ? lo * lo : lo;
+        a[c * 8 + 2 * e + 1] = pass ? hi * hi : hi;
+      }
+    }
+    warp_column_sums<64>(a, lane);
+    const int cc = col + warp_column_of<64>(lane);
+    atomicAdd(&s_stat[pass * C + cc], a[0]);
+    atomicAdd(&s_stat[pass * C + cc + 1], a[1]);
+  }
+}
+
+// the same for a 32-column slice (BLOCK_N = 64 kernels: 4 chunks per thread, one column per lane afterwards)
+__device__ __forceinline__ void accumulate_stats32(const uint4 (&o)[4], bool row_valid, float* s_stat, int C, int col,
+                                                   int lane) {
+#pragma unroll
+  for (int pass = 0; pass < 2; ++pass) {
+    float a[32];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      const uint32_t w[4] = {o[c].x, o[c].y, o[c].z, o[c].w};
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float lo = row_valid ? bf16_lo(w[e]) : 0.f, hi = row_valid ? bf16_hi(w[e]) : 0.f;
+        a[c * 8 + 2 * e] = pass ? lo * lo : lo;
+        a[c * 8 + 2 * e + 1] = pass ? hi * hi : hi;
+      }
+    }
+    warp_column_sums<32>(a, lane);
+    atomicAdd(&s_stat[pass * C + col + warp_column_of<32>(lane)], a[0]);
+  }
+}
+
 // Residual rows of this thread's tile slice, fetched line by line and transposed back to pixel ownership:
 // rv[g * 8 + c] = chunk c of 64-channel group g of THIS lane's pixel.  gm_group = global pixel index of lane (lane & 24)
 // of the warp; rows >= M_total read as zero.
@@ -63,7 +135,7 @@ template <int kCols, typename Release>
 __device__ __forceinline__ void epilogue_lines(uint32_t t_addr, const float* __restrict__ bias, bool has_res,
                                                const uint4 (&rv)[kCols / 8], __nv_bfloat16* __restrict__ out,
                                                long long gm_group, long long M_total, int Cout, int col0, int relu,
-                                               int lane, Release release) {
+                                               int lane, Release release, float* s_stat = nullptr) {
   static_assert(kCols % 64 == 0, "line-granular epilogue needs 64-channel groups");
   const int l8 = lane & 7;
   const long long gbase = gm_group + (lane & 24);
@@ -97,6 +169,7 @@ __device__ __forceinline__ void epilogue_lines(uint32_t t_addr, const float* __r
                                   pack_bf16x2(f[6], f[7]));
       }
     }
+    if (s_stat != nullptr) accumulate_stats64(o, gm_group + lane < M_total, s_stat, Cout, col0 + g * 64, lane);
     transpose8x8_u4(o, l8);  // o[j] = chunk l8 of the group's pixel j
 #pragma unroll
     for (int j = 0; j < 8; ++j) {

@@ -19,6 +19,8 @@ There is no autograd and no PyTorch fallback on this path; torch is used for mem
 """
 from __future__ import annotations
 
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -143,6 +145,9 @@ class NativeTrainer:
         self.dz0 = torch.empty(s.M * 64, **bf)
         self.scratch = torch.zeros(9 * 512 * 512, **f32)   # wgrad partial sums [R*R][Cin][Cout]
         self.sums = torch.zeros(2 * 512, dtype=torch.float64, device=dev)
+        # forward batch statistics, filled by the conv epilogues (two: a block's conv2 and its projection are in flight together)
+        self.fstats = [torch.zeros(2 * 512, dtype=torch.float64, device=dev) for _ in range(2)]
+        self.fused_stats = os.environ.get("PB200_NO_FUSED_STATS") is None
         self.sqnorm = torch.zeros(1, dtype=torch.float64, device=dev)
         self.zero_bias = torch.zeros(512, **f32)
         nk = 2 * self.model.n_keypoints
@@ -187,15 +192,21 @@ class NativeTrainer:
         self._prof = None
         return out
 
-    def _conv(self, x, B, H, W, Cin, w, Cout, R, stride, pad, out, residual=None, relu=0):
+    def _conv(self, x, B, H, W, Cin, w, Cout, R, stride, pad, out, residual=None, relu=0, stats=None):
+        """stats: double [2][Cout] that the conv epilogue fills with the batch statistics of `out` (zeroed here)"""
+        if stats is not None:
+            stats.zero_()
         _lib.check(self.lib.pb200_train_conv(x.data_ptr(), B, H, W, Cin, w.data_ptr(), self.zero_bias.data_ptr(), Cout, R,
-                                             stride, pad, _lib.ptr(residual), relu, out.data_ptr(), self._s()))
+                                             stride, pad, _lib.ptr(residual), relu, out.data_ptr(), _lib.ptr(stats), self._s()))
 
-    def _bn_forward(self, c, residual=None, relu=1):
+    def _bn_forward(self, c, residual=None, relu=1, stats=None):
+        """stats: the buffer the conv epilogue filled (fused statistics); None = a separate statistics pass over z"""
         bn = c.bn
-        _lib.check(self.lib.pb200_train_bn_stats(c.z.data_ptr(), c.M, c.Cout, self.sums.data_ptr(), self._s()))
+        if stats is None:
+            stats = self.sums
+            _lib.check(self.lib.pb200_train_bn_stats(c.z.data_ptr(), c.M, c.Cout, stats.data_ptr(), self._s()))
         _lib.check(self.lib.pb200_train_bn_apply(
-            c.z.data_ptr(), self.sums.data_ptr(), bn.weight.data_ptr(), bn.bias.data_ptr(), bn.running_mean.data_ptr(),
+            c.z.data_ptr(), stats.data_ptr(), bn.weight.data_ptr(), bn.bias.data_ptr(), bn.running_mean.data_ptr(),
             bn.running_var.data_ptr(), float(bn.momentum), float(bn.eps), c.mean.data_ptr(), c.invstd.data_ptr(),
             _lib.ptr(residual), relu, c.y.data_ptr(), c.M, c.Cout, self._s()))
         bn.num_batches_tracked += 1
@@ -228,7 +239,7 @@ class NativeTrainer:
         """gradient w.r.t. the conv input: stride-1 conv of dz (zero-stuffed for stride-2 layers) with the flipped filter"""
         _lib.check(self.lib.pb200_train_conv(dz_or_stuffed.data_ptr(), self.B, c.Hin, c.Win, c.Cout, c.w_dgrad.data_ptr(),
                                              self.zero_bias.data_ptr(), c.Cin, c.R, 1, c.R // 2, _lib.ptr(residual), 0,
-                                             out.data_ptr(), self._s()))
+                                             out.data_ptr(), None, self._s()))
 
     def _pack_weights(self):
         if self._pack_table is None:
@@ -252,21 +263,22 @@ class NativeTrainer:
         self._pack_weights()
         s = self.stem
         _lib.check(self.lib.pb200_train_stem_im2col(x.data_ptr(), B, m.num_channels, m.H, m.W, self.A.data_ptr(), self._s()))
-        self._conv(self.A, B, s.Ho, s.Wo, 256, s.w_fwd, 64, 1, 1, 0, s.z)
-        self._bn_forward(s, relu=1)
+        f0, f1 = (self.fstats if self.fused_stats else (None, None))
+        self._conv(self.A, B, s.Ho, s.Wo, 256, s.w_fwd, 64, 1, 1, 0, s.z, stats=f0)
+        self._bn_forward(s, relu=1, stats=f0)
         _lib.check(self.lib.pb200_train_maxpool(s.y.data_ptr(), self.pool.data_ptr(), self.pool_idx.data_ptr(), B, s.Ho, s.Wo,
                                                 64, self._s()))
         cur = self.pool
         for c1, c2, ds in self.blocks:
-            self._conv(cur, B, c1.Hin, c1.Win, c1.Cin, c1.w_fwd, c1.Cout, c1.R, c1.stride, c1.pad, c1.z)
-            self._bn_forward(c1, relu=1)
-            self._conv(c1.y, B, c2.Hin, c2.Win, c2.Cin, c2.w_fwd, c2.Cout, c2.R, 1, c2.pad, c2.z)
+            self._conv(cur, B, c1.Hin, c1.Win, c1.Cin, c1.w_fwd, c1.Cout, c1.R, c1.stride, c1.pad, c1.z, stats=f0)
+            self._bn_forward(c1, relu=1, stats=f0)
+            self._conv(c1.y, B, c2.Hin, c2.Win, c2.Cin, c2.w_fwd, c2.Cout, c2.R, 1, c2.pad, c2.z, stats=f0)
             idn = cur
             if ds is not None:
-                self._conv(cur, B, ds.Hin, ds.Win, ds.Cin, ds.w_fwd, ds.Cout, 1, ds.stride, 0, ds.z)
-                self._bn_forward(ds, relu=0)
+                self._conv(cur, B, ds.Hin, ds.Win, ds.Cin, ds.w_fwd, ds.Cout, 1, ds.stride, 0, ds.z, stats=f1)
+                self._bn_forward(ds, relu=0, stats=f1)
                 idn = ds.y
-            self._bn_forward(c2, residual=idn, relu=1)
+            self._bn_forward(c2, residual=idn, relu=1, stats=f0)
             c1.x_in = cur
             cur = c2.y
         last = self.blocks[-1][1]

@@ -83,7 +83,7 @@ def test_dgrad_stride1_is_a_conv_with_the_flipped_transposed_filter(case):
     dzd = dz.cuda()
     # dgrad: input channels = Cout, output channels = Cin
     L.check(L.lib().pb200_train_conv(dzd.data_ptr(), B, H, W, Cout, packed.data_ptr(), zero_bias.data_ptr(), Cin, R, 1, 1,
-                                     None, 0, out.data_ptr(), _stream()))
+                                     None, 0, out.data_ptr(), None, _stream()))
     torch.cuda.synchronize()
     got = out.double().cpu()
     assert torch.isfinite(got).all()
@@ -319,3 +319,43 @@ def test_graph_replayed_steps_match_eager_steps():
         worst = max(worst, d / (noise + 1e-7))
         assert d <= 3 * noise + 1e-4, (n, d, noise)
     print(f"[graph] worst graph-vs-eager / eager-vs-eager mean |dw| ratio {worst:.2f}")
+
+
+STAT_CASES = [
+    # B, H, W, Cin, Cout, R, stride   (Cout 64 -> BLOCK_N 64 path; big M -> CTA-pair kernel; ragged M tile)
+    (2, 64, 64, 64, 64, 3, 1),
+    (3, 16, 16, 128, 256, 3, 1),
+    (5, 8, 8, 512, 512, 3, 1),
+    (40, 32, 32, 128, 128, 3, 1),
+    (4, 32, 32, 64, 128, 1, 2),
+    (3, 8, 8, 256, 512, 3, 1),
+]
+
+
+@pytest.mark.parametrize("case", STAT_CASES, ids=[str(c) for c in STAT_CASES])
+def test_conv_epilogue_batch_statistics(case):
+    """pb200_train_conv's fused per-channel sum / sum of squares == the statistics of the bf16 tensor it wrote."""
+    L = _lib()
+    B, H, W, Cin, Cout, R, stride = case
+    g = torch.Generator().manual_seed(sum(case))
+    w = (torch.randn(Cout, Cin, R, R, generator=g) / (R * R * Cin) ** 0.5).cuda().contiguous()
+    x = torch.randn(B, H, W, Cin, generator=g).bfloat16().cuda()
+    packed = torch.empty(Cin * R * R * Cout, dtype=torch.bfloat16, device="cuda")
+    L.check(L.lib().pb200_train_pack_weights(w.data_ptr(), Cout, Cin, R, 0, packed.data_ptr(), _stream()))
+    zero_bias = torch.zeros(512, dtype=torch.float32, device="cuda")
+    Ho, Wo = (H + 2 * (R // 2) - R) // stride + 1, (W + 2 * (R // 2) - R) // stride + 1
+    out = torch.full((B, Ho, Wo, Cout), float("nan"), dtype=torch.bfloat16, device="cuda")
+    stats = torch.zeros(2 * Cout, dtype=torch.float64, device="cuda")
+    L.check(L.lib().pb200_train_conv(x.data_ptr(), B, H, W, Cin, packed.data_ptr(), zero_bias.data_ptr(), Cout, R, stride, R // 2,
+                                     None, 0, out.data_ptr(), stats.data_ptr(), _stream()))
+    torch.cuda.synchronize()
+    z = out.double().reshape(-1, Cout)
+    assert torch.isfinite(z).all()
+    want = torch.cat([z.sum(0), (z * z).sum(0)])
+    scale = torch.cat([z.abs().sum(0), (z * z).sum(0)]) + 1e-6
+    assert float(((stats - want).abs() / scale).max()) < 1e-5
+    # and the separate pass agrees with it
+    sums = torch.zeros(2 * Cout, dtype=torch.float64, device="cuda")
+    L.check(L.lib().pb200_train_bn_stats(out.data_ptr(), z.shape[0], Cout, sums.data_ptr(), _stream()))
+    torch.cuda.synchronize()
+    assert float(((stats - sums).abs() / scale).max()) < 1e-5
