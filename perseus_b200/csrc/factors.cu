@@ -19,9 +19,26 @@ __device__ __forceinline__ void copy_out(double* __restrict__ dst, const double*
   for (int i = threadIdx.x; i < n; i += blockDim.x) dst[i] = src[i];
 }
 
+// Stages one output block (N doubles per factor, held in registers) through the CTA's buffer and writes it out in
+// consecutive 8-byte words.
+template <int N, int M>
+__device__ __forceinline__ void stage_out(double* sm, double* __restrict__ dst, const double (&vals)[M], bool live, int cnt) {
+  static_assert(N <= M, "block larger than its register array");
+  __syncthreads();  // the previous contents (inputs / the last block) have been consumed
+  if (live) {
+#pragma unroll
+    for (int i = 0; i < N; ++i) sm[threadIdx.x * N + i] = vals[i];
+  }
+  __syncthreads();
+  copy_out(dst, sm, cnt * N);
+}
+
 // ---- dynamics -----------------------------------------------------------------------------
-// smem per block: inputs 30 doubles/factor, outputs 114 doubles/factor (padded strides are odd
-// multiples so that per-thread records do not collide on banks more than 2-way).
+// smem per block: ONE staging buffer of 36 doubles/factor (36.9 KB at 128 threads).  The 30 input doubles per factor
+// are staged in it first; the outputs (6 + 36 + 18 + 18 + 36 doubles per factor) are then staged and copied out one
+// block at a time while the rest waits in registers.  (Staging all 114 output doubles at once needed 147 KB per CTA:
+// one CTA = 4 warps per SM, and ncu showed the kernel latency-bound at 6 % occupancy; this form is register-limited
+// to 2 CTAs per SM.)
 template <bool JAC>
 __global__ void __launch_bounds__(kFacThreads)
 dynamics_kernel(const double* __restrict__ pose1, const double* __restrict__ angvel,
@@ -35,45 +52,29 @@ dynamics_kernel(const double* __restrict__ pose1, const double* __restrict__ ang
   double* s_p1 = sm;                       // 12 * T
   double* s_p2 = s_p1 + 12 * kFacThreads;  // 12 * T
   double* s_w = s_p2 + 12 * kFacThreads;   // 3 * T
-  double* s_v = s_w + 3 * kFacThreads;     // 3 * T
-  double* s_out = s_v + 3 * kFacThreads;   // JAC ? 114*T : 6*T
+  double* s_v = s_w + 3 * kFacThreads;     // 3 * T   (30 * T in all; the buffer holds 36 * T when JAC)
   copy_in(s_p1, pose1 + base * 12, cnt * 12);
   copy_in(s_p2, pose2 + base * 12, cnt * 12);
   copy_in(s_w, angvel + base * 3, cnt * 3);
   copy_in(s_v, vel + base * 3, cnt * 3);
   __syncthreads();
   const int t = threadIdx.x;
-  double* o_res = s_out;                                   // 6 * T
-  double* o_h0 = s_out + 6 * kFacThreads;                  // 36 * T
-  double* o_h1 = o_h0 + 36 * kFacThreads;                  // 18 * T
-  double* o_h2 = o_h1 + 18 * kFacThreads;                  // 18 * T
-  double* o_h3 = o_h2 + 18 * kFacThreads;                  // 36 * T
-  if (t < cnt) {
+  const bool live = t < cnt;
+  double r[6], h0[JAC ? 36 : 1], h1[JAC ? 18 : 1], h2[JAC ? 18 : 1], h3[JAC ? 36 : 1];
+  if (live) {
     const fm::Pose x1 = fm::load_pose12(s_p1 + t * 12);
     const fm::Pose x2 = fm::load_pose12(s_p2 + t * 12);
     const fm::V3 w = fm::v3(s_w[t * 3], s_w[t * 3 + 1], s_w[t * 3 + 2]);
     const fm::V3 v = fm::v3(s_v[t * 3], s_v[t * 3 + 1], s_v[t * 3 + 2]);
-    double r[6];
-    if (JAC) {
-      double h0[36], h1[18], h2[18], h3[36];
-      fm::dynamics_factor(x1, w, v, x2, dt, world_frame, 1, r, h0, h1, h2, h3);
-#pragma unroll
-      for (int i = 0; i < 36; ++i) { o_h0[t * 36 + i] = h0[i]; o_h3[t * 36 + i] = h3[i]; }
-#pragma unroll
-      for (int i = 0; i < 18; ++i) { o_h1[t * 18 + i] = h1[i]; o_h2[t * 18 + i] = h2[i]; }
-    } else {
-      fm::dynamics_factor(x1, w, v, x2, dt, world_frame, 0, r, nullptr, nullptr, nullptr, nullptr);
-    }
-#pragma unroll
-    for (int i = 0; i < 6; ++i) o_res[t * 6 + i] = r[i];
+    if (JAC) fm::dynamics_factor(x1, w, v, x2, dt, world_frame, 1, r, h0, h1, h2, h3);
+    else fm::dynamics_factor(x1, w, v, x2, dt, world_frame, 0, r, nullptr, nullptr, nullptr, nullptr);
   }
-  __syncthreads();
-  copy_out(resid + base * 6, o_res, cnt * 6);
-  if (JAC) {
-    copy_out(H0 + base * 36, o_h0, cnt * 36);
-    copy_out(H1 + base * 18, o_h1, cnt * 18);
-    copy_out(H2 + base * 18, o_h2, cnt * 18);
-    copy_out(H3 + base * 36, o_h3, cnt * 36);
+  stage_out<6>(sm, resid + base * 6, r, live, cnt);
+  if constexpr (JAC) {
+    stage_out<36>(sm, H0 + base * 36, h0, live, cnt);
+    stage_out<18>(sm, H1 + base * 18, h1, live, cnt);
+    stage_out<18>(sm, H2 + base * 18, h2, live, cnt);
+    stage_out<36>(sm, H3 + base * 36, h3, live, cnt);
   }
 }
 
@@ -164,7 +165,7 @@ extern "C" int pb200_factors_dynamics(const double* pose1, const double* ang_vel
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const unsigned grid = static_cast<unsigned>((N + kFacThreads - 1) / kFacThreads);
   if (jac) {
-    const size_t smem = sizeof(double) * kFacThreads * (30 + 114);
+    const size_t smem = sizeof(double) * kFacThreads * 36;
     static bool attr_set = false;
     if (!attr_set) {
       PB_CUDA(cudaFuncSetAttribute(dynamics_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -174,7 +175,7 @@ extern "C" int pb200_factors_dynamics(const double* pose1, const double* ang_vel
     dynamics_kernel<true><<<grid, kFacThreads, smem, st>>>(pose1, ang_vel1, vel1, pose2, dt,
                                                             world_frame, resid, H0, H1, H2, H3, N);
   } else {
-    const size_t smem = sizeof(double) * kFacThreads * (30 + 6);
+    const size_t smem = sizeof(double) * kFacThreads * 30;
     dynamics_kernel<false><<<grid, kFacThreads, smem, st>>>(
         pose1, ang_vel1, vel1, pose2, dt, world_frame, resid, nullptr, nullptr, nullptr, nullptr, N);
   }
