@@ -231,6 +231,40 @@ def measure_factors(dev, peaks, N=10_000, big=1_000_000):
         res[f"poses_{n}"] = {"ms": ms, "poses_per_s": n / (ms * 1e-3), "algorithmic_GBps": nbytes / (ms * 1e-3) / 1e9,
                              "hbm_frac": nbytes / (ms * 1e-3) / 1e9 / peaks["hbm_gbs"]}
     res["what"] = "per pose: 8 projection (resid + 2x6 J) + 1 dynamics (resid + 4 J blocks) + 1 const-vel factor, fp64"
+    # CPU baselines of the same work: (i) one factor per call, the way GTSAM drives the reference's
+    # Python callbacks (factors.py:54-61), on a bounded sample; (ii) the float64 restatement vectorised over all poses
+    from oracle import factors_oracle as fo
+
+    rng = np.random.default_rng(0)
+    n = N
+    R1, t1 = fo.pose_exp(rng.standard_normal((n, 6)) * np.array([0.5, 0.5, 0.5, 0.05, 0.05, 0.05]))
+    t1[:, 2] += 0.45
+    R2, t2 = fo.pose_exp(rng.standard_normal((n, 6)) * np.array([0.5, 0.5, 0.5, 0.05, 0.05, 0.05]))
+    wv, vv = rng.standard_normal((n, 3)), rng.standard_normal((n, 3))
+    K5n = np.array([221.7, 221.7, 0.0, 128.0, 128.0])
+    cn = np.array([[a, b, c] for a in (-1, 1) for b in (-1, 1) for c in (-1, 1)], dtype=np.float64) * 0.0175
+    mn = rng.uniform(0, 255, (n, 8, 2))
+
+    def cpu_all(sl):
+        fo.keypoint_projection_factor(R1[sl], t1[sl], K5n, mn[sl], cn)
+        fo.pose_dynamics_factor(R1[sl], t1[sl], wv[sl], vv[sl], R2[sl], t2[sl], 0.1, "world")
+        fo.constant_velocity_factor(vv[sl], wv[sl])
+
+    cpu_all(slice(0, 64))
+    t0 = time.perf_counter()
+    cpu_all(slice(0, n))
+    vec_s = time.perf_counter() - t0
+    m = 200
+    t0 = time.perf_counter()
+    for i in range(m):
+        cpu_all(slice(i, i + 1))
+    loop_s = time.perf_counter() - t0
+    res["cpu_baseline"] = {
+        "vectorised_poses_per_s": n / vec_s, "vectorised_ms_per_10k": vec_s * 1e3 * (10_000 / n),
+        "per_factor_loop_poses_per_s": m / loop_s, "per_factor_loop_s_per_10k_extrapolated": loop_s / m * 10_000,
+        "kind": "port", "cores": os.cpu_count(),
+        "sample": f"oracle/factors_oracle.py float64: all {n} poses vectorised (numpy); {m} poses one call per pose",
+    }
     return res
 
 

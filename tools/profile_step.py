@@ -1,5 +1,8 @@
-"""Minimal forward loop for ncu captures: python tools_profile_step.py [B] [steps] [C]."""
+"""Minimal forward loop for ncu captures: python tools/profile_step.py [B] [steps] [C]."""
+import os
 import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
 import torch
 
