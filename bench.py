@@ -107,6 +107,17 @@ class ClockSampler:
                 "samples": len(s)}
 
 
+def cpu_model() -> str:
+    try:
+        with open("/proc/cpuinfo") as fh:
+            for line in fh:
+                if line.lower().startswith("model name"):
+                    return line.split(":", 1)[1].strip()
+    except OSError:
+        pass
+    return "unknown"
+
+
 def cpu_reference_fps(frames: int, chunk: int, warmup_frames: int = 8):
     """The reference's PyTorch CPU path (oracle port: same torchvision module tree, fp32, no_grad,
     all host threads) on a bounded sample of the workload: u8 -> f32 ingest, forward, decode."""
@@ -475,7 +486,7 @@ def run_reference(args):
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": WORKLOAD, "note": "reference PyTorch CPU path (torchvision resnet18 module tree, "
                    f"fp32, no_grad); each step = a {chunk}-frame sample of the batch"},
-        "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": "port",
+        "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "cpu": cpu_model(), "kind": "port",
                          "sample": f"{done_steps} steps x {chunk} frames (u8->f32 ingest + forward + decode), fp32"},
         "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
@@ -596,6 +607,20 @@ def run_native(args):
 
     value = world * BATCH * args.steps / (ms * 1e-3)
     e2e = world * BATCH * args.steps / (ms_e2e * 1e-3)
+    strong = None
+    if world > 1 and BATCH % world == 0:
+        # strong scaling too — ONE 256-frame batch split over the N GPUs (256/N frames per rank)
+        bs = BATCH // world
+
+        def step_strong(i):
+            model.ingest(devbuf[i % NBUF][:bs], out=frames)
+            return model.forward_ingested(frames, bs)[1]
+
+        for i in range(5):
+            step_strong(i)
+        ms_s = timed(step_strong, args.steps)
+        strong = {"global_batch": BATCH, "per_gpu_batch": bs, "frames_per_s": BATCH * args.steps / (ms_s * 1e-3),
+                  "ms_per_step": ms_s / args.steps}
     training = measure_training(dev, rank, world) if not args.no_training else None
 
     line = None
@@ -667,9 +692,10 @@ def run_native(args):
             "latency": latency,
             "factors": factors,
             "other_modes": other,
+            "strong_scaling": strong,
             "training_step": training,
             "library_bar": library_bar,
-            "cpu_baseline": {"value": cpu_fps, "unit": "frames/s", "cores": cores, "kind": "port",
+            "cpu_baseline": {"value": cpu_fps, "unit": "frames/s", "cores": cores, "cpu": cpu_model(), "kind": "port",
                              "sample": f"256 frames in 32-frame batches, fp32, {cpu_dt:.1f} s (reference PyTorch "
                                        "CPU path: u8->f32 ingest + torchvision resnet18 forward + decode)"},
         }
