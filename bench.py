@@ -674,7 +674,8 @@ def run_native(args):
         factors = measure_factors(dev, peaks)
         other = measure_other_modes(dev, devbuf)
         library_bar = measure_library_bar(dev, devbuf)
-        cpu_fps, cores, cpu_dt = cpu_reference_fps(256, 32)
+        # cpu_baseline: rank 0 at N = 1 only (under torchrun the other ranks' processes and OMP_NUM_THREADS=1 distort it)
+        cpu_fps, cores, cpu_dt = cpu_reference_fps(256, 32) if world == 1 else (None, os.cpu_count() or 1, 0.0)
         launches_per_step = 1 + len(rows)
         line = {
             "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
@@ -695,7 +696,8 @@ def run_native(args):
             "strong_scaling": strong,
             "training_step": training,
             "library_bar": library_bar,
-            "cpu_baseline": {"value": cpu_fps, "unit": "frames/s", "cores": cores, "cpu": cpu_model(), "kind": "port",
+            "cpu_baseline": None if cpu_fps is None else {
+                             "value": cpu_fps, "unit": "frames/s", "cores": cores, "cpu": cpu_model(), "kind": "port",
                              "sample": f"256 frames in 32-frame batches, fp32, {cpu_dt:.1f} s (reference PyTorch "
                                        "CPU path: u8->f32 ingest + torchvision resnet18 forward + decode)"},
         }
