@@ -146,6 +146,11 @@ int pb200_debug_conv_bf16(const void* in_nhwc, int B, int H, int W, int Cin, con
 
 /* Same for the split-bf16 ("bf16x3") mode: activations, residual and output are NHWC bf16 with 2*C
  * channels per pixel, [hi(C) | lo(C)], value = hi + lo. */
+/* Unit-test entry of the fused projection (K-extension): out = [relu](conv3x3/1(in) + bias +
+ * conv1x1/2(ds_in)) with ds_in bf16 [B][2H][2W][ds_Cin]; wds_oi_host fp32 [Cout][ds_Cin]; HOST weights. */
+int pb200_debug_conv_ds_bf16(const void* in_nhwc, int B, int H, int W, int Cin, const float* w_oihw_host,
+                             const float* bias_host, int Cout, const void* ds_in_nhwc, int ds_Cin,
+                             const float* wds_oi_host, int relu, void* out_nhwc, pb200_stream stream);
 int pb200_debug_conv_split(const void* in_nhwc2, int B, int H, int W, int Cin, const float* w_oihw_host,
                            const float* bias_host, int Cout, int R, int stride, int pad,
                            const void* residual_nhwc2_or_null, int relu, void* out_nhwc2,

@@ -57,6 +57,10 @@ SIGNATURES = {
         [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_int,
          c_void_p, c_void_p],
     ),
+    "pb200_debug_conv_ds_bf16": (
+        c_int,
+        [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p],
+    ),
     "pb200_debug_conv_split": (
         c_int,
         [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_int,

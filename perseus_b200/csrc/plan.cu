@@ -739,6 +739,45 @@ extern "C" int pb200_debug_conv_bf16(const void* in_nhwc, int B, int H, int W, i
   return rc;
 }
 
+extern "C" int pb200_debug_conv_ds_bf16(const void* in_nhwc, int B, int H, int W, int Cin, const float* w_oihw_host,
+                                        const float* bias_host, int Cout, const void* ds_in_nhwc, int ds_Cin,
+                                        const float* wds_oi_host, int relu, void* out_nhwc, pb200_stream stream) {
+  if (int rc = require_device()) return rc;
+  if (int rc = umma_conv_init()) return rc;
+  PB_CHECK(in_nhwc && w_oihw_host && bias_host && ds_in_nhwc && wds_oi_host && out_nhwc, "debug_conv_ds: null argument");
+  const int R = 3;
+  const size_t K = static_cast<size_t>(R) * R * Cin, Krow = K + ds_Cin;  // K-extension: [taps x Cin | ds_Cin]
+  std::vector<uint16_t> wp(Krow * Cout);
+  for (int co = 0; co < Cout; ++co) {
+    for (int ci = 0; ci < Cin; ++ci)
+      for (int r = 0; r < R; ++r)
+        for (int s = 0; s < R; ++s)
+          wp[co * Krow + (static_cast<size_t>(r) * R + s) * Cin + ci] =
+              f32_to_bf16_rne(w_oihw_host[((static_cast<size_t>(co) * Cin + ci) * R + r) * R + s]);
+    for (int ci = 0; ci < ds_Cin; ++ci) wp[co * Krow + K + ci] = f32_to_bf16_rne(wds_oi_host[static_cast<size_t>(co) * ds_Cin + ci]);
+  }
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  void *dw = nullptr, *db = nullptr;
+  PB_CUDA(cudaMalloc(&dw, wp.size() * 2));
+  PB_CUDA(cudaMalloc(&db, sizeof(float) * Cout));
+  int rc = PB200_OK;
+  if (cudaMemcpyAsync(dw, wp.data(), wp.size() * 2, cudaMemcpyHostToDevice, st) != cudaSuccess ||
+      cudaMemcpyAsync(db, bias_host, sizeof(float) * Cout, cudaMemcpyHostToDevice, st) != cudaSuccess)
+    rc = PB200_ERR_CUDA;
+  UmmaConvLaunch L;
+  if (rc == PB200_OK) {
+    int bn = Cout < 256 ? Cout : 256;
+    rc = build_umma_conv(&L, in_nhwc, B, H, W, Cin, dw, static_cast<const float*>(db), nullptr, out_nhwc, Cout, R, 1, 1,
+                         relu, bn, 0, 0, ds_in_nhwc, 2 * H, 2 * W, ds_Cin);
+  }
+  if (rc == PB200_OK) rc = launch_umma_conv(L, st);
+  cudaError_t e = cudaStreamSynchronize(st);
+  if (rc == PB200_OK && e != cudaSuccess) rc = cuda_fail(e, "debug_conv_ds sync", __FILE__, __LINE__);
+  cudaFree(dw);
+  cudaFree(db);
+  return rc;
+}
+
 extern "C" int pb200_debug_conv_split(const void* in_nhwc2, int B, int H, int W, int Cin,
                                       const float* w_oihw_host, const float* bias_host, int Cout, int R,
                                       int stride, int pad, const void* residual_nhwc2_or_null, int relu,

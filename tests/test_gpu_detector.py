@@ -135,6 +135,44 @@ def test_umma_conv_layer_vs_exact_operand_reference(case, cluster, monkeypatch):
     assert not bad.any(), f"{int(bad.sum())} / {bad.numel()} outputs off; max err {float(err.max()):.4f}; first bad idx {bad.nonzero()[:4].tolist()}"
 
 
+DS_CASES = [
+    # (B, H, W, Cin = Cout, ds_Cin): conv2 of layer2.0 / layer3.0 / layer4.0 with the block's 1x1/2 projection fused in
+    (3, 32, 32, 128, 64),
+    (2, 16, 16, 256, 128),
+    (3, 8, 8, 512, 256),
+]
+
+
+@pytest.mark.parametrize("cluster", ["1", "p"])
+@pytest.mark.parametrize("case", DS_CASES, ids=[str(c) for c in DS_CASES])
+def test_umma_conv_with_fused_projection_vs_exact_operand_reference(case, cluster, monkeypatch):
+    """conv3x3(y1) + conv1x1/2(x) accumulated in ONE TMEM tile (extra K columns through the parity-(0,0) map) vs the two
+    F.conv2d in fp64 on the same bf16 operands: the projection is never rounded, so the only error is the final rounding."""
+    from perseus_b200 import _lib
+
+    monkeypatch.setenv("PB200_FORCE_CLUSTER", cluster)
+    B, H, W, C, Cds = case
+    g = torch.Generator().manual_seed(sum(case))
+    y1 = torch.randn(B, H, W, C, generator=g).bfloat16()
+    x = torch.randn(B, 2 * H, 2 * W, Cds, generator=g).bfloat16()
+    w = (torch.randn(C, C, 3, 3, generator=g) / (9 * C) ** 0.5).bfloat16().float()
+    wds = (torch.randn(C, Cds, generator=g) / Cds ** 0.5).bfloat16().float()
+    bias = torch.randn(C, generator=g)
+    want = torch.nn.functional.conv2d(y1.double().permute(0, 3, 1, 2), w.double(), bias.double(), 1, 1)
+    want = want + torch.nn.functional.conv2d(x.double().permute(0, 3, 1, 2), wds.double()[:, :, None, None], None, 2, 0)
+    want = want.permute(0, 2, 3, 1).relu()
+    out = torch.full((B, H, W, C), float("nan"), dtype=torch.bfloat16, device="cuda")
+    y1d, xd = y1.cuda(), x.cuda()
+    _lib.check(_lib.lib().pb200_debug_conv_ds_bf16(y1d.data_ptr(), B, H, W, C, w.contiguous().data_ptr(), bias.data_ptr(), C,
+                                                   xd.data_ptr(), Cds, wds.contiguous().data_ptr(), 1, out.data_ptr(),
+                                                   _lib.current_stream_ptr()))
+    torch.cuda.synchronize()
+    got = out.double().cpu()
+    assert torch.isfinite(got).all(), "unwritten (NaN) outputs"
+    err = (got - want).abs()
+    bad = err > 2.0 ** -7 * want.abs() + 1e-2
+    assert not bad.any(), f"{int(bad.sum())} / {bad.numel()} outputs off; max err {float(err.max()):.4f}"
+
 
 def _split(t: torch.Tensor):
     hi = t.float().bfloat16()
