@@ -215,6 +215,14 @@ int pb200_train_pack_all(const int64_t* table_dev, int n, int64_t total, pb200_s
 int pb200_train_conv(const void* in_nhwc, int B, int H, int W, int Cin, const void* wpacked, const float* bias,
                      int Cout, int R, int stride, int pad, const void* residual_or_null, int relu,
                      void* out_nhwc, double* stats_or_null, pb200_stream stream);
+/* data gradient of a STRIDE-2 convolution (3x3 pad 1 or 1x1 pad 0) without zero-stuffing: one small stride-1 convolution
+ * of dz per output parity (2a+ph, 2b+pw) with the 1 / 2 / 2 / 4 filter taps that reach it (1 / 0 / 0 / 0 for 1x1), written
+ * straight to the strided pixels.  dz bf16 [B][Ho][Wo][Cout]; w_dgrad_packed = pack mode 1 of the layer; dx bf16
+ * [B][2Ho][2Wo][Cin]; residual00 (same shape as dx) is added at the parity-(0,0) pixels only — the block's 1x1/2 projection
+ * gradient, which exists only there.  A 1x1 layer writes ONLY the parity-(0,0) pixels of dx. */
+int pb200_train_dgrad_s2(const void* dz_nhwc, int B, int Ho, int Wo, int Cout, const void* w_dgrad_packed,
+                         const float* zero_bias, int Cin, int R, const void* residual00_or_null, void* dx_nhwc,
+                         pb200_stream stream);
 /* weight gradient: scratch[R*R][Cin][Cout] (fp32, zeroed by the caller) += x^T (*) dz over all pixels. */
 int pb200_train_wgrad(const void* x_nhwc, const void* dz_nhwc, int B, int H, int W, int Cin, int Cout, int R,
                       int stride, int pad, float* scratch, pb200_stream stream);

@@ -77,6 +77,9 @@ SIGNATURES = {
         [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_int,
          c_void_p, c_void_p, c_void_p],
     ),
+    "pb200_train_dgrad_s2": (
+        c_int, [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p]
+    ),
     "pb200_train_wgrad": (
         c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p]
     ),

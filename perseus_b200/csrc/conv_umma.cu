@@ -123,19 +123,12 @@ conv_umma_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams
         ho0 = 0;
       }
       // the issue loop is kept as light as possible: one warp must feed a k-block every 128-512 MMA cycles
-      const int taps = p.S * p.S;
       int kcol = 0;
-      for (int tap = 0; tap < taps; ++tap) {
-        const int r = tap / p.S, s = tap - r * p.S;
-        int dh = r - p.pad, dw = s - p.pad, mi = 0;
-        if (p.stride == 2) {
-          const int hp = dh & 1, wp = dw & 1;
-          dh = (dh - hp) >> 1;
-          dw = (dw - wp) >> 1;
-          mi = hp * 2 + wp;
-        }
-        const CUtensorMap* amap = &maps.a[mi];
-        const int hrow = ho0 + dh;
+      for (int tap = 0; tap < p.ntaps; ++tap) {
+        const int dw = p.tap_dw[tap];
+        const CUtensorMap* amap = &maps.a[p.tap_mi[tap]];
+        const int hrow = ho0 + p.tap_dh[tap];
+        kcol = p.tap_k[tap];
         for (int cb = 0; cb < p.cblocks; ++cb, kcol += Cfg::kBlockK) {
           // SPLIT ("bf16x3"): a = a_hi + a_lo (channels [0,Cin) and [Cin,2Cin) of the activation tensor),
           // w = w_hi + w_lo (columns [0,Ktot) and [Ktot,2Ktot) of the packed weights); three k-blocks per
@@ -232,6 +225,7 @@ conv_umma_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams
     const int q = warp & 3;  // TMEM lane quarter this warp may access
     const int half = (warp - 2) >> 2;
     const int row = q * 32 + lane;
+    const RowMap rmap = {p.up2, p.up_ph, p.up_pw, p.up_lh, p.up_lw};
     int it = 0;
     for (int st = cluster_id; st < p.num_super; st += num_clusters, ++it) {
       const int m_super = st / p.num_n_tiles;
@@ -300,7 +294,7 @@ conv_umma_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams
         // line-granular path (umma_epilogue.cuh): residual and output move as complete 128-byte lines
         const long long gm_group = static_cast<long long>(m_tile) * kTileM + q * 32;
         if (has_res) {
-          load_residual_lines<kCols>(static_cast<const __nv_bfloat16*>(p.residual), gm_group, p.M_total, p.Cout, col0, lane, rv);
+          load_residual_lines<kCols>(static_cast<const __nv_bfloat16*>(p.residual), gm_group, p.M_total, p.Cout, col0, lane, rv, rmap);
         } else {
 #pragma unroll
           for (int j = 0; j < kVec; ++j) rv[j] = make_uint4(0, 0, 0, 0);
@@ -313,11 +307,11 @@ conv_umma_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams
                                 tc_fence_before();
                                 __syncwarp();
                                 if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
-                              }, p.stats != nullptr ? s_stat : nullptr);
+                              }, p.stats != nullptr ? s_stat : nullptr, rmap);
         continue;
       }
       if (has_res && valid) {
-        const uint4* res = reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(p.residual) + gm * p.Cout + col0);
+        const uint4* res = reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(p.residual) + rmap(gm) * p.Cout + col0);
 #pragma unroll
         for (int j = 0; j < kVec; ++j) rv[j] = __ldg(res + j);
       } else {
@@ -327,7 +321,7 @@ conv_umma_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams
       mbar_wait(&tmem_full_bar[acc], acc_phase);
       tc_fence_after();
       const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BLOCK_N + half * kCols;
-      uint4* out_row = reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(p.out) + gm * p.Cout + col0);
+      uint4* out_row = reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(p.out) + rmap(gm) * p.Cout + col0);
       const float* bias = s_bias + col0;
 #pragma unroll
       for (int chunk = 0; chunk < kChunks; ++chunk) {
@@ -479,6 +473,22 @@ int build_umma_conv(UmmaConvLaunch* L, const void* in, int B, int Hin, int Win, 
   p.S = R;
   p.cblocks = Cin / 64;
   p.num_kblocks = R * R * p.cblocks * (split ? 3 : 1);
+  p.ntaps = R * R;
+  for (int t = 0; t < R * R; ++t) {
+    const int r = t / R, sx = t - r * R;
+    int dh = r - pad, dw = sx - pad, mi = 0;
+    if (stride == 2) {
+      const int hp = dh & 1, wp = dw & 1;
+      dh = (dh - hp) >> 1;
+      dw = (dw - wp) >> 1;
+      mi = hp * 2 + wp;
+    }
+    p.tap_dh[t] = dh;
+    p.tap_dw[t] = dw;
+    p.tap_mi[t] = mi;
+    p.tap_k[t] = t * Cin;
+  }
+  p.up2 = p.up_ph = p.up_pw = p.up_lh = p.up_lw = 0;
   p.ds_cblocks = 0;
   PB_CHECK(stats == nullptr || !split, "umma conv: fused statistics are not available in split mode");
   if (ds_in != nullptr) {
@@ -556,6 +566,50 @@ int build_umma_conv(UmmaConvLaunch* L, const void* in, int B, int Hin, int Win, 
   }
   return encode_weight_map(&L->maps.b, wpacked, Cout, (R * R * Cin + (ds_in != nullptr ? ds_Cin : 0)) * (split ? 2 : 1),
                            block_n / p.cl, 128);
+}
+
+int build_umma_dgrad_s2(UmmaConvLaunch* L, const void* dz, int B, int Ho, int Wo, int Cout_f, const void* w_dgrad,
+                        const float* zero_bias, const void* residual_or_null, void* dx, int Cin_f, int R, int ph, int pw,
+                        int block_n) {
+  PB_CHECK(R == 3 || R == 1, "dgrad_s2: R = %d (3x3 pad 1 or 1x1 pad 0)", R);
+  PB_CHECK(ph >= 0 && ph < 2 && pw >= 0 && pw < 2, "dgrad_s2: parity (%d, %d)", ph, pw);
+  PB_CHECK((Ho & (Ho - 1)) == 0 && (Wo & (Wo - 1)) == 0, "dgrad_s2: Ho x Wo = %d x %d must be powers of two", Ho, Wo);
+  // the tile grid is the LOW-resolution dz grid; A boxes come from dz at stride 1 (zero fill outside = the taps that
+  // fall off the bottom / right edge), B from the full data-gradient operand at the selected taps' k columns
+  if (int rc = build_umma_conv(L, dz, B, Ho, Wo, Cout_f, w_dgrad, zero_bias, residual_or_null, dx, Cin_f, R, 1, R / 2, 0,
+                               block_n))
+    return rc;
+  UmmaConvParams& p = L->p;
+  // forward: z[i] reads x[2i + r - pad].  For x row u = 2a + ph the forward taps are r = ph + pad (mod 2):
+  // R = 3: ph = 0 -> r = 1 (i = a); ph = 1 -> r = 0 (i = a + 1), r = 2 (i = a).  R = 1: ph = 0 -> r = 0 (i = a); ph = 1 -> none
+  int rr[2], ri[2], nr = 0, cc[2], ci[2], nc = 0;
+  if (R == 3) {
+    if (ph == 0) { rr[nr] = 1; ri[nr++] = 0; } else { rr[nr] = 0; ri[nr++] = 1; rr[nr] = 2; ri[nr++] = 0; }
+    if (pw == 0) { cc[nc] = 1; ci[nc++] = 0; } else { cc[nc] = 0; ci[nc++] = 1; cc[nc] = 2; ci[nc++] = 0; }
+  } else {
+    if (ph == 0) { rr[nr] = 0; ri[nr++] = 0; }
+    if (pw == 0) { cc[nc] = 0; ci[nc++] = 0; }
+  }
+  p.ntaps = 0;
+  for (int a = 0; a < nr; ++a)
+    for (int b = 0; b < nc; ++b) {
+      const int t = p.ntaps++;
+      p.tap_dh[t] = ri[a];
+      p.tap_dw[t] = ci[b];
+      p.tap_mi[t] = 0;
+      p.tap_k[t] = ((R - 1 - rr[a]) * R + (R - 1 - cc[b])) * Cout_f;  // pack mode 1 stores w[r][s] at tap (R-1-r, R-1-s)
+    }
+  p.num_kblocks = p.ntaps * p.cblocks;
+  if (p.ntaps == 0) p.num_tiles = 0;  // nothing to launch: this parity receives no gradient through the conv
+  p.up2 = 1;
+  p.up_ph = ph;
+  p.up_pw = pw;
+  p.up_lh = 0;
+  while ((1 << p.up_lh) < Ho) ++p.up_lh;
+  p.up_lw = 0;
+  while ((1 << p.up_lw) < Wo) ++p.up_lw;
+  L->flops = 2.0 * static_cast<double>(p.M_total) * Cin_f * p.ntaps * Cout_f;
+  return PB200_OK;
 }
 
 template <int BLOCK_N, bool SPLIT>

@@ -26,6 +26,14 @@ struct UmmaConvParams {
   int imgs_per_tile;  // 128/(Ho*Wo) when the image is smaller than a tile, else 1
   int bh;             // output rows per tile
   int stride, pad, S, cblocks;
+  // the filter taps the producers walk, in k order: offset of the tap's A box relative to the tile's first output pixel
+  // (in the tap's map: parity-split for stride 2), map index, first k column of the tap's weight block.  Filled by
+  // build_umma_conv for an R x R conv; a stride-2 data gradient installs the 1 / 2 / 2 / 4 taps of one output parity.
+  int ntaps;
+  int tap_dh[9], tap_dw[9], tap_mi[9], tap_k[9];
+  // output row mapping: up2 = 1 writes row gm = (n, a, b) of the Ho x Wo tile grid to pixel (2a + up_ph, 2b + up_pw) of a
+  // [B][2Ho][2Wo][Cout] tensor (and reads the residual there): one output parity of a stride-2 data gradient
+  int up2, up_ph, up_pw, up_lh, up_lw;  // up_lh / up_lw = log2(Ho), log2(Wo)
   int ds_cblocks;  // fused downsample: extra 64-channel k-blocks read through maps.ds after the R*S taps (0 = none)
   int relu;
   const float* bias;            // [Cout] (folded BN shift)
@@ -55,6 +63,13 @@ int build_umma_conv(UmmaConvLaunch* L, const void* in, int B, int Hin, int Win, 
                     // the same tile: the packed weight rows carry ds_Cin extra columns after R*R*Cin (K-extension)
                     const void* ds_in = nullptr, int ds_Hin = 0, int ds_Win = 0, int ds_Cin = 0,
                     double* stats = nullptr /* fused batch statistics of the output (non-split) */);
+// One output parity (ph, pw) of the data gradient of a stride-2 R x R (R = 3 pad 1, or R = 1 pad 0) convolution:
+// dx[2a+ph, 2b+pw] (+= residual there) = sum over the forward taps (r, s) of that parity of dz[a+di, b+dj] . w[r][s]^T.
+// dz: bf16 [B][Ho][Wo][Cout_f]; w_dgrad: the data-gradient operand [Cin_f][(R-1-r, R-1-s), Cout_f] (pack mode 1);
+// dx / residual: bf16 [B][2Ho][2Wo][Cin_f].  Returns PB200_OK with L->p.num_tiles = 0 when the parity has no tap.
+int build_umma_dgrad_s2(UmmaConvLaunch* L, const void* dz, int B, int Ho, int Wo, int Cout_f, const void* w_dgrad,
+                        const float* zero_bias, const void* residual_or_null, void* dx, int Cin_f, int R, int ph, int pw,
+                        int block_n);
 int launch_umma_conv(const UmmaConvLaunch& L, cudaStream_t st);  // dispatches on L.pair
 // conv_umma2.cu
 int umma_pair_init();

@@ -108,19 +108,12 @@ conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParam
       }
       // the issue loop is kept as light as possible: one warp must feed a k-block every 256-512 MMA cycles
       const int n_row = n_tile * BLOCK_N + crank * (BLOCK_N / 2);
-      const int taps = p.S * p.S;
       int kcol = 0;
-      for (int tap = 0; tap < taps; ++tap) {
-        const int r = tap / p.S, s = tap - r * p.S;
-        int dh = r - p.pad, dw = s - p.pad, mi = 0;
-        if (p.stride == 2) {
-          const int hp = dh & 1, wp = dw & 1;
-          dh = (dh - hp) >> 1;
-          dw = (dw - wp) >> 1;
-          mi = hp * 2 + wp;
-        }
-        const CUtensorMap* amap = &maps.a[mi];
-        const int hrow = ho0 + dh;
+      for (int tap = 0; tap < p.ntaps; ++tap) {
+        const int dw = p.tap_dw[tap];
+        const CUtensorMap* amap = &maps.a[p.tap_mi[tap]];
+        const int hrow = ho0 + p.tap_dh[tap];
+        kcol = p.tap_k[tap];
         for (int cb = 0; cb < p.cblocks; ++cb, kcol += 64) {
           if ((g++ & 1u) == static_cast<uint32_t>(pi)) {
           mbar_wait(&empty_bar[stage], phase ^ 1u);
@@ -198,6 +191,7 @@ conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParam
     const int q = warp & 3;
     const int half = (warp - 2) >> 2;
     const int row = q * 32 + lane;
+    const RowMap rmap = {p.up2, p.up_ph, p.up_pw, p.up_lh, p.up_lw};
     int it = 0;
     for (int st = pair_id; st < p.num_super; st += num_pairs, ++it) {
       const int m_super = st / p.num_n_tiles;
@@ -213,7 +207,7 @@ conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParam
         // line-granular path (umma_epilogue.cuh): residual and output move as complete 128-byte lines
         const long long gm_group = static_cast<long long>(m_tile) * 128 + q * 32;
         if (has_res) {
-          load_residual_lines<kCols>(static_cast<const __nv_bfloat16*>(p.residual), gm_group, p.M_total, p.Cout, col0, lane, rv);
+          load_residual_lines<kCols>(static_cast<const __nv_bfloat16*>(p.residual), gm_group, p.M_total, p.Cout, col0, lane, rv, rmap);
         } else {
 #pragma unroll
           for (int j = 0; j < kVec; ++j) rv[j] = make_uint4(0, 0, 0, 0);
@@ -229,11 +223,11 @@ conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParam
                                   if (crank == 0) mbar_arrive(&tmem_empty_bar[acc]);
                                   else mbar_arrive_cluster(mapa_u32(&tmem_empty_bar[acc], 0));
                                 }
-                              }, p.stats != nullptr ? s_stat : nullptr);
+                              }, p.stats != nullptr ? s_stat : nullptr, rmap);
         continue;
       }
       if (has_res && valid) {
-        const uint4* res = reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(p.residual) + gm * p.Cout + col0);
+        const uint4* res = reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(p.residual) + rmap(gm) * p.Cout + col0);
 #pragma unroll
         for (int j = 0; j < kVec; ++j) rv[j] = __ldg(res + j);
       } else {
@@ -243,7 +237,7 @@ conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParam
       mbar_wait(&tmem_full_bar[acc], (it >> 1) & 1u);
       tc_fence_after();
       const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BLOCK_N + half * kCols;
-      uint4* out_row = reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(p.out) + gm * p.Cout + col0);
+      uint4* out_row = reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(p.out) + rmap(gm) * p.Cout + col0);
       const float* bias = s_bias + col0;
 #pragma unroll
       for (int chunk = 0; chunk < kChunks; ++chunk) {

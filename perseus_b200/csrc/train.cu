@@ -105,6 +105,38 @@ extern "C" int pb200_train_conv(const void* in_nhwc, int B, int H, int W, int Ci
   return launch_umma_conv(L, static_cast<cudaStream_t>(stream));
 }
 
+extern "C" int pb200_train_dgrad_s2(const void* dz_nhwc, int B, int Ho, int Wo, int Cout, const void* w_dgrad_packed,
+                                    const float* zero_bias, int Cin, int R, const void* residual00_or_null,
+                                    void* dx_nhwc, pb200_stream stream) {
+  if (int rc = require_device()) return rc;
+  if (int rc = umma_conv_init()) return rc;
+  PB_CHECK(dz_nhwc && w_dgrad_packed && zero_bias && dx_nhwc, "train_dgrad_s2: null argument");
+  int bn = 64;
+  {
+    const long long m_tiles = (static_cast<long long>(B) * Ho * Wo + 127) / 128;
+    long long best_cost = -1;
+    for (int c = 64; c <= 256 && c <= Cin; c *= 2) {
+      if (Cin % c) continue;
+      const long long tiles = m_tiles * (Cin / c);
+      const long long rounds = (tiles + num_sms() - 1) / num_sms();
+      const long long cost = rounds * (c / 2 < 48 ? 48 : c / 2);
+      if (best_cost < 0 || cost <= best_cost) {
+        bn = c;
+        best_cost = cost;
+      }
+    }
+  }
+  for (int ph = 0; ph < 2; ++ph)
+    for (int pw = 0; pw < 2; ++pw) {
+      UmmaConvLaunch L;
+      const void* res = (ph == 0 && pw == 0) ? residual00_or_null : nullptr;
+      if (int rc = build_umma_dgrad_s2(&L, dz_nhwc, B, Ho, Wo, Cout, w_dgrad_packed, zero_bias, res, dx_nhwc, Cin, R, ph, pw, bn))
+        return rc;
+      if (int rc = launch_umma_conv(L, static_cast<cudaStream_t>(stream))) return rc;
+    }
+  return PB200_OK;
+}
+
 extern "C" int pb200_train_wgrad(const void* x_nhwc, const void* dz_nhwc, int B, int H, int W, int Cin, int Cout,
                                  int R, int stride, int pad, float* scratch, pb200_stream stream) {
   if (int rc = require_device()) return rc;

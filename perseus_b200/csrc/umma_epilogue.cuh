@@ -11,6 +11,19 @@
 
 namespace pb200 {
 
+// Output row -> pixel index of the output tensor.  Identity for a normal convolution; for one output parity of a
+// stride-2 data gradient (UmmaConvParams::up2) row (n, a, b) of the Ho x Wo tile grid is pixel (2a + ph, 2b + pw) of the
+// [B][2Ho][2Wo] tensor (Ho, Wo powers of two).
+struct RowMap {
+  int up2, ph, pw, lh, lw;
+  __device__ __forceinline__ long long operator()(long long gm) const {
+    if (!up2) return gm;
+    const long long n = gm >> (lh + lw);
+    const int a = static_cast<int>(gm >> lw) & ((1 << lh) - 1), b = static_cast<int>(gm) & ((1 << lw) - 1);
+    return (((n << (lh + 1)) + 2 * a + ph) << (lw + 1)) + 2 * b + pw;
+  }
+};
+
 // In-place 8x8 transpose of 16-byte elements across the 8 lanes of a group: before, lane l holds o[j] = element (l, j);
 // after, o[j] = element (j, l).  An involution: the same call maps back.
 __device__ __forceinline__ void transpose8x8_u4(uint4 (&o)[8], int l8) {
@@ -110,7 +123,7 @@ __device__ __forceinline__ void accumulate_stats32(const uint4 (&o)[4], bool row
 template <int kCols>
 __device__ __forceinline__ void load_residual_lines(const __nv_bfloat16* __restrict__ residual, long long gm_group,
                                                     long long M_total, int Cout, int col0, int lane,
-                                                    uint4 (&rv)[kCols / 8]) {
+                                                    uint4 (&rv)[kCols / 8], const RowMap rmap = RowMap{0, 0, 0, 0, 0}) {
   static_assert(kCols % 64 == 0, "line-granular epilogue needs 64-channel groups");
   const int l8 = lane & 7;
   const long long gbase = gm_group + (lane & 24);
@@ -120,7 +133,7 @@ __device__ __forceinline__ void load_residual_lines(const __nv_bfloat16* __restr
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       const long long gmj = gbase + j;
-      t[j] = gmj < M_total ? __ldg(reinterpret_cast<const uint4*>(residual + gmj * Cout + col0 + g * 64) + l8)
+      t[j] = gmj < M_total ? __ldg(reinterpret_cast<const uint4*>(residual + rmap(gmj) * Cout + col0 + g * 64) + l8)
                            : make_uint4(0, 0, 0, 0);
     }
     transpose8x8_u4(t, l8);
@@ -135,7 +148,8 @@ template <int kCols, typename Release>
 __device__ __forceinline__ void epilogue_lines(uint32_t t_addr, const float* __restrict__ bias, bool has_res,
                                                const uint4 (&rv)[kCols / 8], __nv_bfloat16* __restrict__ out,
                                                long long gm_group, long long M_total, int Cout, int col0, int relu,
-                                               int lane, Release release, float* s_stat = nullptr) {
+                                               int lane, Release release, float* s_stat = nullptr,
+                                               const RowMap rmap = RowMap{0, 0, 0, 0, 0}) {
   static_assert(kCols % 64 == 0, "line-granular epilogue needs 64-channel groups");
   const int l8 = lane & 7;
   const long long gbase = gm_group + (lane & 24);
@@ -174,7 +188,7 @@ __device__ __forceinline__ void epilogue_lines(uint32_t t_addr, const float* __r
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       const long long gmj = gbase + j;
-      if (gmj < M_total) reinterpret_cast<uint4*>(out + gmj * Cout + col0 + g * 64)[l8] = o[j];
+      if (gmj < M_total) reinterpret_cast<uint4*>(out + rmap(gmj) * Cout + col0 + g * 64)[l8] = o[j];
     }
   }
 }

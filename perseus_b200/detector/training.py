@@ -139,7 +139,10 @@ class NativeTrainer:
         self.dzd = torch.empty(act1, **bf)
         self.g_idn = torch.empty(act1, **bf)
         self.tmp = torch.empty(act1, **bf)
-        stuffed = max([4 * c.M * c.Cout for c in self.convs if c.stride == 2 and not c.stem] + [8])
+        # stride-2 data gradients: per-parity sub-convolutions (pb200_train_dgrad_s2); PB200_STUFFED_DGRAD=1 keeps the
+        # older zero-stuffed formulation (4x the MACs, two extra tensors) for A/B measurements
+        self.parity_dgrad = os.environ.get("PB200_STUFFED_DGRAD") is None
+        stuffed = 8 if self.parity_dgrad else max([4 * c.M * c.Cout for c in self.convs if c.stride == 2 and not c.stem] + [8])
         self.stuffed = [torch.empty(stuffed, **bf) for _ in range(2)]
         self.dy0 = torch.empty(s.M * 64, **bf)   # gradient w.r.t. the stem activation (after max-pool backward)
         self.dz0 = torch.empty(s.M * 64, **bf)
@@ -235,6 +238,13 @@ class NativeTrainer:
         _lib.check(self.lib.pb200_train_unpack_wgrad(self.scratch.data_ptr(), c.Cout, c.Cin, c.R, c.Cin,
                                                      self._g(c.conv.weight).data_ptr(), self._s()))
 
+    def _dgrad_s2(self, c, dz, out, residual00=None):
+        """gradient w.r.t. the input of a stride-2 conv: one small stride-1 conv of dz per output parity, written to the
+        strided pixels; a 1x1 layer only has the parity-(0,0) pixels (residual00 is added there)"""
+        _lib.check(self.lib.pb200_train_dgrad_s2(dz.data_ptr(), self.B, c.Ho, c.Wo, c.Cout, c.w_dgrad.data_ptr(),
+                                                 self.zero_bias.data_ptr(), c.Cin, c.R, _lib.ptr(residual00), out.data_ptr(),
+                                                 self._s()))
+
     def _dgrad(self, c, dz_or_stuffed, out, residual=None):
         """gradient w.r.t. the conv input: stride-1 conv of dz (zero-stuffed for stride-2 layers) with the flipped filter"""
         _lib.check(self.lib.pb200_train_conv(dz_or_stuffed.data_ptr(), self.B, c.Hin, c.Win, c.Cout, c.w_dgrad.data_ptr(),
@@ -307,9 +317,15 @@ class NativeTrainer:
             self._wgrad(c2, c1.y, self.dz)
             self._dgrad(c2, self.dz, self.dT)                      # gradient w.r.t. y1 (before its ReLU mask)
             st = c1.stride == 2
-            self._bn_backward(c1, self.dT, "z", self.dz, stuffed=self.stuffed[0] if st else None)
+            par = self.parity_dgrad and st and ds is not None and ds.stride == 2
+            self._bn_backward(c1, self.dT, "z", self.dz, stuffed=self.stuffed[0] if (st and not par) else None)
             self._wgrad(c1, c1.x_in, self.dz)
-            if ds is not None:
+            if par:
+                self._bn_backward(ds, self.g_idn, None, self.dzd)
+                self._wgrad(ds, c1.x_in, self.dzd)
+                self._dgrad_s2(ds, self.dzd, self.tmp)                       # parity-(0,0) pixels of tmp only
+                self._dgrad_s2(c1, self.dz, other, residual00=self.tmp)      # all four parities; + tmp at (0,0)
+            elif ds is not None:
                 self._bn_backward(ds, self.g_idn, None, self.dzd, stuffed=self.stuffed[1] if ds.stride == 2 else None)
                 self._wgrad(ds, c1.x_in, self.dzd)
                 self._dgrad(ds, self.stuffed[1] if ds.stride == 2 else self.dzd, self.tmp)

@@ -359,3 +359,46 @@ def test_conv_epilogue_batch_statistics(case):
     L.check(L.lib().pb200_train_bn_stats(out.data_ptr(), z.shape[0], Cout, sums.data_ptr(), _stream()))
     torch.cuda.synchronize()
     assert float(((stats - sums).abs() / scale).max()) < 1e-5
+
+
+DGRAD_S2_CASES = [
+    # B, Ho, Wo, Cin (forward input channels), Cout, R
+    (3, 32, 32, 64, 128, 3),    # layer2.0.conv1: N = 64 tiles
+    (2, 16, 16, 128, 256, 3),   # layer3.0.conv1
+    (5, 8, 8, 256, 512, 3),     # layer4.0.conv1: two images per tile, ragged tail
+    (3, 32, 32, 64, 128, 1),    # layer2.0.downsample
+    (3, 8, 8, 256, 512, 1),
+]
+
+
+@pytest.mark.parametrize("with_res", [False, True])
+@pytest.mark.parametrize("case", DGRAD_S2_CASES, ids=[str(c) for c in DGRAD_S2_CASES])
+def test_dgrad_stride2_by_output_parity(case, with_res):
+    """pb200_train_dgrad_s2 == the exact input gradient of a stride-2 conv (fp64 on the same bf16 operands)."""
+    L = _lib()
+    B, Ho, Wo, Cin, Cout, R = case
+    H, W = 2 * Ho, 2 * Wo
+    g = torch.Generator().manual_seed(sum(case) + with_res)
+    w = (torch.randn(Cout, Cin, R, R, generator=g) / (R * R * Cin) ** 0.5)
+    dz = torch.randn(B, Ho, Wo, Cout, generator=g).bfloat16()
+    want = torch.nn.grad.conv2d_input((B, Cin, H, W), w.bfloat16().double(), dz.double().permute(0, 3, 1, 2), stride=2,
+                                      padding=R // 2).permute(0, 2, 3, 1)
+    res = torch.randn(B, H, W, Cin, generator=g).bfloat16() if with_res else None
+    if with_res:
+        want = want.clone()
+        want[:, 0::2, 0::2] += res.double()[:, 0::2, 0::2]  # the projection's gradient lives on the parity-(0,0) pixels
+    packed = torch.empty(Cin * R * R * Cout, dtype=torch.bfloat16, device="cuda")
+    wd = w.cuda().contiguous()
+    L.check(L.lib().pb200_train_pack_weights(wd.data_ptr(), Cout, Cin, R, 1, packed.data_ptr(), _stream()))
+    zero_bias = torch.zeros(512, dtype=torch.float32, device="cuda")
+    out = torch.full((B, H, W, Cin), float("nan"), dtype=torch.bfloat16, device="cuda")
+    L.check(L.lib().pb200_train_dgrad_s2(dz.cuda().data_ptr(), B, Ho, Wo, Cout, packed.data_ptr(), zero_bias.data_ptr(), Cin, R,
+                                         None if res is None else res.cuda().data_ptr(), out.data_ptr(), _stream()))
+    torch.cuda.synchronize()
+    got = out.double().cpu()
+    if R == 1:  # a 1x1/2 layer touches the parity-(0,0) pixels only; the others are left as they were
+        assert torch.isnan(got[:, 1::2]).all() and torch.isnan(got[:, :, 1::2]).all()
+        got, want = got[:, 0::2, 0::2], want[:, 0::2, 0::2]
+    assert torch.isfinite(got).all()
+    err = (got - want).abs()
+    assert (err <= 2.0 ** -7 * want.abs() + 1e-2).all(), float(err.max())
