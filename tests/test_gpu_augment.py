@@ -161,3 +161,39 @@ def test_module_drop_in_and_failure_modes():
     assert torch.equal(vo[:, 3].cpu()[kept], (0.035 * xc / 0.035)[kept])
     with pytest.raises(RuntimeError):
         val(x4.cpu(), kp.cpu())
+
+
+def test_no_write_outside_the_output_tensors():
+    """Outputs carved out of a sentinel-filled arena (compute-sanitizer is not available on the pool): the kernels must not
+    touch a byte outside [B][C_out][H][W] / [B][K][2] / [B][H][W] even on ragged tiles."""
+    dev = torch.device("cuda", 0)
+    B, H, W, K = 3, 37, 70, 8
+    cfg = host.AugmentationConfig()
+    x = synthetic_batch(B, H, W, 13).to(dev).contiguous().float()
+    ip, fp, rough = _params(cfg, B, 5, H, W, 3)
+    lib = host._lib.lib()
+    guard = 4096
+    n_out, n_kp, n_pl = B * 4 * H * W, B * K * 2, B * H * W
+    arena = torch.full((guard + n_out + guard + n_kp + guard + n_pl + guard,), 7.5, dtype=torch.float32, device=dev)
+    o0, k0, p0 = guard, guard + n_out + guard, guard + n_out + guard + n_kp + guard
+    out, kpo, pl = arena[o0:o0 + n_out], arena[k0:k0 + n_kp], arena[p0:p0 + n_pl]
+    S = lib.pb200_plasma_side(H, W)
+    scratch = torch.empty(B, S, S, dtype=torch.float32, device=dev)
+    rough_d = torch.from_numpy(rough).to(dev)
+    import ctypes
+
+    host._lib.check(lib.pb200_plasma(rough_d.data_ptr(), ctypes.c_uint64(5), scratch.data_ptr(), pl.data_ptr(), B, H, W,
+                                     host._lib.current_stream_ptr()))
+    counts = torch.empty(B, dtype=torch.int32, device=dev)
+    kp = (torch.rand(B, K, 2) * 30).to(dev)
+    st = host.config_struct(host.kernel_config(cfg, True))
+    ip_d, fp_d = torch.from_numpy(ip).to(dev), torch.from_numpy(fp).to(dev)
+    host._lib.check(lib.pb200_augment(x.data_ptr(), ip_d.data_ptr(), fp_d.data_ptr(),
+                                      pl.data_ptr(), ctypes.byref(st), ctypes.c_uint64(9), counts.data_ptr(), kp.data_ptr(),
+                                      out.data_ptr(), kpo.data_ptr(), B, 5, 4, H, W, K, host._lib.current_stream_ptr()))
+    torch.cuda.synchronize()
+    mask = torch.ones_like(arena, dtype=torch.bool)
+    for a, n in ((o0, n_out), (k0, n_kp), (p0, n_pl)):
+        mask[a:a + n] = False
+    assert bool((arena[mask] == 7.5).all())
+    assert bool((out != 7.5).any()) and torch.isfinite(out).all() and torch.isfinite(kpo).all() and torch.isfinite(pl).all()

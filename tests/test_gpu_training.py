@@ -402,3 +402,34 @@ def test_dgrad_stride2_by_output_parity(case, with_res):
     assert torch.isfinite(got).all()
     err = (got - want).abs()
     assert (err <= 2.0 ** -7 * want.abs() + 1e-2).all(), float(err.max())
+
+
+def test_strided_and_statistics_epilogues_stay_inside_their_tensors():
+    """Sentinel arenas around the outputs of the per-parity stride-2 data gradient and of the statistics-fusing conv."""
+    L = _lib()
+    B, Ho, Wo, Cin, Cout, R = 5, 8, 8, 256, 512, 3
+    g = torch.Generator().manual_seed(1)
+    w = (torch.randn(Cout, Cin, R, R, generator=g) / (R * R * Cin) ** 0.5).cuda().contiguous()
+    dz = torch.randn(B, Ho, Wo, Cout, generator=g).bfloat16().cuda()
+    packed = torch.empty(Cin * R * R * Cout, dtype=torch.bfloat16, device="cuda")
+    L.check(L.lib().pb200_train_pack_weights(w.data_ptr(), Cout, Cin, R, 1, packed.data_ptr(), _stream()))
+    zero_bias = torch.zeros(512, dtype=torch.float32, device="cuda")
+    n, guard = B * 2 * Ho * 2 * Wo * Cin, 8192
+    arena = torch.full((guard + n + guard,), 3.0, dtype=torch.bfloat16, device="cuda")
+    out = arena[guard:guard + n]
+    L.check(L.lib().pb200_train_dgrad_s2(dz.data_ptr(), B, Ho, Wo, Cout, packed.data_ptr(), zero_bias.data_ptr(), Cin, R, None,
+                                         out.data_ptr(), _stream()))
+    torch.cuda.synchronize()
+    assert bool((arena[:guard] == 3.0).all()) and bool((arena[guard + n:] == 3.0).all()) and torch.isfinite(out.float()).all()
+    # statistics-fusing forward conv: output and the 2*Cout doubles
+    x = torch.randn(B, Ho, Wo, Cin, generator=g).bfloat16().cuda()
+    L.check(L.lib().pb200_train_pack_weights(w.data_ptr(), Cout, Cin, R, 0, packed.data_ptr(), _stream()))
+    n2 = B * Ho * Wo * Cout
+    arena2 = torch.full((guard + n2 + guard,), 3.0, dtype=torch.bfloat16, device="cuda")
+    sarena = torch.full((64 + 2 * Cout + 64,), -1.0, dtype=torch.float64, device="cuda")
+    sarena[64:64 + 2 * Cout] = 0
+    L.check(L.lib().pb200_train_conv(x.data_ptr(), B, Ho, Wo, Cin, packed.data_ptr(), zero_bias.data_ptr(), Cout, R, 1, 1, None, 0,
+                                     arena2[guard:guard + n2].data_ptr(), sarena[64:].data_ptr(), _stream()))
+    torch.cuda.synchronize()
+    assert bool((arena2[:guard] == 3.0).all()) and bool((arena2[guard + n2:] == 3.0).all())
+    assert bool((sarena[:64] == -1).all()) and bool((sarena[64 + 2 * Cout:] == -1).all())
