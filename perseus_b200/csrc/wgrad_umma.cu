@@ -41,6 +41,24 @@ __host__ __device__ constexpr uint32_t umma_idesc_bf16_mn(uint32_t M, uint32_t N
   return (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | ((N >> 3) << 17) | ((M >> 4) << 24);
 }
 
+// work item -> (unit pair, N tile, K slice).  The K slice is the SLOWEST index: the ~148 items in flight at any moment
+// are all (pair, N tile) combinations of a few pixel slices, so the x and dz rows of a slice are fetched from HBM once
+// and served to the other pairs / taps from L2 (with the pair slowest every pair streamed both tensors from HBM again).
+struct WgItem {
+  int pair, n_tile, kb0, kb1;
+};
+__device__ __forceinline__ WgItem wg_item(const WgradParams& p, int it) {
+  const int base = p.num_pairs * p.n_tiles;
+  const int ks = it / base;
+  const int rem = it - ks * base;
+  WgItem w;
+  w.pair = rem / p.n_tiles;
+  w.n_tile = rem - w.pair * p.n_tiles;
+  w.kb0 = static_cast<int>(static_cast<long long>(p.kblocks_total) * ks / p.ksplit);
+  w.kb1 = static_cast<int>(static_cast<long long>(p.kblocks_total) * (ks + 1) / p.ksplit);
+  return w;
+}
+
 template <int BLOCK_N>
 __global__ void __launch_bounds__(kWgThreads, 1)
 wgrad_umma_kernel(const __grid_constant__ WgradMaps maps, const WgradParams p) {
@@ -82,20 +100,13 @@ wgrad_umma_kernel(const __grid_constant__ WgradMaps maps, const WgradParams p) {
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_slot;
 
-  // work item -> (pair, n_tile, k slice)
-  const int items_per_pair = p.n_tiles * p.ksplit;
-
   if (warp == 0) {
     // ================================ TMA producer ================================
     int stage = 0;
     uint32_t phase = 0;
     for (int it = blockIdx.x; it < p.num_items; it += gridDim.x) {
-      const int pair = it / items_per_pair;
-      const int rem = it - pair * items_per_pair;
-      const int n_tile = rem / p.ksplit;
-      const int ks = rem - n_tile * p.ksplit;
-      const int kb0 = static_cast<int>(static_cast<long long>(p.kblocks_total) * ks / p.ksplit);
-      const int kb1 = static_cast<int>(static_cast<long long>(p.kblocks_total) * (ks + 1) / p.ksplit);
+      const WgItem w = wg_item(p, it);
+      const int pair = w.pair, n_tile = w.n_tile, kb0 = w.kb0, kb1 = w.kb1;
       // the two units of this pair (the second one of an odd tail repeats the first and is discarded)
       int u_tap[2], u_cb[2];
 #pragma unroll
@@ -157,10 +168,8 @@ wgrad_umma_kernel(const __grid_constant__ WgradMaps maps, const WgradParams p) {
     uint32_t phase = 0;
     int n = 0;
     for (int it = blockIdx.x; it < p.num_items; it += gridDim.x, ++n) {
-      const int rem = it % items_per_pair;
-      const int ks = rem % p.ksplit;
-      const int kb0 = static_cast<int>(static_cast<long long>(p.kblocks_total) * ks / p.ksplit);
-      const int kb1 = static_cast<int>(static_cast<long long>(p.kblocks_total) * (ks + 1) / p.ksplit);
+      const WgItem w = wg_item(p, it);
+      const int kb0 = w.kb0, kb1 = w.kb1;
       const int acc = n & 1;
       mbar_wait(&tmem_empty_bar[acc], ((n >> 1) & 1u) ^ 1u);
       tc_fence_after();
@@ -200,12 +209,8 @@ wgrad_umma_kernel(const __grid_constant__ WgradMaps maps, const WgradParams p) {
     const int row = q * 32 + lane;  // 0..127: unit (row / 64), channel row % 64
     int n = 0;
     for (int it = blockIdx.x; it < p.num_items; it += gridDim.x, ++n) {
-      const int pair = it / items_per_pair;
-      const int rem = it - pair * items_per_pair;
-      const int n_tile = rem / p.ksplit;
-      const int ks = rem - n_tile * p.ksplit;
-      const int kb0 = static_cast<int>(static_cast<long long>(p.kblocks_total) * ks / p.ksplit);
-      const int kb1 = static_cast<int>(static_cast<long long>(p.kblocks_total) * (ks + 1) / p.ksplit);
+      const WgItem w = wg_item(p, it);
+      const int pair = w.pair, n_tile = w.n_tile, kb0 = w.kb0, kb1 = w.kb1;
       const int acc = n & 1;
       const int u = 2 * pair + (row >> 6);
       const bool valid = u < p.num_units && kb1 > kb0;
@@ -304,11 +309,25 @@ int build_wgrad(WgradLaunch* L, const void* x, const void* dz, float* dw_scratch
   p.num_pairs = (p.num_units + 1) / 2;
   p.n_tiles = Cout / block_n;
   p.kblocks_total = static_cast<int>((M + kWgKBlock - 1) / kWgKBlock);
-  // split-K so that the persistent grid has about two work items per SM, each with >= 4 k-blocks
+  // split-K: at most two work items per SM (the second one's main loop overlaps the first one's atomics), each with
+  // >= 4 k-blocks, and the count that fills the last wave best (rounding the count UP to two per SM left a third,
+  // nearly empty wave: 300 items on 148 SMs cost three rounds instead of two)
   const int base = p.num_pairs * p.n_tiles;
-  int ks = (2 * num_sms() + base - 1) / base;
-  if (ks > p.kblocks_total / 4) ks = p.kblocks_total / 4;
-  if (ks < 1) ks = 1;
+  const int sms = num_sms();
+  int ks_max = p.kblocks_total / 4;
+  if (ks_max < 1) ks_max = 1;
+  int ks = 1;
+  double best = -1.0;
+  for (int k = 1; k <= ks_max; ++k) {
+    const long long items = static_cast<long long>(base) * k;
+    const long long rounds = (items + sms - 1) / sms;
+    if (rounds > 2) break;
+    const double fill = static_cast<double>(items) / static_cast<double>(rounds * sms);
+    if (fill >= best) {
+      best = fill;
+      ks = k;
+    }
+  }
   p.ksplit = ks;
   p.num_items = base * ks;
   p.dw = dw_scratch;

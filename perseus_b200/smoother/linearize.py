@@ -118,8 +118,9 @@ def chain_solve(D: torch.Tensor, O: torch.Tensor, g: torch.Tensor):
     delta = torch.empty(W, T, 12, dtype=torch.float64, device=dev)
     status = torch.empty(W, dtype=torch.int32, device=dev)
     Oc = O.contiguous() if T > 1 else None
+    Dc, gc = D.contiguous(), g.contiguous()  # held until after the launch (a temporary's block could be handed out again)
     with torch.cuda.device(dev):
-        _lib.check(_lib.lib().pb200_smoother_solve(D.contiguous().data_ptr(), _lib.ptr(Oc), g.contiguous().data_ptr(),
+        _lib.check(_lib.lib().pb200_smoother_solve(Dc.data_ptr(), _lib.ptr(Oc), gc.data_ptr(),
                                                    work.data_ptr(), delta.data_ptr(), status.data_ptr(), W, T,
                                                    _lib.current_stream_ptr()))
     return delta, status

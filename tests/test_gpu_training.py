@@ -392,8 +392,9 @@ def test_dgrad_stride2_by_output_parity(case, with_res):
     L.check(L.lib().pb200_train_pack_weights(wd.data_ptr(), Cout, Cin, R, 1, packed.data_ptr(), _stream()))
     zero_bias = torch.zeros(512, dtype=torch.float32, device="cuda")
     out = torch.full((B, H, W, Cin), float("nan"), dtype=torch.bfloat16, device="cuda")
-    L.check(L.lib().pb200_train_dgrad_s2(dz.cuda().data_ptr(), B, Ho, Wo, Cout, packed.data_ptr(), zero_bias.data_ptr(), Cin, R,
-                                         None if res is None else res.cuda().data_ptr(), out.data_ptr(), _stream()))
+    dz_d, res_d = dz.cuda(), None if res is None else res.cuda()  # held: a temporary's block could be reused before the launch
+    L.check(L.lib().pb200_train_dgrad_s2(dz_d.data_ptr(), B, Ho, Wo, Cout, packed.data_ptr(), zero_bias.data_ptr(), Cin, R,
+                                         None if res_d is None else res_d.data_ptr(), out.data_ptr(), _stream()))
     torch.cuda.synchronize()
     got = out.double().cpu()
     if R == 1:  # a 1x1/2 layer touches the parity-(0,0) pixels only; the others are left as they were
