@@ -12,15 +12,19 @@
 //
 //   * warp 0 (one elected lane): streams frame row-PAIRS (4224 contiguous bytes) into a 16-slot ring with
 //     cp.async.bulk (no tensor map).
-//   * warp 1 (one elected lane): per iteration 2 x 14 tcgen05.mma (M128 N64 K16) = the conv-row pair
+//   * warp 1 (one elected lane): per iteration 10 tcgen05.mma M128 N128 K16 + 8 M128 N64 K16 = the conv-row pair
 //     (2k, 2k+1) into one of two 128-column TMEM accumulator stages; the weights (28 KB image) stay
 //     resident in shared memory for the CTA's lifetime.
-//   * warps 2..9: epilogue.  Thread = conv column x 32 channels.  TMEM -> vertical running 3-max in fp32
-//     registers on the raw accumulators; once per pooled row: +bias, ReLU, bf16x2 pack -> horizontal
-//     3-max by warp shuffles (one 64-byte shared-memory hand-off per warp boundary) -> even lanes store the
-//     pooled pixel in the P8 layout (layout.h), borders included.  Post-ReLU values are >= 0, so the
-//     pool's -inf padding can be 0 horizontally.
+//   * warps 2..17: epilogue.  Thread = conv column x 16 channels.  TMEM -> vertical running 3-max in fp32
+//     registers on the raw accumulators; once per pooled row: +bias, ReLU, bf16x2 pack -> horizontal 3-max: the two
+//     lanes of a column pair split the channel words of their pool centre, so one pair exchange + one shift by two
+//     lanes per word do it (the epilogue is bound by the shuffle / shared-memory pipe, not by issue slots or latency:
+//     16 warps x 16 channels measured the same as 8 x 32; halving the shuffles and vectorising the warp-boundary
+//     hand-off took 0.03 ms off) -> both lanes store their half of the pooled pixel in the P8 layout (layout.h),
+//     borders included.  Post-ReLU values are >= 0, so the pool's -inf padding can be 0 horizontally.
 //   * work unit = (image, band of PB pooled rows); a band below the top recomputes one conv-row pair.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "layout.h"
 
@@ -28,15 +32,21 @@ namespace pb200 {
 
 namespace {
 
-constexpr int kThreads = 320;  // producer warp + MMA warp + 8 epilogue warps
+// epilogue warps: 4 TMEM lane quarters x (kEpiWarps / 4) channel groups; threads = producer warp + MMA warp + epilogue
+constexpr int stem_threads(int epi_warps) { return 64 + 32 * epi_warps; }
 constexpr int kRowBytes = 2112;           // (256 + 8) px * 4 ch * 2 B
 constexpr int kPairBytes = 2 * kRowBytes; // 4224
+constexpr int kAcc = 2;                   // TMEM accumulator stages of 128 columns (power of two)
+constexpr int kAccShift = 1;
 constexpr int kRing = 16;                 // row-pair slots
 constexpr int kBSbo = kStemK / 8 * 128;   // 3584: 8-channel groups of the weight image
 constexpr int kSmemW = 0;
-constexpr int kSmemRing = kStemWimgBytes;                     // 28672
+// Second copy of the weight image, 8 K-chunks (= two filter rows) further than a whole image: read through ONE N = 128
+// descriptor (8-channel groups kBSbo apart), rows 64..127 of B are then the SAME channels two filter rows earlier.
+constexpr int kSmemW2 = kStemWimgBytes + 8 * 128;             // 29696
+constexpr int kSmemRing = kSmemW2 + kStemWimgBytes;           // 58368
 constexpr int kSmemXchg = kSmemRing + kRing * kPairBytes;     // + 67584
-constexpr int kSmemBias = kSmemXchg + 2 * 4 * 128;            // + 1024
+constexpr int kSmemBias = kSmemXchg + 2 * 4 * 128;            // + 1024 ([2][4 quarters][64 channels] bf16)
 constexpr int kSmemTotal = kSmemBias + 64 * 4 + 128;          // + alignment slack
 
 struct StemPoolParams {
@@ -53,20 +63,22 @@ __device__ __forceinline__ uint32_t hmax2_u32(uint32_t a, uint32_t b) {
   return *reinterpret_cast<uint32_t*>(&r);
 }
 
-__global__ void __launch_bounds__(kThreads, 1) stem_pool_kernel(const StemPoolParams p) {
+template <int kEpiWarps>
+__device__ __forceinline__ void stem_pool_body(const StemPoolParams& p) {
+  constexpr int kCh = 64 / (kEpiWarps / 4);  // channels per epilogue thread
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t full_bar[kRing];
   __shared__ __align__(8) uint64_t empty_bar[kRing];
   __shared__ __align__(8) uint64_t w_bar;
-  __shared__ __align__(8) uint64_t tmem_full_bar[2];
-  __shared__ __align__(8) uint64_t tmem_empty_bar[2];
+  __shared__ __align__(8) uint64_t tmem_full_bar[kAcc];
+  __shared__ __align__(8) uint64_t tmem_empty_bar[kAcc];
   __shared__ uint32_t tmem_base_slot;
 
   const uint32_t raw_addr = smem_u32(smem_raw);
   uint8_t* smem = smem_raw + (((raw_addr + 127u) & ~127u) - raw_addr);
   uint8_t* s_w = smem + kSmemW;
   uint8_t* s_ring = smem + kSmemRing;
-  uint32_t* s_xchg = reinterpret_cast<uint32_t*>(smem + kSmemXchg);  // [2][4][32]
+  uint32_t* s_xchg = reinterpret_cast<uint32_t*>(smem + kSmemXchg);  // [2][4 lane quarters][4 channel quarters][8]
   float* s_bias = reinterpret_cast<float*>(smem + kSmemBias);
 
   const int warp = threadIdx.x >> 5;
@@ -79,14 +91,15 @@ __global__ void __launch_bounds__(kThreads, 1) stem_pool_kernel(const StemPoolPa
       mbar_init(&empty_bar[i], 1);
     }
     mbar_init(&w_bar, 1);
-    mbar_init(&tmem_full_bar[0], 1);
-    mbar_init(&tmem_full_bar[1], 1);
-    mbar_init(&tmem_empty_bar[0], 8);
-    mbar_init(&tmem_empty_bar[1], 8);
+#pragma unroll
+    for (int i = 0; i < kAcc; ++i) {
+      mbar_init(&tmem_full_bar[i], 1);
+      mbar_init(&tmem_empty_bar[i], kEpiWarps);
+    }
     fence_barrier_init();
   }
   if (warp == 1) {
-    tmem_alloc(&tmem_base_slot, 256);
+    tmem_alloc(&tmem_base_slot, 128 * kAcc);
     tmem_relinquish();
   }
   if (threadIdx.x >= 64 && threadIdx.x < 128) s_bias[threadIdx.x - 64] = __ldg(p.bias + threadIdx.x - 64);
@@ -107,8 +120,9 @@ __global__ void __launch_bounds__(kThreads, 1) stem_pool_kernel(const StemPoolPa
     // ================================ producer ====================================
     // whole warp runs the loop (warp-uniform operands); one elected lane issues the copies
     if (elect_one()) {
-      mbar_expect_tx(&w_bar, kStemWimgBytes);
+      mbar_expect_tx(&w_bar, 2 * kStemWimgBytes);
       bulk_load_1d(s_w, p.wimg, kStemWimgBytes, &w_bar);
+      bulk_load_1d(s_w + kSmemW2, p.wimg, kStemWimgBytes, &w_bar);
     }
     uint32_t G = 0;
     for (int u = blockIdx.x; u < p.num_units; u += gridDim.x) {
@@ -130,7 +144,14 @@ __global__ void __launch_bounds__(kThreads, 1) stem_pool_kernel(const StemPoolPa
     }
   } else if (warp == 1) {
     // ================================ MMA issuer ==================================
-    constexpr uint32_t idesc = umma_idesc_bf16(128, 64);
+    // Frame row fr of the iteration's nine (relative to 4k) feeds conv row 2k through filter row fr and conv row 2k+1
+    // through filter row fr - 2.  For fr = 2..6 both exist: ONE N = 128 MMA (B = [W_fr ; W_fr-2] via the shifted second
+    // weight copy) fills accumulator columns [0,64) and [64,128) from a single read of the A rows -- the N = 64 MMA is
+    // bound by its shared-memory operand fetch (~85 cycles measured for the unaligned no-swizzle rows), not by math.
+    // Those five go first (the first one initialises all 128 columns); fr = 0, 1 (conv row 2k only) and fr = 7, 8
+    // (conv row 2k+1 only) follow as N = 64 accumulations: 18 MMAs per pair instead of 28.
+    constexpr uint32_t idesc64 = umma_idesc_bf16(128, 64);
+    constexpr uint32_t idesc128 = umma_idesc_bf16(128, 128);
     const uint32_t tm = warp_uniform(tmem_base);
     const uint32_t a_hi = desc_hi_interleaved(128);
     const uint32_t b_hi = desc_hi_interleaved(kBSbo);
@@ -147,22 +168,23 @@ __global__ void __launch_bounds__(kThreads, 1) stem_pool_kernel(const StemPoolPa
         const uint32_t Gi = G + 2 * i;
         mbar_wait(&full_bar[(Gi + 3) % kRing], ((Gi + 3) / kRing) & 1u);
         mbar_wait(&full_bar[(Gi + 4) % kRing], ((Gi + 4) / kRing) & 1u);
-        const int acc = it & 1;
-        mbar_wait(&tmem_empty_bar[acc], ((it >> 1) & 1u) ^ 1u);
+        const int acc = it & (kAcc - 1);
+        mbar_wait(&tmem_empty_bar[acc], ((it >> kAccShift) & 1u) ^ 1u);
         tc_fence_after();
         if (elect_one()) {
+          const uint32_t d_tmem = tm + acc * 128;
+          {
 #pragma unroll
-          for (int e = 0; e < 2; ++e) {  // e = 0: conv row 2k (columns [0,64)), e = 1: conv row 2k+1 (columns [64,128))
-            const uint32_t d_tmem = tm + acc * 128 + e * 64;
-#pragma unroll
-            for (int r = 0; r < 7; ++r) {
-              const int fr = 2 * e + r;  // frame row relative to 4k
+            for (int j = 0; j < 9; ++j) {
+              const int fr = j < 5 ? j + 2 : (j < 7 ? j - 5 : j);  // 2 3 4 5 6 | 0 1 | 7 8
               const uint32_t row = ring_addr + ((Gi + (fr >> 1)) % kRing) * kPairBytes + (fr & 1) * kRowBytes;
               const uint32_t a_lo = desc_lo(row, 16);
+              const int r = fr <= 6 ? fr : fr - 2;               // filter row of the FIRST 64 B rows
+              const uint32_t d = d_tmem + (fr > 6 ? 64 : 0);
 #pragma unroll
               for (int h = 0; h < 2; ++h)
-                umma_bf16_split(d_tmem, a_lo + 2 * h, a_hi, b_lo0 + (r * 4 + h * 2) * 8, b_hi, idesc,
-                                (r | h) != 0 ? 1u : 0u);
+                umma_bf16_split(d, a_lo + 2 * h, a_hi, b_lo0 + (r * 4 + h * 2) * 8, b_hi, j < 5 ? idesc128 : idesc64,
+                                (j | h) != 0 ? 1u : 0u);
             }
           }
           umma_commit(&tmem_full_bar[acc]);
@@ -179,17 +201,18 @@ __global__ void __launch_bounds__(kThreads, 1) stem_pool_kernel(const StemPoolPa
     }
   } else {
     // ================================ epilogue ====================================
-    // 8 warps: warp -> (TMEM lane quarter q, channel half).  Thread = conv column x 32 channels.
+    // 16 warps: warp -> (TMEM lane quarter q, channel quarter cq).  Thread = conv column x 16 channels.
     // Per iteration: both conv rows of the pair come out of TMEM, the vertical 3-max (with the carried odd
     // row) runs in fp32 on the RAW accumulators, then bias, ReLU, the bf16 rounding and the horizontal 3-max
     // happen once per POOLED row.  Exact: x -> bf16(relu(x + b)) is monotone, so it commutes with max.
     const int q = warp & 3;                // TMEM lane quarter
-    const int half = (warp - 2) >> 2;      // channels [32*half, 32*half + 32)
+    const int cq = (warp - 2) >> 2;        // channels [kCh*cq, kCh*cq + kCh)
     const int wo = q * 32 + lane;          // conv output column
     constexpr int Wp8 = 66;                // padded pooled width
+    constexpr int kPlanes = kCh / 8;       // P8 chunk planes per thread
     const long long plane = static_cast<long long>(p.Hpool + 2) * Wp8;  // elements (16 B) per chunk plane
-    const float* bias = s_bias + 32 * half;
-    const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + half * 32;
+    const float* bias = s_bias + kCh * cq;
+    const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + cq * kCh;
     int it = 0;
     uint32_t fin = 0;
     for (int u = blockIdx.x; u < p.num_units; u += gridDim.x) {
@@ -197,37 +220,44 @@ __global__ void __launch_bounds__(kThreads, 1) stem_pool_kernel(const StemPoolPa
       const int band = u - n * p.bands_per_img;
       const int k0 = band == 0 ? 0 : band * p.PB - 1;
       const int n_it = p.PB + (band == 0 ? 0 : 1);
-      uint4* out_img = reinterpret_cast<uint4*>(p.out + n * p.out_img_bytes) + 4 * half * plane;
+      uint4* out_img = reinterpret_cast<uint4*>(p.out + n * p.out_img_bytes) + kPlanes * cq * plane;
       // top / bottom zero border rows of the P8 tensor
       if (band == 0 && wo < Wp8) {
 #pragma unroll
-        for (int j = 0; j < 4; ++j) out_img[j * plane + wo] = make_uint4(0, 0, 0, 0);
+        for (int j = 0; j < kPlanes; ++j) out_img[j * plane + wo] = make_uint4(0, 0, 0, 0);
       }
       if (band == p.bands_per_img - 1 && wo < Wp8) {
 #pragma unroll
-        for (int j = 0; j < 4; ++j)
+        for (int j = 0; j < kPlanes; ++j)
           out_img[j * plane + static_cast<long long>(p.Hpool + 1) * Wp8 + wo] = make_uint4(0, 0, 0, 0);
       }
-      float podd[32];
+      float podd[kCh];
 #pragma unroll
-      for (int k = 0; k < 32; ++k) podd[k] = -INFINITY;
+      for (int k = 0; k < kCh; ++k) podd[k] = -INFINITY;
       for (int i = 0; i < n_it; ++i, ++it) {
-        const int a = it & 1;
-        mbar_wait(&tmem_full_bar[a], (it >> 1) & 1u);
+        const int a = it & (kAcc - 1);
+        mbar_wait(&tmem_full_bar[a], (it >> kAccShift) & 1u);
         tc_fence_after();
-        uint32_t xe[32], xo[32];
-        tmem_ld_32x32(t_lane + a * 128, xe);
-        tmem_ld_32x32(t_lane + a * 128 + 64, xo);
-        tmem_ld_wait_regs(xe);
-        tmem_ld_wait_regs(xo);
+        uint32_t xe[kCh], xo[kCh];
+        if constexpr (kCh == 16) {
+          tmem_ld_32x16(t_lane + a * 128, xe);
+          tmem_ld_32x16(t_lane + a * 128 + 64, xo);
+          tmem_ld_wait_regs16(xe);
+          tmem_ld_wait_regs16(xo);
+        } else {
+          tmem_ld_32x32(t_lane + a * 128, xe);
+          tmem_ld_32x32(t_lane + a * 128 + 64, xo);
+          tmem_ld_wait_regs(xe);
+          tmem_ld_wait_regs(xo);
+        }
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&tmem_empty_bar[a]);
         const bool owned = i > 0 || band == 0;  // the leading iteration of a lower band only produces podd
-        uint32_t v[16];
+        uint32_t v[kCh / 2];
         if (owned) {
 #pragma unroll
-          for (int k = 0; k < 16; ++k) {
+          for (int k = 0; k < kCh / 2; ++k) {
             const float2 b = *reinterpret_cast<const float2*>(bias + 2 * k);
             const float m0 = fmaxf(fmaxf(podd[2 * k], __uint_as_float(xe[2 * k])), __uint_as_float(xo[2 * k]));
             const float m1 = fmaxf(fmaxf(podd[2 * k + 1], __uint_as_float(xe[2 * k + 1])), __uint_as_float(xo[2 * k + 1]));
@@ -235,35 +265,60 @@ __global__ void __launch_bounds__(kThreads, 1) stem_pool_kernel(const StemPoolPa
           }
         }
 #pragma unroll
-        for (int k = 0; k < 32; ++k) podd[k] = __uint_as_float(xo[k]);
+        for (int k = 0; k < kCh; ++k) podd[k] = __uint_as_float(xo[k]);
         if (!owned) continue;
-        // horizontal 3-max: hand the warp's last column to the next warp through shared memory
-        uint32_t* xw = s_xchg + (((fin & 1) * 4 + q) * 2 + half) * 16;
+        // horizontal 3-max.  Pool centres are the EVEN columns; the two lanes of a column pair (c, c+1) share the
+        // work of centre c: the even lane finishes the first half of this thread's channel words, the odd lane the
+        // second half, so one pair exchange + one shift by two lanes per word replace a shuffle up and a shuffle down
+        // of every word (the epilogue was bound by the shuffle / shared-memory pipe).  The warp's last column goes to
+        // the next warp through shared memory (vector accesses by the two lanes that need it).
+        constexpr int kW = kCh / 2, kHW = kW / 2;  // bf16x2 words per thread / per finishing lane
+        uint32_t* xw = s_xchg + (((fin & 1) * 4 + q) * (kEpiWarps / 4) + cq) * kW;
         if (lane == 31) {
 #pragma unroll
-          for (int k = 0; k < 4; ++k)
+          for (int k = 0; k < kW / 4; ++k)
             reinterpret_cast<uint4*>(xw)[k] = make_uint4(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
         }
-        named_bar_sync(1, 256);
-        const uint32_t* xr = s_xchg + (((fin & 1) * 4 + (q > 0 ? q - 1 : 0)) * 2 + half) * 16;
-        ++fin;
+        const bool odd = (lane & 1) != 0;
+        uint32_t mine[kHW], part[kHW];
 #pragma unroll
-        for (int k = 0; k < 16; ++k) {
-          uint32_t left = __shfl_up_sync(0xffffffffu, v[k], 1);
-          const uint32_t right = __shfl_down_sync(0xffffffffu, v[k], 1);
-          if (lane == 0) left = q > 0 ? xr[k] : 0u;  // column -1 is the pool's padding (values are >= 0)
-          v[k] = hmax2_u32(hmax2_u32(left, v[k]), right);  // lane 31 (odd column) is never a pool centre
+        for (int j = 0; j < kHW; ++j) {
+          const uint32_t send = odd ? v[j] : v[kHW + j];  // what the pair partner finishes
+          part[j] = __shfl_xor_sync(0xffffffffu, send, 1);
+          mine[j] = odd ? v[kHW + j] : v[j];
+        }
+        named_bar_sync(1, 32 * kEpiWarps);
+        uint32_t edge[kHW];
+#pragma unroll
+        for (int j = 0; j < kHW; ++j) edge[j] = 0u;  // column -1 is the pool's padding (values are >= 0)
+        if (lane < 2 && q > 0) {
+          const uint4* xr = reinterpret_cast<const uint4*>(s_xchg + (((fin & 1) * 4 + q - 1) * (kEpiWarps / 4) + cq) * kW + (odd ? kHW : 0));
+#pragma unroll
+          for (int k = 0; k < kHW / 4; ++k) {
+            const uint4 t = xr[k];
+            edge[4 * k] = t.x; edge[4 * k + 1] = t.y; edge[4 * k + 2] = t.z; edge[4 * k + 3] = t.w;
+          }
+        }
+        ++fin;
+        // column c-1 of the words a lane finishes sits two lanes to the left: as `part` of an even lane, `mine` of an odd
+#pragma unroll
+        for (int j = 0; j < kHW; ++j) {
+          uint32_t left = __shfl_up_sync(0xffffffffu, odd ? mine[j] : part[j], 2);
+          if (lane < 2) left = edge[j];
+          mine[j] = hmax2_u32(hmax2_u32(left, mine[j]), part[j]);
         }
         const int po = k0 + i;
         uint4* orow = out_img + static_cast<long long>(po + 1) * Wp8;
-        if ((lane & 1) == 0) {
-          const int pw = wo >> 1;
+        const int pw = wo >> 1;
+        constexpr int kLanePlanes = kHW / 4;  // P8 chunk planes a lane stores
 #pragma unroll
-          for (int j = 0; j < 4; ++j) orow[j * plane + pw + 1] = make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-        } else if (wo == 1 || wo == 127) {
+        for (int j = 0; j < kLanePlanes; ++j)
+          orow[((odd ? kLanePlanes : 0) + j) * plane + pw + 1] =
+              make_uint4(mine[4 * j], mine[4 * j + 1], mine[4 * j + 2], mine[4 * j + 3]);
+        if (wo == 1 || wo == 127) {
           const int col = wo == 1 ? 0 : Wp8 - 1;
 #pragma unroll
-          for (int j = 0; j < 4; ++j) orow[j * plane + col] = make_uint4(0, 0, 0, 0);
+          for (int j = 0; j < kPlanes; ++j) orow[j * plane + col] = make_uint4(0, 0, 0, 0);
         }
       }
     }
@@ -273,16 +328,21 @@ __global__ void __launch_bounds__(kThreads, 1) stem_pool_kernel(const StemPoolPa
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, 256);
+    tmem_dealloc(tmem_base, 128 * kAcc);
   }
 }
+
+// 16 epilogue warps x 16 channels (18 warps: 5 on one scheduler, so at most 96 registers per thread) or 8 x 32
+__global__ void __maxnreg__(96) stem_pool_kernel16(const StemPoolParams p) { stem_pool_body<16>(p); }
+__global__ void __launch_bounds__(stem_threads(8), 1) stem_pool_kernel8(const StemPoolParams p) { stem_pool_body<8>(p); }
 
 }  // namespace
 
 int stem_pool_init() {
   static bool done = false;
   if (done) return PB200_OK;
-  PB_CUDA(cudaFuncSetAttribute(stem_pool_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
+  PB_CUDA(cudaFuncSetAttribute(stem_pool_kernel16, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
+  PB_CUDA(cudaFuncSetAttribute(stem_pool_kernel8, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
   done = true;
   return PB200_OK;
 }
@@ -309,13 +369,15 @@ int launch_stem_pool(const void* frames, const void* wimg, const float* bias, vo
   const int grid = p.num_units < num_sms() ? p.num_units : num_sms();
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(grid);
-  cfg.blockDim = dim3(kThreads);
+  const bool wide = getenv("PB200_STEM_EPI8") != nullptr;
+  cfg.blockDim = dim3(stem_threads(wide ? 8 : 16));
   cfg.dynamicSmemBytes = kSmemTotal;
   cfg.stream = st;
   cudaLaunchAttribute attr[1];
   cfg.attrs = attr;
   cfg.numAttrs = pdl_launch_attrs(attr);
-  PB_CUDA(cudaLaunchKernelEx(&cfg, stem_pool_kernel, p));
+  if (wide) PB_CUDA(cudaLaunchKernelEx(&cfg, stem_pool_kernel8, p));
+  else PB_CUDA(cudaLaunchKernelEx(&cfg, stem_pool_kernel16, p));
   return PB200_OK;
 }
 
