@@ -15,6 +15,8 @@
 //     (M128 N64 K16) per tile into one of two TMEM accumulators; warps 2..5: epilogue
 //     (TMEM -> +bias (+residual) -> ReLU -> bf16 -> 16-byte stores, lanes = consecutive positions so
 //     every store instruction of a warp is one contiguous 512-byte run in P8).
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "layout.h"
 
@@ -22,7 +24,7 @@ namespace pb200 {
 
 namespace {
 
-constexpr int kThreads = 192;
+constexpr int p8_threads(int epi_warps) { return 64 + 32 * epi_warps; }
 constexpr int kStages = 4;
 constexpr int kChunks = 8;                       // Cin / 8
 constexpr int kWBytes = 64 * 576 * 2;            // 73728
@@ -43,7 +45,11 @@ struct ConvP8Params {
   long long plane_bytes;    // bytes per P8 chunk plane
 };
 
-__global__ void __launch_bounds__(kThreads, 1) conv_p8_kernel(const ConvP8Params p) {
+// kEpiWarps = 4 (thread = position x 64 channels) or 8 (x 32 channels).  With 4 the epilogue has ONE warp per scheduler
+// and its ~350 dependent instructions per tile take longer than the tile's 36 MMAs (1728 cycles): latency-bound.
+template <int kEpiWarps>
+__device__ __forceinline__ void conv_p8_body(const ConvP8Params& p) {
+  constexpr int kNch = 8 / (kEpiWarps / 4);  // 8-channel chunks (P8 planes) per epilogue thread
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t full_bar[kStages];
   __shared__ __align__(8) uint64_t empty_bar[kStages];
@@ -71,8 +77,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_p8_kernel(const ConvP8Params
     mbar_init(&w_bar, 1);
     mbar_init(&tmem_full_bar[0], 1);
     mbar_init(&tmem_full_bar[1], 1);
-    mbar_init(&tmem_empty_bar[0], 4);
-    mbar_init(&tmem_empty_bar[1], 4);
+    mbar_init(&tmem_empty_bar[0], kEpiWarps);
+    mbar_init(&tmem_empty_bar[1], kEpiWarps);
     fence_barrier_init();
   }
   if (warp == 1) {
@@ -157,13 +163,14 @@ __global__ void __launch_bounds__(kThreads, 1) conv_p8_kernel(const ConvP8Params
     // ================================ epilogue ====================================
     pdl_wait();  // residual reads / output writes must follow the previous kernel (the output buffer may be its input)
     const int q = warp & 3;
+    const int j0 = ((warp - 2) >> 2) * kNch;  // first chunk plane of this thread
     const int m = q * 32 + lane;
     const long long plane16 = p.plane_bytes / 16;
     int it = 0;
     const bool has_res = p.residual != nullptr;
     // residual tile of THIS thread's row: loaded one tile ahead (right after the previous tile consumed
     // its copy) so the DRAM latency hides behind the previous tile's stores and the accumulator wait
-    uint4 rv[8];
+    uint4 rv[kNch];
     auto load_residual = [&](int tile) {
       bool ok = false;
       if (has_res && tile < p.num_tiles) {
@@ -173,16 +180,19 @@ __global__ void __launch_bounds__(kThreads, 1) conv_p8_kernel(const ConvP8Params
         if (q0 < p.H * p.Wp && q0 - h * p.Wp < p.W) {
           const uint4* res = reinterpret_cast<const uint4*>(p.residual + n * p.img_bytes) + q0 + p.Wp + 1;
 #pragma unroll
-          for (int j = 0; j < 8; ++j) rv[j] = __ldg(res + j * plane16);
+          for (int j = 0; j < kNch; ++j) rv[j] = __ldg(res + (j0 + j) * plane16);
           ok = true;
         }
       }
       if (!ok) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) rv[j] = make_uint4(0, 0, 0, 0);
+        for (int j = 0; j < kNch; ++j) rv[j] = make_uint4(0, 0, 0, 0);
       }
     };
     load_residual(blockIdx.x);
+    float bias[8 * kNch];
+#pragma unroll
+    for (int e = 0; e < 8 * kNch; ++e) bias[e] = s_bias[8 * j0 + e];
     for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
       const int n = tile / p.tiles_per_img;
       const int ti = tile - n * p.tiles_per_img;
@@ -195,23 +205,23 @@ __global__ void __launch_bounds__(kThreads, 1) conv_p8_kernel(const ConvP8Params
       const long long opos = static_cast<long long>(q0) + p.Wp + 1;  // padded position of this output
       mbar_wait(&tmem_full_bar[a], (it >> 1) & 1u);
       tc_fence_after();
-      const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + a * 64;
-      uint32_t x0[32], x1[32];
-      tmem_ld_32x32(t_addr, x0);
-      tmem_ld_32x32(t_addr + 32, x1);
-      tmem_ld_wait_regs(x0);
-      tmem_ld_wait_regs(x1);
+      const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + a * 64 + 8 * j0;
+      uint32_t x[kNch / 4][32];
+#pragma unroll
+      for (int c = 0; c < kNch / 4; ++c) tmem_ld_32x32(t_addr + 32 * c, x[c]);
+#pragma unroll
+      for (int c = 0; c < kNch / 4; ++c) tmem_ld_wait_regs(x[c]);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tmem_empty_bar[a]);
 
-      uint4 o[8];
+      uint4 o[kNch];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const uint32_t* x = j < 4 ? &x0[8 * j] : &x1[8 * (j - 4)];
+      for (int j = 0; j < kNch; ++j) {
+        const uint32_t* xj = &x[j / 4][8 * (j % 4)];
         float f[8];
 #pragma unroll
-        for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(x[e]) + s_bias[8 * j + e];
+        for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(xj[e]) + bias[8 * j + e];
         if (has_res) {
           f[0] += bf16_lo(rv[j].x); f[1] += bf16_hi(rv[j].x);
           f[2] += bf16_lo(rv[j].y); f[3] += bf16_hi(rv[j].y);
@@ -228,16 +238,16 @@ __global__ void __launch_bounds__(kThreads, 1) conv_p8_kernel(const ConvP8Params
       }
       load_residual(tile + gridDim.x);  // rv is dead from here on: prefetch the next tile's residual
       if (p.out_nhwc) {
-        // NHWC pixel = 8 chunks = one 128-byte line.  A lane holds the 8 chunks of ITS position; storing them directly
-        // makes every store instruction touch 32 different lines with 16 bytes each.  An 8x8 transpose inside each
-        // group of 8 lanes (3 butterfly stages of 16-byte shuffles) turns lane l into the owner of chunk l%8 of the
-        // group's 8 positions, so one instruction writes 4 complete lines.
-        const int l8 = lane & 7;
+        // NHWC pixel = 8 chunks = one 128-byte line.  A lane holds kNch chunks of ITS position; storing them directly
+        // makes every store instruction touch 32 different lines with 16 bytes each.  A kNch x kNch transpose inside
+        // each group of kNch lanes (butterfly stages of 16-byte shuffles) turns lane l into the owner of chunk
+        // j0 + l % kNch of the group's positions, so one instruction writes complete 16 * kNch-byte runs.
+        const int ln = lane & (kNch - 1);
 #pragma unroll
-        for (int sft = 4; sft >= 1; sft >>= 1) {
-          const bool up = (l8 & sft) != 0;
+        for (int sft = kNch / 2; sft >= 1; sft >>= 1) {
+          const bool up = (ln & sft) != 0;
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
+          for (int j = 0; j < kNch; ++j) {
             if (j & sft) continue;
             const uint4 send = up ? o[j] : o[j | sft];
             uint4 recv;
@@ -249,28 +259,28 @@ __global__ void __launch_bounds__(kThreads, 1) conv_p8_kernel(const ConvP8Params
             else o[j | sft] = recv;
           }
         }
-        // pixel index of this lane's own position (-1: not an output); position 8g + j lives in lane 8g + j
+        // pixel index of this lane's own position (-1: not an output); position g*kNch + j lives in lane g*kNch + j
         const long long own = valid ? (static_cast<long long>(n) * p.H + h) * p.W + w : -1;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const long long pix = __shfl_sync(0xffffffffu, own, (lane & 24) + j);
-          if (pix >= 0) reinterpret_cast<uint4*>(p.out)[pix * 8 + l8] = o[j];
+        for (int j = 0; j < kNch; ++j) {
+          const long long pix = __shfl_sync(0xffffffffu, own, (lane & ~(kNch - 1)) + j);
+          if (pix >= 0) reinterpret_cast<uint4*>(p.out)[pix * 8 + j0 + ln] = o[j];
         }
       } else {
         uint4* oimg = reinterpret_cast<uint4*>(p.out + n * p.img_bytes);
         if (in_plane) {
 #pragma unroll
-          for (int j = 0; j < 8; ++j) oimg[j * plane16 + opos] = o[j];
+          for (int j = 0; j < kNch; ++j) oimg[(j0 + j) * plane16 + opos] = o[j];
         }
         // the zero border rows the flattened tiles do not reach
         if (ti == 0 && m < p.Wp + 1) {
 #pragma unroll
-          for (int j = 0; j < 8; ++j) oimg[j * plane16 + m] = make_uint4(0, 0, 0, 0);
+          for (int j = 0; j < kNch; ++j) oimg[(j0 + j) * plane16 + m] = make_uint4(0, 0, 0, 0);
         }
         if (ti == p.tiles_per_img - 1 && m < p.Wp - 1) {
           const long long bpos = static_cast<long long>(p.H + 1) * p.Wp + 1 + m;
 #pragma unroll
-          for (int j = 0; j < 8; ++j) oimg[j * plane16 + bpos] = make_uint4(0, 0, 0, 0);
+          for (int j = 0; j < kNch; ++j) oimg[(j0 + j) * plane16 + bpos] = make_uint4(0, 0, 0, 0);
         }
       }
     }
@@ -284,6 +294,9 @@ __global__ void __launch_bounds__(kThreads, 1) conv_p8_kernel(const ConvP8Params
   }
 }
 
+__global__ void __launch_bounds__(p8_threads(8), 1) conv_p8_kernel(const ConvP8Params p) { conv_p8_body<8>(p); }
+__global__ void __launch_bounds__(p8_threads(4), 1) conv_p8_kernel4(const ConvP8Params p) { conv_p8_body<4>(p); }
+
 constexpr int kMaxDynSmem = 227 * 1024 - 1024;  // the kernel also has ~400 B of static shared memory
 inline int patch_pitch_for(int Wp) { return ((128 + 2 * Wp + 2) * 16 + 127) / 128 * 128; }
 inline int smem_bytes_for(int Wp) { return kWBytes + kStages * kChunks * patch_pitch_for(Wp) + 128; }
@@ -294,6 +307,7 @@ int conv_p8_init() {
   static bool done = false;
   if (done) return PB200_OK;
   PB_CUDA(cudaFuncSetAttribute(conv_p8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem));
+  PB_CUDA(cudaFuncSetAttribute(conv_p8_kernel4, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem));
   done = true;
   return PB200_OK;
 }
@@ -324,13 +338,15 @@ int launch_conv_p8(const void* in_p8, const void* wimg, const float* bias, const
   const int grid = p.num_tiles < num_sms() ? p.num_tiles : num_sms();
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(grid);
-  cfg.blockDim = dim3(kThreads);
+  const bool narrow = getenv("PB200_P8_EPI4") != nullptr;
+  cfg.blockDim = dim3(p8_threads(narrow ? 4 : 8));
   cfg.dynamicSmemBytes = smem_bytes_for(Wp);
   cfg.stream = st;
   cudaLaunchAttribute attr[1];
   cfg.attrs = attr;
   cfg.numAttrs = pdl_launch_attrs(attr);
-  PB_CUDA(cudaLaunchKernelEx(&cfg, conv_p8_kernel, p));
+  if (narrow) PB_CUDA(cudaLaunchKernelEx(&cfg, conv_p8_kernel4, p));
+  else PB_CUDA(cudaLaunchKernelEx(&cfg, conv_p8_kernel, p));
   return PB200_OK;
 }
 
