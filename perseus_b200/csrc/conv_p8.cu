@@ -168,10 +168,10 @@ __device__ __forceinline__ void conv_p8_body(const ConvP8Params& p) {
     const long long plane16 = p.plane_bytes / 16;
     int it = 0;
     const bool has_res = p.residual != nullptr;
-    // residual tile of THIS thread's row: loaded one tile ahead (right after the previous tile consumed
-    // its copy) so the DRAM latency hides behind the previous tile's stores and the accumulator wait
-    uint4 rv[kNch];
-    auto load_residual = [&](int tile) {
+    // residual tiles of THIS thread's row: loaded TWO tiles ahead into two register sets (one tile of lead, ~1.3 us,
+    // still left the epilogue waiting on HBM for the residual at the top of every tile)
+    uint4 rv0[kNch], rv1[kNch];
+    auto load_residual = [&](int tile, uint4 (&rv)[kNch]) {
       bool ok = false;
       if (has_res && tile < p.num_tiles) {
         const int n = tile / p.tiles_per_img;
@@ -189,11 +189,12 @@ __device__ __forceinline__ void conv_p8_body(const ConvP8Params& p) {
         for (int j = 0; j < kNch; ++j) rv[j] = make_uint4(0, 0, 0, 0);
       }
     };
-    load_residual(blockIdx.x);
+    load_residual(blockIdx.x, rv0);
+    load_residual(blockIdx.x + gridDim.x, rv1);
     float bias[8 * kNch];
 #pragma unroll
     for (int e = 0; e < 8 * kNch; ++e) bias[e] = s_bias[8 * j0 + e];
-    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+    auto process = [&](int tile, uint4 (&rv)[kNch]) {
       const int n = tile / p.tiles_per_img;
       const int ti = tile - n * p.tiles_per_img;
       const int q0 = ti * 128 + m;
@@ -236,7 +237,7 @@ __device__ __forceinline__ void conv_p8_body(const ConvP8Params& p) {
                                   pack_bf16x2(f[6], f[7]))
                      : make_uint4(0, 0, 0, 0);
       }
-      load_residual(tile + gridDim.x);  // rv is dead from here on: prefetch the next tile's residual
+      load_residual(tile + 2 * gridDim.x, rv);  // rv is dead from here on: prefetch the residual of the tile after next
       if (p.out_nhwc) {
         // NHWC pixel = 8 chunks = one 128-byte line.  A lane holds kNch chunks of ITS position; storing them directly
         // makes every store instruction touch 32 different lines with 16 bytes each.  A kNch x kNch transpose inside
@@ -283,6 +284,11 @@ __device__ __forceinline__ void conv_p8_body(const ConvP8Params& p) {
           for (int j = 0; j < kNch; ++j) oimg[(j0 + j) * plane16 + bpos] = make_uint4(0, 0, 0, 0);
         }
       }
+      ++it;
+    };
+    for (int tile = blockIdx.x; tile < p.num_tiles; tile += 2 * gridDim.x) {
+      process(tile, rv0);
+      if (tile + static_cast<int>(gridDim.x) < p.num_tiles) process(tile + gridDim.x, rv1);
     }
   }
 
