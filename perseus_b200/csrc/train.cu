@@ -251,7 +251,10 @@ bn_apply_kernel(const uint4* __restrict__ z, const double* __restrict__ sums, co
   const int C8 = C / 8;
   // C8 is a power of two <= 64 (host check) and both the CTA size and the grid stride are multiples of it, so a thread
   // keeps ONE channel group for the whole loop: its 8 scales / shifts live in registers
-  const int c0 = (static_cast<int>(threadIdx.x) & (C8 - 1)) * 8;
+  // The tensor is walked from its END: z was just written front to back by the producing conv, so its tail is what L2
+  // still holds -- a front-to-back pass would miss on the (evicted) head and push the tail out before reaching it.
+  // Element index total-1-j: the channel group of a thread is C8-1 - (tid mod C8), still fixed.
+  const int c0 = (C8 - 1 - (static_cast<int>(threadIdx.x) & (C8 - 1))) * 8;
   float sc[8], sh[8];
 #pragma unroll
   for (int e = 0; e < 8; ++e) {
@@ -261,7 +264,8 @@ bn_apply_kernel(const uint4* __restrict__ z, const double* __restrict__ sums, co
   const long long total = M * C8;
   const long long step = static_cast<long long>(gridDim.x) * kBnThreads;
 #pragma unroll 4
-  for (long long i = static_cast<long long>(blockIdx.x) * kBnThreads + threadIdx.x; i < total; i += step) {
+  for (long long j = static_cast<long long>(blockIdx.x) * kBnThreads + threadIdx.x; j < total; j += step) {
+    const long long i = total - 1 - j;
     float f[8];
     unpack8(__ldg(z + i), f);
 #pragma unroll
@@ -303,8 +307,11 @@ bn_bwd_reduce_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ y_m
     nb[e] = mask_from_z ? beta[c] - mu[e] * sc[e] : 0.f;
   }
   float a[8] = {0, 0, 0, 0, 0, 0, 0, 0}, q[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  // rows interleaved over the CTAs (not one contiguous range per CTA): the pass ends on the tensor's tail, which is
+  // where bn_bwd_apply_kernel (walking backwards) starts and finds dy / z still in L2
+  const long long rstep = static_cast<long long>(gridDim.x) * rs.lanes;
 #pragma unroll 2
-  for (long long r = rs.row0 + rs.rl; r < rs.row1; r += rs.lanes) {
+  for (long long r = static_cast<long long>(blockIdx.x) * rs.lanes + rs.rl; r < M; r += rstep) {
     const long long i = r * C8 + rs.cg;
     float g[8], zz[8];
     unpack8(__ldg(dy + i), g);
@@ -361,7 +368,7 @@ bn_bwd_apply_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ y_ma
   }
   __syncthreads();
   const int C8 = C / 8;
-  const int cg = static_cast<int>(threadIdx.x) & (C8 - 1);  // fixed per thread (see bn_apply_kernel)
+  const int cg = C8 - 1 - (static_cast<int>(threadIdx.x) & (C8 - 1));  // fixed per thread; back-to-front walk (bn_apply_kernel)
   float k[8], A[8], Bc[8], sh[8];
 #pragma unroll
   for (int e = 0; e < 8; ++e) {
@@ -374,7 +381,8 @@ bn_bwd_apply_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ y_ma
   const long long total = M * C8;
   const long long step = static_cast<long long>(gridDim.x) * kBnThreads;
 #pragma unroll 2
-  for (long long i = static_cast<long long>(blockIdx.x) * kBnThreads + threadIdx.x; i < total; i += step) {
+  for (long long j = static_cast<long long>(blockIdx.x) * kBnThreads + threadIdx.x; j < total; j += step) {
+    const long long i = total - 1 - j;
     float g[8], zz[8], o[8];
     unpack8(__ldg(dy + i), g);
     unpack8(__ldg(z + i), zz);
@@ -403,10 +411,12 @@ bn_bwd_apply_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ y_ma
   }
 }
 
-static inline int bn_grid(long long M, int C) {
+// one resident wave (per_sm = the kernel's __launch_bounds__ occupancy), and at least 16 vectors per thread: a small
+// tensor gets few CTAs, so its 2*C fp64 atomics per CTA and the per-CTA constant prologue stay negligible
+static inline int bn_grid(long long M, int C, int per_sm) {
   const long long vec = M * (C / 8);
-  long long g = (vec + kBnThreads * 4 - 1) / (kBnThreads * 4);
-  const long long cap = static_cast<long long>(num_sms()) * 8;
+  long long g = (vec + kBnThreads * 16 - 1) / (kBnThreads * 16);
+  const long long cap = static_cast<long long>(num_sms()) * per_sm;
   if (g > cap) g = cap;
   if (g < 1) g = 1;
   return static_cast<int>(g);
@@ -422,7 +432,7 @@ extern "C" int pb200_train_bn_stats(const void* z, int64_t M, int C, double* sum
   PB_BN_CHECK(C);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   PB_CUDA(cudaMemsetAsync(sums, 0, sizeof(double) * 2 * C, st));
-  bn_stats_kernel<<<bn_grid(M, C), kBnThreads, 0, st>>>(static_cast<const uint4*>(z), M, C, sums);
+  bn_stats_kernel<<<bn_grid(M, C, 4), kBnThreads, 0, st>>>(static_cast<const uint4*>(z), M, C, sums);
   PB_CUDA(cudaGetLastError());
   return PB200_OK;
 }
@@ -434,7 +444,7 @@ extern "C" int pb200_train_bn_apply(const void* z, const double* sums, const flo
   if (int rc = require_device()) return rc;
   PB_CHECK(z && sums && gamma && beta && save_mean && save_invstd && y, "train_bn_apply: null argument");
   PB_BN_CHECK(C);
-  bn_apply_kernel<<<bn_grid(M, C), kBnThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+  bn_apply_kernel<<<bn_grid(M, C, 4), kBnThreads, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const uint4*>(z), sums, gamma, beta, running_mean, running_var, momentum, eps, save_mean, save_invstd,
       static_cast<const uint4*>(residual_or_null), relu, static_cast<uint4*>(y), M, C);
   PB_CUDA(cudaGetLastError());
@@ -455,7 +465,7 @@ extern "C" int pb200_train_bn_backward(const void* dy, const void* y_mask_or_nul
   PB_CUDA(cudaMemsetAsync(sums, 0, sizeof(double) * 2 * C, st));
   if (stuffed_out_or_null != nullptr)
     PB_CUDA(cudaMemsetAsync(stuffed_out_or_null, 0, static_cast<size_t>(M) * 4 * C * 2, st));
-  const int grid = bn_grid(M, C);
+  const int grid = bn_grid(M, C, 3);
   // beta given (and no y tensor): the layer had no residual input, so its ReLU mask is recomputed from z with the
   // forward's own affine map instead of reading y (one tensor less per pass)
   const int mask_from_z = (beta_or_null != nullptr && y_mask_or_null == nullptr) ? 1 : 0;
