@@ -592,42 +592,66 @@ maxpool_train_kernel(const uint4* __restrict__ in, uint4* __restrict__ out, uint
                         am[4] | (am[5] << 8) | (am[6] << 16) | (am[7] << 24));
 }
 
-// gather form: every input pixel sums the gradients of the (<= 4) windows whose argmax it is
+// gather form: every input pixel sums the gradients of the (<= 4) windows whose argmax it is.  A thread owns the 2x2
+// input block (2a..2a+1, 2b..2b+1) x 8 channels: its four pixels only see windows (a | a+1, b | b+1), so four
+// (argmax, gradient) loads serve four outputs (one pixel per thread visited nine windows for the same four); one
+// resident wave of CTAs walks the blocks (131 k one-vector CTAs with 64-bit div/mod ran at 1.3 TB/s).
 __global__ void __launch_bounds__(256)
 maxpool_bwd_kernel(const uint4* __restrict__ dout, const uint2* __restrict__ idx, uint4* __restrict__ din, int B, int H,
                    int W, int C8, int Ho, int Wo) {
-  const long long total = static_cast<long long>(B) * H * W * C8;
-  const long long gid = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (gid >= total) return;
-  const int c = static_cast<int>(gid % C8);
-  long long p = gid / C8;
-  const int w = static_cast<int>(p % W);
-  p /= W;
-  const int h = static_cast<int>(p % H);
-  const int b = static_cast<int>(p / H);
-  float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-  // windows (ho, wo) with 2*ho - 1 <= h <= 2*ho + 1
-  const int ho_lo = h / 2, ho_hi = (h + 1) / 2;
-  const int wo_lo = w / 2, wo_hi = (w + 1) / 2;
-  for (int ho = ho_lo; ho <= ho_hi; ++ho) {
-    if (ho >= Ho) continue;
-    const int r = h - (2 * ho - 1);
-    for (int wo = wo_lo; wo <= wo_hi; ++wo) {
-      if (wo >= Wo) continue;
-      const int s = w - (2 * wo - 1);
-      const uint32_t me = r * 3 + s;
-      const long long o = ((static_cast<long long>(b) * Ho + ho) * Wo + wo) * C8 + c;
-      const uint2 iv = __ldg(idx + o);
-      float g[8];
-      unpack8(__ldg(dout + o), g);
+  const unsigned total = static_cast<unsigned>(B) * Ho * Wo * C8;  // host: < 2^31
+  const unsigned step = gridDim.x * blockDim.x;
+  for (unsigned gid = blockIdx.x * blockDim.x + threadIdx.x; gid < total; gid += step) {
+    const unsigned c = gid % C8;
+    unsigned p = gid / C8;
+    const unsigned wb = p % Wo;
+    p /= Wo;
+    const unsigned ha = p % Ho;
+    const unsigned b = p / Ho;
+    float acc[2][2][8];
 #pragma unroll
-      for (int e = 0; e < 8; ++e) {
-        const uint32_t word = e < 4 ? iv.x : iv.y;
-        if (((word >> (8 * (e & 3))) & 0xffu) == me) acc[e] += g[e];
+    for (int i = 0; i < 2; ++i)
+#pragma unroll
+      for (int j = 0; j < 2; ++j)
+#pragma unroll
+        for (int e = 0; e < 8; ++e) acc[i][j][e] = 0.f;
+#pragma unroll
+    for (int dh = 0; dh < 2; ++dh) {
+      const unsigned ho = ha + dh;
+      if (ho >= static_cast<unsigned>(Ho)) continue;
+#pragma unroll
+      for (int dw = 0; dw < 2; ++dw) {
+        const unsigned wo = wb + dw;
+        if (wo >= static_cast<unsigned>(Wo)) continue;
+        const long long o = ((static_cast<long long>(b) * Ho + ho) * Wo + wo) * C8 + c;
+        const uint2 iv = __ldg(idx + o);
+        float g[8];
+        unpack8(__ldg(dout + o), g);
+        // window (ho, wo) covers input rows 2ho-1..2ho+1: of this block, rows i with r = 2ha + i - (2ho - 1) in [0, 3)
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+          const int r = i + 1 - 2 * dh;  // dh = 0: r = 1, 2;  dh = 1: r = -1 (not covered), 0
+          if (r < 0) continue;
+#pragma unroll
+          for (int j = 0; j < 2; ++j) {
+            const int sft = j + 1 - 2 * dw;
+            if (sft < 0) continue;
+            const uint32_t me = static_cast<uint32_t>(r * 3 + sft);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+              const uint32_t word = e < 4 ? iv.x : iv.y;
+              if (((word >> (8 * (e & 3))) & 0xffu) == me) acc[i][j][e] += g[e];
+            }
+          }
+        }
       }
     }
+#pragma unroll
+    for (int i = 0; i < 2; ++i)
+#pragma unroll
+      for (int j = 0; j < 2; ++j)
+        din[((static_cast<long long>(b) * H + 2 * ha + i) * W + 2 * wb + j) * C8 + c] = pack8(acc[i][j]);
   }
-  din[gid] = pack8(acc);
 }
 
 }  // namespace pb200
@@ -683,8 +707,11 @@ extern "C" int pb200_train_maxpool_backward(const void* dout, const void* idx, v
   if (int rc = require_device()) return rc;
   PB_CHECK(dout && idx && din && C % 8 == 0 && H % 2 == 0 && W % 2 == 0, "train_maxpool_backward: bad argument");
   const int Ho = H / 2, Wo = W / 2;
-  const long long total = static_cast<long long>(B) * H * W * (C / 8);
-  maxpool_bwd_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+  const long long total = static_cast<long long>(B) * Ho * Wo * (C / 8);
+  PB_CHECK(total < (1LL << 31), "train_maxpool_backward: tensor too large");
+  long long grid = (total + 255) / 256;
+  if (grid > static_cast<long long>(num_sms()) * 8) grid = static_cast<long long>(num_sms()) * 8;
+  maxpool_bwd_kernel<<<static_cast<unsigned>(grid), 256, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const uint4*>(dout), static_cast<const uint2*>(idx), static_cast<uint4*>(din), B, H, W, C / 8, Ho, Wo);
   PB_CUDA(cudaGetLastError());
   return PB200_OK;
@@ -753,20 +780,40 @@ smooth_l1_kernel(const float* __restrict__ pred, const float* __restrict__ targe
   if (threadIdx.x == 0) *loss = s_part[0] * invn;
 }
 
-// d fc.weight[o][c] = sum_b dpred[b][o] feat[b][c]; d fc.bias[o] = sum_b dpred[b][o]   (grid = n_out CTAs)
+// d fc.weight[o][c] = sum_b dpred[b][o] feat[b][c]; d fc.bias[o] = sum_b dpred[b][o].  CTA = 32 channels (lanes) x 8 batch
+// slices (warps); a thread keeps all n_out (<= 32) partial sums of its channel, the warps are combined through shared
+// memory.  (One CTA per output walking the whole batch sequentially took 110 us for 0.5 MB of input.)
 __global__ void __launch_bounds__(256)
 head_bwd_params_kernel(const float* __restrict__ dpred, const float* __restrict__ feat, int B, int C, int n_out,
                        float* __restrict__ dW, float* __restrict__ db) {
-  const int o = blockIdx.x;
-  for (int c = threadIdx.x; c < C; c += 256) {
-    float acc = 0.f;
-    for (int b = 0; b < B; ++b) acc = fmaf(dpred[b * n_out + o], feat[static_cast<long long>(b) * C + c], acc);
-    dW[o * C + c] = acc;
+  __shared__ float s_part[8][32][33];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + lane;
+  float acc[32];
+#pragma unroll
+  for (int o = 0; o < 32; ++o) acc[o] = 0.f;
+  if (c < C) {
+    for (int b = warp; b < B; b += 8) {
+      const float f = __ldg(feat + static_cast<long long>(b) * C + c);
+#pragma unroll
+      for (int o = 0; o < 32; ++o)
+        if (o < n_out) acc[o] = fmaf(__ldg(dpred + b * n_out + o), f, acc[o]);
+    }
   }
-  if (threadIdx.x == 0) {
-    float acc = 0.f;
-    for (int b = 0; b < B; ++b) acc += dpred[b * n_out + o];
-    db[o] = acc;
+#pragma unroll
+  for (int o = 0; o < 32; ++o) s_part[warp][o][lane] = acc[o];
+  __syncthreads();
+  for (int i = threadIdx.x; i < n_out * 32; i += 256) {
+    const int o = i >> 5, l = i & 31;
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) t += s_part[w][o][l];
+    if (blockIdx.x * 32 + l < C) dW[o * C + blockIdx.x * 32 + l] = t;
+  }
+  if (blockIdx.x == 0 && threadIdx.x < n_out) {
+    float t = 0.f;
+    for (int b = 0; b < B; ++b) t += dpred[b * n_out + threadIdx.x];
+    db[threadIdx.x] = t;
   }
 }
 
@@ -856,7 +903,8 @@ extern "C" int pb200_train_head_backward(const float* dpred, const float* feat, 
   if (int rc = require_device()) return rc;
   PB_CHECK(dpred && feat && fc_w && d_fc_w && d_fc_b && dy_nhwc, "train_head_backward: null argument");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  head_bwd_params_kernel<<<n_out, 256, 0, st>>>(dpred, feat, B, C, n_out, d_fc_w, d_fc_b);
+  PB_CHECK(n_out >= 1 && n_out <= 32, "train_head_backward: n_out = %d unsupported (1..32)", n_out);
+  head_bwd_params_kernel<<<(C + 31) / 32, 256, 0, st>>>(dpred, feat, B, C, n_out, d_fc_w, d_fc_b);
   head_bwd_input_kernel<<<B, 256, sizeof(float) * C, st>>>(dpred, fc_w, HW, C, n_out, static_cast<__nv_bfloat16*>(dy_nhwc));
   PB_CUDA(cudaGetLastError());
   return PB200_OK;
