@@ -206,8 +206,9 @@ int pb200_factors_constvel(const double* vel1, const double* vel2, double* resid
 int pb200_train_pack_weights(const float* w_oihw, int Cout, int Cin, int R, int mode, void* out_bf16,
                              pb200_stream stream);
 /* every weight pack of a step in one launch.  table_dev: int64 [n][8] on the device, one row per conv:
- * {w fp32 OIHW ptr, forward operand ptr, data-gradient operand ptr or 0, Cout, Cin, R, first element index,
- *  kind (0 conv, 1 conv1 -> [64][256] im2col operand)}; total = sum of the element counts. */
+ * {w fp32 OIHW ptr, forward operand ptr, data-gradient operand ptr or 0, Cout, Cin, R, first TILE index,
+ *  kind (0 conv, 1 conv1 -> [64][256] im2col operand)}; a conv has (Cout/32)*(Cin/32) tiles (both multiples of 32),
+ *  conv1 has 64; total = sum of the tile counts. */
 int pb200_train_pack_all(const int64_t* table_dev, int n, int64_t total, pb200_stream stream);
 /* convolution on NHWC bf16 with device-packed weights; out = [relu](conv + bias [+ residual]).
  * stats_or_null: double [2][Cout], ZEROED BY THE CALLER: the epilogue adds the per-channel sum and sum of squares of the

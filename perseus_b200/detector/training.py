@@ -255,7 +255,8 @@ class NativeTrainer:
         if self._pack_table is None:
             rows, start = [], 0
             for c in self.convs:
-                n = 64 * 256 if c.stem else c.Cout * c.Cin * c.R * c.R
+                # tiles of the pack kernel: 256 elements of conv1's [64][256] operand, else 32 x 32 channels x R*R taps
+                n = 64 if c.stem else (c.Cout // 32) * (c.Cin // 32)
                 rows.append([c.conv.weight.data_ptr(), c.w_fwd.data_ptr(), 0 if c.stem else c.w_dgrad.data_ptr(), c.Cout,
                              c.Cin_real if c.stem else c.Cin, c.R, start, 1 if c.stem else 0])
                 start += n

@@ -434,3 +434,35 @@ def test_strided_and_statistics_epilogues_stay_inside_their_tensors():
     torch.cuda.synchronize()
     assert bool((arena2[:guard] == 3.0).all()) and bool((arena2[guard + n2:] == 3.0).all())
     assert bool((sarena[:64] == -1).all()) and bool((sarena[64 + 2 * Cout:] == -1).all())
+
+
+def test_pack_all_equals_the_single_packs():
+    """pb200_train_pack_all (tile-staged, one launch for every conv) == pb200_train_pack_weights / _stem_pack per conv."""
+    L = _lib()
+    g = torch.Generator().manual_seed(5)
+    specs = [(64, 4, 7, True), (64, 64, 3, False), (128, 64, 3, False), (128, 64, 1, False), (512, 256, 3, False)]
+    rows, keep, start = [], [], 0
+    for Cout, Cin, R, stem in specs:
+        w = torch.randn(Cout, Cin, R, R, generator=g).cuda().contiguous()
+        n = 64 * 256 if stem else Cout * Cin * R * R
+        fwd = torch.full((n,), float("nan"), dtype=torch.bfloat16, device="cuda")
+        dgr = None if stem else torch.full((n,), float("nan"), dtype=torch.bfloat16, device="cuda")
+        tiles = 64 if stem else (Cout // 32) * (Cin // 32)
+        rows.append([w.data_ptr(), fwd.data_ptr(), 0 if stem else dgr.data_ptr(), Cout, Cin, R, start, 1 if stem else 0])
+        start += tiles
+        keep.append((w, fwd, dgr))
+    table = torch.tensor(rows, dtype=torch.int64, device="cuda")
+    L.check(L.lib().pb200_train_pack_all(table.data_ptr(), len(specs), start, _stream()))
+    torch.cuda.synchronize()
+    for (Cout, Cin, R, stem), (w, fwd, dgr) in zip(specs, keep):
+        ref = torch.empty_like(fwd)
+        if stem:
+            L.check(L.lib().pb200_train_stem_pack(w.data_ptr(), Cin, ref.data_ptr(), _stream()))
+        else:
+            L.check(L.lib().pb200_train_pack_weights(w.data_ptr(), Cout, Cin, R, 0, ref.data_ptr(), _stream()))
+        torch.cuda.synchronize()
+        assert torch.equal(fwd.view(torch.int16), ref.view(torch.int16)), (Cout, Cin, R, "forward operand")
+        if dgr is not None:
+            L.check(L.lib().pb200_train_pack_weights(w.data_ptr(), Cout, Cin, R, 1, ref.data_ptr(), _stream()))
+            torch.cuda.synchronize()
+            assert torch.equal(dgr.view(torch.int16), ref.view(torch.int16)), (Cout, Cin, R, "data-gradient operand")
