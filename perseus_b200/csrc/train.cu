@@ -553,11 +553,11 @@ __global__ void stem_unpack_kernel(const float* __restrict__ scratch, int C, flo
 __global__ void __launch_bounds__(256)
 maxpool_train_kernel(const uint4* __restrict__ in, uint4* __restrict__ out, uint2* __restrict__ idx, int B, int H, int W,
                      int C8, int Ho, int Wo) {
-  const long long total = static_cast<long long>(B) * Ho * Wo * C8;
-  const long long gid = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (gid >= total) return;
+  const unsigned total = static_cast<unsigned>(B) * Ho * Wo * C8;  // host: < 2^31
+  const unsigned gstep = gridDim.x * blockDim.x;
+  for (unsigned gid = blockIdx.x * blockDim.x + threadIdx.x; gid < total; gid += gstep) {  // one resident wave
   const int c = static_cast<int>(gid % C8);
-  long long p = gid / C8;
+  unsigned p = gid / C8;
   const int wo = static_cast<int>(p % Wo);
   p /= Wo;
   const int ho = static_cast<int>(p % Ho);
@@ -590,6 +590,7 @@ maxpool_train_kernel(const uint4* __restrict__ in, uint4* __restrict__ out, uint
   out[gid] = pack8(m);
   idx[gid] = make_uint2(am[0] | (am[1] << 8) | (am[2] << 16) | (am[3] << 24),
                         am[4] | (am[5] << 8) | (am[6] << 16) | (am[7] << 24));
+  }
 }
 
 // gather form: every input pixel sums the gradients of the (<= 4) windows whose argmax it is.  A thread owns the 2x2
@@ -696,7 +697,10 @@ extern "C" int pb200_train_maxpool(const void* in, void* out, void* idx, int B, 
   PB_CHECK(in && out && idx && C % 8 == 0 && H % 2 == 0 && W % 2 == 0, "train_maxpool: bad argument");
   const int Ho = H / 2, Wo = W / 2;
   const long long total = static_cast<long long>(B) * Ho * Wo * (C / 8);
-  maxpool_train_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+  PB_CHECK(total < (1LL << 31), "train_maxpool: tensor too large");
+  long long grid = (total + 255) / 256;
+  if (grid > static_cast<long long>(num_sms()) * 8) grid = static_cast<long long>(num_sms()) * 8;
+  maxpool_train_kernel<<<static_cast<unsigned>(grid), 256, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const uint4*>(in), static_cast<uint4*>(out), static_cast<uint2*>(idx), B, H, W, C / 8, Ho, Wo);
   PB_CUDA(cudaGetLastError());
   return PB200_OK;
