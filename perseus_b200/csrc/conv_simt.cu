@@ -97,6 +97,119 @@ __global__ void __launch_bounds__(256) conv_simt_kernel(SimtConv c) {
   }
 }
 
+// ---- dedicated fp32 stem (conv1 7x7/2 on the zero-margined frames buffer) ------------------------------
+// The generic kernel above gathers one scalar per (pixel, k) with a division per K step; on the stem (the
+// largest GEMM of the fp32 and split-bf16 modes: M = B*128*128, K = 224) it is shared-memory bound.  Here a
+// persistent CTA keeps the whole [224][64] filter in shared memory and walks 8 x 32 output tiles: the input
+// patch (21 rows x 70 pixels x 4 channels) is staged once, split by column parity so that the 32 lanes of a
+// warp (= 32 consecutive output columns of a stride-2 conv) read consecutive 16-byte pixels for every tap;
+// a warp owns 8 output channels (filter reads are broadcasts), a thread 8 output rows x 8 channels.
+// Same K order (r, tap, channel) as the generic kernel, so the sums are bit-identical; the zero-weight
+// tap 0 (layout.h) and, for RGB models, the empty fourth channel are skipped.
+constexpr int ST_ROWS = 8, ST_COLS = 32;
+constexpr int ST_PR = 2 * ST_ROWS + 5;   // patch rows
+constexpr int ST_PCOLS = 2 * ST_COLS + 6;  // patch pixels per row
+constexpr int ST_PC = 36;                // float4 per parity plane and row (35 used)
+constexpr int ST_W_BYTES = kStemK * 64 * 4;
+constexpr int ST_SMEM = ST_W_BYTES + 2 * ST_PR * ST_PC * 16;
+
+template <int NC>
+__global__ void __launch_bounds__(256, 2)
+stem_f32_kernel(const float4* __restrict__ frames, const float* __restrict__ w, const float* __restrict__ bias,
+                float* __restrict__ out, int B, int H, int W, int relu) {
+  extern __shared__ __align__(16) unsigned char st_smem[];
+  float4* ws = reinterpret_cast<float4*>(st_smem);                  // [k][16] float4 = [k][co]
+  float4* patch = reinterpret_cast<float4*>(st_smem + ST_W_BYTES);  // [parity][row][ST_PC]
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int i = tid; i < kStemK * 16; i += 256) ws[i] = __ldg(reinterpret_cast<const float4*>(w) + i);
+  const int Ho = H / 2, Wo = W / 2, FH = H + kFrameMarginTop + kFrameMarginBottom,
+            FW = W + kFrameMarginLeft + kFrameMarginRight;
+  const int tiles_x = Wo / ST_COLS, tiles_y = Ho / ST_ROWS;
+  const long long ntiles = static_cast<long long>(B) * tiles_y * tiles_x;
+  float bv[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) bv[j] = __ldg(bias + warp * 8 + j);
+
+  for (long long t = blockIdx.x; t < ntiles; t += gridDim.x) {
+    const int tx = static_cast<int>(t % tiles_x);
+    const int ty = static_cast<int>((t / tiles_x) % tiles_y);
+    const long long b = t / (static_cast<long long>(tiles_x) * tiles_y);
+    const float4* src = frames + (b * FH + 2 * ty * ST_ROWS) * FW + 2 * tx * ST_COLS;
+    __syncthreads();  // the previous tile's reads of the patch are done
+    for (int i = tid; i < ST_PR * ST_PCOLS; i += 256) {
+      const int r = i / ST_PCOLS, c = i - r * ST_PCOLS;
+      patch[((c & 1) * ST_PR + r) * ST_PC + (c >> 1)] = __ldg(src + static_cast<long long>(r) * FW + c);
+    }
+    __syncthreads();
+    float acc[8][8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+#pragma unroll 1
+    for (int r = 0; r < 7; ++r) {
+#pragma unroll
+      for (int s8 = 1; s8 < kStemTaps; ++s8) {
+        const float4* pa = patch + ((s8 & 1) * ST_PR + r) * ST_PC + (s8 >> 1) + lane;
+        float4 a[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) a[i] = pa[2 * i * ST_PC];  // output row i reads patch row 2i + r
+        const float4* wk = ws + (r * (kStemTaps * kFrameC) + s8 * kFrameC) * 16 + warp * 2;
+#pragma unroll
+        for (int c = 0; c < NC; ++c) {
+          const float4 w0 = wk[c * 16], w1 = wk[c * 16 + 1];
+          const float wv[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const float av = c == 0 ? a[i].x : (c == 1 ? a[i].y : (c == 2 ? a[i].z : a[i].w));
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(av, wv[j], acc[i][j]);
+          }
+        }
+      }
+    }
+    float* o = out + ((b * Ho + ty * ST_ROWS) * Wo + tx * ST_COLS + lane) * 64 + warp * 8;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      float v[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        v[j] = acc[i][j] + bv[j];
+        if (relu) v[j] = fmaxf(v[j], 0.f);
+      }
+      float4* dst = reinterpret_cast<float4*>(o + static_cast<long long>(i) * Wo * 64);
+      dst[0] = make_float4(v[0], v[1], v[2], v[3]);
+      dst[1] = make_float4(v[4], v[5], v[6], v[7]);
+    }
+  }
+}
+
+bool stem_f32_supported(const SimtConv& c) {
+  return c.Cin == kFrameC && c.R == 7 && c.S == kStemTaps && c.stride == 2 && c.pad == 0 && c.Cout == 64 &&
+         c.residual == nullptr && c.Ho % ST_ROWS == 0 && c.Wo % ST_COLS == 0 &&
+         c.Hin == 2 * c.Ho + kFrameMarginTop + kFrameMarginBottom &&
+         c.Win == 2 * c.Wo + kFrameMarginLeft + kFrameMarginRight;
+}
+
+int launch_stem_f32(const SimtConv& c, int real_channels, cudaStream_t st) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    PB_CUDA(cudaFuncSetAttribute(stem_f32_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, ST_SMEM));
+    PB_CUDA(cudaFuncSetAttribute(stem_f32_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, ST_SMEM));
+    attr_set = true;
+  }
+  const long long ntiles = static_cast<long long>(c.B) * (c.Ho / ST_ROWS) * (c.Wo / ST_COLS);
+  const long long cap = 2LL * num_sms();
+  const unsigned grid = static_cast<unsigned>(ntiles < cap ? ntiles : cap);
+  const float4* in = reinterpret_cast<const float4*>(c.in);
+  if (real_channels <= 3)
+    stem_f32_kernel<3><<<grid, 256, ST_SMEM, st>>>(in, c.w, c.bias, c.out, c.B, 2 * c.Ho, 2 * c.Wo, c.relu);
+  else
+    stem_f32_kernel<4><<<grid, 256, ST_SMEM, st>>>(in, c.w, c.bias, c.out, c.B, 2 * c.Ho, 2 * c.Wo, c.relu);
+  PB_CUDA(cudaGetLastError());
+  return PB200_OK;
+}
+
 int launch_conv_simt(const SimtConv& c, cudaStream_t st) {
   const long long M = static_cast<long long>(c.B) * c.Ho * c.Wo;
   dim3 grid(static_cast<unsigned>((M + SBM - 1) / SBM), static_cast<unsigned>((c.Cout + SBN - 1) / SBN));

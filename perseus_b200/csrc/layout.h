@@ -92,5 +92,8 @@ struct SimtConv {
   int B, Hin, Win, Cin, Ho, Wo, Cout, R, S, stride, pad, relu;
 };
 int launch_conv_simt(const SimtConv& c, cudaStream_t st);
+// dedicated fp32 stem over the frames buffer (fp32 and split-bf16 modes); real_channels = the model's 3 or 4
+bool stem_f32_supported(const SimtConv& c);
+int launch_stem_f32(const SimtConv& c, int real_channels, cudaStream_t st);
 
 }  // namespace pb200

@@ -502,6 +502,7 @@ static int run_op(pb200_plan* pl, const Op& op, const void* frames, void* ws, fl
       } else {
         s.Hin = c.Hin; s.Win = c.Win; s.Cin = c.Cin; s.R = c.R; s.S = c.R; s.stride = c.stride; s.pad = c.pad;
       }
+      if (c.stem && stem_f32_supported(s)) return launch_stem_f32(s, pl->C, st);
       return launch_conv_simt(s, st);
     }
     case OP_STEM_POOL: {
@@ -588,7 +589,8 @@ extern "C" const char* pb200_plan_op_kernel(const pb200_plan* plan, int i) {
     case OP_MAXPOOL: k = plan->split ? "maxpool_split_kernel" : (plan->bf16 ? "maxpool_bf16_kernel" : "maxpool_f32_kernel"); break;
     case OP_HEAD: k = "head_kernel"; break;
     case OP_CONV:
-      if (!plan->bf16 && !(plan->split && !plan->convs[op.conv].stem)) k = "conv_simt_kernel";
+      if (!plan->bf16 && !(plan->split && !plan->convs[op.conv].stem))
+        k = (plan->convs[op.conv].stem && plan->H % 16 == 0 && plan->W % 64 == 0) ? "stem_f32_kernel" : "conv_simt_kernel";
       else if (plan->cache_B < 0 || plan->umma.size() != plan->convs.size()) k = "conv_umma*";
       else {
         const UmmaConvLaunch& L = plan->umma[op.conv];
