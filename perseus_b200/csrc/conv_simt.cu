@@ -2,6 +2,7 @@
 // reproduces the reference's fp32 forward to <= 1e-3 px.  FFMA only, fp32 accumulation in K
 // order; eval-mode BatchNorm is already folded into w / bias, ReLU and the residual add are
 // fused in the epilogue (torchvision BasicBlock.forward, resnet.py:89-105).
+#include <cstdlib>
 #include "common.cuh"
 #include "layout.h"
 
@@ -113,7 +114,7 @@ constexpr int ST_PC = 36;                // float4 per parity plane and row (35 
 constexpr int ST_W_BYTES = kStemK * 64 * 4;
 constexpr int ST_SMEM = ST_W_BYTES + 2 * ST_PR * ST_PC * 16;
 
-template <int NC>
+template <int NC, bool PACKED>
 __global__ void __launch_bounds__(256, 2)
 stem_f32_kernel(const float4* __restrict__ frames, const float* __restrict__ w, const float* __restrict__ bias,
                 float* __restrict__ out, int B, int H, int W, int relu) {
@@ -141,11 +142,12 @@ stem_f32_kernel(const float4* __restrict__ frames, const float* __restrict__ w, 
       patch[((c & 1) * ST_PR + r) * ST_PC + (c >> 1)] = __ldg(src + static_cast<long long>(r) * FW + c);
     }
     __syncthreads();
-    float acc[8][8];
+    // accumulators as channel pairs: one FFMA2 (fma.rn.f32x2) per pair, same per-element arithmetic and order
+    float2 acc[8][4];
 #pragma unroll
     for (int i = 0; i < 8; ++i)
 #pragma unroll
-      for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+      for (int j = 0; j < 4; ++j) acc[i][j] = make_float2(0.f, 0.f);
 #pragma unroll 1
     for (int r = 0; r < 7; ++r) {
 #pragma unroll
@@ -158,12 +160,21 @@ stem_f32_kernel(const float4* __restrict__ frames, const float* __restrict__ w, 
 #pragma unroll
         for (int c = 0; c < NC; ++c) {
           const float4 w0 = wk[c * 16], w1 = wk[c * 16 + 1];
-          const float wv[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+          const float2 wv[4] = {make_float2(w0.x, w0.y), make_float2(w0.z, w0.w), make_float2(w1.x, w1.y),
+                                make_float2(w1.z, w1.w)};
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
             const float av = c == 0 ? a[i].x : (c == 1 ? a[i].y : (c == 2 ? a[i].z : a[i].w));
+            const float2 av2 = make_float2(av, av);
 #pragma unroll
-            for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(av, wv[j], acc[i][j]);
+            for (int j = 0; j < 4; ++j) {
+              if (PACKED) {
+                acc[i][j] = __ffma2_rn(av2, wv[j], acc[i][j]);
+              } else {
+                acc[i][j].x = fmaf(av, wv[j].x, acc[i][j].x);
+                acc[i][j].y = fmaf(av, wv[j].y, acc[i][j].y);
+              }
+            }
           }
         }
       }
@@ -173,9 +184,13 @@ stem_f32_kernel(const float4* __restrict__ frames, const float* __restrict__ w, 
     for (int i = 0; i < 8; ++i) {
       float v[8];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        v[j] = acc[i][j] + bv[j];
-        if (relu) v[j] = fmaxf(v[j], 0.f);
+      for (int j = 0; j < 4; ++j) {
+        v[2 * j] = acc[i][j].x + bv[2 * j];
+        v[2 * j + 1] = acc[i][j].y + bv[2 * j + 1];
+      }
+      if (relu) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = fmaxf(v[j], 0.f);
       }
       float4* dst = reinterpret_cast<float4*>(o + static_cast<long long>(i) * Wo * 64);
       dst[0] = make_float4(v[0], v[1], v[2], v[3]);
@@ -192,20 +207,23 @@ bool stem_f32_supported(const SimtConv& c) {
 }
 
 int launch_stem_f32(const SimtConv& c, int real_channels, cudaStream_t st) {
+  // PB200_STEM_F32_SCALAR=1 selects the scalar-FFMA build of the same kernel (A/B of the packed FFMA2 issue rate)
+  static const bool scalar = [] { const char* e = getenv("PB200_STEM_F32_SCALAR"); return e && e[0] == '1'; }();
   static bool attr_set = false;
   if (!attr_set) {
-    PB_CUDA(cudaFuncSetAttribute(stem_f32_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, ST_SMEM));
-    PB_CUDA(cudaFuncSetAttribute(stem_f32_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, ST_SMEM));
+    PB_CUDA(cudaFuncSetAttribute(stem_f32_kernel<3, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, ST_SMEM));
+    PB_CUDA(cudaFuncSetAttribute(stem_f32_kernel<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, ST_SMEM));
+    PB_CUDA(cudaFuncSetAttribute(stem_f32_kernel<3, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, ST_SMEM));
+    PB_CUDA(cudaFuncSetAttribute(stem_f32_kernel<4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, ST_SMEM));
     attr_set = true;
   }
   const long long ntiles = static_cast<long long>(c.B) * (c.Ho / ST_ROWS) * (c.Wo / ST_COLS);
   const long long cap = 2LL * num_sms();
   const unsigned grid = static_cast<unsigned>(ntiles < cap ? ntiles : cap);
   const float4* in = reinterpret_cast<const float4*>(c.in);
-  if (real_channels <= 3)
-    stem_f32_kernel<3><<<grid, 256, ST_SMEM, st>>>(in, c.w, c.bias, c.out, c.B, 2 * c.Ho, 2 * c.Wo, c.relu);
-  else
-    stem_f32_kernel<4><<<grid, 256, ST_SMEM, st>>>(in, c.w, c.bias, c.out, c.B, 2 * c.Ho, 2 * c.Wo, c.relu);
+  auto k = real_channels <= 3 ? (scalar ? stem_f32_kernel<3, false> : stem_f32_kernel<3, true>)
+                              : (scalar ? stem_f32_kernel<4, false> : stem_f32_kernel<4, true>);
+  k<<<grid, 256, ST_SMEM, st>>>(in, c.w, c.bias, c.out, c.B, 2 * c.Ho, 2 * c.Wo, c.relu);
   PB_CUDA(cudaGetLastError());
   return PB200_OK;
 }
