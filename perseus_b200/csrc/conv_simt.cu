@@ -114,7 +114,7 @@ constexpr int ST_PC = 36;                // float4 per parity plane and row (35 
 constexpr int ST_W_BYTES = kStemK * 64 * 4;
 constexpr int ST_SMEM = ST_W_BYTES + 2 * ST_PR * ST_PC * 16;
 
-template <int NC, bool PACKED>
+template <int NC, int MODE>  // MODE 0: scalar FFMA, 1: FFMA2, 2: FFMA2 for six of the eight rows + scalar FFMA for two
 __global__ void __launch_bounds__(256, 2)
 stem_f32_kernel(const float4* __restrict__ frames, const float* __restrict__ w, const float* __restrict__ bias,
                 float* __restrict__ out, int B, int H, int W, int relu) {
@@ -168,7 +168,7 @@ stem_f32_kernel(const float4* __restrict__ frames, const float* __restrict__ w, 
             const float2 av2 = make_float2(av, av);
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-              if (PACKED) {
+              if (MODE == 1 || (MODE == 2 && (i % 4) != 3)) {
                 acc[i][j] = __ffma2_rn(av2, wv[j], acc[i][j]);
               } else {
                 acc[i][j].x = fmaf(av, wv[j].x, acc[i][j].x);
@@ -207,22 +207,23 @@ bool stem_f32_supported(const SimtConv& c) {
 }
 
 int launch_stem_f32(const SimtConv& c, int real_channels, cudaStream_t st) {
-  // PB200_STEM_F32_SCALAR=1 selects the scalar-FFMA build of the same kernel (A/B of the packed FFMA2 issue rate)
-  static const bool scalar = [] { const char* e = getenv("PB200_STEM_F32_SCALAR"); return e && e[0] == '1'; }();
+  // PB200_STEM_F32_MODE=0/1/2 selects the scalar-FFMA, packed-FFMA2 (default) or mixed build of the same kernel (A/B)
+  static const int mode = [] { const char* e = getenv("PB200_STEM_F32_MODE"); return e ? atoi(e) : 1; }();
+  typedef void (*kern_t)(const float4*, const float*, const float*, float*, int, int, int, int);
+  static const kern_t table[2][3] = {{stem_f32_kernel<3, 0>, stem_f32_kernel<3, 1>, stem_f32_kernel<3, 2>},
+                                     {stem_f32_kernel<4, 0>, stem_f32_kernel<4, 1>, stem_f32_kernel<4, 2>}};
   static bool attr_set = false;
   if (!attr_set) {
-    PB_CUDA(cudaFuncSetAttribute(stem_f32_kernel<3, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, ST_SMEM));
-    PB_CUDA(cudaFuncSetAttribute(stem_f32_kernel<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, ST_SMEM));
-    PB_CUDA(cudaFuncSetAttribute(stem_f32_kernel<3, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, ST_SMEM));
-    PB_CUDA(cudaFuncSetAttribute(stem_f32_kernel<4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, ST_SMEM));
+    for (int a = 0; a < 2; ++a)
+      for (int m = 0; m < 3; ++m)
+        PB_CUDA(cudaFuncSetAttribute(table[a][m], cudaFuncAttributeMaxDynamicSharedMemorySize, ST_SMEM));
     attr_set = true;
   }
   const long long ntiles = static_cast<long long>(c.B) * (c.Ho / ST_ROWS) * (c.Wo / ST_COLS);
   const long long cap = 2LL * num_sms();
   const unsigned grid = static_cast<unsigned>(ntiles < cap ? ntiles : cap);
   const float4* in = reinterpret_cast<const float4*>(c.in);
-  auto k = real_channels <= 3 ? (scalar ? stem_f32_kernel<3, false> : stem_f32_kernel<3, true>)
-                              : (scalar ? stem_f32_kernel<4, false> : stem_f32_kernel<4, true>);
+  const kern_t k = table[real_channels <= 3 ? 0 : 1][mode >= 0 && mode <= 2 ? mode : 1];
   k<<<grid, 256, ST_SMEM, st>>>(in, c.w, c.bias, c.out, c.B, 2 * c.Ho, 2 * c.Wo, c.relu);
   PB_CUDA(cudaGetLastError());
   return PB200_OK;
