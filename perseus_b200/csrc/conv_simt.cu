@@ -207,8 +207,11 @@ bool stem_f32_supported(const SimtConv& c) {
 }
 
 int launch_stem_f32(const SimtConv& c, int real_channels, cudaStream_t st) {
-  // PB200_STEM_F32_MODE=0/1/2 selects the scalar-FFMA, packed-FFMA2 (default) or mixed build of the same kernel (A/B)
-  static const int mode = [] { const char* e = getenv("PB200_STEM_F32_MODE"); return e ? atoi(e) : 1; }();
+  // PB200_STEM_F32_MODE (read per call, for A/B and the parity test): 0 scalar FFMA, 1 packed FFMA2 (default),
+  // 2 mixed, -1 the generic conv_simt_kernel on this layer
+  const char* env = getenv("PB200_STEM_F32_MODE");
+  const int mode = env ? atoi(env) : 1;
+  if (mode < 0) return launch_conv_simt(c, st);
   typedef void (*kern_t)(const float4*, const float*, const float*, float*, int, int, int, int);
   static const kern_t table[2][3] = {{stem_f32_kernel<3, 0>, stem_f32_kernel<3, 1>, stem_f32_kernel<3, 2>},
                                      {stem_f32_kernel<4, 0>, stem_f32_kernel<4, 1>, stem_f32_kernel<4, 2>}};

@@ -359,6 +359,22 @@ def test_forward_fp32_mode_matches_reference(C):
         assert mx64 <= tol
 
 
+@pytest.mark.parametrize("mode", ["0", "1", "2"])
+@pytest.mark.parametrize("C", [3, 4])
+def test_stem_f32_kernel_bit_identical_to_generic_simt_conv(C, mode, monkeypatch):
+    """The dedicated fp32 stem (conv_simt.cu::stem_f32_kernel, scalar / FFMA2 / mixed builds) keeps the generic
+    kernel's K order, so the whole fp32 forward must not change by a single bit; odd batch = ragged last wave."""
+    model, _ = gu.native_model(C, "fp32", seed=0, randomize_bn=True)
+    g = torch.Generator().manual_seed(11)
+    x = torch.rand(5, C, 256, 256, generator=g).cuda()
+    monkeypatch.setenv("PB200_STEM_F32_MODE", "-1")
+    want = model(x).clone()
+    monkeypatch.setenv("PB200_STEM_F32_MODE", mode)
+    got = model(x).clone()
+    assert torch.isfinite(want).all()
+    assert torch.equal(got, want)
+
+
 @pytest.mark.parametrize("C", [3, 4])
 def test_forward_bf16_mode_matches_operand_matched_reference(C):
     model, sd = gu.native_model(C, "bf16")
