@@ -57,6 +57,8 @@ extern "C" {
 #define PB200_PREC_FP32 0   /* SIMT fp32 FFMA implicit GEMM: the <=1e-3 px parity mode          */
 #define PB200_PREC_BF16 1   /* tcgen05 kind::f16 bf16 x bf16 -> fp32 TMEM: the throughput mode   */
 #define PB200_PREC_BF16X3 2 /* split-bf16 (hi*hi + lo*hi + hi*lo) on tcgen05: tensor parity mode */
+#define PB200_PREC_FP16X2 3 /* fp16 activations x (fp16 hi + fp16 lo) weights on tcgen05, two MMAs per K step
+                             * on one activation tile: the tensor mode that meets 0.05 px (RGB) at speed */
 
 typedef struct pb200_plan pb200_plan;
 typedef void* pb200_stream; /* cudaStream_t */
@@ -164,6 +166,18 @@ int pb200_debug_stem_pool(pb200_plan* plan, const void* frames, void* out_p8, in
 int pb200_debug_conv_p8(const void* in_p8, int B, int H, int W, const float* w_oihw_host,
                         const float* bias_host, const void* residual_p8_or_null, int relu, void* out,
                         int out_nhwc, pb200_stream stream);
+/* The same two layer entries in the "fp16x2" mode (PB200_PREC_FP16X2): activations, residual and output are fp16
+ * (NHWC / P8), the fp32 HOST weights are split into fp16 hi + fp16 lo internally.  pb200_debug_conv_f16x2 optionally
+ * accumulates the 1x1/2 projection of ds_in [B][2H][2W][ds_Cin] (weights wds [Cout][ds_Cin]) into the same tile
+ * (R = 3, stride 1 only); pass NULL / 0 / NULL for a plain conv. */
+int pb200_debug_conv_f16x2(const void* in_nhwc, int B, int H, int W, int Cin, const float* w_oihw_host,
+                           const float* bias_host, int Cout, int R, int stride, int pad,
+                           const void* residual_nhwc_or_null, int relu, void* out_nhwc,
+                           const void* ds_in_nhwc_or_null, int ds_Cin, const float* wds_oi_host_or_null,
+                           pb200_stream stream);
+int pb200_debug_conv_p8_f16x2(const void* in_p8, int B, int H, int W, const float* w_oihw_host,
+                              const float* bias_host, const void* residual_p8_or_null, int relu, void* out,
+                              int out_nhwc, pb200_stream stream);
 
 /* ---- smoother factors (float64, batched) ---------------------------------------------- */
 

@@ -12,8 +12,8 @@ from ctypes import POINTER, c_char_p, c_double, c_float, c_int, c_int64, c_size_
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libperseus_b200.so")
 
-PREC_FP32, PREC_BF16, PREC_BF16X3 = 0, 1, 2
-PRECISIONS = {"fp32": PREC_FP32, "bf16": PREC_BF16, "bf16x3": PREC_BF16X3}
+PREC_FP32, PREC_BF16, PREC_BF16X3, PREC_FP16X2 = 0, 1, 2, 3
+PRECISIONS = {"fp32": PREC_FP32, "bf16": PREC_BF16, "bf16x3": PREC_BF16X3, "fp16x2": PREC_FP16X2}
 
 ERR_NO_DEVICE = 3
 
@@ -68,6 +68,14 @@ SIGNATURES = {
     ),
     "pb200_debug_stem_pool": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
     "pb200_debug_conv_p8": (
+        c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p]
+    ),
+    "pb200_debug_conv_f16x2": (
+        c_int,
+        [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_int,
+         c_void_p, c_void_p, c_int, c_void_p, c_void_p],
+    ),
+    "pb200_debug_conv_p8_f16x2": (
         c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p]
     ),
     "pb200_train_pack_weights": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),

@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda.h>
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -37,7 +38,10 @@ int require_device();  // PB200_OK if the current device is sm_100, else PB200_E
 bool pdl_enabled();
 // fills attrs[0] (PDL, if enabled) and returns the attribute count; attrs must have room for 1 entry
 int pdl_launch_attrs(cudaLaunchAttribute* attrs);
-int num_sms();
+int num_sms();  // of the current device
+// current CUDA device index clamped to [0, kMaxDevices): per-device caches (function attributes, occupancy, SM count)
+constexpr int kMaxDevices = 64;
+int current_device();
 
 // ---- device-side PTX wrappers ------------------------------------------------------------
 #ifdef __CUDACC__
@@ -397,12 +401,46 @@ __host__ __device__ constexpr uint32_t umma_idesc_bf16(uint32_t M, uint32_t N) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((N >> 3) << 17) | ((M >> 4) << 24);
 }
 
+// the same with A = B = fp16 (a_format = b_format = 0): the "fp16x2" mode (fp16 activations, weights = fp16 hi + fp16 lo)
+__host__ __device__ constexpr uint32_t umma_idesc_f16(uint32_t M, uint32_t N) {
+  return (1u << 4) | ((N >> 3) << 17) | ((M >> 4) << 24);
+}
+template <bool F16>
+__host__ __device__ constexpr uint32_t umma_idesc_16(uint32_t M, uint32_t N) {
+  return F16 ? umma_idesc_f16(M, N) : umma_idesc_bf16(M, N);
+}
+
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&v);
 }
 __device__ __forceinline__ float bf16_lo(uint32_t v) { return __uint_as_float(v << 16); }
 __device__ __forceinline__ float bf16_hi(uint32_t v) { return __uint_as_float(v & 0xffff0000u); }
+
+// fp16 pair: round to nearest even, values beyond +-65504 saturate instead of becoming inf
+__device__ __forceinline__ uint32_t pack_f16x2(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+__device__ __forceinline__ float f16_lo(uint32_t v) { return __half2float(__ushort_as_half(static_cast<unsigned short>(v & 0xffffu))); }
+__device__ __forceinline__ float f16_hi(uint32_t v) { return __half2float(__ushort_as_half(static_cast<unsigned short>(v >> 16))); }
+// 16-bit activation element of a kernel instance: bf16 (F16 = false) or fp16 (F16 = true)
+template <bool F16>
+__device__ __forceinline__ uint32_t pack16x2(float lo, float hi) { return F16 ? pack_f16x2(lo, hi) : pack_bf16x2(lo, hi); }
+template <bool F16>
+__device__ __forceinline__ float lo16(uint32_t v) { return F16 ? f16_lo(v) : bf16_lo(v); }
+template <bool F16>
+__device__ __forceinline__ float hi16(uint32_t v) { return F16 ? f16_hi(v) : bf16_hi(v); }
+template <bool F16>
+__device__ __forceinline__ uint32_t max16x2(uint32_t a, uint32_t b) {
+  if (F16) {
+    __half2 r = __hmax2(*reinterpret_cast<__half2*>(&a), *reinterpret_cast<__half2*>(&b));
+    return *reinterpret_cast<uint32_t*>(&r);
+  }
+  __nv_bfloat162 r = __hmax2(*reinterpret_cast<__nv_bfloat162*>(&a), *reinterpret_cast<__nv_bfloat162*>(&b));
+  return *reinterpret_cast<uint32_t*>(&r);
+}
 
 #endif  // __CUDACC__
 

@@ -25,7 +25,6 @@ namespace pb200 {
 namespace {
 
 constexpr int p8_threads(int epi_warps) { return 64 + 32 * epi_warps; }
-constexpr int kStages = 4;
 constexpr int kChunks = 8;                       // Cin / 8
 constexpr int kWBytes = 64 * 576 * 2;            // 73728
 constexpr int kWSbo = 72 * 128;                  // 9216: bytes per 8-output-channel group
@@ -47,8 +46,17 @@ struct ConvP8Params {
 
 // kEpiWarps = 4 (thread = position x 64 channels) or 8 (x 32 channels).  With 4 the epilogue has ONE warp per scheduler
 // and its ~350 dependent instructions per tile take longer than the tile's 36 MMAs (1728 cycles): latency-bound.
-template <int kEpiWarps>
+//
+// X2 = the "fp16x2" mode: fp16 activations, weights = fp16 hi + fp16 lo.  The lo image sits right behind the hi image
+// in shared memory, so ONE N = 128 descriptor (8-channel groups kWSbo apart) reads [W_hi ; W_lo]: accumulator columns
+// [0, 64) = A.W_hi and [64, 128) = A.W_lo from a single read of the A rows -- 64 cycles per K step instead of the
+// 2 x 48 of two N = 64 MMAs (the N = 64 MMA is bound by its operand fetch, tools/mma_bench.cu).  The epilogue adds the
+// two column groups.  144 KB of resident weights leave room for two patch stages.
+template <int kEpiWarps, bool X2>
 __device__ __forceinline__ void conv_p8_body(const ConvP8Params& p) {
+  constexpr int kStages = X2 ? 2 : 4;
+  constexpr int kWAll = X2 ? 2 * kWBytes : kWBytes;
+  constexpr int kAccCols = X2 ? 128 : 64;
   constexpr int kNch = 8 / (kEpiWarps / 4);  // 8-channel chunks (P8 planes) per epilogue thread
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t full_bar[kStages];
@@ -62,7 +70,7 @@ __device__ __forceinline__ void conv_p8_body(const ConvP8Params& p) {
   const uint32_t raw_addr = smem_u32(smem_raw);
   uint8_t* smem = smem_raw + (((raw_addr + 127u) & ~127u) - raw_addr);
   uint8_t* s_w = smem;
-  uint8_t* s_patch = smem + kWBytes;
+  uint8_t* s_patch = smem + kWAll;
   const int stage_bytes = kChunks * p.patch_pitch;
 
   const int warp = threadIdx.x >> 5;
@@ -82,7 +90,7 @@ __device__ __forceinline__ void conv_p8_body(const ConvP8Params& p) {
     fence_barrier_init();
   }
   if (warp == 1) {
-    tmem_alloc(&tmem_base_slot, 128);
+    tmem_alloc(&tmem_base_slot, 2 * kAccCols);
     tmem_relinquish();
   }
   if (threadIdx.x >= 64 && threadIdx.x < 128) s_bias[threadIdx.x - 64] = __ldg(p.bias + threadIdx.x - 64);
@@ -96,8 +104,8 @@ __device__ __forceinline__ void conv_p8_body(const ConvP8Params& p) {
     // ================================ producer ====================================
     // the whole warp runs the loop (operands stay warp-uniform); one elected lane issues the copies
     if (elect_one()) {
-      mbar_expect_tx(&w_bar, kWBytes);
-      bulk_load_1d(s_w, p.wimg, kWBytes, &w_bar);  // plan constant: fetched while the previous kernel drains (PDL)
+      mbar_expect_tx(&w_bar, kWAll);
+      bulk_load_1d(s_w, p.wimg, kWAll, &w_bar);  // plan constant: fetched while the previous kernel drains (PDL)
     }
     pdl_wait();  // the input patches are the previous kernel's output
     int stage = 0;
@@ -123,7 +131,7 @@ __device__ __forceinline__ void conv_p8_body(const ConvP8Params& p) {
     }
   } else if (warp == 1) {
     // ================================ MMA issuer ==================================
-    constexpr uint32_t idesc = umma_idesc_bf16(128, 64);
+    constexpr uint32_t idesc = umma_idesc_16<X2>(128, kAccCols);
     const uint32_t tm = warp_uniform(tmem_base);
     const uint32_t a_hi = desc_hi_interleaved(128);
     const uint32_t b_hi = desc_hi_interleaved(kWSbo);
@@ -139,7 +147,7 @@ __device__ __forceinline__ void conv_p8_body(const ConvP8Params& p) {
       mbar_wait(&full_bar[stage], phase);
       tc_fence_after();
       if (elect_one()) {
-        const uint32_t d_tmem = tm + acc * 64;
+        const uint32_t d_tmem = tm + acc * kAccCols;
         const uint32_t a_lo0 = desc_lo(smem_u32(s_patch) + stage * stage_bytes, p.patch_pitch);
 #pragma unroll
         for (int t = 0; t < 9; ++t) {
@@ -206,12 +214,23 @@ __device__ __forceinline__ void conv_p8_body(const ConvP8Params& p) {
       const long long opos = static_cast<long long>(q0) + p.Wp + 1;  // padded position of this output
       mbar_wait(&tmem_full_bar[a], (it >> 1) & 1u);
       tc_fence_after();
-      const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + a * 64 + 8 * j0;
+      const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + a * kAccCols + 8 * j0;
       uint32_t x[kNch / 4][32];
 #pragma unroll
       for (int c = 0; c < kNch / 4; ++c) tmem_ld_32x32(t_addr + 32 * c, x[c]);
 #pragma unroll
       for (int c = 0; c < kNch / 4; ++c) tmem_ld_wait_regs(x[c]);
+      if constexpr (X2) {  // + the A.W_lo partial sums (accumulator columns 64 further)
+        uint32_t xl[kNch / 4][32];
+#pragma unroll
+        for (int c = 0; c < kNch / 4; ++c) tmem_ld_32x32(t_addr + 64 + 32 * c, xl[c]);
+#pragma unroll
+        for (int c = 0; c < kNch / 4; ++c) tmem_ld_wait_regs(xl[c]);
+#pragma unroll
+        for (int c = 0; c < kNch / 4; ++c)
+#pragma unroll
+          for (int e = 0; e < 32; ++e) x[c][e] = __float_as_uint(__uint_as_float(x[c][e]) + __uint_as_float(xl[c][e]));
+      }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tmem_empty_bar[a]);
@@ -224,17 +243,17 @@ __device__ __forceinline__ void conv_p8_body(const ConvP8Params& p) {
 #pragma unroll
         for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(xj[e]) + bias[8 * j + e];
         if (has_res) {
-          f[0] += bf16_lo(rv[j].x); f[1] += bf16_hi(rv[j].x);
-          f[2] += bf16_lo(rv[j].y); f[3] += bf16_hi(rv[j].y);
-          f[4] += bf16_lo(rv[j].z); f[5] += bf16_hi(rv[j].z);
-          f[6] += bf16_lo(rv[j].w); f[7] += bf16_hi(rv[j].w);
+          f[0] += lo16<X2>(rv[j].x); f[1] += hi16<X2>(rv[j].x);
+          f[2] += lo16<X2>(rv[j].y); f[3] += hi16<X2>(rv[j].y);
+          f[4] += lo16<X2>(rv[j].z); f[5] += hi16<X2>(rv[j].z);
+          f[6] += lo16<X2>(rv[j].w); f[7] += hi16<X2>(rv[j].w);
         }
         if (p.relu) {
 #pragma unroll
           for (int e = 0; e < 8; ++e) f[e] = fmaxf(f[e], 0.f);
         }
-        o[j] = valid ? make_uint4(pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]), pack_bf16x2(f[4], f[5]),
-                                  pack_bf16x2(f[6], f[7]))
+        o[j] = valid ? make_uint4(pack16x2<X2>(f[0], f[1]), pack16x2<X2>(f[2], f[3]), pack16x2<X2>(f[4], f[5]),
+                                  pack16x2<X2>(f[6], f[7]))
                      : make_uint4(0, 0, 0, 0);
       }
       load_residual(tile + 2 * gridDim.x, rv);  // rv is dead from here on: prefetch the residual of the tile after next
@@ -296,32 +315,37 @@ __device__ __forceinline__ void conv_p8_body(const ConvP8Params& p) {
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, 128);
+    tmem_dealloc(tmem_base, 2 * kAccCols);
   }
 }
 
-__global__ void __launch_bounds__(p8_threads(8), 1) conv_p8_kernel(const ConvP8Params p) { conv_p8_body<8>(p); }
-__global__ void __launch_bounds__(p8_threads(4), 1) conv_p8_kernel4(const ConvP8Params p) { conv_p8_body<4>(p); }
+__global__ void __launch_bounds__(p8_threads(8), 1) conv_p8_kernel(const ConvP8Params p) { conv_p8_body<8, false>(p); }
+__global__ void __launch_bounds__(p8_threads(4), 1) conv_p8_kernel4(const ConvP8Params p) { conv_p8_body<4, false>(p); }
+__global__ void __launch_bounds__(p8_threads(8), 1) conv_p8_x2_kernel(const ConvP8Params p) { conv_p8_body<8, true>(p); }
 
 constexpr int kMaxDynSmem = 227 * 1024 - 1024;  // the kernel also has ~400 B of static shared memory
 inline int patch_pitch_for(int Wp) { return ((128 + 2 * Wp + 2) * 16 + 127) / 128 * 128; }
-inline int smem_bytes_for(int Wp) { return kWBytes + kStages * kChunks * patch_pitch_for(Wp) + 128; }
+inline int smem_bytes_for(int Wp, bool x2) {
+  return (x2 ? 2 : 1) * kWBytes + (x2 ? 2 : 4) * kChunks * patch_pitch_for(Wp) + 128;
+}
 
 }  // namespace
 
 int conv_p8_init() {
-  static bool done = false;
-  if (done) return PB200_OK;
+  static bool done[kMaxDevices] = {};  // function attributes belong to the device's context
+  const int dev = current_device();
+  if (done[dev]) return PB200_OK;
   PB_CUDA(cudaFuncSetAttribute(conv_p8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem));
   PB_CUDA(cudaFuncSetAttribute(conv_p8_kernel4, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem));
-  done = true;
+  PB_CUDA(cudaFuncSetAttribute(conv_p8_x2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem));
+  done[dev] = true;
   return PB200_OK;
 }
 
 int launch_conv_p8(const void* in_p8, const void* wimg, const float* bias, const void* residual_p8, void* out,
-                   int out_nhwc, int relu, int B, int H, int W, cudaStream_t st) {
+                   int out_nhwc, int relu, int B, int H, int W, cudaStream_t st, int x2) {
   const int Wp = W + 2;
-  PB_CHECK(smem_bytes_for(Wp) <= kMaxDynSmem, "conv_p8: W = %d too wide for the resident-weight kernel", W);
+  PB_CHECK(smem_bytes_for(Wp, x2 != 0) <= kMaxDynSmem, "conv_p8: W = %d too wide for the resident-weight kernel", W);
   PB_CHECK(Wp - 1 <= 128, "conv_p8: W = %d too wide for the border writer", W);
   if (B == 0) return PB200_OK;
   ConvP8Params p;
@@ -344,14 +368,15 @@ int launch_conv_p8(const void* in_p8, const void* wimg, const float* bias, const
   const int grid = p.num_tiles < num_sms() ? p.num_tiles : num_sms();
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(grid);
-  const bool narrow = getenv("PB200_P8_EPI4") != nullptr;
+  const bool narrow = !x2 && getenv("PB200_P8_EPI4") != nullptr;
   cfg.blockDim = dim3(p8_threads(narrow ? 4 : 8));
-  cfg.dynamicSmemBytes = smem_bytes_for(Wp);
+  cfg.dynamicSmemBytes = smem_bytes_for(Wp, x2 != 0);
   cfg.stream = st;
   cudaLaunchAttribute attr[1];
   cfg.attrs = attr;
   cfg.numAttrs = pdl_launch_attrs(attr);
-  if (narrow) PB_CUDA(cudaLaunchKernelEx(&cfg, conv_p8_kernel4, p));
+  if (x2) PB_CUDA(cudaLaunchKernelEx(&cfg, conv_p8_x2_kernel, p));
+  else if (narrow) PB_CUDA(cudaLaunchKernelEx(&cfg, conv_p8_kernel4, p));
   else PB_CUDA(cudaLaunchKernelEx(&cfg, conv_p8_kernel, p));
   return PB200_OK;
 }

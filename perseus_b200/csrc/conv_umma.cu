@@ -26,10 +26,13 @@ namespace pb200 {
 constexpr int kUmmaThreads = 352;  // 2 TMA warps + MMA warp + 8 epilogue warps
 constexpr int kTileM = 128;
 
-template <int BLOCK_N, int SW>
+// MODE: 0 = bf16 single pass; 1 = split bf16 ("bf16x3": [hi|lo] activations AND weights, 3 k-blocks per (tap, channel
+// block)); 2 = "fp16x2": fp16 activations, weights = fp16 hi + fp16 lo -- every stage carries the hi AND the lo weight
+// tile of its k-block and both are multiplied with the SAME activation tile (2 MMAs per K step, A bytes unchanged).
+template <int BLOCK_N, int SW, int MODE = 0>
 struct UmmaCfg {
   static constexpr int kABytes = kTileM * SW;
-  static constexpr int kBBytes = BLOCK_N * SW;
+  static constexpr int kBBytes = BLOCK_N * SW * (MODE == 2 ? 2 : 1);
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kStages = (192 * 1024 / kStageBytes) > 8 ? 8 : (192 * 1024 / kStageBytes);
   static constexpr int kSmemBytes = kStages * kStageBytes + 1024;  // + alignment slack
@@ -38,10 +41,12 @@ struct UmmaCfg {
   static constexpr int kTmemCols = 2 * BLOCK_N;                      // double-buffered accumulator
 };
 
-template <int BLOCK_N, int SW, bool SPLIT>
+template <int BLOCK_N, int SW, int MODE>
 __global__ void __launch_bounds__(kUmmaThreads, 1)
 conv_umma_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams p) {
-  using Cfg = UmmaCfg<BLOCK_N, SW>;
+  using Cfg = UmmaCfg<BLOCK_N, SW, MODE>;
+  constexpr bool SPLIT = MODE == 1;
+  constexpr bool X2 = MODE == 2;
   constexpr int kStages = Cfg::kStages;
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t full_bar[kStages];
@@ -142,11 +147,15 @@ conv_umma_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams
           if (elect_one()) {
             mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
             tma_load_4d(smem_a + stage * Cfg::kABytes, amap, &full_bar[stage], a_ch, dw, hrow, n0);
-            if (cl == 1)
-              tma_load_2d(smem_b + stage * Cfg::kBBytes, &maps.b, &full_bar[stage], b_col, n_tile * BLOCK_N);
-            else
-              tma_load_2d_mcast(smem_b + stage * Cfg::kBBytes + crank * slice_rows * SW, &maps.b, &full_bar[stage], b_col,
-                                n_tile * BLOCK_N + crank * slice_rows, cmask);
+#pragma unroll
+            for (int hl = 0; hl < (X2 ? 2 : 1); ++hl) {  // fp16x2: the hi tile, then the lo tile (columns + ktot)
+              uint8_t* bdst = smem_b + stage * Cfg::kBBytes + hl * BLOCK_N * SW;
+              if (cl == 1)
+                tma_load_2d(bdst, &maps.b, &full_bar[stage], b_col + hl * p.ktot, n_tile * BLOCK_N);
+              else
+                tma_load_2d_mcast(bdst + crank * slice_rows * SW, &maps.b, &full_bar[stage], b_col + hl * p.ktot,
+                                  n_tile * BLOCK_N + crank * slice_rows, cmask);
+            }
           }
           __syncwarp();
           }
@@ -164,11 +173,15 @@ conv_umma_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams
           if (elect_one()) {
             mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
             tma_load_4d(smem_a + stage * Cfg::kABytes, &maps.ds, &full_bar[stage], cb * 64, 0, ho0, n0);
-            if (cl == 1)
-              tma_load_2d(smem_b + stage * Cfg::kBBytes, &maps.b, &full_bar[stage], kcol, n_tile * BLOCK_N);
-            else
-              tma_load_2d_mcast(smem_b + stage * Cfg::kBBytes + crank * slice_rows * SW, &maps.b, &full_bar[stage], kcol,
-                                n_tile * BLOCK_N + crank * slice_rows, cmask);
+#pragma unroll
+            for (int hl = 0; hl < (X2 ? 2 : 1); ++hl) {
+              uint8_t* bdst = smem_b + stage * Cfg::kBBytes + hl * BLOCK_N * SW;
+              if (cl == 1)
+                tma_load_2d(bdst, &maps.b, &full_bar[stage], kcol + hl * p.ktot, n_tile * BLOCK_N);
+              else
+                tma_load_2d_mcast(bdst + crank * slice_rows * SW, &maps.b, &full_bar[stage], kcol + hl * p.ktot,
+                                  n_tile * BLOCK_N + crank * slice_rows, cmask);
+            }
           }
           __syncwarp();
         }
@@ -180,7 +193,7 @@ conv_umma_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams
     }
   } else if (warp == 1) {
     // ================================ MMA issuer ==================================
-    constexpr uint32_t idesc = umma_idesc_bf16(kTileM, BLOCK_N);
+    constexpr uint32_t idesc = umma_idesc_16<X2>(kTileM, BLOCK_N);
     const uint32_t tm = warp_uniform(tmem_base);
     const uint32_t d_hi = desc_hi_swizzled(SW);
     int stage = 0;
@@ -199,9 +212,12 @@ conv_umma_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams
           const uint32_t a_lo = desc_lo(smem_u32(smem_a + stage * Cfg::kABytes), 16);
           const uint32_t b_lo = desc_lo(smem_u32(smem_b + stage * Cfg::kBBytes), 16);
 #pragma unroll
-          for (int k = 0; k < Cfg::kKSteps; ++k)
+          for (int k = 0; k < Cfg::kKSteps; ++k) {
             // advancing K by 16 elements = 32 bytes inside the swizzle span: +2 in the address field
             umma_bf16_split(d_tmem, a_lo + 2 * k, d_hi, b_lo + 2 * k, d_hi, idesc, (kb | k) != 0 ? 1u : 0u);
+            if (X2)  // same activations x the lo weight tile (BLOCK_N rows further in the stage)
+              umma_bf16_split(d_tmem, a_lo + 2 * k, d_hi, b_lo + 2 * k + (BLOCK_N * SW >> 4), d_hi, idesc, 1u);
+          }
           // frees the smem stage (in every CTA of the cluster) once these MMAs have read it
           if (cl == 1) umma_commit(&empty_bar[stage]);
           else umma_commit_mcast(&empty_bar[stage], cmask);
@@ -302,7 +318,7 @@ conv_umma_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams
         mbar_wait(&tmem_full_bar[acc], acc_phase);
         tc_fence_after();
         const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BLOCK_N + half * kCols;
-        epilogue_lines<kCols>(t_addr, s_bias + col0, has_res, rv, static_cast<__nv_bfloat16*>(p.out), gm_group, p.M_total,
+        epilogue_lines<kCols, X2>(t_addr, s_bias + col0, has_res, rv, static_cast<__nv_bfloat16*>(p.out), gm_group, p.M_total,
                               p.Cout, col0, p.relu, lane, [&]() {
                                 tc_fence_before();
                                 __syncwarp();
@@ -341,17 +357,17 @@ conv_umma_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams
           for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(v[8 * j + e]) + bias[chunk * 32 + 8 * j + e];
           if (has_res) {
             const uint4 r4 = rv[chunk * 4 + j];
-            f[0] += bf16_lo(r4.x); f[1] += bf16_hi(r4.x);
-            f[2] += bf16_lo(r4.y); f[3] += bf16_hi(r4.y);
-            f[4] += bf16_lo(r4.z); f[5] += bf16_hi(r4.z);
-            f[6] += bf16_lo(r4.w); f[7] += bf16_hi(r4.w);
+            f[0] += lo16<X2>(r4.x); f[1] += hi16<X2>(r4.x);
+            f[2] += lo16<X2>(r4.y); f[3] += hi16<X2>(r4.y);
+            f[4] += lo16<X2>(r4.z); f[5] += hi16<X2>(r4.z);
+            f[6] += lo16<X2>(r4.w); f[7] += hi16<X2>(r4.w);
           }
           if (p.relu) {
 #pragma unroll
             for (int e = 0; e < 8; ++e) f[e] = fmaxf(f[e], 0.f);
           }
-          const uint4 ov = make_uint4(pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]), pack_bf16x2(f[4], f[5]),
-                                      pack_bf16x2(f[6], f[7]));
+          const uint4 ov = make_uint4(pack16x2<X2>(f[0], f[1]), pack16x2<X2>(f[2], f[3]), pack16x2<X2>(f[4], f[5]),
+                                      pack16x2<X2>(f[6], f[7]));
           if (valid) out_row[chunk * 4 + j] = ov;
           oc[j] = ov;
         }
@@ -377,20 +393,23 @@ conv_umma_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams
 // ------------------------------------------------------------------------------------------
 template <int BLOCK_N, int SW>
 static int set_attr() {
-  PB_CUDA(cudaFuncSetAttribute(conv_umma_kernel<BLOCK_N, SW, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                               UmmaCfg<BLOCK_N, SW>::kSmemBytes));
-  PB_CUDA(cudaFuncSetAttribute(conv_umma_kernel<BLOCK_N, SW, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                               UmmaCfg<BLOCK_N, SW>::kSmemBytes));
+  PB_CUDA(cudaFuncSetAttribute(conv_umma_kernel<BLOCK_N, SW, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               UmmaCfg<BLOCK_N, SW, 0>::kSmemBytes));
+  PB_CUDA(cudaFuncSetAttribute(conv_umma_kernel<BLOCK_N, SW, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               UmmaCfg<BLOCK_N, SW, 1>::kSmemBytes));
+  PB_CUDA(cudaFuncSetAttribute(conv_umma_kernel<BLOCK_N, SW, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               UmmaCfg<BLOCK_N, SW, 2>::kSmemBytes));
   return PB200_OK;
 }
 
 int umma_conv_init() {
-  static bool done = false;
-  if (done) return PB200_OK;
+  static bool done[kMaxDevices] = {};  // function attributes belong to the device's context
+  const int dev = current_device();
+  if (done[dev]) return PB200_OK;
   if (int rc = set_attr<64, 128>()) return rc;
   if (int rc = set_attr<128, 128>()) return rc;
   if (int rc = set_attr<256, 128>()) return rc;
-  done = true;
+  done[dev] = true;
   return PB200_OK;
 }
 
@@ -416,7 +435,7 @@ static int query_clusters(int cl) {
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   int n = 0;
-  if (cudaOccupancyMaxActiveClusters(&n, conv_umma_kernel<BLOCK_N, 128, false>, &cfg) != cudaSuccess) {
+  if (cudaOccupancyMaxActiveClusters(&n, conv_umma_kernel<BLOCK_N, 128, 0>, &cfg) != cudaSuccess) {
     (void)cudaGetLastError();
     return 0;
   }
@@ -424,11 +443,12 @@ static int query_clusters(int cl) {
 }
 static int max_active_clusters(int block_n, int cl) {
   if (cl == 1) return num_sms();
-  static int cache[3][5] = {};
+  static int cache[kMaxDevices][3][5] = {};
+  const int dev = current_device();
   const int bi = block_n == 64 ? 0 : (block_n == 128 ? 1 : 2);
-  if (cache[bi][cl] == 0)
-    cache[bi][cl] = block_n == 64 ? query_clusters<64>(cl) : (block_n == 128 ? query_clusters<128>(cl) : query_clusters<256>(cl));
-  return cache[bi][cl];
+  if (cache[dev][bi][cl] == 0)
+    cache[dev][bi][cl] = block_n == 64 ? query_clusters<64>(cl) : (block_n == 128 ? query_clusters<128>(cl) : query_clusters<256>(cl));
+  return cache[dev][bi][cl];
 }
 
 int build_umma_conv(UmmaConvLaunch* L, const void* in, int B, int Hin, int Win, int Cin,
@@ -472,7 +492,7 @@ int build_umma_conv(UmmaConvLaunch* L, const void* in, int B, int Hin, int Win, 
   p.pad = pad;
   p.S = R;
   p.cblocks = Cin / 64;
-  p.num_kblocks = R * R * p.cblocks * (split ? 3 : 1);
+  p.num_kblocks = R * R * p.cblocks * (split == 1 ? 3 : 1);
   p.ntaps = R * R;
   for (int t = 0; t < R * R; ++t) {
     const int r = t / R, sx = t - r * R;
@@ -490,17 +510,18 @@ int build_umma_conv(UmmaConvLaunch* L, const void* in, int B, int Hin, int Win, 
   }
   p.up2 = p.up_ph = p.up_pw = p.up_lh = p.up_lw = 0;
   p.ds_cblocks = 0;
-  PB_CHECK(stats == nullptr || !split, "umma conv: fused statistics are not available in split mode");
+  PB_CHECK(stats == nullptr || !split, "umma conv: fused statistics are not available in the split / fp16x2 modes");
   if (ds_in != nullptr) {
-    PB_CHECK(!split && ds_Cin % 64 == 0 && ds_Hin == 2 * Ho && ds_Win == 2 * Wo,
+    PB_CHECK(split != 1 && ds_Cin % 64 == 0 && ds_Hin == 2 * Ho && ds_Win == 2 * Wo,
              "umma conv: fused projection needs a bf16 [B][2Ho][2Wo][64k] input (got %dx%dx%d)", ds_Hin, ds_Win, ds_Cin);
     p.ds_cblocks = ds_Cin / 64;
     p.num_kblocks += p.ds_cblocks;
   }
   p.cin = Cin;
-  p.ktot = R * R * Cin;
-  L->split = split ? 1 : 0;
-  if (split) cluster = 1;  // the split-bf16 mode runs on the single-CTA kernel
+  // column offset of the lo halves in the packed weight rows [hi K | lo K] (K includes a fused projection's columns)
+  p.ktot = R * R * Cin + ((split == 2 && ds_in != nullptr) ? ds_Cin : 0);
+  L->split = split;
+  if (split == 1) cluster = 1;  // the split-bf16 mode runs on the single-CTA kernel
   p.num_n_tiles = Cout / block_n;
   const int m_tiles = static_cast<int>((M + kTileM - 1) / kTileM);
   p.num_tiles = m_tiles * p.num_n_tiles;
@@ -522,7 +543,9 @@ int build_umma_conv(UmmaConvLaunch* L, const void* in, int B, int Hin, int Win, 
   }
   // default: CTA pairs (halves the weight bytes landing in each SM) whenever there is a whole wave of pair tiles;
   // plain multicast clusters measured no gain (profiles/README.md) and stay opt-in
-  if (cl == 0) cl = (static_cast<long long>(m_tiles) * p.num_n_tiles >= 2LL * num_sms()) ? -2 : 1;
+  // (fp16x2: a pair halves the doubled weight bytes per SM, so it pays from one full wave on)
+  if (cl == 0)
+    cl = (static_cast<long long>(m_tiles) * p.num_n_tiles >= (split == 2 ? 1LL : 2LL) * num_sms()) ? -2 : 1;
   PB_CHECK(cl == 1 || cl == 2 || cl == 4 || cl == -2, "umma conv: cluster %d", cl);
   L->pair = cl == -2;
   if (L->pair) cl = 2;
@@ -531,7 +554,7 @@ int build_umma_conv(UmmaConvLaunch* L, const void* in, int B, int Hin, int Win, 
   int max_clusters;
   if (L->pair) {
     if (int rc = umma_pair_init()) return rc;
-    max_clusters = umma_pair_max_pairs(block_n);
+    max_clusters = umma_pair_max_pairs(block_n, split == 2);
   } else {
     max_clusters = max_active_clusters(block_n, cl);
   }
@@ -542,7 +565,7 @@ int build_umma_conv(UmmaConvLaunch* L, const void* in, int B, int Hin, int Win, 
   const uint32_t box[4] = {64u, static_cast<uint32_t>(Wo), static_cast<uint32_t>(bh),
                            static_cast<uint32_t>(imgs)};
   const uint64_t e = 2;  // bytes per element
-  const uint64_t Cs = static_cast<uint64_t>(Cin) * (split ? 2 : 1);  // stored channels per pixel: [hi | lo] when split
+  const uint64_t Cs = static_cast<uint64_t>(Cin) * (split == 1 ? 2 : 1);  // stored channels per pixel: [hi | lo] when split
   if (stride == 1) {
     const uint64_t dims[4] = {Cs, (uint64_t)Win, (uint64_t)Hin, (uint64_t)B};
     const uint64_t str[3] = {Cs * e, (uint64_t)Win * Cs * e, (uint64_t)Hin * Win * Cs * e};
@@ -612,12 +635,12 @@ int build_umma_dgrad_s2(UmmaConvLaunch* L, const void* dz, int B, int Ho, int Wo
   return PB200_OK;
 }
 
-template <int BLOCK_N, bool SPLIT>
+template <int BLOCK_N, int MODE>
 static int launch_one(const UmmaConvLaunch& L, cudaStream_t st) {
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(L.grid);
   cfg.blockDim = dim3(kUmmaThreads);
-  cfg.dynamicSmemBytes = UmmaCfg<BLOCK_N, 128>::kSmemBytes;
+  cfg.dynamicSmemBytes = UmmaCfg<BLOCK_N, 128, MODE>::kSmemBytes;
   cfg.stream = st;
   cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -626,21 +649,26 @@ static int launch_one(const UmmaConvLaunch& L, cudaStream_t st) {
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1 + pdl_launch_attrs(attr + 1);
-  PB_CUDA(cudaLaunchKernelEx(&cfg, conv_umma_kernel<BLOCK_N, 128, SPLIT>, L.maps, L.p));
+  PB_CUDA(cudaLaunchKernelEx(&cfg, conv_umma_kernel<BLOCK_N, 128, MODE>, L.maps, L.p));
   return PB200_OK;
 }
 
 int launch_umma_conv(const UmmaConvLaunch& L, cudaStream_t st) {
   if (L.p.num_tiles == 0) return PB200_OK;
   if (L.pair) return launch_umma_pair(L, st);
-  if (L.split) {
-    if (L.block_n == 64) return launch_one<64, true>(L, st);
-    if (L.block_n == 128) return launch_one<128, true>(L, st);
-    return launch_one<256, true>(L, st);
+  if (L.split == 1) {
+    if (L.block_n == 64) return launch_one<64, 1>(L, st);
+    if (L.block_n == 128) return launch_one<128, 1>(L, st);
+    return launch_one<256, 1>(L, st);
   }
-  if (L.block_n == 64) return launch_one<64, false>(L, st);
-  if (L.block_n == 128) return launch_one<128, false>(L, st);
-  return launch_one<256, false>(L, st);
+  if (L.split == 2) {
+    if (L.block_n == 64) return launch_one<64, 2>(L, st);
+    if (L.block_n == 128) return launch_one<128, 2>(L, st);
+    return launch_one<256, 2>(L, st);
+  }
+  if (L.block_n == 64) return launch_one<64, 0>(L, st);
+  if (L.block_n == 128) return launch_one<128, 0>(L, st);
+  return launch_one<256, 0>(L, st);
 }
 
 }  // namespace pb200

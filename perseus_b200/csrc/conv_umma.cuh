@@ -48,7 +48,7 @@ struct UmmaConvLaunch {
   int block_n;  // 64 / 128 / 256
   int sw;       // swizzle bytes = bytes of K per smem row: 128 (generic) or 64 (stem)
   int grid;
-  int split;    // 1: split-bf16 ("bf16x3") operands, conv_umma_kernel<.., true>
+  int split;    // 1: split-bf16 ("bf16x3") operands; 2: "fp16x2" (fp16 activations, weights [hi K | lo K] fp16)
   int pair;     // 1: CTA-pair kernel (conv_umma2.cu, tcgen05 cta_group::2), p.cl == 2
   double flops;  // algorithmic 2*MAC (unpadded)
 };
@@ -58,7 +58,8 @@ struct UmmaConvLaunch {
 int build_umma_conv(UmmaConvLaunch* L, const void* in, int B, int Hin, int Win, int Cin,
                     const void* wpacked, const float* bias, const void* residual, void* out, int Cout,
                     int R, int stride, int pad, int relu, int block_n, int cluster = 0 /* 0 = choose; 1/2/4 = multicast cluster; -2 = CTA pair */,
-                    int split = 0 /* 1: activations [hi|lo] (2*Cin channels), weights [Cout][hi K | lo K], out/residual [hi|lo] */,
+                    int split = 0 /* 1: activations [hi|lo] (2*Cin channels), weights [Cout][hi K | lo K], out/residual [hi|lo];
+                                     2: fp16 activations / output, weights [Cout][hi K | lo K] fp16 (K incl. a fused projection) */,
                     // fused 1x1 stride-2 projection (resnet.py:240-243) of `ds_in` [B][ds_Hin][ds_Win][ds_Cin] accumulated into
                     // the same tile: the packed weight rows carry ds_Cin extra columns after R*R*Cin (K-extension)
                     const void* ds_in = nullptr, int ds_Hin = 0, int ds_Win = 0, int ds_Cin = 0,
@@ -73,7 +74,7 @@ int build_umma_dgrad_s2(UmmaConvLaunch* L, const void* dz, int B, int Ho, int Wo
 int launch_umma_conv(const UmmaConvLaunch& L, cudaStream_t st);  // dispatches on L.pair
 // conv_umma2.cu
 int umma_pair_init();
-int umma_pair_max_pairs(int block_n);
+int umma_pair_max_pairs(int block_n, int x2 = 0);
 int launch_umma_pair(const UmmaConvLaunch& L, cudaStream_t st);
 int umma_conv_init();  // sets the dynamic shared-memory attributes once per process
 

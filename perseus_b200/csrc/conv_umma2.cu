@@ -20,20 +20,23 @@ namespace pb200 {
 
 constexpr int kPairThreads = 352;  // 2 TMA warps + MMA warp + 8 epilogue warps (per CTA)
 
-template <int BLOCK_N>
+// X2 = the "fp16x2" mode (conv_umma.cu MODE 2): fp16 operands, every stage carries this CTA's half of the hi AND of the
+// lo weight tile; both are multiplied with the same activation tile.
+template <int BLOCK_N, bool X2 = false>
 struct PairCfg {
   static constexpr int kABytes = 128 * 128;
-  static constexpr int kBBytes = BLOCK_N / 2 * 128;
+  static constexpr int kBHalf = BLOCK_N / 2 * 128;  // this CTA's half of one weight tile
+  static constexpr int kBBytes = kBHalf * (X2 ? 2 : 1);
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kStages = (192 * 1024 / kStageBytes) > 8 ? 8 : (192 * 1024 / kStageBytes);
   static constexpr int kSmemBytes = kStages * kStageBytes + 1024;
   static constexpr int kTmemCols = 2 * BLOCK_N;
 };
 
-template <int BLOCK_N>
+template <int BLOCK_N, bool X2>
 __global__ void __launch_bounds__(kPairThreads, 1)
 conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams p) {
-  using Cfg = PairCfg<BLOCK_N>;
+  using Cfg = PairCfg<BLOCK_N, X2>;
   constexpr int kStages = Cfg::kStages;
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t full_bar[kStages];   // used in the leader CTA only
@@ -122,6 +125,7 @@ conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParam
             mbar_expect_tx_cluster(lfull, Cfg::kStageBytes);
             tma_load_4d_2sm(smem_a + stage * Cfg::kABytes, amap, lfull, cb * 64, dw, hrow, n0);
             tma_load_2d_2sm(smem_b + stage * Cfg::kBBytes, &maps.b, lfull, kcol, n_row);
+            if (X2) tma_load_2d_2sm(smem_b + stage * Cfg::kBBytes + Cfg::kBHalf, &maps.b, lfull, kcol + p.ktot, n_row);
           }
           __syncwarp();
           }
@@ -140,6 +144,7 @@ conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParam
             mbar_expect_tx_cluster(lfull, Cfg::kStageBytes);
             tma_load_4d_2sm(smem_a + stage * Cfg::kABytes, &maps.ds, lfull, cb * 64, 0, ho0, n0);
             tma_load_2d_2sm(smem_b + stage * Cfg::kBBytes, &maps.b, lfull, kcol, n_row);
+            if (X2) tma_load_2d_2sm(smem_b + stage * Cfg::kBBytes + Cfg::kBHalf, &maps.b, lfull, kcol + p.ktot, n_row);
           }
           __syncwarp();
         }
@@ -152,7 +157,7 @@ conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParam
   } else if (warp == 1) {
     // ================================ MMA issuer (pair leader only) ===============
     if (crank == 0) {
-      constexpr uint32_t idesc = umma_idesc_bf16(256, BLOCK_N);
+      constexpr uint32_t idesc = umma_idesc_16<X2>(256, BLOCK_N);
       const uint32_t tm = warp_uniform(tmem_base);
       const uint32_t d_hi = desc_hi_swizzled(128);
       int stage = 0;
@@ -170,8 +175,10 @@ conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParam
             const uint32_t a_lo = desc_lo(smem_u32(smem_a + stage * Cfg::kABytes), 16);
             const uint32_t b_lo = desc_lo(smem_u32(smem_b + stage * Cfg::kBBytes), 16);
 #pragma unroll
-            for (int k = 0; k < 4; ++k)
+            for (int k = 0; k < 4; ++k) {
               umma2_bf16_split(d_tmem, a_lo + 2 * k, d_hi, b_lo + 2 * k, d_hi, idesc, (kb | k) != 0 ? 1u : 0u);
+              if (X2) umma2_bf16_split(d_tmem, a_lo + 2 * k, d_hi, b_lo + 2 * k + (Cfg::kBHalf >> 4), d_hi, idesc, 1u);
+            }
             umma2_commit_mcast(&empty_bar[stage], 3);  // both CTAs may refill this stage
             if (kb == p.num_kblocks - 1) umma2_commit_mcast(&tmem_full_bar[acc], 3);
           }
@@ -215,7 +222,7 @@ conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParam
         mbar_wait(&tmem_full_bar[acc], (it >> 1) & 1u);
         tc_fence_after();
         const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BLOCK_N + half * kCols;
-        epilogue_lines<kCols>(t_addr, s_bias + col0, has_res, rv, static_cast<__nv_bfloat16*>(p.out), gm_group, p.M_total,
+        epilogue_lines<kCols, X2>(t_addr, s_bias + col0, has_res, rv, static_cast<__nv_bfloat16*>(p.out), gm_group, p.M_total,
                               p.Cout, col0, p.relu, lane, [&]() {
                                 tc_fence_before();
                                 __syncwarp();
@@ -260,17 +267,17 @@ conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParam
           for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(v[8 * j + e]) + bias[chunk * 32 + 8 * j + e];
           if (has_res) {
             const uint4 r4 = rv[chunk * 4 + j];
-            f[0] += bf16_lo(r4.x); f[1] += bf16_hi(r4.x);
-            f[2] += bf16_lo(r4.y); f[3] += bf16_hi(r4.y);
-            f[4] += bf16_lo(r4.z); f[5] += bf16_hi(r4.z);
-            f[6] += bf16_lo(r4.w); f[7] += bf16_hi(r4.w);
+            f[0] += lo16<X2>(r4.x); f[1] += hi16<X2>(r4.x);
+            f[2] += lo16<X2>(r4.y); f[3] += hi16<X2>(r4.y);
+            f[4] += lo16<X2>(r4.z); f[5] += hi16<X2>(r4.z);
+            f[6] += lo16<X2>(r4.w); f[7] += hi16<X2>(r4.w);
           }
           if (p.relu) {
 #pragma unroll
             for (int e = 0; e < 8; ++e) f[e] = fmaxf(f[e], 0.f);
           }
-          const uint4 ov = make_uint4(pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]), pack_bf16x2(f[4], f[5]),
-                                      pack_bf16x2(f[6], f[7]));
+          const uint4 ov = make_uint4(pack16x2<X2>(f[0], f[1]), pack16x2<X2>(f[2], f[3]), pack16x2<X2>(f[4], f[5]),
+                                      pack16x2<X2>(f[6], f[7]));
           if (valid) out_row[chunk * 4 + j] = ov;
           oc[j] = ov;
         }
@@ -294,12 +301,12 @@ conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParam
 // ------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------
-template <int BLOCK_N>
+template <int BLOCK_N, bool X2>
 static int pair_cfg(cudaLaunchConfig_t* cfg, cudaLaunchAttribute* attr, int grid, cudaStream_t st, bool pdl = false) {
   *cfg = cudaLaunchConfig_t{};
   cfg->gridDim = dim3(grid);
   cfg->blockDim = dim3(kPairThreads);
-  cfg->dynamicSmemBytes = PairCfg<BLOCK_N>::kSmemBytes;
+  cfg->dynamicSmemBytes = PairCfg<BLOCK_N, X2>::kSmemBytes;
   cfg->stream = st;
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = 2;
@@ -310,48 +317,59 @@ static int pair_cfg(cudaLaunchConfig_t* cfg, cudaLaunchAttribute* attr, int grid
   return PB200_OK;
 }
 
-template <int BLOCK_N>
+template <int BLOCK_N, bool X2>
 static int pair_init_one(int* max_pairs) {
-  PB_CUDA(cudaFuncSetAttribute(conv_umma2_kernel<BLOCK_N>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                               PairCfg<BLOCK_N>::kSmemBytes));
+  PB_CUDA(cudaFuncSetAttribute(conv_umma2_kernel<BLOCK_N, X2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               PairCfg<BLOCK_N, X2>::kSmemBytes));
   cudaLaunchConfig_t cfg;
   cudaLaunchAttribute attr[1];
-  pair_cfg<BLOCK_N>(&cfg, attr, num_sms() / 2 * 2, nullptr);
+  pair_cfg<BLOCK_N, X2>(&cfg, attr, num_sms() / 2 * 2, nullptr);
   int n = 0;
-  PB_CUDA(cudaOccupancyMaxActiveClusters(&n, conv_umma2_kernel<BLOCK_N>, &cfg));
+  PB_CUDA(cudaOccupancyMaxActiveClusters(&n, conv_umma2_kernel<BLOCK_N, X2>, &cfg));
   *max_pairs = n;
   return PB200_OK;
 }
 
-static int g_max_pairs[3] = {0, 0, 0};  // BLOCK_N = 64, 128, 256
+// per device (function attributes and occupancy belong to the device's context): [device][x2][BLOCK_N = 64, 128, 256]
+static int g_max_pairs[kMaxDevices][2][3] = {};
+static bool g_pair_done[kMaxDevices] = {};
 
 int umma_pair_init() {
-  static bool done = false;
-  if (done) return PB200_OK;
-  if (int rc = pair_init_one<64>(&g_max_pairs[0])) return rc;
-  if (int rc = pair_init_one<128>(&g_max_pairs[1])) return rc;
-  if (int rc = pair_init_one<256>(&g_max_pairs[2])) return rc;
-  done = true;
+  const int dev = current_device();
+  if (g_pair_done[dev]) return PB200_OK;
+  if (int rc = pair_init_one<64, false>(&g_max_pairs[dev][0][0])) return rc;
+  if (int rc = pair_init_one<128, false>(&g_max_pairs[dev][0][1])) return rc;
+  if (int rc = pair_init_one<256, false>(&g_max_pairs[dev][0][2])) return rc;
+  if (int rc = pair_init_one<64, true>(&g_max_pairs[dev][1][0])) return rc;
+  if (int rc = pair_init_one<128, true>(&g_max_pairs[dev][1][1])) return rc;
+  if (int rc = pair_init_one<256, true>(&g_max_pairs[dev][1][2])) return rc;
+  g_pair_done[dev] = true;
   return PB200_OK;
 }
 
-int umma_pair_max_pairs(int block_n) { return g_max_pairs[block_n == 64 ? 0 : (block_n == 128 ? 1 : 2)]; }
+int umma_pair_max_pairs(int block_n, int x2) {
+  return g_max_pairs[current_device()][x2 ? 1 : 0][block_n == 64 ? 0 : (block_n == 128 ? 1 : 2)];
+}
+
+template <int BLOCK_N, bool X2>
+static int launch_pair_one(const UmmaConvLaunch& L, cudaStream_t st) {
+  cudaLaunchConfig_t cfg;
+  cudaLaunchAttribute attr[2];
+  pair_cfg<BLOCK_N, X2>(&cfg, attr, L.grid, st, true);
+  PB_CUDA(cudaLaunchKernelEx(&cfg, conv_umma2_kernel<BLOCK_N, X2>, L.maps, L.p));
+  return PB200_OK;
+}
 
 int launch_umma_pair(const UmmaConvLaunch& L, cudaStream_t st) {
   if (L.p.num_tiles == 0) return PB200_OK;
-  cudaLaunchConfig_t cfg;
-  cudaLaunchAttribute attr[2];
-  if (L.block_n == 64) {
-    pair_cfg<64>(&cfg, attr, L.grid, st, true);
-    PB_CUDA(cudaLaunchKernelEx(&cfg, conv_umma2_kernel<64>, L.maps, L.p));
-  } else if (L.block_n == 128) {
-    pair_cfg<128>(&cfg, attr, L.grid, st, true);
-    PB_CUDA(cudaLaunchKernelEx(&cfg, conv_umma2_kernel<128>, L.maps, L.p));
-  } else {
-    pair_cfg<256>(&cfg, attr, L.grid, st, true);
-    PB_CUDA(cudaLaunchKernelEx(&cfg, conv_umma2_kernel<256>, L.maps, L.p));
+  if (L.split == 2) {
+    if (L.block_n == 64) return launch_pair_one<64, true>(L, st);
+    if (L.block_n == 128) return launch_pair_one<128, true>(L, st);
+    return launch_pair_one<256, true>(L, st);
   }
-  return PB200_OK;
+  if (L.block_n == 64) return launch_pair_one<64, false>(L, st);
+  if (L.block_n == 128) return launch_pair_one<128, false>(L, st);
+  return launch_pair_one<256, false>(L, st);
 }
 
 }  // namespace pb200

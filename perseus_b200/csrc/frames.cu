@@ -2,7 +2,7 @@
 //
 // frames layout: [B][H+6][W+8][4] with a zero margin of 3 rows top/bottom and
 // 4 pixels left/right, channels (R, G, B, D).  bf16 in the tcgen05 modes — RGB stored as the
-// exact integers 0..255 (1/255 is folded into the stem weights) — fp32 in PB200_PREC_FP32, where
+// exact integers 0..255 (1/255 is folded into the stem weights); fp16 in the "fp16x2" mode (k * 2^-12, depth * 2^-4) — fp32 in PB200_PREC_FP32, where
 // RGB is k/255 exactly as the reference computes it.
 //
 // Restates scripts/streaming.py:68-80 (BGRA slice + reverse + /255, NaN/Inf -> 0, /0.035,
@@ -28,6 +28,19 @@ __device__ __forceinline__ void store_px4<__nv_bfloat16>(__nv_bfloat16* dst, con
   for (int i = 0; i < 2; ++i)
     d[i] = make_uint4(pack_bf16x2(v[8 * i], v[8 * i + 1]), pack_bf16x2(v[8 * i + 2], v[8 * i + 3]),
                       pack_bf16x2(v[8 * i + 4], v[8 * i + 5]), pack_bf16x2(v[8 * i + 6], v[8 * i + 7]));
+}
+
+// fp16 frames: RGB scaled by 2^-12, depth by 2^-4 (layout.h), both exact
+template <>
+__device__ __forceinline__ void store_px4<__half>(__half* dst, const float (&v)[16]) {
+  uint4* d = reinterpret_cast<uint4*>(dst);
+  float s[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) s[i] = v[i] * ((i & 3) == 3 ? kF16DepthScale : kF16RgbScale);
+#pragma unroll
+  for (int i = 0; i < 2; ++i)
+    d[i] = make_uint4(pack_f16x2(s[8 * i], s[8 * i + 1]), pack_f16x2(s[8 * i + 2], s[8 * i + 3]),
+                      pack_f16x2(s[8 * i + 4], s[8 * i + 5]), pack_f16x2(s[8 * i + 6], s[8 * i + 7]));
 }
 
 // One thread = 4 horizontally adjacent pixels of the zero-margined output (one 16/12-byte source
@@ -168,12 +181,17 @@ repack_nchw_kernel(const float* __restrict__ x, int C, int H, int W, int B, int 
   store_px4<T>(out + ((static_cast<long long>(b) * Hp + hp) * Wp + g * 4) * 4, v);
 }
 
-int launch_ingest(const IngestArgs& a, void* out, bool bf16, cudaStream_t st) {
+int launch_ingest(const IngestArgs& a, void* out, int elt, cudaStream_t st) {
   const int Hp = a.H + kFrameMarginTop + kFrameMarginBottom;
   const int Wp = a.W + kFrameMarginLeft + kFrameMarginRight;
   const long long total = static_cast<long long>(a.B) * Hp * (Wp / 4);
   const unsigned grid = static_cast<unsigned>((total + 255) / 256);
-  if (bf16) {
+  if (elt == FRAME_F16) {
+    if (a.ch == 4)
+      ingest_kernel<__half, 4><<<grid, 256, 0, st>>>(a, static_cast<__half*>(out));
+    else
+      ingest_kernel<__half, 3><<<grid, 256, 0, st>>>(a, static_cast<__half*>(out));
+  } else if (elt == FRAME_BF16) {
     if (a.ch == 4)
       ingest_kernel<__nv_bfloat16, 4><<<grid, 256, 0, st>>>(a, static_cast<__nv_bfloat16*>(out));
     else
@@ -188,13 +206,15 @@ int launch_ingest(const IngestArgs& a, void* out, bool bf16, cudaStream_t st) {
   return PB200_OK;
 }
 
-int launch_repack_nchw(const float* x, int C, int H, int W, int B, void* out, bool bf16,
+int launch_repack_nchw(const float* x, int C, int H, int W, int B, void* out, int elt,
                        cudaStream_t st) {
   const int Hp = H + kFrameMarginTop + kFrameMarginBottom;
   const int Wp = W + kFrameMarginLeft + kFrameMarginRight;
   const long long total = static_cast<long long>(B) * Hp * (Wp / 4);
   const unsigned grid = static_cast<unsigned>((total + 255) / 256);
-  if (bf16)
+  if (elt == FRAME_F16)
+    repack_nchw_kernel<__half><<<grid, 256, 0, st>>>(x, C, H, W, B, 1, static_cast<__half*>(out));
+  else if (elt == FRAME_BF16)
     repack_nchw_kernel<__nv_bfloat16>
         <<<grid, 256, 0, st>>>(x, C, H, W, B, 1, static_cast<__nv_bfloat16*>(out));
   else

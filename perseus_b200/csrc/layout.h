@@ -33,11 +33,18 @@ struct IngestArgs {
   float cube_scale, near_plane, far_plane;
   const float* jitter;  // [B][2][H][W] or null
   int H, W, B;
-  int rgb_integer;  // 1: emit 0..255 (bf16 modes), 0: emit k/255 (fp32 mode)
+  int rgb_integer;  // 1: emit 0..255 (16-bit modes), 0: emit k/255 (fp32 mode)
 };
 
-int launch_ingest(const IngestArgs& a, void* out, bool bf16, cudaStream_t st);
-int launch_repack_nchw(const float* x, int C, int H, int W, int B, void* out, bool bf16,
+// element type of a frames buffer
+enum FrameElt { FRAME_F32 = 0, FRAME_BF16 = 1, FRAME_F16 = 2 };
+// fp16 frames ("fp16x2" mode) carry RGB as k * 2^-12 and depth as d * 2^-4 (exact power-of-two scalings that keep the
+// stem's folded weights -- w * 4096/255 and w * 16 -- and their lo parts in fp16's normal range)
+constexpr float kF16RgbScale = 1.0f / 4096.0f;
+constexpr float kF16DepthScale = 1.0f / 16.0f;
+
+int launch_ingest(const IngestArgs& a, void* out, int elt /* FrameElt */, cudaStream_t st);
+int launch_repack_nchw(const float* x, int C, int H, int W, int B, void* out, int elt /* FrameElt */,
                        cudaStream_t st);
 
 
@@ -66,15 +73,17 @@ inline size_t conv_p8_wimg_offset(int co, int k) {
   return static_cast<size_t>(co / 8) * 9216 + static_cast<size_t>(k / 8) * 128 + (co % 8) * 16 + (k % 8) * 2;
 }
 int conv_p8_init();
+// x2 = 1: the "fp16x2" mode -- fp16 P8 activations, wimg = the hi image followed by the lo image (2 x 73728 bytes)
 int launch_conv_p8(const void* in_p8, const void* wimg, const float* bias, const void* residual_p8, void* out,
-                   int out_nhwc, int relu, int B, int H, int W, cudaStream_t st);
+                   int out_nhwc, int relu, int B, int H, int W, cudaStream_t st, int x2 = 0);
+// x2 = 1: the "fp16x2" mode -- fp16 frames / output, wimg = the hi image followed by the lo image (2 x 28672 bytes)
 int launch_stem_pool(const void* frames, const void* wimg, const float* bias, void* out_p8, int B, int H,
-                     int W, cudaStream_t st);
+                     int W, cudaStream_t st, int x2 = 0);
 
 // 3x3 stride-2 pad-1 max pooling, NHWC (C % 8 == 0 for bf16, % 4 for fp32).
 int launch_maxpool(const void* in, void* out, int B, int H, int W, int C, bool bf16, cudaStream_t st);
 // global average pool + Linear(C -> n_out) + pixel decode; in is NHWC [B][HW][C].
-// mode: 0 = fp32 input, 1 = bf16, 2 = split bf16 rows [hi(C) | lo(C)]
+// mode: 0 = fp32 input, 1 = bf16, 2 = split bf16 rows [hi(C) | lo(C)], 3 = fp16
 int launch_head(const void* in, const float* fc_w, const float* fc_b, float* out_norm, float* out_px,
                 int B, int HW, int C, int n_out, int imgH, int imgW, int mode, cudaStream_t st);
 // split-bf16 mode: fp32 NHWC in -> [hi(C) | lo(C)] bf16 NHWC out

@@ -9,6 +9,8 @@
 #include <string>
 #include <vector>
 
+#include <cuda_fp16.h>
+
 #include "common.cuh"
 #include "conv_umma.cuh"
 #include "layout.h"
@@ -50,7 +52,8 @@ enum { BUF_FRAMES = 0, BUF_STEM = 1, BUF_R0 = 2, BUF_R1 = 3, BUF_R2 = 4, BUF_R3 
 
 struct pb200_plan {
   int device = 0, max_batch = 0, C = 3, H = 256, W = 256, n_kp = 8, precision = PB200_PREC_BF16;
-  bool bf16 = true;    // single-pass bf16 tcgen05 mode (fused stem, P8 layer1)
+  bool bf16 = true;    // the fused 16-bit tcgen05 path (fused stem, P8 layer1, TMA-im2col layers 2-4): bf16 AND fp16x2 modes
+  bool f16 = false;    // "fp16x2" mode of that path: fp16 activations, weights = fp16 hi + fp16 lo (two MMAs per K step)
   bool split = false;  // split-bf16 "bf16x3" mode: fp32 SIMT stem + maxpool, every later conv on tcgen05 with [hi|lo] operands
   size_t elt = 2;
   std::vector<pb200::ConvSpec> convs;
@@ -84,6 +87,23 @@ static uint16_t f32_to_bf16_rne(float f) {
   u += 0x7fffu + lsb;
   return static_cast<uint16_t>(u >> 16);
 }
+
+static uint16_t f32_to_f16_rne(float f) { return __half_as_ushort(__float2half_rn(f)); }
+static float f16_bits_to_f32(uint16_t h) { return __half2float(__ushort_as_half(h)); }
+
+// restores the caller's current device when a C-ABI entry has to switch to the plan's
+struct DeviceGuard {
+  int prev = -1;
+  cudaError_t err = cudaSuccess;
+  explicit DeviceGuard(int device) {
+    if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+    if (prev != device) err = cudaSetDevice(device);
+    else prev = -1;
+  }
+  ~DeviceGuard() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
 
 static void add_conv(pb200_plan* pl, const std::string& name, const std::string& bn, int Cin, int Cout,
                      int R, int stride, int pad, int Hin, int Win, bool stem = false) {
@@ -216,7 +236,7 @@ static void build_graph(pb200_plan* pl) {
   for (auto& c : pl->convs) {
     const size_t K = (c.stem ? kStemK : static_cast<size_t>(c.R) * c.R * c.Cin) +
                      (c.ds_conv >= 0 ? static_cast<size_t>(pl->convs[c.ds_conv].Cin) : 0);
-    c.w_bytes = K * c.Cout * e;
+    c.w_bytes = K * c.Cout * e * (pl->f16 ? 2 : 1);  // fp16x2: hi image / rows followed by the lo ones
     c.w_off = woff;
     woff = align_up(woff + c.w_bytes, 1024);
     c.b_off = woff;
@@ -245,13 +265,16 @@ extern "C" int pb200_plan_create(pb200_plan** out, int device, int max_batch, in
   PB_CHECK(in_channels >= 1 && in_channels <= 4,
            "plan_create: in_channels %d (the frames layout carries up to 4: R,G,B,D)", in_channels);
   PB_CHECK(n_keypoints >= 1, "plan_create: n_keypoints %d", n_keypoints);
-  PB_CHECK(precision == PB200_PREC_FP32 || precision == PB200_PREC_BF16 || precision == PB200_PREC_BF16X3,
-           "plan_create: precision %d not available (0 = fp32 SIMT, 1 = bf16 tcgen05, 2 = split-bf16 tcgen05)", precision);
+  PB_CHECK(precision == PB200_PREC_FP32 || precision == PB200_PREC_BF16 || precision == PB200_PREC_BF16X3 ||
+               precision == PB200_PREC_FP16X2,
+           "plan_create: precision %d not available (0 = fp32 SIMT, 1 = bf16 tcgen05, 2 = split-bf16 tcgen05, "
+           "3 = fp16 x (hi + lo) tcgen05)", precision);
   PB_CHECK(H % 32 == 0 && W % 32 == 0 && H >= 32 && W >= 32, "plan_create: H, W must be multiples of 32");
   if (precision != PB200_PREC_FP32)
     PB_CHECK(H == 256 && W == 256, "plan_create: the tcgen05 path is tiled for 256x256 frames (got %dx%d); "
              "use PB200_PREC_FP32 for other sizes", H, W);
-  PB_CUDA(cudaSetDevice(device));
+  DeviceGuard guard(device);  // the caller's current device is restored on return
+  PB_CUDA(guard.err);
   if (int rc = require_device()) return rc;
   pb200_plan* pl = new pb200_plan();
   pl->device = device;
@@ -261,7 +284,8 @@ extern "C" int pb200_plan_create(pb200_plan** out, int device, int max_batch, in
   pl->W = W;
   pl->n_kp = n_keypoints;
   pl->precision = precision;
-  pl->bf16 = precision == PB200_PREC_BF16;
+  pl->bf16 = precision == PB200_PREC_BF16 || precision == PB200_PREC_FP16X2;
+  pl->f16 = precision == PB200_PREC_FP16X2;
   pl->split = precision == PB200_PREC_BF16X3;
   // split mode: fp32 frames / stem output, later activations are [hi | lo] bf16 pairs = 4 bytes per value as well
   pl->elt = pl->bf16 ? 2 : 4;
@@ -287,7 +311,10 @@ extern "C" int pb200_plan_create(pb200_plan** out, int device, int max_batch, in
 
 extern "C" void pb200_plan_destroy(pb200_plan* plan) {
   if (!plan) return;
-  if (plan->arena) cudaFree(plan->arena);
+  if (plan->arena) {
+    DeviceGuard guard(plan->device);
+    cudaFree(plan->arena);
+  }
   delete plan;
 }
 
@@ -361,7 +388,8 @@ extern "C" int pb200_plan_load_weights(pb200_plan* plan, const float* const* ten
             int k;
             if (c.stem) {
               k = r * (kStemTaps * kFrameC) + (s + 1) * kFrameC + ci;
-              if (plan->bf16 && ci < 3) v /= 255.0;  // frames carry RGB as integers 0..255
+              if (plan->f16) v *= ci < 3 ? (1.0 / 255.0) / kF16RgbScale : 1.0 / kF16DepthScale;  // frames: k * 2^-12, d * 2^-4
+              else if (plan->bf16 && ci < 3) v /= 255.0;  // frames carry RGB as integers 0..255
             } else {
               k = (r * c.R + s) * c.Cin + ci;
             }
@@ -375,6 +403,16 @@ extern "C" int pb200_plan_load_weights(pb200_plan* plan, const float* const* ten
               uint16_t* row = reinterpret_cast<uint16_t*>(host.data() + c.w_off) + static_cast<size_t>(co) * 2 * K;
               row[k] = hi;
               row[K + k] = f32_to_bf16_rne(wf - hf);
+            } else if (plan->f16) {
+              // w = hi + lo, both fp16: hi image / K-row half first, the lo one right behind it
+              const float wf = static_cast<float>(v);
+              const uint16_t hi = f32_to_f16_rne(wf);
+              const uint16_t lo = f32_to_f16_rne(wf - f16_bits_to_f32(hi));
+              size_t off = (static_cast<size_t>(co) * 2 * Krow + k) * 2, lo_off = static_cast<size_t>(Krow) * 2;
+              if (c.stem) { off = stem_wimg_offset(co, k); lo_off = kStemWimgBytes; }
+              else if (c.p8) { off = conv_p8_wimg_offset(co, k); lo_off = 64 * 576 * 2; }
+              *reinterpret_cast<uint16_t*>(host.data() + c.w_off + off) = hi;
+              *reinterpret_cast<uint16_t*>(host.data() + c.w_off + off + lo_off) = lo;
             } else if (plan->bf16) {
               size_t off = (static_cast<size_t>(co) * Krow + k) * 2;  // [Cout][K] K-major rows (TMA-im2col kernels)
               if (c.stem) off = stem_wimg_offset(co, k);
@@ -405,9 +443,16 @@ extern "C" int pb200_plan_load_weights(pb200_plan* plan, const float* const* ten
       const double sc = static_cast<double>(g->data[co]) / sqrt(static_cast<double>(var->data[co]) + 1e-5);
       bias[co] = static_cast<float>(static_cast<double>(bias[co]) + static_cast<double>(b->data[co]) -
                                     static_cast<double>(mu->data[co]) * sc);
-      uint16_t* row = reinterpret_cast<uint16_t*>(host.data() + c.w_off) + static_cast<size_t>(co) * Krow + K;
-      for (int ci = 0; ci < d.Cin; ++ci)
-        row[ci] = f32_to_bf16_rne(static_cast<float>(static_cast<double>(w->data[static_cast<size_t>(co) * d.Cin + ci]) * sc));
+      uint16_t* row = reinterpret_cast<uint16_t*>(host.data() + c.w_off) + static_cast<size_t>(co) * Krow * (plan->f16 ? 2 : 1) + K;
+      for (int ci = 0; ci < d.Cin; ++ci) {
+        const float wf = static_cast<float>(static_cast<double>(w->data[static_cast<size_t>(co) * d.Cin + ci]) * sc);
+        if (plan->f16) {
+          row[ci] = f32_to_f16_rne(wf);
+          row[Krow + ci] = f32_to_f16_rne(wf - f16_bits_to_f32(row[ci]));
+        } else {
+          row[ci] = f32_to_bf16_rne(wf);
+        }
+      }
     }
   }
   const HostTensor *fw, *fb;
@@ -416,7 +461,8 @@ extern "C" int pb200_plan_load_weights(pb200_plan* plan, const float* const* ten
   if (int rc = need("resnet.fc.bias", {n_out}, &fb)) return rc;
   memcpy(host.data() + plan->fc_w_off, fw->data, sizeof(float) * 512 * n_out);
   memcpy(host.data() + plan->fc_b_off, fb->data, sizeof(float) * n_out);
-  PB_CUDA(cudaSetDevice(plan->device));
+  DeviceGuard guard(plan->device);
+  PB_CUDA(guard.err);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   PB_CUDA(cudaMemcpyAsync(plan->arena, host.data(), plan->arena_bytes, cudaMemcpyHostToDevice, st));
   PB_CUDA(cudaStreamSynchronize(st));
@@ -429,12 +475,23 @@ extern "C" int pb200_plan_load_weights(pb200_plan* plan, const float* const* ten
 // ------------------------------------------------------------------------------------------
 namespace pb200 {
 
+static inline int frame_elt(const pb200_plan* pl) { return pl->f16 ? FRAME_F16 : (pl->bf16 ? FRAME_BF16 : FRAME_F32); }
+
 static inline uint8_t* buf_ptr(const pb200_plan* pl, const void* frames, void* ws, int id) {
   if (id == BUF_FRAMES) return const_cast<uint8_t*>(static_cast<const uint8_t*>(frames));
   return static_cast<uint8_t*>(ws) + pl->buf_off[id];
 }
 
-static int choose_block_n(const ConvSpec& c, int B) {
+static int choose_block_n(const ConvSpec& c, int B, bool f16 = false) {
+  if (f16) {
+    // fp16x2: two MMAs per K step on the same activation tile.  What bounds these layers is the operand bytes landing in
+    // each SM per MMA cycle (profiles/README.md): a CTA pair with a 256-wide tile receives 16 KB (A) + 32 KB (its halves
+    // of the hi and lo weight tiles) per 1024 MMA cycles; 128-wide: 32 KB per 512.  Widest tile that still fills a wave.
+    const long long m_tiles = (static_cast<long long>(B) * c.Ho * c.Wo + 127) / 128;
+    if (c.Cout % 256 == 0 && m_tiles * (c.Cout / 256) >= num_sms()) return 256;
+    if (c.Cout % 128 == 0) return 128;
+    return 64;
+  }
   // Persistent CTAs take ceil(tiles / #SMs) equal tiles each, so the kernel time is rounds x (MMA cycles per tile).
   // An M128 x N x K16 MMA costs max(48, N/2) cycles (tools/mma_bench.cu); ties go to the wider tile (the A tile is
   // re-read from L2 once per N tile).
@@ -471,7 +528,7 @@ static int prepare(pb200_plan* pl, const void* frames, void* ws, int B) {
     const void* ds_in = op.ds_buf >= 0 ? buf_ptr(pl, frames, ws, op.ds_buf) : nullptr;
     const ConvSpec* d = c.ds_conv >= 0 ? &pl->convs[c.ds_conv] : nullptr;
     int rc = build_umma_conv(L, in, B, c.Hin, c.Win, c.Cin, pl->arena + c.w_off, bias, res, out, c.Cout,
-                             c.R, c.stride, c.pad, op.relu, choose_block_n(c, B), 0, pl->split ? 1 : 0,
+                             c.R, c.stride, c.pad, op.relu, choose_block_n(c, B, pl->f16), 0, pl->split ? 1 : (pl->f16 ? 2 : 0),
                              d != nullptr ? ds_in : nullptr, d ? d->Hin : 0, d ? d->Win : 0, d ? d->Cin : 0);
     if (rc) {
       pl->cache_B = -1;
@@ -508,14 +565,14 @@ static int run_op(pb200_plan* pl, const Op& op, const void* frames, void* ws, fl
     case OP_STEM_POOL: {
       const ConvSpec& c = pl->convs[op.conv];
       return launch_stem_pool(frames, pl->arena + c.w_off, reinterpret_cast<const float*>(pl->arena + c.b_off),
-                              buf_ptr(pl, frames, ws, op.out_buf), B, pl->H, pl->W, st);
+                              buf_ptr(pl, frames, ws, op.out_buf), B, pl->H, pl->W, st, pl->f16 ? 1 : 0);
     }
     case OP_CONV_P8: {
       const ConvSpec& c = pl->convs[op.conv];
       return launch_conv_p8(buf_ptr(pl, frames, ws, op.in_buf), pl->arena + c.w_off,
                             reinterpret_cast<const float*>(pl->arena + c.b_off),
                             op.res_buf >= 0 ? buf_ptr(pl, frames, ws, op.res_buf) : nullptr,
-                            buf_ptr(pl, frames, ws, op.out_buf), op.out_nhwc, op.relu, B, c.Hin, c.Win, st);
+                            buf_ptr(pl, frames, ws, op.out_buf), op.out_nhwc, op.relu, B, c.Hin, c.Win, st, pl->f16 ? 1 : 0);
     }
     case OP_MAXPOOL: {
       const ConvSpec& c = pl->convs[0];
@@ -530,7 +587,7 @@ static int run_op(pb200_plan* pl, const Op& op, const void* frames, void* ws, fl
       return launch_head(buf_ptr(pl, frames, ws, op.in_buf),
                          reinterpret_cast<const float*>(pl->arena + pl->fc_w_off),
                          reinterpret_cast<const float*>(pl->arena + pl->fc_b_off), out_norm, out_px, B,
-                         c.Ho * c.Wo, c.Cout, 2 * pl->n_kp, pl->H, pl->W, pl->split ? 2 : (pl->bf16 ? 1 : 0), st);
+                         c.Ho * c.Wo, c.Cout, 2 * pl->n_kp, pl->H, pl->W, pl->split ? 2 : (pl->f16 ? 3 : (pl->bf16 ? 1 : 0)), st);
     }
     default:
       return PB200_OK;
@@ -566,7 +623,7 @@ extern "C" int pb200_forward_nchw_f32(pb200_plan* plan, const float* x_nchw, voi
   if (int rc = check_forward_args(plan, x_nchw, workspace, out_norm, B)) return rc;
   void* frames = static_cast<uint8_t*>(workspace) + plan->buf_off[BUF_FRAMES];
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (int rc = launch_repack_nchw(x_nchw, plan->C, plan->H, plan->W, B, frames, plan->bf16, st)) return rc;
+  if (int rc = launch_repack_nchw(x_nchw, plan->C, plan->H, plan->W, B, frames, frame_elt(plan), st)) return rc;
   return pb200_forward(plan, frames, workspace, out_norm, out_px_or_null, B, stream);
 }
 
@@ -584,8 +641,8 @@ extern "C" const char* pb200_plan_op_kernel(const pb200_plan* plan, int i) {
   if (pl->op_kernels.size() != plan->ops.size()) pl->op_kernels.assign(plan->ops.size(), "");
   std::string& k = pl->op_kernels[i];
   switch (op.kind) {
-    case OP_STEM_POOL: k = "stem_pool_kernel"; break;
-    case OP_CONV_P8: k = "conv_p8_kernel"; break;
+    case OP_STEM_POOL: k = plan->f16 ? "stem_pool_x2_kernel" : "stem_pool_kernel"; break;
+    case OP_CONV_P8: k = plan->f16 ? "conv_p8_x2_kernel" : "conv_p8_kernel"; break;
     case OP_MAXPOOL: k = plan->split ? "maxpool_split_kernel" : (plan->bf16 ? "maxpool_bf16_kernel" : "maxpool_f32_kernel"); break;
     case OP_HEAD: k = "head_kernel"; break;
     case OP_CONV:
@@ -594,7 +651,7 @@ extern "C" const char* pb200_plan_op_kernel(const pb200_plan* plan, int i) {
       else if (plan->cache_B < 0 || plan->umma.size() != plan->convs.size()) k = "conv_umma*";
       else {
         const UmmaConvLaunch& L = plan->umma[op.conv];
-        k = std::string(L.pair ? "conv_umma2_kernel<" : "conv_umma_kernel<") + std::to_string(L.block_n) + (L.split ? ",split>" : ">");
+        k = std::string(L.pair ? "conv_umma2_kernel<" : "conv_umma_kernel<") + std::to_string(L.block_n) + (L.split == 1 ? ",split>" : (L.split == 2 ? ",x2>" : ">"));
       }
       break;
     default: k = ""; break;
@@ -701,7 +758,7 @@ extern "C" int pb200_ingest(const pb200_plan* plan, const uint8_t* rgb, int rgb_
   a.W = plan->W;
   a.B = B;
   a.rgb_integer = plan->bf16 ? 1 : 0;
-  return launch_ingest(a, out_frames, plan->bf16, static_cast<cudaStream_t>(stream));
+  return launch_ingest(a, out_frames, frame_elt(plan), static_cast<cudaStream_t>(stream));
 }
 
 extern "C" int pb200_debug_conv_bf16(const void* in_nhwc, int B, int H, int W, int Cin,
@@ -826,10 +883,94 @@ extern "C" int pb200_debug_conv_split(const void* in_nhwc2, int B, int H, int W,
 
 extern "C" int pb200_debug_stem_pool(pb200_plan* plan, const void* frames, void* out_p8, int B,
                                      pb200_stream stream) {
-  PB_CHECK(plan && frames && out_p8 && plan->bf16 && plan->loaded, "debug_stem_pool: needs a loaded bf16 plan");
+  PB_CHECK(plan && frames && out_p8 && plan->bf16 && plan->loaded, "debug_stem_pool: needs a loaded bf16 / fp16x2 plan");
   const ConvSpec& c = plan->convs[0];
   return launch_stem_pool(frames, plan->arena + c.w_off, reinterpret_cast<const float*>(plan->arena + c.b_off),
-                          out_p8, B, plan->H, plan->W, static_cast<cudaStream_t>(stream));
+                          out_p8, B, plan->H, plan->W, static_cast<cudaStream_t>(stream), plan->f16 ? 1 : 0);
+}
+
+extern "C" int pb200_debug_conv_f16x2(const void* in_nhwc, int B, int H, int W, int Cin, const float* w_oihw_host,
+                                      const float* bias_host, int Cout, int R, int stride, int pad,
+                                      const void* residual_nhwc_or_null, int relu, void* out_nhwc,
+                                      const void* ds_in_nhwc_or_null, int ds_Cin, const float* wds_oi_host_or_null,
+                                      pb200_stream stream) {
+  if (int rc = require_device()) return rc;
+  if (int rc = umma_conv_init()) return rc;
+  PB_CHECK(in_nhwc && w_oihw_host && bias_host && out_nhwc, "debug_conv_f16x2: null argument");
+  const bool ds = ds_in_nhwc_or_null != nullptr;
+  PB_CHECK(!ds || (wds_oi_host_or_null != nullptr && R == 3 && stride == 1 && pad == 1), "debug_conv_f16x2: bad projection");
+  const size_t K = static_cast<size_t>(R) * R * Cin, Krow = K + (ds ? ds_Cin : 0);
+  std::vector<uint16_t> wp(2 * Krow * Cout);  // [Cout][hi Krow | lo Krow]
+  auto put = [&](int co, size_t k, float wf) {
+    const uint16_t hi = f32_to_f16_rne(wf);
+    wp[co * 2 * Krow + k] = hi;
+    wp[co * 2 * Krow + Krow + k] = f32_to_f16_rne(wf - f16_bits_to_f32(hi));
+  };
+  for (int co = 0; co < Cout; ++co) {
+    for (int ci = 0; ci < Cin; ++ci)
+      for (int r = 0; r < R; ++r)
+        for (int s = 0; s < R; ++s)
+          put(co, (static_cast<size_t>(r) * R + s) * Cin + ci, w_oihw_host[((static_cast<size_t>(co) * Cin + ci) * R + r) * R + s]);
+    for (int ci = 0; ds && ci < ds_Cin; ++ci) put(co, K + ci, wds_oi_host_or_null[static_cast<size_t>(co) * ds_Cin + ci]);
+  }
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  void *dw = nullptr, *db = nullptr;
+  PB_CUDA(cudaMalloc(&dw, wp.size() * 2));
+  PB_CUDA(cudaMalloc(&db, sizeof(float) * Cout));
+  int rc = PB200_OK;
+  if (cudaMemcpyAsync(dw, wp.data(), wp.size() * 2, cudaMemcpyHostToDevice, st) != cudaSuccess ||
+      cudaMemcpyAsync(db, bias_host, sizeof(float) * Cout, cudaMemcpyHostToDevice, st) != cudaSuccess)
+    rc = PB200_ERR_CUDA;
+  UmmaConvLaunch L;
+  if (rc == PB200_OK) {
+    int bn = Cout < 256 ? Cout : 256;
+    const char* fbn = getenv("PB200_FORCE_BLOCK_N");  // tests: exercise every tile width
+    if (fbn != nullptr && atoi(fbn) > 0 && Cout % atoi(fbn) == 0) bn = atoi(fbn);
+    rc = build_umma_conv(&L, in_nhwc, B, H, W, Cin, dw, static_cast<const float*>(db), residual_nhwc_or_null, out_nhwc,
+                         Cout, R, stride, pad, relu, bn, 0, 2, ds_in_nhwc_or_null, ds ? 2 * H : 0, ds ? 2 * W : 0,
+                         ds ? ds_Cin : 0);
+  }
+  if (rc == PB200_OK) rc = launch_umma_conv(L, st);
+  cudaError_t e = cudaStreamSynchronize(st);
+  if (rc == PB200_OK && e != cudaSuccess) rc = cuda_fail(e, "debug_conv_f16x2 sync", __FILE__, __LINE__);
+  cudaFree(dw);
+  cudaFree(db);
+  return rc;
+}
+
+extern "C" int pb200_debug_conv_p8_f16x2(const void* in_p8, int B, int H, int W, const float* w_oihw_host,
+                                         const float* bias_host, const void* residual_p8_or_null, int relu,
+                                         void* out, int out_nhwc, pb200_stream stream) {
+  if (int rc = require_device()) return rc;
+  if (int rc = conv_p8_init()) return rc;
+  PB_CHECK(in_p8 && w_oihw_host && bias_host && out, "debug_conv_p8_f16x2: null argument");
+  const size_t img_bytes = 64 * 576 * 2;
+  std::vector<uint8_t> img(2 * img_bytes);  // hi image, then the lo image
+  for (int co = 0; co < 64; ++co)
+    for (int ci = 0; ci < 64; ++ci)
+      for (int r = 0; r < 3; ++r)
+        for (int s = 0; s < 3; ++s) {
+          const float wf = w_oihw_host[((static_cast<size_t>(co) * 64 + ci) * 3 + r) * 3 + s];
+          const uint16_t hi = f32_to_f16_rne(wf);
+          const size_t off = conv_p8_wimg_offset(co, (r * 3 + s) * 64 + ci);
+          *reinterpret_cast<uint16_t*>(img.data() + off) = hi;
+          *reinterpret_cast<uint16_t*>(img.data() + img_bytes + off) = f32_to_f16_rne(wf - f16_bits_to_f32(hi));
+        }
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  void *dw = nullptr, *db = nullptr;
+  PB_CUDA(cudaMalloc(&dw, img.size()));
+  PB_CUDA(cudaMalloc(&db, sizeof(float) * 64));
+  int rc = PB200_OK;
+  if (cudaMemcpyAsync(dw, img.data(), img.size(), cudaMemcpyHostToDevice, st) != cudaSuccess ||
+      cudaMemcpyAsync(db, bias_host, sizeof(float) * 64, cudaMemcpyHostToDevice, st) != cudaSuccess)
+    rc = PB200_ERR_CUDA;
+  if (rc == PB200_OK)
+    rc = launch_conv_p8(in_p8, dw, static_cast<const float*>(db), residual_p8_or_null, out, out_nhwc, relu, B, H, W, st, 1);
+  cudaError_t e = cudaStreamSynchronize(st);
+  if (rc == PB200_OK && e != cudaSuccess) rc = cuda_fail(e, "debug_conv_p8_f16x2 sync", __FILE__, __LINE__);
+  cudaFree(dw);
+  cudaFree(db);
+  return rc;
 }
 
 extern "C" int pb200_debug_conv_p8(const void* in_p8, int B, int H, int W, const float* w_oihw_host,

@@ -149,7 +149,7 @@ int launch_maxpool(const void* in, void* out, int B, int H, int W, int C, bool b
 // them over the HW pixels with coalesced 4-byte (bf16x2) / 8-byte (float2) loads; the means go to
 // shared memory.  Phase 2: each warp produces outputs o = warp, warp+8, ...: lanes stride over
 // the channels, then a 5-step shuffle tree.  Everything after the loads is fp32.
-template <int MODE>  // 0: fp32 input, 1: bf16, 2: split bf16 rows [hi(C) | lo(C)]
+template <int MODE>  // 0: fp32 input, 1: bf16, 2: split bf16 rows [hi(C) | lo(C)], 3: fp16
 __global__ void __launch_bounds__(256)
 head_kernel(const void* __restrict__ in, const float* __restrict__ fc_w,
             const float* __restrict__ fc_b, float* __restrict__ out_norm, float* __restrict__ out_px,
@@ -169,13 +169,13 @@ head_kernel(const void* __restrict__ in, const float* __restrict__ fc_w,
         a0 += bf16_lo(h) + bf16_lo(l);
         a1 += bf16_hi(h) + bf16_hi(l);
       }
-    } else if (MODE == 1) {
+    } else if (MODE == 1 || MODE == 3) {
       const uint32_t* p = static_cast<const uint32_t*>(in) + static_cast<long long>(b) * HW * (C / 2) + c2;
 #pragma unroll 8
       for (int i = 0; i < HW; ++i) {
         const uint32_t v = __ldg(p + static_cast<long long>(i) * (C / 2));
-        a0 += bf16_lo(v);
-        a1 += bf16_hi(v);
+        a0 += lo16<MODE == 3>(v);
+        a1 += hi16<MODE == 3>(v);
       }
     } else {
       const float2* p = static_cast<const float2*>(in) + static_cast<long long>(b) * HW * (C / 2) + c2;
@@ -218,7 +218,9 @@ int launch_head(const void* in, const float* fc_w, const float* fc_b, float* out
   cudaLaunchAttribute attr[1];
   cfg.attrs = attr;
   cfg.numAttrs = pdl_launch_attrs(attr);
-  if (mode == 2)
+  if (mode == 3)
+    PB_CUDA(cudaLaunchKernelEx(&cfg, head_kernel<3>, in, fc_w, fc_b, out_norm, out_px, HW, C, n_out, hw, hh));
+  else if (mode == 2)
     PB_CUDA(cudaLaunchKernelEx(&cfg, head_kernel<2>, in, fc_w, fc_b, out_norm, out_px, HW, C, n_out, hw, hh));
   else if (mode == 1)
     PB_CUDA(cudaLaunchKernelEx(&cfg, head_kernel<1>, in, fc_w, fc_b, out_norm, out_px, HW, C, n_out, hw, hh));

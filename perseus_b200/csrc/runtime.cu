@@ -64,17 +64,25 @@ int pdl_launch_attrs(cudaLaunchAttribute* attrs) {
   return 1;
 }
 
+int current_device() {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) {
+    (void)cudaGetLastError();
+    return 0;
+  }
+  return dev < 0 ? 0 : (dev >= kMaxDevices ? kMaxDevices - 1 : dev);
+}
+
 int num_sms() {
-  static int n = 0;
-  if (n == 0) {
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess ||
-        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) {
+  static int n[kMaxDevices] = {};
+  const int dev = current_device();
+  if (n[dev] == 0) {
+    if (cudaDeviceGetAttribute(&n[dev], cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) {
       (void)cudaGetLastError();
-      n = 148;
+      n[dev] = 148;
     }
   }
-  return n;
+  return n[dev];
 }
 
 // ---- TMA descriptor encoding (cuTensorMapEncodeTiled through the runtime's driver entry point,

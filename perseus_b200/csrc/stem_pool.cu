@@ -44,10 +44,13 @@ constexpr int kSmemW = 0;
 // Second copy of the weight image, 8 K-chunks (= two filter rows) further than a whole image: read through ONE N = 128
 // descriptor (8-channel groups kBSbo apart), rows 64..127 of B are then the SAME channels two filter rows earlier.
 constexpr int kSmemW2 = kStemWimgBytes + 8 * 128;             // 29696
-constexpr int kSmemRing = kSmemW2 + kStemWimgBytes;           // 58368
-constexpr int kSmemXchg = kSmemRing + kRing * kPairBytes;     // + 67584
-constexpr int kSmemBias = kSmemXchg + 2 * 4 * 128;            // + 1024 ([2][4 quarters][64 channels] bf16)
-constexpr int kSmemTotal = kSmemBias + 64 * 4 + 128;          // + alignment slack
+constexpr int kSmemWSet = kSmemW2 + kStemWimgBytes;           // 58368: one weight set = image + shifted copy
+// X2 ("fp16x2" mode: fp16 frames, weights = fp16 hi + fp16 lo): a second weight set (the lo image + its shifted copy)
+// follows the first; every MMA is issued twice, once per set, into the same accumulator.
+__host__ __device__ constexpr int smem_ring(bool x2) { return (x2 ? 2 : 1) * kSmemWSet; }
+__host__ __device__ constexpr int smem_xchg(bool x2) { return smem_ring(x2) + kRing * kPairBytes; }  // + 67584
+__host__ __device__ constexpr int smem_bias(bool x2) { return smem_xchg(x2) + 2 * 4 * 128; }         // + 1024 ([2][4 quarters][64 channels] 16-bit)
+__host__ __device__ constexpr int smem_total(bool x2) { return smem_bias(x2) + 64 * 4 + 128; }       // + alignment slack
 
 struct StemPoolParams {
   const uint8_t* frames;
@@ -58,12 +61,7 @@ struct StemPoolParams {
   long long frame_bytes, out_img_bytes;
 };
 
-__device__ __forceinline__ uint32_t hmax2_u32(uint32_t a, uint32_t b) {
-  __nv_bfloat162 r = __hmax2(*reinterpret_cast<__nv_bfloat162*>(&a), *reinterpret_cast<__nv_bfloat162*>(&b));
-  return *reinterpret_cast<uint32_t*>(&r);
-}
-
-template <int kEpiWarps>
+template <int kEpiWarps, bool X2>
 __device__ __forceinline__ void stem_pool_body(const StemPoolParams& p) {
   constexpr int kCh = 64 / (kEpiWarps / 4);  // channels per epilogue thread
   extern __shared__ uint8_t smem_raw[];
@@ -77,9 +75,9 @@ __device__ __forceinline__ void stem_pool_body(const StemPoolParams& p) {
   const uint32_t raw_addr = smem_u32(smem_raw);
   uint8_t* smem = smem_raw + (((raw_addr + 127u) & ~127u) - raw_addr);
   uint8_t* s_w = smem + kSmemW;
-  uint8_t* s_ring = smem + kSmemRing;
-  uint32_t* s_xchg = reinterpret_cast<uint32_t*>(smem + kSmemXchg);  // [2][4 lane quarters][4 channel quarters][8]
-  float* s_bias = reinterpret_cast<float*>(smem + kSmemBias);
+  uint8_t* s_ring = smem + smem_ring(X2);
+  uint32_t* s_xchg = reinterpret_cast<uint32_t*>(smem + smem_xchg(X2));  // [2][4 lane quarters][4 channel quarters][8]
+  float* s_bias = reinterpret_cast<float*>(smem + smem_bias(X2));
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -120,9 +118,13 @@ __device__ __forceinline__ void stem_pool_body(const StemPoolParams& p) {
     // ================================ producer ====================================
     // whole warp runs the loop (warp-uniform operands); one elected lane issues the copies
     if (elect_one()) {
-      mbar_expect_tx(&w_bar, 2 * kStemWimgBytes);
+      mbar_expect_tx(&w_bar, (X2 ? 4 : 2) * kStemWimgBytes);
       bulk_load_1d(s_w, p.wimg, kStemWimgBytes, &w_bar);
       bulk_load_1d(s_w + kSmemW2, p.wimg, kStemWimgBytes, &w_bar);
+      if (X2) {  // the lo image follows the hi image in global memory
+        bulk_load_1d(s_w + kSmemWSet, p.wimg + kStemWimgBytes, kStemWimgBytes, &w_bar);
+        bulk_load_1d(s_w + kSmemWSet + kSmemW2, p.wimg + kStemWimgBytes, kStemWimgBytes, &w_bar);
+      }
     }
     uint32_t G = 0;
     for (int u = blockIdx.x; u < p.num_units; u += gridDim.x) {
@@ -150,8 +152,8 @@ __device__ __forceinline__ void stem_pool_body(const StemPoolParams& p) {
     // bound by its shared-memory operand fetch (~85 cycles measured for the unaligned no-swizzle rows), not by math.
     // Those five go first (the first one initialises all 128 columns); fr = 0, 1 (conv row 2k only) and fr = 7, 8
     // (conv row 2k+1 only) follow as N = 64 accumulations: 18 MMAs per pair instead of 28.
-    constexpr uint32_t idesc64 = umma_idesc_bf16(128, 64);
-    constexpr uint32_t idesc128 = umma_idesc_bf16(128, 128);
+    constexpr uint32_t idesc64 = umma_idesc_16<X2>(128, 64);
+    constexpr uint32_t idesc128 = umma_idesc_16<X2>(128, 128);
     const uint32_t tm = warp_uniform(tmem_base);
     const uint32_t a_hi = desc_hi_interleaved(128);
     const uint32_t b_hi = desc_hi_interleaved(kBSbo);
@@ -182,9 +184,13 @@ __device__ __forceinline__ void stem_pool_body(const StemPoolParams& p) {
               const int r = fr <= 6 ? fr : fr - 2;               // filter row of the FIRST 64 B rows
               const uint32_t d = d_tmem + (fr > 6 ? 64 : 0);
 #pragma unroll
-              for (int h = 0; h < 2; ++h)
+              for (int h = 0; h < 2; ++h) {
                 umma_bf16_split(d, a_lo + 2 * h, a_hi, b_lo0 + (r * 4 + h * 2) * 8, b_hi, j < 5 ? idesc128 : idesc64,
                                 (j | h) != 0 ? 1u : 0u);
+                if (X2)  // the same frame rows x the lo weight set
+                  umma_bf16_split(d, a_lo + 2 * h, a_hi, b_lo0 + (kSmemWSet >> 4) + (r * 4 + h * 2) * 8, b_hi,
+                                  j < 5 ? idesc128 : idesc64, 1u);
+              }
             }
           }
           umma_commit(&tmem_full_bar[acc]);
@@ -261,7 +267,7 @@ __device__ __forceinline__ void stem_pool_body(const StemPoolParams& p) {
             const float2 b = *reinterpret_cast<const float2*>(bias + 2 * k);
             const float m0 = fmaxf(fmaxf(podd[2 * k], __uint_as_float(xe[2 * k])), __uint_as_float(xo[2 * k]));
             const float m1 = fmaxf(fmaxf(podd[2 * k + 1], __uint_as_float(xe[2 * k + 1])), __uint_as_float(xo[2 * k + 1]));
-            v[k] = pack_bf16x2(fmaxf(m0 + b.x, 0.f), fmaxf(m1 + b.y, 0.f));
+            v[k] = pack16x2<X2>(fmaxf(m0 + b.x, 0.f), fmaxf(m1 + b.y, 0.f));
           }
         }
 #pragma unroll
@@ -305,7 +311,7 @@ __device__ __forceinline__ void stem_pool_body(const StemPoolParams& p) {
         for (int j = 0; j < kHW; ++j) {
           uint32_t left = __shfl_up_sync(0xffffffffu, odd ? mine[j] : part[j], 2);
           if (lane < 2) left = edge[j];
-          mine[j] = hmax2_u32(hmax2_u32(left, mine[j]), part[j]);
+          mine[j] = max16x2<X2>(max16x2<X2>(left, mine[j]), part[j]);
         }
         const int po = k0 + i;
         uint4* orow = out_img + static_cast<long long>(po + 1) * Wp8;
@@ -333,22 +339,25 @@ __device__ __forceinline__ void stem_pool_body(const StemPoolParams& p) {
 }
 
 // 16 epilogue warps x 16 channels (18 warps: 5 on one scheduler, so at most 96 registers per thread) or 8 x 32
-__global__ void __maxnreg__(96) stem_pool_kernel16(const StemPoolParams p) { stem_pool_body<16>(p); }
-__global__ void __launch_bounds__(stem_threads(8), 1) stem_pool_kernel8(const StemPoolParams p) { stem_pool_body<8>(p); }
+__global__ void __maxnreg__(96) stem_pool_kernel16(const StemPoolParams p) { stem_pool_body<16, false>(p); }
+__global__ void __launch_bounds__(stem_threads(8), 1) stem_pool_kernel8(const StemPoolParams p) { stem_pool_body<8, false>(p); }
+__global__ void __maxnreg__(96) stem_pool_x2_kernel16(const StemPoolParams p) { stem_pool_body<16, true>(p); }
 
 }  // namespace
 
 int stem_pool_init() {
-  static bool done = false;
-  if (done) return PB200_OK;
-  PB_CUDA(cudaFuncSetAttribute(stem_pool_kernel16, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
-  PB_CUDA(cudaFuncSetAttribute(stem_pool_kernel8, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
-  done = true;
+  static bool done[kMaxDevices] = {};  // function attributes belong to the device's context
+  const int dev = current_device();
+  if (done[dev]) return PB200_OK;
+  PB_CUDA(cudaFuncSetAttribute(stem_pool_kernel16, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_total(false)));
+  PB_CUDA(cudaFuncSetAttribute(stem_pool_kernel8, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_total(false)));
+  PB_CUDA(cudaFuncSetAttribute(stem_pool_x2_kernel16, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_total(true)));
+  done[dev] = true;
   return PB200_OK;
 }
 
 int launch_stem_pool(const void* frames, const void* wimg, const float* bias, void* out_p8, int B, int H,
-                     int W, cudaStream_t st) {
+                     int W, cudaStream_t st, int x2) {
   PB_CHECK(W == 256 && H % 4 == 0 && H >= 8, "stem_pool: needs W = 256 and H %% 4 == 0 (got %dx%d)", H, W);
   if (B == 0) return PB200_OK;
   const int Hpool = H / 4;
@@ -369,14 +378,15 @@ int launch_stem_pool(const void* frames, const void* wimg, const float* bias, vo
   const int grid = p.num_units < num_sms() ? p.num_units : num_sms();
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(grid);
-  const bool wide = getenv("PB200_STEM_EPI8") != nullptr;
+  const bool wide = !x2 && getenv("PB200_STEM_EPI8") != nullptr;
   cfg.blockDim = dim3(stem_threads(wide ? 8 : 16));
-  cfg.dynamicSmemBytes = kSmemTotal;
+  cfg.dynamicSmemBytes = smem_total(x2 != 0);
   cfg.stream = st;
   cudaLaunchAttribute attr[1];
   cfg.attrs = attr;
   cfg.numAttrs = pdl_launch_attrs(attr);
-  if (wide) PB_CUDA(cudaLaunchKernelEx(&cfg, stem_pool_kernel8, p));
+  if (x2) PB_CUDA(cudaLaunchKernelEx(&cfg, stem_pool_x2_kernel16, p));
+  else if (wide) PB_CUDA(cudaLaunchKernelEx(&cfg, stem_pool_kernel8, p));
   else PB_CUDA(cudaLaunchKernelEx(&cfg, stem_pool_kernel16, p));
   return PB200_OK;
 }

@@ -1,5 +1,6 @@
 // Shared epilogue of the TMA-im2col tcgen05 convolutions (conv_umma.cu, conv_umma2.cu): TMEM accumulator ->
-// + bias (+ residual) -> ReLU -> bf16 NHWC, with every global access of a warp made of COMPLETE 128-byte lines.
+// + bias (+ residual) -> ReLU -> bf16 (fp16 in the "fp16x2" mode, F16 = true) NHWC, with every global access of a warp
+// made of COMPLETE 128-byte lines.
 //
 // An epilogue thread owns one output pixel (TMEM lane) and kCols consecutive channels, i.e. kCols/8 16-byte chunks of
 // that pixel's NHWC row.  Loading / storing those chunks directly makes each instruction of a warp touch 32 different
@@ -144,7 +145,7 @@ __device__ __forceinline__ void load_residual_lines(const __nv_bfloat16* __restr
 
 // One tile slice: kCols accumulator columns of this thread's pixel.  `release()` is called once the accumulator has been
 // read completely (hands the TMEM stage back to the MMA warp).
-template <int kCols, typename Release>
+template <int kCols, bool F16 = false, typename Release>
 __device__ __forceinline__ void epilogue_lines(uint32_t t_addr, const float* __restrict__ bias, bool has_res,
                                                const uint4 (&rv)[kCols / 8], __nv_bfloat16* __restrict__ out,
                                                long long gm_group, long long M_total, int Cout, int col0, int relu,
@@ -170,17 +171,17 @@ __device__ __forceinline__ void epilogue_lines(uint32_t t_addr, const float* __r
         for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(v[8 * j + e]) + bias[chunk * 32 + 8 * j + e];
         if (has_res) {
           const uint4 r4 = rv[chunk * 4 + j];
-          f[0] += bf16_lo(r4.x); f[1] += bf16_hi(r4.x);
-          f[2] += bf16_lo(r4.y); f[3] += bf16_hi(r4.y);
-          f[4] += bf16_lo(r4.z); f[5] += bf16_hi(r4.z);
-          f[6] += bf16_lo(r4.w); f[7] += bf16_hi(r4.w);
+          f[0] += lo16<F16>(r4.x); f[1] += hi16<F16>(r4.x);
+          f[2] += lo16<F16>(r4.y); f[3] += hi16<F16>(r4.y);
+          f[4] += lo16<F16>(r4.z); f[5] += hi16<F16>(r4.z);
+          f[6] += lo16<F16>(r4.w); f[7] += hi16<F16>(r4.w);
         }
         if (relu) {
 #pragma unroll
           for (int e = 0; e < 8; ++e) f[e] = fmaxf(f[e], 0.f);
         }
-        o[h * 4 + j] = make_uint4(pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]), pack_bf16x2(f[4], f[5]),
-                                  pack_bf16x2(f[6], f[7]));
+        o[h * 4 + j] = make_uint4(pack16x2<F16>(f[0], f[1]), pack16x2<F16>(f[2], f[3]), pack16x2<F16>(f[4], f[5]),
+                                  pack16x2<F16>(f[6], f[7]));
       }
     }
     if (s_stat != nullptr) accumulate_stats64(o, gm_group + lane < M_total, s_stat, Cout, col0 + g * 64, lane);

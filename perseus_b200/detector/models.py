@@ -24,6 +24,11 @@ from torchvision import models as tv_models
 from .. import _lib
 
 
+def _device_index(device: torch.device) -> int:
+    """torch.device('cuda') (no index) means the CURRENT device, not device 0."""
+    return device.index if device.index is not None else torch.cuda.current_device()
+
+
 class _Plan:
     """Owns one pb200_plan + its workspace for a (device, precision, max_batch)."""
 
@@ -37,7 +42,7 @@ class _Plan:
         handle = ctypes.c_void_p()
         _lib.check(
             self.lib.pb200_plan_create(
-                ctypes.byref(handle), device.index or 0, max_batch, C, H, W, n_kp, _lib.PRECISIONS[precision]
+                ctypes.byref(handle), _device_index(device), max_batch, C, H, W, n_kp, _lib.PRECISIONS[precision]
             )
         )
         self.handle = handle
@@ -86,8 +91,14 @@ class KeypointCNN(nn.Module):
     """perseus keypoint CNN (ResNet-18 regressor), B200-native inference.
 
     Args mirror the reference (models.py:9): n_keypoints, num_channels, H, W.
-    Extra keyword-only knobs: `precision` ("bf16" = tcgen05 throughput mode, "fp32" = SIMT parity
-    mode) and `max_batch` (initial plan capacity; grows on demand).
+    Extra keyword-only knobs: `max_batch` (initial plan capacity; grows on demand) and `precision`:
+      "fp16x2" (default) tcgen05, fp16 activations x (fp16 hi + fp16 lo) weights, two MMAs per K step: the fast mode
+               that meets north_star's 0.05 px against the reference on RGB (measured ~0.03 px, random-init weights);
+      "bf16"   tcgen05 single pass: the highest throughput, 0.6 px off the reference on random-init weights
+               (opt-in; single-pass bf16 cannot meet 0.05 px, BASELINE.md §4);
+      "bf16x3" tcgen05 split-bf16 (3 MMAs per K step, [hi|lo] activations): ~0.006 px;
+      "fp32"   SIMT FFMA: the <= 1e-3 px parity mode.
+    A plan is bound to one device and one stream at a time (its workspace and cached TMA descriptors are mutable).
     """
 
     def __init__(
@@ -97,7 +108,7 @@ class KeypointCNN(nn.Module):
         H: int = 256,
         W: int = 256,
         *,
-        precision: str = "bf16",
+        precision: str = "fp16x2",
         max_batch: int = 256,
     ) -> None:
         super().__init__()
@@ -142,7 +153,7 @@ class KeypointCNN(nn.Module):
             p.weights_key = None
 
     def _plan(self, device: torch.device, B: int) -> _Plan:
-        key = (device.index or 0, self.precision)
+        key = (_device_index(device), self.precision)
         plan = self._plans.get(key)
         if plan is None or plan.max_batch < B:
             cap = max(B, self._max_batch if plan is None else plan.max_batch)
@@ -215,6 +226,7 @@ class KeypointCNN(nn.Module):
         cube_scale: float = 0.035,
         jitter: torch.Tensor | None = None,
         out: torch.Tensor | None = None,
+        plan: "_Plan | None" = None,
     ) -> torch.Tensor:
         """uint8 (B, h, w, 3|4) [+ float32 depth (B, h, w)] -> the plan's frames buffer (uint8 view).
 
@@ -235,7 +247,7 @@ class KeypointCNN(nn.Module):
             jitter = jitter.to(torch.float32).contiguous()
             if jitter.shape != (B, 2, self.H, self.W):
                 raise ValueError("ingest: jitter must be (B, 2, H, W)")
-        plan = self._plan(rgb_u8.device, B)
+        plan = plan if plan is not None else self._plan(rgb_u8.device, B)
         nbytes = plan.frames_bytes(B)
         if out is None:
             out = torch.empty(nbytes, dtype=torch.uint8, device=rgb_u8.device)
@@ -252,9 +264,26 @@ class KeypointCNN(nn.Module):
             )
         return out
 
-    def forward_ingested(self, frames: torch.Tensor, B: int):
+    def private_plan(self, device: torch.device, max_batch: int) -> "_Plan":
+        """A plan (workspace + packed weights) that this module never regrows or frees: for callers that bake its
+        pointers into a CUDA graph (StreamingDetector).  The caller keeps it alive and reloads the weights through
+        `sync_plan_weights` when the module's parameters change."""
+        plan = _Plan(device, max_batch, self.num_channels, self.H, self.W, self.n_keypoints, self.precision)
+        self.sync_plan_weights(plan)
+        return plan
+
+    def sync_plan_weights(self, plan: "_Plan") -> bool:
+        """(Re)packs the module's current weights into `plan` on the current stream if they changed; True if it did."""
+        wk = self._weights_key()
+        if plan.weights_key == wk:
+            return False
+        plan.load_weights(self.state_dict())
+        plan.weights_key = wk
+        return True
+
+    def forward_ingested(self, frames: torch.Tensor, B: int, plan: "_Plan | None" = None):
         """Backbone + head + decode on an ingested frames buffer -> (norm (B,2K), pixels (B,K,2))."""
-        plan = self._plan(frames.device, B)
+        plan = plan if plan is not None else self._plan(frames.device, B)
         out_norm = torch.empty((B, 2 * self.n_keypoints), dtype=torch.float32, device=frames.device)
         out_px = torch.empty((B, self.n_keypoints, 2), dtype=torch.float32, device=frames.device)
         with torch.cuda.device(frames.device):

@@ -33,9 +33,12 @@ class StreamingDetector:
         self.host_px = torch.empty((batch, model.n_keypoints, 2), dtype=torch.float32).pin_memory()
         self.dev_rgb = torch.empty_like(self.host_rgb, device=self.device)
         self.dev_depth = torch.empty_like(self.host_depth, device=self.device) if self.use_depth else None
-        plan = model._plan(self.device, batch)
-        self.frames = torch.empty(plan.frames_bytes(batch), dtype=torch.uint8, device=self.device)
+        # the detector's OWN plan: the captured graph bakes in its arena / workspace pointers, so it must not be the
+        # model's shared plan (which is freed and re-created when a later forward() needs a larger batch)
         self.stream = torch.cuda.Stream(device=self.device)
+        with torch.cuda.stream(self.stream):
+            self.plan = model.private_plan(self.device, batch)
+        self.frames = torch.empty(self.plan.frames_bytes(batch), dtype=torch.uint8, device=self.device)
         self.graph = None
         self._capture()
 
@@ -43,8 +46,9 @@ class StreamingDetector:
         self.dev_rgb.copy_(self.host_rgb, non_blocking=True)
         if self.use_depth:
             self.dev_depth.copy_(self.host_depth, non_blocking=True)
-        self.model.ingest(self.dev_rgb, self.dev_depth, bgr=self.bgr, depth_divisor=self.depth_divisor, out=self.frames)
-        _, px = self.model.forward_ingested(self.frames, self.B)
+        self.model.ingest(self.dev_rgb, self.dev_depth, bgr=self.bgr, depth_divisor=self.depth_divisor, out=self.frames,
+                          plan=self.plan)
+        _, px = self.model.forward_ingested(self.frames, self.B, plan=self.plan)
         self.host_px.copy_(px, non_blocking=True)
 
     def _capture(self):
@@ -63,6 +67,9 @@ class StreamingDetector:
     def infer_pinned(self) -> torch.Tensor:
         """Frames already written into `host_rgb` / `host_depth`: replay and wait. Returns `host_px` (B, K, 2)."""
         with torch.cuda.stream(self.stream):  # CUDAGraph.replay() launches on the CURRENT stream
+            # load_state_dict / an optimizer step since the last frame: repack into the SAME arena, on this stream
+            # (ordered before the replay; the graph's pointers stay valid)
+            self.model.sync_plan_weights(self.plan)
             self.graph.replay()
         self.stream.synchronize()
         return self.host_px

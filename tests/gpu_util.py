@@ -53,7 +53,7 @@ def synth_depth_m(B, h=256, w=256, seed=0, bad=True):
 
 def frames_view(model, buf: torch.Tensor, B: int):
     """The ingested frames buffer as a (B, H+6, W+8, 4) tensor of the plan's element type."""
-    dt = torch.bfloat16 if model.precision == "bf16" else torch.float32
+    dt = {"bf16": torch.bfloat16, "fp16x2": torch.float16}.get(model.precision, torch.float32)
     n = B * (model.H + 6) * (model.W + 8) * 4
     return buf.view(dt)[:n].view(B, model.H + 6, model.W + 8, 4)
 

@@ -234,29 +234,22 @@ def test_umma_conv_split_layer_vs_fp64(case):
     assert not bad.any(), f"{int(bad.sum())} / {bad.numel()} outputs off; max err {float(err.max()):.6f}; first bad idx {bad.nonzero()[:4].tolist()}"
 
 
-@pytest.mark.parametrize("C", [3, 4])
-def test_forward_bf16x3_mode_meets_the_bf16_tolerance(C):
-    """north_star: bf16-mode outputs within 0.05 px of the reference.  Single-pass bf16 cannot (0.6-0.9 px on
-    random-init weights, like PyTorch's own bf16); the split-bf16 tcgen05 mode does."""
+def _bf16x3_errors(C, bn):
     g = np.load(gu.os.path.join(gu.os.path.dirname(__file__), "golden", "detector_golden.npz"))
-    for bn in (0, 1):
-        model, sd = gu.native_model(C, "bf16x3", seed=0, randomize_bn=bool(bn))
-        x = golden_input(C)
-        y = model(x.cuda())
-        assert y.shape == (2, 16) and y.dtype == torch.float32
-        mx32, _ = gu.px_err(y, torch.from_numpy(g[f"c{C}_bn{bn}_out32"]))
-        emu = do.bf16x3_emulated_forward(sd, x)
-        mx_emu, _ = gu.px_err(y, emu)
-        # random-init RGBD outputs leave the frame by 24x (|y| up to 24.5 normalised = 3100 px, depth enters at 3-14
-        # data units), so the 0.05 px bound is applied per unit of output range: 0.05 px * max(1, max |y|)
-        scale = max(1.0, float(np.abs(g[f"c{C}_bn{bn}_out32"]).max()))
-        print(f"[bf16x3 C={C} bn={bn}] vs reference fp32 {mx32:.5f} px | vs split emulation {mx_emu:.5f} px | "
-              f"output range x{scale:.1f}")
-        assert mx32 <= 0.05 * scale, f"C={C} bn={bn}: {mx32:.4f} px vs the reference"
-        if C == 3:
-            assert mx32 <= 0.05  # in-frame outputs: the plain north_star bound
-    # u8 frames path (ingest -> forward -> decode) on a larger ragged batch
-    model, sd = gu.native_model(C, "bf16x3", max_batch=8)
+    model, sd = gu.native_model(C, "bf16x3", seed=0, randomize_bn=bool(bn))
+    x = golden_input(C)
+    y = model(x.cuda())
+    assert y.shape == (2, 16) and y.dtype == torch.float32
+    mx32, _ = gu.px_err(y, torch.from_numpy(g[f"c{C}_bn{bn}_out32"]))
+    mx_emu, _ = gu.px_err(y, do.bf16x3_emulated_forward(sd, x))
+    print(f"[bf16x3 C={C} bn={bn}] vs reference fp32 {mx32:.5f} px | vs split emulation {mx_emu:.5f} px | "
+          f"max |y| {float(np.abs(g[f'c{C}_bn{bn}_out32']).max()):.1f}")
+    return mx32, mx_emu
+
+
+def _frames_path_error(C, precision):
+    """u8 frames path (ingest -> forward -> decode) on a ragged batch vs the fp32 reference, in plain pixels"""
+    model, sd = gu.native_model(C, precision, max_batch=8)
     B = 5
     rgb = gu.synth_u8_frames(B, 256, 256, 3, seed=11)
     depth = gu.synth_depth_m(B, 256, 256, seed=11) if C == 4 else None
@@ -265,9 +258,31 @@ def test_forward_bf16x3_mode_meets_the_bf16_tolerance(C):
         torch.cat([rgb[b].flip(-1), torch.zeros(256, 256, 1, dtype=torch.uint8)], -1).numpy(),
         None if depth is None else depth[b].numpy(), C) for b in range(B)])
     want = do.denormalize_pixel_coordinates(do.reference_forward(sd, x).reshape(B, 8, 2), 256, 256)
-    err = float((px.cpu() - want).abs().max())
-    print(f"[bf16x3 C={C}] forward_frames: {err:.5f} px vs the reference")
-    assert err <= 0.05 * max(1.0, float(want.abs().max()) / 255.0)
+    return float((px.cpu() - want).abs().max())
+
+
+def test_forward_bf16x3_rgb_meets_the_bf16_mode_tolerance():
+    """north_star: tensor-core-mode outputs within 0.05 px of the reference.  Single-pass bf16 cannot (0.6-0.9 px on
+    random-init weights, like PyTorch's own bf16); the split-bf16 tcgen05 mode does on RGB (measured ~0.006 px)."""
+    for bn in (0, 1):
+        mx32, _ = _bf16x3_errors(3, bn)
+        assert mx32 <= 0.05, f"bn={bn}: {mx32:.4f} px vs the reference"
+    err = _frames_path_error(3, "bf16x3")
+    print(f"[bf16x3 C=3] forward_frames: {err:.5f} px vs the reference")
+    assert err <= 0.05
+
+
+def test_forward_bf16x3_rgbd_bound_not_met_reports_plain_pixels():
+    """RGBD, random-init weights: outputs reach +-24.5 normalised = 3100 px (depth enters at 3-14 data units) and the
+    0.05 px bound is NOT met: 0.11 px measured on B200 (r01; the emulation with exact accumulation gives 0.014 px, the
+    rest is fp32 accumulation in the tensor core at that output range).  Asserted: the measured value + 20 %, in plain
+    pixels, no range scaling."""
+    for bn in (0, 1):
+        mx32, _ = _bf16x3_errors(4, bn)
+        assert mx32 <= 0.132, f"bn={bn}: {mx32:.4f} px vs the reference"
+    err = _frames_path_error(4, "bf16x3")
+    print(f"[bf16x3 C=4] forward_frames: {err:.5f} px vs the reference (bound 0.05 px NOT met on RGBD)")
+    assert err <= 0.2
 
 
 # ---- P8-layout kernels: fused stem + maxpool, resident-weight 3x3 conv ---------------------------------
@@ -343,20 +358,37 @@ def test_conv_p8_vs_exact_operand_reference(B, use_res, relu, nhwc):
     assert not bad.any(), f"{int(bad.sum())}/{bad.numel()} off; max err {float(err.max()):.4f}; first {bad.nonzero()[:4].tolist()}"
 
 # ---- whole forward --------------------------------------------------------------------------------
-@pytest.mark.parametrize("C", [3, 4])
-def test_forward_fp32_mode_matches_reference(C):
-    """BASELINE.json configs[0] through forward(x): golden fixture generated by the real reference."""
+def _fp32_errors(C, bn):
     g = np.load(gu.os.path.join(gu.os.path.dirname(__file__), "golden", "detector_golden.npz"))
+    model, sd = gu.native_model(C, "fp32", seed=0, randomize_bn=bool(bn))
+    x = golden_input(C)
+    y = model(x.cuda())
+    assert y.shape == (2, 16) and y.dtype == torch.float32
+    mx32, _ = gu.px_err(y, torch.from_numpy(g[f"c{C}_bn{bn}_out32"]))
+    mx64, _ = gu.px_err(y, torch.from_numpy(g[f"c{C}_bn{bn}_out64"]))
+    ref_own, _ = gu.px_err(torch.from_numpy(g[f"c{C}_bn{bn}_out32"]), torch.from_numpy(g[f"c{C}_bn{bn}_out64"]))
+    print(f"[fp32 C={C} bn={bn}] vs reference fp32 {mx32:.2e} px | vs fp64 truth {mx64:.2e} px | reference fp32 vs its "
+          f"own fp64 run {ref_own:.2e} px")
+    return mx32, mx64, ref_own
+
+
+def test_forward_fp32_mode_rgb_matches_reference_to_1e3_px():
+    """BASELINE.json configs[0] through forward(x): golden fixture generated by the real reference; north_star's
+    1e-3 px fp32-mode bound, RGB."""
     for bn in (0, 1):
-        model, sd = gu.native_model(C, "fp32", seed=0, randomize_bn=bool(bn))
-        x = golden_input(C)
-        y = model(x.cuda())
-        assert y.shape == (2, 16) and y.dtype == torch.float32
-        mx32, _ = gu.px_err(y, torch.from_numpy(g[f"c{C}_bn{bn}_out32"]))
-        mx64, _ = gu.px_err(y, torch.from_numpy(g[f"c{C}_bn{bn}_out64"]))
-        tol = 1e-3 if C == 3 else 4e-3
-        assert mx32 <= tol, f"C={C} bn={bn}: {mx32:.2e} px vs reference fp32 (vs fp64 truth {mx64:.2e})"
-        assert mx64 <= tol
+        mx32, mx64, _ = _fp32_errors(3, bn)
+        assert mx32 <= 1e-3 and mx64 <= 1e-3, f"bn={bn}: {mx32:.2e} px vs reference fp32 (vs fp64 truth {mx64:.2e})"
+
+
+def test_forward_fp32_mode_rgbd_1e3_px_not_met_is_the_references_own_fp32_noise():
+    """RGBD, random-init weights (outputs up to 3100 px): the 1e-3 px bound is NOT met against the reference's fp32
+    run, because that run is itself 1.1e-3 px away from its own fp64 evaluation -- two fp32
+    summation orders at this output range.  Asserted in plain pixels: within 4e-3 px of the reference and no further
+    from fp64 truth than the reference's own fp32 run is + 1e-3 px."""
+    for bn in (0, 1):
+        mx32, mx64, ref_own = _fp32_errors(4, bn)
+        assert mx32 <= 4e-3, f"bn={bn}: {mx32:.2e} px vs reference fp32"
+        assert mx64 <= ref_own + 1e-3, f"bn={bn}: {mx64:.2e} px vs fp64 truth (reference's own: {ref_own:.2e})"
 
 
 @pytest.mark.parametrize("mode", ["0", "1", "2"])
@@ -387,10 +419,13 @@ def test_forward_bf16_mode_matches_operand_matched_reference(C):
     mx_emu_ref, _ = gu.px_err(emu, ref)
     print(f"[bf16 C={C}] vs emulation max {mx:.4f} mean {mean:.4f} px | vs fp32 ref max {mx_ref:.3f} mean "
           f"{mean_ref:.3f} px | emulation vs ref {mx_emu_ref:.3f} px")
-    scale = float(ref.abs().max())
-    assert mx <= 0.5 * max(1.0, scale / 4), f"bf16 path vs operand-matched emulation: {mx:.3f} px"
-    # format noise, not a bug: same order of magnitude as the emulation's own distance to fp32
-    assert mx_ref <= 3.0 * mx_emu_ref + 0.5
+    # plain pixels, no range scaling.  RGB: measured 0.21 px on B200 (r01).  RGBD outputs reach +-3100 px on random-init
+    # weights, one bf16 ulp there is 8-16 px: the kernel-vs-emulation distance is a handful of 1-ulp activation flips.
+    bound = 0.3 if C == 3 else 3.0
+    assert mx <= bound, f"bf16 path vs operand-matched emulation: {mx:.3f} px (bound {bound} px)"
+    # vs the fp32 reference single-pass bf16 is NOT within north_star's 0.05 px (0.6 px RGB): reported above; the
+    # kernel must not be further from the reference than the emulation's own distance + the bound above
+    assert mx_ref <= mx_emu_ref + bound
 
 
 def test_forward_frames_equals_forward_on_ingested_tensor():
@@ -439,15 +474,31 @@ def test_load_state_dict_refreshes_device_weights():
     assert gu.px_err(y1, do.reference_forward(sd, x.cpu()))[0] <= 1e-3
 
 
-def test_full_size_batch256_properties():
-    """BASELINE.json configs[1] size: batch 256 bf16.  Oracle-free properties: every frame equals
-    the same frame evaluated in a batch of 2; all outputs finite."""
-    model, _ = gu.native_model(3, "bf16", max_batch=256)
-    rgb = gu.synth_u8_frames(256, seed=11).cuda()
-    px = model.forward_frames(rgb)
+@pytest.mark.parametrize("C", [3, 4])
+def test_full_size_batch256_bf16_sampled_frames_vs_emulation(C):
+    """BASELINE.json configs[1] (RGB) and configs[2] (RGBD) at FULL size: batch 256 bf16 through ingest -> backbone ->
+    head -> decode.  8 sampled frames against the operand-matched bf16 emulation of the reference (plain pixels), plus
+    the size-independent property that every frame equals the same frame evaluated in a batch of 2; all outputs finite."""
+    model, sd = gu.native_model(C, "bf16", max_batch=256)
+    rgb = gu.synth_u8_frames(256, seed=11)
+    depth = gu.synth_depth_m(256, seed=11) if C == 4 else None
+    dd = None if depth is None else depth.cuda()
+    px = model.forward_frames(rgb.cuda(), dd, depth_divisor=0.035)
     assert px.shape == (256, 8, 2) and torch.isfinite(px).all()
     for i in (0, 127, 254):
-        assert torch.equal(model.forward_frames(rgb[i:i + 2]), px[i:i + 2])
+        assert torch.equal(model.forward_frames(rgb[i:i + 2].cuda(), None if dd is None else dd[i:i + 2], depth_divisor=0.035),
+                           px[i:i + 2])
+    idx = [0, 1, 63, 64, 127, 128, 254, 255]
+    x = torch.stack([do.streaming_ingest(
+        torch.cat([rgb[b].flip(-1), torch.zeros(256, 256, 1, dtype=torch.uint8)], -1).numpy(),
+        None if depth is None else depth[b].numpy(), C) for b in idx])
+    emu = do.denormalize_pixel_coordinates(do.bf16_emulated_forward(sd, x).reshape(len(idx), 8, 2), 256, 256)
+    ref = do.denormalize_pixel_coordinates(do.reference_forward(sd, x).reshape(len(idx), 8, 2), 256, 256)
+    got = px.cpu()[idx]
+    e_emu, e_ref = float((got - emu).abs().max()), float((got - ref).abs().max())
+    print(f"[bf16 C={C} bs256, 8 sampled frames] vs emulation {e_emu:.4f} px | vs reference fp32 {e_ref:.4f} px "
+          "(single-pass bf16 does not meet 0.05 px)")
+    assert e_emu <= (0.3 if C == 3 else 3.0)
 
 
 def test_streaming_detector_graph_matches_eager_path():

@@ -134,3 +134,23 @@ def test_bf16x3_emulation_meets_the_bf16_tolerance_on_the_golden_vectors(C):
     y = do.bf16x3_emulated_forward(sd, x)
     err = float(((y.double() - torch.from_numpy(g[f"c{C}_bn1_out32"]).double()).abs() * 127.5).max())
     assert err <= 0.05, err
+
+
+def test_fp16x2_emulation_meets_the_bf16_mode_tolerance_on_rgb_golden():
+    """The arithmetic of the "fp16x2" tcgen05 mode (fp16 activations x fp16 hi + lo weights, exact accumulation),
+    emulated on the CPU, is within north_star's 0.05 px of the REAL reference's fp32 outputs (golden fixture) on RGB;
+    on random-init RGBD (outputs up to 3100 px) it is not (0.25-0.30 px), which the GPU tests report in plain pixels."""
+    import numpy as np
+
+    from oracle.make_golden import golden_input
+
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "detector_golden.npz"))
+    for bn in (0, 1):
+        sd = do.seeded_state_dict(3, 8, seed=0, randomize_bn=bool(bn))
+        y = do.fp16x2_emulated_forward(sd, golden_input(3))
+        err = float((y.double() - torch.from_numpy(g[f"c3_bn{bn}_out32"]).double()).abs().max() * 127.5)
+        assert err <= 0.04, err
+    sd = do.seeded_state_dict(4, 8, seed=0, randomize_bn=True)
+    y = do.fp16x2_emulated_forward(sd, golden_input(4))
+    err = float((y.double() - torch.from_numpy(g["c4_bn1_out32"]).double()).abs().max() * 127.5)
+    assert 0.05 < err <= 0.4, err
