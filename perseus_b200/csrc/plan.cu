@@ -352,9 +352,10 @@ extern "C" int pb200_plan_load_weights(pb200_plan* plan, const float* const* ten
     t.data = tensors[i];
     t.shape.assign(shapes[i], shapes[i] + ndims[i]);
     std::string nm(names[i]);
-    const std::string mod = "module.";
-    size_t pos;
-    while ((pos = nm.find(mod)) != std::string::npos) nm.erase(pos, mod.size());  // validate.py:94-96
+    for (const std::string mod : {"module.", "_orig_mod."}) {  // validate.py:94-96 (DDP); torch.compile saves (train.py:194-196)
+      size_t pos;
+      while ((pos = nm.find(mod)) != std::string::npos) nm.erase(pos, mod.size());
+    }
     sd[nm] = t;
   }
   auto need = [&](const std::string& key, std::vector<int64_t> shape, const HostTensor** out) -> int {

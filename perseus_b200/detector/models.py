@@ -167,6 +167,36 @@ class KeypointCNN(nn.Module):
             plan.weights_key = wk
         return plan
 
+    # ---- checkpoints ---------------------------------------------------------------------------
+    _PREFIXES = ("_orig_mod.", "module.")
+
+    @classmethod
+    def normalise_keys(cls, state_dict: dict) -> dict:
+        """Reference checkpoints are `torch.save(model.state_dict())` (train.py:355): under DDP every key carries
+        `module.` (train.py:152), under `torch.compile` (train.py:194-196) `_orig_mod.`, possibly both.  The reference
+        callers strip `module.` themselves (validate.py:94-96) and fail on `_orig_mod.`; here both are accepted."""
+        out = {}
+        for k, v in state_dict.items():
+            changed = True
+            while changed:
+                changed = False
+                for pre in cls._PREFIXES:
+                    if pre in k:
+                        k = k.replace(pre, "")
+                        changed = True
+            out[k] = v
+        return out
+
+    def load_state_dict(self, state_dict, strict: bool = True, assign: bool = False):
+        return super().load_state_dict(self.normalise_keys(state_dict), strict=strict, assign=assign)
+
+    def load_checkpoint(self, path, map_location="cpu") -> "KeypointCNN":
+        """validate.py:93-98 / streaming.py:113-119 in one call: `torch.load(path, weights_only=True)`, prefix strip,
+        strict load, `.eval()`."""
+        sd = torch.load(str(path), weights_only=True, map_location=map_location)
+        self.load_state_dict(sd, strict=True)
+        return self.eval()
+
     # ---- reference API -----------------------------------------------------------------------
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         """x: (B, num_channels, H, W) float, RGB in [0,1], depth in data units -> (B, 2*n_keypoints)."""

@@ -46,7 +46,7 @@ class _Conv:
 class NativeTrainer:
     def __init__(self, model, batch: int, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8,
                  weight_decay: float = 1e-2, max_norm: float = 1.0, l1_beta: float = 1.0, process_group=None,
-                 use_graph: bool = True):
+                 use_graph: bool = True, broadcast_buffers: bool = True, overlap_allreduce: bool = True):
         p0 = next(model.parameters())
         if not p0.is_cuda:
             raise RuntimeError("NativeTrainer: the model must be on a B200 (cuda); there is no CPU training path")
@@ -63,6 +63,18 @@ class NativeTrainer:
         self.step_count = 0
         self.use_graph = use_graph   # forward + backward captured once into a CUDA graph (~250 launches per step)
         self._graph, self._eager_steps = None, 0
+        # DistributedDataParallel semantics mirrored (train.py:152, default arguments):
+        #  * broadcast_buffers=True: before every forward rank 0's BatchNorm running statistics replace every rank's
+        #    (ONE broadcast of the flat 9,600-element buffer); batch statistics stay per rank (no SyncBN in the reference),
+        #    so the running statistics follow rank 0's batches and rank 0's are what a checkpoint holds;
+        #  * gradient all-reduce overlapped with backward: the flat gradient is reduced in two buckets, [layer4, fc]
+        #    (80 % of the bytes, complete after the first two blocks of backward) on NCCL's stream under the rest of
+        #    backward, then [conv1 .. layer3].
+        self.broadcast_buffers = broadcast_buffers
+        self.overlap_allreduce = overlap_allreduce and self.world > 1
+        self._tail_work = None
+        self._graph2 = None
+        self.verify = None   # set to a dict by verify_next_step(): filled with the cross-rank checks of the next step
         self._flatten()
         self._build_graph()
         self._allocate()
@@ -87,8 +99,25 @@ class NativeTrainer:
             self.grad_of[id(p)] = gview
             off += k
         self.n_params = n
-        if self.world > 1:  # DDP's initial parameter broadcast (train.py:152)
+        # first element of the [layer4, fc] gradient bucket (model.parameters() order: conv1, bn1, layer1 .. layer4, fc)
+        first4 = next(self.model.resnet.layer4.parameters())
+        self.tail_off = 0
+        for p in params:
+            if p is first4:
+                break
+            self.tail_off += p.numel()
+        # BatchNorm running statistics in ONE flat buffer (DDP broadcasts the module's buffers before each forward)
+        bufs = [b for nme, b in self.model.named_buffers() if not nme.endswith("num_batches_tracked")]
+        self.flat_bn = torch.empty(sum(b.numel() for b in bufs), **f32)
+        off = 0
+        for b in bufs:
+            k = b.numel()
+            self.flat_bn[off:off + k].copy_(b.detach().reshape(-1).float())
+            b.data = self.flat_bn[off:off + k].view(b.shape)
+            off += k
+        if self.world > 1:  # DDP's initial parameter / buffer broadcast (train.py:152)
             dist.broadcast(self.flat_p, src=0, group=self.pg)
+            dist.broadcast(self.flat_bn, src=0, group=self.pg)
 
     def _g(self, p):
         return self.grad_of[id(p)]
@@ -301,6 +330,20 @@ class NativeTrainer:
 
     def backward(self, target: torch.Tensor) -> torch.Tensor:
         """SmoothL1Loss(pred, target) (train.py:119,290) and the gradient of every parameter into the flat buffer."""
+        loss = self.backward_tail(target)
+        self._after_tail()
+        self.backward_rest()
+        return loss
+
+    def _after_tail(self):
+        """the [layer4, fc] gradients are complete on the current stream: start their all-reduce under the rest of backward"""
+        if self.overlap_allreduce and self.tail_off > 0:
+            if self.verify is not None:
+                self.verify["_tail_local"] = self.flat_g[self.tail_off:self.tail_off + self.verify["n"]].clone()
+            self._tail_work = dist.all_reduce(self.flat_g[self.tail_off:], op=dist.ReduceOp.SUM, group=self.pg, async_op=True)
+
+    def backward_tail(self, target: torch.Tensor) -> torch.Tensor:
+        """loss, head and layer4: everything whose parameter gradients live in flat_g[tail_off:]"""
         B, m = self.B, self.model
         fc = m.resnet.fc
         n_out = fc.weight.shape[0]
@@ -312,7 +355,23 @@ class NativeTrainer:
         _lib.check(self.lib.pb200_train_head_backward(self.dpred.data_ptr(), self.feat.data_ptr(), fc.weight.data_ptr(), B,
                                                       last.Ho * last.Wo, last.Cout, n_out, self._g(fc.weight).data_ptr(),
                                                       self._g(fc.bias).data_ptr(), dY.data_ptr(), self._s()))
-        for c1, c2, ds in reversed(self.blocks):
+        self._dY = (dY, other)
+        self._backward_blocks(self.blocks[6:])
+        return self.loss
+
+    def backward_rest(self) -> None:
+        """layer3 .. layer1 and the stem"""
+        self._backward_blocks(self.blocks[:6])
+        dY, _ = self._dY
+        s = self.stem
+        _lib.check(self.lib.pb200_train_maxpool_backward(dY.data_ptr(), self.pool_idx.data_ptr(), self.dy0.data_ptr(), self.B, s.Ho,
+                                                         s.Wo, 64, self._s()))
+        self._bn_backward(s, self.dy0, "z", self.dz0)
+        self._wgrad(s, self.A, self.dz0)
+
+    def _backward_blocks(self, blocks) -> None:
+        dY, other = self._dY
+        for c1, c2, ds in reversed(blocks):
             # out = relu(bn2(z2) + idn): g = dY * [out > 0] feeds bn2's backward and the identity branch
             self._bn_backward(c2, dY, c2.y, self.dz, g_out=self.g_idn)
             self._wgrad(c2, c1.y, self.dz)
@@ -334,17 +393,26 @@ class NativeTrainer:
             else:
                 self._dgrad(c1, self.dz, other, residual=self.g_idn)
             dY, other = other, dY
-        s = self.stem
-        _lib.check(self.lib.pb200_train_maxpool_backward(dY.data_ptr(), self.pool_idx.data_ptr(), self.dy0.data_ptr(), B, s.Ho,
-                                                         s.Wo, 64, self._s()))
-        self._bn_backward(s, self.dy0, "z", self.dz0)
-        self._wgrad(s, self.A, self.dz0)
-        return self.loss
+        self._dY = (dY, other)
 
     def optimizer_step(self):
-        """gradient all-reduce (NCCL, one call on the flat buffer) + clip_grad_norm_ + AdamW (train.py:300-303)."""
+        """gradient all-reduce (NCCL, SUM; 1/world is folded into the optimizer kernel) + clip_grad_norm_ + AdamW
+        (train.py:300-303).  With overlap the [layer4, fc] bucket has been in flight since backward_tail()."""
         if self.world > 1:
-            dist.all_reduce(self.flat_g, op=dist.ReduceOp.SUM, group=self.pg)
+            vf = self.verify
+            if self._tail_work is not None:
+                if vf is not None:
+                    vf["_head_local"] = self.flat_g[:vf["n"]].clone()
+                self._tail_work.wait()  # the current stream waits for NCCL's
+                self._tail_work = None
+                dist.all_reduce(self.flat_g[:self.tail_off], op=dist.ReduceOp.SUM, group=self.pg)
+            else:
+                if vf is not None:
+                    vf["_head_local"] = self.flat_g[:vf["n"]].clone()
+                    vf["_tail_local"] = self.flat_g[self.tail_off:self.tail_off + vf["n"]].clone()
+                dist.all_reduce(self.flat_g, op=dist.ReduceOp.SUM, group=self.pg)
+            if vf is not None:
+                self._finish_verify()
         self.step_count += 1
         _lib.check(self.lib.pb200_train_adamw_step(
             self.flat_p.data_ptr(), self.flat_g.data_ptr(), self.flat_m.data_ptr(), self.flat_v.data_ptr(), self.n_params,
@@ -352,9 +420,55 @@ class NativeTrainer:
             1.0 / self.world, float(self.max_norm), self.sqnorm.data_ptr(), self._s()))
         self.model.refresh_weights()  # the eval-mode native forward re-folds BN from the updated parameters
 
+    # ---- cross-rank checks (what DDP guarantees, train.py:130,152,300) ---------------------------------------------
+    def verify_next_step(self, n: int = 1 << 20) -> dict:
+        """Arms the checks for the NEXT step(); the returned dict is filled in by that step:
+          grad_allreduce_max_rel_err : |all-reduced gradient - sum of the all-gathered per-rank gradients| over the first n
+                                       elements of each bucket, relative to the largest entry
+          params_identical           : bit-identical flat parameters on every rank after the optimizer step
+          bn_buffers_follow_rank0    : every rank entered the step with rank 0's BatchNorm running statistics"""
+        self.verify = {"n": int(min(n, self.tail_off if self.tail_off > 0 else self.n_params, self.n_params - self.tail_off))}
+        return self.verify
+
+    def _gather(self, t: torch.Tensor) -> list:
+        out = [torch.empty_like(t) for _ in range(self.world)]
+        dist.all_gather(out, t.contiguous(), group=self.pg)
+        return out
+
+    def _finish_verify(self) -> None:
+        vf, n = self.verify, self.verify["n"]
+        worst = 0.0
+        for key, off in (("_head_local", 0), ("_tail_local", self.tail_off)):
+            parts = self._gather(vf.pop(key))
+            want = torch.stack(parts).double().sum(0)
+            got = self.flat_g[off:off + n].double()
+            worst = max(worst, float((got - want).abs().max() / want.abs().max().clamp_min(1e-30)))
+        vf["grad_allreduce_max_rel_err"] = worst
+        vf["_pending_params"] = True
+
+    def _finish_verify_params(self) -> None:
+        vf = self.verify
+        # a checksum cannot prove bit equality; compare the whole buffer against rank 0's
+        ref = self.flat_p.clone()
+        dist.broadcast(ref, src=0, group=self.pg)
+        same = torch.tensor([int(torch.equal(ref, self.flat_p))], device=self.dev)
+        dist.all_reduce(same, op=dist.ReduceOp.MIN, group=self.pg)
+        vf["params_identical"] = bool(same.item())
+        vf.pop("_pending_params")
+        vf["world"] = self.world
+        self.verify = None
+
     def step(self, x: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
         """One training step; returns the (device) loss of this batch."""
         with torch.cuda.device(self.dev):
+            if self.world > 1 and self.broadcast_buffers:
+                dist.broadcast(self.flat_bn, src=0, group=self.pg)  # DDP's per-forward buffer broadcast (train.py:152)
+                if self.verify is not None:
+                    ref = self.flat_bn.clone()
+                    dist.broadcast(ref, src=0, group=self.pg)
+                    same = torch.tensor([int(torch.equal(ref, self.flat_bn))], device=self.dev)
+                    dist.all_reduce(same, op=dist.ReduceOp.MIN, group=self.pg)
+                    self.verify["bn_buffers_follow_rank0"] = bool(same.item())
             if not self.use_graph:
                 self.forward(x)
                 loss = self.backward(target)
@@ -363,10 +477,24 @@ class NativeTrainer:
                 self.t_static.copy_(target.reshape(self.B, -1), non_blocking=True)
                 if self._graph is not None:
                     self._graph.replay()
+                    if self._graph2 is not None:  # the [layer4, fc] all-reduce runs under the second half of backward
+                        self._after_tail()
+                        self._graph2.replay()
                 elif self._eager_steps < 2:  # first steps eagerly: one-off attribute / occupancy queries happen here
                     self.forward(self.x_static)
                     self.backward(self.t_static)
                     self._eager_steps += 1
+                elif self.overlap_allreduce:
+                    g1, g2 = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(g1):
+                        self.forward(self.x_static)
+                        self.backward_tail(self.t_static)
+                    with torch.cuda.graph(g2, pool=g1.pool()):
+                        self.backward_rest()
+                    self._graph, self._graph2 = g1, g2
+                    g1.replay()
+                    self._after_tail()
+                    g2.replay()
                 else:
                     graph = torch.cuda.CUDAGraph()
                     with torch.cuda.graph(graph):
@@ -376,6 +504,8 @@ class NativeTrainer:
                     graph.replay()
                 loss = self.loss
             self.optimizer_step()
+            if self.verify is not None and self.verify.get("_pending_params"):
+                self._finish_verify_params()
         return loss
 
 

@@ -199,3 +199,48 @@ def test_projection_cheirality_flag():
     Rb, tb = np.eye(3)[None], np.array([[0.0, 0.0, -1.0]])
     _, _, cheir = fo.keypoint_projection_factor(Rb, tb, (300, 300, 0, 128, 128), np.zeros((1, 1, 2)), np.zeros((1, 3)))
     assert cheir.all()
+
+
+# ---- projection factor: an independent, autograd-defined statement -------------------------------------------------
+def pinhole_restated(Tb, Tc, K3, p_body, dx):
+    """The reference's OTHER pinhole code path, data_generation/data_utils.py:17-66 (`get_pixel_coordinates`:
+    camera_to_object = camera_pose^-1 @ object_pose, then pypose `point2pixel` = K (T p) / z), restated with 4x4
+    matrices in torch float64 (pypose is absent).  It shares no formula with oracle/factors_oracle.py: homogeneous
+    matrix products, a matrix exponential for the right perturbation T_body Exp(dx) (tangent [rot; trans]), and the
+    3x3 intrinsics matrix instead of Cal3_S2's closed form.  Jacobians come from autograd."""
+    cam_to_obj = torch.linalg.inv(Tc) @ (Tb @ _t_se3_exp(dx))
+    q = cam_to_obj[:3, :3] @ p_body + cam_to_obj[:3, 3]
+    uvw = K3 @ q
+    return uvw[:2] / uvw[2]
+
+
+@pytest.mark.parametrize("skew", [0.0, 3.5])
+@pytest.mark.parametrize("with_camera_pose", [False, True])
+def test_projection_matches_autograd_defined_pinhole(skew, with_camera_pose):
+    rng = np.random.default_rng(5)
+    N, P = 6, 8
+    xi = rng.standard_normal((N, 6)) * np.array([0.6, 0.6, 0.6, 0.05, 0.05, 0.05])
+    Rb, tb = fo.pose_exp(xi)
+    tb[:, 2] += 0.45
+    if with_camera_pose:
+        Rc, tc = fo.pose_exp(np.array([[0.2, -0.1, 0.3, 0.02, -0.03, 0.05]]))
+        Rc, tc = Rc[0], tc[0]
+    else:
+        Rc, tc = np.eye(3), np.zeros(3)
+    K5 = np.array([221.7, 230.1, skew, 128.0, 120.0])
+    K3 = torch.tensor([[K5[0], K5[2], K5[3]], [0.0, K5[1], K5[4]], [0.0, 0.0, 1.0]], dtype=torch.float64)
+    corners = np.array([[a, b, c] for a in (-1, 1) for b in (-1, 1) for c in (-1, 1)], dtype=np.float64) * 0.0175
+    meas = rng.uniform(0, 255, (N, P, 2))
+    err, H, cheir = fo.keypoint_projection_factor(Rb, tb, K5, meas, corners, Rc if with_camera_pose else None,
+                                                  tc if with_camera_pose else None)
+    assert not cheir.any()
+    Tc = _mat4(Rc, tc)
+    z6 = torch.zeros(6, dtype=torch.float64)
+    for n in range(N):
+        Tb = _mat4(Rb[n], tb[n])
+        for p in range(P):
+            pb = torch.tensor(corners[p])
+            pix = pinhole_restated(Tb, Tc, K3, pb, z6)
+            assert np.allclose(err[n, p], pix.numpy() - meas[n, p], atol=1e-9)
+            J = torch.autograd.functional.jacobian(lambda d: pinhole_restated(Tb, Tc, K3, pb, d), z6)
+            assert np.allclose(H[n, p], J.numpy(), atol=1e-8), (n, p)
