@@ -305,7 +305,8 @@ def measure_other_modes(dev, devbuf, iters=20):
 
     out = {}
     n = len(devbuf)
-    for name, C, precision in (("rgbd_bs256_bf16", 4, "bf16"), ("rgb_bs256_bf16x3", 3, "bf16x3")):
+    for name, C, precision in (("rgbd_bs256_bf16", 4, "bf16"), ("rgbd_bs256_fp16x2", 4, "fp16x2"),
+                               ("rgb_bs256_bf16x3", 3, "bf16x3")):
         try:
             m = KeypointCNN(num_channels=C, precision=precision, max_batch=BATCH)
             m.load_state_dict(random_init_state_dict(C, 8, seed=0))
@@ -333,22 +334,54 @@ def measure_other_modes(dev, devbuf, iters=20):
     return out
 
 
-def measure_library_bar(dev, devbuf, iters=20):
+def _fold_bn_resnet(net):
+    """eval-mode BatchNorm folded into the preceding conv (weights scaled, bias added) and replaced by Identity: what an
+    inference deployment of the reference would do before handing the graph to cuDNN."""
+    import torch
+
+    def fuse(conv, bn):
+        sc = bn.weight / torch.sqrt(bn.running_var + bn.eps)
+        fused = torch.nn.Conv2d(conv.in_channels, conv.out_channels, conv.kernel_size, conv.stride, conv.padding, bias=True)
+        fused.weight.data = conv.weight.data * sc[:, None, None, None]
+        fused.bias.data = bn.bias.data - bn.running_mean.data * sc
+        return fused
+
+    net.conv1, net.bn1 = fuse(net.conv1, net.bn1), torch.nn.Identity()
+    for layer in (net.layer1, net.layer2, net.layer3, net.layer4):
+        for blk in layer:
+            blk.conv1, blk.bn1 = fuse(blk.conv1, blk.bn1), torch.nn.Identity()
+            blk.conv2, blk.bn2 = fuse(blk.conv2, blk.bn2), torch.nn.Identity()
+            if blk.downsample is not None:
+                blk.downsample = torch.nn.Sequential(fuse(blk.downsample[0], blk.downsample[1]))
+    return net
+
+
+def measure_library_bar(dev, devbuf, iters=20, compile_too=True):
     """The library bar on the same GPU: the reference's torchvision ResNet-18 module tree run by
-    PyTorch/cuDNN in bf16 channels_last under a CUDA graph, same u8 frames, same step (u8 -> bf16 /255 NCHW-as-NHWC,
-    forward, pixel decode).  Reported next to the native number; none of this repo's kernels run here."""
+    PyTorch/cuDNN in bf16 channels_last, same u8 frames, same step (u8 -> bf16 /255 NCHW-as-NHWC, forward, pixel
+    decode).  Variants: as the reference ships it (eval BatchNorm as separate kernels), with BatchNorm folded into the
+    convs (cuDNN's best case: conv + bias epilogues), each eager and under a CUDA graph, and the folded model through
+    torch.compile (inductor fuses the elementwise tails).  None of this repo's kernels run here."""
     import torch
     from torchvision import models as tv
 
     from perseus_b200.detector.synthetic import random_init_state_dict
 
-    try:
+    res = {"what": "torchvision resnet18 (reference module tree) via PyTorch/cuDNN, bf16 channels_last, bs256, "
+                   "u8->bf16 + forward + decode", "cudnn": torch.backends.cudnn.version()}
+    n = len(devbuf)
+
+    def build(fold):
         net = tv.resnet18(weights=None)
         net.fc = torch.nn.Linear(512, 16)
         sd = {k[len("resnet."):]: v for k, v in random_init_state_dict(3, 8, seed=0).items()}
         net.load_state_dict(sd)
-        net = net.eval().to(dev).to(torch.bfloat16).to(memory_format=torch.channels_last)
-        n = len(devbuf)
+        net.eval()
+        if fold:
+            net = _fold_bn_resnet(net)
+        return net.to(dev).to(torch.bfloat16).to(memory_format=torch.channels_last)
+
+    def bench_variant(net, tag, graph_it=True):
         static_in = torch.empty_like(devbuf[0])
 
         def fwd():
@@ -364,30 +397,102 @@ def measure_library_bar(dev, devbuf, iters=20):
                     fwd()
             torch.cuda.current_stream().wait_stream(s)
             torch.cuda.synchronize()
-            graph = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(graph):
-                out = fwd()  # noqa: F841
-
-            def step_graph(i):
-                static_in.copy_(devbuf[i % n])
-                graph.replay()
 
             def step_eager(i):
                 static_in.copy_(devbuf[i % n])
                 fwd()
 
-            ms_g = _event_time(step_graph, iters)
             ms_e = _event_time(step_eager, iters)
-        res = {"what": "torchvision resnet18 (reference module tree) via PyTorch/cuDNN, bf16 channels_last, bs256, "
-                       "u8->bf16 + forward + decode",
-               "cuda_graph_frames_per_s": BATCH / (ms_g * 1e-3), "cuda_graph_ms_per_step": ms_g,
-               "eager_frames_per_s": BATCH / (ms_e * 1e-3), "eager_ms_per_step": ms_e,
-               "cudnn": torch.backends.cudnn.version()}
-        del graph, net
+            res[f"{tag}eager_frames_per_s"] = BATCH / (ms_e * 1e-3)
+            res[f"{tag}eager_ms_per_step"] = ms_e
+            if graph_it:
+                graph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(graph):
+                    out = fwd()  # noqa: F841
+
+                def step_graph(i):
+                    static_in.copy_(devbuf[i % n])
+                    graph.replay()
+
+                ms_g = _event_time(step_graph, iters)
+                res[f"{tag}cuda_graph_frames_per_s"] = BATCH / (ms_g * 1e-3)
+                res[f"{tag}cuda_graph_ms_per_step"] = ms_g
+                del graph
+
+    for fold, tag in ((False, ""), (True, "bn_folded_")):
+        try:
+            net = build(fold)
+            bench_variant(net, tag)
+            del net
+        except Exception as e:
+            res[f"{tag}error"] = repr(e)[:300]
         torch.cuda.empty_cache()
-        return res
-    except Exception as e:
-        return {"error": repr(e)[:300]}
+    if compile_too:
+        try:
+            t0 = time.perf_counter()
+            net = torch.compile(build(True))
+            bench_variant(net, "bn_folded_compiled_", graph_it=False)
+            res["compile_s"] = time.perf_counter() - t0
+            del net
+        except Exception as e:
+            res["bn_folded_compiled_error"] = repr(e)[:300]
+        torch.cuda.empty_cache()
+    best = max((v for k, v in res.items() if k.endswith("frames_per_s")), default=None)
+    res["best_frames_per_s"] = best
+    return res
+
+
+def measure_factors_sharded(dev, rank, world, peaks, total=1_000_000):
+    """factor evaluation sharded by pose index over the ranks (perseus_b200.sharding.shard_range),
+    constants replicated, no collective on the data path; 1 M poses in total, CUDA events, max over ranks.  Every rank
+    calls this (the timing reduction is a collective); rank 0 reports."""
+    import torch
+    import torch.distributed as dist
+
+    from perseus_b200.sharding import shard_range
+    from perseus_b200.smoother import constant_velocity_batch, keypoint_projection_batch, pose_dynamics_batch
+
+    lo, hi = shard_range(total, rank, world)
+    n = hi - lo
+    g = torch.Generator().manual_seed(1000 + rank)
+    q = torch.nn.functional.normalize(torch.randn(2, n, 4, generator=g, dtype=torch.float64), dim=-1)
+    w, x, y, z = q.unbind(-1)
+    R = torch.stack([1 - 2 * (y * y + z * z), 2 * (x * y - z * w), 2 * (x * z + y * w),
+                     2 * (x * y + z * w), 1 - 2 * (x * x + z * z), 2 * (y * z - x * w),
+                     2 * (x * z - y * w), 2 * (y * z + x * w), 1 - 2 * (x * x + y * y)], -1)
+    t = torch.randn(2, n, 3, generator=g, dtype=torch.float64) * 0.05
+    t[..., 2] += 0.45
+    pose = torch.cat([R, t], -1).to(dev)
+    wv = torch.randn(n, 3, generator=g, dtype=torch.float64).to(dev)
+    vv = torch.randn(n, 3, generator=g, dtype=torch.float64).to(dev)
+    K5 = torch.tensor([221.7, 221.7, 0.0, 128.0, 128.0], dtype=torch.float64, device=dev)
+    corners = torch.tensor([[a, b, c] for a in (-1, 1) for b in (-1, 1) for c in (-1, 1)], dtype=torch.float64, device=dev) * 0.0175
+    meas = (torch.rand(n, 8, 2, generator=g, dtype=torch.float64) * 255).to(dev)
+
+    def step():
+        keypoint_projection_batch(pose[0], K5, meas, corners)
+        pose_dynamics_batch(pose[0], wv, vv, pose[1], 0.1, "world")
+        constant_velocity_batch(vv, wv)
+
+    for _ in range(3):
+        step()
+    dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    reps = 5
+    e0.record()
+    for _ in range(reps):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    tms = torch.tensor([e0.elapsed_time(e1) / reps], device=dev)
+    dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+    ms = float(tms.item())
+    nbytes = total * (1120 + 1152 + 72 + 144)
+    return {"total_poses": total, "poses_per_rank": n, "ranks": world, "ms": ms, "poses_per_s": total / (ms * 1e-3),
+            "algorithmic_GBps_aggregate": nbytes / (ms * 1e-3) / 1e9,
+            "hbm_frac_per_gpu": nbytes / world / (ms * 1e-3) / 1e9 / peaks["hbm_gbs"],
+            "what": "1 M poses sharded by index (shard_range), constants replicated, no collective; max over ranks"}
 
 
 def measure_training(dev, rank, world, steps=12, warmup=4):
@@ -422,6 +527,17 @@ def measure_training(dev, rank, world, steps=12, warmup=4):
         return tr.step(xa, ya.reshape(BATCH, 8, 2))
 
     out = {}
+    if world > 1:
+        # what DDP guarantees (train.py:130,152,300), checked on a real step over NCCL: reduced gradient = sum of the
+        # all-gathered per-rank gradients (1 M-element slice of each bucket), bit-identical parameters on every rank after
+        # the optimizer, BatchNorm running statistics broadcast from rank 0 before the forward
+        for i in range(3):
+            step(i, False)
+        chk = tr.verify_next_step(1 << 20)
+        step(3, False)
+        out["ddp_checks"] = dict(chk)
+        out["ddp_checks"]["overlapped_allreduce"] = tr._graph2 is not None
+        out["ddp_checks"]["buckets_bytes"] = [4 * tr.tail_off, 4 * (tr.n_params - tr.tail_off)]
     for name, with_aug in (("step", False), ("augment_plus_step", True)):
         for i in range(warmup):
             step(i, with_aug)
@@ -442,7 +558,8 @@ def measure_training(dev, rank, world, steps=12, warmup=4):
         out[name] = {"frames_per_s": world * BATCH * steps / (ms * 1e-3), "ms_per_step": ms / steps}
     out["loss_finite"] = bool(torch.isfinite(loss).all())
     out["what"] = ("RGBD bs256/GPU, bf16 activations + fp32 master weights, tcgen05 fwd/dgrad/wgrad, batch-stat BatchNorm, "
-                   f"one NCCL all-reduce of {4 * tr.n_params} gradient bytes per step, clip 1.0 + AdamW; weak scaling; "
+                   f"NCCL all-reduce of {4 * tr.n_params} gradient bytes per step in two buckets ([layer4, fc] overlapped with the "
+                   "rest of backward), per-forward BN-buffer broadcast from rank 0 (DDP semantics), clip 1.0 + AdamW; weak scaling; "
                    "augment_plus_step adds the fused train-time augmentation (5-channel batch -> RGBD + key points)")
     out["steps"] = steps
     del tr, model, aug, xs5
@@ -493,6 +610,115 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
+class Pipeline:
+    """One precision mode of the detector on this rank: the resident step (u8 batch already in HBM) and the
+    end-to-end step (pinned host frames in, pinned host keypoints out, H2D + D2H inside the timed region)."""
+
+    def __init__(self, precision, dev, sd, host, devbuf, copy_streams=1):
+        import torch
+
+        from perseus_b200.detector import KeypointCNN
+
+        self.torch = torch
+        self.precision = precision
+        self.dev = dev
+        self.host, self.devbuf, self.nbuf = host, devbuf, len(devbuf)
+        self.model = KeypointCNN(num_channels=3, precision=precision, max_batch=BATCH)
+        self.model.load_state_dict(sd)
+        self.model.eval().to(dev)
+        plan = self.model._plan(dev, BATCH)
+        self.frames = torch.empty(plan.frames_bytes(BATCH), dtype=torch.uint8, device=dev)
+        # e2e: the public API fed from PINNED HOST frames.  Double-buffered: the H2D copy of batch i+1 runs on a copy
+        # stream while batch i computes; the keypoints of every step are copied back to pinned host memory and the
+        # host reads step i-1's result while step i is in flight (all of it inside the timed region).
+        self.copy_streams = [torch.cuda.Stream(device=dev) for _ in range(copy_streams)]
+        self.dev_in = [torch.empty_like(devbuf[0]) for _ in range(2)]
+        self.px_pinned = [torch.empty((BATCH, 8, 2), dtype=torch.float32).pin_memory() for _ in range(2)]
+        self.ev_copied = [[torch.cuda.Event() for _ in self.copy_streams] for _ in range(2)]
+        self.ev_consumed = [torch.cuda.Event() for _ in range(2)]
+        self.ev_done = [torch.cuda.Event() for _ in range(2)]
+        self.steps = 0
+        self.checksum = 0.0
+
+    def step_resident(self, i):
+        self.model.ingest(self.devbuf[i % self.nbuf], out=self.frames)
+        return self.model.forward_ingested(self.frames, BATCH)[1]
+
+    def _enqueue_copy(self, i):
+        torch = self.torch
+        n = len(self.copy_streams)
+        src, dst = self.host[i % self.nbuf], self.dev_in[i % 2]
+        rows = BATCH // n
+        for c, cs in enumerate(self.copy_streams):  # one plain cudaMemcpyAsync per copy stream (n = 1: the whole batch)
+            with torch.cuda.stream(cs):
+                cs.wait_event(self.ev_consumed[i % 2])
+                dst[c * rows:(c + 1) * rows].copy_(src[c * rows:(c + 1) * rows], non_blocking=True)
+                self.ev_copied[i % 2][c].record(cs)
+
+    def step_e2e(self, i):
+        torch = self.torch
+        main = torch.cuda.current_stream()
+        if i == 0:
+            for e in self.ev_consumed:
+                e.record(main)
+            self._enqueue_copy(0)
+        if i + 1 < self.steps:
+            self._enqueue_copy(i + 1)
+        for e in self.ev_copied[i % 2]:
+            main.wait_event(e)
+        self.model.ingest(self.dev_in[i % 2], out=self.frames)
+        self.ev_consumed[i % 2].record(main)
+        px = self.model.forward_ingested(self.frames, BATCH)[1]
+        self.px_pinned[i % 2].copy_(px, non_blocking=True)
+        self.ev_done[i % 2].record(main)
+        if i > 0:  # the caller consumes step i-1's keypoints while step i runs
+            self.ev_done[(i - 1) % 2].synchronize()
+            self.checksum += float(self.px_pinned[(i - 1) % 2][0, 0, 0])
+        if i + 1 == self.steps:
+            self.ev_done[i % 2].synchronize()
+            self.checksum += float(self.px_pinned[i % 2][0, 0, 0])
+        return self.px_pinned[i % 2]
+
+    def h2d_only(self, i):
+        """the e2e step's host->device traffic alone (same buffers, same copy streams, no compute): its ceiling"""
+        self._enqueue_copy(i)
+        for e in self.ev_copied[i % 2]:
+            self.torch.cuda.current_stream().wait_event(e)
+        self.ev_consumed[i % 2].record(self.torch.cuda.current_stream())
+
+
+def measure_parity(dev, sd_rgb, rgb_u8_host, n_frames=8):
+    """px error of EVERY precision mode against the reference's fp32 forward (oracle port of the reference's PyTorch
+    CPU path, pinned bit-for-bit to the real reference class) on frames of this run's own synthetic batch, through the
+    public u8 path (ingest -> backbone -> head -> decode).  north_star bounds: 1e-3 px (fp32 mode), 0.05 px (bf16 mode)."""
+    import torch
+
+    from oracle import detector_oracle as do
+    from perseus_b200.detector import KeypointCNN
+
+    idx = [int(i) for i in torch.linspace(0, rgb_u8_host.shape[0] - 1, n_frames)]
+    rgb = rgb_u8_host[idx].clone()
+    x = torch.stack([do.dataset_ingest(rgb[b].numpy(), None) for b in range(len(idx))])
+    ref = do.denormalize_pixel_coordinates(do.reference_forward(sd_rgb, x).reshape(len(idx), 8, 2), H, W)
+    out = {"frames": len(idx), "reference": "reference PyTorch fp32 CPU forward (oracle port, bit-identical to the real class)",
+           "bounds_px": {"fp32": 1e-3, "bf16_mode": 0.05}, "modes": {}}
+    for precision in ("fp32", "bf16x3", "fp16x2", "bf16"):
+        try:
+            m = KeypointCNN(num_channels=3, precision=precision, max_batch=len(idx))
+            m.load_state_dict(sd_rgb)
+            m.eval().to(dev)
+            px = m.forward_frames(rgb.to(dev)).cpu()
+            err = (px - ref).abs()
+            bound = 1e-3 if precision == "fp32" else 0.05
+            out["modes"][precision] = {"max_px": float(err.max()), "mean_px": float(err.mean()), "bound_px": bound,
+                                       "meets_bound": bool(float(err.max()) <= bound)}
+            del m
+        except Exception as e:
+            out["modes"][precision] = {"error": repr(e)[:200]}
+    torch.cuda.empty_cache()
+    return out
+
+
 def run_native(args):
     import torch
 
@@ -508,64 +734,21 @@ def run_native(args):
     dev = torch.device("cuda", local)
     torch.cuda.set_device(dev)
 
-    from perseus_b200.detector import KeypointCNN
     from perseus_b200.detector.synthetic import random_init_state_dict
 
     sd = random_init_state_dict(3, 8, seed=0)
-    model = KeypointCNN(num_channels=3, precision="bf16", max_batch=BATCH)
-    model.load_state_dict(sd)
-    model.eval().to(dev)
 
     # synthetic frames: NBUF distinct batches so consecutive steps never re-read a batch from L2
     NBUF = 4
     g = torch.Generator().manual_seed(1234 + rank)
     host = [torch.randint(0, 256, (BATCH, H, W, 3), dtype=torch.uint8, generator=g).pin_memory() for _ in range(NBUF)]
     devbuf = [h.to(dev) for h in host]
-    plan = model._plan(dev, BATCH)
-    frames = torch.empty(plan.frames_bytes(BATCH), dtype=torch.uint8, device=dev)
-
-    def step_resident(i):
-        model.ingest(devbuf[i % NBUF], out=frames)
-        return model.forward_ingested(frames, BATCH)[1]
-
-    # e2e: the public API fed from PINNED HOST frames.  Double-buffered: the H2D copy of batch i+1 runs on a
-    # copy stream while batch i computes; the keypoints of every step are copied back to pinned host memory
-    # and the host reads step i-1's result while step i is in flight (all of it inside the timed region).
-    copy_stream = torch.cuda.Stream(device=dev)
-    dev_in = [torch.empty_like(devbuf[0]) for _ in range(2)]
-    px_pinned = [torch.empty((BATCH, 8, 2), dtype=torch.float32).pin_memory() for _ in range(2)]
-    ev_copied = [torch.cuda.Event() for _ in range(2)]
-    ev_consumed = [torch.cuda.Event() for _ in range(2)]
-    ev_done = [torch.cuda.Event() for _ in range(2)]
-    state = {"steps": 0, "checksum": 0.0}
-
-    def enqueue_copy(i):
-        with torch.cuda.stream(copy_stream):
-            copy_stream.wait_event(ev_consumed[i % 2])
-            dev_in[i % 2].copy_(host[i % NBUF], non_blocking=True)
-            ev_copied[i % 2].record(copy_stream)
-
-    def step_e2e(i):
-        main = torch.cuda.current_stream()
-        if i == 0:
-            for e in ev_consumed:
-                e.record(main)
-            enqueue_copy(0)
-        if i + 1 < state["steps"]:
-            enqueue_copy(i + 1)
-        main.wait_event(ev_copied[i % 2])
-        model.ingest(dev_in[i % 2], out=frames)
-        ev_consumed[i % 2].record(main)
-        px = model.forward_ingested(frames, BATCH)[1]
-        px_pinned[i % 2].copy_(px, non_blocking=True)
-        ev_done[i % 2].record(main)
-        if i > 0:  # the caller consumes step i-1's keypoints while step i runs
-            ev_done[(i - 1) % 2].synchronize()
-            state["checksum"] += float(px_pinned[(i - 1) % 2][0, 0, 0])
-        if i + 1 == state["steps"]:
-            ev_done[i % 2].synchronize()
-            state["checksum"] += float(px_pinned[i % 2][0, 0, 0])
-        return px_pinned[i % 2]
+    n_copy = int(os.environ.get("PB200_COPY_STREAMS", "1"))
+    # headline: single-pass bf16 (BASELINE.json metric "bs256 bf16"); parity mode: fp16x2, the tensor-core mode that
+    # meets north_star's 0.05 px (RGB) -- both measured the same way, side by side
+    pipe = Pipeline("bf16", dev, sd, host, devbuf, n_copy)
+    pipe2 = Pipeline("fp16x2", dev, sd, host, devbuf, n_copy)
+    model, frames = pipe.model, pipe.frames
 
     def barrier():
         if world > 1:
@@ -592,18 +775,36 @@ def run_native(args):
         barrier()
         return ms
 
+    def run_pipeline(p):
+        for i in range(max(args.warmup, 3)):
+            p.step_resident(i)
+        ms = timed(p.step_resident, args.steps)
+        p.steps = 3
+        for i in range(3):
+            p.step_e2e(i)
+        torch.cuda.synchronize()
+        p.steps = args.steps
+        ms_e2e = timed(p.step_e2e, args.steps)
+        return ms, ms_e2e
+
     sampler = ClockSampler(local)
     sampler.start()
-    for i in range(max(args.warmup, 3)):
-        step_resident(i)
-    ms = timed(step_resident, args.steps)
-    state["steps"] = 3
-    for i in range(3):
-        step_e2e(i)
-    torch.cuda.synchronize()
-    state["steps"] = args.steps
-    ms_e2e = timed(step_e2e, args.steps)
+    ms, ms_e2e = run_pipeline(pipe)
     clocks = sampler.stop()
+    sampler2 = ClockSampler(local)
+    sampler2.start()
+    ms2, ms2_e2e = run_pipeline(pipe2)
+    clocks2 = sampler2.stop()
+    # H2D ceiling of the e2e step: every rank streams its pinned batches with the same copies, no compute
+    for i in range(3):
+        pipe.h2d_only(i)
+    ms_h2d = timed(pipe.h2d_only, args.steps)
+    # sustained: the same resident step for >= 2 s (power-capped clocks), reported beside the burst headline
+    sus_steps = max(args.steps, int(os.environ.get("PB200_SUSTAINED_STEPS", "2000")))
+    sampler3 = ClockSampler(local)
+    sampler3.start()
+    ms_sus = timed(pipe.step_resident, sus_steps)
+    clocks3 = sampler3.stop()
 
     value = world * BATCH * args.steps / (ms * 1e-3)
     e2e = world * BATCH * args.steps / (ms_e2e * 1e-3)
@@ -621,18 +822,26 @@ def run_native(args):
         ms_s = timed(step_strong, args.steps)
         strong = {"global_batch": BATCH, "per_gpu_batch": bs, "frames_per_s": BATCH * args.steps / (ms_s * 1e-3),
                   "ms_per_step": ms_s / args.steps}
+    factors_sharded = measure_factors_sharded(dev, rank, world, load_peaks()) if world > 1 else None
     training = measure_training(dev, rank, world) if not args.no_training else None
 
     line = None
     if rank == 0:
         peaks = load_peaks()
-        # roofline of the dominant kernel (largest share of the step): per-launch CUDA events on the launching stream
+        # ---- roofline of the dominant kernel: per-launch CUDA events on the launching stream --------------------
         reps = 5
         acc = None
-        for _ in range(reps):
-            rows = model.profile_ops(frames, BATCH)
+        ing_ms = 0.0
+        for r in range(reps):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            model.ingest(devbuf[r % NBUF], out=frames)
+            e1.record()
+            rows = model.profile_ops(frames, BATCH)  # synchronises
+            ing_ms += e0.elapsed_time(e1)
             acc = rows if acc is None else [(a[0], a[1] + b[1], a[2], a[3], a[4]) for a, b in zip(acc, rows)]
-        rows = [(n, t / reps, f, b, k) for n, t, f, b, k in acc]
+        rows = [("ingest (u8 HWC -> frames)", ing_ms / reps, 0.0, float(BATCH) * 589_824, "ingest_kernel")]
+        rows += [(n, t / reps, f, b, k) for n, t, f, b, k in acc]
         tot_ms = sum(r[1] for r in rows)
         by_kernel = {}
         for n, t, f, b, k in rows:
@@ -641,10 +850,19 @@ def run_native(args):
             e["flops"] += f
             e["bytes"] += b
             e["launches"] += 1
-        dom = max((k for k in by_kernel if by_kernel[k]["flops"] > 1e6), key=lambda k: by_kernel[k]["ms"])
-        conv_ms = sum(e["ms"] for e in by_kernel.values() if e["flops"] > 1e6)
-        conv_flops = sum(e["flops"] for e in by_kernel.values() if e["flops"] > 1e6)
-        peak = peaks["bf16_tflops_sustained"]
+
+        def is_conv(k):  # the tcgen05 convolution kernels (the head's 4 MFLOP GEMV is not one)
+            return k.startswith(("conv_", "stem_pool"))
+
+        dom = max((k for k in by_kernel if is_conv(k)), key=lambda k: by_kernel[k]["ms"])
+        conv_ms = sum(e["ms"] for k, e in by_kernel.items() if is_conv(k))
+        conv_flops = sum(e["flops"] for k, e in by_kernel.items() if is_conv(k))
+        # peak by the run's own clock regime: a short burst at the maximum SM clock is divided by the burst peak, a
+        # power-capped long run by the sustained one; both fractions are printed
+        timed_s = ms * 1e-3
+        at_max = clocks.get("sm_mhz") and clocks.get("sm_max_mhz") and clocks["sm_mhz"] >= 0.97 * clocks["sm_max_mhz"]
+        burst_regime = bool(at_max and timed_s < 1.0)
+        peak = peaks["bf16_tflops"] if burst_regime else peaks["bf16_tflops_sustained"]
         try:
             with open(os.path.join(ROOT, "profiles", "traffic.json")) as fh:
                 traffic = json.load(fh)
@@ -652,31 +870,54 @@ def run_native(args):
             traffic = {}
         d = by_kernel[dom]
         achieved = d["flops"] / (d["ms"] * 1e-3) / 1e12
+        step_tflops = BATCH * FLOPS_PER_FRAME_RGB / (ms / args.steps * 1e-3) / 1e12
+        sus_tflops = BATCH * FLOPS_PER_FRAME_RGB / (ms_sus / sus_steps * 1e-3) / 1e12
         roofline = {
             "bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
             "traffic": traffic.get(dom, {}).get("dram_bytes_per_launch"),
             "kernel": dom, "launches_per_step": d["launches"],
             "algorithmic_flops_per_launch": d["flops"] / d["launches"], "avg_launch_ms": d["ms"] / d["launches"],
-            "peak_source": peaks["source"] + ", sustained bf16 (kernel timed inside a long step); burst "
-                           f"{peaks['bf16_tflops']}",
+            "peak_source": peaks["source"] + (": burst bf16 peak (timed region %.2f s at %s MHz = max clock)" % (timed_s, clocks.get("sm_mhz"))
+                                              if burst_regime else ": sustained bf16 peak (power-capped / long timed region)"),
+            "frac_vs_burst_peak": achieved / peaks["bf16_tflops"],
+            "frac_vs_sustained_peak": achieved / peaks["bf16_tflops_sustained"],
+            "peaks": {"bf16_tflops_burst": peaks["bf16_tflops"], "bf16_tflops_sustained": peaks["bf16_tflops_sustained"],
+                      "hbm_gbs": peaks["hbm_gbs"]},
             "share_of_step": d["ms"] / tot_ms,
+            "tensor_pipe_active_pct_ncu": traffic.get(dom, {}).get("tensor_pipe_active_pct"),
+            "traffic_source": "profiles/traffic.json: per-kernel averages of the committed ncu launch list of this command "
+                              "(profiles/README.md names the file); not measurable inside an unprofiled run",
             "all_tcgen05_conv_kernels": {"achieved": conv_flops / (conv_ms * 1e-3) / 1e12,
                                          "frac": conv_flops / (conv_ms * 1e-3) / 1e12 / peak, "share_of_step": conv_ms / tot_ms},
-            "whole_step_frac": (BATCH * FLOPS_PER_FRAME_RGB / (ms / args.steps * 1e-3) / 1e12) / peak,
+            "whole_step": {"TFLOPs": step_tflops, "frac": step_tflops / peak, "frac_vs_burst_peak": step_tflops / peaks["bf16_tflops"],
+                           "frac_vs_sustained_peak": step_tflops / peaks["bf16_tflops_sustained"]},
+            "whole_step_frac": step_tflops / peak,
             "per_kernel": {k: {"ms": round(e["ms"], 4), "launches": e["launches"],
-                               "TFLOPs": round(e["flops"] / (e["ms"] * 1e-3) / 1e12, 1) if e["flops"] > 1e6 else None,
+                               "TFLOPs": round(e["flops"] / (e["ms"] * 1e-3) / 1e12, 1) if is_conv(k) else None,
                                "GBps": round(e["bytes"] / (e["ms"] * 1e-3) / 1e9, 1),
-                               "dram_bytes_per_launch_ncu": traffic.get(k, {}).get("dram_bytes_per_launch")}
+                               "hbm_frac": None if is_conv(k) else round(e["bytes"] / (e["ms"] * 1e-3) / 1e9 / peaks["hbm_gbs"], 3),
+                               "dram_bytes_per_launch_ncu": traffic.get(k, {}).get("dram_bytes_per_launch"),
+                               "tensor_pipe_active_pct_ncu": traffic.get(k, {}).get("tensor_pipe_active_pct")}
                            for k, e in by_kernel.items()},
             "per_op_ms": {n: round(t, 4) for n, t, _, _, _ in rows},
         }
+        sustained = {"steps": sus_steps, "value": world * BATCH * sus_steps / (ms_sus * 1e-3), "unit": "frames/s",
+                     "ms_per_step": ms_sus / sus_steps, "timed_s": ms_sus * 1e-3, "clocks": clocks3,
+                     "whole_step_TFLOPs": sus_tflops, "whole_step_frac_vs_sustained_peak": sus_tflops / peaks["bf16_tflops_sustained"],
+                     "whole_step_frac_vs_burst_peak": sus_tflops / peaks["bf16_tflops"]}
+        parity = measure_parity(dev, sd, host[0])
         latency = measure_latency(model, dev)
         factors = measure_factors(dev, peaks)
+        if factors_sharded is not None:
+            factors["sharded"] = factors_sharded
         other = measure_other_modes(dev, devbuf)
-        library_bar = measure_library_bar(dev, devbuf)
+        library_bar = measure_library_bar(dev, devbuf, compile_too=(world == 1 and not args.no_compile))
         # cpu_baseline: rank 0 at N = 1 only (under torchrun the other ranks' processes and OMP_NUM_THREADS=1 distort it)
         cpu_fps, cores, cpu_dt = cpu_reference_fps(256, 32) if world == 1 else (None, os.cpu_count() or 1, 0.0)
-        launches_per_step = 1 + len(rows)
+        launches_per_step = len(rows)
+        h2d_bytes = BATCH * H * W * 3
+        h2d_fps = world * BATCH * args.steps / (ms_h2d * 1e-3)
+        pm = parity["modes"]
         line = {
             "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
@@ -686,10 +927,33 @@ def run_native(args):
                        "l2": f"inputs rotate over {NBUF} distinct batches ({NBUF * BATCH * H * W * 3 / 1e6:.0f} MB) "
                              "and each step streams ~1.4 GB of activations (> 126 MB L2)"},
             "clocks": clocks,
-            "e2e": {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": BATCH * H * W * 3,
-                    "d2h_bytes_per_step": BATCH * 8 * 2 * 4, "ms_per_step": ms_e2e / args.steps},
+            "e2e": {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": h2d_bytes,
+                    "d2h_bytes_per_step": BATCH * 8 * 2 * 4, "ms_per_step": ms_e2e / args.steps,
+                    "h2d_ceiling_frames_per_s": h2d_fps, "h2d_ceiling_ms_per_step": ms_h2d / args.steps,
+                    "h2d_ceiling_GBps_per_gpu": h2d_bytes / (ms_h2d / args.steps * 1e-3) / 1e9,
+                    "frac_of_h2d_ceiling": e2e / h2d_fps,
+                    "limiter": ("host->device copy of the u8 batch (pinned host memory -> PCIe): e2e is within 5 % of the "
+                                "copy-only ceiling measured in this run" if e2e >= 0.95 * h2d_fps else
+                                "compute (the copy-only ceiling is higher than the resident step rate)" if h2d_fps > 1.02 * value
+                                else "copy and compute comparable"),
+                    "copy_streams": n_copy},
             "gpu_launches": launches_per_step * args.steps,
             "roofline": roofline,
+            "sustained": sustained,
+            "parity": parity,
+            # the tensor-core mode that MEETS north_star's 0.05 px (RGB), measured exactly like the headline
+            "parity_mode": {"precision": "fp16x2", "dtype": "fp16 activations x (fp16 hi + fp16 lo) weights, fp32 accumulate",
+                            "value": world * BATCH * args.steps / (ms2 * 1e-3), "unit": "frames/s", "ms_per_step": ms2 / args.steps,
+                            "e2e": {"value": world * BATCH * args.steps / (ms2_e2e * 1e-3), "unit": "frames/s",
+                                    "ms_per_step": ms2_e2e / args.steps, "h2d_bytes_per_step": h2d_bytes,
+                                    "d2h_bytes_per_step": BATCH * 8 * 2 * 4},
+                            "max_px_vs_reference": pm.get("fp16x2", {}).get("max_px"),
+                            "meets_0p05_px": pm.get("fp16x2", {}).get("meets_bound"),
+                            "headline_mode_max_px_vs_reference": pm.get("bf16", {}).get("max_px"),
+                            "algorithmic_TFLOPs": BATCH * FLOPS_PER_FRAME_RGB / (ms2 / args.steps * 1e-3) / 1e12,
+                            "issued_mma_TFLOPs": 2 * BATCH * FLOPS_PER_FRAME_RGB / (ms2 / args.steps * 1e-3) / 1e12,
+                            "issued_mma_frac_of_burst_peak": 2 * BATCH * FLOPS_PER_FRAME_RGB / (ms2 / args.steps * 1e-3) / 1e12 / peaks["bf16_tflops"],
+                            "clocks": clocks2},
             "latency": latency,
             "factors": factors,
             "other_modes": other,
@@ -717,6 +981,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--no-training", action="store_true", help="skip the configs[3] training-step section")
+    ap.add_argument("--no-compile", action="store_true", help="skip the torch.compile variant of the library bar")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
