@@ -612,12 +612,13 @@ def run_reference(args):
 
 class Pipeline:
     """One precision mode of the detector on this rank: the resident step (u8 batch already in HBM) and the
-    end-to-end step (pinned host frames in, pinned host keypoints out, H2D + D2H inside the timed region)."""
+    end-to-end step through the public batched API (perseus_b200.detector.BatchPipeline: pinned host frames in, pinned
+    host keypoints out; the H2D copy of every batch and the D2H read of every result are inside the timed region)."""
 
     def __init__(self, precision, dev, sd, host, devbuf, copy_streams=1):
         import torch
 
-        from perseus_b200.detector import KeypointCNN
+        from perseus_b200.detector import BatchPipeline, KeypointCNN
 
         self.torch = torch
         self.precision = precision
@@ -628,15 +629,8 @@ class Pipeline:
         self.model.eval().to(dev)
         plan = self.model._plan(dev, BATCH)
         self.frames = torch.empty(plan.frames_bytes(BATCH), dtype=torch.uint8, device=dev)
-        # e2e: the public API fed from PINNED HOST frames.  Double-buffered: the H2D copy of batch i+1 runs on a copy
-        # stream while batch i computes; the keypoints of every step are copied back to pinned host memory and the
-        # host reads step i-1's result while step i is in flight (all of it inside the timed region).
-        self.copy_streams = [torch.cuda.Stream(device=dev) for _ in range(copy_streams)]
-        self.dev_in = [torch.empty_like(devbuf[0]) for _ in range(2)]
-        self.px_pinned = [torch.empty((BATCH, 8, 2), dtype=torch.float32).pin_memory() for _ in range(2)]
-        self.ev_copied = [[torch.cuda.Event() for _ in self.copy_streams] for _ in range(2)]
-        self.ev_consumed = [torch.cuda.Event() for _ in range(2)]
-        self.ev_done = [torch.cuda.Event() for _ in range(2)]
+        self.bp = BatchPipeline(self.model, BATCH, H, W, 3, copy_streams=copy_streams)
+        self.lag = 2  # the caller reads batch i-2's keypoints while batches i-1 and i are in flight
         self.steps = 0
         self.checksum = 0.0
 
@@ -644,47 +638,16 @@ class Pipeline:
         self.model.ingest(self.devbuf[i % self.nbuf], out=self.frames)
         return self.model.forward_ingested(self.frames, BATCH)[1]
 
-    def _enqueue_copy(self, i):
-        torch = self.torch
-        n = len(self.copy_streams)
-        src, dst = self.host[i % self.nbuf], self.dev_in[i % 2]
-        rows = BATCH // n
-        for c, cs in enumerate(self.copy_streams):  # one plain cudaMemcpyAsync per copy stream (n = 1: the whole batch)
-            with torch.cuda.stream(cs):
-                cs.wait_event(self.ev_consumed[i % 2])
-                dst[c * rows:(c + 1) * rows].copy_(src[c * rows:(c + 1) * rows], non_blocking=True)
-                self.ev_copied[i % 2][c].record(cs)
-
     def step_e2e(self, i):
-        torch = self.torch
-        main = torch.cuda.current_stream()
-        if i == 0:
-            for e in self.ev_consumed:
-                e.record(main)
-            self._enqueue_copy(0)
-        if i + 1 < self.steps:
-            self._enqueue_copy(i + 1)
-        for e in self.ev_copied[i % 2]:
-            main.wait_event(e)
-        self.model.ingest(self.dev_in[i % 2], out=self.frames)
-        self.ev_consumed[i % 2].record(main)
-        px = self.model.forward_ingested(self.frames, BATCH)[1]
-        self.px_pinned[i % 2].copy_(px, non_blocking=True)
-        self.ev_done[i % 2].record(main)
-        if i > 0:  # the caller consumes step i-1's keypoints while step i runs
-            self.ev_done[(i - 1) % 2].synchronize()
-            self.checksum += float(self.px_pinned[(i - 1) % 2][0, 0, 0])
-        if i + 1 == self.steps:
-            self.ev_done[i % 2].synchronize()
-            self.checksum += float(self.px_pinned[i % 2][0, 0, 0])
-        return self.px_pinned[i % 2]
+        t = self.bp.submit(self.host[i % self.nbuf])
+        if i >= self.lag:
+            self.checksum += float(self.bp.result(t - self.lag)[0, 0, 0])
+        if i + 1 == self.steps:  # the last results are read inside the timed region too
+            for k in range(min(self.lag, self.steps) - 1, -1, -1):
+                self.checksum += float(self.bp.result(t - k)[0, 0, 0])
 
     def h2d_only(self, i):
-        """the e2e step's host->device traffic alone (same buffers, same copy streams, no compute): its ceiling"""
-        self._enqueue_copy(i)
-        for e in self.ev_copied[i % 2]:
-            self.torch.cuda.current_stream().wait_event(e)
-        self.ev_consumed[i % 2].record(self.torch.cuda.current_stream())
+        self.bp.copy_only(self.host[i % self.nbuf])
 
 
 def measure_parity(dev, sd_rgb, rgb_u8_host, n_frames=8):
@@ -757,13 +720,15 @@ def run_native(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(fn, steps):
+    def timed(fn, steps, stream=None):
+        """CUDA events on the stream the work is launched on (torch's current stream, or the pipeline's compute stream)"""
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for i in range(steps):
-            fn(i)
-        e1.record()
+        with torch.cuda.stream(stream if stream is not None else torch.cuda.current_stream()):
+            e0.record()
+            for i in range(steps):
+                fn(i)
+            e1.record()
         torch.cuda.synchronize()
         ms = e0.elapsed_time(e1)
         if world > 1:
@@ -779,12 +744,12 @@ def run_native(args):
         for i in range(max(args.warmup, 3)):
             p.step_resident(i)
         ms = timed(p.step_resident, args.steps)
-        p.steps = 3
-        for i in range(3):
+        p.steps = 4
+        for i in range(4):
             p.step_e2e(i)
         torch.cuda.synchronize()
         p.steps = args.steps
-        ms_e2e = timed(p.step_e2e, args.steps)
+        ms_e2e = timed(p.step_e2e, args.steps, stream=p.bp.compute)
         return ms, ms_e2e
 
     sampler = ClockSampler(local)
@@ -798,7 +763,7 @@ def run_native(args):
     # H2D ceiling of the e2e step: every rank streams its pinned batches with the same copies, no compute
     for i in range(3):
         pipe.h2d_only(i)
-    ms_h2d = timed(pipe.h2d_only, args.steps)
+    ms_h2d = timed(pipe.h2d_only, args.steps, stream=pipe.bp.compute)
     # sustained: the same resident step for >= 2 s (power-capped clocks), reported beside the burst headline
     sus_steps = max(args.steps, int(os.environ.get("PB200_SUSTAINED_STEPS", "2000")))
     sampler3 = ClockSampler(local)
@@ -831,16 +796,14 @@ def run_native(args):
         # ---- roofline of the dominant kernel: per-launch CUDA events on the launching stream --------------------
         reps = 5
         acc = None
-        ing_ms = 0.0
         for r in range(reps):
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
             model.ingest(devbuf[r % NBUF], out=frames)
-            e1.record()
             rows = model.profile_ops(frames, BATCH)  # synchronises
-            ing_ms += e0.elapsed_time(e1)
             acc = rows if acc is None else [(a[0], a[1] + b[1], a[2], a[3], a[4]) for a, b in zip(acc, rows)]
-        rows = [("ingest (u8 HWC -> frames)", ing_ms / reps, 0.0, float(BATCH) * 589_824, "ingest_kernel")]
+        # the ingest kernel: 16 back-to-back launches over the rotating batches (one launch after an idle sync would time
+        # the launch latency, not the kernel)
+        ing_ms = _event_time(lambda i: model.ingest(devbuf[i % NBUF], out=frames), 16)
+        rows = [("ingest (u8 HWC -> frames)", ing_ms, 0.0, float(BATCH) * 589_824, "ingest_kernel")]
         rows += [(n, t / reps, f, b, k) for n, t, f, b, k in acc]
         tot_ms = sum(r[1] for r in rows)
         by_kernel = {}
@@ -914,7 +877,7 @@ def run_native(args):
         library_bar = measure_library_bar(dev, devbuf, compile_too=(world == 1 and not args.no_compile))
         # cpu_baseline: rank 0 at N = 1 only (under torchrun the other ranks' processes and OMP_NUM_THREADS=1 distort it)
         cpu_fps, cores, cpu_dt = cpu_reference_fps(256, 32) if world == 1 else (None, os.cpu_count() or 1, 0.0)
-        launches_per_step = len(rows)
+        launches_per_step = 1 + model._plan(dev, BATCH).lib.pb200_plan_launches_at(model._plan(dev, BATCH).handle, BATCH)
         h2d_bytes = BATCH * H * W * 3
         h2d_fps = world * BATCH * args.steps / (ms_h2d * 1e-3)
         pm = parity["modes"]
@@ -936,7 +899,10 @@ def run_native(args):
                                 "copy-only ceiling measured in this run" if e2e >= 0.95 * h2d_fps else
                                 "compute (the copy-only ceiling is higher than the resident step rate)" if h2d_fps > 1.02 * value
                                 else "copy and compute comparable"),
-                    "copy_streams": n_copy},
+                    "copy_streams": n_copy,
+                    "api": "perseus_b200.detector.BatchPipeline.submit(pinned u8 batch) / .result(ticket): one cudaMemcpyAsync "
+                           "per batch on a copy stream, one CUDA-graph replay (ingest+backbone+head+decode) per batch, "
+                           "16 KB D2H per batch; the host reads batch i-2 while i-1, i are in flight"},
             "gpu_launches": launches_per_step * args.steps,
             "roofline": roofline,
             "sustained": sustained,

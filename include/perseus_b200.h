@@ -130,8 +130,10 @@ const char* pb200_plan_op_kernel(const pb200_plan* plan, int i);
 int pb200_plan_op_work(const pb200_plan* plan, int i, int B, double* flops, double* bytes);
 int pb200_forward_profile(pb200_plan* plan, const void* frames, void* workspace, float* out_norm,
                           float* out_px_or_null, int B, pb200_stream stream, float* ms);
-/* number of kernel launches one pb200_forward issues */
+/* number of kernel launches one pb200_forward issues (batch sizes up to the L2 chunk of the front layers) */
 int pb200_plan_launches_per_forward(const pb200_plan* plan);
+/* the same at batch size B: the fused stem + layer1 kernels run once per L2 chunk of frames */
+int pb200_plan_launches_at(const pb200_plan* plan, int B);
 
 /* ---- stand-alone pieces (also used by the parity tests) ------------------------------- */
 

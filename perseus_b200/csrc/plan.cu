@@ -73,6 +73,12 @@ struct pb200_plan {
   std::vector<pb200::UmmaConvLaunch> umma;  // per conv
   std::vector<std::string> op_names;
   std::vector<std::string> op_kernels;  // kernel each op launches (known after the first forward at a batch size)
+  // L2 chunking of the front of the network (fused stem + the four layer1 convs, P8 layout): these five kernels move
+  // 10 x 140 MB of activations per 256 frames and are co-bound by HBM; run on sub-batches of l1_chunk frames their
+  // three P8 buffers (22 MB each at 40 frames) stay L2-resident and only the frames and the NHWC hand-over to layer2
+  // touch HBM.  40 frames = 1320 layer1 tiles = 8.92 waves of 148 SMs.  0 = off (PB200_L1_CHUNK overrides).
+  int l1_chunk = 40;
+  int n_front = 0;  // leading ops that are chunked (OP_STEM_POOL + OP_CONV_P8 x 4)
 };
 
 namespace pb200 {
@@ -231,6 +237,12 @@ static void build_graph(pb200_plan* pl) {
     off += align_up(pl->buf_per_frame[i] * pl->max_batch + (i >= BUF_P8A ? kP8SlackBytes : 0), 1024);
   }
   pl->workspace_bytes = off;
+  pl->n_front = 0;
+  if (pl->bf16)
+    while (pl->n_front < static_cast<int>(pl->ops.size()) &&
+           (pl->ops[pl->n_front].kind == OP_STEM_POOL || pl->ops[pl->n_front].kind == OP_CONV_P8))
+      ++pl->n_front;
+  if (const char* e = getenv("PB200_L1_CHUNK")) pl->l1_chunk = atoi(e);
   // weight arena
   size_t woff = 0;
   for (auto& c : pl->convs) {
@@ -478,38 +490,61 @@ namespace pb200 {
 
 static inline int frame_elt(const pb200_plan* pl) { return pl->f16 ? FRAME_F16 : (pl->bf16 ? FRAME_BF16 : FRAME_F32); }
 
-static inline uint8_t* buf_ptr(const pb200_plan* pl, const void* frames, void* ws, int id) {
-  if (id == BUF_FRAMES) return const_cast<uint8_t*>(static_cast<const uint8_t*>(frames));
-  return static_cast<uint8_t*>(ws) + pl->buf_off[id];
+// n0 = first frame of an L2 chunk (0 when the op runs on the whole batch): offsets the frames and the NHWC buffers; the
+// P8 buffers of a chunked run are chunk-local (always at their base, so they are re-used chunk after chunk in L2)
+static inline uint8_t* buf_ptr(const pb200_plan* pl, const void* frames, void* ws, int id, int n0 = 0) {
+  if (id == BUF_FRAMES)
+    return const_cast<uint8_t*>(static_cast<const uint8_t*>(frames)) + static_cast<size_t>(n0) * pl->buf_per_frame[BUF_FRAMES];
+  return static_cast<uint8_t*>(ws) + pl->buf_off[id] + (id >= BUF_P8A ? 0 : static_cast<size_t>(n0) * pl->buf_per_frame[id]);
 }
 
-static int choose_block_n(const ConvSpec& c, int B, bool f16 = false) {
-  if (f16) {
-    // fp16x2: two MMAs per K step on the same activation tile.  What bounds these layers is the operand bytes landing in
-    // each SM per MMA cycle (profiles/README.md): a CTA pair with a 256-wide tile receives 16 KB (A) + 32 KB (its halves
-    // of the hi and lo weight tiles) per 1024 MMA cycles; 128-wide: 32 KB per 512.  Widest tile that still fills a wave.
-    const long long m_tiles = (static_cast<long long>(B) * c.Ho * c.Wo + 127) / 128;
-    if (c.Cout % 256 == 0 && m_tiles * (c.Cout / 256) >= num_sms()) return 256;
-    if (c.Cout % 128 == 0) return 128;
-    return 64;
-  }
-  // Persistent CTAs take ceil(tiles / #SMs) equal tiles each, so the kernel time is rounds x (MMA cycles per tile).
-  // An M128 x N x K16 MMA costs max(48, N/2) cycles (tools/mma_bench.cu); ties go to the wider tile (the A tile is
-  // re-read from L2 once per N tile).
+// Tile choice of a TMA-im2col conv: BLOCK_N in {64, 128, 256} x {single CTA, CTA pair}.  Cost model (cycles per 64-deep
+// k-block and per CTA, measured with tools/mma_bench.cu and the r01/r02 per-op profiles): persistent CTAs take
+// ceil(items / units) equal work items; a k-block costs max(MMA issue time, shared-memory traffic / bandwidth), where
+//   MMA     = 4 K-steps x passes x max(48, N/2) cycles (an M128 x N x K16 MMA; passes = 2 in the fp16x2 mode),
+//   traffic = what the MMAs READ from shared memory (4 x passes x (4 KB of A + 32 B per weight row held by this CTA))
+//             + what TMA WRITES into it (16 KB of A + 128 B per weight row and pass),
+// at 128 B/clk x 0.85.  A pair holds half of the weight rows per CTA, which is what makes the wide tiles pay: the r01
+// choice (pair<128> for layer3, single<256> for layer4) sat at 452 / 903 cycles per k-block where pair<256> needs 602
+// for twice / the same the work (measured 473 / 810).
+static void choose_tile(const ConvSpec& c, int B, bool f16, int* block_n, int* cluster) {
   const long long m_tiles = (static_cast<long long>(B) * c.Ho * c.Wo + 127) / 128;
-  int best = 64;
-  long long best_cost = -1;
+  const int passes = f16 ? 2 : 1;
+  double best_cost = -1.0;
+  *block_n = 64;
+  *cluster = 1;
   for (int bn = 64; bn <= 256 && bn <= c.Cout; bn *= 2) {
     if (c.Cout % bn) continue;
-    const long long tiles = m_tiles * (c.Cout / bn);
-    const long long rounds = (tiles + num_sms() - 1) / num_sms();
-    const long long cost = rounds * (bn / 2 < 48 ? 48 : bn / 2);
-    if (best_cost < 0 || cost <= best_cost) {
-      best = bn;
-      best_cost = cost;
+    for (int pair = 0; pair < 2; ++pair) {
+      if (pair && m_tiles < 2) continue;
+      const long long n_tiles = c.Cout / bn;
+      const long long items = (pair ? (m_tiles + 1) / 2 : m_tiles) * n_tiles;
+      const long long units = pair ? num_sms() / 2 : num_sms();
+      const long long rounds = (items + units - 1) / units;
+      const int brows = pair ? bn / 2 : bn;
+      const double mma = 4.0 * passes * (bn / 2 < 48 ? 48 : bn / 2);
+      const double smem = 4.0 * passes * (4096 + brows * 32) + 16384 + passes * brows * 128.0;
+      const double t = mma > smem / (128.0 * 0.85) ? mma : smem / (128.0 * 0.85);
+      const double cost = static_cast<double>(rounds) * t;
+      if (best_cost < 0 || cost < best_cost * 0.999) {
+        best_cost = cost;
+        *block_n = bn;
+        *cluster = pair ? -2 : 1;
+      }
     }
   }
-  return best;
+  if (const char* e = getenv("PB200_R01_TILES")) {  // A/B: the round-1 choice (rounds x MMA cycles only, pairs from 2 waves on)
+    if (e[0] == '1' && !f16) {
+      double bc = -1;
+      for (int bn = 64; bn <= 256 && bn <= c.Cout; bn *= 2) {
+        if (c.Cout % bn) continue;
+        const long long tiles = m_tiles * (c.Cout / bn);
+        const double cost = static_cast<double>((tiles + num_sms() - 1) / num_sms()) * (bn / 2 < 48 ? 48 : bn / 2);
+        if (bc < 0 || cost <= bc) { bc = cost; *block_n = bn; }
+      }
+      *cluster = 0;
+    }
+  }
 }
 
 // (re)build the TMA descriptors / launch parameters when a pointer or the batch size changed
@@ -528,8 +563,11 @@ static int prepare(pb200_plan* pl, const void* frames, void* ws, int B) {
     const float* bias = reinterpret_cast<const float*>(pl->arena + c.b_off);
     const void* ds_in = op.ds_buf >= 0 ? buf_ptr(pl, frames, ws, op.ds_buf) : nullptr;
     const ConvSpec* d = c.ds_conv >= 0 ? &pl->convs[c.ds_conv] : nullptr;
+    int bn = 64, cluster = 0;
+    choose_tile(c, B, pl->f16, &bn, &cluster);
+    if (pl->split) cluster = 1;  // the split-bf16 mode runs on the single-CTA kernel
     int rc = build_umma_conv(L, in, B, c.Hin, c.Win, c.Cin, pl->arena + c.w_off, bias, res, out, c.Cout,
-                             c.R, c.stride, c.pad, op.relu, choose_block_n(c, B, pl->f16), 0, pl->split ? 1 : (pl->f16 ? 2 : 0),
+                             c.R, c.stride, c.pad, op.relu, bn, cluster, pl->split ? 1 : (pl->f16 ? 2 : 0),
                              d != nullptr ? ds_in : nullptr, d ? d->Hin : 0, d ? d->Win : 0, d ? d->Cin : 0);
     if (rc) {
       pl->cache_B = -1;
@@ -543,7 +581,7 @@ static int prepare(pb200_plan* pl, const void* frames, void* ws, int B) {
 }
 
 static int run_op(pb200_plan* pl, const Op& op, const void* frames, void* ws, float* out_norm,
-                  float* out_px, int B, cudaStream_t st) {
+                  float* out_px, int B, cudaStream_t st, int n0 = 0) {
   switch (op.kind) {
     case OP_CONV: {
       const ConvSpec& c = pl->convs[op.conv];
@@ -565,15 +603,16 @@ static int run_op(pb200_plan* pl, const Op& op, const void* frames, void* ws, fl
     }
     case OP_STEM_POOL: {
       const ConvSpec& c = pl->convs[op.conv];
-      return launch_stem_pool(frames, pl->arena + c.w_off, reinterpret_cast<const float*>(pl->arena + c.b_off),
-                              buf_ptr(pl, frames, ws, op.out_buf), B, pl->H, pl->W, st, pl->f16 ? 1 : 0);
+      return launch_stem_pool(buf_ptr(pl, frames, ws, BUF_FRAMES, n0), pl->arena + c.w_off,
+                              reinterpret_cast<const float*>(pl->arena + c.b_off),
+                              buf_ptr(pl, frames, ws, op.out_buf, n0), B, pl->H, pl->W, st, pl->f16 ? 1 : 0);
     }
     case OP_CONV_P8: {
       const ConvSpec& c = pl->convs[op.conv];
-      return launch_conv_p8(buf_ptr(pl, frames, ws, op.in_buf), pl->arena + c.w_off,
+      return launch_conv_p8(buf_ptr(pl, frames, ws, op.in_buf, n0), pl->arena + c.w_off,
                             reinterpret_cast<const float*>(pl->arena + c.b_off),
-                            op.res_buf >= 0 ? buf_ptr(pl, frames, ws, op.res_buf) : nullptr,
-                            buf_ptr(pl, frames, ws, op.out_buf), op.out_nhwc, op.relu, B, c.Hin, c.Win, st, pl->f16 ? 1 : 0);
+                            op.res_buf >= 0 ? buf_ptr(pl, frames, ws, op.res_buf, n0) : nullptr,
+                            buf_ptr(pl, frames, ws, op.out_buf, n0), op.out_nhwc, op.relu, B, c.Hin, c.Win, st, pl->f16 ? 1 : 0);
     }
     case OP_MAXPOOL: {
       const ConvSpec& c = pl->convs[0];
@@ -595,6 +634,10 @@ static int run_op(pb200_plan* pl, const Op& op, const void* frames, void* ws, fl
   }
 }
 
+static inline bool front_chunked(const pb200_plan* pl, int B) {
+  return pl->n_front > 0 && pl->l1_chunk > 0 && B > pl->l1_chunk;
+}
+
 static int check_forward_args(pb200_plan* plan, const void* frames, void* ws, float* out_norm, int B) {
   PB_CHECK(plan && frames && ws && out_norm, "forward: null argument");
   PB_CHECK(B >= 1 && B <= plan->max_batch, "forward: batch %d outside [1, max_batch=%d]", B,
@@ -613,8 +656,17 @@ extern "C" int pb200_forward(pb200_plan* plan, const void* frames, void* workspa
   if (int rc = check_forward_args(plan, frames, workspace, out_norm, B)) return rc;
   if (int rc = prepare(plan, frames, workspace, B)) return rc;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  for (const auto& op : plan->ops)
-    if (int rc = run_op(plan, op, frames, workspace, out_norm, out_px_or_null, B, st)) return rc;
+  size_t first = 0;
+  if (front_chunked(plan, B)) {
+    for (int n0 = 0; n0 < B; n0 += plan->l1_chunk) {
+      const int Bc = B - n0 < plan->l1_chunk ? B - n0 : plan->l1_chunk;
+      for (int i = 0; i < plan->n_front; ++i)
+        if (int rc = run_op(plan, plan->ops[i], frames, workspace, out_norm, out_px_or_null, Bc, st, n0)) return rc;
+    }
+    first = plan->n_front;
+  }
+  for (size_t i = first; i < plan->ops.size(); ++i)
+    if (int rc = run_op(plan, plan->ops[i], frames, workspace, out_norm, out_px_or_null, B, st)) return rc;
   return PB200_OK;
 }
 
@@ -660,7 +712,14 @@ extern "C" const char* pb200_plan_op_kernel(const pb200_plan* plan, int i) {
   return k.c_str();
 }
 extern "C" int pb200_plan_launches_per_forward(const pb200_plan* plan) {
-  return plan ? static_cast<int>(plan->ops.size()) : 0;
+  return plan ? static_cast<int>(plan->ops.size()) : 0;  // at batch sizes <= l1_chunk; see pb200_plan_launches_at
+}
+extern "C" int pb200_plan_launches_at(const pb200_plan* plan, int B) {
+  if (!plan) return 0;
+  const int n = static_cast<int>(plan->ops.size());
+  if (!front_chunked(plan, B)) return n;
+  const int chunks = (B + plan->l1_chunk - 1) / plan->l1_chunk;
+  return n - plan->n_front + chunks * plan->n_front;
 }
 
 extern "C" int pb200_plan_op_work(const pb200_plan* plan, int i, int B, double* flops, double* bytes) {
@@ -702,20 +761,37 @@ extern "C" int pb200_forward_profile(pb200_plan* plan, const void* frames, void*
   if (int rc = prepare(plan, frames, workspace, B)) return rc;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int n = static_cast<int>(plan->ops.size());
-  std::vector<cudaEvent_t> ev(n + 1);
+  // launch list in execution order: (op, first frame, frames); the chunked front ops appear once per L2 chunk and their
+  // times are summed per op
+  struct Launch { int op, n0, b; };
+  std::vector<Launch> seq;
+  int first = 0;
+  if (front_chunked(plan, B)) {
+    for (int n0 = 0; n0 < B; n0 += plan->l1_chunk)
+      for (int i = 0; i < plan->n_front; ++i) seq.push_back({i, n0, B - n0 < plan->l1_chunk ? B - n0 : plan->l1_chunk});
+    first = plan->n_front;
+  }
+  for (int i = first; i < n; ++i) seq.push_back({i, 0, B});
+  std::vector<cudaEvent_t> ev(seq.size() + 1);
   for (auto& e : ev) PB_CUDA(cudaEventCreate(&e));
   int rc = PB200_OK;
   PB_CUDA(cudaEventRecord(ev[0], st));
-  for (int i = 0; i < n && rc == PB200_OK; ++i) {
-    rc = run_op(plan, plan->ops[i], frames, workspace, out_norm, out_px_or_null, B, st);
-    if (rc == PB200_OK && cudaEventRecord(ev[i + 1], st) != cudaSuccess) rc = PB200_ERR_CUDA;
+  for (size_t j = 0; j < seq.size() && rc == PB200_OK; ++j) {
+    rc = run_op(plan, plan->ops[seq[j].op], frames, workspace, out_norm, out_px_or_null, seq[j].b, st, seq[j].n0);
+    if (rc == PB200_OK && cudaEventRecord(ev[j + 1], st) != cudaSuccess) rc = PB200_ERR_CUDA;
   }
   if (rc == PB200_OK) {
     cudaError_t e = cudaStreamSynchronize(st);
     if (e != cudaSuccess) rc = cuda_fail(e, "cudaStreamSynchronize", __FILE__, __LINE__);
   }
-  if (rc == PB200_OK)
-    for (int i = 0; i < n; ++i) cudaEventElapsedTime(&ms[i], ev[i], ev[i + 1]);
+  if (rc == PB200_OK) {
+    for (int i = 0; i < n; ++i) ms[i] = 0.f;
+    for (size_t j = 0; j < seq.size(); ++j) {
+      float t = 0.f;
+      cudaEventElapsedTime(&t, ev[j], ev[j + 1]);
+      ms[seq[j].op] += t;
+    }
+  }
   for (auto& e : ev) cudaEventDestroy(e);
   return rc;
 }

@@ -311,11 +311,15 @@ class KeypointCNN(nn.Module):
         plan.weights_key = wk
         return True
 
-    def forward_ingested(self, frames: torch.Tensor, B: int, plan: "_Plan | None" = None):
-        """Backbone + head + decode on an ingested frames buffer -> (norm (B,2K), pixels (B,K,2))."""
+    def forward_ingested(self, frames: torch.Tensor, B: int, plan: "_Plan | None" = None, out_norm: torch.Tensor | None = None,
+                         out_px: torch.Tensor | None = None):
+        """Backbone + head + decode on an ingested frames buffer -> (norm (B,2K), pixels (B,K,2)); `out_norm` / `out_px`
+        may be preallocated float32 cuda tensors (graph-captured callers)."""
         plan = plan if plan is not None else self._plan(frames.device, B)
-        out_norm = torch.empty((B, 2 * self.n_keypoints), dtype=torch.float32, device=frames.device)
-        out_px = torch.empty((B, self.n_keypoints, 2), dtype=torch.float32, device=frames.device)
+        if out_norm is None:
+            out_norm = torch.empty((B, 2 * self.n_keypoints), dtype=torch.float32, device=frames.device)
+        if out_px is None:
+            out_px = torch.empty((B, self.n_keypoints, 2), dtype=torch.float32, device=frames.device)
         with torch.cuda.device(frames.device):
             _lib.check(
                 plan.lib.pb200_forward(
