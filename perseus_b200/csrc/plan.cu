@@ -74,10 +74,12 @@ struct pb200_plan {
   std::vector<std::string> op_names;
   std::vector<std::string> op_kernels;  // kernel each op launches (known after the first forward at a batch size)
   // L2 chunking of the front of the network (fused stem + the four layer1 convs, P8 layout): these five kernels move
-  // 10 x 140 MB of activations per 256 frames and are co-bound by HBM; run on sub-batches of l1_chunk frames their
-  // three P8 buffers (22 MB each at 40 frames) stay L2-resident and only the frames and the NHWC hand-over to layer2
-  // touch HBM.  40 frames = 1320 layer1 tiles = 8.92 waves of 148 SMs.  0 = off (PB200_L1_CHUNK overrides).
-  int l1_chunk = 40;
+  // 10 x 140 MB of activations per 256 frames; run on sub-batches of l1_chunk frames their three P8 buffers stay
+  // L2-resident and only the frames and the NHWC hand-over to layer2 touch HBM.  MEASURED (r02, profiles/README.md): a
+  // loss -- every extra launch of these persistent kernels costs ~9 us of pipeline fill / drain / tail imbalance, more
+  // than the HBM time it saves (stem + layer1 0.43 ms unchunked, 0.55 / 0.58 / 0.72 ms at 86 / 64 / 40 frames per
+  // chunk).  OFF by default; PB200_L1_CHUNK=<frames> enables it for A/B runs.
+  int l1_chunk = 0;
   int n_front = 0;  // leading ops that are chunked (OP_STEM_POOL + OP_CONV_P8 x 4)
 };
 
@@ -550,7 +552,9 @@ static void choose_tile(const ConvSpec& c, int B, bool f16, int* block_n, int* c
 // (re)build the TMA descriptors / launch parameters when a pointer or the batch size changed
 static int prepare(pb200_plan* pl, const void* frames, void* ws, int B) {
   if (!pl->bf16 && !pl->split) return PB200_OK;
-  if (pl->cache_frames == frames && pl->cache_ws == ws && pl->cache_B == B) return PB200_OK;
+  // the tensor maps cover workspace buffers only (the stem reads `frames` through a plain pointer argument), so a caller
+  // may alternate frames buffers (ingest of batch i+1 under the forward of batch i) without re-encoding anything
+  if (pl->cache_ws == ws && pl->cache_B == B) return PB200_OK;
   pl->umma.assign(pl->convs.size(), UmmaConvLaunch());
   for (const auto& op : pl->ops) {
     if (op.kind != OP_CONV) continue;

@@ -6,9 +6,11 @@ is the same loop as a software pipeline, so the copy of batch i+1 and the read-b
 of batch i:
 
   copy stream(s)  : one plain cudaMemcpyAsync per submitted batch (per copy stream) into one of `slots` device buffers
-  compute stream  : ONE CUDA-graph replay per batch (fused ingest -> backbone -> head + pixel decode; ~20 kernels whose
-                    launches would otherwise cost ~0.1 ms of host time per step) + the 16 KB keypoint copy into a ring
-                    of pinned result buffers
+  ingest stream   : the fused ingest kernel of batch i+1 (HBM-bound) runs under the tensor-bound convolutions of batch i,
+                    mostly in the gaps between their launches
+  compute stream  : ONE CUDA-graph replay per batch (backbone -> head + pixel decode; ~19 kernels whose launches would
+                    otherwise cost ~0.1 ms of host time per step) + the 16 KB keypoint copy into a ring of pinned
+                    result buffers
   host            : `submit()` never blocks on the GPU; `result(ticket)` waits for that batch's keypoints only.
 
 The graphs bake in the pointers of a PRIVATE plan (KeypointCNN.private_plan), so later forward() calls on the module
@@ -39,7 +41,8 @@ class BatchPipeline:
         self.use_depth = model.num_channels == 4
         self.slots, self.results = slots, results
         dev = self.device
-        self.compute = torch.cuda.Stream(device=dev)
+        self.compute = torch.cuda.Stream(device=dev, priority=-1)
+        self.pre = torch.cuda.Stream(device=dev)  # ingest of the next batch
         self.copies = [torch.cuda.Stream(device=dev) for _ in range(max(1, copy_streams))]
         with torch.cuda.stream(self.compute):
             self.plan = model.private_plan(dev, batch)
@@ -47,21 +50,25 @@ class BatchPipeline:
         self.dev_rgb = [torch.empty(shape, dtype=torch.uint8, device=dev) for _ in range(slots)]
         self.dev_depth = ([torch.empty(shape[:3], dtype=torch.float32, device=dev) for _ in range(slots)]
                           if self.use_depth else [None] * slots)
-        self.frames = torch.empty(self.plan.frames_bytes(batch), dtype=torch.uint8, device=dev)
+        self.frames = [torch.empty(self.plan.frames_bytes(batch), dtype=torch.uint8, device=dev) for _ in range(slots)]
         self.px_dev = [torch.empty((batch, model.n_keypoints, 2), dtype=torch.float32, device=dev) for _ in range(slots)]
         self.norm_dev = [torch.empty((batch, 2 * model.n_keypoints), dtype=torch.float32, device=dev) for _ in range(slots)]
         self.host_px = [torch.empty((batch, model.n_keypoints, 2), dtype=torch.float32).pin_memory() for _ in range(results)]
         self.ev_copied = [[torch.cuda.Event() for _ in self.copies] for _ in range(slots)]
-        self.ev_free = [torch.cuda.Event() for _ in range(slots)]
+        self.ev_free = [torch.cuda.Event() for _ in range(slots)]      # dev_rgb[s] consumed (ingest done)
+        self.ev_ingested = [torch.cuda.Event() for _ in range(slots)]  # frames[s] ready
+        self.ev_fwd = [torch.cuda.Event() for _ in range(slots)]       # frames[s] consumed (forward done)
         self.ev_done = [torch.cuda.Event() for _ in range(results)]
         self.graphs = [None] * slots
         self.ticket = 0
         self._capture()
 
-    def _run(self, s: int):
+    def _ingest(self, s: int):
         self.model.ingest(self.dev_rgb[s], self.dev_depth[s], bgr=self.bgr, depth_divisor=self.depth_divisor,
-                          out=self.frames, plan=self.plan)
-        return self.model.forward_ingested(self.frames, self.B, plan=self.plan, out_norm=self.norm_dev[s],
+                          out=self.frames[s], plan=self.plan)
+
+    def _run(self, s: int):
+        return self.model.forward_ingested(self.frames[s], self.B, plan=self.plan, out_norm=self.norm_dev[s],
                                            out_px=self.px_dev[s])[1]
 
     def _capture(self):
@@ -70,15 +77,18 @@ class BatchPipeline:
                 self.dev_rgb[s].zero_()
                 if self.use_depth:
                     self.dev_depth[s].fill_(0.3)
-            for _ in range(2):  # warm-up: builds the plan's TMA descriptors for these pointers before capture
-                self._run(0)
+            for s in range(self.slots):
+                self._ingest(s)
+            self._run(0)  # warm-up: one-off attribute / occupancy queries happen here, not under capture
         self.compute.synchronize()
         for s in range(self.slots):
+            # the plan caches its TMA descriptors per (frames, workspace, batch): each slot's frames buffer differs only in
+            # the stem's input pointer (a kernel argument), so re-preparing per slot is cheap and happens at capture time
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g, stream=self.compute):
                 self._run(s)
             self.graphs[s] = g
-        for e in self.ev_free:
+        for e in self.ev_free + self.ev_fwd:
             e.record(self.compute)
         self.compute.synchronize()
 
@@ -102,12 +112,18 @@ class BatchPipeline:
                     if self.use_depth:
                         self.dev_depth[s][lo:hi].copy_(host_depth[lo:hi], non_blocking=True)
                 self.ev_copied[s][c].record(cs)
-        with torch.cuda.stream(self.compute):
+        with torch.cuda.stream(self.pre):
             for e in self.ev_copied[s]:
-                self.compute.wait_event(e)
+                self.pre.wait_event(e)
+            self.pre.wait_event(self.ev_fwd[s])  # the previous batch in this slot's frames buffer has been consumed
+            self._ingest(s)
+            self.ev_free[s].record(self.pre)
+            self.ev_ingested[s].record(self.pre)
+        with torch.cuda.stream(self.compute):
+            self.compute.wait_event(self.ev_ingested[s])
             self.model.sync_plan_weights(self.plan)
             self.graphs[s].replay()
-            self.ev_free[s].record(self.compute)
+            self.ev_fwd[s].record(self.compute)
             self.host_px[r].copy_(self.px_dev[s], non_blocking=True)
             self.ev_done[r].record(self.compute)
         self.ticket = t + 1
@@ -138,5 +154,6 @@ class BatchPipeline:
 
     def drain(self) -> None:
         self.compute.synchronize()
+        self.pre.synchronize()
         for cs in self.copies:
             cs.synchronize()
