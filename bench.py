@@ -242,6 +242,42 @@ def measure_factors(dev, peaks, N=10_000, big=1_000_000):
         res[f"poses_{n}"] = {"ms": ms, "poses_per_s": n / (ms * 1e-3), "algorithmic_GBps": nbytes / (ms * 1e-3) / 1e9,
                              "hbm_frac": nbytes / (ms * 1e-3) / 1e9 / peaks["hbm_gbs"]}
     res["what"] = "per pose: 8 projection (resid + 2x6 J) + 1 dynamics (resid + 4 J blocks) + 1 const-vel factor, fp64"
+    # the same work as ONE launch (pb200_factors_chain: W windows x T states, what the smoother evaluates per
+    # linearisation), outputs preallocated; eager call and CUDA-graph replay
+    from perseus_b200.smoother.linearize import chain_factors
+
+    for Wn, Tn in ((1000, 10), (100_000, 10)):
+        n = Wn * Tn
+        g = torch.Generator().manual_seed(1)
+        qn = torch.nn.functional.normalize(torch.randn(n, 4, generator=g, dtype=torch.float64), dim=-1)
+        w, x, y, z = qn.unbind(-1)
+        R = torch.stack([1 - 2 * (y * y + z * z), 2 * (x * y - z * w), 2 * (x * z + y * w),
+                         2 * (x * y + z * w), 1 - 2 * (x * x + z * z), 2 * (y * z - x * w),
+                         2 * (x * z - y * w), 2 * (y * z + x * w), 1 - 2 * (x * x + y * y)], -1)
+        t = torch.randn(n, 3, generator=g, dtype=torch.float64) * 0.05
+        t[..., 2] += 0.45
+        poses = torch.cat([R, t], -1).reshape(Wn, Tn, 12).to(dev)
+        wv = torch.randn(Wn, Tn, 3, generator=g, dtype=torch.float64).to(dev)
+        vv = torch.randn(Wn, Tn, 3, generator=g, dtype=torch.float64).to(dev)
+        meas = (torch.rand(Wn, Tn, 8, 2, generator=g, dtype=torch.float64) * 255).to(dev)
+        out = chain_factors(poses, wv, vv, meas, corners, K5, 0.1)
+        call = lambda i: chain_factors(poses, wv, vv, meas, corners, K5, 0.1, out=out)  # noqa: E731
+        ms_call = _event_time(call, 20 if n <= 10_000 else 5)
+        s_ = torch.cuda.Stream(device=dev)
+        s_.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s_):
+            call(0)
+        torch.cuda.current_stream().wait_stream(s_)
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            call(0)
+        ms_graph = _event_time(lambda i: graph.replay(), 50 if n <= 10_000 else 5)
+        nbytes = n * (1120 + 72) + Wn * (Tn - 1) * (1152 + 144)
+        res[f"chain_fused_{n}"] = {"windows": Wn, "states_per_window": Tn, "launches": 1, "ms_eager_call": ms_call,
+                                   "ms_graph_replay": ms_graph, "poses_per_s": n / (ms_graph * 1e-3),
+                                   "algorithmic_GBps": nbytes / (ms_graph * 1e-3) / 1e9,
+                                   "hbm_frac": nbytes / (ms_graph * 1e-3) / 1e9 / peaks["hbm_gbs"]}
+        del graph
     # CPU baselines of the same work: (i) one factor per call, the way GTSAM drives the reference's
     # Python callbacks (factors.py:54-61), on a bounded sample; (ii) the float64 restatement vectorised over all poses
     from oracle import factors_oracle as fo

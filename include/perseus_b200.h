@@ -210,6 +210,18 @@ int pb200_factors_dynamics(const double* pose1, const double* ang_vel1, const do
 int pb200_factors_constvel(const double* vel1, const double* vel2, double* resid, double* H0,
                            double* H1, int64_t N, pb200_stream stream);
 
+/* One launch for a whole chain problem (what the smoother evaluates per linearisation): W windows of T states,
+ * poses [W][T][12], ang_vel / vel [W][T][3], meas [W][T][P][2].  Evaluates every KeypointProjectionFactor
+ * (factors.py:216-275), every PoseDynamicsFactor between consecutive states of a window (:54-142, pose1 / pose2 read from
+ * the one pose array) and both ConstantVelocityFactor residuals (:160-171; their Jacobians are the constants -I, I).
+ * Outputs have the layouts of the three calls above: proj_resid [W*T][P][2], proj_jac [W*T][P] 2x6 column-major,
+ * cheirality [W*T][P]; dyn_resid [W*(T-1)][6], H0..H3 column-major, cv_*_resid [W*(T-1)][3] (unused when T == 1). */
+int pb200_factors_chain(const double* poses, const double* ang_vel, const double* vel, const double* meas,
+                        const double* pts_body, const double* K5, const double* cam_pose12_or_null, double dt,
+                        int world_frame, double* proj_resid, double* proj_jac, uint8_t* cheirality,
+                        double* dyn_resid, double* H0, double* H1, double* H2, double* H3, double* cv_angvel_resid,
+                        double* cv_vel_resid, int W, int T, int P, pb200_stream stream);
+
 /* ---- training-step operators (train.py:259-304) -----------------------------------------------
  * Hand-written kernels for the data-parallel training step: tcgen05 forward / data-gradient / weight-gradient
  * convolutions on NHWC bf16, batch-statistics BatchNorm forward + backward, max-pool backward, the regression

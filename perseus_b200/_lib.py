@@ -143,6 +143,10 @@ SIGNATURES = {
          c_int64, c_void_p],
     ),
     "pb200_factors_constvel": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p]),
+    "pb200_factors_chain": (
+        c_int,
+        [c_void_p] * 7 + [c_double, c_int] + [c_void_p] * 10 + [c_int, c_int, c_int, c_void_p],
+    ),
 }
 
 _lib = None

@@ -552,6 +552,20 @@ int build_umma_conv(UmmaConvLaunch* L, const void* in, int B, int Hin, int Win, 
   p.cl = cl;
   p.num_super = (m_tiles + cl - 1) / cl * p.num_n_tiles;
   int max_clusters;
+  L->resb = 0;
+  p.a_stages = 0;
+  if (L->pair && split == 0 && p.num_n_tiles == 1 && stats == nullptr && !getenv("PB200_NO_RESB")) {
+    // resident weights (conv_umma2.cu RESB): this CTA's half of all k-blocks + at least 3 activation stages must fit
+    const int resb_bytes = p.num_kblocks * (block_n / 2) * 128;
+    const int budget = 216 * 1024;  // + 1 KB alignment slack + ~7.4 KB static shared memory < 227 KB
+    int stages = (budget - resb_bytes) / (128 * 128);
+    if (stages > 8) stages = 8;
+    if (stages >= 3) {
+      L->resb = 1;
+      p.a_stages = stages;
+      L->smem = stages * 128 * 128 + resb_bytes + 1024;
+    }
+  }
   if (L->pair) {
     if (int rc = umma_pair_init()) return rc;
     max_clusters = umma_pair_max_pairs(block_n, split == 2);
@@ -603,6 +617,7 @@ int build_umma_dgrad_s2(UmmaConvLaunch* L, const void* dz, int B, int Ho, int Wo
                                block_n))
     return rc;
   UmmaConvParams& p = L->p;
+  L->resb = 0;  // the tap table below re-orders the k columns: the resident-weights walk (columns kb * 64) does not apply
   // forward: z[i] reads x[2i + r - pad].  For x row u = 2a + ph the forward taps are r = ph + pad (mod 2):
   // R = 3: ph = 0 -> r = 1 (i = a); ph = 1 -> r = 0 (i = a + 1), r = 2 (i = a).  R = 1: ph = 0 -> r = 0 (i = a); ph = 1 -> none
   int rr[2], ri[2], nr = 0, cc[2], ci[2], nc = 0;

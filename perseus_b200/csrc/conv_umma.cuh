@@ -35,6 +35,7 @@ struct UmmaConvParams {
   // [B][2Ho][2Wo][Cout] tensor (and reads the residual there): one output parity of a stride-2 data gradient
   int up2, up_ph, up_pw, up_lh, up_lw;  // up_lh / up_lw = log2(Ho), log2(Wo)
   int ds_cblocks;  // fused downsample: extra 64-channel k-blocks read through maps.ds after the R*S taps (0 = none)
+  int a_stages;    // resident-weights pair kernel (UmmaConvLaunch::resb): activation ring stages (2..8)
   int relu;
   const float* bias;            // [Cout] (folded BN shift)
   const void* residual;         // bf16 [M_total][Cout] or null
@@ -50,6 +51,8 @@ struct UmmaConvLaunch {
   int grid;
   int split;    // 1: split-bf16 ("bf16x3") operands; 2: "fp16x2" (fp16 activations, weights [hi K | lo K] fp16)
   int pair;     // 1: CTA-pair kernel (conv_umma2.cu, tcgen05 cta_group::2), p.cl == 2
+  int resb;     // 1: pair kernel with the whole weight matrix resident in shared memory (single N tile; layer2)
+  int smem;     // dynamic shared memory of the resb launch
   double flops;  // algorithmic 2*MAC (unpadded)
 };
 

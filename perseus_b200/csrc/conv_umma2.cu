@@ -33,24 +33,31 @@ struct PairCfg {
   static constexpr int kTmemCols = 2 * BLOCK_N;
 };
 
-template <int BLOCK_N, bool X2>
+// RESB = resident weights: when the conv has ONE N tile (BLOCK_N = Cout: layer2) and this CTA's half of the whole packed
+// weight matrix fits next to an activation ring (18-19 k-blocks x 8 KB at Cout = 128), the producers load it ONCE per
+// CTA and afterwards only activation tiles move: per 64-deep k-block 16 KB land in shared memory instead of 24 KB, on
+// layers that are bound by shared-memory traffic (MMA operand reads + TMA fills), not by MMA issue.
+template <int BLOCK_N, bool X2, bool RESB>
 __global__ void __launch_bounds__(kPairThreads, 1)
 conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams p) {
   using Cfg = PairCfg<BLOCK_N, X2>;
-  constexpr int kStages = Cfg::kStages;
+  constexpr int kStages = RESB ? 8 : Cfg::kStages;  // RESB: p.a_stages (<= 8) activation stages, set by the host
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t full_bar[kStages];   // used in the leader CTA only
   __shared__ __align__(8) uint64_t empty_bar[kStages];  // per CTA: its stage buffers are free again
   __shared__ __align__(8) uint64_t tmem_full_bar[2];    // per CTA: accumulator stage complete
   __shared__ __align__(8) uint64_t tmem_empty_bar[2];   // leader only: both CTAs' epilogues drained the stage
+  __shared__ __align__(8) uint64_t resb_bar;            // leader only: both CTAs' resident weight halves have landed
   __shared__ uint32_t tmem_base_slot;
   __shared__ float s_bias[512];
   __shared__ float s_stat[2 * 512];  // training forward: per-CTA partial sum / sum of squares per output channel
 
   const uint32_t raw_addr = smem_u32(smem_raw);
   uint8_t* tiles = smem_raw + (((raw_addr + 1023u) & ~1023u) - raw_addr);
+  const int nst = RESB ? p.a_stages : kStages;  // stages of the ring
+  const int stage_b = RESB ? 0 : Cfg::kBBytes;  // bytes of weights per ring stage
   uint8_t* smem_a = tiles;
-  uint8_t* smem_b = tiles + kStages * Cfg::kABytes;
+  uint8_t* smem_b = tiles + nst * Cfg::kABytes;  // RESB: the resident weights, k-block kb at + kb * kBHalf
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -68,6 +75,7 @@ conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParam
     mbar_init(&tmem_full_bar[1], 1);
     mbar_init(&tmem_empty_bar[0], 16);  // 8 epilogue warps x 2 CTAs
     mbar_init(&tmem_empty_bar[1], 16);
+    mbar_init(&resb_bar, 2);
     fence_barrier_init();
   }
   if (warp == 1) {
@@ -97,6 +105,17 @@ conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParam
     int stage = 0;
     uint32_t phase = 0;
     const uint32_t lfull0 = mapa_u32(&full_bar[0], 0);
+    if (RESB && pi == 0 && pair_id < p.num_super) {
+      // this CTA's half (rows crank * BLOCK_N/2 ..) of EVERY k-block of the packed weights, once; k-blocks are stored in
+      // the producers' walking order (taps x channel blocks, then the fused projection's blocks): columns kb * 64
+      if (elect_one()) {
+        const uint32_t lres = mapa_u32(&resb_bar, 0);
+        mbar_expect_tx_cluster(lres, static_cast<uint32_t>(p.num_kblocks) * Cfg::kBHalf);
+        for (int kb = 0; kb < p.num_kblocks; ++kb)
+          tma_load_2d_2sm(smem_b + kb * Cfg::kBHalf, &maps.b, lres, kb * 64, crank * (BLOCK_N / 2));
+      }
+      __syncwarp();
+    }
     for (int st = pair_id; st < p.num_super; st += num_pairs) {
       const int m_super = st / p.num_n_tiles;
       const int n_tile = st - m_super * p.num_n_tiles;
@@ -122,14 +141,16 @@ conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParam
           mbar_wait(&empty_bar[stage], phase ^ 1u);
           if (elect_one()) {
             const uint32_t lfull = lfull0 + stage * 8;  // the leader's full barrier of this stage
-            mbar_expect_tx_cluster(lfull, Cfg::kStageBytes);
+            mbar_expect_tx_cluster(lfull, Cfg::kABytes + stage_b);
             tma_load_4d_2sm(smem_a + stage * Cfg::kABytes, amap, lfull, cb * 64, dw, hrow, n0);
-            tma_load_2d_2sm(smem_b + stage * Cfg::kBBytes, &maps.b, lfull, kcol, n_row);
-            if (X2) tma_load_2d_2sm(smem_b + stage * Cfg::kBBytes + Cfg::kBHalf, &maps.b, lfull, kcol + p.ktot, n_row);
+            if (!RESB) {
+              tma_load_2d_2sm(smem_b + stage * Cfg::kBBytes, &maps.b, lfull, kcol, n_row);
+              if (X2) tma_load_2d_2sm(smem_b + stage * Cfg::kBBytes + Cfg::kBHalf, &maps.b, lfull, kcol + p.ktot, n_row);
+            }
           }
           __syncwarp();
           }
-          if (++stage == kStages) {
+          if (++stage == nst) {
             stage = 0;
             phase ^= 1u;
           }
@@ -141,14 +162,16 @@ conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParam
           mbar_wait(&empty_bar[stage], phase ^ 1u);
           if (elect_one()) {
             const uint32_t lfull = lfull0 + stage * 8;
-            mbar_expect_tx_cluster(lfull, Cfg::kStageBytes);
+            mbar_expect_tx_cluster(lfull, Cfg::kABytes + stage_b);
             tma_load_4d_2sm(smem_a + stage * Cfg::kABytes, &maps.ds, lfull, cb * 64, 0, ho0, n0);
-            tma_load_2d_2sm(smem_b + stage * Cfg::kBBytes, &maps.b, lfull, kcol, n_row);
-            if (X2) tma_load_2d_2sm(smem_b + stage * Cfg::kBBytes + Cfg::kBHalf, &maps.b, lfull, kcol + p.ktot, n_row);
+            if (!RESB) {
+              tma_load_2d_2sm(smem_b + stage * Cfg::kBBytes, &maps.b, lfull, kcol, n_row);
+              if (X2) tma_load_2d_2sm(smem_b + stage * Cfg::kBBytes + Cfg::kBHalf, &maps.b, lfull, kcol + p.ktot, n_row);
+            }
           }
           __syncwarp();
         }
-        if (++stage == kStages) {
+        if (++stage == nst) {
           stage = 0;
           phase ^= 1u;
         }
@@ -163,6 +186,7 @@ conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParam
       int stage = 0;
       uint32_t phase = 0;
       int it = 0;
+      if (RESB && pair_id < p.num_super) mbar_wait(&resb_bar, 0);
       for (int st = pair_id; st < p.num_super; st += num_pairs, ++it) {
         const int acc = it & 1;
         mbar_wait(&tmem_empty_bar[acc], ((it >> 1) & 1u) ^ 1u);
@@ -173,7 +197,7 @@ conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParam
           tc_fence_after();
           if (elect_one()) {
             const uint32_t a_lo = desc_lo(smem_u32(smem_a + stage * Cfg::kABytes), 16);
-            const uint32_t b_lo = desc_lo(smem_u32(smem_b + stage * Cfg::kBBytes), 16);
+            const uint32_t b_lo = desc_lo(smem_u32(smem_b + (RESB ? kb * Cfg::kBHalf : stage * Cfg::kBBytes)), 16);
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
               umma2_bf16_split(d_tmem, a_lo + 2 * k, d_hi, b_lo + 2 * k, d_hi, idesc, (kb | k) != 0 ? 1u : 0u);
@@ -183,7 +207,7 @@ conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParam
             if (kb == p.num_kblocks - 1) umma2_commit_mcast(&tmem_full_bar[acc], 3);
           }
           __syncwarp();
-          if (++stage == kStages) {
+          if (++stage == nst) {
             stage = 0;
             phase ^= 1u;
           }
@@ -317,15 +341,20 @@ static int pair_cfg(cudaLaunchConfig_t* cfg, cudaLaunchAttribute* attr, int grid
   return PB200_OK;
 }
 
+constexpr int kResbMaxSmem = 217 * 1024;  // resident-weights launches (build_umma_conv sizes them to <= 216 KB + 1 KB)
+
 template <int BLOCK_N, bool X2>
 static int pair_init_one(int* max_pairs) {
-  PB_CUDA(cudaFuncSetAttribute(conv_umma2_kernel<BLOCK_N, X2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  PB_CUDA(cudaFuncSetAttribute(conv_umma2_kernel<BLOCK_N, X2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                PairCfg<BLOCK_N, X2>::kSmemBytes));
+  if (!X2)
+    PB_CUDA(cudaFuncSetAttribute(conv_umma2_kernel<BLOCK_N, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 kResbMaxSmem));
   cudaLaunchConfig_t cfg;
   cudaLaunchAttribute attr[1];
   pair_cfg<BLOCK_N, X2>(&cfg, attr, num_sms() / 2 * 2, nullptr);
   int n = 0;
-  PB_CUDA(cudaOccupancyMaxActiveClusters(&n, conv_umma2_kernel<BLOCK_N, X2>, &cfg));
+  PB_CUDA(cudaOccupancyMaxActiveClusters(&n, conv_umma2_kernel<BLOCK_N, X2, false>, &cfg));
   *max_pairs = n;
   return PB200_OK;
 }
@@ -356,7 +385,12 @@ static int launch_pair_one(const UmmaConvLaunch& L, cudaStream_t st) {
   cudaLaunchConfig_t cfg;
   cudaLaunchAttribute attr[2];
   pair_cfg<BLOCK_N, X2>(&cfg, attr, L.grid, st, true);
-  PB_CUDA(cudaLaunchKernelEx(&cfg, conv_umma2_kernel<BLOCK_N, X2>, L.maps, L.p));
+  if (!X2 && L.resb) {
+    cfg.dynamicSmemBytes = L.smem;
+    PB_CUDA(cudaLaunchKernelEx(&cfg, conv_umma2_kernel<BLOCK_N, false, true>, L.maps, L.p));
+  } else {
+    PB_CUDA(cudaLaunchKernelEx(&cfg, conv_umma2_kernel<BLOCK_N, X2, false>, L.maps, L.p));
+  }
   return PB200_OK;
 }
 

@@ -83,13 +83,12 @@ dynamics_kernel(const double* __restrict__ pose1, const double* __restrict__ ang
 // consecutive poses (P divides the run when P | 128; otherwise poses straddle blocks, which is
 // fine because every thread indexes its own pose).
 template <bool JAC>
-__global__ void __launch_bounds__(kFacThreads)
-projection_kernel(const double* __restrict__ poses, const double* __restrict__ meas,
-                  const double* __restrict__ pts_body, const double* __restrict__ K5,
-                  const double* __restrict__ cam12, double* __restrict__ resid,
-                  double* __restrict__ jac, uint8_t* __restrict__ cheir, long long NP, int P) {
-  extern __shared__ double sm[];
-  const long long base = static_cast<long long>(blockIdx.x) * kFacThreads;
+__device__ __forceinline__ void projection_block(double* sm, long long block, const double* __restrict__ poses,
+                                                 const double* __restrict__ meas, const double* __restrict__ pts_body,
+                                                 const double* __restrict__ K5, const double* __restrict__ cam12,
+                                                 double* __restrict__ resid, double* __restrict__ jac,
+                                                 uint8_t* __restrict__ cheir, long long NP, int P) {
+  const long long base = block * kFacThreads;
   const int cnt = static_cast<int>(min(static_cast<long long>(kFacThreads), NP - base));
   const long long pose_lo = base / P;
   const long long pose_hi = (base + cnt - 1) / P;
@@ -134,6 +133,82 @@ projection_kernel(const double* __restrict__ poses, const double* __restrict__ m
   if (JAC) copy_out(jac + base * 12, s_jac, cnt * 12);
 }
 
+template <bool JAC>
+__global__ void __launch_bounds__(kFacThreads)
+projection_kernel(const double* __restrict__ poses, const double* __restrict__ meas,
+                  const double* __restrict__ pts_body, const double* __restrict__ K5,
+                  const double* __restrict__ cam12, double* __restrict__ resid,
+                  double* __restrict__ jac, uint8_t* __restrict__ cheir, long long NP, int P) {
+  extern __shared__ double sm[];
+  projection_block<JAC>(sm, blockIdx.x, poses, meas, pts_body, K5, cam12, resid, jac, cheir, NP, P);
+}
+
+// ---- one launch for a whole chain problem ----------------------------------------------------------------------
+// W windows of T states (poses [W][T][12], ang_vel / vel [W][T][3], meas [W][T][P][2]): every projection factor, every
+// dynamics factor between consecutive states of a window and both constant-velocity residuals, in ONE grid: blocks
+// [0, nb_proj) are projection blocks, the rest dynamics blocks (which also emit the two velocity differences of their
+// pairs).  At the reference's problem size (10 k poses) three separate launches were launch-latency-bound (0.107 ms for
+// ~15 us of work each); pose1 / pose2 of a pair are read from the one pose array (no gathered copies).
+struct ChainArgs {
+  const double *poses, *ang_vel, *vel, *meas, *pts_body, *K5, *cam12;
+  double dt;
+  int world_frame;
+  double *proj_resid, *proj_jac;
+  uint8_t* cheir;
+  double *dyn_resid, *H0, *H1, *H2, *H3, *cvw_resid, *cvv_resid;
+  long long NP, npairs;
+  int T, P, nb_proj;
+};
+
+__global__ void __launch_bounds__(kFacThreads) chain_factors_kernel(const ChainArgs a) {
+  extern __shared__ double sm[];
+  if (static_cast<int>(blockIdx.x) < a.nb_proj) {
+    projection_block<true>(sm, blockIdx.x, a.poses, a.meas, a.pts_body, a.K5, a.cam12, a.proj_resid, a.proj_jac, a.cheir,
+                           a.NP, a.P);
+    return;
+  }
+  const long long base = static_cast<long long>(blockIdx.x - a.nb_proj) * kFacThreads;
+  const int cnt = static_cast<int>(min(static_cast<long long>(kFacThreads), a.npairs - base));
+  const int Tm1 = a.T - 1;
+  auto state_of = [&](long long pair) { return pair / Tm1 * a.T + pair % Tm1; };  // index of the pair's FIRST state
+  const long long lo = state_of(base), hi = state_of(base + cnt - 1) + 1;        // states [lo, hi] are touched
+  const int nst = static_cast<int>(hi - lo + 1);                                 // <= 2 * kFacThreads
+  double* s_pose = sm;                   // 12 * nst
+  double* s_w = s_pose + 12 * nst;       // 3 * nst
+  double* s_v = s_w + 3 * nst;           // 3 * nst   (18 * nst <= 36 * kFacThreads doubles: the staging buffer)
+  copy_in(s_pose, a.poses + lo * 12, nst * 12);
+  copy_in(s_w, a.ang_vel + lo * 3, nst * 3);
+  copy_in(s_v, a.vel + lo * 3, nst * 3);
+  __syncthreads();
+  const int t = threadIdx.x;
+  const bool live = t < cnt;
+  double r[6], h0[36], h1[18], h2[18], h3[36], cv[6];
+  if (live) {
+    const int i = static_cast<int>(state_of(base + t) - lo);
+    const fm::Pose x1 = fm::load_pose12(s_pose + i * 12);
+    const fm::Pose x2 = fm::load_pose12(s_pose + (i + 1) * 12);
+    const fm::V3 w = fm::v3(s_w[i * 3], s_w[i * 3 + 1], s_w[i * 3 + 2]);
+    const fm::V3 v = fm::v3(s_v[i * 3], s_v[i * 3 + 1], s_v[i * 3 + 2]);
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {  // ConstantVelocityFactor residuals (factors.py:169) of this pair
+      cv[k] = s_w[(i + 1) * 3 + k] - s_w[i * 3 + k];
+      cv[3 + k] = s_v[(i + 1) * 3 + k] - s_v[i * 3 + k];
+    }
+    fm::dynamics_factor(x1, w, v, x2, a.dt, a.world_frame, 1, r, h0, h1, h2, h3);
+  }
+  stage_out<6>(sm, a.dyn_resid + base * 6, r, live, cnt);
+  {
+    double c3[3] = {cv[0], cv[1], cv[2]};
+    stage_out<3>(sm, a.cvw_resid + base * 3, c3, live, cnt);
+    double d3[3] = {cv[3], cv[4], cv[5]};
+    stage_out<3>(sm, a.cvv_resid + base * 3, d3, live, cnt);
+  }
+  stage_out<36>(sm, a.H0 + base * 36, h0, live, cnt);
+  stage_out<18>(sm, a.H1 + base * 18, h1, live, cnt);
+  stage_out<18>(sm, a.H2 + base * 18, h2, live, cnt);
+  stage_out<36>(sm, a.H3 + base * 36, h3, live, cnt);
+}
+
 __global__ void constvel_kernel(const double* __restrict__ v1, const double* __restrict__ v2,
                                 double* __restrict__ resid, double* __restrict__ H0,
                                 double* __restrict__ H1, long long n3, long long n9) {
@@ -166,11 +241,11 @@ extern "C" int pb200_factors_dynamics(const double* pose1, const double* ang_vel
   const unsigned grid = static_cast<unsigned>((N + kFacThreads - 1) / kFacThreads);
   if (jac) {
     const size_t smem = sizeof(double) * kFacThreads * 36;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static bool attr_set[kMaxDevices] = {};  // function attributes belong to the device's context
+    if (!attr_set[current_device()]) {
       PB_CUDA(cudaFuncSetAttribute(dynamics_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                    static_cast<int>(smem)));
-      attr_set = true;
+      attr_set[current_device()] = true;
     }
     dynamics_kernel<true><<<grid, kFacThreads, smem, st>>>(pose1, ang_vel1, vel1, pose2, dt,
                                                             world_frame, resid, H0, H1, H2, H3, N);
@@ -206,6 +281,41 @@ extern "C" int pb200_factors_projection(const double* poses, const double* meas,
                                                                cam_pose12_or_null, resid, nullptr,
                                                                cheirality_or_null, NP, P);
   }
+  PB_CUDA(cudaGetLastError());
+  return PB200_OK;
+}
+
+extern "C" int pb200_factors_chain(const double* poses, const double* ang_vel, const double* vel, const double* meas,
+                                   const double* pts_body, const double* K5, const double* cam_pose12_or_null, double dt,
+                                   int world_frame, double* proj_resid, double* proj_jac, uint8_t* cheirality,
+                                   double* dyn_resid, double* H0, double* H1, double* H2, double* H3, double* cv_angvel_resid,
+                                   double* cv_vel_resid, int W, int T, int P, pb200_stream stream) {
+  if (int rc = require_device()) return rc;
+  PB_CHECK(W >= 0 && T >= 1 && P > 0, "factors_chain: bad W/T/P");
+  if (W == 0) return PB200_OK;
+  PB_CHECK(poses && ang_vel && vel && meas && pts_body && K5 && proj_resid && proj_jac && cheirality,
+           "factors_chain: null input / projection output");
+  PB_CHECK(T == 1 || (dyn_resid && H0 && H1 && H2 && H3 && cv_angvel_resid && cv_vel_resid),
+           "factors_chain: T > 1 needs the dynamics / constant-velocity outputs");
+  ChainArgs a;
+  a.poses = poses; a.ang_vel = ang_vel; a.vel = vel; a.meas = meas; a.pts_body = pts_body; a.K5 = K5;
+  a.cam12 = cam_pose12_or_null; a.dt = dt; a.world_frame = world_frame;
+  a.proj_resid = proj_resid; a.proj_jac = proj_jac; a.cheir = cheirality;
+  a.dyn_resid = dyn_resid; a.H0 = H0; a.H1 = H1; a.H2 = H2; a.H3 = H3; a.cvw_resid = cv_angvel_resid; a.cvv_resid = cv_vel_resid;
+  a.NP = static_cast<long long>(W) * T * P;
+  a.npairs = static_cast<long long>(W) * (T - 1);
+  a.T = T; a.P = P;
+  a.nb_proj = static_cast<int>((a.NP + kFacThreads - 1) / kFacThreads);
+  const long long nb_dyn = (a.npairs + kFacThreads - 1) / kFacThreads;
+  const size_t smem_proj = sizeof(double) * (12 * (kFacThreads + 1) + 16 * kFacThreads);
+  const size_t smem_dyn = sizeof(double) * kFacThreads * 36;
+  const size_t smem = smem_proj > smem_dyn ? smem_proj : smem_dyn;
+  static bool attr_set[kMaxDevices] = {};
+  if (!attr_set[current_device()]) {
+    PB_CUDA(cudaFuncSetAttribute(chain_factors_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    attr_set[current_device()] = true;
+  }
+  chain_factors_kernel<<<static_cast<unsigned>(a.nb_proj + nb_dyn), kFacThreads, smem, static_cast<cudaStream_t>(stream)>>>(a);
   PB_CUDA(cudaGetLastError());
   return PB200_OK;
 }

@@ -708,7 +708,7 @@ extern "C" const char* pb200_plan_op_kernel(const pb200_plan* plan, int i) {
       else if (plan->cache_B < 0 || plan->umma.size() != plan->convs.size()) k = "conv_umma*";
       else {
         const UmmaConvLaunch& L = plan->umma[op.conv];
-        k = std::string(L.pair ? "conv_umma2_kernel<" : "conv_umma_kernel<") + std::to_string(L.block_n) + (L.split == 1 ? ",split>" : (L.split == 2 ? ",x2>" : ">"));
+        k = std::string(L.pair ? "conv_umma2_kernel<" : "conv_umma_kernel<") + std::to_string(L.block_n) + (L.split == 1 ? ",split>" : (L.split == 2 ? ",x2>" : (L.resb ? ",resB>" : ">")));
       }
       break;
     default: k = ""; break;

@@ -61,20 +61,51 @@ def pose_retract(pose12: torch.Tensor, xi: torch.Tensor) -> torch.Tensor:
     return torch.cat([Rn.reshape(*Rn.shape[:-2], 9), tn], dim=-1)
 
 
-def chain_factors(poses, ang_vel, vel, meas, pts_body, K5, dt, camera_pose=None, vel_frame="world"):
+def chain_factors(poses, ang_vel, vel, meas, pts_body, K5, dt, camera_pose=None, vel_frame="world", fused=True, out=None):
     """Evaluates every factor of W chains of T states.  poses (W,T,12), ang_vel / vel (W,T,3), meas (W,T,P,2).
-    Returns a dict of residuals and Jacobians in the layouts the C ABI produces (column-major Jacobians)."""
+    Returns a dict of residuals and Jacobians in the layouts the C ABI produces (column-major Jacobians).
+    fused=True: ONE launch (pb200_factors_chain); False: the three per-kind launches (same results, used as a check).
+    `out`: a dict returned by an earlier call with the same shapes, whose buffers are overwritten (no allocation)."""
     W, T = poses.shape[:2]
     P = pts_body.shape[0]
-    pr, pJ, cheir = keypoint_projection_batch(poses.reshape(W * T, 12), K5, meas.reshape(W * T, P, 2), pts_body, camera_pose)
-    out = {"proj_r": pr, "proj_J": pJ, "cheirality": cheir.reshape(W, T, P)}
+    if not fused:
+        pr, pJ, cheir = keypoint_projection_batch(poses.reshape(W * T, 12), K5, meas.reshape(W * T, P, 2), pts_body, camera_pose)
+        res = {"proj_r": pr, "proj_J": pJ, "cheirality": cheir.reshape(W, T, P)}
+        if T > 1:
+            p1, p2 = poses[:, :-1].reshape(-1, 12), poses[:, 1:].reshape(-1, 12)
+            dr, Hs = pose_dynamics_batch(p1, ang_vel[:, :-1].reshape(-1, 3), vel[:, :-1].reshape(-1, 3), p2, dt, vel_frame)
+            cw, _ = constant_velocity_batch(ang_vel[:, :-1].reshape(-1, 3), ang_vel[:, 1:].reshape(-1, 3), jacobians=False)
+            cv, _ = constant_velocity_batch(vel[:, :-1].reshape(-1, 3), vel[:, 1:].reshape(-1, 3), jacobians=False)
+            res.update(dyn_r=dr, H=Hs, cvw_r=cw, cvv_r=cv)
+        return res
+    assert vel_frame in ["world", "body"], "vel_frame must be 'world' or 'body'."
+    dev = poses.device
+    f64 = dict(dtype=torch.float64, device=dev)
+    poses, ang_vel, vel, meas = (t.to(torch.float64).contiguous() for t in (poses, ang_vel, vel, meas))
+    pts_body = pts_body.to(torch.float64).contiguous()
+    K5 = torch.as_tensor(K5, **f64).contiguous()
+    cam = None if camera_pose is None else camera_pose.to(torch.float64).contiguous()
+    N, M = W * T, W * (T - 1)
+    if out is None:
+        raw = {"proj_r": torch.empty(N, P, 2, **f64), "proj_Jc": torch.empty(N, P, 6, 2, **f64),
+               "cheir_u8": torch.empty(N, P, dtype=torch.uint8, device=dev)}
+        if T > 1:
+            raw.update(dyn_r=torch.empty(M, 6, **f64), Hc=[torch.empty(M, c, 6, **f64) for c in (6, 3, 3, 6)],
+                       cvw_r=torch.empty(M, 3, **f64), cvv_r=torch.empty(M, 3, **f64))
+    else:
+        raw = out["_raw"]
+    Hc = raw.get("Hc", [None] * 4)
+    with torch.cuda.device(dev):
+        _lib.check(_lib.lib().pb200_factors_chain(
+            poses.data_ptr(), ang_vel.data_ptr(), vel.data_ptr(), meas.data_ptr(), pts_body.data_ptr(), K5.data_ptr(),
+            _lib.ptr(cam), float(dt), int(vel_frame == "world"), raw["proj_r"].data_ptr(), raw["proj_Jc"].data_ptr(),
+            raw["cheir_u8"].data_ptr(), _lib.ptr(raw.get("dyn_r")), *[_lib.ptr(h) for h in Hc], _lib.ptr(raw.get("cvw_r")),
+            _lib.ptr(raw.get("cvv_r")), W, T, P, _lib.current_stream_ptr()))
+    res = {"proj_r": raw["proj_r"], "proj_J": raw["proj_Jc"].transpose(2, 3), "cheirality": raw["cheir_u8"].bool().reshape(W, T, P),
+           "_raw": raw}
     if T > 1:
-        p1, p2 = poses[:, :-1].reshape(-1, 12), poses[:, 1:].reshape(-1, 12)
-        dr, Hs = pose_dynamics_batch(p1, ang_vel[:, :-1].reshape(-1, 3), vel[:, :-1].reshape(-1, 3), p2, dt, vel_frame)
-        cw, _ = constant_velocity_batch(ang_vel[:, :-1].reshape(-1, 3), ang_vel[:, 1:].reshape(-1, 3), jacobians=False)
-        cv, _ = constant_velocity_batch(vel[:, :-1].reshape(-1, 3), vel[:, 1:].reshape(-1, 3), jacobians=False)
-        out.update(dyn_r=dr, H=Hs, cvw_r=cw, cvv_r=cv)
-    return out
+        res.update(dyn_r=raw["dyn_r"], H=[h.transpose(1, 2) for h in Hc], cvw_r=raw["cvw_r"], cvv_r=raw["cvv_r"])
+    return res
 
 
 def chain_cost(f: dict, sig: ChainSigmas) -> torch.Tensor:

@@ -129,3 +129,37 @@ def test_projection_cheirality_and_full_size_linearity():
     r0, _, _ = keypoint_projection_batch(p, k, _cuda(meas), c, jacobians=False)
     r1, _, _ = keypoint_projection_batch(p, k, _cuda(meas + 3.0), c, jacobians=False)
     assert (r0 - r1 - 3.0).abs().max().item() < 1e-9
+
+
+@pytest.mark.parametrize("W,T,frame", [(1, 1, "world"), (300, 2, "world"), (7, 19, "body"), (1, 1000, "world"), (129, 3, "world")])
+def test_fused_chain_launch_equals_the_three_per_kind_launches(W, T, frame):
+    """pb200_factors_chain (ONE launch: projection blocks + dynamics blocks that also emit the constant-velocity
+    residuals, pose1 / pose2 read from the one pose array) vs the three separate kernels: identical bits."""
+    from perseus_b200.smoother.linearize import chain_factors
+
+    rng = np.random.default_rng(W * 1000 + T)
+    P = 8
+    R, t = fo.pose_exp(rng.standard_normal((W * T, 6)) * np.array([0.5, 0.5, 0.5, 0.05, 0.05, 0.05]))
+    t[:, 2] += 0.45
+    poses = _pose12(R, t).reshape(W, T, 12)
+    w, v = _cuda(rng.standard_normal((W, T, 3))), _cuda(rng.standard_normal((W, T, 3)))
+    meas = _cuda(rng.uniform(0, 255, (W, T, P, 2)))
+    pts = _cuda(np.array([[a, b, c] for a in (-1, 1) for b in (-1, 1) for c in (-1, 1)], dtype=np.float64) * 0.0175)
+    K5 = _cuda(np.array([221.7, 221.7, 0.5, 128.0, 128.0]))
+    a = chain_factors(poses, w, v, meas, pts, K5, 0.1, None, frame, fused=True)
+    b = chain_factors(poses, w, v, meas, pts, K5, 0.1, None, frame, fused=False)
+    assert torch.equal(a["proj_r"], b["proj_r"]) and torch.equal(a["proj_J"], b["proj_J"])
+    assert torch.equal(a["cheirality"], b["cheirality"])
+    if T > 1:
+        assert torch.equal(a["dyn_r"], b["dyn_r"])
+        for i in range(4):
+            assert torch.equal(a["H"][i], b["H"][i]), f"H[{i}]"
+        assert torch.equal(a["cvw_r"], b["cvw_r"]) and torch.equal(a["cvv_r"], b["cvv_r"])
+        want, _ = fo.pose_dynamics_factor(R.reshape(W, T, 3, 3)[:, :-1].reshape(-1, 3, 3), t.reshape(W, T, 3)[:, :-1].reshape(-1, 3),
+                                          w.cpu().numpy()[:, :-1].reshape(-1, 3), v.cpu().numpy()[:, :-1].reshape(-1, 3),
+                                          R.reshape(W, T, 3, 3)[:, 1:].reshape(-1, 3, 3), t.reshape(W, T, 3)[:, 1:].reshape(-1, 3),
+                                          0.1, frame, jacobians=False)
+        assert np.allclose(a["dyn_r"].cpu().numpy(), want, atol=1e-9)
+    # re-using the output buffers (no allocation) gives the same result
+    c = chain_factors(poses, w, v, meas, pts, K5, 0.1, None, frame, fused=True, out=a)
+    assert c["proj_r"].data_ptr() == a["proj_r"].data_ptr() and torch.equal(c["proj_r"], b["proj_r"])
