@@ -161,6 +161,8 @@ def measure_latency(model, dev, iters=200):
     """BASELINE.json 'bs1 p50 ms' (configs[4] shape): ZED-shaped 376x672 BGRA frame in PINNED HOST memory ->
     keypoints in pinned host memory, wall clock around one CUDA-graph replay + stream sync (H2D, ingest, forward,
     decode, D2H inside).  Also the device-only time of the same graph (CUDA events)."""
+    import time
+
     import torch
 
     from perseus_b200.detector import StreamingDetector
@@ -190,6 +192,34 @@ def measure_latency(model, dev, iters=200):
         out[f"bs{B}_device_p50_ms"] = _p50(devt)
     out["what"] = ("pinned-host BGRA 376x672 frame -> pinned-host keypoints, one CUDA-graph replay (H2D + ingest + "
                    "backbone + head/decode + D2H) + sync; wall clock p50 over %d frames" % iters)
+    # camera frame in -> smoothed pose out: the detector's keypoints go straight into a fixed-lag
+    # window of T = 10 states and two Gauss-Newton iterations run behind the detector in the same CUDA graph
+    try:
+        from perseus_b200.detector import BatchPipeline
+        from perseus_b200.smoother import FixedLagSmoother
+
+        corners = torch.tensor([[a, b, c] for a in (-1, 1) for b in (-1, 1) for c in (-1, 1)], dtype=torch.float64, device=dev) * 0.0175
+        for B in (1, 2):
+            sm = FixedLagSmoother(B, 10, corners, [221.7, 221.7, 0.0, 128.0, 128.0], 0.01, iters=2, lam=1e-3, prior=1.0)
+            bp = BatchPipeline(model, B, 376, 672, 4, bgr=True, post=sm.push, slots=2)
+            sm.poses[..., 11] = 0.45
+            g = torch.Generator().manual_seed(10 + B)
+            frames = [torch.randint(0, 256, (B, 376, 672, 4), dtype=torch.uint8, generator=g).pin_memory() for _ in range(4)]
+            for i in range(20):
+                bp.result_post(bp.submit(frames[i % 4]))
+            wall = []
+            for i in range(iters):
+                t0 = time.perf_counter()
+                bp.result_post(bp.submit(frames[i % 4]))
+                wall.append((time.perf_counter() - t0) * 1e3)
+            out[f"camera_to_pose_bs{B}_p50_ms"] = _p50(wall)
+            out[f"camera_to_pose_bs{B}_p99_ms"] = sorted(wall)[int(len(wall) * 0.99) - 1]
+            del bp, sm
+        out["camera_to_pose_what"] = ("pinned-host BGRA frame(s) -> pinned-host newest Pose3 of a T = 10 fixed-lag window per "
+                                      "camera: H2D, ingest, backbone, head/decode, window advance, 2 x (fused factor launch, "
+                                      "normal equations, block-tridiagonal Cholesky, retraction), D2H; one graph replay per frame")
+    except Exception as e:
+        out["camera_to_pose_error"] = repr(e)[:300]
     return out
 
 

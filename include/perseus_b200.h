@@ -369,6 +369,17 @@ int pb200_smoother_normal_equations(const double* proj_resid, const double* proj
 int pb200_smoother_solve(const double* D, const double* O, const double* g, double* work, double* delta,
                          int32_t* status_or_null, int W, int T, pb200_stream stream);
 
+/* x <- x (+) delta for n states (gtsam Values::retract): pose * Pose3::Expmap(delta[0:6]) (tangent [rot; trans]),
+ * ang_vel + delta[6:9], vel + delta[9:12].  Outputs may alias the inputs. */
+int pb200_smoother_retract(const double* poses, const double* ang_vel, const double* vel, const double* delta,
+                           double* poses_out, double* ang_vel_out, double* vel_out, int64_t n, pb200_stream stream);
+
+/* Fixed-lag window advance, in place, W windows of T states: drops state 0, appends the dynamics factor's own prediction
+ * of the newest state (factors.py:100-105: pose * Exp(dt [ang_vel; v_body]); velocities carried over) and writes the
+ * detector's pixel keypoints (float32 [W][P][2], the layout pb200_forward's out_px has) as its measurement row. */
+int pb200_smoother_push(double* poses, double* ang_vel, double* vel, double* meas, const float* keypoints_px, double dt,
+                        int world_frame, int W, int T, int P, pb200_stream stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -108,6 +108,8 @@ SIGNATURES = {
         c_int,
         [c_void_p] * 9 + [POINTER(c_double), c_double, c_double, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p],
     ),
+    "pb200_smoother_retract": (c_int, [c_void_p] * 7 + [c_int64, c_void_p]),
+    "pb200_smoother_push": (c_int, [c_void_p] * 5 + [c_double, c_int, c_int, c_int, c_int, c_void_p]),
     "pb200_smoother_solve": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p]),
     "pb200_augment": (
         c_int,

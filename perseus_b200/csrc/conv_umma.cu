@@ -554,7 +554,10 @@ int build_umma_conv(UmmaConvLaunch* L, const void* in, int B, int Hin, int Win, 
   int max_clusters;
   L->resb = 0;
   p.a_stages = 0;
-  if (L->pair && split == 0 && p.num_n_tiles == 1 && stats == nullptr && !getenv("PB200_NO_RESB")) {
+  // OFF by default: measured on layer2 (r02, profiles/README.md) it is 5 % SLOWER than streaming the weight tile with the
+  // activations (0.274 vs 0.261 ms for the four layer2 convs) -- the layer is not bound by the bytes of its weight tile,
+  // and the resident image leaves 4 activation stages instead of 8.  PB200_RESB=1 enables it for A/B runs.
+  if (L->pair && split == 0 && p.num_n_tiles == 1 && stats == nullptr && getenv("PB200_RESB")) {
     // resident weights (conv_umma2.cu RESB): this CTA's half of all k-blocks + at least 3 activation stages must fit
     const int resb_bytes = p.num_kblocks * (block_n / 2) * 128;
     const int budget = 216 * 1024;  // + 1 KB alignment slack + ~7.4 KB static shared memory < 227 KB

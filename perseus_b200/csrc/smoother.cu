@@ -13,6 +13,7 @@
 //   chain_solve_kernel      : one warp per window: block-tridiagonal Cholesky (L_k, M_k = O_k L_k^-T), forward and
 //                             backward substitution, fp64, everything staged in shared memory
 #include "common.cuh"
+#include "factors_math.h"
 
 namespace pb200 {
 
@@ -211,9 +212,109 @@ chain_solve_kernel(const double* __restrict__ D, const double* __restrict__ O, c
   if (lane == 0 && status != nullptr) status[w] = ok ? 0 : 1;
 }
 
+// ---- retraction: x <- x (+) delta for every state (gtsam Values::retract: Pose3::retract = pose * Expmap(xi), vectors add)
+__global__ void retract_kernel(const double* __restrict__ poses, const double* __restrict__ ang_vel,
+                               const double* __restrict__ vel, const double* __restrict__ delta, double* __restrict__ poses_out,
+                               double* __restrict__ ang_vel_out, double* __restrict__ vel_out, long long n) {
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double* d = delta + i * kS;
+  const fm::Pose x = fm::load_pose12(poses + i * 12);
+  const fm::Pose y = fm::compose(x, fm::pose_exp(fm::v3(d[0], d[1], d[2]), fm::v3(d[3], d[4], d[5])));
+#pragma unroll
+  for (int k = 0; k < 9; ++k) poses_out[i * 12 + k] = y.R.m[k];
+  poses_out[i * 12 + 9] = y.t.x; poses_out[i * 12 + 10] = y.t.y; poses_out[i * 12 + 11] = y.t.z;
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    ang_vel_out[i * 3 + k] = ang_vel[i * 3 + k] + d[6 + k];
+    vel_out[i * 3 + k] = vel[i * 3 + k] + d[9 + k];
+  }
+}
+
+// ---- fixed-lag window advance: drop the oldest state, append the prediction of the newest, insert its measurement
+// One CTA per window.  New state = the dynamics factor's own prediction (factors.py:100-105): pose_T-1 * Exp(dt [w; v_b]),
+// v_b = R^T v for a world-frame velocity; velocities carried over (the constant-velocity prior).  The measurement row is
+// the detector's pixel keypoints (float32 [W][P][2], what head_kernel writes) widened to float64 in place.
+__global__ void __launch_bounds__(128) window_push_kernel(double* __restrict__ poses, double* __restrict__ ang_vel,
+                                                          double* __restrict__ vel, double* __restrict__ meas,
+                                                          const float* __restrict__ keypoints_px, double dt, int world_frame,
+                                                          int T, int P) {
+  extern __shared__ double sm[];
+  const int w = blockIdx.x;
+  const int per = 12 + 3 + 3 + 2 * P;  // doubles per state
+  double* pw = poses + static_cast<long long>(w) * T * 12;
+  double* aw = ang_vel + static_cast<long long>(w) * T * 3;
+  double* vw = vel + static_cast<long long>(w) * T * 3;
+  double* mw = meas + static_cast<long long>(w) * T * 2 * P;
+  // stage states 1 .. T-1 (the survivors), then write them back one slot earlier
+  for (int i = threadIdx.x; i < (T - 1) * per; i += blockDim.x) {
+    const int k = i / per + 1, j = i % per;
+    sm[i] = j < 12 ? pw[k * 12 + j] : (j < 15 ? aw[k * 3 + j - 12] : (j < 18 ? vw[k * 3 + j - 15] : mw[k * 2 * P + j - 18]));
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < (T - 1) * per; i += blockDim.x) {
+    const int k = i / per, j = i % per;
+    if (j < 12) pw[k * 12 + j] = sm[i];
+    else if (j < 15) aw[k * 3 + j - 12] = sm[i];
+    else if (j < 18) vw[k * 3 + j - 15] = sm[i];
+    else mw[k * 2 * P + j - 18] = sm[i];
+  }
+  // the new newest state, predicted from the old newest (the last staged row; for T == 1 the state itself)
+  if (threadIdx.x == 0) {
+    const double* last = T > 1 ? sm + (T - 2) * per : nullptr;
+    double p12[12], wv[3], vv[3];
+    for (int j = 0; j < 12; ++j) p12[j] = last ? last[j] : pw[j];
+    for (int j = 0; j < 3; ++j) {
+      wv[j] = last ? last[12 + j] : aw[j];
+      vv[j] = last ? last[15 + j] : vw[j];
+    }
+    const fm::Pose x = fm::load_pose12(p12);
+    const fm::V3 om = fm::v3(wv[0], wv[1], wv[2]);
+    fm::V3 vb = fm::v3(vv[0], vv[1], vv[2]);
+    if (world_frame) vb = fm::mulT(x.R, vb);
+    const fm::Pose y = fm::compose(x, fm::pose_exp(fm::scale(dt, om), fm::scale(dt, vb)));
+    double* po = pw + (T - 1) * 12;
+    for (int k = 0; k < 9; ++k) po[k] = y.R.m[k];
+    po[9] = y.t.x; po[10] = y.t.y; po[11] = y.t.z;
+    for (int j = 0; j < 3; ++j) {
+      aw[(T - 1) * 3 + j] = wv[j];
+      vw[(T - 1) * 3 + j] = vv[j];
+    }
+  }
+  for (int i = threadIdx.x; i < 2 * P; i += blockDim.x)
+    mw[(T - 1) * 2 * P + i] = static_cast<double>(keypoints_px[static_cast<long long>(w) * 2 * P + i]);
+}
+
 }  // namespace pb200
 
 using namespace pb200;
+
+extern "C" int pb200_smoother_retract(const double* poses, const double* ang_vel, const double* vel, const double* delta,
+                                      double* poses_out, double* ang_vel_out, double* vel_out, int64_t n,
+                                      pb200_stream stream) {
+  if (int rc = require_device()) return rc;
+  PB_CHECK(n >= 0, "smoother_retract: n < 0");
+  if (n == 0) return PB200_OK;
+  PB_CHECK(poses && ang_vel && vel && delta && poses_out && ang_vel_out && vel_out, "smoother_retract: null argument");
+  retract_kernel<<<static_cast<unsigned>((n + 127) / 128), 128, 0, static_cast<cudaStream_t>(stream)>>>(
+      poses, ang_vel, vel, delta, poses_out, ang_vel_out, vel_out, n);
+  PB_CUDA(cudaGetLastError());
+  return PB200_OK;
+}
+
+extern "C" int pb200_smoother_push(double* poses, double* ang_vel, double* vel, double* meas, const float* keypoints_px,
+                                   double dt, int world_frame, int W, int T, int P, pb200_stream stream) {
+  if (int rc = require_device()) return rc;
+  PB_CHECK(W >= 0 && T >= 1 && P >= 1, "smoother_push: bad W/T/P");
+  if (W == 0) return PB200_OK;
+  PB_CHECK(poses && ang_vel && vel && meas && keypoints_px, "smoother_push: null argument");
+  const size_t smem = sizeof(double) * static_cast<size_t>(T > 1 ? T - 1 : 1) * (18 + 2 * P);
+  PB_CHECK(smem <= 48 * 1024, "smoother_push: window of %d states x %d points does not fit the staging buffer", T, P);
+  window_push_kernel<<<W, 128, smem, static_cast<cudaStream_t>(stream)>>>(poses, ang_vel, vel, meas, keypoints_px, dt,
+                                                                         world_frame, T, P);
+  PB_CUDA(cudaGetLastError());
+  return PB200_OK;
+}
 
 extern "C" int pb200_smoother_normal_equations(const double* proj_resid, const double* proj_jac, const double* dyn_resid,
                                                const double* H0, const double* H1, const double* H2, const double* H3,

@@ -26,7 +26,11 @@ from .models import KeypointCNN
 class BatchPipeline:
     def __init__(self, model: KeypointCNN, batch: int, src_h: int | None = None, src_w: int | None = None,
                  channels: int = 3, *, bgr: bool = False, depth_divisor: float = 1.0, slots: int = 2, results: int = 4,
-                 copy_streams: int = 1, device: torch.device | None = None):
+                 copy_streams: int = 1, device: torch.device | None = None, post=None):
+        """post: optional callable(px (B, K, 2) float32 device tensor) -> device tensor with a FIXED address, captured into
+        every batch's CUDA graph right behind the detector (e.g. FixedLagSmoother.push: keypoints go straight into the
+        smoother's measurement buffer and the newest pose comes back with `result_post`).  It must not allocate or
+        synchronise.  A stateful `post` is executed once during construction (warm-up): reset its state afterwards."""
         if model.training:
             raise RuntimeError("BatchPipeline needs model.eval()")
         self.model = model
@@ -60,9 +64,11 @@ class BatchPipeline:
         self.ev_ingested = [torch.cuda.Event() for _ in range(slots)]  # frames[s] ready
         self.ev_fwd = [torch.cuda.Event() for _ in range(slots)]       # frames[s] consumed (forward done)
         self.ev_read = [torch.cuda.Event() for _ in range(slots)]      # px_dev[s] copied to the host
+        self.ev_post_read = torch.cuda.Event()
         self.ev_done = [torch.cuda.Event() for _ in range(results)]
         self.graphs = [None] * slots
         self.ticket = 0
+        self.post, self.post_dev, self.host_post = post, None, None
         self._capture()
 
     def _ingest(self, s: int):
@@ -70,8 +76,16 @@ class BatchPipeline:
                           out=self.frames[s], plan=self.plan)
 
     def _run(self, s: int):
-        return self.model.forward_ingested(self.frames[s], self.B, plan=self.plan, out_norm=self.norm_dev[s],
-                                           out_px=self.px_dev[s])[1]
+        px = self.model.forward_ingested(self.frames[s], self.B, plan=self.plan, out_norm=self.norm_dev[s],
+                                         out_px=self.px_dev[s])[1]
+        if self.post is not None:
+            out = self.post(px)
+            if self.post_dev is None:
+                self.post_dev = out
+                self.host_post = [torch.empty(out.shape, dtype=out.dtype).pin_memory() for _ in range(self.results)]
+            elif out.data_ptr() != self.post_dev.data_ptr():
+                raise RuntimeError("BatchPipeline: `post` must return the same device tensor on every call")
+        return px
 
     def _capture(self):
         with torch.cuda.stream(self.compute):
@@ -90,7 +104,7 @@ class BatchPipeline:
             with torch.cuda.graph(g, stream=self.compute):
                 self._run(s)
             self.graphs[s] = g
-        for e in self.ev_free + self.ev_fwd + self.ev_read:
+        for e in self.ev_free + self.ev_fwd + self.ev_read + [self.ev_post_read]:
             e.record(self.compute)
         self.compute.synchronize()
 
@@ -125,11 +139,16 @@ class BatchPipeline:
             self.compute.wait_event(self.ev_ingested[s])
             self.model.sync_plan_weights(self.plan)
             self.compute.wait_event(self.ev_read[s])  # px_dev[s] of the batch two submits ago has been read back
+            if self.post_dev is not None:
+                self.compute.wait_event(self.ev_post_read)  # the shared `post` output of the previous batch has been read
             self.graphs[s].replay()
             self.ev_fwd[s].record(self.compute)
         with torch.cuda.stream(self.d2h):
             self.d2h.wait_event(self.ev_fwd[s])
             self.host_px[r].copy_(self.px_dev[s], non_blocking=True)
+            if self.post_dev is not None:
+                self.host_post[r].copy_(self.post_dev, non_blocking=True)
+                self.ev_post_read.record(self.d2h)
             self.ev_done[r].record(self.d2h)
             self.ev_read[s].record(self.d2h)
         self.ticket = t + 1
@@ -142,6 +161,14 @@ class BatchPipeline:
             raise ValueError(f"result: ticket {ticket} is not outstanding (next ticket {self.ticket}, ring {self.results})")
         self.ev_done[ticket % self.results].synchronize()
         return self.host_px[ticket % self.results]
+
+    def result_post(self, ticket: int) -> torch.Tensor:
+        """The `post` output of `ticket` in pinned host memory (same lifetime rule as `result`): read back right after its
+        batch's graph; the next batch's graph waits for that read-back, so every ticket sees its own snapshot."""
+        if self.post_dev is None:
+            raise RuntimeError("result_post: the pipeline was built without `post`")
+        self.result(ticket)
+        return self.host_post[ticket % self.results]
 
     def copy_only(self, host_rgb: torch.Tensor) -> None:
         """The pipeline's host -> device traffic alone (same buffers and copy streams, no compute): its ceiling."""

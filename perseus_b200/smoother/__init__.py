@@ -12,3 +12,4 @@ from .linearize import (  # noqa: F401,E402
     normal_equations,
     pose_retract,
 )
+from .fixed_lag import FixedLagSmoother  # noqa: F401,E402

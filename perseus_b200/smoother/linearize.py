@@ -38,27 +38,26 @@ def _hat(w: torch.Tensor) -> torch.Tensor:
     return torch.stack([z, -w[..., 2], w[..., 1], w[..., 2], z, -w[..., 0], -w[..., 1], w[..., 0], z], -1).reshape(*w.shape[:-1], 3, 3)
 
 
+def retract(poses: torch.Tensor, ang_vel: torch.Tensor, vel: torch.Tensor, delta: torch.Tensor):
+    """gtsam Values.retract on every state, one launch (pb200_smoother_retract): poses (...,12) * Pose3.Expmap(delta[...,:6])
+    (full SE(3) exponential, tangent [rot; trans]), ang_vel + delta[...,6:9], vel + delta[...,9:12]."""
+    if not poses.is_cuda:
+        raise RuntimeError("retract: cuda float64 tensors required (no CPU fallback)")
+    f = lambda t: t.to(torch.float64).contiguous()  # noqa: E731
+    poses, ang_vel, vel, delta = f(poses), f(ang_vel), f(vel), f(delta)
+    n = poses.numel() // 12
+    po, ao, vo = torch.empty_like(poses), torch.empty_like(ang_vel), torch.empty_like(vel)
+    with torch.cuda.device(poses.device):
+        _lib.check(_lib.lib().pb200_smoother_retract(poses.data_ptr(), ang_vel.data_ptr(), vel.data_ptr(), delta.data_ptr(),
+                                                     po.data_ptr(), ao.data_ptr(), vo.data_ptr(), n, _lib.current_stream_ptr()))
+    return po, ao, vo
+
+
 def pose_retract(pose12: torch.Tensor, xi: torch.Tensor) -> torch.Tensor:
     """Pose3.retract = pose * Expmap(xi) (full SE(3) exponential, tangent [rot; trans]); (…,12), (…,6) -> (…,12)."""
-    w, v = xi[..., :3], xi[..., 3:]
-    th2 = (w * w).sum(-1, keepdim=True).unsqueeze(-1)
-    th = th2.sqrt()
-    small = th < 1e-6
-    ths = torch.where(small, torch.ones_like(th), th)
-    A = torch.where(small, 1 - th2 / 6, torch.sin(ths) / ths)
-    B = torch.where(small, 0.5 - th2 / 24, (1 - torch.cos(ths)) / (ths * ths))
-    C = torch.where(small, 1.0 / 6 - th2 / 120, (ths - torch.sin(ths)) / (ths * ths * ths))
-    K = _hat(w)
-    K2 = K @ K
-    eye = torch.eye(3, dtype=xi.dtype, device=xi.device).expand_as(K)
-    Rinc = eye + A * K + B * K2
-    V = eye + B * K + C * K2
-    tinc = (V @ v.unsqueeze(-1)).squeeze(-1)
-    R = pose12[..., :9].reshape(*pose12.shape[:-1], 3, 3)
-    t = pose12[..., 9:]
-    Rn = R @ Rinc
-    tn = t + (R @ tinc.unsqueeze(-1)).squeeze(-1)
-    return torch.cat([Rn.reshape(*Rn.shape[:-2], 9), tn], dim=-1)
+    z = torch.zeros(*xi.shape[:-1], 3, dtype=torch.float64, device=xi.device)
+    d = torch.cat([xi.to(torch.float64), z, z], dim=-1)
+    return retract(pose12, z, z, d)[0]
 
 
 def chain_factors(poses, ang_vel, vel, meas, pts_body, K5, dt, camera_pose=None, vel_frame="world", fused=True, out=None):
@@ -166,6 +165,6 @@ def gauss_newton_step(poses, ang_vel, vel, meas, pts_body, K5, dt, sigmas: Optio
     f = chain_factors(poses, ang_vel, vel, meas, pts_body, K5, dt, camera_pose, vel_frame)
     D, O, g = normal_equations(f, W, T, P, sig, lam, prior)
     delta, status = chain_solve(D, O, g)
-    new_poses = pose_retract(poses, delta[..., :6])
-    return new_poses, ang_vel + delta[..., 6:9], vel + delta[..., 9:12], {
+    new_poses, new_w, new_v = retract(poses, ang_vel, vel, delta)
+    return new_poses, new_w, new_v, {
         "cost": chain_cost(f, sig), "delta": delta, "status": status, "D": D, "O": O, "g": g, "factors": f}

@@ -524,3 +524,13 @@ def test_streaming_detector_graph_matches_eager_path():
     x = do.streaming_ingest(bgra[0].numpy(), None, 3)[None]
     want = do.denormalize_pixel_coordinates(do.reference_forward(sd, x).reshape(1, 8, 2), 256, 256)
     assert (got - want).abs().max() <= 1e-3
+
+
+@pytest.mark.parametrize("case", [CONV_CASES[1], CONV_CASES[2], CONV_CASES[4]], ids=str)
+def test_pair_conv_resident_weights_variant(case, monkeypatch):
+    """conv_umma2_kernel<.., RESB>: the CTA pair keeps its halves of the whole weight matrix in shared memory and streams
+    activations only (single-N-tile convs; opt-in with PB200_RESB=1 after it measured slower on layer2)."""
+    monkeypatch.setenv("PB200_RESB", "1")
+    test_umma_conv_layer_vs_exact_operand_reference(case, "p", monkeypatch)
+    if case is CONV_CASES[4]:
+        test_umma_conv_with_fused_projection_vs_exact_operand_reference(DS_CASES[0], "p", monkeypatch)

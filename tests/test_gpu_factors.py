@@ -134,7 +134,8 @@ def test_projection_cheirality_and_full_size_linearity():
 @pytest.mark.parametrize("W,T,frame", [(1, 1, "world"), (300, 2, "world"), (7, 19, "body"), (1, 1000, "world"), (129, 3, "world")])
 def test_fused_chain_launch_equals_the_three_per_kind_launches(W, T, frame):
     """pb200_factors_chain (ONE launch: projection blocks + dynamics blocks that also emit the constant-velocity
-    residuals, pose1 / pose2 read from the one pose array) vs the three separate kernels: identical bits."""
+    residuals, pose1 / pose2 read from the one pose array) vs the three separate kernels: equal to 1e-12 (the same
+    inlined arithmetic compiled in two kernels may contract different multiply-adds), and to the oracle to 1e-9."""
     from perseus_b200.smoother.linearize import chain_factors
 
     rng = np.random.default_rng(W * 1000 + T)
@@ -148,12 +149,13 @@ def test_fused_chain_launch_equals_the_three_per_kind_launches(W, T, frame):
     K5 = _cuda(np.array([221.7, 221.7, 0.5, 128.0, 128.0]))
     a = chain_factors(poses, w, v, meas, pts, K5, 0.1, None, frame, fused=True)
     b = chain_factors(poses, w, v, meas, pts, K5, 0.1, None, frame, fused=False)
-    assert torch.equal(a["proj_r"], b["proj_r"]) and torch.equal(a["proj_J"], b["proj_J"])
+    close = lambda x, y: torch.allclose(x, y, rtol=1e-12, atol=1e-12)  # noqa: E731
+    assert close(a["proj_r"], b["proj_r"]) and close(a["proj_J"], b["proj_J"])
     assert torch.equal(a["cheirality"], b["cheirality"])
     if T > 1:
-        assert torch.equal(a["dyn_r"], b["dyn_r"])
+        assert close(a["dyn_r"], b["dyn_r"])
         for i in range(4):
-            assert torch.equal(a["H"][i], b["H"][i]), f"H[{i}]"
+            assert close(a["H"][i], b["H"][i]), f"H[{i}]"
         assert torch.equal(a["cvw_r"], b["cvw_r"]) and torch.equal(a["cvv_r"], b["cvv_r"])
         want, _ = fo.pose_dynamics_factor(R.reshape(W, T, 3, 3)[:, :-1].reshape(-1, 3, 3), t.reshape(W, T, 3)[:, :-1].reshape(-1, 3),
                                           w.cpu().numpy()[:, :-1].reshape(-1, 3), v.cpu().numpy()[:, :-1].reshape(-1, 3),
@@ -162,4 +164,4 @@ def test_fused_chain_launch_equals_the_three_per_kind_launches(W, T, frame):
         assert np.allclose(a["dyn_r"].cpu().numpy(), want, atol=1e-9)
     # re-using the output buffers (no allocation) gives the same result
     c = chain_factors(poses, w, v, meas, pts, K5, 0.1, None, frame, fused=True, out=a)
-    assert c["proj_r"].data_ptr() == a["proj_r"].data_ptr() and torch.equal(c["proj_r"], b["proj_r"])
+    assert c["proj_r"].data_ptr() == a["proj_r"].data_ptr() and close(c["proj_r"], b["proj_r"])
