@@ -215,12 +215,12 @@ int launch_stem_f32(const SimtConv& c, int real_channels, cudaStream_t st) {
   typedef void (*kern_t)(const float4*, const float*, const float*, float*, int, int, int, int);
   static const kern_t table[2][3] = {{stem_f32_kernel<3, 0>, stem_f32_kernel<3, 1>, stem_f32_kernel<3, 2>},
                                      {stem_f32_kernel<4, 0>, stem_f32_kernel<4, 1>, stem_f32_kernel<4, 2>}};
-  static bool attr_set = false;
-  if (!attr_set) {
+  static bool attr_set[kMaxDevices] = {};  // function attributes belong to the device's context
+  if (!attr_set[current_device()]) {
     for (int a = 0; a < 2; ++a)
       for (int m = 0; m < 3; ++m)
         PB_CUDA(cudaFuncSetAttribute(table[a][m], cudaFuncAttributeMaxDynamicSharedMemorySize, ST_SMEM));
-    attr_set = true;
+    attr_set[current_device()] = true;
   }
   const long long ntiles = static_cast<long long>(c.B) * (c.Ho / ST_ROWS) * (c.Wo / ST_COLS);
   const long long cap = 2LL * num_sms();

@@ -261,12 +261,13 @@ static int wg_set_attr() {
 }
 
 int wgrad_umma_init() {
-  static bool done = false;
-  if (done) return PB200_OK;
+  static bool done[kMaxDevices] = {};  // function attributes belong to the device's context
+  const int dev = current_device();
+  if (done[dev]) return PB200_OK;
   if (int rc = wg_set_attr<64>()) return rc;
   if (int rc = wg_set_attr<128>()) return rc;
   if (int rc = wg_set_attr<256>()) return rc;
-  done = true;
+  done[dev] = true;
   return PB200_OK;
 }
 
