@@ -54,7 +54,12 @@ struct ConvP8Params {
 // two column groups.  144 KB of resident weights leave room for two patch stages.
 template <int kEpiWarps, bool X2>
 __device__ __forceinline__ void conv_p8_body(const ConvP8Params& p) {
-  constexpr int kStages = X2 ? 2 : 4;
+  // X2: the 144 KB of weights leave 67 KB for patches = two whole-tile stages, i.e. ONE tile of prefetch (1.2 us of
+  // MMAs) against ~2 us of patch latency.  The ring is therefore cut into HALF-tile stages (4 of the 8 channel chunks
+  // each, 4 stages): the producer runs three half-stages ahead of the MMAs.
+  constexpr int kSplit = X2 ? 2 : 1;               // stages per tile
+  constexpr int kStageChunks = kChunks / kSplit;   // channel chunks per stage
+  constexpr int kStages = 4;
   constexpr int kWAll = X2 ? 2 * kWBytes : kWBytes;
   constexpr int kAccCols = X2 ? 128 : 64;
   constexpr int kNch = 8 / (kEpiWarps / 4);  // 8-channel chunks (P8 planes) per epilogue thread
@@ -71,7 +76,7 @@ __device__ __forceinline__ void conv_p8_body(const ConvP8Params& p) {
   uint8_t* smem = smem_raw + (((raw_addr + 127u) & ~127u) - raw_addr);
   uint8_t* s_w = smem;
   uint8_t* s_patch = smem + kWAll;
-  const int stage_bytes = kChunks * p.patch_pitch;
+  const int stage_bytes = kStageChunks * p.patch_pitch;
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -115,18 +120,21 @@ __device__ __forceinline__ void conv_p8_body(const ConvP8Params& p) {
       const int n = tile / p.tiles_per_img;
       const int q0 = (tile - n * p.tiles_per_img) * 128;
       const uint8_t* src = p.in + n * p.img_bytes + static_cast<long long>(q0) * 16;
-      mbar_wait(&empty_bar[stage], phase ^ 1u);
-      if (elect_one()) {
-        mbar_expect_tx(&full_bar[stage], chunk_bytes * kChunks);
-        uint8_t* dst = s_patch + stage * stage_bytes;
 #pragma unroll
-        for (int j = 0; j < kChunks; ++j)
-          bulk_load_1d(dst + j * p.patch_pitch, src + j * p.plane_bytes, chunk_bytes, &full_bar[stage]);
-      }
-      __syncwarp();
-      if (++stage == kStages) {
-        stage = 0;
-        phase ^= 1u;
+      for (int h = 0; h < kSplit; ++h) {
+        mbar_wait(&empty_bar[stage], phase ^ 1u);
+        if (elect_one()) {
+          mbar_expect_tx(&full_bar[stage], chunk_bytes * kStageChunks);
+          uint8_t* dst = s_patch + stage * stage_bytes;
+#pragma unroll
+          for (int j = 0; j < kStageChunks; ++j)
+            bulk_load_1d(dst + j * p.patch_pitch, src + (h * kStageChunks + j) * p.plane_bytes, chunk_bytes, &full_bar[stage]);
+        }
+        __syncwarp();
+        if (++stage == kStages) {
+          stage = 0;
+          phase ^= 1u;
+        }
       }
     }
   } else if (warp == 1) {
@@ -144,27 +152,30 @@ __device__ __forceinline__ void conv_p8_body(const ConvP8Params& p) {
     for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
       const int acc = it & 1;
       mbar_wait(&tmem_empty_bar[acc], ((it >> 1) & 1u) ^ 1u);
-      mbar_wait(&full_bar[stage], phase);
-      tc_fence_after();
-      if (elect_one()) {
-        const uint32_t d_tmem = tm + acc * kAccCols;
-        const uint32_t a_lo0 = desc_lo(smem_u32(s_patch) + stage * stage_bytes, p.patch_pitch);
 #pragma unroll
-        for (int t = 0; t < 9; ++t) {
-          const int r = t / 3, s = t - 3 * r;
-          const uint32_t a_tap = a_lo0 + static_cast<uint32_t>(r * p.Wp + s);  // (r*Wp + s) * 16 B >> 4
+      for (int h = 0; h < kSplit; ++h) {
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        if (elect_one()) {
+          const uint32_t d_tmem = tm + acc * kAccCols;
+          const uint32_t a_lo0 = desc_lo(smem_u32(s_patch) + stage * stage_bytes, p.patch_pitch);
 #pragma unroll
-          for (int kk = 0; kk < 4; ++kk)
-            umma_bf16_split(d_tmem, a_tap + 2 * kk * pitch16, a_hi, b_lo0 + (t * 8 + 2 * kk) * 8, b_hi, idesc,
-                            (t | kk) != 0 ? 1u : 0u);
+          for (int t = 0; t < 9; ++t) {
+            const int r = t / 3, s = t - 3 * r;
+            const uint32_t a_tap = a_lo0 + static_cast<uint32_t>(r * p.Wp + s);  // (r*Wp + s) * 16 B >> 4
+#pragma unroll
+            for (int kk = 0; kk < kStageChunks / 2; ++kk)  // K = 16 = two channel chunks of this stage
+              umma_bf16_split(d_tmem, a_tap + 2 * kk * pitch16, a_hi, b_lo0 + (t * 8 + h * kStageChunks + 2 * kk) * 8, b_hi,
+                              idesc, (h | t | kk) != 0 ? 1u : 0u);
+          }
+          umma_commit(&empty_bar[stage]);
+          if (h == kSplit - 1) umma_commit(&tmem_full_bar[acc]);
         }
-        umma_commit(&empty_bar[stage]);
-        umma_commit(&tmem_full_bar[acc]);
-      }
-      __syncwarp();
-      if (++stage == kStages) {
-        stage = 0;
-        phase ^= 1u;
+        __syncwarp();
+        if (++stage == kStages) {
+          stage = 0;
+          phase ^= 1u;
+        }
       }
     }
   } else {
@@ -325,8 +336,8 @@ __global__ void __launch_bounds__(p8_threads(8), 1) conv_p8_x2_kernel(const Conv
 
 constexpr int kMaxDynSmem = 227 * 1024 - 1024;  // the kernel also has ~400 B of static shared memory
 inline int patch_pitch_for(int Wp) { return ((128 + 2 * Wp + 2) * 16 + 127) / 128 * 128; }
-inline int smem_bytes_for(int Wp, bool x2) {
-  return (x2 ? 2 : 1) * kWBytes + (x2 ? 2 : 4) * kChunks * patch_pitch_for(Wp) + 128;
+inline int smem_bytes_for(int Wp, bool x2) {  // 4 stages of 8 (whole tile) / 4 (half tile, X2) chunk planes
+  return (x2 ? 2 : 1) * kWBytes + 4 * (x2 ? kChunks / 2 : kChunks) * patch_pitch_for(Wp) + 128;
 }
 
 }  // namespace

@@ -4,6 +4,8 @@
 //
 // Replaces the per-factor Python callbacks of perseus/smoother/factors.py (:54-142, :160-171,
 // :216-275) that GTSAM invokes one at a time on the CPU.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "factors_math.h"
 
@@ -38,9 +40,11 @@ __device__ __forceinline__ void stage_out(double* sm, double* __restrict__ dst, 
 // are staged in it first; the outputs (6 + 36 + 18 + 18 + 36 doubles per factor) are then staged and copied out one
 // block at a time while the rest waits in registers.  (Staging all 114 output doubles at once needed 147 KB per CTA:
 // one CTA = 4 warps per SM, and ncu showed the kernel latency-bound at 6 % occupancy; this form is register-limited
-// to 2 CTAs per SM.)
-template <bool JAC>
-__global__ void __launch_bounds__(kFacThreads)
+// to 2 CTAs per SM.  r02: capping the registers at 168 (3 CTAs per SM, 1.4 KB of spills per thread) is 12 % faster.)
+// MINB = minimum resident CTAs per SM the compiler must allow (register cap 65536 / (128 * MINB)): 1 = no cap (255
+// registers, 2 CTAs per SM by registers), 3 / 4 = 168 / 128 registers with spills to local memory (A/B: PB200_DYN_MINB)
+template <bool JAC, int MINB>
+__global__ void __launch_bounds__(kFacThreads, MINB)
 dynamics_kernel(const double* __restrict__ pose1, const double* __restrict__ angvel,
                 const double* __restrict__ vel, const double* __restrict__ pose2, double dt,
                 int world_frame, double* __restrict__ resid, double* __restrict__ H0,
@@ -243,15 +247,22 @@ extern "C" int pb200_factors_dynamics(const double* pose1, const double* ang_vel
     const size_t smem = sizeof(double) * kFacThreads * 36;
     static bool attr_set[kMaxDevices] = {};  // function attributes belong to the device's context
     if (!attr_set[current_device()]) {
-      PB_CUDA(cudaFuncSetAttribute(dynamics_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                   static_cast<int>(smem)));
+      PB_CUDA(cudaFuncSetAttribute(dynamics_kernel<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+      PB_CUDA(cudaFuncSetAttribute(dynamics_kernel<true, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+      PB_CUDA(cudaFuncSetAttribute(dynamics_kernel<true, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
       attr_set[current_device()] = true;
     }
-    dynamics_kernel<true><<<grid, kFacThreads, smem, st>>>(pose1, ang_vel1, vel1, pose2, dt,
-                                                            world_frame, resid, H0, H1, H2, H3, N);
+    const char* e = getenv("PB200_DYN_MINB");
+    const int minb = e ? atoi(e) : 3;  // measured at 1 M pairs (r02): 0.761 / 0.667 / 0.716 ms for caps 255 / 168 / 128 registers
+    if (minb == 4)
+      dynamics_kernel<true, 4><<<grid, kFacThreads, smem, st>>>(pose1, ang_vel1, vel1, pose2, dt, world_frame, resid, H0, H1, H2, H3, N);
+    else if (minb == 3)
+      dynamics_kernel<true, 3><<<grid, kFacThreads, smem, st>>>(pose1, ang_vel1, vel1, pose2, dt, world_frame, resid, H0, H1, H2, H3, N);
+    else
+      dynamics_kernel<true, 1><<<grid, kFacThreads, smem, st>>>(pose1, ang_vel1, vel1, pose2, dt, world_frame, resid, H0, H1, H2, H3, N);
   } else {
     const size_t smem = sizeof(double) * kFacThreads * 30;
-    dynamics_kernel<false><<<grid, kFacThreads, smem, st>>>(
+    dynamics_kernel<false, 1><<<grid, kFacThreads, smem, st>>>(
         pose1, ang_vel1, vel1, pose2, dt, world_frame, resid, nullptr, nullptr, nullptr, nullptr, N);
   }
   PB_CUDA(cudaGetLastError());
