@@ -177,6 +177,11 @@ int pb200_debug_conv_f16x2(const void* in_nhwc, int B, int H, int W, int Cin, co
                            const void* residual_nhwc_or_null, int relu, void* out_nhwc,
                            const void* ds_in_nhwc_or_null, int ds_Cin, const float* wds_oi_host_or_null,
                            pb200_stream stream);
+/* One 3x3/1 conv with Cout = 128 through the halo-patch / resident-weights pair kernel (csrc/conv_halo.cu, layer2), NHWC bf16,
+ * optionally with the fused 1x1/2 projection of ds_in [B][2H][2W][ds_Cin] (weights wds [Cout][ds_Cin]). */
+int pb200_debug_conv_halo(const void* in_nhwc, int B, int H, int W, int Cin, const float* w_oihw_host,
+                          const float* bias_host, int Cout, const void* residual_nhwc_or_null, int relu, void* out_nhwc,
+                          const void* ds_in_nhwc_or_null, int ds_Cin, const float* wds_oi_host_or_null, pb200_stream stream);
 int pb200_debug_conv_p8_f16x2(const void* in_p8, int B, int H, int W, const float* w_oihw_host,
                               const float* bias_host, const void* residual_p8_or_null, int relu, void* out,
                               int out_nhwc, pb200_stream stream);

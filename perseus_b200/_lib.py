@@ -76,6 +76,11 @@ SIGNATURES = {
         [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_int,
          c_void_p, c_void_p, c_int, c_void_p, c_void_p],
     ),
+    "pb200_debug_conv_halo": (
+        c_int,
+        [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p,
+         c_void_p],
+    ),
     "pb200_debug_conv_p8_f16x2": (
         c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p]
     ),

@@ -15,7 +15,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libperseus_b200.so")
 STAMP = os.path.join(HERE, ".build_stamp")
 
-SOURCES = ["runtime.cu", "frames.cu", "pool_head.cu", "conv_simt.cu", "conv_umma.cu", "conv_umma2.cu", "stem_pool.cu", "conv_p8.cu", "factors.cu", "plan.cu", "wgrad_umma.cu", "train.cu", "augment.cu", "smoother.cu"]
+SOURCES = ["runtime.cu", "frames.cu", "pool_head.cu", "conv_simt.cu", "conv_umma.cu", "conv_umma2.cu", "conv_halo.cu", "stem_pool.cu", "conv_p8.cu", "factors.cu", "plan.cu", "wgrad_umma.cu", "train.cu", "augment.cu", "smoother.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-O3", "-lineinfo", "-std=c++17",

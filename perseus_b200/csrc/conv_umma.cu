@@ -128,13 +128,14 @@ conv_umma_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams
         ho0 = 0;
       }
       // the issue loop is kept as light as possible: one warp must feed a k-block every 128-512 MMA cycles
+      // K order: 64-channel block outermost, filter taps inside (the order csrc/conv_halo.cu walks its patches in)
       int kcol = 0;
-      for (int tap = 0; tap < p.ntaps; ++tap) {
-        const int dw = p.tap_dw[tap];
-        const CUtensorMap* amap = &maps.a[p.tap_mi[tap]];
-        const int hrow = ho0 + p.tap_dh[tap];
-        kcol = p.tap_k[tap];
-        for (int cb = 0; cb < p.cblocks; ++cb, kcol += Cfg::kBlockK) {
+      for (int cb = 0; cb < p.cblocks; ++cb) {
+        for (int tap = 0; tap < p.ntaps; ++tap) {
+          const int dw = p.tap_dw[tap];
+          const CUtensorMap* amap = &maps.a[p.tap_mi[tap]];
+          const int hrow = ho0 + p.tap_dh[tap];
+          kcol = p.tap_k[tap] + cb * Cfg::kBlockK;
           // SPLIT ("bf16x3"): a = a_hi + a_lo (channels [0,Cin) and [Cin,2Cin) of the activation tensor),
           // w = w_hi + w_lo (columns [0,Ktot) and [Ktot,2Ktot) of the packed weights); three k-blocks per
           // (tap, channel block): a_hi*w_hi, a_lo*w_hi, a_hi*w_lo (lo*lo is below fp32 resolution)
@@ -150,7 +151,10 @@ conv_umma_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams
 #pragma unroll
             for (int hl = 0; hl < (X2 ? 2 : 1); ++hl) {  // fp16x2: the hi tile, then the lo tile (columns + ktot)
               uint8_t* bdst = smem_b + stage * Cfg::kBBytes + hl * BLOCK_N * SW;
-              if (cl == 1)
+              if (cl == 1 && p.b_tiled)  // KT layout (conv_umma.cuh): one contiguous run of 512-byte rows
+                tma_load_2d(bdst, &maps.b, &full_bar[stage], 0,
+                            (((hl * p.kb_total + (b_col >> 6)) * p.Cout) + n_tile * BLOCK_N) >> 2);
+              else if (cl == 1)
                 tma_load_2d(bdst, &maps.b, &full_bar[stage], b_col + hl * p.ktot, n_tile * BLOCK_N);
               else
                 tma_load_2d_mcast(bdst + crank * slice_rows * SW, &maps.b, &full_bar[stage], b_col + hl * p.ktot,
@@ -167,6 +171,7 @@ conv_umma_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams
         }
       }
       // fused 1x1/2 projection of the block input: extra k-blocks whose A tile is the (2 ho, 2 wo) pixel of ds_in
+      kcol = p.ntaps * p.cin;  // the projection's columns follow the R*S*Cin columns of the conv
       for (int cb = 0; cb < p.ds_cblocks; ++cb, kcol += Cfg::kBlockK) {
         if ((g++ & 1u) == static_cast<uint32_t>(pi)) {
           mbar_wait(&empty_bar[stage], phase ^ 1u);
@@ -176,7 +181,10 @@ conv_umma_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams
 #pragma unroll
             for (int hl = 0; hl < (X2 ? 2 : 1); ++hl) {
               uint8_t* bdst = smem_b + stage * Cfg::kBBytes + hl * BLOCK_N * SW;
-              if (cl == 1)
+              if (cl == 1 && p.b_tiled)
+                tma_load_2d(bdst, &maps.b, &full_bar[stage], 0,
+                            (((hl * p.kb_total + (kcol >> 6)) * p.Cout) + n_tile * BLOCK_N) >> 2);
+              else if (cl == 1)
                 tma_load_2d(bdst, &maps.b, &full_bar[stage], kcol + hl * p.ktot, n_tile * BLOCK_N);
               else
                 tma_load_2d_mcast(bdst + crank * slice_rows * SW, &maps.b, &full_bar[stage], kcol + hl * p.ktot,
@@ -454,7 +462,7 @@ static int max_active_clusters(int block_n, int cl) {
 int build_umma_conv(UmmaConvLaunch* L, const void* in, int B, int Hin, int Win, int Cin,
                     const void* wpacked, const float* bias, const void* residual, void* out, int Cout,
                     int R, int stride, int pad, int relu, int block_n, int cluster, int split, const void* ds_in,
-                    int ds_Hin, int ds_Win, int ds_Cin, double* stats) {
+                    int ds_Hin, int ds_Win, int ds_Cin, double* stats, int b_tiled) {
   PB_CHECK(stride == 1 || stride == 2, "umma conv: stride %d unsupported", stride);
   PB_CHECK(Cin % 64 == 0, "umma conv: Cin %d not a multiple of 64", Cin);
   PB_CHECK(block_n == 64 || block_n == 128 || block_n == 256, "umma conv: block_n %d", block_n);
@@ -604,8 +612,20 @@ int build_umma_conv(UmmaConvLaunch* L, const void* in, int B, int Hin, int Win, 
     const uint64_t str[3] = {2 * dC * e, 2 * (uint64_t)ds_Win * dC * e, (uint64_t)ds_Hin * ds_Win * dC * e};
     if (int rc = encode_tma_bf16(&L->maps.ds, ds_in, 4, dims, str, box, 128)) return rc;
   }
-  return encode_weight_map(&L->maps.b, wpacked, Cout, (R * R * Cin + (ds_in != nullptr ? ds_Cin : 0)) * (split ? 2 : 1),
-                           block_n / p.cl, 128);
+  const int Krow = R * R * Cin + (ds_in != nullptr ? ds_Cin : 0);
+  p.b_tiled = b_tiled ? 1 : 0;
+  p.kb_total = Krow / 64;
+  if (b_tiled) {
+    PB_CHECK(split != 1 && (L->pair || p.cl == 1), "umma conv: KT-layout weights need the single-CTA or the pair kernel");
+    // the packed buffer as 512-byte rows; a CTA's tile of one k-block = (rows held by the CTA) / 4 consecutive rows
+    const int rows_cta = block_n / p.cl;
+    const uint64_t total = static_cast<uint64_t>(split == 2 ? 2 : 1) * p.kb_total * Cout * 128;
+    const uint64_t dims[2] = {256, total / 512};
+    const uint64_t strides[1] = {512};
+    const uint32_t box[2] = {256u, static_cast<uint32_t>(rows_cta / 4)};
+    return encode_tma_bf16(&L->maps.b, wpacked, 2, dims, strides, box, 0);
+  }
+  return encode_weight_map(&L->maps.b, wpacked, Cout, Krow * (split ? 2 : 1), block_n / p.cl, 128);
 }
 
 int build_umma_dgrad_s2(UmmaConvLaunch* L, const void* dz, int B, int Ho, int Wo, int Cout_f, const void* w_dgrad,

@@ -36,6 +36,14 @@ struct UmmaConvParams {
   int up2, up_ph, up_pw, up_lh, up_lw;  // up_lh / up_lw = log2(Ho), log2(Wo)
   int ds_cblocks;  // fused downsample: extra 64-channel k-blocks read through maps.ds after the R*S taps (0 = none)
   int a_stages;    // resident-weights pair kernel (UmmaConvLaunch::resb): activation ring stages (2..8)
+  // k-block-tiled weights ("KT" layout, b_tiled = 1): the packed weights are stored as the shared-memory images the
+  // kernels consume -- for every (hi/lo half, k-block) a [Cout][128 B] slab whose 16-byte chunks are already XOR-swizzled
+  // (chunk ^ (row % 8), the SWIZZLE_128B pattern) -- so a CTA's weight tile of a k-block is ONE contiguous run that TMA
+  // moves as a few 512-byte rows (no-swizzle map) instead of one 128-byte row per output channel: the TMA-im2col layers
+  // were bound by the TMA engine's row rate (rows per k-block x ~2.3 cycles: 192 rows = 452 cycles on layer2 for 256
+  // cycles of MMAs), and the weight rows were a third to a half of them.
+  int b_tiled;
+  int kb_total;    // k-blocks per weight row half (= K / 64), KT layout
   int relu;
   const float* bias;            // [Cout] (folded BN shift)
   const void* residual;         // bf16 [M_total][Cout] or null
@@ -66,7 +74,13 @@ int build_umma_conv(UmmaConvLaunch* L, const void* in, int B, int Hin, int Win, 
                     // fused 1x1 stride-2 projection (resnet.py:240-243) of `ds_in` [B][ds_Hin][ds_Win][ds_Cin] accumulated into
                     // the same tile: the packed weight rows carry ds_Cin extra columns after R*R*Cin (K-extension)
                     const void* ds_in = nullptr, int ds_Hin = 0, int ds_Win = 0, int ds_Cin = 0,
-                    double* stats = nullptr /* fused batch statistics of the output (non-split) */);
+                    double* stats = nullptr /* fused batch statistics of the output (non-split) */,
+                    int b_tiled = 0 /* wpacked is in the KT layout (umma_pack_kt_offset); single-CTA and pair kernels only */);
+// byte offset of weight element (half hl, output channel n, k) in the KT layout; Krow = K per half (multiple of 64)
+inline size_t umma_pack_kt_offset(int hl, int n, int k, int Cout, int Krow) {
+  const size_t kb = static_cast<size_t>(k) / 64, kk = static_cast<size_t>(k) % 64;
+  return ((static_cast<size_t>(hl) * (Krow / 64) + kb) * Cout + n) * 128 + (((kk / 8) ^ (static_cast<size_t>(n) % 8)) * 16) + (kk % 8) * 2;
+}
 // One output parity (ph, pw) of the data gradient of a stride-2 R x R (R = 3 pad 1, or R = 1 pad 0) convolution:
 // dx[2a+ph, 2b+pw] (+= residual there) = sum over the forward taps (r, s) of that parity of dz[a+di, b+dj] . w[r][s]^T.
 // dz: bf16 [B][Ho][Wo][Cout_f]; w_dgrad: the data-gradient operand [Cin_f][(R-1-r, R-1-s), Cout_f] (pack mode 1);
@@ -80,5 +94,19 @@ int umma_pair_init();
 int umma_pair_max_pairs(int block_n, int x2 = 0);
 int launch_umma_pair(const UmmaConvLaunch& L, cudaStream_t st);
 int umma_conv_init();  // sets the dynamic shared-memory attributes once per process
+
+// conv_halo.cu: 3x3/1 conv with Cout = 128 whose KT-layout weights stay resident in a CTA pair's shared memory and whose
+// activations arrive as ONE halo patch per tile and 64-channel block (layer2).  in / out / residual: NHWC bf16;
+// wpacked_kt: KT layout (umma_pack_kt_offset) incl. the fused projection's columns; ds_in: [B][2H][2W][ds_Cin] or null.
+struct HaloLaunch {
+  UmmaConvMaps maps;
+  alignas(8) unsigned char params[160];
+  int grid, smem;
+  double flops;
+};
+bool conv_halo_supported(int B, int H, int W, int Cin, int Cout, int R, int stride, int pad, int ds_Cin);
+int build_conv_halo(HaloLaunch* L, const void* in, int B, int H, int W, int Cin, const void* wpacked_kt, const float* bias,
+                    const void* residual, void* out, int Cout, int relu, const void* ds_in, int ds_Cin);
+int launch_conv_halo(const HaloLaunch& L, cudaStream_t st);
 
 }  // namespace pb200

@@ -112,7 +112,8 @@ conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParam
         const uint32_t lres = mapa_u32(&resb_bar, 0);
         mbar_expect_tx_cluster(lres, static_cast<uint32_t>(p.num_kblocks) * Cfg::kBHalf);
         for (int kb = 0; kb < p.num_kblocks; ++kb)
-          tma_load_2d_2sm(smem_b + kb * Cfg::kBHalf, &maps.b, lres, kb * 64, crank * (BLOCK_N / 2));
+          if (p.b_tiled) tma_load_2d_2sm(smem_b + kb * Cfg::kBHalf, &maps.b, lres, 0, (kb * p.Cout + crank * (BLOCK_N / 2)) >> 2);
+          else tma_load_2d_2sm(smem_b + kb * Cfg::kBHalf, &maps.b, lres, kb * 64, crank * (BLOCK_N / 2));
       }
       __syncwarp();
     }
@@ -130,13 +131,15 @@ conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParam
       }
       // the issue loop is kept as light as possible: one warp must feed a k-block every 256-512 MMA cycles
       const int n_row = n_tile * BLOCK_N + crank * (BLOCK_N / 2);
+      // K order: 64-channel block outermost, filter taps inside (the same order csrc/conv_halo.cu walks its patches in, so
+      // that a frame's result does not depend on which of the two kernels its batch size selects)
       int kcol = 0;
-      for (int tap = 0; tap < p.ntaps; ++tap) {
-        const int dw = p.tap_dw[tap];
-        const CUtensorMap* amap = &maps.a[p.tap_mi[tap]];
-        const int hrow = ho0 + p.tap_dh[tap];
-        kcol = p.tap_k[tap];
-        for (int cb = 0; cb < p.cblocks; ++cb, kcol += 64) {
+      for (int cb = 0; cb < p.cblocks; ++cb) {
+        for (int tap = 0; tap < p.ntaps; ++tap) {
+          const int dw = p.tap_dw[tap];
+          const CUtensorMap* amap = &maps.a[p.tap_mi[tap]];
+          const int hrow = ho0 + p.tap_dh[tap];
+          kcol = p.tap_k[tap] + cb * 64;
           if ((g++ & 1u) == static_cast<uint32_t>(pi)) {
           mbar_wait(&empty_bar[stage], phase ^ 1u);
           if (elect_one()) {
@@ -144,8 +147,14 @@ conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParam
             mbar_expect_tx_cluster(lfull, Cfg::kABytes + stage_b);
             tma_load_4d_2sm(smem_a + stage * Cfg::kABytes, amap, lfull, cb * 64, dw, hrow, n0);
             if (!RESB) {
-              tma_load_2d_2sm(smem_b + stage * Cfg::kBBytes, &maps.b, lfull, kcol, n_row);
-              if (X2) tma_load_2d_2sm(smem_b + stage * Cfg::kBBytes + Cfg::kBHalf, &maps.b, lfull, kcol + p.ktot, n_row);
+              if (p.b_tiled) {  // KT layout: this CTA's rows of k-block kcol/64 are one contiguous run of 512-byte rows
+                const int row = ((kcol >> 6) * p.Cout + n_row) >> 2;
+                tma_load_2d_2sm(smem_b + stage * Cfg::kBBytes, &maps.b, lfull, 0, row);
+                if (X2) tma_load_2d_2sm(smem_b + stage * Cfg::kBBytes + Cfg::kBHalf, &maps.b, lfull, 0, row + ((p.kb_total * p.Cout) >> 2));
+              } else {
+                tma_load_2d_2sm(smem_b + stage * Cfg::kBBytes, &maps.b, lfull, kcol, n_row);
+                if (X2) tma_load_2d_2sm(smem_b + stage * Cfg::kBBytes + Cfg::kBHalf, &maps.b, lfull, kcol + p.ktot, n_row);
+              }
             }
           }
           __syncwarp();
@@ -157,6 +166,7 @@ conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParam
         }
       }
       // fused 1x1/2 projection of the block input: extra k-blocks whose A tile is the (2 ho, 2 wo) pixel of ds_in
+      kcol = p.ntaps * p.cin;  // the projection's columns follow the R*S*Cin columns of the conv
       for (int cb = 0; cb < p.ds_cblocks; ++cb, kcol += 64) {
         if ((g++ & 1u) == static_cast<uint32_t>(pi)) {
           mbar_wait(&empty_bar[stage], phase ^ 1u);
@@ -165,8 +175,14 @@ conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParam
             mbar_expect_tx_cluster(lfull, Cfg::kABytes + stage_b);
             tma_load_4d_2sm(smem_a + stage * Cfg::kABytes, &maps.ds, lfull, cb * 64, 0, ho0, n0);
             if (!RESB) {
-              tma_load_2d_2sm(smem_b + stage * Cfg::kBBytes, &maps.b, lfull, kcol, n_row);
-              if (X2) tma_load_2d_2sm(smem_b + stage * Cfg::kBBytes + Cfg::kBHalf, &maps.b, lfull, kcol + p.ktot, n_row);
+              if (p.b_tiled) {
+                const int row = ((kcol >> 6) * p.Cout + n_row) >> 2;
+                tma_load_2d_2sm(smem_b + stage * Cfg::kBBytes, &maps.b, lfull, 0, row);
+                if (X2) tma_load_2d_2sm(smem_b + stage * Cfg::kBBytes + Cfg::kBHalf, &maps.b, lfull, 0, row + ((p.kb_total * p.Cout) >> 2));
+              } else {
+                tma_load_2d_2sm(smem_b + stage * Cfg::kBBytes, &maps.b, lfull, kcol, n_row);
+                if (X2) tma_load_2d_2sm(smem_b + stage * Cfg::kBBytes + Cfg::kBHalf, &maps.b, lfull, kcol + p.ktot, n_row);
+              }
             }
           }
           __syncwarp();
@@ -197,7 +213,10 @@ conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParam
           tc_fence_after();
           if (elect_one()) {
             const uint32_t a_lo = desc_lo(smem_u32(smem_a + stage * Cfg::kABytes), 16);
-            const uint32_t b_lo = desc_lo(smem_u32(smem_b + (RESB ? kb * Cfg::kBHalf : stage * Cfg::kBBytes)), 16);
+            // RESB: the resident k-blocks sit in weight order (tap-major); the walk is channel-block-major
+            const int nreg = p.ntaps * p.cblocks;
+            const int kbw = kb < nreg ? (kb % p.ntaps) * p.cblocks + kb / p.ntaps : kb;
+            const uint32_t b_lo = desc_lo(smem_u32(smem_b + (RESB ? kbw * Cfg::kBHalf : stage * Cfg::kBBytes)), 16);
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
               umma2_bf16_split(d_tmem, a_lo + 2 * k, d_hi, b_lo + 2 * k, d_hi, idesc, (kb | k) != 0 ? 1u : 0u);

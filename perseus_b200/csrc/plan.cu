@@ -71,6 +71,8 @@ struct pb200_plan {
   void* cache_ws = nullptr;
   int cache_B = -1;
   std::vector<pb200::UmmaConvLaunch> umma;  // per conv
+  std::vector<pb200::HaloLaunch> halo;      // per conv (grid == 0: the conv does not run on conv_halo.cu)
+  bool use_halo = true;                     // bf16 mode, KT weights: layer2's stride-1 convs on the halo-patch kernel
   std::vector<std::string> op_names;
   std::vector<std::string> op_kernels;  // kernel each op launches (known after the first forward at a batch size)
   // L2 chunking of the front of the network (fused stem + the four layer1 convs, P8 layout): these five kernels move
@@ -80,6 +82,9 @@ struct pb200_plan {
   // than the HBM time it saves (stem + layer1 0.43 ms unchunked, 0.55 / 0.58 / 0.72 ms at 86 / 64 / 40 frames per
   // chunk).  OFF by default; PB200_L1_CHUNK=<frames> enables it for A/B runs.
   int l1_chunk = 0;
+  // weights of the TMA-im2col layers in the k-block-tiled "KT" layout (conv_umma.cuh): the TMA engine moves a CTA's
+  // weight tile as a few 512-byte rows instead of one 128-byte row per output channel.  PB200_NO_BTILED=1: row-major.
+  bool b_tiled = true;
   int n_front = 0;  // leading ops that are chunked (OP_STEM_POOL + OP_CONV_P8 x 4)
 };
 
@@ -245,6 +250,8 @@ static void build_graph(pb200_plan* pl) {
            (pl->ops[pl->n_front].kind == OP_STEM_POOL || pl->ops[pl->n_front].kind == OP_CONV_P8))
       ++pl->n_front;
   if (const char* e = getenv("PB200_L1_CHUNK")) pl->l1_chunk = atoi(e);
+  pl->b_tiled = (pl->bf16 || pl->f16) && getenv("PB200_NO_BTILED") == nullptr;
+  pl->use_halo = pl->b_tiled && !pl->f16 && getenv("PB200_NO_HALO") == nullptr;
   // weight arena
   size_t woff = 0;
   for (auto& c : pl->convs) {
@@ -426,12 +433,14 @@ extern "C" int pb200_plan_load_weights(pb200_plan* plan, const float* const* ten
               size_t off = (static_cast<size_t>(co) * 2 * Krow + k) * 2, lo_off = static_cast<size_t>(Krow) * 2;
               if (c.stem) { off = stem_wimg_offset(co, k); lo_off = kStemWimgBytes; }
               else if (c.p8) { off = conv_p8_wimg_offset(co, k); lo_off = 64 * 576 * 2; }
+              else if (plan->b_tiled) { off = umma_pack_kt_offset(0, co, k, c.Cout, Krow); lo_off = umma_pack_kt_offset(1, co, k, c.Cout, Krow) - off; }
               *reinterpret_cast<uint16_t*>(host.data() + c.w_off + off) = hi;
               *reinterpret_cast<uint16_t*>(host.data() + c.w_off + off + lo_off) = lo;
             } else if (plan->bf16) {
               size_t off = (static_cast<size_t>(co) * Krow + k) * 2;  // [Cout][K] K-major rows (TMA-im2col kernels)
               if (c.stem) off = stem_wimg_offset(co, k);
               else if (c.p8) off = conv_p8_wimg_offset(co, k);
+              else if (plan->b_tiled) off = umma_pack_kt_offset(0, co, k, c.Cout, Krow);
               *reinterpret_cast<uint16_t*>(host.data() + c.w_off + off) = f32_to_bf16_rne(static_cast<float>(v));
             } else {
               reinterpret_cast<float*>(host.data() + c.w_off)[static_cast<size_t>(k) * c.Cout + co] =
@@ -459,13 +468,18 @@ extern "C" int pb200_plan_load_weights(pb200_plan* plan, const float* const* ten
       bias[co] = static_cast<float>(static_cast<double>(bias[co]) + static_cast<double>(b->data[co]) -
                                     static_cast<double>(mu->data[co]) * sc);
       uint16_t* row = reinterpret_cast<uint16_t*>(host.data() + c.w_off) + static_cast<size_t>(co) * Krow * (plan->f16 ? 2 : 1) + K;
+      auto at = [&](int hl, int ci) -> uint16_t& {  // element (half, co, K + ci) of the packed weights
+        if (plan->b_tiled) return *reinterpret_cast<uint16_t*>(host.data() + c.w_off + umma_pack_kt_offset(hl, co, K + ci, c.Cout, Krow));
+        return row[hl * Krow + ci];
+      };
       for (int ci = 0; ci < d.Cin; ++ci) {
         const float wf = static_cast<float>(static_cast<double>(w->data[static_cast<size_t>(co) * d.Cin + ci]) * sc);
         if (plan->f16) {
-          row[ci] = f32_to_f16_rne(wf);
-          row[Krow + ci] = f32_to_f16_rne(wf - f16_bits_to_f32(row[ci]));
+          const uint16_t hi = f32_to_f16_rne(wf);
+          at(0, ci) = hi;
+          at(1, ci) = f32_to_f16_rne(wf - f16_bits_to_f32(hi));
         } else {
-          row[ci] = f32_to_bf16_rne(wf);
+          at(0, ci) = f32_to_bf16_rne(wf);
         }
       }
     }
@@ -556,6 +570,7 @@ static int prepare(pb200_plan* pl, const void* frames, void* ws, int B) {
   // may alternate frames buffers (ingest of batch i+1 under the forward of batch i) without re-encoding anything
   if (pl->cache_ws == ws && pl->cache_B == B) return PB200_OK;
   pl->umma.assign(pl->convs.size(), UmmaConvLaunch());
+  pl->halo.assign(pl->convs.size(), HaloLaunch());
   for (const auto& op : pl->ops) {
     if (op.kind != OP_CONV) continue;
     const ConvSpec& c = pl->convs[op.conv];
@@ -567,12 +582,22 @@ static int prepare(pb200_plan* pl, const void* frames, void* ws, int B) {
     const float* bias = reinterpret_cast<const float*>(pl->arena + c.b_off);
     const void* ds_in = op.ds_buf >= 0 ? buf_ptr(pl, frames, ws, op.ds_buf) : nullptr;
     const ConvSpec* d = c.ds_conv >= 0 ? &pl->convs[c.ds_conv] : nullptr;
+    if (pl->use_halo && conv_halo_supported(B, c.Hin, c.Win, c.Cin, c.Cout, c.R, c.stride, c.pad, d ? d->Cin : 0)) {
+      int rc = build_conv_halo(&pl->halo[op.conv], in, B, c.Hin, c.Win, c.Cin, pl->arena + c.w_off, bias, res, out, c.Cout,
+                               op.relu, d ? ds_in : nullptr, d ? d->Cin : 0);
+      if (rc) {
+        pl->cache_B = -1;
+        return rc;
+      }
+      continue;
+    }
     int bn = 64, cluster = 0;
     choose_tile(c, B, pl->f16, &bn, &cluster);
     if (pl->split) cluster = 1;  // the split-bf16 mode runs on the single-CTA kernel
     int rc = build_umma_conv(L, in, B, c.Hin, c.Win, c.Cin, pl->arena + c.w_off, bias, res, out, c.Cout,
                              c.R, c.stride, c.pad, op.relu, bn, cluster, pl->split ? 1 : (pl->f16 ? 2 : 0),
-                             d != nullptr ? ds_in : nullptr, d ? d->Hin : 0, d ? d->Win : 0, d ? d->Cin : 0);
+                             d != nullptr ? ds_in : nullptr, d ? d->Hin : 0, d ? d->Win : 0, d ? d->Cin : 0, nullptr,
+                             (pl->b_tiled && !pl->split) ? 1 : 0);
     if (rc) {
       pl->cache_B = -1;
       return rc;
@@ -589,6 +614,7 @@ static int run_op(pb200_plan* pl, const Op& op, const void* frames, void* ws, fl
   switch (op.kind) {
     case OP_CONV: {
       const ConvSpec& c = pl->convs[op.conv];
+      if (pl->bf16 && !c.stem && pl->halo[op.conv].grid > 0) return launch_conv_halo(pl->halo[op.conv], st);
       if (pl->bf16 || (pl->split && !c.stem)) return launch_umma_conv(pl->umma[op.conv], st);
       SimtConv s;
       s.in = reinterpret_cast<const float*>(buf_ptr(pl, frames, ws, op.in_buf));
@@ -706,6 +732,7 @@ extern "C" const char* pb200_plan_op_kernel(const pb200_plan* plan, int i) {
       if (!plan->bf16 && !(plan->split && !plan->convs[op.conv].stem))
         k = (plan->convs[op.conv].stem && plan->H % 16 == 0 && plan->W % 64 == 0) ? "stem_f32_kernel" : "conv_simt_kernel";
       else if (plan->cache_B < 0 || plan->umma.size() != plan->convs.size()) k = "conv_umma*";
+      else if (plan->halo.size() == plan->convs.size() && plan->halo[op.conv].grid > 0) k = "conv_halo_kernel";
       else {
         const UmmaConvLaunch& L = plan->umma[op.conv];
         k = std::string(L.pair ? "conv_umma2_kernel<" : "conv_umma_kernel<") + std::to_string(L.block_n) + (L.split == 1 ? ",split>" : (L.split == 2 ? ",x2>" : (L.resb ? ",resB>" : ">")));
@@ -842,6 +869,14 @@ extern "C" int pb200_ingest(const pb200_plan* plan, const uint8_t* rgb, int rgb_
   return launch_ingest(a, out_frames, frame_elt(plan), static_cast<cudaStream_t>(stream));
 }
 
+// the single-layer test entries pack their weights in the KT layout unless a multicast cluster is forced (those CTAs hold
+// row slices of ONE tile and keep the row-major tensor map) or PB200_NO_BTILED asks for the row-major path
+static bool debug_b_tiled() {
+  if (getenv("PB200_NO_BTILED")) return false;
+  const char* f = getenv("PB200_FORCE_CLUSTER");
+  return !(f != nullptr && f[1] == 0 && (f[0] == '2' || f[0] == '4'));
+}
+
 extern "C" int pb200_debug_conv_bf16(const void* in_nhwc, int B, int H, int W, int Cin,
                                      const float* w_oihw_host, const float* bias_host, int Cout, int R,
                                      int stride, int pad, const void* residual_nhwc_or_null, int relu,
@@ -850,13 +885,16 @@ extern "C" int pb200_debug_conv_bf16(const void* in_nhwc, int B, int H, int W, i
   if (int rc = umma_conv_init()) return rc;
   PB_CHECK(in_nhwc && w_oihw_host && bias_host && out_nhwc, "debug_conv: null argument");
   const size_t K = static_cast<size_t>(R) * R * Cin;
+  const bool tiled = debug_b_tiled() && K % 64 == 0;
   std::vector<uint16_t> wp(K * Cout);
   for (int co = 0; co < Cout; ++co)
     for (int ci = 0; ci < Cin; ++ci)
       for (int r = 0; r < R; ++r)
-        for (int s = 0; s < R; ++s)
-          wp[co * K + (static_cast<size_t>(r) * R + s) * Cin + ci] =
+        for (int s = 0; s < R; ++s) {
+          const size_t k = (static_cast<size_t>(r) * R + s) * Cin + ci;
+          wp[tiled ? umma_pack_kt_offset(0, co, static_cast<int>(k), Cout, static_cast<int>(K)) / 2 : co * K + k] =
               f32_to_bf16_rne(w_oihw_host[((static_cast<size_t>(co) * Cin + ci) * R + r) * R + s]);
+        }
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   void *dw = nullptr, *db = nullptr;
   PB_CUDA(cudaMalloc(&dw, wp.size() * 2));
@@ -869,7 +907,8 @@ extern "C" int pb200_debug_conv_bf16(const void* in_nhwc, int B, int H, int W, i
   if (rc == PB200_OK) {
     int bn = Cout < 256 ? Cout : 256;
     rc = build_umma_conv(&L, in_nhwc, B, H, W, Cin, dw, static_cast<const float*>(db),
-                         residual_nhwc_or_null, out_nhwc, Cout, R, stride, pad, relu, bn);
+                         residual_nhwc_or_null, out_nhwc, Cout, R, stride, pad, relu, bn, 0, 0, nullptr, 0, 0, 0, nullptr,
+                         tiled ? 1 : 0);
   }
   if (rc == PB200_OK) rc = launch_umma_conv(L, st);
   cudaError_t e = cudaStreamSynchronize(st);
@@ -888,13 +927,17 @@ extern "C" int pb200_debug_conv_ds_bf16(const void* in_nhwc, int B, int H, int W
   const int R = 3;
   const size_t K = static_cast<size_t>(R) * R * Cin, Krow = K + ds_Cin;  // K-extension: [taps x Cin | ds_Cin]
   std::vector<uint16_t> wp(Krow * Cout);
+  const bool tiled = debug_b_tiled();
+  auto at = [&](int co, size_t k) -> uint16_t& {
+    return wp[tiled ? umma_pack_kt_offset(0, co, static_cast<int>(k), Cout, static_cast<int>(Krow)) / 2 : co * Krow + k];
+  };
   for (int co = 0; co < Cout; ++co) {
     for (int ci = 0; ci < Cin; ++ci)
       for (int r = 0; r < R; ++r)
         for (int s = 0; s < R; ++s)
-          wp[co * Krow + (static_cast<size_t>(r) * R + s) * Cin + ci] =
+          at(co, (static_cast<size_t>(r) * R + s) * Cin + ci) =
               f32_to_bf16_rne(w_oihw_host[((static_cast<size_t>(co) * Cin + ci) * R + r) * R + s]);
-    for (int ci = 0; ci < ds_Cin; ++ci) wp[co * Krow + K + ci] = f32_to_bf16_rne(wds_oi_host[static_cast<size_t>(co) * ds_Cin + ci]);
+    for (int ci = 0; ci < ds_Cin; ++ci) at(co, K + ci) = f32_to_bf16_rne(wds_oi_host[static_cast<size_t>(co) * ds_Cin + ci]);
   }
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   void *dw = nullptr, *db = nullptr;
@@ -908,7 +951,7 @@ extern "C" int pb200_debug_conv_ds_bf16(const void* in_nhwc, int B, int H, int W
   if (rc == PB200_OK) {
     int bn = Cout < 256 ? Cout : 256;
     rc = build_umma_conv(&L, in_nhwc, B, H, W, Cin, dw, static_cast<const float*>(db), nullptr, out_nhwc, Cout, R, 1, 1,
-                         relu, bn, 0, 0, ds_in_nhwc, 2 * H, 2 * W, ds_Cin);
+                         relu, bn, 0, 0, ds_in_nhwc, 2 * H, 2 * W, ds_Cin, nullptr, tiled ? 1 : 0);
   }
   if (rc == PB200_OK) rc = launch_umma_conv(L, st);
   cudaError_t e = cudaStreamSynchronize(st);
@@ -970,6 +1013,46 @@ extern "C" int pb200_debug_stem_pool(pb200_plan* plan, const void* frames, void*
                           out_p8, B, plan->H, plan->W, static_cast<cudaStream_t>(stream), plan->f16 ? 1 : 0);
 }
 
+extern "C" int pb200_debug_conv_halo(const void* in_nhwc, int B, int H, int W, int Cin, const float* w_oihw_host,
+                                     const float* bias_host, int Cout, const void* residual_nhwc_or_null, int relu,
+                                     void* out_nhwc, const void* ds_in_nhwc_or_null, int ds_Cin,
+                                     const float* wds_oi_host_or_null, pb200_stream stream) {
+  if (int rc = require_device()) return rc;
+  PB_CHECK(in_nhwc && w_oihw_host && bias_host && out_nhwc, "debug_conv_halo: null argument");
+  const bool ds = ds_in_nhwc_or_null != nullptr;
+  PB_CHECK(!ds || wds_oi_host_or_null != nullptr, "debug_conv_halo: projection weights missing");
+  PB_CHECK(conv_halo_supported(B, H, W, Cin, Cout, 3, 1, 1, ds ? ds_Cin : 0), "debug_conv_halo: unsupported shape");
+  const int K = 9 * Cin, Krow = K + (ds ? ds_Cin : 0);
+  std::vector<uint16_t> wp(static_cast<size_t>(Krow) * Cout);
+  for (int co = 0; co < Cout; ++co) {
+    for (int ci = 0; ci < Cin; ++ci)
+      for (int r = 0; r < 3; ++r)
+        for (int s = 0; s < 3; ++s)
+          wp[umma_pack_kt_offset(0, co, (r * 3 + s) * Cin + ci, Cout, Krow) / 2] =
+              f32_to_bf16_rne(w_oihw_host[((static_cast<size_t>(co) * Cin + ci) * 3 + r) * 3 + s]);
+    for (int ci = 0; ds && ci < ds_Cin; ++ci)
+      wp[umma_pack_kt_offset(0, co, K + ci, Cout, Krow) / 2] = f32_to_bf16_rne(wds_oi_host_or_null[static_cast<size_t>(co) * ds_Cin + ci]);
+  }
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  void *dw = nullptr, *db = nullptr;
+  PB_CUDA(cudaMalloc(&dw, wp.size() * 2));
+  PB_CUDA(cudaMalloc(&db, sizeof(float) * Cout));
+  int rc = PB200_OK;
+  if (cudaMemcpyAsync(dw, wp.data(), wp.size() * 2, cudaMemcpyHostToDevice, st) != cudaSuccess ||
+      cudaMemcpyAsync(db, bias_host, sizeof(float) * Cout, cudaMemcpyHostToDevice, st) != cudaSuccess)
+    rc = PB200_ERR_CUDA;
+  HaloLaunch L;
+  if (rc == PB200_OK)
+    rc = build_conv_halo(&L, in_nhwc, B, H, W, Cin, dw, static_cast<const float*>(db), residual_nhwc_or_null, out_nhwc, Cout,
+                         relu, ds_in_nhwc_or_null, ds ? ds_Cin : 0);
+  if (rc == PB200_OK) rc = launch_conv_halo(L, st);
+  cudaError_t e = cudaStreamSynchronize(st);
+  if (rc == PB200_OK && e != cudaSuccess) rc = cuda_fail(e, "debug_conv_halo sync", __FILE__, __LINE__);
+  cudaFree(dw);
+  cudaFree(db);
+  return rc;
+}
+
 extern "C" int pb200_debug_conv_f16x2(const void* in_nhwc, int B, int H, int W, int Cin, const float* w_oihw_host,
                                       const float* bias_host, int Cout, int R, int stride, int pad,
                                       const void* residual_nhwc_or_null, int relu, void* out_nhwc,
@@ -981,11 +1064,18 @@ extern "C" int pb200_debug_conv_f16x2(const void* in_nhwc, int B, int H, int W, 
   const bool ds = ds_in_nhwc_or_null != nullptr;
   PB_CHECK(!ds || (wds_oi_host_or_null != nullptr && R == 3 && stride == 1 && pad == 1), "debug_conv_f16x2: bad projection");
   const size_t K = static_cast<size_t>(R) * R * Cin, Krow = K + (ds ? ds_Cin : 0);
-  std::vector<uint16_t> wp(2 * Krow * Cout);  // [Cout][hi Krow | lo Krow]
+  std::vector<uint16_t> wp(2 * Krow * Cout);  // [Cout][hi Krow | lo Krow], or the KT layout (hi slabs, then lo slabs)
+  const bool tiled = debug_b_tiled();
   auto put = [&](int co, size_t k, float wf) {
     const uint16_t hi = f32_to_f16_rne(wf);
-    wp[co * 2 * Krow + k] = hi;
-    wp[co * 2 * Krow + Krow + k] = f32_to_f16_rne(wf - f16_bits_to_f32(hi));
+    const uint16_t lo = f32_to_f16_rne(wf - f16_bits_to_f32(hi));
+    if (tiled) {
+      wp[umma_pack_kt_offset(0, co, static_cast<int>(k), Cout, static_cast<int>(Krow)) / 2] = hi;
+      wp[umma_pack_kt_offset(1, co, static_cast<int>(k), Cout, static_cast<int>(Krow)) / 2] = lo;
+    } else {
+      wp[co * 2 * Krow + k] = hi;
+      wp[co * 2 * Krow + Krow + k] = lo;
+    }
   };
   for (int co = 0; co < Cout; ++co) {
     for (int ci = 0; ci < Cin; ++ci)
@@ -1009,7 +1099,7 @@ extern "C" int pb200_debug_conv_f16x2(const void* in_nhwc, int B, int H, int W, 
     if (fbn != nullptr && atoi(fbn) > 0 && Cout % atoi(fbn) == 0) bn = atoi(fbn);
     rc = build_umma_conv(&L, in_nhwc, B, H, W, Cin, dw, static_cast<const float*>(db), residual_nhwc_or_null, out_nhwc,
                          Cout, R, stride, pad, relu, bn, 0, 2, ds_in_nhwc_or_null, ds ? 2 * H : 0, ds ? 2 * W : 0,
-                         ds ? ds_Cin : 0);
+                         ds ? ds_Cin : 0, nullptr, tiled ? 1 : 0);
   }
   if (rc == PB200_OK) rc = launch_umma_conv(L, st);
   cudaError_t e = cudaStreamSynchronize(st);

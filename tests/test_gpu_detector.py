@@ -534,3 +534,60 @@ def test_pair_conv_resident_weights_variant(case, monkeypatch):
     test_umma_conv_layer_vs_exact_operand_reference(case, "p", monkeypatch)
     if case is CONV_CASES[4]:
         test_umma_conv_with_fused_projection_vs_exact_operand_reference(DS_CASES[0], "p", monkeypatch)
+
+
+HALO_CASES = [
+    # (B, H, W, Cin, residual, relu, ds_Cin)
+    (2, 32, 32, 128, True, True, 0),     # layer2.1.conv2
+    (4, 32, 32, 128, False, True, 0),    # layer2.1.conv1
+    (3, 32, 32, 128, False, True, 64),   # layer2.0.conv2 + fused projection, odd batch (the pair's second image is missing)
+    (2, 64, 64, 64, True, False, 0),     # a different width: 33 tiles per image, patch rows of 66 pixels
+]
+
+
+@pytest.mark.parametrize("case", HALO_CASES, ids=[str(c) for c in HALO_CASES])
+def test_conv_halo_vs_exact_operand_reference(case):
+    """csrc/conv_halo.cu (halo patch + resident KT weights, CTA pairs over image pairs) vs F.conv2d in fp64 on the same bf16
+    operands; every output pixel must be written (NaN-initialised output) and nothing outside the tensor."""
+    from perseus_b200 import _lib
+
+    B, H, W, Cin, use_res, relu, Cds = case
+    Cout = 128
+    g = torch.Generator().manual_seed(sum(case) + 3)
+    x = torch.randn(B, H, W, Cin, generator=g).bfloat16()
+    w = (torch.randn(Cout, Cin, 3, 3, generator=g) / (9 * Cin) ** 0.5).bfloat16().float()
+    bias = torch.randn(Cout, generator=g)
+    res = torch.randn(B, H, W, Cout, generator=g).bfloat16() if use_res else None
+    want = torch.nn.functional.conv2d(x.double().permute(0, 3, 1, 2), w.double(), bias.double(), 1, 1)
+    xds = wds = None
+    if Cds:
+        xds = torch.randn(B, 2 * H, 2 * W, Cds, generator=g).bfloat16()
+        wds = (torch.randn(Cout, Cds, generator=g) / Cds ** 0.5).bfloat16().float()
+        want = want + torch.nn.functional.conv2d(xds.double().permute(0, 3, 1, 2), wds.double()[:, :, None, None], None, 2, 0)
+    want = want.permute(0, 2, 3, 1)
+    if use_res:
+        want = want + res.double()
+    if relu:
+        want = want.relu()
+    guard = 4096
+    buf = torch.full((B * H * W * Cout + 2 * guard,), float("nan"), dtype=torch.bfloat16, device="cuda")
+    outd = buf[guard:-guard].view(B, H, W, Cout)
+    xd = x.cuda()
+    resd = res.cuda() if use_res else None
+    xdsd = xds.cuda() if Cds else None
+    wc, bc = w.contiguous(), bias.contiguous()
+    wdsc = wds.contiguous() if Cds else None
+    _lib.check(_lib.lib().pb200_debug_conv_halo(
+        xd.data_ptr(), B, H, W, Cin, wc.data_ptr(), bc.data_ptr(), Cout, None if resd is None else resd.data_ptr(), int(relu),
+        outd.data_ptr(), None if xdsd is None else xdsd.data_ptr(), Cds, None if wdsc is None else wdsc.data_ptr(),
+        _lib.current_stream_ptr()))
+    torch.cuda.synchronize()
+    assert torch.isnan(buf[:guard]).all() and torch.isnan(buf[-guard:]).all(), "wrote outside the output tensor"
+    # widths whose 128-position tile would need more than the 7-row halo box are refused, not mis-computed
+    assert _lib.lib().pb200_debug_conv_halo(xd.data_ptr(), B, 16, 16, Cin, wc.data_ptr(), bc.data_ptr(), Cout, None, 1,
+                                            outd.data_ptr(), None, 0, None, _lib.current_stream_ptr()) == 1
+    got = outd.double().cpu()
+    assert torch.isfinite(got).all(), "unwritten (NaN) outputs"
+    err = (got - want).abs()
+    bad = err > 2.0 ** -7 * want.abs() + 1e-2
+    assert not bad.any(), f"{int(bad.sum())} / {bad.numel()} outputs off; max err {float(err.max()):.4f}; first bad idx {bad.nonzero()[:4].tolist()}"
