@@ -293,9 +293,10 @@ __device__ __forceinline__ void stem_pool_body(const StemPoolParams& p) {
           part[j] = __shfl_xor_sync(0xffffffffu, send, 1);
           mine[j] = odd ? v[kHW + j] : v[j];
         }
-        // only the four lane-quarter warps of one channel group exchange boundary columns: a 128-thread barrier per channel
-        // group instead of one over all epilogue warps (the groups run ahead of each other by up to an accumulator stage)
-        named_bar_sync(1 + cq, 128);
+        // one barrier over ALL epilogue warps, although only the four lane-quarter warps of a channel group exchange
+        // columns: per-group 128-thread barriers measured 13 % SLOWER (0.1265 vs 0.1118 ms, r02) -- the groups drift apart and
+        // the accumulator stage is released by the slowest one
+        named_bar_sync(1, 32 * kEpiWarps);
         uint32_t edge[kHW];
 #pragma unroll
         for (int j = 0; j < kHW; ++j) edge[j] = 0u;  // column -1 is the pool's padding (values are >= 0)
