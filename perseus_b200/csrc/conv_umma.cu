@@ -459,6 +459,41 @@ static int max_active_clusters(int block_n, int cl) {
   return cache[dev][bi][cl];
 }
 
+// Tile choice of a TMA-im2col conv: BLOCK_N in {64, 128, 256} x {single CTA, CTA pair}.  Cost model (cycles per 64-deep
+// k-block and per CTA, measured with tools/mma_bench.cu and the r01/r02 per-op profiles): persistent CTAs take
+// ceil(items / units) equal work items; a k-block costs max(MMA issue time, shared-memory traffic / bandwidth), where
+//   MMA     = 4 K-steps x passes x max(48, N/2) cycles (an M128 x N x K16 MMA; passes = 2 in the fp16x2 mode),
+//   traffic = what the MMAs READ from shared memory (4 x passes x (4 KB of A + 32 B per weight row held by this CTA))
+//             + what TMA WRITES into it (16 KB of A + 128 B per weight row and pass),
+// at 128 B/clk x 0.85.  A pair holds half of the weight rows per CTA, which is what makes the wide tiles pay: the r01
+// choice (pair<128> for layer3, single<256> for layer4) sat at 452 / 903 cycles per k-block where pair<256> needs 602
+// for twice / the same the work (measured 473 / 810).  cluster: 1 = single CTA, -2 = CTA pair.
+void umma_choose_tile(long long m_tiles, int Cout, int passes, int* block_n, int* cluster) {
+  double best_cost = -1.0;
+  *block_n = 64;
+  *cluster = 1;
+  for (int bn = 64; bn <= 256 && bn <= Cout; bn *= 2) {
+    if (Cout % bn) continue;
+    for (int pair = 0; pair < 2; ++pair) {
+      if (pair && m_tiles < 2) continue;
+      const long long n_tiles = Cout / bn;
+      const long long items = (pair ? (m_tiles + 1) / 2 : m_tiles) * n_tiles;
+      const long long units = pair ? num_sms() / 2 : num_sms();
+      const long long rounds = (items + units - 1) / units;
+      const int brows = pair ? bn / 2 : bn;
+      const double mma = 4.0 * passes * (bn / 2 < 48 ? 48 : bn / 2);
+      const double smem = 4.0 * passes * (4096 + brows * 32) + 16384 + passes * brows * 128.0;
+      const double t = mma > smem / (128.0 * 0.85) ? mma : smem / (128.0 * 0.85);
+      const double cost = static_cast<double>(rounds) * t;
+      if (best_cost < 0 || cost < best_cost * 0.999) {
+        best_cost = cost;
+        *block_n = bn;
+        *cluster = pair ? -2 : 1;
+      }
+    }
+  }
+}
+
 int build_umma_conv(UmmaConvLaunch* L, const void* in, int B, int Hin, int Win, int Cin,
                     const void* wpacked, const float* bias, const void* residual, void* out, int Cout,
                     int R, int stride, int pad, int relu, int block_n, int cluster, int split, const void* ds_in,

@@ -88,6 +88,8 @@ inline size_t umma_pack_kt_offset(int hl, int n, int k, int Cout, int Krow) {
 int build_umma_dgrad_s2(UmmaConvLaunch* L, const void* dz, int B, int Ho, int Wo, int Cout_f, const void* w_dgrad,
                         const float* zero_bias, const void* residual_or_null, void* dx, int Cin_f, int R, int ph, int pw,
                         int block_n);
+// BLOCK_N and {single CTA (1), CTA pair (-2)} for m_tiles x Cout outputs by the shared-memory-traffic cost model (passes = 2: fp16x2)
+void umma_choose_tile(long long m_tiles, int Cout, int passes, int* block_n, int* cluster);
 int launch_umma_conv(const UmmaConvLaunch& L, cudaStream_t st);  // dispatches on L.pair
 // conv_umma2.cu
 int umma_pair_init();

@@ -514,41 +514,9 @@ static inline uint8_t* buf_ptr(const pb200_plan* pl, const void* frames, void* w
   return static_cast<uint8_t*>(ws) + pl->buf_off[id] + (id >= BUF_P8A ? 0 : static_cast<size_t>(n0) * pl->buf_per_frame[id]);
 }
 
-// Tile choice of a TMA-im2col conv: BLOCK_N in {64, 128, 256} x {single CTA, CTA pair}.  Cost model (cycles per 64-deep
-// k-block and per CTA, measured with tools/mma_bench.cu and the r01/r02 per-op profiles): persistent CTAs take
-// ceil(items / units) equal work items; a k-block costs max(MMA issue time, shared-memory traffic / bandwidth), where
-//   MMA     = 4 K-steps x passes x max(48, N/2) cycles (an M128 x N x K16 MMA; passes = 2 in the fp16x2 mode),
-//   traffic = what the MMAs READ from shared memory (4 x passes x (4 KB of A + 32 B per weight row held by this CTA))
-//             + what TMA WRITES into it (16 KB of A + 128 B per weight row and pass),
-// at 128 B/clk x 0.85.  A pair holds half of the weight rows per CTA, which is what makes the wide tiles pay: the r01
-// choice (pair<128> for layer3, single<256> for layer4) sat at 452 / 903 cycles per k-block where pair<256> needs 602
-// for twice / the same the work (measured 473 / 810).
 static void choose_tile(const ConvSpec& c, int B, bool f16, int* block_n, int* cluster) {
   const long long m_tiles = (static_cast<long long>(B) * c.Ho * c.Wo + 127) / 128;
-  const int passes = f16 ? 2 : 1;
-  double best_cost = -1.0;
-  *block_n = 64;
-  *cluster = 1;
-  for (int bn = 64; bn <= 256 && bn <= c.Cout; bn *= 2) {
-    if (c.Cout % bn) continue;
-    for (int pair = 0; pair < 2; ++pair) {
-      if (pair && m_tiles < 2) continue;
-      const long long n_tiles = c.Cout / bn;
-      const long long items = (pair ? (m_tiles + 1) / 2 : m_tiles) * n_tiles;
-      const long long units = pair ? num_sms() / 2 : num_sms();
-      const long long rounds = (items + units - 1) / units;
-      const int brows = pair ? bn / 2 : bn;
-      const double mma = 4.0 * passes * (bn / 2 < 48 ? 48 : bn / 2);
-      const double smem = 4.0 * passes * (4096 + brows * 32) + 16384 + passes * brows * 128.0;
-      const double t = mma > smem / (128.0 * 0.85) ? mma : smem / (128.0 * 0.85);
-      const double cost = static_cast<double>(rounds) * t;
-      if (best_cost < 0 || cost < best_cost * 0.999) {
-        best_cost = cost;
-        *block_n = bn;
-        *cluster = pair ? -2 : 1;
-      }
-    }
-  }
+  umma_choose_tile(m_tiles, c.Cout, f16 ? 2 : 1, block_n, cluster);  // conv_umma.cu: the shared-memory-traffic cost model
   if (const char* e = getenv("PB200_R01_TILES")) {  // A/B: the round-1 choice (rounds x MMA cycles only, pairs from 2 waves on)
     if (e[0] == '1' && !f16) {
       double bc = -1;

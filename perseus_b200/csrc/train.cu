@@ -82,25 +82,17 @@ extern "C" int pb200_train_conv(const void* in_nhwc, int B, int H, int W, int Ci
   if (int rc = umma_conv_init()) return rc;
   PB_CHECK(in_nhwc && wpacked && bias && out_nhwc, "train_conv: null argument");
   UmmaConvLaunch L;
-  int bn = Cout < 256 ? Cout : 256;
-  // same tile choice as the inference plan: rounds x MMA cost
+  // same tile choice as the inference plan (conv_umma.cu: shared-memory-traffic cost model); PB200_FORCE_CLUSTER still
+  // overrides the cluster shape in the tests
+  int bn = 64, cluster = 0;
   {
     const int Ho = (H + 2 * pad - R) / stride + 1, Wo = (W + 2 * pad - R) / stride + 1;
     const long long m_tiles = (static_cast<long long>(B) * Ho * Wo + 127) / 128;
-    long long best_cost = -1;
-    for (int c = 64; c <= 256 && c <= Cout; c *= 2) {
-      if (Cout % c) continue;
-      const long long tiles = m_tiles * (Cout / c);
-      const long long rounds = (tiles + num_sms() - 1) / num_sms();
-      const long long cost = rounds * (c / 2 < 48 ? 48 : c / 2);
-      if (best_cost < 0 || cost <= best_cost) {
-        bn = c;
-        best_cost = cost;
-      }
-    }
+    umma_choose_tile(m_tiles, Cout, 1, &bn, &cluster);
+    if (getenv("PB200_FORCE_CLUSTER") != nullptr) cluster = 0;
   }
   if (int rc = build_umma_conv(&L, in_nhwc, B, H, W, Cin, wpacked, bias, residual_or_null, out_nhwc, Cout, R, stride,
-                               pad, relu, bn, 0, 0, nullptr, 0, 0, 0, stats_or_null))
+                               pad, relu, bn, cluster, 0, nullptr, 0, 0, 0, stats_or_null))
     return rc;
   return launch_umma_conv(L, static_cast<cudaStream_t>(stream));
 }
