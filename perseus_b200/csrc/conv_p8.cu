@@ -15,6 +15,10 @@
 //     (M128 N64 K16) per tile into one of two TMEM accumulators; warps 2..5: epilogue
 //     (TMEM -> +bias (+residual) -> ReLU -> bf16 -> 16-byte stores, lanes = consecutive positions so
 //     every store instruction of a warp is one contiguous 512-byte run in P8).
+//   * PAIR (default): two CTAs of a cluster work on tiles 2j and 2j+1 with ONE tcgen05.mma.cta_group::2 per K step
+//     (M = 256: 128 patch rows from each CTA; each CTA holds HALF of the weight rows: output channels 32c..32c+31 in
+//     bf16, the W_hi or the W_lo image in fp16x2).  The N = 64 MMA is bound by its operand fetch (6 KB per K step from one
+//     SM's shared memory for 32 cycles of math); in a pair every SM fetches 4 KB of patch + half of the weights.
 #include <stdlib.h>
 
 #include "common.cuh"
@@ -52,15 +56,16 @@ struct ConvP8Params {
 // [0, 64) = A.W_hi and [64, 128) = A.W_lo from a single read of the A rows -- 64 cycles per K step instead of the
 // 2 x 48 of two N = 64 MMAs (the N = 64 MMA is bound by its operand fetch, tools/mma_bench.cu).  The epilogue adds the
 // two column groups.  144 KB of resident weights leave room for two patch stages.
-template <int kEpiWarps, bool X2>
+template <int kEpiWarps, bool X2, bool PAIR = false>
 __device__ __forceinline__ void conv_p8_body(const ConvP8Params& p) {
   // X2: the 144 KB of weights leave 67 KB for patches = two whole-tile stages, i.e. ONE tile of prefetch (1.2 us of
   // MMAs) against ~2 us of patch latency.  The ring is therefore cut into HALF-tile stages (4 of the 8 channel chunks
   // each, 4 stages): the producer runs three half-stages ahead of the MMAs.
-  constexpr int kSplit = X2 ? 2 : 1;               // stages per tile
+  // PAIR: each CTA keeps half of the weight rows (36 / 72 KB): room for 5 / 4 WHOLE-tile stages.
+  constexpr int kSplit = (X2 && !PAIR) ? 2 : 1;    // stages per tile
   constexpr int kStageChunks = kChunks / kSplit;   // channel chunks per stage
-  constexpr int kStages = 4;
-  constexpr int kWAll = X2 ? 2 * kWBytes : kWBytes;
+  constexpr int kStages = (PAIR && !X2) ? 5 : 4;
+  constexpr int kWAll = (X2 ? 2 * kWBytes : kWBytes) / (PAIR ? 2 : 1);  // resident weight bytes of THIS CTA
   constexpr int kAccCols = X2 ? 128 : 64;
   constexpr int kNch = 8 / (kEpiWarps / 4);  // 8-channel chunks (P8 planes) per epilogue thread
   extern __shared__ uint8_t smem_raw[];
@@ -80,27 +85,40 @@ __device__ __forceinline__ void conv_p8_body(const ConvP8Params& p) {
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  const int crank = PAIR ? static_cast<int>(cluster_ctarank()) : 0;
+  const bool leader = crank == 0;
+  // PAIR: blockIdx.x = 2 * pair + crank, so "tile = blockIdx.x + i * gridDim.x" hands the pair tiles 2j and 2j+1; both
+  // CTAs run as long as the LEADER's tile exists (the peer of an odd last tile re-reads it and stores nothing)
+  auto alive = [&](int tile) { return tile - crank < p.num_tiles; };
 
   if (threadIdx.x == 0) {
+    // PAIR: the leader's full / weight barriers also take one arrival relayed from the peer (its patch / weights landed);
+    // the leader's accumulator-free barriers take both CTAs' epilogue warps
 #pragma unroll
     for (int i = 0; i < kStages; ++i) {
-      mbar_init(&full_bar[i], 1);
+      mbar_init(&full_bar[i], (PAIR && leader) ? 2 : 1);
       mbar_init(&empty_bar[i], 1);
     }
-    mbar_init(&w_bar, 1);
+    mbar_init(&w_bar, (PAIR && leader) ? 2 : 1);
     mbar_init(&tmem_full_bar[0], 1);
     mbar_init(&tmem_full_bar[1], 1);
-    mbar_init(&tmem_empty_bar[0], kEpiWarps);
-    mbar_init(&tmem_empty_bar[1], kEpiWarps);
+    mbar_init(&tmem_empty_bar[0], PAIR ? 2 * kEpiWarps : kEpiWarps);
+    mbar_init(&tmem_empty_bar[1], PAIR ? 2 * kEpiWarps : kEpiWarps);
     fence_barrier_init();
   }
   if (warp == 1) {
-    tmem_alloc(&tmem_base_slot, 2 * kAccCols);
-    tmem_relinquish();
+    if constexpr (PAIR) {
+      tmem_alloc2(&tmem_base_slot, 2 * kAccCols);
+      tmem_relinquish2();
+    } else {
+      tmem_alloc(&tmem_base_slot, 2 * kAccCols);
+      tmem_relinquish();
+    }
   }
   if (threadIdx.x >= 64 && threadIdx.x < 128) s_bias[threadIdx.x - 64] = __ldg(p.bias + threadIdx.x - 64);
   tc_fence_before();
   __syncthreads();
+  if constexpr (PAIR) cluster_sync_all();
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_slot;
   pdl_launch_dependents();
@@ -110,15 +128,17 @@ __device__ __forceinline__ void conv_p8_body(const ConvP8Params& p) {
     // the whole warp runs the loop (operands stay warp-uniform); one elected lane issues the copies
     if (elect_one()) {
       mbar_expect_tx(&w_bar, kWAll);
-      bulk_load_1d(s_w, p.wimg, kWAll, &w_bar);  // plan constant: fetched while the previous kernel drains (PDL)
+      // plan constant: fetched while the previous kernel drains (PDL).  PAIR: this CTA's half of the rows
+      bulk_load_1d(s_w, p.wimg + crank * kWAll, kWAll, &w_bar);
     }
     pdl_wait();  // the input patches are the previous kernel's output
     int stage = 0;
     uint32_t phase = 0;
     const uint32_t chunk_bytes = static_cast<uint32_t>(p.npos) * 16u;
-    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
-      const int n = tile / p.tiles_per_img;
-      const int q0 = (tile - n * p.tiles_per_img) * 128;
+    for (int tile = blockIdx.x; alive(tile); tile += gridDim.x) {
+      const int tl = tile < p.num_tiles ? tile : p.num_tiles - 1;
+      const int n = tl / p.tiles_per_img;
+      const int q0 = (tl - n * p.tiles_per_img) * 128;
       const uint8_t* src = p.in + n * p.img_bytes + static_cast<long long>(q0) * 16;
 #pragma unroll
       for (int h = 0; h < kSplit; ++h) {
@@ -139,42 +159,70 @@ __device__ __forceinline__ void conv_p8_body(const ConvP8Params& p) {
     }
   } else if (warp == 1) {
     // ================================ MMA issuer ==================================
-    constexpr uint32_t idesc = umma_idesc_16<X2>(128, kAccCols);
-    const uint32_t tm = warp_uniform(tmem_base);
-    const uint32_t a_hi = desc_hi_interleaved(128);
-    const uint32_t b_hi = desc_hi_interleaved(kWSbo);
-    const uint32_t b_lo0 = desc_lo(smem_u32(s_w), 128);
-    const uint32_t pitch16 = static_cast<uint32_t>(p.patch_pitch) >> 4;
-    mbar_wait(&w_bar, 0);
-    int stage = 0;
-    uint32_t phase = 0;
-    int it = 0;
-    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
-      const int acc = it & 1;
-      mbar_wait(&tmem_empty_bar[acc], ((it >> 1) & 1u) ^ 1u);
-#pragma unroll
-      for (int h = 0; h < kSplit; ++h) {
+    if (PAIR && !leader) {
+      // the peer relays "my weights / my patch of this stage have landed" to the leader's barriers: cp.async.bulk can
+      // only credit a barrier of the CTA it writes to, and the leader's MMAs read both CTAs' shared memory
+      const uint32_t lw = mapa_u32(&w_bar, 0);
+      const uint32_t lfull0 = mapa_u32(&full_bar[0], 0);
+      mbar_wait(&w_bar, 0);
+      if (lane == 0) mbar_arrive_cluster(lw);
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; alive(tile); tile += gridDim.x) {
         mbar_wait(&full_bar[stage], phase);
-        tc_fence_after();
-        if (elect_one()) {
-          const uint32_t d_tmem = tm + acc * kAccCols;
-          const uint32_t a_lo0 = desc_lo(smem_u32(s_patch) + stage * stage_bytes, p.patch_pitch);
-#pragma unroll
-          for (int t = 0; t < 9; ++t) {
-            const int r = t / 3, s = t - 3 * r;
-            const uint32_t a_tap = a_lo0 + static_cast<uint32_t>(r * p.Wp + s);  // (r*Wp + s) * 16 B >> 4
-#pragma unroll
-            for (int kk = 0; kk < kStageChunks / 2; ++kk)  // K = 16 = two channel chunks of this stage
-              umma_bf16_split(d_tmem, a_tap + 2 * kk * pitch16, a_hi, b_lo0 + (t * 8 + h * kStageChunks + 2 * kk) * 8, b_hi,
-                              idesc, (h | t | kk) != 0 ? 1u : 0u);
-          }
-          umma_commit(&empty_bar[stage]);
-          if (h == kSplit - 1) umma_commit(&tmem_full_bar[acc]);
-        }
+        if (lane == 0) mbar_arrive_cluster(lfull0 + stage * 8);
         __syncwarp();
         if (++stage == kStages) {
           stage = 0;
           phase ^= 1u;
+        }
+      }
+    } else {
+      constexpr uint32_t idesc = umma_idesc_16<X2>(PAIR ? 256 : 128, kAccCols);
+      const uint32_t tm = warp_uniform(tmem_base);
+      const uint32_t a_hi = desc_hi_interleaved(128);
+      const uint32_t b_hi = desc_hi_interleaved(kWSbo);
+      const uint32_t b_lo0 = desc_lo(smem_u32(s_w), 128);
+      const uint32_t pitch16 = static_cast<uint32_t>(p.patch_pitch) >> 4;
+      mbar_wait(&w_bar, 0);
+      int stage = 0;
+      uint32_t phase = 0;
+      int it = 0;
+      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+        const int acc = it & 1;
+        mbar_wait(&tmem_empty_bar[acc], ((it >> 1) & 1u) ^ 1u);
+#pragma unroll
+        for (int h = 0; h < kSplit; ++h) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          if (elect_one()) {
+            const uint32_t d_tmem = tm + acc * kAccCols;
+            const uint32_t a_lo0 = desc_lo(smem_u32(s_patch) + stage * stage_bytes, p.patch_pitch);
+#pragma unroll
+            for (int t = 0; t < 9; ++t) {
+              const int r = t / 3, s = t - 3 * r;
+              const uint32_t a_tap = a_lo0 + static_cast<uint32_t>(r * p.Wp + s);  // (r*Wp + s) * 16 B >> 4
+#pragma unroll
+              for (int kk = 0; kk < kStageChunks / 2; ++kk) {  // K = 16 = two channel chunks of this stage
+                const uint32_t b_lo = b_lo0 + (t * 8 + h * kStageChunks + 2 * kk) * 8;
+                const uint32_t accum = (h | t | kk) != 0 ? 1u : 0u;
+                if constexpr (PAIR) umma2_bf16_split(d_tmem, a_tap + 2 * kk * pitch16, a_hi, b_lo, b_hi, idesc, accum);
+                else umma_bf16_split(d_tmem, a_tap + 2 * kk * pitch16, a_hi, b_lo, b_hi, idesc, accum);
+              }
+            }
+            if constexpr (PAIR) {
+              umma2_commit_mcast(&empty_bar[stage], 3);  // both CTAs may refill this stage
+              if (h == kSplit - 1) umma2_commit_mcast(&tmem_full_bar[acc], 3);
+            } else {
+              umma_commit(&empty_bar[stage]);
+              if (h == kSplit - 1) umma_commit(&tmem_full_bar[acc]);
+            }
+          }
+          __syncwarp();
+          if (++stage == kStages) {
+            stage = 0;
+            phase ^= 1u;
+          }
         }
       }
     }
@@ -192,7 +240,7 @@ __device__ __forceinline__ void conv_p8_body(const ConvP8Params& p) {
     uint4 rv0[kNch], rv1[kNch];
     auto load_residual = [&](int tile, uint4 (&rv)[kNch]) {
       bool ok = false;
-      if (has_res && tile < p.num_tiles) {
+      if (has_res && tile < p.num_tiles) {  // (a peer tile past the end loads nothing)
         const int n = tile / p.tiles_per_img;
         const int q0 = (tile - n * p.tiles_per_img) * 128 + m;
         const int h = q0 / p.Wp;
@@ -213,13 +261,15 @@ __device__ __forceinline__ void conv_p8_body(const ConvP8Params& p) {
     float bias[8 * kNch];
 #pragma unroll
     for (int e = 0; e < 8 * kNch; ++e) bias[e] = s_bias[8 * j0 + e];
+    const uint32_t lempty0 = PAIR ? mapa_u32(&tmem_empty_bar[0], 0) : 0u;
     auto process = [&](int tile, uint4 (&rv)[kNch]) {
+      const bool live = tile < p.num_tiles;  // false only for the peer of an odd last tile
       const int n = tile / p.tiles_per_img;
       const int ti = tile - n * p.tiles_per_img;
       const int q0 = ti * 128 + m;
       const int h = q0 / p.Wp;
       const int w = q0 - h * p.Wp;
-      const bool in_plane = q0 < p.H * p.Wp;
+      const bool in_plane = live && q0 < p.H * p.Wp;
       const bool valid = in_plane && w < p.W;
       const int a = it & 1;
       const long long opos = static_cast<long long>(q0) + p.Wp + 1;  // padded position of this output
@@ -244,7 +294,10 @@ __device__ __forceinline__ void conv_p8_body(const ConvP8Params& p) {
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&tmem_empty_bar[a]);
+      if (lane == 0) {
+        if (leader) mbar_arrive(&tmem_empty_bar[a]);
+        else mbar_arrive_cluster(lempty0 + a * 8);
+      }
 
       uint4 o[kNch];
 #pragma unroll
@@ -304,11 +357,11 @@ __device__ __forceinline__ void conv_p8_body(const ConvP8Params& p) {
           for (int j = 0; j < kNch; ++j) oimg[(j0 + j) * plane16 + opos] = o[j];
         }
         // the zero border rows the flattened tiles do not reach
-        if (ti == 0 && m < p.Wp + 1) {
+        if (live && ti == 0 && m < p.Wp + 1) {
 #pragma unroll
           for (int j = 0; j < kNch; ++j) oimg[(j0 + j) * plane16 + m] = make_uint4(0, 0, 0, 0);
         }
-        if (ti == p.tiles_per_img - 1 && m < p.Wp - 1) {
+        if (live && ti == p.tiles_per_img - 1 && m < p.Wp - 1) {
           const long long bpos = static_cast<long long>(p.H + 1) * p.Wp + 1 + m;
 #pragma unroll
           for (int j = 0; j < kNch; ++j) oimg[(j0 + j) * plane16 + bpos] = make_uint4(0, 0, 0, 0);
@@ -316,28 +369,55 @@ __device__ __forceinline__ void conv_p8_body(const ConvP8Params& p) {
       }
       ++it;
     };
-    for (int tile = blockIdx.x; tile < p.num_tiles; tile += 2 * gridDim.x) {
+    for (int tile = blockIdx.x; alive(tile); tile += 2 * gridDim.x) {
       process(tile, rv0);
-      if (tile + static_cast<int>(gridDim.x) < p.num_tiles) process(tile + gridDim.x, rv1);
+      if (alive(tile + static_cast<int>(gridDim.x))) process(tile + gridDim.x, rv1);
     }
   }
 
   tc_fence_before();
   __syncthreads();
+  if constexpr (PAIR) cluster_sync_all();  // the peer's TMEM / barriers stay alive until the leader's last MMA and commit
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, 2 * kAccCols);
+    if constexpr (PAIR) tmem_dealloc2(tmem_base, 2 * kAccCols);
+    else tmem_dealloc(tmem_base, 2 * kAccCols);
   }
 }
 
 __global__ void __launch_bounds__(p8_threads(8), 1) conv_p8_kernel(const ConvP8Params p) { conv_p8_body<8, false>(p); }
 __global__ void __launch_bounds__(p8_threads(4), 1) conv_p8_kernel4(const ConvP8Params p) { conv_p8_body<4, false>(p); }
 __global__ void __launch_bounds__(p8_threads(8), 1) conv_p8_x2_kernel(const ConvP8Params p) { conv_p8_body<8, true>(p); }
+__global__ void __launch_bounds__(p8_threads(8), 1) conv_p8_pair_kernel(const ConvP8Params p) { conv_p8_body<8, false, true>(p); }
+__global__ void __launch_bounds__(p8_threads(8), 1) conv_p8_x2_pair_kernel(const ConvP8Params p) { conv_p8_body<8, true, true>(p); }
 
 constexpr int kMaxDynSmem = 227 * 1024 - 1024;  // the kernel also has ~400 B of static shared memory
 inline int patch_pitch_for(int Wp) { return ((128 + 2 * Wp + 2) * 16 + 127) / 128 * 128; }
-inline int smem_bytes_for(int Wp, bool x2) {  // 4 stages of 8 (whole tile) / 4 (half tile, X2) chunk planes
+inline int smem_bytes_for(int Wp, bool x2, bool pair = false) {
+  // single CTA: 4 stages of 8 (whole tile) / 4 (half tile, X2) chunk planes; pair: half the weights, 5 / 4 whole-tile stages
+  if (pair) return (x2 ? 2 : 1) * kWBytes / 2 + (x2 ? 4 : 5) * kChunks * patch_pitch_for(Wp) + 128;
   return (x2 ? 2 : 1) * kWBytes + 4 * (x2 ? kChunks / 2 : kChunks) * patch_pitch_for(Wp) + 128;
+}
+
+static int g_p8_max_pairs[kMaxDevices][2] = {};
+
+template <typename K>
+int p8_pair_occupancy(K kernel, int smem, int* out) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(num_sms() / 2 * 2);
+  cfg.blockDim = dim3(p8_threads(8));
+  cfg.dynamicSmemBytes = smem;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  int n = 0;
+  PB_CUDA(cudaOccupancyMaxActiveClusters(&n, kernel, &cfg));
+  *out = n;
+  return PB200_OK;
 }
 
 }  // namespace
@@ -349,6 +429,11 @@ int conv_p8_init() {
   PB_CUDA(cudaFuncSetAttribute(conv_p8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem));
   PB_CUDA(cudaFuncSetAttribute(conv_p8_kernel4, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem));
   PB_CUDA(cudaFuncSetAttribute(conv_p8_x2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem));
+  PB_CUDA(cudaFuncSetAttribute(conv_p8_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem));
+  PB_CUDA(cudaFuncSetAttribute(conv_p8_x2_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem));
+  // co-resident CTA pairs at the largest shared-memory footprint (the detector's 64 x 64 planes use less)
+  if (int rc = p8_pair_occupancy(conv_p8_pair_kernel, kMaxDynSmem, &g_p8_max_pairs[dev][0])) return rc;
+  if (int rc = p8_pair_occupancy(conv_p8_x2_pair_kernel, kMaxDynSmem, &g_p8_max_pairs[dev][1])) return rc;
   done[dev] = true;
   return PB200_OK;
 }
@@ -356,7 +441,11 @@ int conv_p8_init() {
 int launch_conv_p8(const void* in_p8, const void* wimg, const float* bias, const void* residual_p8, void* out,
                    int out_nhwc, int relu, int B, int H, int W, cudaStream_t st, int x2) {
   const int Wp = W + 2;
-  PB_CHECK(smem_bytes_for(Wp, x2 != 0) <= kMaxDynSmem, "conv_p8: W = %d too wide for the resident-weight kernel", W);
+  // the CTA-pair kernels are the default where a pair fits (PB200_P8_NOPAIR=1: the single-CTA kernels)
+  const int max_pairs = g_p8_max_pairs[current_device()][x2 ? 1 : 0];
+  const bool pair = max_pairs > 0 && smem_bytes_for(Wp, x2 != 0, true) <= kMaxDynSmem && getenv("PB200_P8_NOPAIR") == nullptr &&
+                    getenv("PB200_P8_EPI4") == nullptr;
+  PB_CHECK(smem_bytes_for(Wp, x2 != 0, pair) <= kMaxDynSmem, "conv_p8: W = %d too wide for the resident-weight kernel", W);
   PB_CHECK(Wp - 1 <= 128, "conv_p8: W = %d too wide for the border writer", W);
   if (B == 0) return PB200_OK;
   ConvP8Params p;
@@ -376,17 +465,31 @@ int launch_conv_p8(const void* in_p8, const void* wimg, const float* bias, const
   p.out_nhwc = out_nhwc;
   p.plane_bytes = static_cast<long long>(p8_plane_elems(H, W)) * 16;
   p.img_bytes = p.plane_bytes * 8;
-  const int grid = p.num_tiles < num_sms() ? p.num_tiles : num_sms();
+  int grid = p.num_tiles < num_sms() ? p.num_tiles : num_sms();
+  if (pair) {
+    const int tile_pairs = (p.num_tiles + 1) / 2;
+    grid = 2 * (tile_pairs < max_pairs ? tile_pairs : max_pairs);
+  }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(grid);
   const bool narrow = !x2 && getenv("PB200_P8_EPI4") != nullptr;
   cfg.blockDim = dim3(p8_threads(narrow ? 4 : 8));
-  cfg.dynamicSmemBytes = smem_bytes_for(Wp, x2 != 0);
+  cfg.dynamicSmemBytes = smem_bytes_for(Wp, x2 != 0, pair);
   cfg.stream = st;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   cfg.attrs = attr;
-  cfg.numAttrs = pdl_launch_attrs(attr);
-  if (x2) PB_CUDA(cudaLaunchKernelEx(&cfg, conv_p8_x2_kernel, p));
+  cfg.numAttrs = 0;
+  if (pair) {
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.numAttrs = 1;
+  }
+  cfg.numAttrs += pdl_launch_attrs(attr + cfg.numAttrs);
+  if (pair && x2) PB_CUDA(cudaLaunchKernelEx(&cfg, conv_p8_x2_pair_kernel, p));
+  else if (pair) PB_CUDA(cudaLaunchKernelEx(&cfg, conv_p8_pair_kernel, p));
+  else if (x2) PB_CUDA(cudaLaunchKernelEx(&cfg, conv_p8_x2_kernel, p));
   else if (narrow) PB_CUDA(cudaLaunchKernelEx(&cfg, conv_p8_kernel4, p));
   else PB_CUDA(cudaLaunchKernelEx(&cfg, conv_p8_kernel, p));
   return PB200_OK;
