@@ -91,6 +91,36 @@ int build_umma_dgrad_s2(UmmaConvLaunch* L, const void* dz, int B, int Ho, int Wo
 // BLOCK_N and {single CTA (1), CTA pair (-2)} for m_tiles x Cout outputs by the shared-memory-traffic cost model (passes = 2: fp16x2)
 void umma_choose_tile(long long m_tiles, int Cout, int passes, int* block_n, int* cluster);
 int launch_umma_conv(const UmmaConvLaunch& L, cudaStream_t st);  // dispatches on L.pair
+
+// Several pair<256> convolutions in ONE persistent launch (conv_umma2.cu, CHAIN): the work list is the concatenation of
+// the convs' tile lists; tiles of conv c wait for the images they read to be stored by conv dep[c] of the same launch.
+constexpr int kMaxChain = 8;
+struct ChainCtl {
+  int nconv, total_items;
+  int dep[kMaxChain];          // conv (index in the chain) whose output conv c reads as its input; -1: an earlier launch
+  int dep_ratio[kMaxChain];    // M-supers of conv dep[c] per M-super of conv c (same images)
+  int cnt_off[kMaxChain + 1];  // first counter of conv c: one per M-super (256 output pixels = whole images)
+  int target[kMaxChain];       // arrivals that complete an M-super of conv c (16 epilogue warps x N tiles); 0: nobody waits
+  int bias_off[kMaxChain];     // conv c's bias in the kernel's shared-memory bias array
+  int ncnt;                    // counters in use; cnt[ncnt] = finished-CTA ticket
+  unsigned* cnt;               // zero before the first launch; every launch leaves it zero
+};
+struct alignas(64) ChainArgs {
+  UmmaConvMaps maps[kMaxChain];
+  UmmaConvParams p[kMaxChain];
+  ChainCtl ctl;
+};
+struct ChainLaunch {
+  ChainArgs args;
+  int grid = 0;  // 0: no chain
+  int x2 = 0;
+};
+constexpr int kChainCounters = 4096;  // unsigned words a plan reserves for a chain (+ 1 ticket)
+// Builds a chain from launches prepared by build_umma_conv (all pair<256>, Ho*Wo <= 256 so that an M-super holds whole
+// images); dep[i] = index in `convs` of the conv producing conv i's input, or -1.  Returns PB200_OK with C->grid = 0 when
+// the convs do not qualify.
+int build_umma_chain(ChainLaunch* C, const UmmaConvLaunch* const* convs, const int* dep, int n, unsigned* counters);
+int launch_umma_chain(const ChainLaunch& C, cudaStream_t st);
 // conv_umma2.cu
 int umma_pair_init();
 int umma_pair_max_pairs(int block_n, int x2 = 0);

@@ -37,10 +37,41 @@ struct PairCfg {
 // weight matrix fits next to an activation ring (18-19 k-blocks x 8 KB at Cout = 128), the producers load it ONCE per
 // CTA and afterwards only activation tiles move: per 64-deep k-block 16 KB land in shared memory instead of 24 KB, on
 // layers that are bound by shared-memory traffic (MMA operand reads + TMA fills), not by MMA issue.
-template <int BLOCK_N, bool X2, bool RESB>
-__global__ void __launch_bounds__(kPairThreads, 1)
-conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams p) {
+//
+// CHAIN = several convolutions in ONE persistent launch (conv_chain_kernel: the eight convs of layers 3-4).  The work list
+// is the concatenation of the convs' tile lists, handed to the pairs round-robin: the tail of one conv fills up with the
+// head of the next (3.46 / 1.73 waves per conv become 20.8 rounds for the whole list) and six launch ramps / tails go.
+// A tile of conv c reads whole images of conv dep[c]'s output (Ho x Wo <= 256: an M-super = whole images); every
+// epilogue warp bumps the counter of its (conv, M-super) after its stores, the producers of a dependent tile spin on it
+// (same launch, all pairs co-resident, dependencies point backwards in the list: no deadlock), and the last CTA to
+// finish zeroes the counters for the next launch.
+constexpr int kChainBias = 3072;  // floats of bias of all convs of a chain (4 x 256 + 4 x 512)
+
+__device__ __forceinline__ unsigned ld_acquire_gpu(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
+
+template <int BLOCK_N, bool X2, bool RESB, bool CHAIN>
+__device__ __forceinline__ void pair_body(const UmmaConvMaps* __restrict__ mapsv, const UmmaConvParams* __restrict__ pv,
+                                          const ChainCtl* __restrict__ ctl) {
   using Cfg = PairCfg<BLOCK_N, X2>;
+  const UmmaConvParams& p = pv[0];   // prologue / RESB: the (first) conv
+  const UmmaConvMaps& maps = mapsv[0];
+  const int total_items = CHAIN ? ctl->total_items : p.num_super;
+  // item -> (conv c, work item st of that conv)
+  auto decode = [&](int item, int& c, int& st) {
+    c = 0;
+    st = item;
+    if constexpr (CHAIN) {
+      while (st >= pv[c].num_super) {
+        st -= pv[c].num_super;
+        ++c;
+      }
+    }
+  };
   constexpr int kStages = RESB ? 8 : Cfg::kStages;  // RESB: p.a_stages (<= 8) activation stages, set by the host
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t full_bar[kStages];   // used in the leader CTA only
@@ -49,8 +80,8 @@ conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParam
   __shared__ __align__(8) uint64_t tmem_empty_bar[2];   // leader only: both CTAs' epilogues drained the stage
   __shared__ __align__(8) uint64_t resb_bar;            // leader only: both CTAs' resident weight halves have landed
   __shared__ uint32_t tmem_base_slot;
-  __shared__ float s_bias[512];
-  __shared__ float s_stat[2 * 512];  // training forward: per-CTA partial sum / sum of squares per output channel
+  __shared__ float s_bias[CHAIN ? kChainBias : 512];
+  __shared__ float s_stat[CHAIN ? 2 : 2 * 512];  // training forward: per-CTA partial sum / sum of squares per output channel
 
   const uint32_t raw_addr = smem_u32(smem_raw);
   uint8_t* tiles = smem_raw + (((raw_addr + 1023u) & ~1023u) - raw_addr);
@@ -85,9 +116,14 @@ conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParam
   // PDL: the prologue above overlaps the previous kernel's tail; nothing below may run before it has completed
   pdl_launch_dependents();
   pdl_wait();
-  for (int i = threadIdx.x; i < p.Cout; i += kPairThreads) s_bias[i] = __ldg(p.bias + i);
-  if (p.stats != nullptr)
-    for (int i = threadIdx.x; i < 2 * p.Cout; i += kPairThreads) s_stat[i] = 0.f;
+  if constexpr (CHAIN) {
+    for (int c = 0; c < ctl->nconv; ++c)
+      for (int i = threadIdx.x; i < pv[c].Cout; i += kPairThreads) s_bias[ctl->bias_off[c] + i] = __ldg(pv[c].bias + i);
+  } else {
+    for (int i = threadIdx.x; i < p.Cout; i += kPairThreads) s_bias[i] = __ldg(p.bias + i);
+    if (p.stats != nullptr)
+      for (int i = threadIdx.x; i < 2 * p.Cout; i += kPairThreads) s_stat[i] = 0.f;
+  }
   tc_fence_before();
   __syncthreads();
   cluster_sync_all();
@@ -117,10 +153,32 @@ conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParam
       }
       __syncwarp();
     }
-    for (int st = pair_id; st < p.num_super; st += num_pairs) {
+    for (int item = pair_id; item < total_items; item += num_pairs) {
+      int c, st;
+      decode(item, c, st);
+      const UmmaConvParams& p = pv[c];
+      const UmmaConvMaps& maps = mapsv[c];
       const int m_super = st / p.num_n_tiles;
       const int n_tile = st - m_super * p.num_n_tiles;
       const int m_tile = m_super * 2 + crank;
+      if constexpr (CHAIN) {
+        // the images this tile reads must have been stored completely by conv dep[c] (same launch, other pairs)
+        const int d = ctl->dep[c];
+        if (d >= 0) {
+          const int r = ctl->dep_ratio[c];
+          const int nd = ctl->cnt_off[d + 1] - ctl->cnt_off[d];
+          const unsigned want = static_cast<unsigned>(ctl->target[d]);
+          for (int j = m_super * r; j < (m_super + 1) * r && j < nd; ++j) {
+            const unsigned* cp = ctl->cnt + ctl->cnt_off[d] + j;
+            unsigned spins = 0;
+            while (ld_acquire_gpu(cp) < want) {
+              __nanosleep(40);
+              if (++spins > (1u << 24)) __trap();  // ~1 s: a lost arrival must not hang the GPU
+            }
+          }
+          fence_proxy_async_all();  // the TMA loads below (async proxy) read what those generic-proxy stores wrote
+        }
+      }
       int n0, ho0;
       if (p.tiles_per_img > 0) {
         n0 = m_tile / p.tiles_per_img;
@@ -203,7 +261,10 @@ conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParam
       uint32_t phase = 0;
       int it = 0;
       if (RESB && pair_id < p.num_super) mbar_wait(&resb_bar, 0);
-      for (int st = pair_id; st < p.num_super; st += num_pairs, ++it) {
+      for (int item = pair_id; item < total_items; item += num_pairs, ++it) {
+        int c, st;
+        decode(item, c, st);
+        const UmmaConvParams& p = pv[c];
         const int acc = it & 1;
         mbar_wait(&tmem_empty_bar[acc], ((it >> 1) & 1u) ^ 1u);
         tc_fence_after();
@@ -241,9 +302,13 @@ conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParam
     const int q = warp & 3;
     const int half = (warp - 2) >> 2;
     const int row = q * 32 + lane;
-    const RowMap rmap = {p.up2, p.up_ph, p.up_pw, p.up_lh, p.up_lw};
     int it = 0;
-    for (int st = pair_id; st < p.num_super; st += num_pairs, ++it) {
+    for (int item = pair_id; item < total_items; item += num_pairs, ++it) {
+      int c, st;
+      decode(item, c, st);
+      const UmmaConvParams& p = pv[c];
+      const float* s_bias_c = CHAIN ? s_bias + ctl->bias_off[c] : s_bias;
+      const RowMap rmap = {p.up2, p.up_ph, p.up_pw, p.up_lh, p.up_lw};
       const int m_super = st / p.num_n_tiles;
       const int n_tile = st - m_super * p.num_n_tiles;
       const int m_tile = m_super * 2 + crank;
@@ -257,7 +322,8 @@ conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParam
         // line-granular path (umma_epilogue.cuh): residual and output move as complete 128-byte lines
         const long long gm_group = static_cast<long long>(m_tile) * 128 + q * 32;
         if (has_res) {
-          load_residual_lines<kCols>(static_cast<const __nv_bfloat16*>(p.residual), gm_group, p.M_total, p.Cout, col0, lane, rv, rmap);
+          // CHAIN: the residual may have been written earlier in this launch by another SM: L2-coherent loads
+          load_residual_lines<kCols, CHAIN>(static_cast<const __nv_bfloat16*>(p.residual), gm_group, p.M_total, p.Cout, col0, lane, rv, rmap);
         } else {
 #pragma unroll
           for (int j = 0; j < kVec; ++j) rv[j] = make_uint4(0, 0, 0, 0);
@@ -265,7 +331,7 @@ conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParam
         mbar_wait(&tmem_full_bar[acc], (it >> 1) & 1u);
         tc_fence_after();
         const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BLOCK_N + half * kCols;
-        epilogue_lines<kCols, X2>(t_addr, s_bias + col0, has_res, rv, static_cast<__nv_bfloat16*>(p.out), gm_group, p.M_total,
+        epilogue_lines<kCols, X2>(t_addr, s_bias_c + col0, has_res, rv, static_cast<__nv_bfloat16*>(p.out), gm_group, p.M_total,
                               p.Cout, col0, p.relu, lane, [&]() {
                                 tc_fence_before();
                                 __syncwarp();
@@ -274,8 +340,17 @@ conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParam
                                   else mbar_arrive_cluster(mapa_u32(&tmem_empty_bar[acc], 0));
                                 }
                               }, p.stats != nullptr ? s_stat : nullptr, rmap);
+        if constexpr (CHAIN) {
+          if (ctl->target[c] > 0) {  // a later conv of the chain reads this M-super: publish this warp's stores
+            __threadfence();
+            fence_proxy_async_all();
+            __syncwarp();
+            if (lane == 0) atomicAdd(ctl->cnt + ctl->cnt_off[c] + m_super, 1u);
+          }
+        }
         continue;
       }
+      static_assert(!CHAIN || kCols % 64 == 0, "chained convs use the line-granular epilogue");
       if (has_res && valid) {
         const uint4* res = reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(p.residual) + rmap(gm) * p.Cout + col0);
 #pragma unroll
@@ -288,7 +363,7 @@ conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParam
       tc_fence_after();
       const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BLOCK_N + half * kCols;
       uint4* out_row = reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(p.out) + rmap(gm) * p.Cout + col0);
-      const float* bias = s_bias + col0;
+      const float* bias = s_bias_c + col0;
 #pragma unroll
       for (int chunk = 0; chunk < kChunks; ++chunk) {
         uint4 oc[4];
@@ -331,14 +406,42 @@ conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParam
 
   tc_fence_before();
   __syncthreads();
-  if (p.stats != nullptr)  // fused batch statistics: one fp64 atomic per channel and CTA
-    for (int i = threadIdx.x; i < 2 * p.Cout; i += kPairThreads)
-      if (s_stat[i] != 0.f) atomicAdd(&p.stats[i], static_cast<double>(s_stat[i]));
+  if constexpr (!CHAIN) {
+    if (p.stats != nullptr)  // fused batch statistics: one fp64 atomic per channel and CTA
+      for (int i = threadIdx.x; i < 2 * p.Cout; i += kPairThreads)
+        if (s_stat[i] != 0.f) atomicAdd(&p.stats[i], static_cast<double>(s_stat[i]));
+  }
   cluster_sync_all();  // the peer's TMEM / barriers stay alive until the leader's last MMA and commit are done
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc2(tmem_base, Cfg::kTmemCols);
   }
+  if constexpr (CHAIN) {
+    // every wait of this CTA is behind it: the last CTA to get here re-arms the counters for the next launch
+    __shared__ unsigned s_ticket;
+    unsigned* fin = ctl->cnt + ctl->ncnt;
+    if (threadIdx.x == 0) {
+      __threadfence();
+      s_ticket = atomicAdd(fin, 1u);
+    }
+    __syncthreads();
+    if (s_ticket == gridDim.x - 1) {
+      for (int i = threadIdx.x; i < ctl->ncnt; i += kPairThreads) ctl->cnt[i] = 0u;
+      if (threadIdx.x == 0) *fin = 0u;
+      __threadfence();
+    }
+  }
+}
+
+template <int BLOCK_N, bool X2, bool RESB>
+__global__ void __launch_bounds__(kPairThreads, 1)
+conv_umma2_kernel(const __grid_constant__ UmmaConvMaps maps, const UmmaConvParams p) {
+  pair_body<BLOCK_N, X2, RESB, false>(&maps, &p, nullptr);
+}
+
+template <bool X2>
+__global__ void __launch_bounds__(kPairThreads, 1) conv_chain_kernel(const __grid_constant__ ChainArgs A) {
+  pair_body<256, X2, false, true>(A.maps, A.p, &A.ctl);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -392,6 +495,89 @@ int umma_pair_init() {
   if (int rc = pair_init_one<128, true>(&g_max_pairs[dev][1][1])) return rc;
   if (int rc = pair_init_one<256, true>(&g_max_pairs[dev][1][2])) return rc;
   g_pair_done[dev] = true;
+  return PB200_OK;
+}
+
+static int g_chain_pairs[kMaxDevices][2] = {};
+
+template <bool X2>
+static int chain_cfg(cudaLaunchConfig_t* cfg, cudaLaunchAttribute* attr, int grid, cudaStream_t st, bool pdl) {
+  pair_cfg<256, X2>(cfg, attr, grid, st, pdl);
+  return PB200_OK;
+}
+
+template <bool X2>
+static int chain_init_one(int* max_pairs) {
+  PB_CUDA(cudaFuncSetAttribute(conv_chain_kernel<X2>, cudaFuncAttributeMaxDynamicSharedMemorySize, PairCfg<256, X2>::kSmemBytes));
+  cudaLaunchConfig_t cfg;
+  cudaLaunchAttribute attr[2];
+  chain_cfg<X2>(&cfg, attr, num_sms() / 2 * 2, nullptr, false);
+  int n = 0;
+  PB_CUDA(cudaOccupancyMaxActiveClusters(&n, conv_chain_kernel<X2>, &cfg));
+  *max_pairs = n;
+  return PB200_OK;
+}
+
+int build_umma_chain(ChainLaunch* C, const UmmaConvLaunch* const* convs, const int* dep, int n, unsigned* counters) {
+  C->grid = 0;
+  if (n < 2 || n > kMaxChain || counters == nullptr) return PB200_OK;
+  if (int rc = umma_pair_init()) return rc;
+  const int dev = current_device();
+  const int x2 = convs[0]->split == 2 ? 1 : 0;
+  if (g_chain_pairs[dev][x2] == 0) {
+    if (int rc = x2 ? chain_init_one<true>(&g_chain_pairs[dev][1]) : chain_init_one<false>(&g_chain_pairs[dev][0])) return rc;
+  }
+  ChainCtl& ctl = C->args.ctl;
+  ctl = ChainCtl{};
+  int items = 0, cnt = 0, bias = 0;
+  for (int i = 0; i < n; ++i) {
+    const UmmaConvLaunch& L = *convs[i];
+    const UmmaConvParams& p = L.p;
+    // whole images per M-super, the pair<256> kernel, the line-granular epilogue, no training statistics
+    if (!L.pair || L.resb || L.block_n != 256 || (L.split == 2) != (x2 != 0) || L.split == 1 || p.stats != nullptr || p.up2 ||
+        p.num_tiles == 0 || 256 % (p.Ho * p.Wo) != 0)
+      return PB200_OK;
+    C->args.maps[i] = L.maps;
+    C->args.p[i] = p;
+    ctl.dep[i] = dep[i];
+    ctl.cnt_off[i] = cnt;
+    ctl.bias_off[i] = bias;
+    const int m_supers = p.num_super / p.num_n_tiles;
+    if (dep[i] >= 0) {
+      if (dep[i] >= i) return PB200_OK;
+      const UmmaConvParams& d = convs[dep[i]]->p;
+      const int mine = p.Ho * p.Wo, theirs = d.Ho * d.Wo;  // output pixels per image
+      if (theirs % mine != 0) return PB200_OK;
+      ctl.dep_ratio[i] = theirs / mine;
+      ctl.target[dep[i]] = 16 * d.num_n_tiles;
+    }
+    items += p.num_super;
+    cnt += m_supers;
+    bias += p.Cout;
+  }
+  ctl.cnt_off[n] = cnt;
+  if (cnt + 1 > kChainCounters || bias > kChainBias) return PB200_OK;
+  ctl.nconv = n;
+  ctl.total_items = items;
+  ctl.ncnt = cnt;
+  ctl.cnt = counters;
+  const int max_pairs = g_chain_pairs[dev][x2];
+  // every pair must be resident at once: the dependency spins rely on it
+  C->grid = 2 * (items < max_pairs ? items : max_pairs);
+  C->x2 = x2;
+  return PB200_OK;
+}
+
+int launch_umma_chain(const ChainLaunch& C, cudaStream_t st) {
+  cudaLaunchConfig_t cfg;
+  cudaLaunchAttribute attr[2];
+  if (C.x2) {
+    chain_cfg<true>(&cfg, attr, C.grid, st, true);
+    PB_CUDA(cudaLaunchKernelEx(&cfg, conv_chain_kernel<true>, C.args));
+  } else {
+    chain_cfg<false>(&cfg, attr, C.grid, st, true);
+    PB_CUDA(cudaLaunchKernelEx(&cfg, conv_chain_kernel<false>, C.args));
+  }
   return PB200_OK;
 }
 

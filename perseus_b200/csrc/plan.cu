@@ -45,8 +45,11 @@ struct Op {
 };
 
 // activation buffer ids
+// BUF_S0..: layers 3-4 of the 16-bit plans run as ONE chained launch (conv_umma2.cu, CHAIN): every conv output of those
+// layers gets a buffer of its own, so that no store of the launch lands in a buffer an earlier conv of the same launch
+// may still be reading for other images
 enum { BUF_FRAMES = 0, BUF_STEM = 1, BUF_R0 = 2, BUF_R1 = 3, BUF_R2 = 4, BUF_R3 = 5, BUF_P8A = 6, BUF_P8B = 7,
-       BUF_P8C = 8, BUF_COUNT = 9 };
+       BUF_P8C = 8, BUF_S0 = 9, BUF_COUNT = 17 };
 
 }  // namespace pb200
 
@@ -73,6 +76,13 @@ struct pb200_plan {
   std::vector<pb200::UmmaConvLaunch> umma;  // per conv
   std::vector<pb200::HaloLaunch> halo;      // per conv (grid == 0: the conv does not run on conv_halo.cu)
   bool use_halo = true;                     // bf16 mode, KT weights: layer2's stride-1 convs on the halo-patch kernel
+  // layers 3-4 (every run of consecutive pair<256> convs) as ONE persistent launch with in-kernel dependencies
+  // (conv_umma2.cu CHAIN); PB200_NO_CHAIN=1: one launch per conv.  chain_at[i] = chain starting at op i (-1: none),
+  // chain_len[i] = ops it covers
+  bool use_chain = true;
+  size_t chain_off = 0;
+  std::vector<pb200::ChainLaunch> chains;
+  std::vector<int> chain_at, chain_len;
   std::vector<std::string> op_names;
   std::vector<std::string> op_kernels;  // kernel each op launches (known after the first forward at a batch size)
   // L2 chunking of the front of the network (fused stem + the four layer1 convs, P8 layout): these five kernels move
@@ -175,23 +185,31 @@ static void build_graph(pb200_plan* pl) {
       pl->ops.push_back(op);
     }
   }
+  int next_fresh = BUF_S0;
+  const bool fuse_ds = pl->bf16 && !getenv("PB200_NO_DS_FUSION");
+  auto ring = [](int buf, int k) { return BUF_R0 + (buf - BUF_R0 + k) % 4; };
+  cur = BUF_R0 + cur;  // from here on `cur` is a buffer id
   for (int L = first_layer; L < 4; ++L) {
     for (int b = 0; b < 2; ++b) {
       const int cout = planes[L];
       const int stride = (L > 0 && b == 0) ? 2 : 1;
       const std::string pre = "layer" + std::to_string(L + 1) + "." + std::to_string(b);
-      const int t = (cur + 1) % 4, y = (cur + 2) % 4, ds = (cur + 3) % 4;
+      // layers 3-4 of the 16-bit plans: fresh buffers (see BUF_S0); otherwise the four-buffer ring
+      const bool fresh = fuse_ds && L >= 2;
+      const int t = fresh ? next_fresh++ : ring(cur, 1);
+      const int y = fresh ? next_fresh++ : ring(cur, 2);
+      const int ds = fresh ? -1 : ring(cur, 3);
       int res = cur;
       int fused_ds = -1;  // bf16 mode: the projection is accumulated inside conv2 (K-extension), never materialised
       if (stride != 1 || cin != cout) {  // resnet.py:240-243
         add_conv(pl, pre + ".downsample.0", pre + ".downsample.1", cin, cout, 1, stride, 0, h, w);
-        if (pl->bf16 && stride == 2 && !getenv("PB200_NO_DS_FUSION")) {
+        if (fuse_ds && stride == 2) {
           fused_ds = static_cast<int>(pl->convs.size()) - 1;
           res = -1;
         } else {
           Op op;
           op.kind = OP_CONV; op.name = pre + ".downsample"; op.conv = static_cast<int>(pl->convs.size()) - 1;
-          op.in_buf = BUF_R0 + cur; op.out_buf = BUF_R0 + ds; op.relu = 0;
+          op.in_buf = cur; op.out_buf = ds; op.relu = 0;
           pl->ops.push_back(op);
           res = ds;
         }
@@ -200,7 +218,7 @@ static void build_graph(pb200_plan* pl) {
       {
         Op op;
         op.kind = OP_CONV; op.name = pre + ".conv1+bn1+relu"; op.conv = static_cast<int>(pl->convs.size()) - 1;
-        op.in_buf = BUF_R0 + cur; op.out_buf = BUF_R0 + t; op.relu = 1;
+        op.in_buf = cur; op.out_buf = t; op.relu = 1;
         pl->ops.push_back(op);
       }
       const int ho = pl->convs.back().Ho, wo = pl->convs.back().Wo;
@@ -209,12 +227,15 @@ static void build_graph(pb200_plan* pl) {
         Op op;
         op.kind = OP_CONV; op.name = pre + (fused_ds >= 0 ? ".conv2+bn2+downsample+add+relu" : ".conv2+bn2+add+relu");
         op.conv = static_cast<int>(pl->convs.size()) - 1;
-        op.in_buf = BUF_R0 + t; op.out_buf = BUF_R0 + y; op.res_buf = res >= 0 ? BUF_R0 + res : -1; op.relu = 1;
+        op.in_buf = t; op.out_buf = y; op.res_buf = res; op.relu = 1;
         if (fused_ds >= 0) {
           pl->convs.back().ds_conv = fused_ds;
-          op.ds_buf = BUF_R0 + cur;
+          op.ds_buf = cur;
         }
         pl->ops.push_back(op);
+      }
+      if (fresh) {
+        pl->buf_per_frame[t] = pl->buf_per_frame[y] = static_cast<size_t>(ho) * wo * cout * pl->elt;
       }
       cur = y;
       h = ho; w = wo; cin = cout;
@@ -222,7 +243,7 @@ static void build_graph(pb200_plan* pl) {
   }
   {
     Op op;
-    op.kind = OP_HEAD; op.name = "avgpool+fc+decode"; op.in_buf = BUF_R0 + cur;
+    op.kind = OP_HEAD; op.name = "avgpool+fc+decode"; op.in_buf = cur;
     pl->ops.push_back(op);
   }
   // buffers (bytes per frame)
@@ -252,6 +273,7 @@ static void build_graph(pb200_plan* pl) {
   if (const char* e = getenv("PB200_L1_CHUNK")) pl->l1_chunk = atoi(e);
   pl->b_tiled = (pl->bf16 || pl->f16) && getenv("PB200_NO_BTILED") == nullptr;
   pl->use_halo = pl->b_tiled && !pl->f16 && getenv("PB200_NO_HALO") == nullptr;
+  pl->use_chain = pl->bf16 && getenv("PB200_NO_CHAIN") == nullptr;
   // weight arena
   size_t woff = 0;
   for (auto& c : pl->convs) {
@@ -267,6 +289,9 @@ static void build_graph(pb200_plan* pl) {
   woff = align_up(woff + sizeof(float) * 512 * 2 * pl->n_kp, 1024);
   pl->fc_b_off = woff;
   woff = align_up(woff + sizeof(float) * 2 * pl->n_kp, 1024);
+  // dependency counters of the chained launch (zero between launches; the weight upload rewrites them with zeros)
+  pl->chain_off = align_up(woff, 1024);
+  woff = pl->chain_off + (kChainCounters + 1) * sizeof(unsigned);
   pl->arena_bytes = woff;
   for (auto& o : pl->ops) pl->op_names.push_back(o.name);
 }
@@ -312,6 +337,7 @@ extern "C" int pb200_plan_create(pb200_plan** out, int device, int max_batch, in
   pl->elt = pl->bf16 ? 2 : 4;
   build_graph(pl);
   cudaError_t e = cudaMalloc(reinterpret_cast<void**>(&pl->arena), pl->arena_bytes);
+  if (e == cudaSuccess) e = cudaMemset(pl->arena + pl->chain_off, 0, (kChainCounters + 1) * sizeof(unsigned));
   if (e != cudaSuccess) {
     delete pl;
     return cuda_fail(e, "cudaMalloc(weight arena)", __FILE__, __LINE__);
@@ -571,6 +597,57 @@ static int prepare(pb200_plan* pl, const void* frames, void* ws, int B) {
       return rc;
     }
   }
+  // chains: maximal runs of consecutive convs on the pair<256> kernel whose outputs are whole images per M-super
+  pl->chains.clear();
+  pl->chain_at.assign(pl->ops.size(), -1);
+  pl->chain_len.assign(pl->ops.size(), 0);
+  if (pl->use_chain && pl->chains.empty()) {
+    auto chainable = [&](size_t i) {
+      const Op& op = pl->ops[i];
+      if (op.kind != OP_CONV || pl->convs[op.conv].stem || pl->halo[op.conv].grid > 0) return false;
+      const UmmaConvLaunch& L = pl->umma[op.conv];
+      return L.pair && !L.resb && L.block_n == 256 && L.p.num_tiles > 0 && 256 % (L.p.Ho * L.p.Wo) == 0;
+    };
+    size_t i = 0;
+    while (i < pl->ops.size()) {
+      if (!chainable(i)) {
+        ++i;
+        continue;
+      }
+      size_t j = i;
+      while (j < pl->ops.size() && chainable(j) && j - i < static_cast<size_t>(kMaxChain)) ++j;
+      // every output buffer of the run must be new to the run (no store may land where an earlier conv still reads)
+      bool safe = true;
+      for (size_t k = i; k < j && safe; ++k)
+        for (size_t m = i; m <= k && safe; ++m) {
+          const Op& a = pl->ops[m];
+          const int o = pl->ops[k].out_buf;
+          if (a.in_buf == o || a.res_buf == o || a.ds_buf == o || (m < k && a.out_buf == o)) safe = false;
+        }
+      if (safe && j - i >= 2 && pl->chains.empty()) {  // one chain per plan (one set of counters)
+        const UmmaConvLaunch* convs[kMaxChain];
+        int dep[kMaxChain];
+        for (size_t k = i; k < j; ++k) {
+          convs[k - i] = &pl->umma[pl->ops[k].conv];
+          dep[k - i] = -1;
+          for (size_t m = i; m < k; ++m)
+            if (pl->ops[m].out_buf == pl->ops[k].in_buf) dep[k - i] = static_cast<int>(m - i);
+        }
+        ChainLaunch C;
+        int rc = build_umma_chain(&C, convs, dep, static_cast<int>(j - i), reinterpret_cast<unsigned*>(pl->arena + pl->chain_off));
+        if (rc) {
+          pl->cache_B = -1;
+          return rc;
+        }
+        if (C.grid > 0) {
+          pl->chain_at[i] = static_cast<int>(pl->chains.size());
+          pl->chain_len[i] = static_cast<int>(j - i);
+          pl->chains.push_back(C);
+        }
+      }
+      i = j;
+    }
+  }
   pl->cache_frames = frames;
   pl->cache_ws = ws;
   pl->cache_B = B;
@@ -663,8 +740,14 @@ extern "C" int pb200_forward(pb200_plan* plan, const void* frames, void* workspa
     }
     first = plan->n_front;
   }
-  for (size_t i = first; i < plan->ops.size(); ++i)
+  for (size_t i = first; i < plan->ops.size(); ++i) {
+    if (!plan->chain_at.empty() && plan->chain_at[i] >= 0) {  // layers 3-4: one persistent launch for the whole run
+      if (int rc = launch_umma_chain(plan->chains[plan->chain_at[i]], st)) return rc;
+      i += plan->chain_len[i] - 1;
+      continue;
+    }
     if (int rc = run_op(plan, plan->ops[i], frames, workspace, out_norm, out_px_or_null, B, st)) return rc;
+  }
   return PB200_OK;
 }
 
@@ -715,7 +798,10 @@ extern "C" int pb200_plan_launches_per_forward(const pb200_plan* plan) {
 }
 extern "C" int pb200_plan_launches_at(const pb200_plan* plan, int B) {
   if (!plan) return 0;
-  const int n = static_cast<int>(plan->ops.size());
+  int n = static_cast<int>(plan->ops.size());
+  if (plan->cache_B == B)  // chains exist once a forward has been prepared at this batch size
+    for (size_t i = 0; i < plan->chain_len.size(); ++i)
+      if (plan->chain_at[i] >= 0) n -= plan->chain_len[i] - 1;
   if (!front_chunked(plan, B)) return n;
   const int chunks = (B + plan->l1_chunk - 1) / plan->l1_chunk;
   return n - plan->n_front + chunks * plan->n_front;

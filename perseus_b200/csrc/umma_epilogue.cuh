@@ -121,7 +121,7 @@ __device__ __forceinline__ void accumulate_stats32(const uint4 (&o)[4], bool row
 // Residual rows of this thread's tile slice, fetched line by line and transposed back to pixel ownership:
 // rv[g * 8 + c] = chunk c of 64-channel group g of THIS lane's pixel.  gm_group = global pixel index of lane (lane & 24)
 // of the warp; rows >= M_total read as zero.
-template <int kCols>
+template <int kCols, bool COHERENT = false>
 __device__ __forceinline__ void load_residual_lines(const __nv_bfloat16* __restrict__ residual, long long gm_group,
                                                     long long M_total, int Cout, int col0, int lane,
                                                     uint4 (&rv)[kCols / 8], const RowMap rmap = RowMap{0, 0, 0, 0, 0}) {
@@ -134,8 +134,8 @@ __device__ __forceinline__ void load_residual_lines(const __nv_bfloat16* __restr
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       const long long gmj = gbase + j;
-      t[j] = gmj < M_total ? __ldg(reinterpret_cast<const uint4*>(residual + rmap(gmj) * Cout + col0 + g * 64) + l8)
-                           : make_uint4(0, 0, 0, 0);
+      const uint4* rp = reinterpret_cast<const uint4*>(residual + rmap(gmj) * Cout + col0 + g * 64) + l8;
+      t[j] = gmj < M_total ? (COHERENT ? __ldcg(rp) : __ldg(rp)) : make_uint4(0, 0, 0, 0);
     }
     transpose8x8_u4(t, l8);
 #pragma unroll

@@ -598,3 +598,37 @@ def test_conv_halo_vs_exact_operand_reference(case):
     err = (got - want).abs()
     bad = err > 2.0 ** -7 * want.abs() + 1e-2
     assert not bad.any(), f"{int(bad.sum())} / {bad.numel()} outputs off; max err {float(err.max()):.4f}; first bad idx {bad.nonzero()[:4].tolist()}"
+
+
+@pytest.mark.parametrize("precision", ["bf16", "fp16x2"])
+@pytest.mark.parametrize("B", [256, 37, 131, 255])
+def test_chained_layers34_bit_equal_to_one_launch_per_conv(precision, B, monkeypatch):
+    """Layers 3-4 run as ONE persistent launch whose tiles wait on in-kernel dependency counters (conv_umma2.cu CHAIN).
+    The arithmetic of a tile is unchanged, so the keypoints must equal the one-launch-per-conv plan bit for bit -- at a full
+    batch, at odd batches (dead peer tiles, partial last M-supers), and on every repeat (the counters re-arm themselves)."""
+    from perseus_b200 import _lib
+
+    from perseus_b200.detector import KeypointCNN
+
+    sd = do.seeded_state_dict(3, 8, seed=0)
+
+    def fresh():  # the plan reads PB200_NO_CHAIN when it is created
+        m = KeypointCNN(num_channels=3, precision=precision, max_batch=B)
+        m.load_state_dict(sd)
+        return m.eval().to(gu.dev())
+
+    monkeypatch.delenv("PB200_NO_CHAIN", raising=False)
+    chained = fresh()
+    x = gu.synth_u8_frames(B, seed=21).cuda()
+    got = [chained.forward_frames(x).clone() for _ in range(3)]
+    n_chain = _lib.lib().pb200_plan_launches_at(chained._plan(gu.dev(), B).handle, B)
+    monkeypatch.setenv("PB200_NO_CHAIN", "1")
+    plain = fresh()
+    want = plain.forward_frames(x)
+    n_plain = _lib.lib().pb200_plan_launches_at(plain._plan(gu.dev(), B).handle, B)
+    print(f"[chain {precision} B={B}] {n_chain} launches chained vs {n_plain} one per conv")
+    if B >= 255:  # smaller batches may select other tile shapes (no pair<256> run to chain)
+        assert n_chain < n_plain, f"no chain was built at B = {B} ({n_chain} vs {n_plain} launches)"
+    assert torch.isfinite(want).all()
+    for g in got:
+        assert torch.equal(g, want)
