@@ -134,6 +134,10 @@ int pb200_forward_profile(pb200_plan* plan, const void* frames, void* workspace,
 int pb200_plan_launches_per_forward(const pb200_plan* plan);
 /* the same at batch size B: the fused stem + layer1 kernels run once per L2 chunk of frames */
 int pb200_plan_launches_at(const pb200_plan* plan, int B);
+/* ops launched together starting at op i: 1 = its own launch; k >= 2 = head of ONE chained persistent launch covering ops
+ * i..i+k-1 (layers 3-4: torchvision resnet.py layer3 / layer4 as called from perseus/detector/models.py:34-40);
+ * 0 = covered by a chain that started earlier.  pb200_forward_profile reports a chain's time at its head op. */
+int pb200_plan_op_chain_len(const pb200_plan* plan, int i);
 
 /* ---- stand-alone pieces (also used by the parity tests) ------------------------------- */
 

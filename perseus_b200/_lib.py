@@ -52,6 +52,7 @@ SIGNATURES = {
     ),
     "pb200_plan_launches_per_forward": (c_int, [c_void_p]),
     "pb200_plan_launches_at": (c_int, [c_void_p, c_int]),
+    "pb200_plan_op_chain_len": (c_int, [c_void_p, c_int]),
     "pb200_decode_pixels": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p]),
     "pb200_debug_conv_bf16": (
         c_int,

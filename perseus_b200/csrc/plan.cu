@@ -768,6 +768,15 @@ extern "C" const char* pb200_plan_op_name(const pb200_plan* plan, int i) {
   if (!plan || i < 0 || i >= static_cast<int>(plan->ops.size())) return "";
   return plan->op_names[i].c_str();
 }
+// ops launched together starting at op i: 1 = its own launch, k >= 2 = head of a chained launch covering ops i..i+k-1,
+// 0 = covered by a chain that started earlier (known once a forward has been prepared at a batch size)
+extern "C" int pb200_plan_op_chain_len(const pb200_plan* plan, int i) {
+  if (!plan || i < 0 || i >= static_cast<int>(plan->ops.size())) return 0;
+  if (plan->chain_at.size() != plan->ops.size()) return 1;
+  for (int h = 0; h <= i; ++h)
+    if (plan->chain_at[h] >= 0 && i < h + plan->chain_len[h]) return h == i ? plan->chain_len[h] : 0;
+  return 1;
+}
 extern "C" const char* pb200_plan_op_kernel(const pb200_plan* plan, int i) {
   if (!plan || i < 0 || i >= static_cast<int>(plan->ops.size())) return "";
   const Op& op = plan->ops[i];
@@ -780,6 +789,10 @@ extern "C" const char* pb200_plan_op_kernel(const pb200_plan* plan, int i) {
     case OP_MAXPOOL: k = plan->split ? "maxpool_split_kernel" : (plan->bf16 ? "maxpool_bf16_kernel" : "maxpool_f32_kernel"); break;
     case OP_HEAD: k = "head_kernel"; break;
     case OP_CONV:
+      if (pb200_plan_op_chain_len(plan, i) != 1) {
+        k = plan->f16 ? "conv_chain_kernel<x2>" : "conv_chain_kernel";
+        break;
+      }
       if (!plan->bf16 && !(plan->split && !plan->convs[op.conv].stem))
         k = (plan->convs[op.conv].stem && plan->H % 16 == 0 && plan->W % 64 == 0) ? "stem_f32_kernel" : "conv_simt_kernel";
       else if (plan->cache_B < 0 || plan->umma.size() != plan->convs.size()) k = "conv_umma*";
@@ -856,13 +869,15 @@ extern "C" int pb200_forward_profile(pb200_plan* plan, const void* frames, void*
       for (int i = 0; i < plan->n_front; ++i) seq.push_back({i, n0, B - n0 < plan->l1_chunk ? B - n0 : plan->l1_chunk});
     first = plan->n_front;
   }
-  for (int i = first; i < n; ++i) seq.push_back({i, 0, B});
+  for (int i = first; i < n; ++i)
+    if (pb200_plan_op_chain_len(plan, i) != 0) seq.push_back({i, 0, B});  // a chain is timed as ONE launch at its head op
   std::vector<cudaEvent_t> ev(seq.size() + 1);
   for (auto& e : ev) PB_CUDA(cudaEventCreate(&e));
   int rc = PB200_OK;
   PB_CUDA(cudaEventRecord(ev[0], st));
   for (size_t j = 0; j < seq.size() && rc == PB200_OK; ++j) {
-    rc = run_op(plan, plan->ops[seq[j].op], frames, workspace, out_norm, out_px_or_null, seq[j].b, st, seq[j].n0);
+    if (pb200_plan_op_chain_len(plan, seq[j].op) >= 2) rc = launch_umma_chain(plan->chains[plan->chain_at[seq[j].op]], st);
+    else rc = run_op(plan, plan->ops[seq[j].op], frames, workspace, out_norm, out_px_or_null, seq[j].b, st, seq[j].n0);
     if (rc == PB200_OK && cudaEventRecord(ev[j + 1], st) != cudaSuccess) rc = PB200_ERR_CUDA;
   }
   if (rc == PB200_OK) {

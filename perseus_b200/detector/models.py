@@ -356,6 +356,14 @@ class KeypointCNN(nn.Module):
         for i in range(n):
             fl, by = ctypes.c_double(), ctypes.c_double()
             _lib.check(plan.lib.pb200_plan_op_work(plan.handle, i, B, ctypes.byref(fl), ctypes.byref(by)))
-            rows.append((plan.lib.pb200_plan_op_name(plan.handle, i).decode(), float(ms[i]), fl.value, by.value,
-                         plan.lib.pb200_plan_op_kernel(plan.handle, i).decode()))
+            name = plan.lib.pb200_plan_op_name(plan.handle, i).decode()
+            k = plan.lib.pb200_plan_op_chain_len(plan.handle, i)
+            if k == 0:  # covered by the chained launch whose row is the last one appended: add this conv's work to it
+                h = rows[-1]
+                rows[-1] = (h[0], h[1], h[2] + fl.value, h[3] + by.value, h[4])
+                continue
+            if k >= 2:
+                last = plan.lib.pb200_plan_op_name(plan.handle, i + k - 1).decode()
+                name = f"{name.split('.')[0]}..{last.split('.')[0]} ({k} convs, one chained launch)"
+            rows.append((name, float(ms[i]), fl.value, by.value, plan.lib.pb200_plan_op_kernel(plan.handle, i).decode()))
         return rows
