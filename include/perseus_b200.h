@@ -357,6 +357,15 @@ int pb200_augment(const float* images, const int32_t* iparams, const float* fpar
 int pb200_plasma_side(int H, int W);
 int pb200_plasma(const float* roughness, uint64_t seed, float* scratch, float* out, int B, int H, int W,
                  pb200_stream stream);
+/* pb200_plasma without caller scratch and without ANY allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  The B x S x S working grids live in a static device array of PB200_PLASMA_STATIC_MAX_FLOATS floats
+ * (4.03 MB = sixteen 257 x 257 grids, held by every GPU that loads the library until exit); B * S * S beyond that is
+ * rejected with PB200_ERR_INVALID and a message naming the limit.  Same arguments otherwise, bit-identical output.  All calls
+ * share the array: calls that overlap on the GPU (different streams / threads) race; calls on one stream are ordered.  The
+ * first call on each device resolves the array's device address (cudaGetSymbolAddress): make it outside graph capture. */
+#define PB200_PLASMA_STATIC_MAX_FLOATS (16 * 257 * 257)
+int pb200_plasma_static(const float* roughness, uint64_t seed, float* out, int B, int H, int W, pb200_stream stream);
 
 /* ---- fixed-lag smoother linearisation -----------------------------------------------------
  * The consumer of the factor entries above: GTSAM's whitening (noiseModel.Diagonal sigmas, factors.py:42,49) +

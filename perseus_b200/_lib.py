@@ -124,6 +124,7 @@ SIGNATURES = {
     ),
     "pb200_plasma_side": (c_int, [c_int, c_int]),
     "pb200_plasma": (c_int, [c_void_p, ctypes.c_uint64, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
+    "pb200_plasma_static": (c_int, [c_void_p, ctypes.c_uint64, c_void_p, c_int, c_int, c_int, c_void_p]),
     "pb200_train_stem_im2col": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
     "pb200_train_stem_pack": (c_int, [c_void_p, c_int, c_void_p, c_void_p]),
     "pb200_train_stem_unpack": (c_int, [c_void_p, c_int, c_void_p, c_void_p]),

@@ -532,3 +532,40 @@ extern "C" int pb200_plasma(const float* roughness, uint64_t seed, float* scratc
   PB_CUDA(cudaGetLastError());
   return PB200_OK;
 }
+
+// ---- the same fractal with NO caller scratch and NO allocation (no counterpart in the reference: added
+// for callers that cannot call cudaMalloc -- code under CUDA graph capture, tight serving loops) ------
+// The S x S working grids live in a file-scope device array of PB200_PLASMA_STATIC_MAX_FLOATS floats (4.03 MB = sixteen
+// 257 x 257 grids) that every GPU that loads the library holds until exit.  In host code `g_plasma_static` is only a
+// stand-in for the symbol, NOT a device address: the address is fetched once per device, with that device current, by
+// cudaGetSymbolAddress and passed to the kernel.  Every call shares the array: calls that overlap on the GPU (two streams,
+// two host threads) race on it; calls on one stream are ordered.  Nothing has to start at zero -- the kernel writes every
+// grid point (corners / centres / edge midpoints of every level) before any read of it -- so the previous call's contents
+// are simply overwritten.
+namespace pb200 {
+static __device__ __align__(256) float g_plasma_static[PB200_PLASMA_STATIC_MAX_FLOATS];
+}  // namespace pb200
+
+extern "C" int pb200_plasma_static(const float* roughness, uint64_t seed, float* out, int B, int H, int W,
+                                   pb200_stream stream) {
+  if (int rc = require_device()) return rc;
+  PB_CHECK(roughness && out && B >= 0 && H >= 1 && W >= 1, "plasma_static: bad argument");
+  const int S = pb200_plasma_side(H, W);
+  const long long need = static_cast<long long>(B) * S * S;
+  PB_CHECK(static_cast<long long>(S) * S < (1LL << 31) && need <= static_cast<long long>(PB200_PLASMA_STATIC_MAX_FLOATS),
+           "plasma_static: %d images of %d x %d need %lld scratch floats, the built-in scratch holds %lld "
+           "(PB200_PLASMA_STATIC_MAX_FLOATS); use pb200_plasma with caller scratch for larger problems",
+           B, H, W, need, static_cast<long long>(PB200_PLASMA_STATIC_MAX_FLOATS));
+  if (B == 0) return PB200_OK;
+  static float* dev_ptr[kMaxDevices] = {};  // per device: the symbol's address in THAT device's copy of the module
+  const int dev = current_device();
+  if (dev_ptr[dev] == nullptr) {
+    float* ptr = nullptr;
+    PB_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&ptr), g_plasma_static));
+    PB_CHECK(ptr != nullptr, "plasma_static: cudaGetSymbolAddress returned a null address on device %d", dev);
+    dev_ptr[dev] = ptr;
+  }
+  plasma_kernel<<<B, 1024, 0, static_cast<cudaStream_t>(stream)>>>(roughness, seed, dev_ptr[dev], out, S, H, W);
+  PB_CUDA(cudaGetLastError());
+  return PB200_OK;
+}
