@@ -14,8 +14,20 @@ namespace pb200 {
 constexpr int kFacThreads = 128;
 
 // Cooperative, coalesced copy of `n` doubles between global and shared memory.
+// Loads are issued in independent batches of 6 per thread before the first store: as a plain load -> store loop (trip
+// count unknown to the compiler) every iteration waited for its own DRAM round trip -- 30 in a row at the top of every
+// dynamics CTA, which ncu showed as the kernel's dominant stall (long scoreboard, 8 of 15 cycles per issued instruction).
 __device__ __forceinline__ void copy_in(double* dst, const double* __restrict__ src, int n) {
-  for (int i = threadIdx.x; i < n; i += blockDim.x) dst[i] = __ldg(src + i);
+  constexpr int U = 6;
+  const int T = blockDim.x;
+  for (int i0 = threadIdx.x; i0 < n; i0 += U * T) {
+    double v[U];
+#pragma unroll
+    for (int k = 0; k < U; ++k) v[k] = (i0 + k * T < n) ? __ldg(src + i0 + k * T) : 0.0;
+#pragma unroll
+    for (int k = 0; k < U; ++k)
+      if (i0 + k * T < n) dst[i0 + k * T] = v[k];
+  }
 }
 __device__ __forceinline__ void copy_out(double* __restrict__ dst, const double* src, int n) {
   for (int i = threadIdx.x; i < n; i += blockDim.x) dst[i] = src[i];
@@ -35,14 +47,65 @@ __device__ __forceinline__ void stage_out(double* sm, double* __restrict__ dst, 
   copy_out(dst, sm, cnt * N);
 }
 
+// fm::dynamics_factor_io's view of a CUDA thread (see factors_math.h for why): inputs are RE-READ from the CTA's staged
+// copy in shared memory whenever the factor needs them, two poses can be parked in shared memory, and every output block
+// leaves the thread at once through the warp's staging slice: the warp's 32 factors write a chunk of <= 9 doubles each
+// (lane stride odd in 8-byte units: conflict-free), the warp copies the chunk out in runs of consecutive 8-byte words,
+// and the slice is free again.  Only __syncwarp is involved: every lane of the warp runs the factor, lanes past the end
+// on factor 0's inputs (their results are not copied out).
+constexpr int kDynChunk = 9;
+constexpr int kDynSlice = 32 * kDynChunk;  // doubles per warp staging slice
+struct DynWarpIO {
+  const double *p1, *p2, *pw, *pv;  // this thread's inputs in shared memory (12, 12, 3, 3 doubles)
+  double *st0, *st1;                // this thread's two parked poses (12 doubles each)
+  double* s;                        // this warp's staging slice
+  int lane, cnt;                    // factors of this warp that exist (0..32)
+  double *r, *h0, *h1, *h2, *h3;    // global outputs of the warp's first factor
+  __device__ __forceinline__ fm::Pose x1() const { return fm::load_pose12(p1); }
+  __device__ __forceinline__ fm::Pose x2() const { return fm::load_pose12(p2); }
+  __device__ __forceinline__ fm::V3 w() const { return fm::v3(pw[0], pw[1], pw[2]); }
+  __device__ __forceinline__ fm::V3 v() const { return fm::v3(pv[0], pv[1], pv[2]); }
+  __device__ __forceinline__ void put_pose(int k, const fm::Pose& p) {
+    double* d = k ? st1 : st0;
+#pragma unroll
+    for (int i = 0; i < 9; ++i) d[i] = p.R.m[i];
+    d[9] = p.t.x; d[10] = p.t.y; d[11] = p.t.z;
+  }
+  __device__ __forceinline__ fm::Pose get_pose(int k) const { return fm::load_pose12(k ? st1 : st0); }
+  template <int N>
+  __device__ __forceinline__ void put(double* __restrict__ dst, const double (&v)[N]) {
+    constexpr int C = (N % kDynChunk == 0) ? kDynChunk : N;  // 9, or the whole block (6 / 3 doubles)
+    constexpr int CS = C | 1;                                // lane stride
+    static_assert(C <= kDynChunk, "chunk larger than the staging slice");
+#pragma unroll
+    for (int c = 0; c < N / C; ++c) {
+#pragma unroll
+      for (int e = 0; e < C; ++e) s[lane * CS + e] = v[c * C + e];
+      __syncwarp();
+      for (int i = lane; i < cnt * C; i += 32) {
+        const int f = i / C, e = i - f * C;
+        dst[f * N + c * C + e] = s[f * CS + e];
+      }
+      __syncwarp();
+    }
+  }
+  __device__ __forceinline__ void resid(const double (&v)[6]) { put<6>(r, v); }
+  __device__ __forceinline__ void H0(const double (&v)[36]) { put<36>(h0, v); }
+  __device__ __forceinline__ void H1(const double (&v)[18]) { put<18>(h1, v); }
+  __device__ __forceinline__ void H2(const double (&v)[18]) { put<18>(h2, v); }
+  __device__ __forceinline__ void H3(const double (&v)[36]) { put<36>(h3, v); }
+};
+
 // ---- dynamics -----------------------------------------------------------------------------
-// smem per block: ONE staging buffer of 36 doubles/factor (36.9 KB at 128 threads).  The 30 input doubles per factor
-// are staged in it first; the outputs (6 + 36 + 18 + 18 + 36 doubles per factor) are then staged and copied out one
-// block at a time while the rest waits in registers.  (Staging all 114 output doubles at once needed 147 KB per CTA:
-// one CTA = 4 warps per SM, and ncu showed the kernel latency-bound at 6 % occupancy; this form is register-limited
-// to 2 CTAs per SM.  r02: capping the registers at 168 (3 CTAs per SM, 1.4 KB of spills per thread) is 12 % faster.)
-// MINB = minimum resident CTAs per SM the compiler must allow (register cap 65536 / (128 * MINB)): 1 = no cap (255
-// registers, 2 CTAs per SM by registers), 3 / 4 = 168 / 128 registers with spills to local memory (A/B: PB200_DYN_MINB)
+// One thread per factor; fm::dynamics_factor_io (factors_math.h) re-reads its inputs from the CTA's staged copy, parks the
+// increment and the relative pose in shared memory and hands every output block to the warp's staging slice as soon as it
+// is complete, so that 128 registers hold the factor without spills.  smem per CTA: 30 input + 12 parked doubles per
+// factor + 4 staging slices = 52.2 KB -> 4 CTAs (16 warps) per SM.
+// r02 history at 1 M factors (profiles/r02_factors_dynamics.txt): dense 6x6 Jacobian products held in registers until a
+// CTA-wide staged copy-out 0.667 ms (168 registers, 1.4 KB of spills) -> block-triangular products + per-warp staging
+// 0.481 -> closed-form coefficient matrices, no spills 0.469 -> batched input loads 0.345 ms = 3.34 TB/s.
+// MINB = minimum resident CTAs per SM the compiler must allow (register cap 65536 / (128 * MINB)); default 4
+// (PB200_DYN_MINB=1/3/5/6 for A/B: 0.435 / 0.358 / 0.360 / 0.394 ms)
 template <bool JAC, int MINB>
 __global__ void __launch_bounds__(kFacThreads, MINB)
 dynamics_kernel(const double* __restrict__ pose1, const double* __restrict__ angvel,
@@ -54,32 +117,31 @@ dynamics_kernel(const double* __restrict__ pose1, const double* __restrict__ ang
   const long long base = static_cast<long long>(blockIdx.x) * kFacThreads;
   const int cnt = static_cast<int>(min(static_cast<long long>(kFacThreads), N - base));
   double* s_p1 = sm;                       // 12 * T
-  double* s_p2 = s_p1 + 12 * kFacThreads;  // 12 * T
+  double* s_p2 = s_p1 + 12 * kFacThreads;  // 12 * T  (pose2 is dead once the relative pose exists: parked pose 1 lives here)
   double* s_w = s_p2 + 12 * kFacThreads;   // 3 * T
-  double* s_v = s_w + 3 * kFacThreads;     // 3 * T   (30 * T in all; the buffer holds 36 * T when JAC)
+  double* s_v = s_w + 3 * kFacThreads;     // 3 * T
+  double* s_st = s_v + 3 * kFacThreads;    // 12 * T: parked pose 0
+  double* s_out = s_st + 12 * kFacThreads; // 4 warps x kDynSlice: output staging
   copy_in(s_p1, pose1 + base * 12, cnt * 12);
   copy_in(s_p2, pose2 + base * 12, cnt * 12);
   copy_in(s_w, angvel + base * 3, cnt * 3);
   copy_in(s_v, vel + base * 3, cnt * 3);
-  __syncthreads();
   const int t = threadIdx.x;
-  const bool live = t < cnt;
-  double r[6], h0[JAC ? 36 : 1], h1[JAC ? 18 : 1], h2[JAC ? 18 : 1], h3[JAC ? 36 : 1];
-  if (live) {
-    const fm::Pose x1 = fm::load_pose12(s_p1 + t * 12);
-    const fm::Pose x2 = fm::load_pose12(s_p2 + t * 12);
-    const fm::V3 w = fm::v3(s_w[t * 3], s_w[t * 3 + 1], s_w[t * 3 + 2]);
-    const fm::V3 v = fm::v3(s_v[t * 3], s_v[t * 3 + 1], s_v[t * 3 + 2]);
-    if (JAC) fm::dynamics_factor(x1, w, v, x2, dt, world_frame, 1, r, h0, h1, h2, h3);
-    else fm::dynamics_factor(x1, w, v, x2, dt, world_frame, 0, r, nullptr, nullptr, nullptr, nullptr);
+  if (t >= cnt) {  // threads past the end run the factor on an identity problem of their own (results are not copied out)
+#pragma unroll
+    for (int i = 0; i < 12; ++i) s_p1[t * 12 + i] = s_p2[t * 12 + i] = (i == 0 || i == 4 || i == 8) ? 1.0 : 0.0;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) s_w[t * 3 + i] = s_v[t * 3 + i] = 0.0;
   }
-  stage_out<6>(sm, resid + base * 6, r, live, cnt);
-  if constexpr (JAC) {
-    stage_out<36>(sm, H0 + base * 36, h0, live, cnt);
-    stage_out<18>(sm, H1 + base * 18, h1, live, cnt);
-    stage_out<18>(sm, H2 + base * 18, h2, live, cnt);
-    stage_out<36>(sm, H3 + base * 36, h3, live, cnt);
-  }
+  __syncthreads();
+  const int warp = t >> 5;
+  const long long wbase = base + warp * 32;
+  const int wcnt = max(0, min(32, cnt - warp * 32));
+  DynWarpIO io{s_p1 + t * 12, s_p2 + t * 12, s_w + t * 3, s_v + t * 3, s_st + t * 12, s_p2 + t * 12,
+               s_out + warp * kDynSlice, t & 31, wcnt, resid + wbase * 6,
+               JAC ? H0 + wbase * 36 : nullptr, JAC ? H1 + wbase * 18 : nullptr, JAC ? H2 + wbase * 18 : nullptr,
+               JAC ? H3 + wbase * 36 : nullptr};
+  fm::dynamics_factor_io(io, dt, world_frame, JAC ? 1 : 0);
 }
 
 // ---- projection -----------------------------------------------------------------------------
@@ -185,32 +247,31 @@ __global__ void __launch_bounds__(kFacThreads) chain_factors_kernel(const ChainA
   copy_in(s_v, a.vel + lo * 3, nst * 3);
   __syncthreads();
   const int t = threadIdx.x;
-  const bool live = t < cnt;
-  double r[6], h0[36], h1[18], h2[18], h3[36], cv[6];
-  if (live) {
-    const int i = static_cast<int>(state_of(base + t) - lo);
-    const fm::Pose x1 = fm::load_pose12(s_pose + i * 12);
-    const fm::Pose x2 = fm::load_pose12(s_pose + (i + 1) * 12);
-    const fm::V3 w = fm::v3(s_w[i * 3], s_w[i * 3 + 1], s_w[i * 3 + 2]);
-    const fm::V3 v = fm::v3(s_v[i * 3], s_v[i * 3 + 1], s_v[i * 3 + 2]);
+  const int ti = t < cnt ? t : 0;  // lanes past the end evaluate pair 0 again (their results are not copied out)
+  const int i = static_cast<int>(state_of(base + ti) - lo);
+  double cv[6];
 #pragma unroll
-    for (int k = 0; k < 3; ++k) {  // ConstantVelocityFactor residuals (factors.py:169) of this pair
-      cv[k] = s_w[(i + 1) * 3 + k] - s_w[i * 3 + k];
-      cv[3 + k] = s_v[(i + 1) * 3 + k] - s_v[i * 3 + k];
-    }
-    fm::dynamics_factor(x1, w, v, x2, a.dt, a.world_frame, 1, r, h0, h1, h2, h3);
+  for (int k = 0; k < 3; ++k) {  // ConstantVelocityFactor residuals (factors.py:169) of this pair
+    cv[k] = s_w[(i + 1) * 3 + k] - s_w[i * 3 + k];
+    cv[3 + k] = s_v[(i + 1) * 3 + k] - s_v[i * 3 + k];
   }
-  stage_out<6>(sm, a.dyn_resid + base * 6, r, live, cnt);
+  // the states stay where they are (a pair's second state is the next pair's first): parked poses and the staging
+  // slices have their own space behind the 36 * T doubles of inputs
+  double* s_st = sm + 36 * kFacThreads;       // 24 * T
+  double* s_out = s_st + 24 * kFacThreads;    // 4 warps x kDynSlice
+  const int warp = t >> 5;
+  const long long wbase = base + warp * 32;
+  const int wcnt = max(0, min(32, cnt - warp * 32));
+  DynWarpIO io{s_pose + i * 12, s_pose + (i + 1) * 12, s_w + i * 3, s_v + i * 3, s_st + t * 24, s_st + t * 24 + 12,
+               s_out + warp * kDynSlice, t & 31, wcnt, a.dyn_resid + wbase * 6, a.H0 + wbase * 36, a.H1 + wbase * 18,
+               a.H2 + wbase * 18, a.H3 + wbase * 36};
   {
-    double c3[3] = {cv[0], cv[1], cv[2]};
-    stage_out<3>(sm, a.cvw_resid + base * 3, c3, live, cnt);
-    double d3[3] = {cv[3], cv[4], cv[5]};
-    stage_out<3>(sm, a.cvv_resid + base * 3, d3, live, cnt);
+    const double c3[3] = {cv[0], cv[1], cv[2]};
+    io.put<3>(a.cvw_resid + wbase * 3, c3);
+    const double d3[3] = {cv[3], cv[4], cv[5]};
+    io.put<3>(a.cvv_resid + wbase * 3, d3);
   }
-  stage_out<36>(sm, a.H0 + base * 36, h0, live, cnt);
-  stage_out<18>(sm, a.H1 + base * 18, h1, live, cnt);
-  stage_out<18>(sm, a.H2 + base * 18, h2, live, cnt);
-  stage_out<36>(sm, a.H3 + base * 36, h3, live, cnt);
+  fm::dynamics_factor_io(io, a.dt, a.world_frame, 1);
 }
 
 __global__ void constvel_kernel(const double* __restrict__ v1, const double* __restrict__ v2,
@@ -243,25 +304,32 @@ extern "C" int pb200_factors_dynamics(const double* pose1, const double* ang_vel
   if (N == 0) return PB200_OK;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const unsigned grid = static_cast<unsigned>((N + kFacThreads - 1) / kFacThreads);
+  // 30 inputs + 12 parked doubles per factor, 4 staging slices: 52.2 KB (4 CTAs per SM)
+  const size_t smem = sizeof(double) * (kFacThreads * 42 + 4 * kDynSlice);
+  static bool attr_set[kMaxDevices] = {};  // function attributes belong to the device's context
+  if (!attr_set[current_device()]) {
+    PB_CUDA(cudaFuncSetAttribute(dynamics_kernel<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    PB_CUDA(cudaFuncSetAttribute(dynamics_kernel<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    PB_CUDA(cudaFuncSetAttribute(dynamics_kernel<true, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    PB_CUDA(cudaFuncSetAttribute(dynamics_kernel<true, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    PB_CUDA(cudaFuncSetAttribute(dynamics_kernel<true, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    PB_CUDA(cudaFuncSetAttribute(dynamics_kernel<true, 6>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    attr_set[current_device()] = true;
+  }
   if (jac) {
-    const size_t smem = sizeof(double) * kFacThreads * 36;
-    static bool attr_set[kMaxDevices] = {};  // function attributes belong to the device's context
-    if (!attr_set[current_device()]) {
-      PB_CUDA(cudaFuncSetAttribute(dynamics_kernel<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-      PB_CUDA(cudaFuncSetAttribute(dynamics_kernel<true, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-      PB_CUDA(cudaFuncSetAttribute(dynamics_kernel<true, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-      attr_set[current_device()] = true;
-    }
     const char* e = getenv("PB200_DYN_MINB");
-    const int minb = e ? atoi(e) : 3;  // measured at 1 M pairs (r02): 0.761 / 0.667 / 0.716 ms for caps 255 / 168 / 128 registers
-    if (minb == 4)
+    const int minb = e ? atoi(e) : 4;
+    if (minb == 6)
+      dynamics_kernel<true, 6><<<grid, kFacThreads, smem, st>>>(pose1, ang_vel1, vel1, pose2, dt, world_frame, resid, H0, H1, H2, H3, N);
+    else if (minb == 5)
+      dynamics_kernel<true, 5><<<grid, kFacThreads, smem, st>>>(pose1, ang_vel1, vel1, pose2, dt, world_frame, resid, H0, H1, H2, H3, N);
+    else if (minb == 4)
       dynamics_kernel<true, 4><<<grid, kFacThreads, smem, st>>>(pose1, ang_vel1, vel1, pose2, dt, world_frame, resid, H0, H1, H2, H3, N);
     else if (minb == 3)
       dynamics_kernel<true, 3><<<grid, kFacThreads, smem, st>>>(pose1, ang_vel1, vel1, pose2, dt, world_frame, resid, H0, H1, H2, H3, N);
     else
       dynamics_kernel<true, 1><<<grid, kFacThreads, smem, st>>>(pose1, ang_vel1, vel1, pose2, dt, world_frame, resid, H0, H1, H2, H3, N);
   } else {
-    const size_t smem = sizeof(double) * kFacThreads * 30;
     dynamics_kernel<false, 1><<<grid, kFacThreads, smem, st>>>(
         pose1, ang_vel1, vel1, pose2, dt, world_frame, resid, nullptr, nullptr, nullptr, nullptr, N);
   }
@@ -332,7 +400,7 @@ extern "C" int pb200_factors_chain(const double* poses, const double* ang_vel, c
     if (nb_dyn == 0) return PB200_OK;
   }
   const size_t smem_proj = sizeof(double) * (12 * (kFacThreads + 1) + 16 * kFacThreads);
-  const size_t smem_dyn = sizeof(double) * kFacThreads * 36;
+  const size_t smem_dyn = sizeof(double) * (kFacThreads * 60 + 4 * kDynSlice);  // 36 T of states, 24 T parked, staging
   const size_t smem = smem_proj > smem_dyn ? smem_proj : smem_dyn;
   static bool attr_set[kMaxDevices] = {};
   if (!attr_set[current_device()]) {

@@ -22,6 +22,18 @@ void shim_dynamics(const double* pose1, const double* angvel, const double* vel,
   }
 }
 
+// the dense 6x6 form of the same factor (every structural zero multiplied out): cross-check of the block-triangular algebra
+void shim_dynamics_dense(const double* pose1, const double* angvel, const double* vel, const double* pose2,
+                         double dt, int world_frame, double* resid, double* H0, double* H1, double* H2, double* H3,
+                         int64_t N) {
+  for (int64_t i = 0; i < N; ++i) {
+    const Pose x1 = load_pose12(pose1 + 12 * i), x2 = load_pose12(pose2 + 12 * i);
+    const V3 w = v3(angvel[3 * i], angvel[3 * i + 1], angvel[3 * i + 2]);
+    const V3 v = v3(vel[3 * i], vel[3 * i + 1], vel[3 * i + 2]);
+    dynamics_factor_dense(x1, w, v, x2, dt, world_frame, 1, resid + 6 * i, H0 + 36 * i, H1 + 18 * i, H2 + 18 * i, H3 + 36 * i);
+  }
+}
+
 void shim_projection(const double* poses, const double* meas, const double* pts, const double* K5,
                      const double* cam12, int jac, double* resid, double* J, uint8_t* cheir,
                      int64_t N, int P) {

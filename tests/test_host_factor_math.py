@@ -59,6 +59,36 @@ def test_dynamics_matches_oracle(shim, frame):
     assert np.array_equal(res, res2)
 
 
+@pytest.mark.parametrize("frame", ["world", "body"])
+@pytest.mark.parametrize("rel_scale", [1.0, 1e-9])
+def test_block_triangular_dynamics_equals_the_dense_6x6_form(shim, frame, rel_scale):
+    """dynamics_factor multiplies the [[A,0],[B,A]] Jacobians blockwise (factors_math.h); the dense 6x6 form multiplies the
+    structural zeros out and builds the coefficient matrices (Jr, Jr^-1, Q) as GTSAM writes them, from products of skew
+    matrices, where dynamics_factor uses their outer-product closed forms: equal up to rounding, at generic poses and in the
+    small-angle branches."""
+    N = 3000
+    R1, t1, R2, t2, w, v = random_problem(N, 3)
+    if rel_scale < 1.0:  # x2 ~ x1 * Exp(dt * twist): the logarithm's and the Jacobians' small-angle branches
+        w, v = w * rel_scale, v * rel_scale
+        R2, t2 = R1.copy(), t1.copy()
+    p1, p2 = pose12(R1, t1), pose12(R2, t2)
+    out = []
+    for dense in (False, True):
+        res = np.zeros((N, 6))
+        H0, H1, H2, H3 = np.zeros((N, 36)), np.zeros((N, 18)), np.zeros((N, 18)), np.zeros((N, 36))
+        if dense:
+            shim.shim_dynamics_dense(_p(p1), _p(w), _p(v), _p(p2), ctypes.c_double(0.1), int(frame == "world"),
+                                     _p(res), _p(H0), _p(H1), _p(H2), _p(H3), ctypes.c_int64(N))
+        else:
+            shim.shim_dynamics(_p(p1), _p(w), _p(v), _p(p2), ctypes.c_double(0.1), int(frame == "world"), 1,
+                               _p(res), _p(H0), _p(H1), _p(H2), _p(H3), ctypes.c_int64(N))
+        out.append((res, H0, H1, H2, H3))
+    for a, b in zip(*out):
+        assert np.isfinite(a).all()
+        scale = max(1.0, float(np.abs(b).max()))
+        assert np.abs(a - b).max() <= 2e-12 * scale, float(np.abs(a - b).max())
+
+
 def test_so3_log_branches(shim):
     rng = np.random.default_rng(3)
     ax = rng.standard_normal((64, 3))

@@ -15,7 +15,7 @@ pose = torch.cat([R, t], -1).to(dev)
 wv, vv = torch.randn(n, 3, generator=g, dtype=torch.float64).to(dev), torch.randn(n, 3, generator=g, dtype=torch.float64).to(dev)
 res = {}
 ref = None
-for minb in ("1", "3", "4"):
+for minb in (sys.argv[1:] or ("1", "3", "4", "5", "6")):
     os.environ["PB200_DYN_MINB"] = minb
     for _ in range(3):
         r, H = pose_dynamics_batch(pose[0], wv, vv, pose[1], 0.1)

@@ -1,4 +1,4 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 300 python tools/e2e_probe.py bf16 > gpurun_out/g_e2e_probe.json 2> gpurun_out/g_e2e_probe.err; echo "probe exit $?"; cat gpurun_out/g_e2e_probe.json; tail -3 gpurun_out/g_e2e_probe.err
-PB200_NO_PDL=1 timeout 300 python tools/e2e_probe.py bf16 > gpurun_out/g_e2e_probe_nopdl.json 2> gpurun_out/g_e2e_probe_nopdl.err; echo "probe nopdl exit $?"; cat gpurun_out/g_e2e_probe_nopdl.json
+timeout 200 python tools/factors_ab.py 4 > gpurun_out/g_plain.json 2>&1 || exit 0
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:dynamics_kernel -s 3 -c 1 -o gpurun_out/g_dyn python tools/factors_ab.py 4 > gpurun_out/g_ncu.log 2>&1; echo "ncu exit $?"; tail -3 gpurun_out/g_ncu.log
