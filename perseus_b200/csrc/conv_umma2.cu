@@ -52,7 +52,9 @@ __device__ __forceinline__ unsigned ld_acquire_gpu(const unsigned* p) {
   asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
-__device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
+// (the form without a state space compiles to MEMBAR.ALL.GPU + FENCE.VIEW.ASYNC: in a TMA producer loop the MEMBAR waits for
+// the warp's own bulk copies in flight and serialises the pipeline; .global is the FENCE.VIEW.ASYNC.G alone)
+__device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async.global;" ::: "memory"); }
 
 template <int BLOCK_N, bool X2, bool RESB, bool CHAIN>
 __device__ __forceinline__ void pair_body(const UmmaConvMaps* __restrict__ mapsv, const UmmaConvParams* __restrict__ pv,
