@@ -48,47 +48,6 @@ struct ConvP8Params {
   long long plane_bytes;    // bytes per P8 chunk plane
 };
 
-// CHAIN: the two convolutions of a layer1 BasicBlock in ONE persistent launch (conv_p8_chain_kernel).  The work list walks
-// the batch in GROUPS of images -- all tiles of conv 0 of the group, then conv 1, then the next group -- so that what
-// conv 1 reads (conv 0's output and the block input as its residual) was written / read a few hundred tiles earlier and
-// is still in L2: one launch per conv, the residual convs are HBM-bound (3 x 140 MB per launch: 0.084-0.090 ms against
-// 0.063 ms without a residual).  A tile of conv 1 waits (producer warp, ld.acquire spin) until the counter of (conv 0,
-// its image) shows that all tiles of that image have been stored; every epilogue warp bumps the counter of its
-// (conv, image) after its stores.  All CTAs are co-resident and dependencies point backwards in the list: no deadlock.
-// The weights of both convs stay resident (2 x 36 KB per CTA of a pair) next to four whole-tile patch stages.  (All FOUR
-// layer1 convs in one launch left room for two tiles of patches only: 0.61 ms instead of 0.31, bound by the latency of
-// the patch loads.)
-struct ConvP8ChainInfo {
-  int nconv, B, group;          // images per group
-  int seg_full, seg_last;       // work items per (group, conv): tiles of the group's images rounded up to an even count
-  int ngroups, total_items;     // total_items is even: a pair's two tiles always belong to the same conv
-  int target;                   // arrivals that complete an image: tiles_per_img x epilogue warps
-  int defer;                    // 1: an epilogue warp publishes a tile two tiles late (see the epilogue); 0: at once
-  unsigned tpi_magic;           // ceil(2^32 / tiles_per_img): k / tiles_per_img = umulhi(k, magic) for every k of a segment
-  int dep[kP8Chain];            // conv whose output conv c reads as its INPUT (-1: an earlier launch)
-  int res_dep[kP8Chain];        // conv whose output conv c reads as its RESIDUAL (-1: none / an earlier launch)
-  unsigned* cnt;                // [nconv][B] arrival counters + 1 ticket; zero before the launch, zero after it
-};
-struct ConvP8ChainArgs {
-  ConvP8Params c[kP8Chain];
-  ConvP8ChainInfo info;
-};
-
-__device__ __forceinline__ unsigned p8_ld_acquire(const unsigned* p) {
-  unsigned v;
-  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-// (the form without a state space compiles to MEMBAR.ALL.GPU + FENCE.VIEW.ASYNC: in a TMA producer loop the MEMBAR waits for
-// the warp's own bulk copies in flight and serialises the pipeline; .global is the FENCE.VIEW.ASYNC.G alone)
-__device__ __forceinline__ void p8_fence_proxy_async() { asm volatile("fence.proxy.async.global;" ::: "memory"); }
-
-struct P8Work {  // one work item
-  int c;      // conv of the chain (0 when not chained)
-  int n, ti;  // image and tile of the image
-  bool live;  // false: padding item (the peer of an odd last tile): runs, stores nothing
-};
-
 // kEpiWarps = 4 (thread = position x 64 channels) or 8 (x 32 channels).  With 4 the epilogue has ONE warp per scheduler
 // and its ~350 dependent instructions per tile take longer than the tile's 36 MMAs (1728 cycles): latency-bound.
 //
@@ -97,19 +56,15 @@ struct P8Work {  // one work item
 // [0, 64) = A.W_hi and [64, 128) = A.W_lo from a single read of the A rows -- 64 cycles per K step instead of the
 // 2 x 48 of two N = 64 MMAs (the N = 64 MMA is bound by its operand fetch, tools/mma_bench.cu).  The epilogue adds the
 // two column groups.  144 KB of resident weights leave room for two patch stages.
-template <int kEpiWarps, bool X2, bool PAIR = false, bool CHAIN = false>
-__device__ __forceinline__ void conv_p8_body(const ConvP8Params* __restrict__ pv, const ConvP8ChainInfo* __restrict__ ci) {
-  static_assert(!CHAIN || (PAIR && !X2), "the chained launch is the bf16 CTA-pair kernel");
-  const ConvP8Params& p = pv[0];  // geometry (identical for every conv of a chain)
-  constexpr int kConvs = CHAIN ? kP8Chain : 1;
+template <int kEpiWarps, bool X2, bool PAIR = false>
+__device__ __forceinline__ void conv_p8_body(const ConvP8Params& p) {
   // X2: the 144 KB of weights leave 67 KB for patches = two whole-tile stages, i.e. ONE tile of prefetch (1.2 us of
   // MMAs) against ~2 us of patch latency.  The ring is therefore cut into HALF-tile stages (4 of the 8 channel chunks
   // each, 4 stages): the producer runs three half-stages ahead of the MMAs.
   // PAIR: each CTA keeps half of the weight rows (36 / 72 KB): room for 5 / 4 WHOLE-tile stages.
-  // CHAIN: 2 x 36 KB of weights: four whole-tile stages.
   constexpr int kSplit = (X2 && !PAIR) ? 2 : 1;    // stages per tile
   constexpr int kStageChunks = kChunks / kSplit;   // channel chunks per stage
-  constexpr int kStages = (PAIR && !X2 && !CHAIN) ? 5 : 4;
+  constexpr int kStages = (PAIR && !X2) ? 5 : 4;
   constexpr int kWAll = (X2 ? 2 * kWBytes : kWBytes) / (PAIR ? 2 : 1);  // resident weight bytes of THIS CTA
   constexpr int kAccCols = X2 ? 128 : 64;
   constexpr int kNch = 8 / (kEpiWarps / 4);  // 8-channel chunks (P8 planes) per epilogue thread
@@ -120,13 +75,12 @@ __device__ __forceinline__ void conv_p8_body(const ConvP8Params* __restrict__ pv
   __shared__ __align__(8) uint64_t tmem_full_bar[2];
   __shared__ __align__(8) uint64_t tmem_empty_bar[2];
   __shared__ uint32_t tmem_base_slot;
-  __shared__ float s_bias[64 * kConvs];
-  __shared__ int s_verified;  // CHAIN: last work item whose input dependency the producer warp has acquired
+  __shared__ float s_bias[64];
 
   const uint32_t raw_addr = smem_u32(smem_raw);
   uint8_t* smem = smem_raw + (((raw_addr + 127u) & ~127u) - raw_addr);
-  uint8_t* s_w = smem;                      // conv c's resident weights at + c * kWAll
-  uint8_t* s_patch = smem + kConvs * kWAll;
+  uint8_t* s_w = smem;
+  uint8_t* s_patch = smem + kWAll;
   const int stage_bytes = kStageChunks * p.patch_pitch;
 
   const int warp = threadIdx.x >> 5;
@@ -135,63 +89,8 @@ __device__ __forceinline__ void conv_p8_body(const ConvP8Params* __restrict__ pv
   const bool leader = crank == 0;
   // PAIR: blockIdx.x = 2 * pair + crank, so "tile = blockIdx.x + i * gridDim.x" hands the pair tiles 2j and 2j+1; both
   // CTAs run as long as the LEADER's tile exists (the peer of an odd last tile re-reads it and stores nothing)
-  const int total_items = CHAIN ? ci->total_items : p.num_tiles;
-  auto alive = [&](int item) { return item - crank < total_items; };
-  // Position in the work list.  CHAIN: (group g, conv c, index k inside the (g, c) segment), stepped incrementally -- a
-  // full decode costs three runtime divisions, and every role needs one per tile (the epilogue, already latency-bound,
-  // two): with decode-per-tile the chained launch ran 1.75x slower than four plain launches.
-  struct Cursor {
-    int item, g, c, k;
-  };
-  auto cur_init = [&](int item) {
-    Cursor q{item, 0, 0, 0};
-    if constexpr (CHAIN) {
-      const int ipg = ci->nconv * ci->seg_full;  // items per full group
-      q.g = item / ipg;
-      if (q.g > ci->ngroups - 1) q.g = ci->ngroups - 1;
-      const int r = item - q.g * ipg;
-      const int seg = q.g == ci->ngroups - 1 ? ci->seg_last : ci->seg_full;
-      q.c = r / seg;
-      q.k = r - q.c * seg;
-    }
-    return q;
-  };
-  auto cur_advance = [&](Cursor& q, int stride) {
-    q.item += stride;
-    if constexpr (CHAIN) {
-      q.k += stride;
-      while (q.g < ci->ngroups) {
-        const int seg = q.g == ci->ngroups - 1 ? ci->seg_last : ci->seg_full;
-        if (q.k < seg) break;
-        q.k -= seg;
-        if (++q.c == ci->nconv) {
-          q.c = 0;
-          ++q.g;
-        }
-      }
-    }
-  };
-  auto work_of = [&](const Cursor& q) {
-    P8Work w;
-    if constexpr (CHAIN) {
-      const int g = q.g < ci->ngroups ? q.g : ci->ngroups - 1;  // (past the end: never used, kept in range)
-      const int ng = g == ci->ngroups - 1 ? ci->B - g * ci->group : ci->group;  // images of this group
-      w.c = q.c < ci->nconv ? q.c : 0;
-      w.live = q.g < ci->ngroups && q.k < ng * p.tiles_per_img;
-      const int kk = w.live ? q.k : 0;
-      const int nn = static_cast<int>(__umulhi(static_cast<unsigned>(kk), ci->tpi_magic));  // kk / tiles_per_img (host-checked)
-      w.n = g * ci->group + nn;
-      w.ti = kk - nn * p.tiles_per_img;
-    } else {
-      w.c = 0;
-      w.live = q.item < p.num_tiles;
-      const int t = w.live ? q.item : p.num_tiles - 1;
-      w.n = t / p.tiles_per_img;
-      w.ti = t - w.n * p.tiles_per_img;
-    }
-    return w;
-  };
-  if (threadIdx.x == 0) s_verified = -1;
+  auto alive = [&](int tile) { return tile - crank < p.num_tiles; };
+
   if (threadIdx.x == 0) {
     // PAIR: the leader's full / weight barriers also take one arrival relayed from the peer (its patch / weights landed);
     // the leader's accumulator-free barriers take both CTAs' epilogue warps
@@ -216,10 +115,7 @@ __device__ __forceinline__ void conv_p8_body(const ConvP8Params* __restrict__ pv
       tmem_relinquish();
     }
   }
-  if (threadIdx.x >= 64 && threadIdx.x < 128) {
-#pragma unroll
-    for (int c = 0; c < kConvs; ++c) s_bias[c * 64 + threadIdx.x - 64] = __ldg(pv[c].bias + threadIdx.x - 64);
-  }
+  if (threadIdx.x >= 64 && threadIdx.x < 128) s_bias[threadIdx.x - 64] = __ldg(p.bias + threadIdx.x - 64);
   tc_fence_before();
   __syncthreads();
   if constexpr (PAIR) cluster_sync_all();
@@ -231,51 +127,19 @@ __device__ __forceinline__ void conv_p8_body(const ConvP8Params* __restrict__ pv
     // ================================ producer ====================================
     // the whole warp runs the loop (operands stay warp-uniform); one elected lane issues the copies
     if (elect_one()) {
-      // plan constants: fetched while the previous kernel drains (PDL).  PAIR: this CTA's half of the rows
-      mbar_expect_tx(&w_bar, kConvs * kWAll);
-#pragma unroll
-      for (int c = 0; c < kConvs; ++c) bulk_load_1d(s_w + c * kWAll, pv[c].wimg + crank * kWAll, kWAll, &w_bar);
+      mbar_expect_tx(&w_bar, kWAll);
+      // plan constant: fetched while the previous kernel drains (PDL).  PAIR: this CTA's half of the rows
+      bulk_load_1d(s_w, p.wimg + crank * kWAll, kWAll, &w_bar);
     }
     pdl_wait();  // the input patches are the previous kernel's output
     int stage = 0;
     uint32_t phase = 0;
     const uint32_t chunk_bytes = static_cast<uint32_t>(p.npos) * 16u;
-    // CHAIN: the counter a tile depends on is read one tile EARLY (the acquire load is issued before the previous tile's
-    // copies and consumed here): a blocking L2 round trip per tile made the producer the bottleneck
-    auto dep_counter = [&](const P8Work& w) -> const unsigned* {
-      if constexpr (CHAIN) {
-        if (w.live && ci->dep[w.c] >= 0) return ci->cnt + ci->dep[w.c] * ci->B + w.n;
-      }
-      return nullptr;
-    };
-    Cursor cur = cur_init(blockIdx.x);
-    P8Work wk = work_of(cur);
-    const unsigned* dep_ptr = alive(cur.item) ? dep_counter(wk) : nullptr;
-    unsigned dep_val = dep_ptr != nullptr ? p8_ld_acquire(dep_ptr) : 0u;
-    while (alive(cur.item)) {
-      const int item = cur.item;
-      const int q0 = wk.ti * 128;
-      const uint8_t* src = pv[wk.c].in + wk.n * p.img_bytes + static_cast<long long>(q0) * 16;
-      if constexpr (CHAIN) {
-        // every tile of this image must have been stored by the conv that produces this conv's input
-        if (dep_ptr != nullptr) {
-          const unsigned want = static_cast<unsigned>(ci->target);
-          unsigned spins = 0;
-          while (dep_val < want) {
-            __nanosleep(40);
-            if (++spins > (1u << 24)) __trap();  // ~1 s: a lost arrival must not hang the GPU
-            dep_val = p8_ld_acquire(dep_ptr);
-          }
-          p8_fence_proxy_async();  // the bulk copies below (async proxy) read what those generic-proxy stores wrote
-        }
-        // tell the epilogue warps (release / acquire at CTA scope: causality carries the acquire above over to them)
-        if (lane == 0) asm volatile("st.release.cta.shared.s32 [%0], %1;" ::"r"(smem_u32(&s_verified)), "r"(item) : "memory");
-      }
-      // the next item (and its counter, read now)
-      cur_advance(cur, gridDim.x);
-      const P8Work wk_next = work_of(cur);
-      dep_ptr = alive(cur.item) ? dep_counter(wk_next) : nullptr;
-      if (dep_ptr != nullptr) dep_val = p8_ld_acquire(dep_ptr);
+    for (int tile = blockIdx.x; alive(tile); tile += gridDim.x) {
+      const int tl = tile < p.num_tiles ? tile : p.num_tiles - 1;
+      const int n = tl / p.tiles_per_img;
+      const int q0 = (tl - n * p.tiles_per_img) * 128;
+      const uint8_t* src = p.in + n * p.img_bytes + static_cast<long long>(q0) * 16;
 #pragma unroll
       for (int h = 0; h < kSplit; ++h) {
         mbar_wait(&empty_bar[stage], phase ^ 1u);
@@ -292,7 +156,6 @@ __device__ __forceinline__ void conv_p8_body(const ConvP8Params* __restrict__ pv
           phase ^= 1u;
         }
       }
-      wk = wk_next;
     }
   } else if (warp == 1) {
     // ================================ MMA issuer ==================================
@@ -305,16 +168,13 @@ __device__ __forceinline__ void conv_p8_body(const ConvP8Params* __restrict__ pv
       if (lane == 0) mbar_arrive_cluster(lw);
       int stage = 0;
       uint32_t phase = 0;
-      for (int item = blockIdx.x; alive(item); item += gridDim.x) {
-#pragma unroll
-        for (int h = 0; h < kSplit; ++h) {
-          mbar_wait(&full_bar[stage], phase);
-          if (lane == 0) mbar_arrive_cluster(lfull0 + stage * 8);
-          __syncwarp();
-          if (++stage == kStages) {
-            stage = 0;
-            phase ^= 1u;
-          }
+      for (int tile = blockIdx.x; alive(tile); tile += gridDim.x) {
+        mbar_wait(&full_bar[stage], phase);
+        if (lane == 0) mbar_arrive_cluster(lfull0 + stage * 8);
+        __syncwarp();
+        if (++stage == kStages) {
+          stage = 0;
+          phase ^= 1u;
         }
       }
     } else {
@@ -328,11 +188,8 @@ __device__ __forceinline__ void conv_p8_body(const ConvP8Params* __restrict__ pv
       int stage = 0;
       uint32_t phase = 0;
       int it = 0;
-      Cursor cur = cur_init(blockIdx.x);
-      for (; cur.item < total_items; cur_advance(cur, gridDim.x), ++it) {
+      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
         const int acc = it & 1;
-        // CHAIN: conv c's weights sit c * kWAll further (a pair's two items belong to the same conv)
-        const uint32_t b_conv = CHAIN ? b_lo0 + static_cast<uint32_t>(cur.c) * (kWAll >> 4) : b_lo0;
         mbar_wait(&tmem_empty_bar[acc], ((it >> 1) & 1u) ^ 1u);
 #pragma unroll
         for (int h = 0; h < kSplit; ++h) {
@@ -341,25 +198,16 @@ __device__ __forceinline__ void conv_p8_body(const ConvP8Params* __restrict__ pv
           if (elect_one()) {
             const uint32_t d_tmem = tm + acc * kAccCols;
             const uint32_t a_lo0 = desc_lo(smem_u32(s_patch) + stage * stage_bytes, p.patch_pitch);
-            // K order of EVERY variant: channel half (32 channels) outermost, then the nine taps, then the half's two
-            // K = 16 steps -- the order the half-tile stages impose -- so that all layer1 kernels (single CTA, pair,
-            // chained; whole- or half-tile stages) produce bit-identical accumulators
-            constexpr int kHalves = 2 / kSplit;  // channel halves inside one stage
 #pragma unroll
-            for (int hh = 0; hh < kHalves; ++hh) {
-              const int gh = h * kHalves + hh;  // channel half of the tile
+            for (int t = 0; t < 9; ++t) {
+              const int r = t / 3, s = t - 3 * r;
+              const uint32_t a_tap = a_lo0 + static_cast<uint32_t>(r * p.Wp + s);  // (r*Wp + s) * 16 B >> 4
 #pragma unroll
-              for (int t = 0; t < 9; ++t) {
-                const int r = t / 3, s = t - 3 * r;
-                const uint32_t a_tap = a_lo0 + static_cast<uint32_t>(r * p.Wp + s);  // (r*Wp + s) * 16 B >> 4
-#pragma unroll
-                for (int kk = 0; kk < 2; ++kk) {  // K = 16 = two channel chunks
-                  const uint32_t b_lo = b_conv + (t * 8 + gh * 4 + 2 * kk) * 8;
-                  const uint32_t accum = (gh | t | kk) != 0 ? 1u : 0u;
-                  const uint32_t a_k = a_tap + static_cast<uint32_t>(2 * (hh * 2 + kk)) * pitch16;
-                  if constexpr (PAIR) umma2_bf16_split(d_tmem, a_k, a_hi, b_lo, b_hi, idesc, accum);
-                  else umma_bf16_split(d_tmem, a_k, a_hi, b_lo, b_hi, idesc, accum);
-                }
+              for (int kk = 0; kk < kStageChunks / 2; ++kk) {  // K = 16 = two channel chunks of this stage
+                const uint32_t b_lo = b_lo0 + (t * 8 + h * kStageChunks + 2 * kk) * 8;
+                const uint32_t accum = (h | t | kk) != 0 ? 1u : 0u;
+                if constexpr (PAIR) umma2_bf16_split(d_tmem, a_tap + 2 * kk * pitch16, a_hi, b_lo, b_hi, idesc, accum);
+                else umma_bf16_split(d_tmem, a_tap + 2 * kk * pitch16, a_hi, b_lo, b_hi, idesc, accum);
               }
             }
             if constexpr (PAIR) {
@@ -386,35 +234,20 @@ __device__ __forceinline__ void conv_p8_body(const ConvP8Params* __restrict__ pv
     const int m = q * 32 + lane;
     const long long plane16 = p.plane_bytes / 16;
     int it = 0;
+    const bool has_res = p.residual != nullptr;
     // residual tiles of THIS thread's row: loaded TWO tiles ahead into two register sets (one tile of lead, ~1.3 us,
-    // still left the epilogue waiting on HBM for the residual at the top of every tile).  CHAIN: a residual written
-    // earlier in this launch is prefetched only once its image's counter shows it complete (else it is loaded when the
-    // tile is processed: its accumulator being ready implies the producer's wait for the image has passed), and it is
-    // read through L2 (another SM wrote it).
+    // still left the epilogue waiting on HBM for the residual at the top of every tile)
     uint4 rv0[kNch], rv1[kNch];
-    bool have0 = false, have1 = false;
-    int pend0 = -1, pend1 = -1;  // CHAIN: counters of the last two tiles, published two tiles late
-    auto load_residual = [&](int item, const P8Work& wk, uint4 (&rv)[kNch], bool at_process) -> bool {
-      if (!alive(item)) return true;
-      const ConvP8Params& pc = pv[wk.c];
+    auto load_residual = [&](int tile, uint4 (&rv)[kNch]) {
       bool ok = false;
-      if (pc.residual != nullptr && wk.live) {
-        if constexpr (CHAIN) {
-          // a residual written in THIS launch (conv 3 reads conv 1's output): its image is complete once the producer
-          // warp has acquired this item's input dependency (conv 2 of the image done implies conv 1 of it done); the
-          // producer publishes the last item it has verified.  at_process: the accumulator is ready, so it has.
-          if (!at_process && ci->res_dep[wk.c] >= 0) {
-            int ver;
-            asm volatile("ld.acquire.cta.shared.s32 %0, [%1];" : "=r"(ver) : "r"(smem_u32(&s_verified)) : "memory");
-            if (ver < item) return false;
-          }
-        }
-        const int q0 = wk.ti * 128 + m;
+      if (has_res && tile < p.num_tiles) {  // (a peer tile past the end loads nothing)
+        const int n = tile / p.tiles_per_img;
+        const int q0 = (tile - n * p.tiles_per_img) * 128 + m;
         const int h = q0 / p.Wp;
         if (q0 < p.H * p.Wp && q0 - h * p.Wp < p.W) {
-          const uint4* res = reinterpret_cast<const uint4*>(pc.residual + wk.n * p.img_bytes) + q0 + p.Wp + 1;
+          const uint4* res = reinterpret_cast<const uint4*>(p.residual + n * p.img_bytes) + q0 + p.Wp + 1;
 #pragma unroll
-          for (int j = 0; j < kNch; ++j) rv[j] = CHAIN ? __ldcg(res + (j0 + j) * plane16) : __ldg(res + (j0 + j) * plane16);
+          for (int j = 0; j < kNch; ++j) rv[j] = __ldg(res + (j0 + j) * plane16);
           ok = true;
         }
       }
@@ -422,30 +255,17 @@ __device__ __forceinline__ void conv_p8_body(const ConvP8Params* __restrict__ pv
 #pragma unroll
         for (int j = 0; j < kNch; ++j) rv[j] = make_uint4(0, 0, 0, 0);
       }
-      return true;
     };
-    // two interleaved item sequences, one per residual register set; a cursor always stands on the item whose residual
-    // its register set holds (or will hold)
-    Cursor cur0 = cur_init(blockIdx.x), cur1 = cur_init(blockIdx.x + gridDim.x);
-    P8Work wk0 = work_of(cur0), wk1 = work_of(cur1);
-    have0 = load_residual(cur0.item, wk0, rv0, false);
-    have1 = load_residual(cur1.item, wk1, rv1, false);
+    load_residual(blockIdx.x, rv0);
+    load_residual(blockIdx.x + gridDim.x, rv1);
     float bias[8 * kNch];
 #pragma unroll
     for (int e = 0; e < 8 * kNch; ++e) bias[e] = s_bias[8 * j0 + e];
     const uint32_t lempty0 = PAIR ? mapa_u32(&tmem_empty_bar[0], 0) : 0u;
-    auto process = [&](Cursor& cur, P8Work& wk_io, uint4 (&rv)[kNch], bool& have) {
-      const int item = cur.item;
-      const P8Work wk = wk_io;
-      const ConvP8Params& pc = pv[wk.c];  // this item's conv (pointers, relu, output layout)
-      const bool live = wk.live;          // false only for a padding item (the peer of an odd last tile)
-      const bool has_res = pc.residual != nullptr;
-      const int n = wk.n;
-      const int ti = wk.ti;
-      if constexpr (CHAIN) {
-#pragma unroll
-        for (int e = 0; e < 8 * kNch; ++e) bias[e] = s_bias[wk.c * 64 + 8 * j0 + e];
-      }
+    auto process = [&](int tile, uint4 (&rv)[kNch]) {
+      const bool live = tile < p.num_tiles;  // false only for the peer of an odd last tile
+      const int n = tile / p.tiles_per_img;
+      const int ti = tile - n * p.tiles_per_img;
       const int q0 = ti * 128 + m;
       const int h = q0 / p.Wp;
       const int w = q0 - h * p.Wp;
@@ -453,24 +273,7 @@ __device__ __forceinline__ void conv_p8_body(const ConvP8Params* __restrict__ pv
       const bool valid = in_plane && w < p.W;
       const int a = it & 1;
       const long long opos = static_cast<long long>(q0) + p.Wp + 1;  // padded position of this output
-      if (!have) have = load_residual(item, wk, rv, false);  // CHAIN: usually verified by now; overlaps the rest of the MMAs
-      if constexpr (CHAIN) {
-        // a warp that waits long for its accumulator publishes what it holds back: the producer of this CTA may be
-        // spinning on a tile whose owner is in turn waiting for one of OUR unpublished tiles
-        int polls = 0;
-        while (!mbar_try_wait(&tmem_full_bar[a], (it >> 1) & 1u)) {  // (suspends; a hot test_wait loop steals issue slots)
-          if (++polls == 8 && (pend0 >= 0 || pend1 >= 0)) {
-            __threadfence();
-            p8_fence_proxy_async();
-            __syncwarp();
-            if (lane == 0 && pend0 >= 0) atomicAdd(ci->cnt + pend0, 1u);
-            if (lane == 0 && pend1 >= 0) atomicAdd(ci->cnt + pend1, 1u);
-            pend0 = pend1 = -1;
-          }
-        }
-      } else {
-        mbar_wait(&tmem_full_bar[a], (it >> 1) & 1u);
-      }
+      mbar_wait(&tmem_full_bar[a], (it >> 1) & 1u);
       tc_fence_after();
       const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + a * kAccCols + 8 * j0;
       uint32_t x[kNch / 4][32];
@@ -495,7 +298,6 @@ __device__ __forceinline__ void conv_p8_body(const ConvP8Params* __restrict__ pv
         if (leader) mbar_arrive(&tmem_empty_bar[a]);
         else mbar_arrive_cluster(lempty0 + a * 8);
       }
-      if (!have) have = load_residual(item, wk, rv, true);  // CHAIN: the prefetch found the residual not yet written
 
       uint4 o[kNch];
 #pragma unroll
@@ -510,7 +312,7 @@ __device__ __forceinline__ void conv_p8_body(const ConvP8Params* __restrict__ pv
           f[4] += lo16<X2>(rv[j].z); f[5] += hi16<X2>(rv[j].z);
           f[6] += lo16<X2>(rv[j].w); f[7] += hi16<X2>(rv[j].w);
         }
-        if (pc.relu) {
+        if (p.relu) {
 #pragma unroll
           for (int e = 0; e < 8; ++e) f[e] = fmaxf(f[e], 0.f);
         }
@@ -518,24 +320,8 @@ __device__ __forceinline__ void conv_p8_body(const ConvP8Params* __restrict__ pv
                                   pack16x2<X2>(f[6], f[7]))
                      : make_uint4(0, 0, 0, 0);
       }
-      if constexpr (CHAIN) {
-        // publish the tile processed TWO tiles ago: its stores were issued ~2 us ago, so the fence finds them done.  BEFORE the
-        // residual prefetch below: the fence (MEMBAR) would wait for those loads as well
-        // (fencing right behind a tile's own stores put their round trip on the epilogue's critical path: 2x slower)
-        if (pend0 >= 0) {
-          __threadfence();
-          p8_fence_proxy_async();
-          __syncwarp();
-          if (lane == 0) atomicAdd(ci->cnt + pend0, 1u);
-        }
-        pend0 = pend1;
-        pend1 = (ci->defer && live && wk.c < ci->nconv - 1) ? wk.c * ci->B + n : -1;
-      }
-      // rv is dead from here on: step this sequence's cursor and prefetch the residual of its next tile (the tile after next)
-      cur_advance(cur, 2 * gridDim.x);
-      wk_io = work_of(cur);
-      have = load_residual(cur.item, wk_io, rv, false);
-      if (pc.out_nhwc) {
+      load_residual(tile + 2 * gridDim.x, rv);  // rv is dead from here on: prefetch the residual of the tile after next
+      if (p.out_nhwc) {
         // NHWC pixel = 8 chunks = one 128-byte line.  A lane holds kNch chunks of ITS position; storing them directly
         // makes every store instruction touch 32 different lines with 16 bytes each.  A kNch x kNch transpose inside
         // each group of kNch lanes (butterfly stages of 16-byte shuffles) turns lane l into the owner of chunk
@@ -562,10 +348,10 @@ __device__ __forceinline__ void conv_p8_body(const ConvP8Params* __restrict__ pv
 #pragma unroll
         for (int j = 0; j < kNch; ++j) {
           const long long pix = __shfl_sync(0xffffffffu, own, (lane & ~(kNch - 1)) + j);
-          if (pix >= 0) reinterpret_cast<uint4*>(pc.out)[pix * 8 + j0 + ln] = o[j];
+          if (pix >= 0) reinterpret_cast<uint4*>(p.out)[pix * 8 + j0 + ln] = o[j];
         }
       } else {
-        uint4* oimg = reinterpret_cast<uint4*>(pc.out + n * p.img_bytes);
+        uint4* oimg = reinterpret_cast<uint4*>(p.out + n * p.img_bytes);
         if (in_plane) {
 #pragma unroll
           for (int j = 0; j < kNch; ++j) oimg[(j0 + j) * plane16 + opos] = o[j];
@@ -581,29 +367,11 @@ __device__ __forceinline__ void conv_p8_body(const ConvP8Params* __restrict__ pv
           for (int j = 0; j < kNch; ++j) oimg[(j0 + j) * plane16 + bpos] = make_uint4(0, 0, 0, 0);
         }
       }
-      if constexpr (CHAIN) {
-        if (!ci->defer && live && wk.c < ci->nconv - 1) {  // short segments: publish at once (a late publish could deadlock)
-          __threadfence();
-          p8_fence_proxy_async();
-          __syncwarp();
-          if (lane == 0) atomicAdd(ci->cnt + wk.c * ci->B + n, 1u);
-        }
-      }
       ++it;
     };
-    while (alive(cur0.item)) {
-      process(cur0, wk0, rv0, have0);
-      if (!alive(cur1.item)) break;  // (then the next item of sequence 0 does not exist either)
-      process(cur1, wk1, rv1, have1);
-    }
-    if constexpr (CHAIN) {  // the last two tiles
-      if (pend0 >= 0 || pend1 >= 0) {
-        __threadfence();
-        p8_fence_proxy_async();
-        __syncwarp();
-        if (lane == 0 && pend0 >= 0) atomicAdd(ci->cnt + pend0, 1u);
-        if (lane == 0 && pend1 >= 0) atomicAdd(ci->cnt + pend1, 1u);
-      }
+    for (int tile = blockIdx.x; alive(tile); tile += 2 * gridDim.x) {
+      process(tile, rv0);
+      if (alive(tile + static_cast<int>(gridDim.x))) process(tile + gridDim.x, rv1);
     }
   }
 
@@ -615,35 +383,15 @@ __device__ __forceinline__ void conv_p8_body(const ConvP8Params* __restrict__ pv
     if constexpr (PAIR) tmem_dealloc2(tmem_base, 2 * kAccCols);
     else tmem_dealloc(tmem_base, 2 * kAccCols);
   }
-  if constexpr (CHAIN) {
-    // every wait of this CTA is behind it: the last CTA to get here re-arms the counters for the next launch
-    __shared__ unsigned s_ticket;
-    const int ncnt = ci->nconv * ci->B;
-    unsigned* fin = ci->cnt + ncnt;
-    if (threadIdx.x == 0) {
-      __threadfence();
-      s_ticket = atomicAdd(fin, 1u);
-    }
-    __syncthreads();
-    if (s_ticket == gridDim.x - 1) {
-      for (int i = threadIdx.x; i < ncnt; i += blockDim.x) ci->cnt[i] = 0u;
-      if (threadIdx.x == 0) *fin = 0u;
-      __threadfence();
-    }
-  }
 }
 
-__global__ void __launch_bounds__(p8_threads(8), 1) conv_p8_kernel(const ConvP8Params p) { conv_p8_body<8, false>(&p, nullptr); }
-__global__ void __launch_bounds__(p8_threads(4), 1) conv_p8_kernel4(const ConvP8Params p) { conv_p8_body<4, false>(&p, nullptr); }
-__global__ void __launch_bounds__(p8_threads(8), 1) conv_p8_x2_kernel(const ConvP8Params p) { conv_p8_body<8, true>(&p, nullptr); }
-__global__ void __launch_bounds__(p8_threads(8), 1) conv_p8_pair_kernel(const ConvP8Params p) { conv_p8_body<8, false, true>(&p, nullptr); }
-__global__ void __launch_bounds__(p8_threads(8), 1) conv_p8_x2_pair_kernel(const ConvP8Params p) { conv_p8_body<8, true, true>(&p, nullptr); }
-__global__ void __launch_bounds__(p8_threads(8), 1) conv_p8_chain_kernel(const __grid_constant__ ConvP8ChainArgs A) {
-  conv_p8_body<8, false, true, true>(A.c, &A.info);
-}
+__global__ void __launch_bounds__(p8_threads(8), 1) conv_p8_kernel(const ConvP8Params p) { conv_p8_body<8, false>(p); }
+__global__ void __launch_bounds__(p8_threads(4), 1) conv_p8_kernel4(const ConvP8Params p) { conv_p8_body<4, false>(p); }
+__global__ void __launch_bounds__(p8_threads(8), 1) conv_p8_x2_kernel(const ConvP8Params p) { conv_p8_body<8, true>(p); }
+__global__ void __launch_bounds__(p8_threads(8), 1) conv_p8_pair_kernel(const ConvP8Params p) { conv_p8_body<8, false, true>(p); }
+__global__ void __launch_bounds__(p8_threads(8), 1) conv_p8_x2_pair_kernel(const ConvP8Params p) { conv_p8_body<8, true, true>(p); }
 
 constexpr int kMaxDynSmem = 227 * 1024 - 1024;  // the kernel also has ~400 B of static shared memory
-constexpr int kChainMaxDynSmem = 227 * 1024 - 3072;  // the chained kernel: 2.2 KB static (four convs' biases)
 inline int patch_pitch_for(int Wp) { return ((128 + 2 * Wp + 2) * 16 + 127) / 128 * 128; }
 inline int smem_bytes_for(int Wp, bool x2, bool pair = false) {
   // single CTA: 4 stages of 8 (whole tile) / 4 (half tile, X2) chunk planes; pair: half the weights, 5 / 4 whole-tile stages
@@ -652,10 +400,6 @@ inline int smem_bytes_for(int Wp, bool x2, bool pair = false) {
 }
 
 static int g_p8_max_pairs[kMaxDevices][2] = {};
-static int g_p8_chain_pairs[kMaxDevices] = {};
-inline int chain_smem_bytes_for(int Wp) {  // both convs' weight halves + four whole-tile stages
-  return kP8Chain * kWBytes / 2 + 4 * kChunks * patch_pitch_for(Wp) + 128;
-}
 
 template <typename K>
 int p8_pair_occupancy(K kernel, int smem, int* out) {
@@ -690,8 +434,6 @@ int conv_p8_init() {
   // co-resident CTA pairs at the largest shared-memory footprint (the detector's 64 x 64 planes use less)
   if (int rc = p8_pair_occupancy(conv_p8_pair_kernel, kMaxDynSmem, &g_p8_max_pairs[dev][0])) return rc;
   if (int rc = p8_pair_occupancy(conv_p8_x2_pair_kernel, kMaxDynSmem, &g_p8_max_pairs[dev][1])) return rc;
-  PB_CUDA(cudaFuncSetAttribute(conv_p8_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kChainMaxDynSmem));
-  if (int rc = p8_pair_occupancy(conv_p8_chain_kernel, kChainMaxDynSmem, &g_p8_chain_pairs[dev])) return rc;
   done[dev] = true;
   return PB200_OK;
 }
@@ -750,80 +492,6 @@ int launch_conv_p8(const void* in_p8, const void* wimg, const float* bias, const
   else if (x2) PB_CUDA(cudaLaunchKernelEx(&cfg, conv_p8_x2_kernel, p));
   else if (narrow) PB_CUDA(cudaLaunchKernelEx(&cfg, conv_p8_kernel4, p));
   else PB_CUDA(cudaLaunchKernelEx(&cfg, conv_p8_kernel, p));
-  return PB200_OK;
-}
-
-bool conv_p8_chain_supported(int B, int H, int W) {
-  const int Wp = W + 2;
-  return B >= 1 && g_p8_chain_pairs[current_device()] > 0 && chain_smem_bytes_for(Wp) <= kChainMaxDynSmem && Wp - 1 <= 128 &&
-         kP8Chain * B + 1 <= kP8ChainCounters;
-}
-
-int launch_conv_p8_chain(const P8ChainConv* convs, int B, int H, int W, int group, unsigned* counters, cudaStream_t st) {
-  PB_CHECK(conv_p8_chain_supported(B, H, W), "conv_p8 chain: unsupported shape B = %d, %d x %d", B, H, W);
-  const int Wp = W + 2;
-  ConvP8ChainArgs A;
-  const int tpi = (H * Wp + 127) / 128;
-  for (int c = 0; c < kP8Chain; ++c) {
-    ConvP8Params& p = A.c[c];
-    p.in = static_cast<const uint8_t*>(convs[c].in);
-    p.wimg = static_cast<const uint8_t*>(convs[c].wimg);
-    p.bias = convs[c].bias;
-    p.residual = static_cast<const uint8_t*>(convs[c].residual);
-    p.out = static_cast<uint8_t*>(convs[c].out);
-    p.H = H;
-    p.W = W;
-    p.Wp = Wp;
-    p.tiles_per_img = tpi;
-    p.num_tiles = B * tpi;
-    p.npos = 128 + 2 * Wp + 2;
-    p.patch_pitch = patch_pitch_for(Wp);
-    p.relu = convs[c].relu;
-    p.out_nhwc = convs[c].out_nhwc;
-    p.plane_bytes = static_cast<long long>(p8_plane_elems(H, W)) * 16;
-    p.img_bytes = p.plane_bytes * 8;
-    A.info.dep[c] = convs[c].dep;
-    A.info.res_dep[c] = convs[c].res_dep;
-  }
-  ConvP8ChainInfo& ci = A.info;
-  if (group < 1) group = 1;
-  if (group > B) group = B;
-  group = (B + (B + group - 1) / group - 1) / ((B + group - 1) / group);  // same number of groups, balanced sizes
-  ci.nconv = kP8Chain;
-  ci.B = B;
-  ci.group = group;
-  ci.ngroups = (B + group - 1) / group;
-  const int last_imgs = B - (ci.ngroups - 1) * group;
-  ci.seg_full = (group * tpi + 1) / 2 * 2;
-  ci.seg_last = (last_imgs * tpi + 1) / 2 * 2;
-  ci.total_items = kP8Chain * ((ci.ngroups - 1) * ci.seg_full + ci.seg_last);
-  ci.target = tpi * 8;  // 8 epilogue warps per tile
-  ci.tpi_magic = static_cast<unsigned>((0x100000000ULL + tpi - 1) / tpi);
-  for (int k = 0; k < (ci.seg_full > ci.seg_last ? ci.seg_full : ci.seg_last); ++k)
-    PB_CHECK(static_cast<int>((static_cast<unsigned long long>(k) * ci.tpi_magic) >> 32) == k / tpi,
-             "conv_p8 chain: reciprocal of %d tiles per image inexact at %d", tpi, k);
-  ci.cnt = counters;
-  const int max_pairs = g_p8_chain_pairs[current_device()];
-  const int item_pairs = ci.total_items / 2;
-  const int grid = 2 * (item_pairs < max_pairs ? item_pairs : max_pairs);  // every pair resident: the spins rely on it
-  // Publishing two tiles late is free of circular waits when a dependency (one segment back in the list, give or take an
-  // image) is further away than the two tiles a CTA may hold back (2 x grid items); the stall breaker in the epilogue
-  // covers the rest, at a price, so short segments publish at once.
-  const int seg_min = ci.seg_last < ci.seg_full ? ci.seg_last : ci.seg_full;
-  ci.defer = seg_min >= 2 * grid + 2 * tpi + 2 ? 1 : 0;
-  cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(grid);
-  cfg.blockDim = dim3(p8_threads(8));
-  cfg.dynamicSmemBytes = chain_smem_bytes_for(Wp);
-  cfg.stream = st;
-  cudaLaunchAttribute attr[2];
-  cfg.attrs = attr;
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = 2;
-  attr[0].val.clusterDim.y = 1;
-  attr[0].val.clusterDim.z = 1;
-  cfg.numAttrs = 1 + pdl_launch_attrs(attr + 1);
-  PB_CUDA(cudaLaunchKernelEx(&cfg, conv_p8_chain_kernel, A));
   return PB200_OK;
 }
 

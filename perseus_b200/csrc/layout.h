@@ -76,22 +76,6 @@ int conv_p8_init();
 // x2 = 1: the "fp16x2" mode -- fp16 P8 activations, wimg = the hi image followed by the lo image (2 x 73728 bytes)
 int launch_conv_p8(const void* in_p8, const void* wimg, const float* bias, const void* residual_p8, void* out,
                    int out_nhwc, int relu, int B, int H, int W, cudaStream_t st, int x2 = 0);
-// The two convolutions of a layer1 BasicBlock as ONE persistent launch (conv_p8.cu, CHAIN): bf16, CTA pairs, work ordered by groups of
-// `group` images so that inputs / residuals written earlier in the launch are still in L2.  dep / res_dep: index (in
-// `convs`) of the conv that writes this conv's input / residual in the same launch, -1 if an earlier launch wrote it.
-// counters: kP8ChainCounters zeroed unsigned words (left zeroed by every launch).
-constexpr int kP8Chain = 2;  // convs per chained launch: one BasicBlock of layer1
-constexpr int kP8ChainCounters = 2048;
-struct P8ChainConv {
-  const void* in;
-  const void* wimg;
-  const float* bias;
-  const void* residual;
-  void* out;
-  int out_nhwc, relu, dep, res_dep;
-};
-bool conv_p8_chain_supported(int B, int H, int W);
-int launch_conv_p8_chain(const P8ChainConv* convs, int B, int H, int W, int group, unsigned* counters, cudaStream_t st);
 // x2 = 1: the "fp16x2" mode -- fp16 frames / output, wimg = the hi image followed by the lo image (2 x 28672 bytes)
 int launch_stem_pool(const void* frames, const void* wimg, const float* bias, void* out_p8, int B, int H,
                      int W, cudaStream_t st, int x2 = 0);

@@ -53,8 +53,6 @@ enum { BUF_FRAMES = 0, BUF_STEM = 1, BUF_R0 = 2, BUF_R1 = 3, BUF_R2 = 4, BUF_R3 
 
 }  // namespace pb200
 
-constexpr int kP8ChainMark = 1 << 20;  // chain_at value of the layer1 chain's head op (not an index into `chains`)
-
 struct pb200_plan {
   int device = 0, max_batch = 0, C = 3, H = 256, W = 256, n_kp = 8, precision = PB200_PREC_BF16;
   bool bf16 = true;    // the fused 16-bit tcgen05 path (fused stem, P8 layer1, TMA-im2col layers 2-4): bf16 AND fp16x2 modes
@@ -85,11 +83,6 @@ struct pb200_plan {
   size_t chain_off = 0;
   std::vector<pb200::ChainLaunch> chains;
   std::vector<int> chain_at, chain_len;
-  // every layer1 BasicBlock (two OP_CONV_P8 ops) as ONE persistent launch ordered by image groups (conv_p8.cu CHAIN; bf16 only).
-  // chain_at[i] == kP8ChainMark marks its head op.  Opt-in (PB200_P8CHAIN=1): a measured loss; PB200_P8_GROUP=<images>
-  bool use_p8_chain = false;
-  int p8_group = 24;
-  size_t p8chain_off = 0;
   std::vector<std::string> op_names;
   std::vector<std::string> op_kernels;  // kernel each op launches (known after the first forward at a batch size)
   // L2 chunking of the front of the network (fused stem + the four layer1 convs, P8 layout): these five kernels move
@@ -281,11 +274,6 @@ static void build_graph(pb200_plan* pl) {
   pl->b_tiled = (pl->bf16 || pl->f16) && getenv("PB200_NO_BTILED") == nullptr;
   pl->use_halo = pl->b_tiled && !pl->f16 && getenv("PB200_NO_HALO") == nullptr;
   pl->use_chain = pl->bf16 && getenv("PB200_NO_CHAIN") == nullptr;
-  // OFF by default (PB200_P8CHAIN=1 enables it): measured 0.46-0.50 ms for layer1 against 0.31 ms with one launch per conv
-  // (profiles/r02_p8chain_negative.txt)
-  pl->use_p8_chain = pl->bf16 && !pl->f16 && getenv("PB200_P8CHAIN") != nullptr && getenv("PB200_NO_P8CHAIN") == nullptr &&
-                     getenv("PB200_P8_NOPAIR") == nullptr;
-  if (const char* e = getenv("PB200_P8_GROUP")) pl->p8_group = atoi(e) > 0 ? atoi(e) : pl->p8_group;
   // weight arena
   size_t woff = 0;
   for (auto& c : pl->convs) {
@@ -304,8 +292,6 @@ static void build_graph(pb200_plan* pl) {
   // dependency counters of the chained launch (zero between launches; the weight upload rewrites them with zeros)
   pl->chain_off = align_up(woff, 1024);
   woff = pl->chain_off + (kChainCounters + 1) * sizeof(unsigned);
-  pl->p8chain_off = woff;
-  woff += kP8ChainCounters * sizeof(unsigned);
   pl->arena_bytes = woff;
   for (auto& o : pl->ops) pl->op_names.push_back(o.name);
 }
@@ -351,8 +337,7 @@ extern "C" int pb200_plan_create(pb200_plan** out, int device, int max_batch, in
   pl->elt = pl->bf16 ? 2 : 4;
   build_graph(pl);
   cudaError_t e = cudaMalloc(reinterpret_cast<void**>(&pl->arena), pl->arena_bytes);
-  if (e == cudaSuccess)
-    e = cudaMemset(pl->arena + pl->chain_off, 0, (kChainCounters + 1 + kP8ChainCounters) * sizeof(unsigned));
+  if (e == cudaSuccess) e = cudaMemset(pl->arena + pl->chain_off, 0, (kChainCounters + 1) * sizeof(unsigned));
   if (e != cudaSuccess) {
     delete pl;
     return cuda_fail(e, "cudaMalloc(weight arena)", __FILE__, __LINE__);
@@ -573,8 +558,6 @@ static void choose_tile(const ConvSpec& c, int B, bool f16, int* block_n, int* c
 }
 
 // (re)build the TMA descriptors / launch parameters when a pointer or the batch size changed
-static inline bool front_chunked(const pb200_plan* pl, int B);
-
 static int prepare(pb200_plan* pl, const void* frames, void* ws, int B) {
   if (!pl->bf16 && !pl->split) return PB200_OK;
   // the tensor maps cover workspace buffers only (the stem reads `frames` through a plain pointer argument), so a caller
@@ -665,18 +648,6 @@ static int prepare(pb200_plan* pl, const void* frames, void* ws, int B) {
       i = j;
     }
   }
-  // layer1: every BasicBlock (two consecutive OP_CONV_P8 ops, the second with a residual) -> one chained launch
-  if (pl->use_p8_chain && !front_chunked(pl, B)) {
-    for (size_t i = 0; i + kP8Chain <= pl->ops.size(); ++i) {
-      if (pl->ops[i].kind != OP_CONV_P8 || pl->ops[i + 1].kind != OP_CONV_P8) continue;
-      if (pl->ops[i].res_buf >= 0 || pl->ops[i + 1].res_buf < 0) continue;  // (conv1, conv2 + residual)
-      const ConvSpec& c0 = pl->convs[pl->ops[i].conv];
-      if (!conv_p8_chain_supported(B, c0.Hin, c0.Win)) break;
-      pl->chain_at[i] = kP8ChainMark;
-      pl->chain_len[i] = kP8Chain;
-      ++i;
-    }
-  }
   pl->cache_frames = frames;
   pl->cache_ws = ws;
   pl->cache_B = B;
@@ -685,26 +656,8 @@ static int prepare(pb200_plan* pl, const void* frames, void* ws, int B) {
 
 // the chained launch whose head is op i (chain_at[i] >= 0)
 static int launch_chain_at(pb200_plan* pl, size_t i, const void* frames, void* ws, int B, cudaStream_t st) {
-  if (pl->chain_at[i] != kP8ChainMark) return launch_umma_chain(pl->chains[pl->chain_at[i]], st);
-  P8ChainConv cv[kP8Chain];
-  const ConvSpec& c0 = pl->convs[pl->ops[i].conv];
-  for (int k = 0; k < kP8Chain; ++k) {
-    const Op& op = pl->ops[i + k];
-    const ConvSpec& c = pl->convs[op.conv];
-    cv[k].in = buf_ptr(pl, frames, ws, op.in_buf);
-    cv[k].wimg = pl->arena + c.w_off;
-    cv[k].bias = reinterpret_cast<const float*>(pl->arena + c.b_off);
-    cv[k].residual = op.res_buf >= 0 ? buf_ptr(pl, frames, ws, op.res_buf) : nullptr;
-    cv[k].out = buf_ptr(pl, frames, ws, op.out_buf);
-    cv[k].out_nhwc = op.out_nhwc;
-    cv[k].relu = op.relu;
-    cv[k].dep = cv[k].res_dep = -1;
-    for (int m = 0; m < k; ++m) {  // the LATEST earlier conv of the chain that writes the buffer
-      if (pl->ops[i + m].out_buf == op.in_buf) cv[k].dep = m;
-      if (op.res_buf >= 0 && pl->ops[i + m].out_buf == op.res_buf) cv[k].res_dep = m;
-    }
-  }
-  return launch_conv_p8_chain(cv, B, c0.Hin, c0.Win, pl->p8_group, reinterpret_cast<unsigned*>(pl->arena + pl->p8chain_off), st);
+  (void)frames; (void)ws; (void)B;
+  return launch_umma_chain(pl->chains[pl->chain_at[i]], st);
 }
 
 static int run_op(pb200_plan* pl, const Op& op, const void* frames, void* ws, float* out_norm,
@@ -838,9 +791,7 @@ extern "C" const char* pb200_plan_op_kernel(const pb200_plan* plan, int i) {
   std::string& k = pl->op_kernels[i];
   switch (op.kind) {
     case OP_STEM_POOL: k = plan->f16 ? "stem_pool_x2_kernel" : "stem_pool_kernel"; break;
-    case OP_CONV_P8:
-      k = pb200_plan_op_chain_len(plan, i) != 1 ? "conv_p8_chain_kernel" : (plan->f16 ? "conv_p8_x2_kernel" : "conv_p8_kernel");
-      break;
+    case OP_CONV_P8: k = plan->f16 ? "conv_p8_x2_kernel" : "conv_p8_kernel"; break;
     case OP_MAXPOOL: k = plan->split ? "maxpool_split_kernel" : (plan->bf16 ? "maxpool_bf16_kernel" : "maxpool_f32_kernel"); break;
     case OP_HEAD: k = "head_kernel"; break;
     case OP_CONV:

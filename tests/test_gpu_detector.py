@@ -506,9 +506,9 @@ def test_full_size_batch256_bf16_sampled_frames_vs_emulation(C):
     print(f"[bf16 C={C} bs256, 8 sampled frames] vs emulation {e_emu:.4f} px | vs reference fp32 {e_ref:.4f} px "
           "(single-pass bf16 does not meet 0.05 px)")
     # RGBD on random-init weights: outputs span +-3100 px, so single-pass bf16 rounding noise is px-sized; kernel and
-    # emulation accumulate in different orders and are two draws of that noise (measured 2.2-3.2 px across the kernels'
-    # accumulation orders of r02, e.g. 3.17 px with layer1's channel-half-major K walk): bound = measured + 25 %
-    assert e_emu <= (0.3 if C == 3 else 4.0)
+    # emulation accumulate in different orders and are two draws of that noise (a different K walk in layer1 alone moved
+    # this figure from 2.4 to 3.17 px in r02): bound = measured + margin
+    assert e_emu <= (0.3 if C == 3 else 3.0)
 
 
 def test_streaming_detector_graph_matches_eager_path():
@@ -632,39 +632,6 @@ def test_chained_layers34_bit_equal_to_one_launch_per_conv(precision, B, monkeyp
     print(f"[chain {precision} B={B}] {n_chain} launches chained vs {n_plain} one per conv")
     if B >= 255:  # smaller batches may select other tile shapes (no pair<256> run to chain)
         assert n_chain < n_plain, f"no chain was built at B = {B} ({n_chain} vs {n_plain} launches)"
-    assert torch.isfinite(want).all()
-    for g in got:
-        assert torch.equal(g, want)
-
-
-@pytest.mark.parametrize("B,group", [(256, 24), (37, 3), (131, 24), (255, 32), (1, 24), (2, 1), (50, 7)])
-def test_chained_layer1_bit_equal_to_one_launch_per_conv(B, group, monkeypatch):
-    """The two convs of every layer1 BasicBlock run as ONE persistent launch ordered by groups of images (conv_p8.cu CHAIN):
-    tiles of the second conv wait on per-image arrival counters of the first.  The arithmetic of a tile is unchanged, so the keypoints
-    must equal the one-launch-per-conv plan bit for bit -- full and odd batches, odd group sizes (padding items), groups that
-    do not divide the batch, and on every repeat (the counters re-arm themselves)."""
-    from perseus_b200 import _lib
-    from perseus_b200.detector import KeypointCNN
-
-    sd = do.seeded_state_dict(3, 8, seed=0)
-
-    def fresh():  # the plan reads the environment when it is created
-        m = KeypointCNN(num_channels=3, precision="bf16", max_batch=B)
-        m.load_state_dict(sd)
-        return m.eval().to(gu.dev())
-
-    monkeypatch.delenv("PB200_NO_P8CHAIN", raising=False)
-    monkeypatch.setenv("PB200_P8CHAIN", "1")  # opt-in: measured slower than one launch per conv (profiles/r02_p8chain_negative.txt)
-    monkeypatch.setenv("PB200_P8_GROUP", str(group))
-    chained = fresh()
-    x = gu.synth_u8_frames(B, seed=23).cuda()
-    got = [chained.forward_frames(x).clone() for _ in range(3)]
-    n_chain = _lib.lib().pb200_plan_launches_at(chained._plan(gu.dev(), B).handle, B)
-    monkeypatch.setenv("PB200_NO_P8CHAIN", "1")
-    plain = fresh()
-    want = plain.forward_frames(x)
-    n_plain = _lib.lib().pb200_plan_launches_at(plain._plan(gu.dev(), B).handle, B)
-    assert n_chain == n_plain - 2, f"layer1 was not chained at B = {B} ({n_chain} vs {n_plain} launches)"
     assert torch.isfinite(want).all()
     for g in got:
         assert torch.equal(g, want)
