@@ -30,7 +30,16 @@ __device__ __forceinline__ void copy_in(double* dst, const double* __restrict__ 
   }
 }
 __device__ __forceinline__ void copy_out(double* __restrict__ dst, const double* src, int n) {
-  for (int i = threadIdx.x; i < n; i += blockDim.x) dst[i] = src[i];
+  constexpr int U = 4;
+  const int T = blockDim.x;
+  for (int i0 = threadIdx.x; i0 < n; i0 += U * T) {
+    double v[U];
+#pragma unroll
+    for (int k = 0; k < U; ++k) v[k] = (i0 + k * T < n) ? src[i0 + k * T] : 0.0;
+#pragma unroll
+    for (int k = 0; k < U; ++k)
+      if (i0 + k * T < n) dst[i0 + k * T] = v[k];
+  }
 }
 
 // Stages one output block (N doubles per factor, held in registers) through the CTA's buffer and writes it out in
@@ -145,6 +154,11 @@ dynamics_kernel(const double* __restrict__ pose1, const double* __restrict__ ang
 }
 
 // ---- projection -----------------------------------------------------------------------------
+// poses a block of kFacThreads consecutive (pose, point) factors can touch: sized by the actual P (the worst case P = 1
+// needs 129 slots = 12 KB and capped the kernel at 6 CTAs per SM; P = 8 needs 17)
+__host__ __device__ inline int proj_pose_slots(int P) { return (kFacThreads + P - 1) / P + 1; }
+inline size_t proj_smem_bytes(int P) { return sizeof(double) * (12 * proj_pose_slots(P) + 16 * kFacThreads); }
+
 // One thread per (pose, point).  A block handles kFacThreads consecutive factors = a run of
 // consecutive poses (P divides the run when P | 128; otherwise poses straddle blocks, which is
 // fine because every thread indexes its own pose).
@@ -159,8 +173,8 @@ __device__ __forceinline__ void projection_block(double* sm, long long block, co
   const long long pose_lo = base / P;
   const long long pose_hi = (base + cnt - 1) / P;
   const int npose = static_cast<int>(pose_hi - pose_lo + 1);
-  double* s_pose = sm;                          // 12 * (T/1 + 1) worst case P = 1
-  double* s_meas = s_pose + 12 * (kFacThreads + 1);  // 2 * T
+  double* s_pose = sm;                          // 12 * proj_pose_slots(P)
+  double* s_meas = s_pose + 12 * proj_pose_slots(P);  // 2 * T
   double* s_res = s_meas + 2 * kFacThreads;     // 2 * T
   double* s_jac = s_res + 2 * kFacThreads;      // 12 * T
   copy_in(s_pose, poses + pose_lo * 12, npose * 12);
@@ -199,8 +213,9 @@ __device__ __forceinline__ void projection_block(double* sm, long long block, co
   if (JAC) copy_out(jac + base * 12, s_jac, cnt * 12);
 }
 
+// 8 CTAs per SM (64 registers; r02 ncu: at 78 registers / 6 CTAs the kernel ran 35 % of its warp slots, stalled on loads)
 template <bool JAC>
-__global__ void __launch_bounds__(kFacThreads)
+__global__ void __launch_bounds__(kFacThreads, 8)
 projection_kernel(const double* __restrict__ poses, const double* __restrict__ meas,
                   const double* __restrict__ pts_body, const double* __restrict__ K5,
                   const double* __restrict__ cam12, double* __restrict__ resid,
@@ -350,7 +365,7 @@ extern "C" int pb200_factors_projection(const double* poses, const double* meas,
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const long long NP = static_cast<long long>(N) * P;
   const unsigned grid = static_cast<unsigned>((NP + kFacThreads - 1) / kFacThreads);
-  const size_t smem = sizeof(double) * (12 * (kFacThreads + 1) + 16 * kFacThreads);
+  const size_t smem = proj_smem_bytes(P);
   if (jac_or_null) {
     projection_kernel<true><<<grid, kFacThreads, smem, st>>>(poses, meas, pts_body, K5,
                                                               cam_pose12_or_null, resid, jac_or_null,
@@ -392,14 +407,14 @@ extern "C" int pb200_factors_chain(const double* poses, const double* ang_vel, c
   // waves on the projection factors run in their own (high-occupancy) kernel: 1.17 vs 1.39 ms at 1 M poses.
   const bool split_launch = a.nb_proj + nb_dyn > 16LL * num_sms();
   if (split_launch) {
-    const size_t smem_p = sizeof(double) * (12 * (kFacThreads + 1) + 16 * kFacThreads);
+    const size_t smem_p = proj_smem_bytes(P);
     projection_kernel<true><<<static_cast<unsigned>(a.nb_proj), kFacThreads, smem_p, st>>>(
         poses, meas, pts_body, K5, cam_pose12_or_null, proj_resid, proj_jac, cheirality, a.NP, P);
     PB_CUDA(cudaGetLastError());
     a.nb_proj = 0;
     if (nb_dyn == 0) return PB200_OK;
   }
-  const size_t smem_proj = sizeof(double) * (12 * (kFacThreads + 1) + 16 * kFacThreads);
+  const size_t smem_proj = proj_smem_bytes(P);
   const size_t smem_dyn = sizeof(double) * (kFacThreads * 60 + 4 * kDynSlice);  // 36 T of states, 24 T parked, staging
   const size_t smem = smem_proj > smem_dyn ? smem_proj : smem_dyn;
   static bool attr_set[kMaxDevices] = {};
