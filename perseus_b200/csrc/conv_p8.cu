@@ -44,6 +44,7 @@ struct ConvP8Params {
   int npos;                 // patch positions per chunk = 128 + 2*Wp + 2
   int patch_pitch;          // bytes between chunk planes of a patch in shared memory (multiple of 128)
   int relu, out_nhwc;
+  int reverse;              // 1: the tile list is walked from the LAST tile to the first (see launch_conv_p8)
   long long img_bytes;      // bytes per P8 image
   long long plane_bytes;    // bytes per P8 chunk plane
 };
@@ -136,7 +137,8 @@ __device__ __forceinline__ void conv_p8_body(const ConvP8Params& p) {
     uint32_t phase = 0;
     const uint32_t chunk_bytes = static_cast<uint32_t>(p.npos) * 16u;
     for (int tile = blockIdx.x; alive(tile); tile += gridDim.x) {
-      const int tl = tile < p.num_tiles ? tile : p.num_tiles - 1;
+      int tl = tile < p.num_tiles ? tile : p.num_tiles - 1;
+      if (p.reverse) tl = p.num_tiles - 1 - tl;
       const int n = tl / p.tiles_per_img;
       const int q0 = (tl - n * p.tiles_per_img) * 128;
       const uint8_t* src = p.in + n * p.img_bytes + static_cast<long long>(q0) * 16;
@@ -241,8 +243,9 @@ __device__ __forceinline__ void conv_p8_body(const ConvP8Params& p) {
     auto load_residual = [&](int tile, uint4 (&rv)[kNch]) {
       bool ok = false;
       if (has_res && tile < p.num_tiles) {  // (a peer tile past the end loads nothing)
-        const int n = tile / p.tiles_per_img;
-        const int q0 = (tile - n * p.tiles_per_img) * 128 + m;
+        const int tl = p.reverse ? p.num_tiles - 1 - tile : tile;
+        const int n = tl / p.tiles_per_img;
+        const int q0 = (tl - n * p.tiles_per_img) * 128 + m;
         const int h = q0 / p.Wp;
         if (q0 < p.H * p.Wp && q0 - h * p.Wp < p.W) {
           const uint4* res = reinterpret_cast<const uint4*>(p.residual + n * p.img_bytes) + q0 + p.Wp + 1;
@@ -264,8 +267,9 @@ __device__ __forceinline__ void conv_p8_body(const ConvP8Params& p) {
     const uint32_t lempty0 = PAIR ? mapa_u32(&tmem_empty_bar[0], 0) : 0u;
     auto process = [&](int tile, uint4 (&rv)[kNch]) {
       const bool live = tile < p.num_tiles;  // false only for the peer of an odd last tile
-      const int n = tile / p.tiles_per_img;
-      const int ti = tile - n * p.tiles_per_img;
+      const int tl = (p.reverse && live) ? p.num_tiles - 1 - tile : tile;
+      const int n = tl / p.tiles_per_img;
+      const int ti = tl - n * p.tiles_per_img;
       const int q0 = ti * 128 + m;
       const int h = q0 / p.Wp;
       const int w = q0 - h * p.Wp;
@@ -438,8 +442,12 @@ int conv_p8_init() {
   return PB200_OK;
 }
 
+// reverse = 1 walks the tile list back to front.  The layer1 tensors (140 MB each) are larger than L2, and every kernel
+// streams through them: when a launch ends, L2 holds the part of its input / output it touched LAST.  A consumer that
+// starts there (a backward walk after a forward producer, and vice versa) finds the first ~60 MB of its input -- and of
+// its residual, which the previous launch read in the same direction -- in L2 instead of HBM.
 int launch_conv_p8(const void* in_p8, const void* wimg, const float* bias, const void* residual_p8, void* out,
-                   int out_nhwc, int relu, int B, int H, int W, cudaStream_t st, int x2) {
+                   int out_nhwc, int relu, int B, int H, int W, cudaStream_t st, int x2, int reverse) {
   const int Wp = W + 2;
   // the CTA-pair kernels are the default where a pair fits (PB200_P8_NOPAIR=1: the single-CTA kernels)
   const int max_pairs = g_p8_max_pairs[current_device()][x2 ? 1 : 0];
@@ -463,6 +471,7 @@ int launch_conv_p8(const void* in_p8, const void* wimg, const float* bias, const
   p.patch_pitch = patch_pitch_for(Wp);
   p.relu = relu;
   p.out_nhwc = out_nhwc;
+  p.reverse = reverse;
   p.plane_bytes = static_cast<long long>(p8_plane_elems(H, W)) * 16;
   p.img_bytes = p.plane_bytes * 8;
   int grid = p.num_tiles < num_sms() ? p.num_tiles : num_sms();

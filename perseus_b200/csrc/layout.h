@@ -75,7 +75,7 @@ inline size_t conv_p8_wimg_offset(int co, int k) {
 int conv_p8_init();
 // x2 = 1: the "fp16x2" mode -- fp16 P8 activations, wimg = the hi image followed by the lo image (2 x 73728 bytes)
 int launch_conv_p8(const void* in_p8, const void* wimg, const float* bias, const void* residual_p8, void* out,
-                   int out_nhwc, int relu, int B, int H, int W, cudaStream_t st, int x2 = 0);
+                   int out_nhwc, int relu, int B, int H, int W, cudaStream_t st, int x2 = 0, int reverse = 0);
 // x2 = 1: the "fp16x2" mode -- fp16 frames / output, wimg = the hi image followed by the lo image (2 x 28672 bytes)
 int launch_stem_pool(const void* frames, const void* wimg, const float* bias, void* out_p8, int B, int H,
                      int W, cudaStream_t st, int x2 = 0);

@@ -42,6 +42,7 @@ struct Op {
   int relu = 0;
   int out_nhwc = 0;  // OP_CONV_P8: write NHWC (hand-over to the TMA-im2col layers) instead of P8
   int ds_buf = -1;   // OP_CONV with a fused downsample: the block input the projection reads
+  int reverse = 0;   // OP_CONV_P8: walk the tiles back to front (alternates launch by launch: launch_conv_p8)
 };
 
 // activation buffer ids
@@ -170,6 +171,8 @@ static void build_graph(pb200_plan* pl) {
       op.kind = OP_CONV_P8; op.name = pre + cn + "+bn" + ((i % 2) ? "+add+relu" : "+relu");
       op.conv = static_cast<int>(pl->convs.size()) - 1;
       op.in_buf = seq_in[i]; op.out_buf = seq_out[i]; op.res_buf = seq_res[i]; op.relu = 1; op.out_nhwc = (i == 3);
+      // the stem walks forward, so conv 0 starts at the end, conv 1 at the front, ... (PB200_P8_NOREVERSE=1: all forward)
+      op.reverse = (i % 2 == 0 && getenv("PB200_P8_NOREVERSE") == nullptr) ? 1 : 0;
       pl->ops.push_back(op);
     }
     first_layer = 1;
@@ -693,7 +696,8 @@ static int run_op(pb200_plan* pl, const Op& op, const void* frames, void* ws, fl
       return launch_conv_p8(buf_ptr(pl, frames, ws, op.in_buf, n0), pl->arena + c.w_off,
                             reinterpret_cast<const float*>(pl->arena + c.b_off),
                             op.res_buf >= 0 ? buf_ptr(pl, frames, ws, op.res_buf, n0) : nullptr,
-                            buf_ptr(pl, frames, ws, op.out_buf, n0), op.out_nhwc, op.relu, B, c.Hin, c.Win, st, pl->f16 ? 1 : 0);
+                            buf_ptr(pl, frames, ws, op.out_buf, n0), op.out_nhwc, op.relu, B, c.Hin, c.Win, st, pl->f16 ? 1 : 0,
+                            op.reverse);
     }
     case OP_MAXPOOL: {
       const ConvSpec& c = pl->convs[0];
@@ -1211,7 +1215,8 @@ extern "C" int pb200_debug_conv_p8_f16x2(const void* in_p8, int B, int H, int W,
       cudaMemcpyAsync(db, bias_host, sizeof(float) * 64, cudaMemcpyHostToDevice, st) != cudaSuccess)
     rc = PB200_ERR_CUDA;
   if (rc == PB200_OK)
-    rc = launch_conv_p8(in_p8, dw, static_cast<const float*>(db), residual_p8_or_null, out, out_nhwc, relu, B, H, W, st, 1);
+    rc = launch_conv_p8(in_p8, dw, static_cast<const float*>(db), residual_p8_or_null, out, out_nhwc, relu, B, H, W, st, 1,
+                        getenv("PB200_DEBUG_P8_REVERSE") != nullptr ? 1 : 0);
   cudaError_t e = cudaStreamSynchronize(st);
   if (rc == PB200_OK && e != cudaSuccess) rc = cuda_fail(e, "debug_conv_p8_f16x2 sync", __FILE__, __LINE__);
   cudaFree(dw);
@@ -1242,7 +1247,8 @@ extern "C" int pb200_debug_conv_p8(const void* in_p8, int B, int H, int W, const
     rc = PB200_ERR_CUDA;
   if (rc == PB200_OK)
     rc = launch_conv_p8(in_p8, dw, static_cast<const float*>(db), residual_p8_or_null, out, out_nhwc, relu, B, H,
-                        W, st);
+                        W, st,
+                        0, getenv("PB200_DEBUG_P8_REVERSE") != nullptr ? 1 : 0);
   cudaError_t e = cudaStreamSynchronize(st);
   if (rc == PB200_OK && e != cudaSuccess) rc = cuda_fail(e, "debug_conv_p8 sync", __FILE__, __LINE__);
   cudaFree(dw);

@@ -316,10 +316,11 @@ def test_stem_pool_fused_vs_operand_matched_reference(C, B):
     assert not bad.any(), f"{int(bad.sum())}/{bad.numel()} off; max err {float(err.max()):.4f}; first {bad.nonzero()[:4].tolist()}"
 
 
+@pytest.mark.parametrize("reverse", [False, True], ids=["fwd", "rev"])
 @pytest.mark.parametrize("single", [False, True], ids=["pair", "single"])
 @pytest.mark.parametrize("B,use_res,relu,nhwc", [(1, False, True, False), (3, True, True, False), (2, True, True, True),
                                                  (5, False, False, False), (11, True, True, False)])
-def test_conv_p8_vs_exact_operand_reference(B, use_res, relu, nhwc, single, monkeypatch):
+def test_conv_p8_vs_exact_operand_reference(B, use_res, relu, nhwc, single, reverse, monkeypatch):
     """layer1 conv (3x3/1, 64->64) on the P8 layout vs F.conv2d in fp64 on the same bf16 operands."""
     from perseus_b200 import _lib
 
@@ -328,6 +329,11 @@ def test_conv_p8_vs_exact_operand_reference(B, use_res, relu, nhwc, single, monk
         monkeypatch.setenv("PB200_P8_NOPAIR", "1")
     else:
         monkeypatch.delenv("PB200_P8_NOPAIR", raising=False)
+    # rev: the tile list walked back to front (what every other layer1 launch of the plan does: launch_conv_p8)
+    if reverse:
+        monkeypatch.setenv("PB200_DEBUG_P8_REVERSE", "1")
+    else:
+        monkeypatch.delenv("PB200_DEBUG_P8_REVERSE", raising=False)
 
     H = W = 64
     g = torch.Generator().manual_seed(100 + B)

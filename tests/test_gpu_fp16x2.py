@@ -115,10 +115,11 @@ def test_x2_conv_with_fused_projection(case, cluster, monkeypatch):
     assert not bad.any(), f"{int(bad.sum())} / {bad.numel()} outputs off; max err {float(err.max()):.5f}"
 
 
+@pytest.mark.parametrize("reverse", [False, True], ids=["fwd", "rev"])
 @pytest.mark.parametrize("single", [False, True], ids=["pair", "single"])
 @pytest.mark.parametrize("B,use_res,relu,nhwc", [(1, False, True, False), (3, True, True, False), (2, True, True, True),
                                                  (5, False, False, False), (11, True, True, False)])
-def test_x2_conv_p8_vs_exact_operand_reference(B, use_res, relu, nhwc, single, monkeypatch):
+def test_x2_conv_p8_vs_exact_operand_reference(B, use_res, relu, nhwc, single, reverse, monkeypatch):
     """layer1 conv on the P8 layout, fp16, ONE N = 128 MMA per K step over [W_hi ; W_lo] (the epilogue adds the halves)."""
     from perseus_b200 import _lib
 
@@ -127,6 +128,11 @@ def test_x2_conv_p8_vs_exact_operand_reference(B, use_res, relu, nhwc, single, m
         monkeypatch.setenv("PB200_P8_NOPAIR", "1")
     else:
         monkeypatch.delenv("PB200_P8_NOPAIR", raising=False)
+    # rev: the tile list walked back to front (what every other layer1 launch of the plan does: launch_conv_p8)
+    if reverse:
+        monkeypatch.setenv("PB200_DEBUG_P8_REVERSE", "1")
+    else:
+        monkeypatch.delenv("PB200_DEBUG_P8_REVERSE", raising=False)
 
     H = W = 64
     g = torch.Generator().manual_seed(200 + B)
