@@ -26,13 +26,22 @@ from .models import KeypointCNN
 class BatchPipeline:
     def __init__(self, model: KeypointCNN, batch: int, src_h: int | None = None, src_w: int | None = None,
                  channels: int = 3, *, bgr: bool = False, depth_divisor: float = 1.0, slots: int = 2, results: int = 4,
-                 copy_streams: int = 1, device: torch.device | None = None, post=None):
+                 copy_streams: int = 1, device: torch.device | None = None, post=None, graph: bool | None = None):
         """post: optional callable(px (B, K, 2) float32 device tensor) -> device tensor with a FIXED address, captured into
         every batch's CUDA graph right behind the detector (e.g. FixedLagSmoother.push: keypoints go straight into the
         smoother's measurement buffer and the newest pose comes back with `result_post`).  It must not allocate or
         synchronise.  A stateful `post` is executed once during construction (warm-up): reset its state afterwards."""
         if model.training:
             raise RuntimeError("BatchPipeline needs model.eval()")
+        # graph=False enqueues the ~12 launches of a forward eagerly instead of replaying a captured graph: the eager chain
+        # keeps programmatic dependent launch between the kernels (a replay serialises them: +0.02 ms per step) at the price
+        # of ~60 us of host time per batch; a `post` hook always runs captured.  Default: PB200_PIPE_EAGER=1 selects eager.
+        # Measured r02 (tools/gpu/r02_x.sh, two runs each): e2e 211.9 / 216.9 k frames/s replayed, 215.0 / 215.4 k eager -- no
+        # difference, so the replay (no host work per batch) stays the default.
+        if graph is None:
+            import os
+            graph = os.environ.get("PB200_PIPE_EAGER") is None
+        self.use_graph = bool(graph) or post is not None
         self.model = model
         self.device = device or next(model.parameters()).device
         if self.device.type != "cuda":
@@ -141,7 +150,10 @@ class BatchPipeline:
             self.compute.wait_event(self.ev_read[s])  # px_dev[s] of the batch two submits ago has been read back
             if self.post_dev is not None:
                 self.compute.wait_event(self.ev_post_read)  # the shared `post` output of the previous batch has been read
-            self.graphs[s].replay()
+            if self.use_graph:
+                self.graphs[s].replay()
+            else:
+                self._run(s)
             self.ev_fwd[s].record(self.compute)
         with torch.cuda.stream(self.d2h):
             self.d2h.wait_event(self.ev_fwd[s])
