@@ -8,7 +8,7 @@ of batch i:
   copy stream(s)  : one plain cudaMemcpyAsync per submitted batch (per copy stream) into one of `slots` device buffers
   ingest stream   : the fused ingest kernel of batch i+1 (HBM-bound) runs under the tensor-bound convolutions of batch i,
                     mostly in the gaps between their launches
-  compute stream  : ONE CUDA-graph replay per batch (backbone -> head + pixel decode; ~19 kernels whose launches would
+  compute stream  : ONE CUDA-graph replay per batch (backbone -> head + pixel decode; ~11 kernels whose launches would
                     otherwise cost ~0.1 ms of host time per step) + the 16 KB keypoint copy into a ring of pinned
                     result buffers
   host            : `submit()` never blocks on the GPU; `result(ticket)` waits for that batch's keypoints only.
