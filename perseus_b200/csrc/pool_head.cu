@@ -158,7 +158,33 @@ head_kernel(const void* __restrict__ in, const float* __restrict__ fc_w,
   pdl_wait();  // launched with programmatic serialization: the last conv's output must be complete
   const int b = blockIdx.x;
   const float inv = 1.0f / static_cast<float>(HW);
-  for (int c2 = threadIdx.x; c2 < C / 2; c2 += blockDim.x) {
+  // 16-bit activations, C = 512, 64 pixels (the detector's shape): thread = (pixel group g of 4, 8-channel chunk): 16
+  // independent 16-byte loads per thread, all in flight at once, then the four groups' partial sums meet in shared
+  // memory.  (One thread per channel pair walked its 64 pixels with 4-byte loads, 8 in flight: ~8 dependent round trips.)
+  __shared__ float s_part[(MODE == 1 || MODE == 3) ? 4 * 512 : 1];
+  const bool fast = (MODE == 1 || MODE == 3) && C == 512 && HW % 4 == 0 && blockDim.x == 256;
+  if (fast) {
+    if constexpr (MODE == 1 || MODE == 3) {
+      const int g = threadIdx.x >> 6, ch = threadIdx.x & 63;  // 64 chunks of 8 channels
+      const int per = HW / 4;
+      const uint4* p = static_cast<const uint4*>(in) + (static_cast<long long>(b) * HW + g * per) * (C / 8) + ch;
+      float a[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll 16
+      for (int i = 0; i < per; ++i) {
+        const uint4 v = __ldg(p + static_cast<long long>(i) * (C / 8));
+        a[0] += lo16<MODE == 3>(v.x); a[1] += hi16<MODE == 3>(v.x);
+        a[2] += lo16<MODE == 3>(v.y); a[3] += hi16<MODE == 3>(v.y);
+        a[4] += lo16<MODE == 3>(v.z); a[5] += hi16<MODE == 3>(v.z);
+        a[6] += lo16<MODE == 3>(v.w); a[7] += hi16<MODE == 3>(v.w);
+      }
+#pragma unroll
+      for (int e = 0; e < 8; ++e) s_part[g * 512 + ch * 8 + e] = a[e];
+      __syncthreads();
+      for (int c = threadIdx.x; c < C; c += blockDim.x)
+        s_mean[c] = ((s_part[c] + s_part[512 + c]) + (s_part[1024 + c] + s_part[1536 + c])) * inv;
+    }
+  }
+  for (int c2 = threadIdx.x; !fast && c2 < C / 2; c2 += blockDim.x) {
     float a0 = 0.f, a1 = 0.f;
     if (MODE == 2) {
       const uint32_t* p = static_cast<const uint32_t*>(in) + static_cast<long long>(b) * HW * C + c2;
