@@ -115,6 +115,14 @@ int pb200_ingest(const pb200_plan* plan, const uint8_t* rgb, int rgb_channels,
 int pb200_forward(pb200_plan* plan, const void* frames, void* workspace, float* out_norm,
                   float* out_px_or_null, int B, pb200_stream stream);
 
+/* pb200_ingest + pb200_forward in one call for the batched RGB workload (perseus/detector/validate.py:109-153 with
+ * data.py:78,84-85: uint8 image batch -> model -> pixel keypoints): rgb is a TIGHT, 16-byte aligned uint8
+ * [B][H][W][3] device batch (bgr = 1: pixels are B, G, R, scripts/streaming.py:69), plan is a bf16 / fp16x2 plan with
+ * 3 input channels.  The stem kernel converts the rows itself, so the frames tensor is neither written nor read and
+ * the ingest launch disappears; results are bit-identical to pb200_ingest (no depth, no crop) + pb200_forward. */
+int pb200_forward_rgb8(pb200_plan* plan, const uint8_t* rgb, int bgr, void* workspace, float* out_norm,
+                       float* out_px_or_null, int B, pb200_stream stream);
+
 /* Compatibility entry used by KeypointCNN.forward(x): x is float [B][C][H][W] (RGB in [0,1],
  * depth in data units); fuses the NCHW->frames repack in front of pb200_forward. */
 int pb200_forward_nchw_f32(pb200_plan* plan, const float* x_nchw, void* workspace, float* out_norm,

@@ -42,6 +42,7 @@ SIGNATURES = {
          c_float, c_void_p, c_void_p, c_int, c_void_p],
     ),
     "pb200_forward": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
+    "pb200_forward_rgb8": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
     "pb200_forward_nchw_f32": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
     "pb200_plan_num_ops": (c_int, [c_void_p]),
     "pb200_plan_op_name": (c_char_p, [c_void_p, c_int]),

@@ -80,6 +80,9 @@ struct pb200_plan {
   // layers 3-4 (every run of consecutive pair<256> convs) as ONE persistent launch with in-kernel dependencies
   // (conv_umma2.cu CHAIN); PB200_NO_CHAIN=1: one launch per conv.  chain_at[i] = chain starting at op i (-1: none),
   // chain_len[i] = ops it covers
+  // set for the duration of pb200_forward_rgb8: the fused stem reads this uint8 batch instead of the frames buffer
+  const void* rgb8_src = nullptr;
+  int rgb8_bgr = 0;
   bool use_chain = true;
   size_t chain_off = 0;
   std::vector<pb200::ChainLaunch> chains;
@@ -689,7 +692,11 @@ static int run_op(pb200_plan* pl, const Op& op, const void* frames, void* ws, fl
       const ConvSpec& c = pl->convs[op.conv];
       return launch_stem_pool(buf_ptr(pl, frames, ws, BUF_FRAMES, n0), pl->arena + c.w_off,
                               reinterpret_cast<const float*>(pl->arena + c.b_off),
-                              buf_ptr(pl, frames, ws, op.out_buf, n0), B, pl->H, pl->W, st, pl->f16 ? 1 : 0);
+                              buf_ptr(pl, frames, ws, op.out_buf, n0), B, pl->H, pl->W, st, pl->f16 ? 1 : 0,
+                              pl->rgb8_src == nullptr ? nullptr
+                                                      : static_cast<const uint8_t*>(pl->rgb8_src) +
+                                                            static_cast<size_t>(n0) * pl->H * pl->W * 3,
+                              pl->rgb8_bgr);
     }
     case OP_CONV_P8: {
       const ConvSpec& c = pl->convs[op.conv];
@@ -759,6 +766,20 @@ extern "C" int pb200_forward(pb200_plan* plan, const void* frames, void* workspa
     if (int rc = run_op(plan, plan->ops[i], frames, workspace, out_norm, out_px_or_null, B, st)) return rc;
   }
   return PB200_OK;
+}
+
+extern "C" int pb200_forward_rgb8(pb200_plan* plan, const uint8_t* rgb, int bgr, void* workspace, float* out_norm,
+                                  float* out_px_or_null, int B, pb200_stream stream) {
+  if (int rc = check_forward_args(plan, rgb, workspace, out_norm, B)) return rc;
+  PB_CHECK(plan->bf16 && plan->C == 3, "forward_rgb8: needs a 16-bit tcgen05 plan (bf16 / fp16x2) with 3 input channels; "
+           "use pb200_ingest + pb200_forward otherwise");
+  PB_CHECK((reinterpret_cast<uintptr_t>(rgb) & 15) == 0, "forward_rgb8: the uint8 batch must be 16-byte aligned");
+  plan->rgb8_src = rgb;
+  plan->rgb8_bgr = bgr ? 1 : 0;
+  // the frames pointer is never dereferenced (the fused stem reads `rgb`); it only has to be non-null
+  const int rc = pb200_forward(plan, rgb, workspace, out_norm, out_px_or_null, B, stream);
+  plan->rgb8_src = nullptr;
+  return rc;
 }
 
 extern "C" int pb200_forward_nchw_f32(pb200_plan* plan, const float* x_nchw, void* workspace,

@@ -34,6 +34,8 @@ namespace {
 
 // epilogue warps: 4 TMEM lane quarters x (kEpiWarps / 4) channel groups; threads = producer warp + MMA warp + epilogue
 constexpr int stem_threads(int epi_warps) { return 64 + 32 * epi_warps; }
+constexpr int kU8Producers = 3;  // U8 kernels: warp 0 and the two warps behind the epilogue warps convert row-pairs (640 threads x 96 registers; 672 do not launch)
+constexpr int stem_threads_u8(int epi_warps) { return stem_threads(epi_warps) + 32 * (kU8Producers - 1); }
 constexpr int kRowBytes = 2112;           // (256 + 8) px * 4 ch * 2 B
 constexpr int kPairBytes = 2 * kRowBytes; // 4224
 // TMEM accumulator stages of 128 columns (power of two).  Four stages (all 512 columns) measured the same as two (0.1123 vs
@@ -55,6 +57,10 @@ __host__ __device__ constexpr int smem_bias(bool x2) { return smem_xchg(x2) + 2 
 __host__ __device__ constexpr int smem_total(bool x2) { return smem_bias(x2) + 64 * 4 + 128; }       // + alignment slack
 
 struct StemPoolParams {
+  // U8 kernels: the stem reads the tight uint8 [B][H][256][3] batch itself (rgb8 != null, frames unused)
+  const uint8_t* rgb8;
+  int bgr;                  // U8: source pixels are B, G, R (scripts/streaming.py:69 reverses them)
+  int H;                    // U8: image rows
   const uint8_t* frames;
   const uint8_t* wimg;
   const float* bias;
@@ -63,7 +69,16 @@ struct StemPoolParams {
   long long frame_bytes, out_img_bytes;
 };
 
-template <int kEpiWarps, bool X2>
+// U8 = the ingest step fused into the producer (RGB uint8 batches, the BASELINE workload): warp 0 loads the image rows
+// itself -- a lane takes 16 pixels = 48 contiguous bytes, the warp one frame row-PAIR per pass --, converts them to the
+// frames encoding (bf16 k, or fp16 k * 2^-12: both exact, bit-identical to csrc/frames.cu::ingest_kernel), writes them
+// into the ring slot and arrives on the slot's barrier.  The 141 MB frames tensor is neither written nor read and the
+// ingest launch disappears.  The ring's left / right margins are zeroed once, margin ROWS are written as zeros.
+// MEASURED (r02, bs 256, tools/gpu/r02_i.sh): bit-identical, 2-3 % faster than ingest + forward under the power cap (1.14
+// vs 1.18 ms) but 8-12 % slower at full clocks (1.11-1.16 vs 1.03 ms) in every variant tried (one / three converting
+// warps; 16-pixel lanes with conflicted stores, with a shuffle transpose, 2-pixel chunks without either): the pooling
+// epilogue already bounds this kernel and the conversion competes with it.  Hence opt-in (pb200_forward_rgb8).
+template <int kEpiWarps, bool X2, bool U8 = false>
 __device__ __forceinline__ void stem_pool_body(const StemPoolParams& p) {
   constexpr int kCh = 64 / (kEpiWarps / 4);  // channels per epilogue thread
   extern __shared__ uint8_t smem_raw[];
@@ -103,6 +118,16 @@ __device__ __forceinline__ void stem_pool_body(const StemPoolParams& p) {
     tmem_relinquish();
   }
   if (threadIdx.x >= 64 && threadIdx.x < 128) s_bias[threadIdx.x - 64] = __ldg(p.bias + threadIdx.x - 64);
+  if constexpr (U8) {
+    // margins of every ring slot (4 pixels = 32 bytes left and right of both rows): zero for the CTA's lifetime (the
+    // converting warps write the pixel area only)
+    for (int i = threadIdx.x; i < kRing * 2 * 2 * 2; i += blockDim.x) {
+      const int slot = i >> 3, r = (i >> 2) & 1, side = (i >> 1) & 1, h = i & 1;
+      *reinterpret_cast<uint4*>(s_ring + slot * kPairBytes + r * kRowBytes + (side ? kRowBytes - 32 : 0) + h * 16) =
+          make_uint4(0, 0, 0, 0);
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -116,10 +141,11 @@ __device__ __forceinline__ void stem_pool_body(const StemPoolParams& p) {
   // leading iteration (k0 = p0 - 1) whose only product is conv row 2k+1 (the carried "previous odd row").
   // Conv rows 2k, 2k+1 read frame rows 4k .. 4k+8, i.e. frame row-pairs 2k .. 2k+4; iteration k releases pairs
   // 2k and 2k+1.  Per unit the ring therefore sees 2*n_it + 3 pairs.
-  if (warp == 0) {
+  constexpr int kFirstExtra = 2 + kEpiWarps;  // U8: warps kFirstExtra.. are producers 1..kU8Producers-1
+  if (warp == 0 || (U8 && warp >= kFirstExtra)) {
     // ================================ producer ====================================
     // whole warp runs the loop (warp-uniform operands); one elected lane issues the copies
-    if (elect_one()) {
+    if (warp == 0 && elect_one()) {
       mbar_expect_tx(&w_bar, (X2 ? 4 : 2) * kStemWimgBytes);
       bulk_load_1d(s_w, p.wimg, kStemWimgBytes, &w_bar);
       bulk_load_1d(s_w + kSmemW2, p.wimg, kStemWimgBytes, &w_bar);
@@ -129,6 +155,135 @@ __device__ __forceinline__ void stem_pool_body(const StemPoolParams& p) {
       }
     }
     uint32_t G = 0;
+    if constexpr (U8) {
+      // ---- fused ingest: kU8Producers warps, warp pi converts the row-pairs G = pi, pi + 3, ... ----
+      // (ONE warp could not keep up: ~1400 cycles of dependent work per pair against the ~800 the kernel spends on one)
+      const int pi = warp == 0 ? 0 : warp - kFirstExtra + 1;
+      const int lrow = lane >> 4;   // row of the pair this lane converts
+      const int lx = lane & 15;     // its 16-pixel group
+      struct Pos {                  // a row-pair of the CTA's work list
+        int u, g, n_pairs, y0;      // unit, pair of the unit, pairs of the unit, image row of the unit's first frame row
+        uint32_t G;                 // running pair count (ring slot / phase)
+        const uint8_t* img;
+      };
+      auto unit_pos = [&](int u, uint32_t G) {
+        Pos q;
+        q.u = u;
+        q.g = 0;
+        q.n_pairs = 0;
+        q.y0 = 0;
+        q.G = G;
+        q.img = p.rgb8;
+        if (u < p.num_units) {
+          const int n = u / p.bands_per_img;
+          const int band = u - n * p.bands_per_img;
+          const int k0 = band == 0 ? 0 : band * p.PB - 1;
+          q.n_pairs = 2 * (p.PB + (band == 0 ? 0 : 1)) + 3;
+          q.y0 = 4 * k0 - kFrameMarginTop;
+          q.img = p.rgb8 + static_cast<long long>(n) * p.H * (256 * 3);
+        }
+        return q;
+      };
+      auto step = [&](Pos& q, int n) {
+        for (int k = 0; k < n && q.u < p.num_units; ++k) {
+          ++q.G;
+          if (++q.g == q.n_pairs) q = unit_pos(q.u + gridDim.x, q.G);
+        }
+      };
+      // Lane -> row lrow of the pair, and in it the 2-pixel chunks c = lx + 16 j (j = 0..7): for every j the 16 lanes of a
+      // row write 256 contiguous bytes of the slot (conflict-free stores without any shuffle; both were tried: a lane owning
+      // 16 consecutive pixels stores with 32-way bank conflicts, and transposing through shuffles loads the pipe this
+      // kernel's epilogue is bound by).  A chunk's 6 source bytes start at 6 c: 4-byte aligned for even c, 2 mod 4 for odd c,
+      // and the parity of c is the lane's -- so every lane issues ONE aligned 32-bit and ONE 16-bit load per chunk.
+      const int odd = lx & 1;
+      auto load_pair = [&](const Pos& q, uint32_t (&v)[8][2]) {
+#pragma unroll
+        for (int jj = 0; jj < 8; ++jj) v[jj][0] = v[jj][1] = 0u;
+        if (q.u < p.num_units) {
+          const int y = q.y0 + 2 * q.g + lrow;
+          if (y >= 0 && y < p.H) {
+            const uint8_t* row = q.img + static_cast<long long>(y) * (256 * 3) + 6 * lx;
+#pragma unroll
+            for (int jj = 0; jj < 8; ++jj) {
+              const uint8_t* b = row + 96 * jj;
+              v[jj][0] = __ldg(reinterpret_cast<const uint32_t*>(b + (odd ? 2 : 0)));
+              v[jj][1] = __ldg(reinterpret_cast<const unsigned short*>(b + (odd ? 0 : 4)));
+            }
+          }
+        }
+      };
+      constexpr int kAhead = 2;     // pairs of THIS warp in flight (6 of the CTA)
+      uint32_t buf[kAhead][8][2];
+      Pos ld = unit_pos(blockIdx.x, 0);
+      step(ld, pi);
+      Pos cv = ld;                  // the pair being converted
+#pragma unroll
+      for (int i = 0; i < kAhead; ++i) {
+        load_pair(ld, buf[i]);
+        step(ld, kU8Producers);
+      }
+      while (cv.u < p.num_units) {
+        {
+          const uint32_t slot = cv.G % kRing, ph = (cv.G / kRing) & 1u;
+          uint32_t cur[8][2];
+#pragma unroll
+          for (int jj = 0; jj < 8; ++jj) {
+            cur[jj][0] = buf[0][jj][0];
+            cur[jj][1] = buf[0][jj][1];
+          }
+#pragma unroll
+          for (int i = 0; i + 1 < kAhead; ++i)
+#pragma unroll
+            for (int jj = 0; jj < 8; ++jj) {
+              buf[i][jj][0] = buf[i + 1][jj][0];
+              buf[i][jj][1] = buf[i + 1][jj][1];
+            }
+          load_pair(ld, buf[kAhead - 1]);  // this warp's pair kAhead further on: in flight while this one is converted
+          step(ld, kU8Producers);
+          mbar_wait(&empty_bar[slot], ph ^ 1u);
+          tc_fence_after();  // the MMAs that read this slot (async proxy) are complete
+          uint4* dst = reinterpret_cast<uint4*>(s_ring + slot * kPairBytes + lrow * kRowBytes + kFrameMarginLeft * 8) + lx;
+          // Exact uint8 -> frames encoding at full instruction rate (I2F runs on a quarter-rate pipe):
+          //   bf16: as_float(0x4B000000 | k) - 2^23 = float(k) exactly; two of them -> cvt.rn.bf16x2 (exact: k < 256)
+          //   fp16: as_half2(0x6400 | k) = 1024 + k; one HFMA2 x * 2^-12 - 0.25 = k * 2^-12 exactly
+#pragma unroll
+          for (int jj = 0; jj < 8; ++jj) {
+            // bytes r0 g0 b0 r1 | g1 b1 of the chunk
+            const uint32_t w0 = odd ? (cur[jj][1] | (cur[jj][0] << 16)) : cur[jj][0];
+            const uint32_t w1 = odd ? (cur[jj][0] >> 16) : cur[jj][1];
+            uint32_t o[4];
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+              // pixel h: bytes 3h, 3h+1, 3h+2 of (w0, w1); selectors 0..3 pick from w0, 4..7 from w1
+              const int b0 = 3 * h;
+              const int sr = p.bgr ? b0 + 2 : b0, sg = b0 + 1, sb = p.bgr ? b0 : b0 + 2;
+              auto byte_of = [&](int sel) -> uint32_t { return __byte_perm(w0, w1, 0x4440 | sel) & 0xffu; };
+              if constexpr (X2) {
+                const uint32_t rg = 0x64006400u | byte_of(sr) | (byte_of(sg) << 16);
+                const uint32_t bz = 0x64006400u | byte_of(sb);
+                const __half2 sc = __float2half2_rn(kF16RgbScale), off = __float2half2_rn(-1024.0f * kF16RgbScale);
+                const __half2 vrg = __hfma2(*reinterpret_cast<const __half2*>(&rg), sc, off);
+                const __half2 vbz = __hfma2(*reinterpret_cast<const __half2*>(&bz), sc, off);
+                o[2 * h] = *reinterpret_cast<const uint32_t*>(&vrg);
+                o[2 * h + 1] = *reinterpret_cast<const uint32_t*>(&vbz);
+              } else {
+                const float fr = __uint_as_float(0x4B000000u | byte_of(sr)) - 8388608.0f;
+                const float fg = __uint_as_float(0x4B000000u | byte_of(sg)) - 8388608.0f;
+                const float fb = __uint_as_float(0x4B000000u | byte_of(sb)) - 8388608.0f;
+                o[2 * h] = pack_bf16x2(fr, fg);
+                o[2 * h + 1] = pack_bf16x2(fb, 0.f);
+              }
+            }
+            dst[16 * jj] = make_uint4(o[0], o[1], o[2], o[3]);
+          }
+          // generic-proxy writes -> visible to the tensor core's (async proxy) operand reads, then the slot is full
+          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&full_bar[slot]);
+        }
+        step(cv, kU8Producers);
+      }
+    } else
     for (int u = blockIdx.x; u < p.num_units; u += gridDim.x) {
       const int n = u / p.bands_per_img;
       const int band = u - n * p.bands_per_img;
@@ -207,7 +362,7 @@ __device__ __forceinline__ void stem_pool_body(const StemPoolParams& p) {
       __syncwarp();
       G += 2 * n_it + 3;
     }
-  } else {
+  } else if (warp < kFirstExtra) {
     // ================================ epilogue ====================================
     // 16 warps: warp -> (TMEM lane quarter q, channel quarter cq).  Thread = conv column x 16 channels.
     // Per iteration: both conv rows of the pair come out of TMEM, the vertical 3-max (with the carried odd
@@ -347,6 +502,8 @@ __device__ __forceinline__ void stem_pool_body(const StemPoolParams& p) {
 __global__ void __maxnreg__(96) stem_pool_kernel16(const StemPoolParams p) { stem_pool_body<16, false>(p); }
 __global__ void __launch_bounds__(stem_threads(8), 1) stem_pool_kernel8(const StemPoolParams p) { stem_pool_body<8, false>(p); }
 __global__ void __maxnreg__(96) stem_pool_x2_kernel16(const StemPoolParams p) { stem_pool_body<16, true>(p); }
+__global__ void __maxnreg__(96) stem_pool_u8_kernel16(const StemPoolParams p) { stem_pool_body<16, false, true>(p); }
+__global__ void __maxnreg__(96) stem_pool_u8_x2_kernel16(const StemPoolParams p) { stem_pool_body<16, true, true>(p); }
 
 }  // namespace
 
@@ -357,19 +514,25 @@ int stem_pool_init() {
   PB_CUDA(cudaFuncSetAttribute(stem_pool_kernel16, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_total(false)));
   PB_CUDA(cudaFuncSetAttribute(stem_pool_kernel8, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_total(false)));
   PB_CUDA(cudaFuncSetAttribute(stem_pool_x2_kernel16, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_total(true)));
+  PB_CUDA(cudaFuncSetAttribute(stem_pool_u8_kernel16, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_total(false)));
+  PB_CUDA(cudaFuncSetAttribute(stem_pool_u8_x2_kernel16, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_total(true)));
   done[dev] = true;
   return PB200_OK;
 }
 
 int launch_stem_pool(const void* frames, const void* wimg, const float* bias, void* out_p8, int B, int H,
-                     int W, cudaStream_t st, int x2) {
+                     int W, cudaStream_t st, int x2, const void* rgb8, int bgr) {
   PB_CHECK(W == 256 && H % 4 == 0 && H >= 8, "stem_pool: needs W = 256 and H %% 4 == 0 (got %dx%d)", H, W);
+  PB_CHECK(rgb8 == nullptr || (reinterpret_cast<uintptr_t>(rgb8) & 15) == 0, "stem_pool: the uint8 batch must be 16-byte aligned");
   if (B == 0) return PB200_OK;
   const int Hpool = H / 4;
   // pooled rows per band: the largest power of two that still gives every SM ~2 units
   int PB = 16;
   while (PB > 1 && (Hpool % PB != 0 || static_cast<long long>(B) * (Hpool / PB) < 2LL * num_sms())) PB >>= 1;
   StemPoolParams p;
+  p.rgb8 = static_cast<const uint8_t*>(rgb8);
+  p.bgr = bgr;
+  p.H = H;
   p.frames = static_cast<const uint8_t*>(frames);
   p.wimg = static_cast<const uint8_t*>(wimg);
   p.bias = bias;
@@ -383,14 +546,16 @@ int launch_stem_pool(const void* frames, const void* wimg, const float* bias, vo
   const int grid = p.num_units < num_sms() ? p.num_units : num_sms();
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(grid);
-  const bool wide = !x2 && getenv("PB200_STEM_EPI8") != nullptr;
-  cfg.blockDim = dim3(stem_threads(wide ? 8 : 16));
+  const bool wide = !x2 && rgb8 == nullptr && getenv("PB200_STEM_EPI8") != nullptr;
+  cfg.blockDim = dim3(rgb8 != nullptr ? stem_threads_u8(16) : stem_threads(wide ? 8 : 16));
   cfg.dynamicSmemBytes = smem_total(x2 != 0);
   cfg.stream = st;
   cudaLaunchAttribute attr[1];
   cfg.attrs = attr;
   cfg.numAttrs = pdl_launch_attrs(attr);
-  if (x2) PB_CUDA(cudaLaunchKernelEx(&cfg, stem_pool_x2_kernel16, p));
+  if (rgb8 != nullptr && x2) PB_CUDA(cudaLaunchKernelEx(&cfg, stem_pool_u8_x2_kernel16, p));
+  else if (rgb8 != nullptr) PB_CUDA(cudaLaunchKernelEx(&cfg, stem_pool_u8_kernel16, p));
+  else if (x2) PB_CUDA(cudaLaunchKernelEx(&cfg, stem_pool_x2_kernel16, p));
   else if (wide) PB_CUDA(cudaLaunchKernelEx(&cfg, stem_pool_kernel8, p));
   else PB_CUDA(cudaLaunchKernelEx(&cfg, stem_pool_kernel16, p));
   return PB200_OK;

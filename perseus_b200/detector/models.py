@@ -17,6 +17,8 @@ from __future__ import annotations
 
 import ctypes
 
+import os
+
 import torch
 from torch import nn
 from torchvision import models as tv_models
@@ -329,12 +331,46 @@ class KeypointCNN(nn.Module):
             )
         return out_norm, out_px
 
+    def fused_rgb8_ok(self, rgb_u8: torch.Tensor, ingest_kwargs: dict | None = None) -> bool:
+        """True when `forward_rgb8` applies: a tight uint8 (B, H, W, 3) cuda batch of the model's size on an RGB model in a
+        16-bit tcgen05 mode, no crop and nothing but `bgr` asked of the ingest step."""
+        kw = ingest_kwargs or {}
+        return (self.num_channels == 3 and self.precision in ("bf16", "fp16x2") and rgb_u8.is_cuda
+                and rgb_u8.dtype == torch.uint8 and rgb_u8.dim() == 4 and tuple(rgb_u8.shape[1:]) == (self.H, self.W, 3)
+                and rgb_u8.is_contiguous() and rgb_u8.data_ptr() % 16 == 0
+                # (the depth arguments act on the depth channel only, which an RGB model does not have)
+                and set(kw) <= {"bgr", "depth_divisor", "clip", "cube_scale", "jitter"})
+
+    def forward_rgb8(self, rgb_u8: torch.Tensor, bgr: bool = False, plan: "_Plan | None" = None,
+                     out_norm: torch.Tensor | None = None, out_px: torch.Tensor | None = None):
+        """uint8 (B, H, W, 3) batch -> (norm (B,2K), pixels (B,K,2)) with the ingest step fused into the stem kernel
+        (pb200_forward_rgb8): bit-identical to ingest() + forward_ingested(), without the frames tensor and its launch."""
+        B = rgb_u8.shape[0]
+        plan = plan if plan is not None else self._plan(rgb_u8.device, B)
+        if out_norm is None:
+            out_norm = torch.empty((B, 2 * self.n_keypoints), dtype=torch.float32, device=rgb_u8.device)
+        if out_px is None:
+            out_px = torch.empty((B, self.n_keypoints, 2), dtype=torch.float32, device=rgb_u8.device)
+        with torch.cuda.device(rgb_u8.device):
+            _lib.check(
+                plan.lib.pb200_forward_rgb8(
+                    plan.handle, rgb_u8.data_ptr(), int(bool(bgr)), plan.workspace.data_ptr(), out_norm.data_ptr(),
+                    out_px.data_ptr(), B, _lib.current_stream_ptr(),
+                )
+            )
+        return out_norm, out_px
+
     def forward_frames(self, rgb_u8: torch.Tensor, depth: torch.Tensor | None = None, **ingest_kwargs):
         """Ingest + forward + decode: uint8 frames -> pixel keypoints (B, K, 2) float32."""
         if self.num_channels == 4 and depth is None:
             raise ValueError("forward_frames: an RGBD model needs a depth tensor")
         if self.num_channels == 3:
             depth = None
+        # Opt-in (PB200_FUSED_INGEST=1): measured r02 at bs 256, the fused stem is 2-3 % FASTER than ingest + forward under the
+        # power cap (1.14 vs 1.18 ms) but 8-12 % slower at full clocks (1.11-1.16 vs 1.03 ms): the conversion work lands on
+        # the SMs whose pooling epilogue already bounds the stem.  It saves the 141 MB frames tensor either way.
+        if os.environ.get("PB200_FUSED_INGEST") is not None and self.fused_rgb8_ok(rgb_u8, ingest_kwargs):
+            return self.forward_rgb8(rgb_u8, bgr=bool(ingest_kwargs.get("bgr", False)))[1]
         frames = self.ingest(rgb_u8, depth, **ingest_kwargs)
         _, px = self.forward_ingested(frames, rgb_u8.shape[0])
         return px

@@ -1,10 +1,28 @@
 #!/bin/bash
+# fused ingest (stem reads uint8): correctness, then A/B against ingest + forward
 mkdir -p gpurun_out
-timeout 600 python -m pytest tests/test_gpu_fp16x2.py tests/test_gpu_factors.py -q -m gpu > gpurun_out/i_tests.log 2>&1; echo "tests exit $?"; tail -3 gpurun_out/i_tests.log
-timeout 300 python tools/profile_ops.py fp16x2 256 3 > gpurun_out/i_ops_fp16x2.json 2> gpurun_out/i_ops.err; python - <<'PY'
-import json
-d = json.load(open("gpurun_out/i_ops_fp16x2.json")); fr = d["ops"]
-g = lambda p: sum(o["ms"] for o in fr if o["op"].startswith(p))
-print("fp16x2: step %.4f sum %.4f | stem %.4f l1 %.4f l2 %.4f l3 %.4f l4 %.4f" % (d["ms_per_step"], d["sum_op_ms"], fr[0]["ms"], g("layer1"), g("layer2"), g("layer3"), g("layer4")))
+timeout 400 python -m pytest tests/test_gpu_fused_ingest.py -q -m gpu -x > gpurun_out/i_tests.log 2>&1; rc=$?; echo "fused tests exit $rc"; tail -6 gpurun_out/i_tests.log
+if [ $rc -ne 0 ]; then exit 0; fi
+python - <<'PY'
+import torch, os, sys
+sys.path.insert(0, os.getcwd())
+from perseus_b200.detector import KeypointCNN
+from perseus_b200.detector.synthetic import random_init_state_dict
+dev = torch.device("cuda", 0)
+for prec in ("bf16", "fp16x2"):
+    m = KeypointCNN(num_channels=3, precision=prec, max_batch=256); m.load_state_dict(random_init_state_dict(3, 8, seed=0)); m.eval().to(dev)
+    g = torch.Generator().manual_seed(0)
+    bufs = [torch.randint(0, 256, (256, 256, 256, 3), dtype=torch.uint8, generator=g).to(dev) for _ in range(4)]  # 201 MB > L2
+    def run(fused, n):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        for i in range(5):
+            (m.forward_rgb8(bufs[i % 4]) if fused else m.forward_ingested(m.ingest(bufs[i % 4], None), 256))
+        torch.cuda.synchronize(); e0.record()
+        for i in range(n):
+            (m.forward_rgb8(bufs[i % 4]) if fused else m.forward_ingested(m.ingest(bufs[i % 4], None), 256))
+        e1.record(); torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / n
+    for rep in range(2):
+        a, b = run(False, 40), run(True, 40)
+        print(f"{prec}: ingest + forward {a:.4f} ms ({256 / a:.1f} k frames/s) | fused {b:.4f} ms ({256 / b:.1f} k frames/s)")
 PY
-timeout 300 python tools/factors_ab.py > gpurun_out/i_factors_ab.json 2> gpurun_out/i_factors_ab.err; cat gpurun_out/i_factors_ab.json; tail -2 gpurun_out/i_factors_ab.err
