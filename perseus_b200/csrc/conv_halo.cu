@@ -48,6 +48,7 @@ struct HaloParams {
   int stage_bytes;            // patch stage size (multiple of 1024)
   int num_kblocks;            // 9 * cblocks + ds_cblocks
   int relu;
+  int reverse;                // walk the pair tiles from the last to the first (L2 reuse across launches: launch_conv_p8)
   const float* bias;
   const void* residual;       // NHWC [B][H][W][Cout] or null
   void* out;
@@ -127,7 +128,8 @@ conv_halo_kernel(const __grid_constant__ UmmaConvMaps maps, const HaloParams p) 
     pdl_wait();  // the activations are the previous kernel's output
     int stage = 0;
     uint32_t phase = 0;
-    for (int pt = pair_id; pt < p.num_pair_tiles; pt += num_pairs) {
+    for (int pti = pair_id; pti < p.num_pair_tiles; pti += num_pairs) {
+      const int pt = p.reverse ? p.num_pair_tiles - 1 - pti : pti;
       const int jp = pt / p.tiles_per_img;
       const int t = pt - jp * p.tiles_per_img;
       int n = 2 * jp + crank;
@@ -161,7 +163,8 @@ conv_halo_kernel(const __grid_constant__ UmmaConvMaps maps, const HaloParams p) 
       uint32_t phase = 0;
       int it = 0;
       if (pair_id < p.num_pair_tiles) mbar_wait(&resb_bar, 0);
-      for (int pt = pair_id; pt < p.num_pair_tiles; pt += num_pairs, ++it) {
+      for (int pti = pair_id; pti < p.num_pair_tiles; pti += num_pairs, ++it) {
+        const int pt = p.reverse ? p.num_pair_tiles - 1 - pti : pti;
         const int t = pt % p.tiles_per_img;
         const int q0 = t * 128;
         const uint32_t pi0 = static_cast<uint32_t>(q0 - (q0 / p.Wp) * p.Wp);  // first A row of tap (0, 0) in the patch
@@ -210,7 +213,8 @@ conv_halo_kernel(const __grid_constant__ UmmaConvMaps maps, const HaloParams p) 
     __nv_bfloat16* out = static_cast<__nv_bfloat16*>(p.out);
     const int col0 = half * kCols;
     int it = 0;
-    for (int pt = pair_id; pt < p.num_pair_tiles; pt += num_pairs, ++it) {
+    for (int pti = pair_id; pti < p.num_pair_tiles; pti += num_pairs, ++it) {
+      const int pt = p.reverse ? p.num_pair_tiles - 1 - pti : pti;
       const int jp = pt / p.tiles_per_img;
       const int t = pt - jp * p.tiles_per_img;
       const int n = 2 * jp + crank;
@@ -295,12 +299,13 @@ bool conv_halo_supported(int B, int H, int W, int Cin, int Cout, int R, int stri
 }
 
 int build_conv_halo(HaloLaunch* L, const void* in, int B, int H, int W, int Cin, const void* wpacked_kt, const float* bias,
-                    const void* residual, void* out, int Cout, int relu, const void* ds_in, int ds_Cin) {
+                    const void* residual, void* out, int Cout, int relu, const void* ds_in, int ds_Cin, int reverse) {
   PB_CHECK(conv_halo_supported(B, H, W, Cin, Cout, 3, 1, 1, ds_in ? ds_Cin : 0), "conv_halo: unsupported shape");
   memset(L, 0, sizeof(*L));
   const int Wp = W + 2;
   HaloParams p = {};
   p.B = B; p.H = H; p.W = W; p.Wp = Wp; p.Cout = Cout;
+  p.reverse = reverse ? 1 : 0;
   p.cblocks = Cin / 64;
   p.ds_cblocks = ds_in ? ds_Cin / 64 : 0;
   p.tiles_per_img = (H * Wp + 127) / 128;

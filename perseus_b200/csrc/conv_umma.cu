@@ -649,6 +649,7 @@ int build_umma_conv(UmmaConvLaunch* L, const void* in, int B, int Hin, int Win, 
   }
   const int Krow = R * R * Cin + (ds_in != nullptr ? ds_Cin : 0);
   p.b_tiled = b_tiled ? 1 : 0;
+  p.reverse = 0;
   p.kb_total = Krow / 64;
   if (b_tiled) {
     PB_CHECK(split != 1 && (L->pair || p.cl == 1), "umma conv: KT-layout weights need the single-CTA or the pair kernel");
@@ -675,6 +676,7 @@ int build_umma_dgrad_s2(UmmaConvLaunch* L, const void* dz, int B, int Ho, int Wo
                                block_n))
     return rc;
   UmmaConvParams& p = L->p;
+  p.reverse = 0;
   L->resb = 0;  // the tap table below re-orders the k columns: the resident-weights walk (columns kb * 64) does not apply
   // forward: z[i] reads x[2i + r - pad].  For x row u = 2a + ph the forward taps are r = ph + pad (mod 2):
   // R = 3: ph = 0 -> r = 1 (i = a); ph = 1 -> r = 0 (i = a + 1), r = 2 (i = a).  R = 1: ph = 0 -> r = 0 (i = a); ph = 1 -> none

@@ -43,6 +43,7 @@ struct UmmaConvParams {
   // were bound by the TMA engine's row rate (rows per k-block x ~2.3 cycles: 192 rows = 452 cycles on layer2 for 256
   // cycles of MMAs), and the weight rows were a third to a half of them.
   int b_tiled;
+  int reverse;     // pair kernel (single conv): walk the work items from the last to the first (L2 reuse across launches)
   int kb_total;    // k-blocks per weight row half (= K / 64), KT layout
   int relu;
   const float* bias;            // [Cout] (folded BN shift)
@@ -138,7 +139,7 @@ struct HaloLaunch {
 };
 bool conv_halo_supported(int B, int H, int W, int Cin, int Cout, int R, int stride, int pad, int ds_Cin);
 int build_conv_halo(HaloLaunch* L, const void* in, int B, int H, int W, int Cin, const void* wpacked_kt, const float* bias,
-                    const void* residual, void* out, int Cout, int relu, const void* ds_in, int ds_Cin);
+                    const void* residual, void* out, int Cout, int relu, const void* ds_in, int ds_Cin, int reverse = 0);
 int launch_conv_halo(const HaloLaunch& L, cudaStream_t st);
 
 }  // namespace pb200

@@ -66,7 +66,7 @@ __device__ __forceinline__ void pair_body(const UmmaConvMaps* __restrict__ mapsv
   // item -> (conv c, work item st of that conv)
   auto decode = [&](int item, int& c, int& st) {
     c = 0;
-    st = item;
+    st = (!CHAIN && p.reverse) ? p.num_super - 1 - item : item;
     if constexpr (CHAIN) {
       while (st >= pv[c].num_super) {
         st -= pv[c].num_super;

@@ -583,8 +583,15 @@ static int prepare(pb200_plan* pl, const void* frames, void* ws, int B) {
     const void* ds_in = op.ds_buf >= 0 ? buf_ptr(pl, frames, ws, op.ds_buf) : nullptr;
     const ConvSpec* d = c.ds_conv >= 0 ? &pl->convs[c.ds_conv] : nullptr;
     if (pl->use_halo && conv_halo_supported(B, c.Hin, c.Win, c.Cin, c.Cout, c.R, c.stride, c.pad, d ? d->Cin : 0)) {
+      // alternate the walk direction launch by launch (launch_conv_p8): the halo conv that follows a forward-walking halo
+      // conv starts at the end of the tensor
+      const size_t idx = static_cast<size_t>(&op - pl->ops.data());
+      const bool prev_fwd_halo = idx > 0 && pl->ops[idx - 1].kind == OP_CONV && !pl->convs[pl->ops[idx - 1].conv].stem &&
+                                 pl->halo[pl->ops[idx - 1].conv].grid > 0 && !pl->ops[idx - 1].reverse;
+      const int rev = prev_fwd_halo && getenv("PB200_P8_NOREVERSE") == nullptr ? 1 : 0;
+      const_cast<Op&>(op).reverse = rev;
       int rc = build_conv_halo(&pl->halo[op.conv], in, B, c.Hin, c.Win, c.Cin, pl->arena + c.w_off, bias, res, out, c.Cout,
-                               op.relu, d ? ds_in : nullptr, d ? d->Cin : 0);
+                               op.relu, d ? ds_in : nullptr, d ? d->Cin : 0, rev);
       if (rc) {
         pl->cache_B = -1;
         return rc;
@@ -601,6 +608,12 @@ static int prepare(pb200_plan* pl, const void* frames, void* ws, int B) {
     if (rc) {
       pl->cache_B = -1;
       return rc;
+    }
+    // layer2's first conv reads the 134 MB hand-over tensor that layer1's last conv has just written front to back: a
+    // backward walk starts in the part L2 still holds (csrc/conv_p8.cu: launch_conv_p8).  PB200_P8_NOREVERSE=1: forward.
+    if (L->pair && !L->resb && op.in_buf == BUF_R0 && getenv("PB200_P8_NOREVERSE") == nullptr) {
+      const size_t idx = static_cast<size_t>(&op - pl->ops.data());
+      if (idx > 0 && pl->ops[idx - 1].kind == OP_CONV_P8 && pl->ops[idx - 1].reverse == 0) L->p.reverse = 1;
     }
   }
   // chains: maximal runs of consecutive convs on the pair<256> kernel whose outputs are whole images per M-super
