@@ -80,7 +80,7 @@ int launch_conv_p8(const void* in_p8, const void* wimg, const float* bias, const
 // rgb8 != null: the ingest step fused into the stem -- it reads the tight, 16-byte aligned uint8 [B][H][256][3] batch
 // itself (bgr: source pixels are B, G, R) and `frames` is not touched
 int launch_stem_pool(const void* frames, const void* wimg, const float* bias, void* out_p8, int B, int H,
-                     int W, cudaStream_t st, int x2 = 0, const void* rgb8 = nullptr, int bgr = 0);
+                     int W, cudaStream_t st, int x2 = 0, const void* rgb8 = nullptr, int bgr = 0, int reverse = 0);
 
 // 3x3 stride-2 pad-1 max pooling, NHWC (C % 8 == 0 for bf16, % 4 for fp32).
 int launch_maxpool(const void* in, void* out, int B, int H, int W, int C, bool bf16, cudaStream_t st);

@@ -160,6 +160,9 @@ static void build_graph(pb200_plan* pl) {
     {
       Op op;
       op.kind = OP_STEM_POOL; op.name = "conv1+bn1+relu+maxpool"; op.conv = 0; op.in_buf = BUF_FRAMES; op.out_buf = BUF_P8A;
+      // the ingest kernel writes the frames front to back: the stem starts at their end (what L2 still holds), and from
+      // here on every launch of layers 1-2 walks the other way than the one before it (PB200_P8_NOREVERSE=1: all forward)
+      op.reverse = getenv("PB200_P8_NOREVERSE") == nullptr ? 1 : 0;
       pl->ops.push_back(op);
     }
     const int seq_in[4] = {BUF_P8A, BUF_P8B, BUF_P8C, BUF_P8B};
@@ -174,8 +177,8 @@ static void build_graph(pb200_plan* pl) {
       op.kind = OP_CONV_P8; op.name = pre + cn + "+bn" + ((i % 2) ? "+add+relu" : "+relu");
       op.conv = static_cast<int>(pl->convs.size()) - 1;
       op.in_buf = seq_in[i]; op.out_buf = seq_out[i]; op.res_buf = seq_res[i]; op.relu = 1; op.out_nhwc = (i == 3);
-      // the stem walks forward, so conv 0 starts at the end, conv 1 at the front, ... (PB200_P8_NOREVERSE=1: all forward)
-      op.reverse = (i % 2 == 0 && getenv("PB200_P8_NOREVERSE") == nullptr) ? 1 : 0;
+      // the stem walks backward, so conv 0 starts at the front, conv 1 at the end, ... (PB200_P8_NOREVERSE=1: all forward)
+      op.reverse = (i % 2 == 1 && getenv("PB200_P8_NOREVERSE") == nullptr) ? 1 : 0;
       pl->ops.push_back(op);
     }
     first_layer = 1;
@@ -586,9 +589,9 @@ static int prepare(pb200_plan* pl, const void* frames, void* ws, int B) {
       // alternate the walk direction launch by launch (launch_conv_p8): the halo conv that follows a forward-walking halo
       // conv starts at the end of the tensor
       const size_t idx = static_cast<size_t>(&op - pl->ops.data());
-      const bool prev_fwd_halo = idx > 0 && pl->ops[idx - 1].kind == OP_CONV && !pl->convs[pl->ops[idx - 1].conv].stem &&
-                                 pl->halo[pl->ops[idx - 1].conv].grid > 0 && !pl->ops[idx - 1].reverse;
-      const int rev = prev_fwd_halo && getenv("PB200_P8_NOREVERSE") == nullptr ? 1 : 0;
+      const bool prev_fwd = idx > 0 && (pl->ops[idx - 1].kind == OP_CONV || pl->ops[idx - 1].kind == OP_CONV_P8) &&
+                            !pl->ops[idx - 1].reverse;
+      const int rev = prev_fwd && getenv("PB200_P8_NOREVERSE") == nullptr ? 1 : 0;
       const_cast<Op&>(op).reverse = rev;
       int rc = build_conv_halo(&pl->halo[op.conv], in, B, c.Hin, c.Win, c.Cin, pl->arena + c.w_off, bias, res, out, c.Cout,
                                op.relu, d ? ds_in : nullptr, d ? d->Cin : 0, rev);
@@ -614,6 +617,7 @@ static int prepare(pb200_plan* pl, const void* frames, void* ws, int B) {
     if (L->pair && !L->resb && op.in_buf == BUF_R0 && getenv("PB200_P8_NOREVERSE") == nullptr) {
       const size_t idx = static_cast<size_t>(&op - pl->ops.data());
       if (idx > 0 && pl->ops[idx - 1].kind == OP_CONV_P8 && pl->ops[idx - 1].reverse == 0) L->p.reverse = 1;
+      const_cast<Op&>(op).reverse = L->p.reverse;  // (the halo conv behind it alternates against this)
     }
   }
   // chains: maximal runs of consecutive convs on the pair<256> kernel whose outputs are whole images per M-super
@@ -709,7 +713,7 @@ static int run_op(pb200_plan* pl, const Op& op, const void* frames, void* ws, fl
                               pl->rgb8_src == nullptr ? nullptr
                                                       : static_cast<const uint8_t*>(pl->rgb8_src) +
                                                             static_cast<size_t>(n0) * pl->H * pl->W * 3,
-                              pl->rgb8_bgr);
+                              pl->rgb8_bgr, op.reverse);
     }
     case OP_CONV_P8: {
       const ConvSpec& c = pl->convs[op.conv];

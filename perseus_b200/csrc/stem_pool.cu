@@ -60,6 +60,7 @@ struct StemPoolParams {
   // U8 kernels: the stem reads the tight uint8 [B][H][256][3] batch itself (rgb8 != null, frames unused)
   const uint8_t* rgb8;
   int bgr;                  // U8: source pixels are B, G, R (scripts/streaming.py:69 reverses them)
+  int reverse;              // walk the units from the last to the first (L2 reuse across launches: launch_conv_p8)
   int H;                    // U8: image rows
   const uint8_t* frames;
   const uint8_t* wimg;
@@ -175,8 +176,9 @@ __device__ __forceinline__ void stem_pool_body(const StemPoolParams& p) {
         q.G = G;
         q.img = p.rgb8;
         if (u < p.num_units) {
-          const int n = u / p.bands_per_img;
-          const int band = u - n * p.bands_per_img;
+          const int ur = p.reverse ? p.num_units - 1 - u : u;  // q.u counts positions of the walk, ur is the unit there
+          const int n = ur / p.bands_per_img;
+          const int band = ur - n * p.bands_per_img;
           const int k0 = band == 0 ? 0 : band * p.PB - 1;
           q.n_pairs = 2 * (p.PB + (band == 0 ? 0 : 1)) + 3;
           q.y0 = 4 * k0 - kFrameMarginTop;
@@ -284,7 +286,8 @@ __device__ __forceinline__ void stem_pool_body(const StemPoolParams& p) {
         step(cv, kU8Producers);
       }
     } else
-    for (int u = blockIdx.x; u < p.num_units; u += gridDim.x) {
+    for (int ui = blockIdx.x; ui < p.num_units; ui += gridDim.x) {
+      const int u = p.reverse ? p.num_units - 1 - ui : ui;
       const int n = u / p.bands_per_img;
       const int band = u - n * p.bands_per_img;
       const int k0 = band == 0 ? 0 : band * p.PB - 1;
@@ -319,7 +322,8 @@ __device__ __forceinline__ void stem_pool_body(const StemPoolParams& p) {
     mbar_wait(&w_bar, 0);
     uint32_t G = 0;
     int it = 0;
-    for (int u = blockIdx.x; u < p.num_units; u += gridDim.x) {
+    for (int ui = blockIdx.x; ui < p.num_units; ui += gridDim.x) {
+      const int u = p.reverse ? p.num_units - 1 - ui : ui;
       const int band = u % p.bands_per_img;
       const int n_it = p.PB + (band == 0 ? 0 : 1);
       for (uint32_t j = 0; j < 3; ++j) mbar_wait(&full_bar[(G + j) % kRing], ((G + j) / kRing) & 1u);
@@ -378,7 +382,8 @@ __device__ __forceinline__ void stem_pool_body(const StemPoolParams& p) {
     const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + cq * kCh;
     int it = 0;
     uint32_t fin = 0;
-    for (int u = blockIdx.x; u < p.num_units; u += gridDim.x) {
+    for (int ui = blockIdx.x; ui < p.num_units; ui += gridDim.x) {
+      const int u = p.reverse ? p.num_units - 1 - ui : ui;
       const int n = u / p.bands_per_img;
       const int band = u - n * p.bands_per_img;
       const int k0 = band == 0 ? 0 : band * p.PB - 1;
@@ -521,7 +526,7 @@ int stem_pool_init() {
 }
 
 int launch_stem_pool(const void* frames, const void* wimg, const float* bias, void* out_p8, int B, int H,
-                     int W, cudaStream_t st, int x2, const void* rgb8, int bgr) {
+                     int W, cudaStream_t st, int x2, const void* rgb8, int bgr, int reverse) {
   PB_CHECK(W == 256 && H % 4 == 0 && H >= 8, "stem_pool: needs W = 256 and H %% 4 == 0 (got %dx%d)", H, W);
   PB_CHECK(rgb8 == nullptr || (reinterpret_cast<uintptr_t>(rgb8) & 15) == 0, "stem_pool: the uint8 batch must be 16-byte aligned");
   if (B == 0) return PB200_OK;
@@ -532,6 +537,7 @@ int launch_stem_pool(const void* frames, const void* wimg, const float* bias, vo
   StemPoolParams p;
   p.rgb8 = static_cast<const uint8_t*>(rgb8);
   p.bgr = bgr;
+  p.reverse = reverse ? 1 : 0;
   p.H = H;
   p.frames = static_cast<const uint8_t*>(frames);
   p.wimg = static_cast<const uint8_t*>(wimg);

@@ -1,7 +1,7 @@
 #!/bin/bash
 # layer1 tile walk direction alternating launch by launch (L2 reuse across launches): tests, then A/B
 mkdir -p gpurun_out
-timeout 400 python -m pytest tests/test_gpu_detector.py tests/test_gpu_fp16x2.py -q -m gpu -x -k "conv_p8 or batch or forward" > gpurun_out/w_tests.log 2>&1; rc=$?; echo "tests exit $rc"; tail -3 gpurun_out/w_tests.log
+timeout 400 python -m pytest tests/test_gpu_detector.py tests/test_gpu_fp16x2.py tests/test_gpu_fused_ingest.py -q -m gpu -x -k "conv_p8 or batch or forward or fused or stem" > gpurun_out/w_tests.log 2>&1; rc=$?; echo "tests exit $rc"; tail -3 gpurun_out/w_tests.log
 if [ $rc -ne 0 ]; then exit 0; fi
 for rep in 1 2; do
 for prec in bf16 fp16x2; do
